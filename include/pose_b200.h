@@ -1,0 +1,222 @@
+/*
+ * pose_b200.h - C ABI of the B200-native pose-descriptor evaluation path.
+ *
+ * This is the drop-in boundary for ONE hot path of mingliangfu/3DPoseEstimation:
+ * descriptor forward -> brute-force kNN against the template DB -> pose-error
+ * reduction.  Every entry point names the reference interface it replaces
+ * (paths relative to the reference checkout).  Plain pointers and sizes only;
+ * no C++ / torch / OpenCV / Caffe types cross this boundary.
+ *
+ * Conventions
+ *   - every function returns PE_OK (0) or a PE_ERR_* code and never throws;
+ *     pe_last_error() returns a thread-local, human-readable message.
+ *   - "host" pointers are ordinary (ideally pinned) host memory owned by the
+ *     caller; "_dev" variants take device pointers on the handle's device and
+ *     are asynchronous on the handle's stream (call pe_*_sync to wait).
+ *   - patches are S x 64 x 64 x C float32, interleaved HWC, exactly the
+ *     memory of reference `Sample.data` (include/datatypes.h:25-27);
+ *     labels are S x 8 float32 {class, qx,qy,qz,qw, tx,ty,tz}
+ *     (src/datasetmanager.cpp:283-289, include/datatypes.h:34-48).
+ *   - descriptor matrices are row-major float32, rows x D, the memory of the
+ *     reference's `Mat descs(S, D, CV_32F)` (src/networkevaluator.cpp:23).
+ *   - there is no CPU fallback: without a CUDA device every compute entry
+ *     point fails with PE_ERR_CUDA.
+ */
+#ifndef POSE_B200_H
+#define POSE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PE_API __attribute__((visibility("default")))
+
+enum {
+    PE_OK = 0,
+    PE_ERR_INVALID = 1,     /* bad argument / shape mismatch                  */
+    PE_ERR_CUDA = 2,        /* CUDA runtime error or no device                */
+    PE_ERR_PARSE = 3,       /* prototxt could not be parsed / unsupported net */
+    PE_ERR_IO = 4,          /* file could not be read / written               */
+    PE_ERR_UNSUPPORTED = 5, /* valid request outside the implemented family   */
+    PE_ERR_NCCL = 6         /* NCCL error                                     */
+};
+
+/* activation kinds reported by pe_net_layer_info (Caffe layer types ReLU/ELU/PReLU) */
+enum { PE_ACT_NONE = 0, PE_ACT_RELU = 1, PE_ACT_ELU = 2, PE_ACT_PRELU = 3 };
+
+typedef struct pe_net pe_net;   /* replaces caffe::Net<float> in TEST phase          */
+typedef struct pe_db pe_db;     /* replaces cv::DescriptorMatcher("BruteForce")+add  */
+typedef struct pe_comm pe_comm; /* NCCL communicator for the row-sharded DB (new)    */
+
+/* ---------------------------------------------------------------- misc --- */
+PE_API int pe_version(void);
+PE_API const char* pe_last_error(void);
+PE_API int pe_device_count(int* n);
+/* number of kernels launched by this library in this process (bench "gpu_launches") */
+PE_API int64_t pe_launch_count(void);
+
+/* pinned host memory + raw device memory helpers (harness plumbing) */
+PE_API int pe_host_alloc(void** p, size_t bytes);
+PE_API int pe_host_free(void* p);
+PE_API int pe_dev_alloc(int device, void** p, size_t bytes);
+PE_API int pe_dev_free(int device, void* p);
+PE_API int pe_memcpy_h2d(int device, void* dst, const void* src, size_t bytes);
+PE_API int pe_memcpy_d2h(int device, void* dst, const void* src, size_t bytes);
+PE_API int pe_dev_memset(int device, void* dst, int value, size_t bytes);
+
+/* CUDA-event timers on a handle's stream (so kernel time is measured on the
+ * stream the kernels are launched on) */
+typedef struct pe_timer pe_timer;
+PE_API int pe_timer_create(int device, pe_timer** t);
+PE_API int pe_timer_start_net(pe_timer* t, pe_net* net);
+PE_API int pe_timer_stop_net(pe_timer* t, pe_net* net);
+PE_API int pe_timer_start_db(pe_timer* t, pe_db* db);
+PE_API int pe_timer_stop_db(pe_timer* t, pe_db* db);
+PE_API int pe_timer_elapsed_ms(pe_timer* t, float* ms); /* synchronises on stop */
+PE_API void pe_timer_destroy(pe_timer* t);
+
+/* ----------------------------------------------------------------- net --- */
+/* Replaces `caffe::Net<float> testCNN(network_path + net_name + ".prototxt", caffe::TEST)`
+ * (src/networksolver.cpp:286).  Parses the TEST-phase subset of a Caffe prototxt
+ * (layers Convolution, Pooling, ReLU, ELU, PReLU, InnerProduct, Slice, Concat,
+ * Silence; `include {phase: TRAIN}` layers are skipped) and accepts the
+ * conv-pool-act-conv-pool-act-FC... family of network/manifold*.prototxt. */
+PE_API int pe_net_create_from_prototxt(const char* path, int device, pe_net** out);
+PE_API int pe_net_create_from_string(const char* prototxt_text, int device, pe_net** out);
+/* Built-in table of the seven reference variants by file stem, e.g.
+ * "manifold_rgbdnor_16" (network/manifold_rgbdnor_16.prototxt). */
+PE_API int pe_net_create_named(const char* variant, int device, pe_net** out);
+PE_API void pe_net_destroy(pe_net* net);
+
+/* input blob N,C,H,W and output dim D: what computeDescriptors reads from
+ * CNN.input_blobs()[0] / output_blobs()[0] (src/networkevaluator.cpp:11-19) */
+PE_API int pe_net_info(const pe_net* net, int* batch, int* channels, int* height, int* width,
+                       int* desc_dim);
+/* channel-select list fed to conv1 (Slice/Concat/Silence, network/manifold_rgb_16.prototxt:6-33) */
+PE_API int pe_net_selected_channels(const pe_net* net, int* sel, int cap, int* n_sel);
+/* human-readable, one TEST-phase layer per line: "conv conv1 16 8", "pool pool1 2 2",
+ * "act relu1 PReLU", "fc ip1 256" ... */
+PE_API int pe_net_describe(const pe_net* net, char* buf, size_t cap);
+
+/* learnable blobs in Caffe order (per layer: weight, bias; PReLU: slope).
+ * Replaces CopyTrainedLayersFrom / ShareTrainedLayersWith (src/networksolver.cpp:307,377). */
+PE_API int pe_net_num_blobs(const pe_net* net, int* n);
+PE_API int pe_net_blob_info(const pe_net* net, int blob, char* name, size_t name_cap,
+                            int64_t* count);
+PE_API int pe_net_set_blob(pe_net* net, int blob, const float* host, int64_t count);
+PE_API int pe_net_get_blob(const pe_net* net, int blob, float* host, int64_t count);
+/* mode 0: Caffe fillers of the prototxts (xavier weights, constant-0 bias, PReLU 0.25);
+ * mode 1: parity fill (xavier weights, bias U(-0.1,0.1), PReLU slopes U(-0.25,0.5)). */
+PE_API int pe_net_fill(pe_net* net, uint64_t seed, int mode);
+/* flat little-endian weight file: magic "PEW1", n_blobs, then per blob {int64 count, floats} */
+PE_API int pe_net_save_weights(const pe_net* net, const char* path);
+PE_API int pe_net_load_weights(pe_net* net, const char* path);
+
+/* networkEvaluator::computeDescriptors (src/networkevaluator.cpp:9-54).
+ * patches: n x H x W x patch_channels (HWC); out: n x D.  patch_channels must
+ * equal the net's input channels (the contract noted at :37-40). */
+PE_API int pe_compute_descriptors(pe_net* net, const float* patches_hwc, int64_t n,
+                                  int patch_channels, float* out_desc);
+PE_API int pe_compute_descriptors_dev(pe_net* net, const float* d_patches_hwc, int64_t n,
+                                      int patch_channels, float* d_out_desc);
+PE_API int pe_net_sync(pe_net* net);
+
+/* deterministic synthetic patches generated on the device (bench / full-size
+ * property tests).  Sample i belongs to object i / poses_per_object. */
+PE_API int pe_synth_patches_dev(pe_net* net, uint64_t seed, int64_t first_index, int64_t n,
+                                int channels, int poses_per_object, float* d_patches_hwc);
+/* labels {class, unit quaternion, 0,0,0} for rows [first, first+n) (host output) */
+PE_API int pe_synth_labels(uint64_t seed, int64_t first_index, int64_t n, int poses_per_object,
+                           float* labels);
+
+/* sign-binarisation of float descriptors to packed bits (bit j of word w is
+ * desc[32*w+j] > 0).  New behaviour: the reference never thresholds bin_ip2
+ * (SURVEY 0); defined in SURVEY 7. */
+PE_API int pe_binarize(pe_net* net, const float* desc, int64_t n, int dim, uint32_t* bits);
+
+/* ------------------------------------------------------------------ db --- */
+/* Replaces `matcher = DescriptorMatcher::create("BruteForce"); matcher->add(DBfeats)`
+ * (src/networkevaluator.cpp:193-196, 263-266; src/networksolver.cpp:466-467).
+ * desc: t_local x dim rows of this shard; row_offset: global index of row 0
+ * (0 when unsharded).  labels_all: t_total x 8 labels of ALL templates (may be
+ * NULL when only pe_knn is used).  poses_per_object = template_set[0].size(). */
+PE_API int pe_db_create(const float* desc, int64_t t_local, int dim, int64_t row_offset,
+                        const float* labels_all, int64_t t_total, int poses_per_object,
+                        int device, pe_db** out);
+PE_API int pe_db_create_dev(const float* d_desc, int64_t t_local, int dim, int64_t row_offset,
+                            const float* labels_all_host, int64_t t_total, int poses_per_object,
+                            int device, pe_db** out);
+/* Hamming DB over packed codes (words_per_code u32 each). */
+PE_API int pe_db_create_hamming(const uint32_t* codes, int64_t t_local, int words_per_code,
+                                int64_t row_offset, const float* labels_all, int64_t t_total,
+                                int poses_per_object, int device, pe_db** out);
+PE_API void pe_db_destroy(pe_db* db);
+PE_API int pe_db_info(const pe_db* db, int64_t* t_local, int64_t* t_total, int* dim,
+                      int* is_hamming);
+PE_API int pe_db_sync(pe_db* db);
+
+/* matcher->knnMatch(queries, matches, k) (src/networkevaluator.cpp:197,267;
+ * src/networksolver.cpp:472): L2 distance sqrt(sum (q-t)^2), k smallest
+ * ascending, ties -> lower index.  out_idx / out_dist are nq x k (global
+ * template indices; -1 / +inf pad when t_total < k). */
+PE_API int pe_knn(pe_db* db, const float* queries, int64_t nq, int k, int32_t* out_idx,
+                  float* out_dist);
+PE_API int pe_knn_dev(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* d_out_idx,
+                      float* d_out_dist);
+/* Hamming variant; distances are bit counts. */
+PE_API int pe_knn_hamming(pe_db* db, const uint32_t* qcodes, int64_t nq, int k, int32_t* out_idx,
+                          int32_t* out_dist);
+PE_API int pe_knn_hamming_dev(pe_db* db, const uint32_t* d_qcodes, int64_t nq, int k,
+                              int32_t* d_out_idx, int32_t* d_out_dist);
+
+/* body of networkEvaluator::computeHistogram after knnMatch
+ * (src/networkevaluator.cpp:269-355).  knn_idx: nq x k global template indices,
+ * q_labels: nq x 8.  rot_inv[class] as `input.rotInv` (config.ini:10).
+ * out: n_bins + 2 floats = normalised bins, mean angle, median angle. */
+PE_API int pe_histogram(pe_db* db, const int32_t* knn_idx, const float* q_labels, int64_t nq,
+                        int k, const int* rot_inv, int n_rot, const float* bins, int n_bins,
+                        float* out);
+/* body of computeConfusionMatrix after knnMatch (src/networkevaluator.cpp:199-245).
+ * class_to_local[c] = local_index[models[c]] (:215-216); out: n_local x n_local,
+ * row-normalised by nr_test_poses. */
+PE_API int pe_confusion(pe_db* db, const int32_t* knn_idx, const float* q_labels, int64_t nq,
+                        int k, const int* class_to_local, int n_classes, int n_local,
+                        int nr_test_poses, float* out);
+/* body of networkSolver::computeKNN after knnMatch with k = 3
+ * (src/networksolver.cpp:474-504).  out: nq x 4 ints {nnObj, nnPose, otherObj,
+ * otherPose}, out_len[q] in {2,4} = maxSimKNNTmpl[obj][pose].size(). */
+PE_API int pe_knn_bootstrap(pe_db* db, const int32_t* knn3_idx, int64_t nq, int nr_query_poses,
+                            int32_t* out, int32_t* out_len);
+/* networkEvaluator::computeKNNAccuracy (src/networkevaluator.cpp:153-175):
+ * max_sim_tmpl0[q] = maxSimTmpl[obj][pose][0]; returns the two percentages. */
+PE_API int pe_knn_accuracy(pe_db* db, const int32_t* max_sim_tmpl0, const int32_t* bootstrap,
+                           int64_t nq, int nr_query_poses, float* intra_pct, float* inter_pct);
+
+/* ----------------------------------------------------------- multi-GPU --- */
+/* One process per GPU.  Rank 0 calls pe_comm_unique_id, the harness ships the
+ * 128 bytes to all ranks, every rank calls pe_comm_create.  New: the reference
+ * is single-process. */
+PE_API int pe_comm_unique_id(char* id128);
+PE_API int pe_comm_create(int rank, int world, const char* id128, int device, pe_comm** out);
+PE_API void pe_comm_destroy(pe_comm* comm);
+PE_API int pe_comm_info(const pe_comm* comm, int* rank, int* world);
+/* all-gather n floats per rank (host buffers; descriptor exchange) */
+PE_API int pe_comm_allgather_f32(pe_comm* comm, const float* send, int64_t n, float* recv);
+PE_API int pe_comm_allreduce_sum_f64(pe_comm* comm, double* buf, int64_t n);
+/* kNN against a row-sharded DB: every rank passes the same nq queries, scans
+ * its shard, candidates are all-gathered over NVLink and merged identically on
+ * every rank (ties -> lower global index). */
+PE_API int pe_knn_sharded(pe_db* db, pe_comm* comm, const float* queries, int64_t nq, int k,
+                          int32_t* out_idx, float* out_dist);
+PE_API int pe_knn_sharded_dev(pe_db* db, pe_comm* comm, const float* d_queries, int64_t nq, int k,
+                              int32_t* d_out_idx, float* d_out_dist);
+PE_API int pe_knn_hamming_sharded(pe_db* db, pe_comm* comm, const uint32_t* qcodes, int64_t nq,
+                                  int k, int32_t* out_idx, int32_t* out_dist);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* POSE_B200_H */

@@ -1,0 +1,192 @@
+"""Pins the CPU oracle against the committed golden vectors (torch / cv2 / scipy / second
+transcription; tests/golden/make_golden.py).  CPU only."""
+import os
+
+import numpy as np
+import pytest
+
+from tests import netdefs
+from tests.golden import make_golden as mg
+
+
+def _rowscale_err(a, b):
+    """max |a-b| relative to the per-row max-abs of b (the acceptance form used for descriptors)"""
+    scale = np.abs(b).max(axis=-1, keepdims=True) + 1e-30
+    return float((np.abs(a - b) / scale).max())
+
+
+@pytest.mark.parametrize("vi,name", list(enumerate(netdefs.VARIANTS)))
+def test_forward_matches_torch(po, synth, golden, vi, name):
+    net = po.parse_prototxt(netdefs.prototxt(name))
+    sel, dim = netdefs.EXPECTED[name]
+    assert net.sel == sel and net.desc_dim == dim
+    assert net.blob_names == netdefs.expected_blob_names(name)
+    blobs = synth.make_blobs(net.blob_names, net.blob_shapes, synth.BASE_SEED + vi, mode=1)
+    patches = synth.make_patches(synth.BASE_SEED, 100 * vi, 3, net.channels, 2)
+    d = po.OracleNet(net, blobs).forward(patches)
+    assert d.shape == golden[f"fwd32_{name}"].shape
+    # fp32 tolerance of BASELINE.json: 1e-4 relative; the oracle sits two orders below it
+    assert _rowscale_err(d, golden[f"fwd32_{name}"]) < 5e-6
+    assert _rowscale_err(d.astype(np.float64), golden[f"fwd64_{name}"]) < 5e-6
+
+
+def test_forward_stages_match_torch(po, synth, golden):
+    vi = list(netdefs.VARIANTS).index("manifold_rgbdnor_16")
+    net = po.parse_prototxt(netdefs.prototxt("manifold_rgbdnor_16"))
+    blobs = synth.make_blobs(net.blob_names, net.blob_shapes, synth.BASE_SEED + vi, mode=1)
+    patch = synth.make_patches(synth.BASE_SEED, 100 * vi, 1, 7, 2)[0]
+    on = po.OracleNet(net, blobs)
+    s2 = on.stage(patch, 2)
+    s5 = on.stage(patch, 5)
+    assert s2.size == 16 * 29 * 29 and s5.size == 7 * 13 * 13  # ceil-mode pooling: 57->29, 25->13
+    np.testing.assert_allclose(s2, golden["stage2_pool1act"].reshape(-1), rtol=0, atol=5e-6)
+    np.testing.assert_allclose(s5, golden["stage5_pool2act"].reshape(-1), rtol=0, atol=5e-6)
+
+
+def test_forward_partial_and_threads(po, synth):
+    """batch boundaries / thread count must not change results (src/networkevaluator.cpp:26-30)"""
+    net = po.parse_prototxt(netdefs.prototxt("manifold_rgbd_16"))
+    on = po.OracleNet(net, synth.make_blobs(net.blob_names, net.blob_shapes, 5, mode=1))
+    x = synth.make_patches(3, 0, 5, 7, 2)
+    a = on.forward(x, threads=1)
+    b = on.forward(x, threads=3)
+    c = np.concatenate([on.forward(x[:2]), on.forward(x[2:])])
+    assert np.array_equal(a, b) and np.array_equal(a, c)
+    assert on.forward(x[:0]).shape == (0, 16)
+
+
+@pytest.mark.parametrize("dim", [16, 3, 64])
+def test_knn_l2_matches_cv2(po, synth, golden, dim):
+    q, t = mg.knn_problem(synth.BASE_SEED + dim, 64, 512, dim)
+    t[100] = t[7]
+    t[300] = t[7]
+    q[5] = t[7]
+    idx, dist, gap = po.knn_l2(q, t, 5, want_gap=True)
+    gi, gd = golden[f"knn_idx_{dim}"], golden[f"knn_dist_{dim}"]
+    np.testing.assert_allclose(dist, gd, rtol=2e-6, atol=1e-7)
+    # query 5 equals templates 7/100/300: the tie must come out lowest index first, as cv2 does
+    assert list(idx[5, :3]) == [7, 100, 300] == list(gi[5, :3])
+    assert list(dist[5, :3]) == [0, 0, 0]
+    mism = idx != gi
+    # any other disagreement may only be a swap of numerically equal distances
+    assert np.all(np.abs(dist[mism] - gd[mism]) <= 2e-6 * np.abs(gd[mism]))
+    assert mism.sum() <= 2
+    assert np.all(np.diff(dist, axis=1) >= 0) and np.all(gap >= 0)
+
+
+def test_knn_l2_edge_cases(po):
+    rng = np.random.default_rng(0)
+    t = rng.standard_normal((3, 16)).astype(np.float32)
+    q = rng.standard_normal((2, 16)).astype(np.float32)
+    idx, dist = po.knn_l2(q, t, 5)            # fewer templates than k -> -1 / inf padding
+    assert np.all(idx[:, 3:] == -1) and np.all(np.isinf(dist[:, 3:]))
+    assert sorted(idx[0, :3]) == [0, 1, 2]
+    idx0, _ = po.knn_l2(q[:0], t, 1)
+    assert idx0.shape == (0, 1)
+    d = po.l2_distance(q[0], t[1])
+    ref = np.sqrt(((q[0].astype(np.float64) - t[1]) ** 2).sum())
+    assert abs(d - ref) < 1e-6 * ref
+
+
+def test_hamming_matches_cv2(po, synth, golden):
+    codes_t = (synth.uniform01(synth.BASE_SEED, 50, 512 * 4) * 2 ** 24).astype(np.uint32).reshape(512, 4)
+    codes_t = codes_t * np.uint32(257) ^ (codes_t >> np.uint32(3))
+    codes_q = codes_t[(np.arange(64) * 5) % 512] ^ (np.uint32(1) << (np.arange(64, dtype=np.uint32) % 32))[:, None]
+    idx, dist = po.knn_hamming(codes_q, codes_t, 5)
+    assert np.array_equal(dist, golden["ham_dist"])          # bit counts: exact
+    assert np.array_equal(idx[:, 0], golden["ham_idx"][:, 0])
+    assert np.all(dist[:, 0] == 4)   # one flipped bit in each of the 4 words
+    # equal bit counts: ours are lowest-index-first; verify against a brute-force stable argsort
+    full = np.array([[bin(int(a) ^ int(b)).count("1") for a, b in zip(qr, tr)] for qr in codes_q for tr in codes_t])
+    full = full.sum(1).reshape(64, 512)
+    ref = np.argsort(full, axis=1, kind="stable")[:, :5]
+    assert np.array_equal(idx, ref)
+
+
+def test_binarize(po):
+    d = np.array([[0.5, -0.1, 0.0, 2.0] + [0.0] * 28 + [1.0] + [-1.0] * 31], np.float32)
+    bits = po.binarize(d)
+    assert bits.shape == (1, 2) and bits[0, 0] == 0b1001 and bits[0, 1] == 1
+
+
+def test_angles_match_scipy(po, synth, golden):
+    qa = synth.random_quaternions(synth.BASE_SEED, 60, 256)
+    qb = synth.random_quaternions(synth.BASE_SEED, 61, 256)
+    qb[:8] = qa[:8]
+    qb[8:16] = -qa[8:16]
+    ang = np.array([po.angular_distance(a, b) for a, b in zip(qa, qb)])
+    r22 = np.array([po.rot22(a) for a in qa])
+    # acos is ill-conditioned at |dot| -> 1: fp32 resolves angles to ~sqrt(eps)
+    np.testing.assert_allclose(ang, golden["angles_rad"], rtol=0, atol=1.5e-3)
+    big = golden["angles_rad"] > 0.1
+    np.testing.assert_allclose(ang[big], golden["angles_rad"][big], rtol=2e-5, atol=0)
+    np.testing.assert_allclose(r22, golden["rot22"], rtol=0, atol=1e-6)
+
+
+@pytest.mark.parametrize("k", [1, 3, 5])
+def test_histogram_confusion_match_second_transcription(po, synth, golden, k):
+    n_obj, nr_t, nr_q, dim = 6, 40, 15, 16
+    q, t, ql, tl = mg.eval_problem(synth.BASE_SEED, n_obj, nr_t, nr_q, dim)
+    rot_inv = np.array([0, 0, 1, 0, 2, 0], np.int32)
+    bins = np.array([-1, 0, 10, 20, 40, 180], np.float32)
+    idx, _ = po.knn_l2(q, t, k)
+    assert np.array_equal(idx, golden[f"eval_idx_k{k}"])      # oracle matcher == cv2 on this set
+    h = po.histogram(idx, ql, tl, nr_t, rot_inv, bins)
+    np.testing.assert_allclose(h[:6], golden[f"eval_hist_k{k}"][:6], rtol=0, atol=1e-7)
+    np.testing.assert_allclose(h[6:], golden[f"eval_hist_k{k}"][6:], rtol=0, atol=1e-3)
+    c2l = np.arange(n_obj, dtype=np.int32)[::-1].copy()
+    cm = po.confusion(idx, ql, tl, c2l, n_obj, nr_q)
+    assert np.array_equal(cm, golden[f"eval_conf_k{k}"])
+    np.testing.assert_allclose(cm.sum(1), 1.0, atol=1e-6)
+
+
+def test_bootstrap_matches_second_transcription(po, golden):
+    out, ln = po.knn_bootstrap(golden["eval_idx_k3"], 15, 40)
+    assert np.array_equal(out, golden["eval_boot"]) and np.array_equal(ln, golden["eval_boot_len"])
+    assert set(np.unique(ln)) <= {2, 4}
+    intra, inter = po.knn_accuracy(out[:, 1], out, 15)
+    assert intra == 100.0 and 0 <= inter <= 100
+
+
+def test_histogram_edge_cases(po, synth):
+    tl = synth.make_labels(1, 2, 4)
+    ql = tl[[0, 5]].copy()
+    bins = np.array([-1, 0, 10, 20, 40, 180], np.float32)
+    # query 0 matched to itself (exact, angle 0); query 1 matched only to the other class
+    idx = np.array([[0], [1]], np.int32)
+    h, err = po.histogram(idx, ql, tl, 4, np.zeros(2, np.int32), bins, want_err=True)
+    # a float32 quaternion is unit only to ~1e-7, and acos near 1 amplifies that to ~0.04 degrees
+    assert 0.0 <= err[0] < 0.1 and err[1] == -1.0
+    np.testing.assert_allclose(h[:6], [0.5] * 6, atol=1e-7)
+    assert h[6] == np.float32(err[0] / np.float32(2)) and h[7] == err[0]
+    # nobody matched -> empty diff vector -> median defined as NaN
+    h2 = po.histogram(np.array([[4], [1]], np.int32), ql, tl, 4, np.zeros(2, np.int32), bins)
+    assert h2[0] == 1.0 and np.isnan(h2[7])
+
+
+def test_merge_topk_equals_unsharded(po):
+    rng = np.random.default_rng(3)
+    t = rng.standard_normal((301, 16)).astype(np.float32)
+    t[200] = t[10]                                           # cross-shard tie
+    q = np.concatenate([rng.standard_normal((9, 16)).astype(np.float32), t[10:11]])
+    full_i, full_d = po.knn_l2(q, t, 4)
+    bounds = [0, 100, 150, 301]
+    ci, cd = [], []
+    for a, b in zip(bounds[:-1], bounds[1:]):
+        i, d = po.knn_l2(q, t[a:b], 4)
+        ci.append(np.where(i >= 0, i + a, -1))
+        cd.append(d)
+    mi, md = po.merge_topk(np.stack(ci), np.stack(cd))
+    assert np.array_equal(mi, full_i) and np.array_equal(md, full_d)
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/network"), reason="reference checkout not present")
+@pytest.mark.parametrize("name", list(netdefs.VARIANTS))
+def test_emitted_prototxt_equals_reference_file(po, name):
+    """the prototxts this repo emits describe the same TEST-phase nets as the reference's files"""
+    a = po.parse_prototxt(netdefs.prototxt(name))
+    b = po.parse_prototxt(open(f"/root/reference/network/{name}.prototxt").read())
+    assert (a.batch, a.channels, a.height, a.width) == (b.batch, b.channels, b.height, b.width)
+    assert a.sel == b.sel and a.desc_dim == b.desc_dim
+    assert a.describe() == b.describe()
+    assert a.blob_names == b.blob_names and a.blob_shapes == b.blob_shapes
