@@ -1,0 +1,482 @@
+"""ctypes binding of libpose_b200.so - the C ABI declared in include/pose_b200.h.
+
+This is plumbing for tests/ and bench.py (numpy arrays in, numpy arrays out).  It never imports
+the CPU oracle and there is no fallback: if the CUDA library is missing or no device is present,
+calls raise PoseError.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpose_b200.so")
+HOST_LIB_PATH = os.path.join(_HERE, "libpose_b200_host.so")
+
+PE_OK, PE_ERR_INVALID, PE_ERR_CUDA, PE_ERR_PARSE, PE_ERR_IO, PE_ERR_UNSUPPORTED, PE_ERR_NCCL = range(7)
+ACT_NAMES = {0: "none", 1: "ReLU", 2: "ELU", 3: "PReLU"}
+
+
+class PoseError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"pose_b200 error {code}: {msg}")
+        self.code = code
+
+
+def build(force: bool = False) -> str:
+    """Compile the CUDA library in-tree with the committed Makefile (nvcc, sm_100a)."""
+    if force or not os.path.exists(LIB_PATH):
+        subprocess.check_call(["make", "-C", os.path.join(_HERE, "csrc"), "-s", "-j8"] + (["-B"] if force else []))
+    return LIB_PATH
+
+
+_lib = None
+fp, ip, u32p, vp = C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_uint32), C.c_void_p
+
+# name -> (restype, argtypes); every symbol include/pose_b200.h declares
+SIGNATURES = {
+    "pe_version": (C.c_int, []),
+    "pe_last_error": (C.c_char_p, []),
+    "pe_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+    "pe_launch_count": (C.c_int64, []),
+    "pe_host_alloc": (C.c_int, [C.POINTER(vp), C.c_size_t]),
+    "pe_host_free": (C.c_int, [vp]),
+    "pe_dev_alloc": (C.c_int, [C.c_int, C.POINTER(vp), C.c_size_t]),
+    "pe_dev_free": (C.c_int, [C.c_int, vp]),
+    "pe_memcpy_h2d": (C.c_int, [C.c_int, vp, vp, C.c_size_t]),
+    "pe_memcpy_d2h": (C.c_int, [C.c_int, vp, vp, C.c_size_t]),
+    "pe_dev_memset": (C.c_int, [C.c_int, vp, C.c_int, C.c_size_t]),
+    "pe_timer_create": (C.c_int, [C.c_int, C.POINTER(vp)]),
+    "pe_timer_start_net": (C.c_int, [vp, vp]),
+    "pe_timer_stop_net": (C.c_int, [vp, vp]),
+    "pe_timer_start_db": (C.c_int, [vp, vp]),
+    "pe_timer_stop_db": (C.c_int, [vp, vp]),
+    "pe_timer_elapsed_ms": (C.c_int, [vp, fp]),
+    "pe_timer_destroy": (None, [vp]),
+    "pe_net_create_from_prototxt": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(vp)]),
+    "pe_net_create_from_string": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(vp)]),
+    "pe_net_create_named": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(vp)]),
+    "pe_net_destroy": (None, [vp]),
+    "pe_net_info": (C.c_int, [vp] + [C.POINTER(C.c_int)] * 5),
+    "pe_net_selected_channels": (C.c_int, [vp, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_int)]),
+    "pe_net_describe": (C.c_int, [vp, C.c_char_p, C.c_size_t]),
+    "pe_net_num_blobs": (C.c_int, [vp, C.POINTER(C.c_int)]),
+    "pe_net_blob_info": (C.c_int, [vp, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_int64)]),
+    "pe_net_set_blob": (C.c_int, [vp, C.c_int, fp, C.c_int64]),
+    "pe_net_get_blob": (C.c_int, [vp, C.c_int, fp, C.c_int64]),
+    "pe_net_fill": (C.c_int, [vp, C.c_uint64, C.c_int]),
+    "pe_net_save_weights": (C.c_int, [vp, C.c_char_p]),
+    "pe_net_load_weights": (C.c_int, [vp, C.c_char_p]),
+    "pe_compute_descriptors": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp]),
+    "pe_compute_descriptors_dev": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp]),
+    "pe_net_sync": (C.c_int, [vp]),
+    "pe_synth_patches_dev": (C.c_int, [vp, C.c_uint64, C.c_int64, C.c_int64, C.c_int, C.c_int, vp]),
+    "pe_synth_labels": (C.c_int, [C.c_uint64, C.c_int64, C.c_int64, C.c_int, fp]),
+    "pe_binarize": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp]),
+    "pe_binarize_dev": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp]),
+    "pe_db_create": (C.c_int, [vp, C.c_int64, C.c_int, C.c_int64, vp, C.c_int64, C.c_int, C.c_int, C.POINTER(vp)]),
+    "pe_db_create_dev": (C.c_int, [vp, C.c_int64, C.c_int, C.c_int64, vp, C.c_int64, C.c_int, C.c_int, C.POINTER(vp)]),
+    "pe_db_create_hamming": (C.c_int, [vp, C.c_int64, C.c_int, C.c_int64, vp, C.c_int64, C.c_int, C.c_int, C.POINTER(vp)]),
+    "pe_db_destroy": (None, [vp]),
+    "pe_db_info": (C.c_int, [vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "pe_db_sync": (C.c_int, [vp]),
+    "pe_knn": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "pe_knn_dev": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "pe_knn_hamming": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "pe_knn_hamming_dev": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "pe_histogram": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, C.c_int, vp, C.c_int, vp]),
+    "pe_histogram_dev": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, C.c_int, vp, C.c_int, vp]),
+    "pe_confusion": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp]),
+    "pe_knn_bootstrap": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "pe_knn_accuracy": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, fp, fp]),
+    "pe_comm_unique_id": (C.c_int, [C.c_char_p]),
+    "pe_comm_create": (C.c_int, [C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(vp)]),
+    "pe_comm_destroy": (None, [vp]),
+    "pe_comm_info": (C.c_int, [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "pe_comm_allgather_f32": (C.c_int, [vp, vp, C.c_int64, vp]),
+    "pe_comm_allreduce_sum_f64": (C.c_int, [vp, vp, C.c_int64]),
+    "pe_knn_sharded": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "pe_knn_sharded_dev": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "pe_knn_hamming_sharded": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
+}
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise PoseError(PE_ERR_CUDA, f"{LIB_PATH} is not built (run __graft_entry__.build()); there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(code: int):
+    if code != PE_OK:
+        raise PoseError(code, lib().pe_last_error().decode(errors="replace"))
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(vp)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def device_count() -> int:
+    n = C.c_int(0)
+    code = lib().pe_device_count(C.byref(n))
+    return n.value if code == PE_OK else 0
+
+
+def launch_count() -> int:
+    return int(lib().pe_launch_count())
+
+
+class DeviceArray:
+    """raw device allocation with a numpy-like shape/dtype tag"""
+
+    def __init__(self, shape, dtype=np.float32, device=0):
+        self.shape = tuple(int(s) for s in np.atleast_1d(shape))
+        self.dtype = np.dtype(dtype)
+        self.device = device
+        self.nbytes = int(np.prod(self.shape)) * self.dtype.itemsize
+        p = vp()
+        check(lib().pe_dev_alloc(device, C.byref(p), max(self.nbytes, 16)))
+        self.ptr = p.value
+
+    @classmethod
+    def from_host(cls, a, device=0):
+        a = np.ascontiguousarray(a)
+        d = cls(a.shape, a.dtype, device)
+        if a.nbytes:
+            check(lib().pe_memcpy_h2d(device, d.ptr, a.ctypes.data_as(vp), a.nbytes))
+        return d
+
+    def to_host(self):
+        out = np.empty(self.shape, self.dtype)
+        if self.nbytes:
+            check(lib().pe_memcpy_d2h(self.device, out.ctypes.data_as(vp), self.ptr, self.nbytes))
+        return out
+
+    def offset(self, n_elems):
+        return self.ptr + int(n_elems) * self.dtype.itemsize
+
+    def free(self):
+        if self.ptr:
+            lib().pe_dev_free(self.device, self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def pinned_empty(shape, dtype=np.float32):
+    """numpy array over cudaMallocHost memory (kept alive by the returned array's base)"""
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) * dtype.itemsize
+    p = vp()
+    check(lib().pe_host_alloc(C.byref(p), max(n, 16)))
+    buf = (C.c_char * max(n, 16)).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    _PINNED[id(buf)] = (buf, p.value)
+    return arr
+
+
+_PINNED: dict = {}
+
+
+class Timer:
+    def __init__(self, device=0):
+        p = vp()
+        check(lib().pe_timer_create(device, C.byref(p)))
+        self.h = p.value
+
+    def start(self, obj):
+        check((lib().pe_timer_start_net if isinstance(obj, Net) else lib().pe_timer_start_db)(self.h, obj.h))
+
+    def stop(self, obj):
+        check((lib().pe_timer_stop_net if isinstance(obj, Net) else lib().pe_timer_stop_db)(self.h, obj.h))
+
+    def elapsed_ms(self) -> float:
+        ms = C.c_float()
+        check(lib().pe_timer_elapsed_ms(self.h, C.byref(ms)))
+        return ms.value
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().pe_timer_destroy(self.h)
+            self.h = None
+
+
+class Net:
+    """replaces caffe::Net<float>(prototxt, caffe::TEST) (reference src/networksolver.cpp:286)"""
+
+    def __init__(self, text: str | None = None, path: str | None = None, named: str | None = None, device: int = 0):
+        h = vp()
+        if named is not None:
+            check(lib().pe_net_create_named(named.encode(), device, C.byref(h)))
+        elif path is not None:
+            check(lib().pe_net_create_from_prototxt(path.encode(), device, C.byref(h)))
+        else:
+            check(lib().pe_net_create_from_string(text.encode(), device, C.byref(h)))
+        self.h = h.value
+        self.device = device
+        v = [C.c_int() for _ in range(5)]
+        check(lib().pe_net_info(self.h, *[C.byref(x) for x in v]))
+        self.batch, self.channels, self.height, self.width, self.desc_dim = [x.value for x in v]
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().pe_net_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    @property
+    def sel(self):
+        buf = (C.c_int * 16)()
+        n = C.c_int()
+        check(lib().pe_net_selected_channels(self.h, buf, 16, C.byref(n)))
+        return [buf[i] for i in range(n.value)]
+
+    def describe(self) -> str:
+        buf = C.create_string_buffer(8192)
+        check(lib().pe_net_describe(self.h, buf, len(buf)))
+        return buf.value.decode()
+
+    def blob_info(self):
+        n = C.c_int()
+        check(lib().pe_net_num_blobs(self.h, C.byref(n)))
+        out = []
+        for b in range(n.value):
+            name = C.create_string_buffer(128)
+            cnt = C.c_int64()
+            check(lib().pe_net_blob_info(self.h, b, name, len(name), C.byref(cnt)))
+            out.append((name.value.decode(), cnt.value))
+        return out
+
+    def set_blobs(self, blobs):
+        for b, arr in enumerate(blobs):
+            a = _f32(arr).reshape(-1)
+            check(lib().pe_net_set_blob(self.h, b, a.ctypes.data_as(fp), a.size))
+
+    def get_blobs(self):
+        out = []
+        for b, (_, cnt) in enumerate(self.blob_info()):
+            a = np.empty(cnt, np.float32)
+            check(lib().pe_net_get_blob(self.h, b, a.ctypes.data_as(fp), cnt))
+            out.append(a)
+        return out
+
+    def fill(self, seed: int, mode: int = 1):
+        check(lib().pe_net_fill(self.h, seed, mode))
+
+    def save_weights(self, path):
+        check(lib().pe_net_save_weights(self.h, str(path).encode()))
+
+    def load_weights(self, path):
+        check(lib().pe_net_load_weights(self.h, str(path).encode()))
+
+    def compute_descriptors(self, patches_hwc: np.ndarray) -> np.ndarray:
+        """networkEvaluator::computeDescriptors: n x H x W x C (HWC) host patches -> n x D"""
+        x = _f32(patches_hwc)
+        n = x.shape[0]
+        c = x.shape[-1] if x.ndim == 4 else self.channels
+        out = np.empty((n, self.desc_dim), np.float32)
+        check(lib().pe_compute_descriptors(self.h, _ptr(x), n, c, _ptr(out)))
+        return out
+
+    def compute_descriptors_dev(self, d_patches, n, d_out, patch_offset=0, out_offset=0):
+        check(lib().pe_compute_descriptors_dev(self.h, d_patches.offset(patch_offset * 4096 * self.channels) if isinstance(d_patches, DeviceArray) else d_patches,
+                                               n, self.channels,
+                                               d_out.offset(out_offset * self.desc_dim) if isinstance(d_out, DeviceArray) else d_out))
+
+    def sync(self):
+        check(lib().pe_net_sync(self.h))
+
+    def synth_patches_dev(self, seed, first, n, poses_per_object, d_out, out_offset=0):
+        ptr = d_out.offset(out_offset * 4096 * self.channels) if isinstance(d_out, DeviceArray) else d_out
+        check(lib().pe_synth_patches_dev(self.h, seed, first, n, self.channels, poses_per_object, ptr))
+
+    def binarize(self, desc: np.ndarray) -> np.ndarray:
+        d = _f32(desc)
+        n, dim = d.shape
+        bits = np.empty((n, (dim + 31) // 32), np.uint32)
+        check(lib().pe_binarize(self.h, _ptr(d), n, dim, _ptr(bits)))
+        return bits
+
+    def binarize_dev(self, d_desc, n, dim, d_bits):
+        check(lib().pe_binarize_dev(self.h, d_desc.ptr, n, dim, d_bits.ptr))
+
+
+def synth_labels(seed, first, n, poses_per_object) -> np.ndarray:
+    out = np.empty((n, 8), np.float32)
+    check(lib().pe_synth_labels(seed, first, n, poses_per_object, out.ctypes.data_as(fp)))
+    return out
+
+
+class TemplateDB:
+    """replaces DescriptorMatcher::create("BruteForce") + add(DBfeats) (src/networkevaluator.cpp:193-196)"""
+
+    def __init__(self, desc=None, labels_all=None, poses_per_object=0, row_offset=0, t_total=None, device=0,
+                 codes=None, d_desc=None, t_local=None, dim=None):
+        h = vp()
+        lab = None if labels_all is None else _f32(labels_all)
+        self.device = device
+        if codes is not None:
+            if isinstance(codes, DeviceArray):
+                tl, words, cptr = codes.shape[0], codes.shape[1], codes.ptr
+            else:
+                codes = np.ascontiguousarray(codes, np.uint32)
+                tl, words, cptr = codes.shape[0], codes.shape[1], _ptr(codes)
+            tt = tl if t_total is None else t_total
+            check(lib().pe_db_create_hamming(cptr, tl, words, row_offset, _ptr(lab), tt, poses_per_object, device, C.byref(h)))
+            self.dim = words
+        elif d_desc is not None:
+            tt = t_local if t_total is None else t_total
+            ptr = d_desc.ptr if isinstance(d_desc, DeviceArray) else d_desc
+            check(lib().pe_db_create_dev(ptr, t_local, dim, row_offset, _ptr(lab), tt, poses_per_object, device, C.byref(h)))
+            self.dim = dim
+        else:
+            d = _f32(desc)
+            tl, dm = d.shape
+            tt = tl if t_total is None else t_total
+            check(lib().pe_db_create(_ptr(d), tl, dm, row_offset, _ptr(lab), tt, poses_per_object, device, C.byref(h)))
+            self.dim = dm
+        self.h = h.value
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().pe_db_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def sync(self):
+        check(lib().pe_db_sync(self.h))
+
+    def knn(self, queries, k):
+        """matcher->knnMatch(queries, matches, k): (idx nq x k, dist nq x k)"""
+        q = _f32(queries)
+        nq = q.shape[0]
+        idx = np.empty((nq, k), np.int32)
+        dist = np.empty((nq, k), np.float32)
+        check(lib().pe_knn(self.h, _ptr(q), nq, k, _ptr(idx), _ptr(dist)))
+        return idx, dist
+
+    def knn_dev(self, d_q, nq, k, d_idx, d_dist):
+        check(lib().pe_knn_dev(self.h, d_q.ptr if isinstance(d_q, DeviceArray) else d_q, nq, k, d_idx.ptr, d_dist.ptr))
+
+    def knn_hamming(self, qcodes, k):
+        q = np.ascontiguousarray(qcodes, np.uint32)
+        nq = q.shape[0]
+        idx = np.empty((nq, k), np.int32)
+        dist = np.empty((nq, k), np.int32)
+        check(lib().pe_knn_hamming(self.h, _ptr(q), nq, k, _ptr(idx), _ptr(dist)))
+        return idx, dist
+
+    def knn_hamming_dev(self, d_q, nq, k, d_idx, d_dist):
+        check(lib().pe_knn_hamming_dev(self.h, d_q.ptr, nq, k, d_idx.ptr, d_dist.ptr))
+
+    def knn_sharded(self, comm, queries, k):
+        q = _f32(queries)
+        nq = q.shape[0]
+        idx = np.empty((nq, k), np.int32)
+        dist = np.empty((nq, k), np.float32)
+        check(lib().pe_knn_sharded(self.h, comm.h if comm else None, _ptr(q), nq, k, _ptr(idx), _ptr(dist)))
+        return idx, dist
+
+    def knn_sharded_dev(self, comm, d_q, nq, k, d_idx, d_dist):
+        check(lib().pe_knn_sharded_dev(self.h, comm.h if comm else None, d_q.ptr if isinstance(d_q, DeviceArray) else d_q,
+                                       nq, k, d_idx.ptr, d_dist.ptr))
+
+    def knn_hamming_sharded(self, comm, qcodes, k):
+        q = np.ascontiguousarray(qcodes, np.uint32)
+        nq = q.shape[0]
+        idx = np.empty((nq, k), np.int32)
+        dist = np.empty((nq, k), np.int32)
+        check(lib().pe_knn_hamming_sharded(self.h, comm.h if comm else None, _ptr(q), nq, k, _ptr(idx), _ptr(dist)))
+        return idx, dist
+
+    def histogram(self, knn_idx, q_labels, rot_inv, bins):
+        """computeHistogram body: n_bins normalised bins + mean + median"""
+        idx, ql = _i32(knn_idx), _f32(q_labels)
+        rot, bn = _i32(rot_inv), _f32(bins)
+        out = np.empty(bn.size + 2, np.float32)
+        check(lib().pe_histogram(self.h, _ptr(idx), _ptr(ql), idx.shape[0], idx.shape[1], _ptr(rot), rot.size, _ptr(bn),
+                                 bn.size, _ptr(out)))
+        return out
+
+    def histogram_dev(self, d_idx, d_qlabels, nq, k, rot_inv, bins):
+        rot, bn = _i32(rot_inv), _f32(bins)
+        out = np.empty(bn.size + 2, np.float32)
+        check(lib().pe_histogram_dev(self.h, d_idx.ptr, d_qlabels.ptr, nq, k, _ptr(rot), rot.size, _ptr(bn), bn.size, _ptr(out)))
+        return out
+
+    def confusion(self, knn_idx, q_labels, class_to_local, n_local, nr_test_poses):
+        idx, ql, c2l = _i32(knn_idx), _f32(q_labels), _i32(class_to_local)
+        out = np.empty((n_local, n_local), np.float32)
+        check(lib().pe_confusion(self.h, _ptr(idx), _ptr(ql), idx.shape[0], idx.shape[1], _ptr(c2l), c2l.size, n_local,
+                                 nr_test_poses, _ptr(out)))
+        return out
+
+    def knn_bootstrap(self, knn3_idx, nr_query_poses):
+        idx = _i32(knn3_idx)
+        nq = idx.shape[0]
+        out = np.empty((nq, 4), np.int32)
+        ln = np.empty(nq, np.int32)
+        check(lib().pe_knn_bootstrap(self.h, _ptr(idx), nq, nr_query_poses, _ptr(out), _ptr(ln)))
+        return out, ln
+
+    def knn_accuracy(self, max_sim_tmpl0, bootstrap, nr_query_poses):
+        m, b = _i32(max_sim_tmpl0), _i32(bootstrap)
+        intra, inter = C.c_float(), C.c_float()
+        check(lib().pe_knn_accuracy(self.h, _ptr(m), _ptr(b), m.size, nr_query_poses, C.byref(intra), C.byref(inter)))
+        return intra.value, inter.value
+
+
+class Comm:
+    """NCCL communicator for the row-sharded DB (one process per GPU)"""
+
+    @staticmethod
+    def unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        check(lib().pe_comm_unique_id(buf))
+        return buf.raw
+
+    def __init__(self, rank, world, uid: bytes, device):
+        h = vp()
+        check(lib().pe_comm_create(rank, world, uid, device, C.byref(h)))
+        self.h = h.value
+        self.rank, self.world = rank, world
+
+    def allgather_f32(self, a):
+        a = _f32(a).reshape(-1)
+        out = np.empty((self.world, a.size), np.float32)
+        check(lib().pe_comm_allgather_f32(self.h, _ptr(a), a.size, _ptr(out)))
+        return out
+
+    def allreduce_sum_f64(self, a):
+        a = np.ascontiguousarray(a, np.float64).copy()
+        check(lib().pe_comm_allreduce_sum_f64(self.h, _ptr(a), a.size))
+        return a
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().pe_comm_destroy(self.h)
+            self.h = None

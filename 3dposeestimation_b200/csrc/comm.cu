@@ -1,0 +1,244 @@
+/*
+ * comm.cu - multi-GPU entry points: one process per GPU, NCCL over NVLink / NVSwitch.
+ *
+ * New relative to the reference, which is single-process.  The template DB is
+ * row-sharded; every rank scans its shard for the same queries, the per-shard candidate lists
+ * (k x {global index, exact distance} per query) are all-gathered and merged identically on
+ * every rank, ties -> lower global index, so the result equals the unsharded
+ * `knnMatch` (reference src/networkevaluator.cpp:267).
+ *
+ * NCCL is bound at run time (dlopen of libnccl.so.2) so the library loads, and every
+ * single-GPU entry point works, on a machine without NCCL.
+ */
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <cstring>
+#include <mutex>
+
+#include "common.h"
+
+namespace pe {
+namespace {
+
+struct NcclApi {
+    void* handle = nullptr;
+    decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+    decltype(&ncclCommInitRank) CommInitRank = nullptr;
+    decltype(&ncclCommDestroy) CommDestroy = nullptr;
+    decltype(&ncclAllGather) AllGather = nullptr;
+    decltype(&ncclAllReduce) AllReduce = nullptr;
+    decltype(&ncclGetErrorString) GetErrorString = nullptr;
+};
+
+NcclApi g_nccl;
+std::once_flag g_nccl_once;
+
+int nccl_load() {
+    std::call_once(g_nccl_once, [] {
+        void* h = nullptr;
+        for (const char* name : {"libnccl.so.2", "libnccl.so"}) {
+            h = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+            if (h) break;
+        }
+        if (!h) return;
+        NcclApi a;
+        a.handle = h;
+        a.GetUniqueId = reinterpret_cast<decltype(a.GetUniqueId)>(dlsym(h, "ncclGetUniqueId"));
+        a.CommInitRank = reinterpret_cast<decltype(a.CommInitRank)>(dlsym(h, "ncclCommInitRank"));
+        a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(dlsym(h, "ncclCommDestroy"));
+        a.AllGather = reinterpret_cast<decltype(a.AllGather)>(dlsym(h, "ncclAllGather"));
+        a.AllReduce = reinterpret_cast<decltype(a.AllReduce)>(dlsym(h, "ncclAllReduce"));
+        a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(dlsym(h, "ncclGetErrorString"));
+        if (a.GetUniqueId && a.CommInitRank && a.CommDestroy && a.AllGather && a.AllReduce && a.GetErrorString) g_nccl = a;
+    });
+    if (!g_nccl.handle) {
+        set_error("NCCL (libnccl.so.2) could not be loaded: %s", dlerror() ? dlerror() : "missing symbols");
+        return PE_ERR_NCCL;
+    }
+    return PE_OK;
+}
+
+#define PE_NCCL(expr)                                                                                   \
+    do {                                                                                                \
+        ncclResult_t _r = (expr);                                                                       \
+        if (_r != ncclSuccess) {                                                                        \
+            set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #expr, g_nccl.GetErrorString(_r));    \
+            return PE_ERR_NCCL;                                                                         \
+        }                                                                                               \
+    } while (0)
+
+}  // namespace
+}  // namespace pe
+
+using namespace pe;
+
+struct pe_comm {
+    int rank = 0, world = 1, device = 0;
+    ncclComm_t comm = nullptr;
+    cudaStream_t stream = nullptr;
+    pe::DevBuf send, recv;
+};
+
+namespace {
+
+/* local top-k -> all-gather of [idx block | dist block] per rank -> merge.  T is float or int. */
+template <typename T>
+int sharded_knn(pe_db* db, pe_comm* comm, const void* d_queries, int64_t nq, int k, int32_t* d_out_idx, T* d_out_dist,
+                bool hamming) {
+    PE_REQUIRE(db != nullptr, "null db");
+    PE_REQUIRE(nq >= 0 && k >= 1 && k <= 16, "bad k / nq");
+    if (nq == 0) return PE_OK;
+    const int world = comm ? comm->world : 1;
+    if (world == 1) {
+        return hamming ? knn_hamming_local(db, static_cast<const uint32_t*>(d_queries), nq, k, d_out_idx, reinterpret_cast<int32_t*>(d_out_dist))
+                       : knn_l2_local(db, static_cast<const float*>(d_queries), nq, k, d_out_idx, reinterpret_cast<float*>(d_out_dist));
+    }
+    PE_REQUIRE(comm->device == db->device, "communicator and DB live on different devices");
+    PE_CUDA(cudaSetDevice(db->device));
+    const size_t block = (size_t)nq * k; /* entries per rank and per half */
+    PE_CHECK(db->gather.reserve((size_t)(world + 1) * 2 * block * 4));
+    int32_t* send = db->gather.as<int32_t>();          /* [idx block | dist block] of this rank */
+    int32_t* recv = send + 2 * block;                  /* world x the same */
+    if (hamming)
+        PE_CHECK(knn_hamming_local(db, static_cast<const uint32_t*>(d_queries), nq, k, send, send + block));
+    else
+        PE_CHECK(knn_l2_local(db, static_cast<const float*>(d_queries), nq, k, send, reinterpret_cast<float*>(send + block)));
+    PE_NCCL(g_nccl.AllGather(send, recv, 2 * block, ncclInt32, comm->comm, db->stream));
+    /* candidate (q, shard, p): idx at shard*2*block + q*k + p, dist `block` entries further */
+    if (hamming)
+        return knn_merge_i32(db, recv + block, recv, 2 * (long long)block, world, nq, k, d_out_idx, reinterpret_cast<int32_t*>(d_out_dist));
+    return knn_merge_f32(db, reinterpret_cast<const float*>(recv + block), recv, 2 * (long long)block, world, nq, k, d_out_idx,
+                         reinterpret_cast<float*>(d_out_dist));
+}
+
+}  // namespace
+
+extern "C" {
+
+int pe_comm_unique_id(char* id128) {
+    PE_REQUIRE(id128 != nullptr, "null pointer");
+    PE_CHECK(nccl_load());
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId id;
+    PE_NCCL(g_nccl.GetUniqueId(&id));
+    memcpy(id128, &id, 128);
+    return PE_OK;
+}
+
+int pe_comm_create(int rank, int world, const char* id128, int device, pe_comm** out) {
+    PE_REQUIRE(out && id128, "null pointer");
+    *out = nullptr;
+    PE_REQUIRE(world >= 1 && rank >= 0 && rank < world, "rank %d outside world %d", rank, world);
+    PE_CHECK(nccl_load());
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) {
+        cudaGetLastError();
+        set_error("device %d not available", device);
+        return PE_ERR_CUDA;
+    }
+    PE_CUDA(cudaSetDevice(device));
+    pe_comm* c = new pe_comm();
+    c->rank = rank; c->world = world; c->device = device;
+    ncclUniqueId id;
+    memcpy(&id, id128, 128);
+    ncclResult_t r = g_nccl.CommInitRank(&c->comm, world, id, rank);
+    if (r != ncclSuccess) {
+        set_error("ncclCommInitRank failed: %s", g_nccl.GetErrorString(r));
+        delete c;
+        return PE_ERR_NCCL;
+    }
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        g_nccl.CommDestroy(c->comm);
+        delete c;
+        set_error("cudaStreamCreate failed");
+        return PE_ERR_CUDA;
+    }
+    *out = c;
+    return PE_OK;
+}
+
+void pe_comm_destroy(pe_comm* comm) {
+    if (!comm) return;
+    cudaSetDevice(comm->device);
+    if (comm->stream) { cudaStreamSynchronize(comm->stream); cudaStreamDestroy(comm->stream); }
+    comm->send.release();
+    comm->recv.release();
+    if (comm->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm->comm);
+    delete comm;
+}
+
+int pe_comm_info(const pe_comm* comm, int* rank, int* world) {
+    PE_REQUIRE(comm != nullptr, "null comm");
+    if (rank) *rank = comm->rank;
+    if (world) *world = comm->world;
+    return PE_OK;
+}
+
+int pe_comm_allgather_f32(pe_comm* comm, const float* send, int64_t n, float* recv) {
+    PE_REQUIRE(comm && recv && n >= 0 && (send || n == 0), "bad arguments");
+    if (n == 0) return PE_OK;
+    PE_CUDA(cudaSetDevice(comm->device));
+    PE_CHECK(comm->send.reserve((size_t)n * 4));
+    PE_CHECK(comm->recv.reserve((size_t)n * 4 * comm->world));
+    PE_CUDA(cudaMemcpyAsync(comm->send.p, send, (size_t)n * 4, cudaMemcpyHostToDevice, comm->stream));
+    PE_NCCL(g_nccl.AllGather(comm->send.p, comm->recv.p, (size_t)n, ncclFloat32, comm->comm, comm->stream));
+    PE_CUDA(cudaMemcpyAsync(recv, comm->recv.p, (size_t)n * 4 * comm->world, cudaMemcpyDeviceToHost, comm->stream));
+    PE_CUDA(cudaStreamSynchronize(comm->stream));
+    return PE_OK;
+}
+
+int pe_comm_allreduce_sum_f64(pe_comm* comm, double* buf, int64_t n) {
+    PE_REQUIRE(comm && n >= 0 && (buf || n == 0), "bad arguments");
+    if (n == 0) return PE_OK;
+    PE_CUDA(cudaSetDevice(comm->device));
+    PE_CHECK(comm->send.reserve((size_t)n * 8));
+    PE_CUDA(cudaMemcpyAsync(comm->send.p, buf, (size_t)n * 8, cudaMemcpyHostToDevice, comm->stream));
+    PE_NCCL(g_nccl.AllReduce(comm->send.p, comm->send.p, (size_t)n, ncclFloat64, ncclSum, comm->comm, comm->stream));
+    PE_CUDA(cudaMemcpyAsync(buf, comm->send.p, (size_t)n * 8, cudaMemcpyDeviceToHost, comm->stream));
+    PE_CUDA(cudaStreamSynchronize(comm->stream));
+    return PE_OK;
+}
+
+int pe_knn_sharded_dev(pe_db* db, pe_comm* comm, const float* d_queries, int64_t nq, int k, int32_t* d_out_idx,
+                       float* d_out_dist) {
+    PE_REQUIRE(db && !db->hamming, "need an L2 DB");
+    return sharded_knn<float>(db, comm, d_queries, nq, k, d_out_idx, d_out_dist, false);
+}
+
+int pe_knn_sharded(pe_db* db, pe_comm* comm, const float* queries, int64_t nq, int k, int32_t* out_idx, float* out_dist) {
+    PE_REQUIRE(db && !db->hamming, "need an L2 DB");
+    PE_REQUIRE(nq >= 0 && k >= 1 && k <= 16, "bad k / nq");
+    if (nq == 0) return PE_OK;
+    PE_REQUIRE(queries && out_idx && out_dist, "null pointer");
+    PE_CUDA(cudaSetDevice(db->device));
+    PE_CHECK(db->q_in.reserve((size_t)nq * db->dim * 4));
+    PE_CHECK(db->out_i.reserve((size_t)nq * k * 4));
+    PE_CHECK(db->out_d.reserve((size_t)nq * k * 4));
+    PE_CUDA(cudaMemcpyAsync(db->q_in.p, queries, (size_t)nq * db->dim * 4, cudaMemcpyHostToDevice, db->stream));
+    PE_CHECK(sharded_knn<float>(db, comm, db->q_in.p, nq, k, db->out_i.as<int32_t>(), db->out_d.as<float>(), false));
+    PE_CUDA(cudaMemcpyAsync(out_idx, db->out_i.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaMemcpyAsync(out_dist, db->out_d.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaStreamSynchronize(db->stream));
+    return PE_OK;
+}
+
+int pe_knn_hamming_sharded(pe_db* db, pe_comm* comm, const uint32_t* qcodes, int64_t nq, int k, int32_t* out_idx,
+                           int32_t* out_dist) {
+    PE_REQUIRE(db && db->hamming, "need a Hamming DB");
+    PE_REQUIRE(nq >= 0 && k >= 1 && k <= 16, "bad k / nq");
+    if (nq == 0) return PE_OK;
+    PE_REQUIRE(qcodes && out_idx && out_dist, "null pointer");
+    PE_CUDA(cudaSetDevice(db->device));
+    PE_CHECK(db->q_in.reserve((size_t)nq * db->words * 4));
+    PE_CHECK(db->out_i.reserve((size_t)nq * k * 4));
+    PE_CHECK(db->out_d.reserve((size_t)nq * k * 4));
+    PE_CUDA(cudaMemcpyAsync(db->q_in.p, qcodes, (size_t)nq * db->words * 4, cudaMemcpyHostToDevice, db->stream));
+    PE_CHECK(sharded_knn<int32_t>(db, comm, db->q_in.p, nq, k, db->out_i.as<int32_t>(), db->out_d.as<int32_t>(), true));
+    PE_CUDA(cudaMemcpyAsync(out_idx, db->out_i.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaMemcpyAsync(out_dist, db->out_d.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaStreamSynchronize(db->stream));
+    return PE_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,168 @@
+/*
+ * common.h - internal declarations shared by the translation units of libpose_b200.so.
+ * Nothing here is part of the public boundary (include/pose_b200.h).
+ */
+#pragma once
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/pose_b200.h"
+
+namespace pe {
+
+/* ---------------------------------------------------------------- errors --- */
+void set_error(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
+extern std::atomic<int64_t> g_launches;
+inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+#define PE_CUDA(expr)                                                                          \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess) {                                                               \
+            pe::set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #expr,                   \
+                          cudaGetErrorString(_e));                                             \
+            return PE_ERR_CUDA;                                                                \
+        }                                                                                      \
+    } while (0)
+
+#define PE_CHECK(expr)                                                                         \
+    do {                                                                                       \
+        int _s = (expr);                                                                       \
+        if (_s != PE_OK) return _s;                                                            \
+    } while (0)
+
+#define PE_REQUIRE(cond, ...)                                                                  \
+    do {                                                                                       \
+        if (!(cond)) {                                                                         \
+            pe::set_error(__VA_ARGS__);                                                        \
+            return PE_ERR_INVALID;                                                             \
+        }                                                                                      \
+    } while (0)
+
+/* after a kernel launch: catches launch-configuration errors and counts the launch */
+#define PE_LAUNCHED()                                                                          \
+    do {                                                                                       \
+        pe::count_launch();                                                                    \
+        PE_CUDA(cudaGetLastError());                                                           \
+    } while (0)
+
+/* a device buffer that grows on demand (never shrinks); bound to one device */
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes, bool zero_new = false);
+    void release();
+    template <typename T>
+    T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+/* ------------------------------------------------------------------ net --- */
+enum { L_CONV = 1, L_POOL = 2, L_ACT = 3, L_FC = 4 };
+
+struct Layer {
+    int kind = 0;
+    std::string name;
+    int a = 0, b = 0;          /* conv: num_output, kernel; pool: kernel, stride; act: PE_ACT_*; fc: num_output */
+    int blob0 = -1, blob1 = -1;
+};
+
+struct NetDef {
+    int batch = 0, channels = 0, height = 0, width = 0;
+    std::vector<int> sel;      /* input-blob channels fed to conv1 */
+    std::vector<Layer> layers;
+    std::vector<std::string> blob_names;
+    std::vector<std::vector<int64_t>> blob_shapes;
+    int desc_dim = 0;
+};
+
+/* prototxt.cpp: TEST-phase view of a Caffe prototxt; returns PE_OK or PE_ERR_PARSE */
+int parse_prototxt(const std::string& text, NetDef* out);
+/* built-in emitter for the seven reference variants (network/manifold*.prototxt) */
+bool builtin_prototxt(const std::string& variant, std::string* text);
+
+struct FcPlan {
+    int in = 0, out = 0;       /* logical sizes */
+    int ld_in = 0;             /* padded row stride of the input activation and of the device weight */
+    int blob_w = -1, blob_b = -1;
+    int act = PE_ACT_NONE, blob_slope = -1;
+    float* d_w = nullptr;      /* [out][ld_in] */
+    float* d_b = nullptr;      /* [out] */
+    float* d_slope = nullptr;  /* [out] or null */
+};
+
+}  // namespace pe
+
+struct pe_net {
+    int device = 0;
+    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+    int num_sms = 0;
+    pe::NetDef def;
+    std::vector<std::vector<float>> blobs; /* host master copy, Caffe order */
+    bool weights_dirty = true;
+
+    /* recognised plan: conv1(16,8) pool(2,2) [act] conv2(7,5) pool(2,2) [act] fc (act fc)*  */
+    int cin = 0;                      /* channels fed to conv1 */
+    int act1 = 0, act2 = 0;
+    int blob_w1 = -1, blob_b1 = -1, blob_s1 = -1, blob_w2 = -1, blob_b2 = -1, blob_s2 = -1;
+    std::vector<pe::FcPlan> fcs;
+    float *d_w1 = nullptr, *d_b1 = nullptr, *d_s1 = nullptr; /* [cin][8][8][16], [16], [16] */
+    float *d_w2 = nullptr, *d_b2 = nullptr, *d_s2 = nullptr; /* [16][5][5][8],  [8],  [8]  */
+    int* d_slot = nullptr;            /* patch channel -> conv1 input slot or -1 */
+
+    /* per-chunk activations (sized for `chunk` patches) and staging for the host entry point */
+    int64_t chunk = 0;
+    pe::DevBuf pool1, pool2, fc_a, fc_b, in_stage[2], out_stage;
+};
+
+struct pe_db {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int num_sms = 0;
+    int64_t t_local = 0, t_total = 0, row_offset = 0;
+    int dim = 0, dim_pad = 0;         /* descriptor dim and its multiple-of-4 padding */
+    int words = 0;                    /* Hamming: u32 words per code */
+    bool hamming = false;
+    int poses_per_object = 0;
+    float* d_desc = nullptr;          /* [t_local][dim_pad], zero padded */
+    float* d_norm = nullptr;          /* [t_local] squared norms */
+    uint32_t* d_codes = nullptr;      /* [t_local][words] */
+    float* d_labels = nullptr;        /* [t_total][8] or null */
+    pe::DevBuf q, q_in, cand_d, cand_i, out_i, out_d, qlab, knn_idx, scratch, scratch2, gather, boot;
+};
+
+namespace pe {
+int net_ensure_device(pe_net* net);
+/* forward.cu */
+int net_upload_weights(pe_net* net);
+int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c, float* d_out,
+                    int ld_out);
+int net_reserve(pe_net* net, int64_t chunk);
+/* knn.cu */
+int db_set_descriptors(pe_db* db, const float* src, bool src_on_device);
+int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist);
+int knn_hamming_local(pe_db* db, const uint32_t* d_qcodes, int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist);
+int knn_merge_f32(pe_db* db, const float* d_cd, const int* d_ci, long long stride_l, int n_lists, int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist);
+int knn_merge_i32(pe_db* db, const int* d_cd, const int* d_ci, long long stride_l, int n_lists, int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist);
+/* pose.cu */
+int pose_histogram_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
+                       const int* rot_inv, int n_rot, const float* bins, int n_bins, float* out_host);
+int pose_confusion_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
+                       const int* class_to_local, int n_classes, int n_local, int nr_test_poses,
+                       float* out_host);
+int pose_bootstrap_dev(pe_db* db, const int* d_knn3, int64_t nq, int nr_query_poses, int* d_out, int* d_len);
+int pose_accuracy_dev(pe_db* db, const int* d_max_sim0, const int* d_boot, int64_t nq, int nr_query_poses,
+                      float* intra_pct, float* inter_pct);
+/* synth.cu */
+int synth_patches_dev(cudaStream_t stream, uint64_t seed, int64_t first, int64_t n, int channels,
+                      int poses_per_object, float* d_out);
+void synth_labels_host(uint64_t seed, int64_t first, int64_t n, int poses_per_object, float* labels);
+uint64_t splitmix64(uint64_t x);
+uint64_t stream_key(uint64_t seed, uint64_t stream);
+}  // namespace pe

@@ -1,0 +1,442 @@
+/*
+ * forward.cu - descriptor forward of the manifold nets on sm_100a (fp32 SIMT path).
+ *
+ * Replaces the `CNN.Forward()` that networkEvaluator::computeDescriptors drives
+ * (reference src/networkevaluator.cpp:33-48) for the layer family of
+ * network/manifold*.prototxt:
+ *     conv 8x8x16 -> maxpool 2/2 (ceil) -> act -> conv 5x5x7 -> maxpool 2/2 (ceil) -> act
+ *     -> FC 256 -> act -> FC D [-> act -> FC 512 -> act -> FC 128]
+ * Kernels
+ *   conv1_pool_act   one CTA per patch (persistent); fuses the reference's HWC->CHW staging
+ *                    copy (:33-42) and the Slice/Concat/Silence channel select
+ *                    (network/manifold_rgb_16.prototxt:6-33) into the load, then conv + bias +
+ *                    pool + activation.  Per thread: 2x4 outputs x 16 filters in registers.
+ *   conv2_pool_act   one CTA per patch; pool1 tile staged with cp.async.
+ *   fc_act           tiled SGEMM with fused bias + activation, used for every InnerProduct.
+ * Order inside a stage is conv -> pool -> act (PReLU with a negative slope is not monotone).
+ */
+#include <cfloat>
+
+#include "common.h"
+
+namespace pe {
+
+namespace {
+
+constexpr int kF1 = 16, kK1 = 8, kO1 = 57, kP1 = 29;
+constexpr int kF2 = 7, kF2P = 8, kK2 = 5, kO2 = 25, kP2 = 13;
+/* conv1 shared-memory planes: 64x64 padded with zero rows/cols so edge tiles read zeros */
+constexpr int kC1Rows = 66, kC1Stride = 68, kC1Plane = kC1Rows * kC1Stride;
+constexpr int kC1Threads = 256;
+constexpr int kC1ColTiles = 15;                 /* 4 output columns per tile: 60 >= 57 */
+constexpr int kC1Tasks = kP1 * kC1ColTiles;     /* (pooled row, column tile) */
+/* pool1 activations in HBM: [n][16][30][32] with a zero border, so conv2 stages them verbatim */
+constexpr int kP1H = 30, kP1W = 32, kP1Plane = kP1H * kP1W, kP1Patch = kF1 * kP1Plane;
+constexpr int kPool2 = kF2 * kP2 * kP2;         /* 1183 = FC fan-in */
+constexpr int kPool2Ld = 1184;
+constexpr int kC2Threads = 192;
+
+__device__ __forceinline__ float apply_act(float v, int act, float slope) {
+    const float pos = fmaxf(v, 0.f), neg = fminf(v, 0.f);
+    if (act == PE_ACT_RELU) return pos;
+    if (act == PE_ACT_ELU) return pos + (expf(neg) - 1.0f);
+    if (act == PE_ACT_PRELU) return pos + slope * neg;
+    return v;
+}
+
+__device__ __forceinline__ float4 ld_stream4(const float4* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+/* ------------------------------------------------------------------ conv1 ---- */
+template <int CIN>
+__global__ void __launch_bounds__(kC1Threads, 1)
+conv1_pool_act_kernel(const float* __restrict__ patches, int patch_c, const int* __restrict__ slot,
+                      const float* __restrict__ w, const float* __restrict__ bias,
+                      const float* __restrict__ slope, int act, float* __restrict__ pool1,
+                      long long n, int vec_ok) {
+    extern __shared__ __align__(16) float smem[];
+    float* planes = smem;                 /* [CIN][66][68] */
+    float* wsm = smem + CIN * kC1Plane;   /* [CIN][8][8][16] */
+    __shared__ int s_slot[8];
+    __shared__ float s_bias[kF1], s_slope[kF1];
+    const int tid = threadIdx.x;
+
+    for (int i = tid; i < CIN * kC1Plane; i += kC1Threads) planes[i] = 0.f;
+    for (int i = tid; i < CIN * 64 * kF1; i += kC1Threads) wsm[i] = w[i];
+    if (tid < 8) s_slot[tid] = tid < patch_c ? slot[tid] : -1;
+    if (tid < kF1) {
+        s_bias[tid] = bias[tid];
+        s_slope[tid] = slope ? slope[tid] : 0.f;
+    }
+    __syncthreads();
+
+    const int total = 4096 * patch_c;
+    for (long long patch = blockIdx.x; patch < n; patch += gridDim.x) {
+        const float* src = patches + patch * (long long)total;
+        /* stage: HWC global -> selected CHW planes in shared memory */
+        if (vec_ok) {
+            const float4* s4 = reinterpret_cast<const float4*>(src);
+            for (int i4 = tid; i4 < total / 4; i4 += kC1Threads) {
+                const float4 v = ld_stream4(s4 + i4);
+                const float vv[4] = {v.x, v.y, v.z, v.w};
+                int pix = (i4 * 4) / patch_c;
+                int ch = i4 * 4 - pix * patch_c;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int sl = s_slot[ch];
+                    if (sl >= 0) planes[sl * kC1Plane + (pix >> 6) * kC1Stride + (pix & 63)] = vv[j];
+                    if (++ch == patch_c) { ch = 0; ++pix; }
+                }
+            }
+        } else {
+            for (int i = tid; i < total; i += kC1Threads) {
+                const int pix = i / patch_c, ch = i - pix * patch_c;
+                const int sl = s_slot[ch];
+                if (sl >= 0) planes[sl * kC1Plane + (pix >> 6) * kC1Stride + (pix & 63)] = __ldg(src + i);
+            }
+        }
+        __syncthreads();
+
+        for (int task = tid; task < kC1Tasks; task += kC1Threads) {
+            const int pr = task / kC1ColTiles, ct = task - pr * kC1ColTiles;
+            float acc[2][4][kF1];
+#pragma unroll
+            for (int f = 0; f < kF1; ++f) {
+                const float b = s_bias[f];
+#pragma unroll
+                for (int px = 0; px < 4; ++px) { acc[0][px][f] = b; acc[1][px][f] = b; }
+            }
+            const float* pl0 = planes + (2 * pr) * kC1Stride + 4 * ct;
+#pragma unroll 1
+            for (int c = 0; c < CIN; ++c) {
+                const float* pl = pl0 + c * kC1Plane;
+                const float4* wc = reinterpret_cast<const float4*>(wsm + c * 64 * kF1);
+#pragma unroll 1
+                for (int ky = 0; ky < kK1; ++ky) {
+                    const float4* ra = reinterpret_cast<const float4*>(pl + ky * kC1Stride);
+                    const float4* rb = reinterpret_cast<const float4*>(pl + (ky + 1) * kC1Stride);
+                    const float4 a0 = ra[0], a1 = ra[1], a2 = ra[2];
+                    const float4 b0 = rb[0], b1 = rb[1], b2 = rb[2];
+                    const float a[12] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w, a2.x, a2.y, a2.z, a2.w};
+                    const float b[12] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w};
+#pragma unroll
+                    for (int kx = 0; kx < kK1; ++kx) {
+                        const float4 w0 = wc[(ky * 8 + kx) * 4 + 0], w1 = wc[(ky * 8 + kx) * 4 + 1];
+                        const float4 w2 = wc[(ky * 8 + kx) * 4 + 2], w3 = wc[(ky * 8 + kx) * 4 + 3];
+                        const float wv[kF1] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w,
+                                               w2.x, w2.y, w2.z, w2.w, w3.x, w3.y, w3.z, w3.w};
+#pragma unroll
+                        for (int px = 0; px < 4; ++px)
+#pragma unroll
+                            for (int f = 0; f < kF1; ++f) {
+                                acc[0][px][f] = fmaf(a[px + kx], wv[f], acc[0][px][f]);
+                                acc[1][px][f] = fmaf(b[px + kx], wv[f], acc[1][px][f]);
+                            }
+                    }
+                }
+            }
+            /* 2x2/2 max pool (Caffe ceil sizing: windows clipped to the 57x57 map), then act */
+            const bool row1 = (2 * pr + 1) < kO1;
+            float* dst = pool1 + patch * (long long)kP1Patch + pr * kP1W;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int pc = 2 * ct + j;
+                if (pc < kP1) {
+                    const bool col1 = (4 * ct + 2 * j + 1) < kO1;
+#pragma unroll
+                    for (int f = 0; f < kF1; ++f) {
+                        float m = acc[0][2 * j][f];
+                        if (col1) m = fmaxf(m, acc[0][2 * j + 1][f]);
+                        if (row1) {
+                            m = fmaxf(m, acc[1][2 * j][f]);
+                            if (col1) m = fmaxf(m, acc[1][2 * j + 1][f]);
+                        }
+                        dst[f * kP1Plane + pc] = apply_act(m, act, s_slope[f]);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+/* ------------------------------------------------------------------ conv2 ---- */
+__global__ void __launch_bounds__(kC2Threads, 3)
+conv2_pool_act_kernel(const float* __restrict__ pool1, const float* __restrict__ w,
+                      const float* __restrict__ bias, const float* __restrict__ slope, int act,
+                      float* __restrict__ pool2, long long n) {
+    extern __shared__ __align__(16) float smem[];
+    float* in = smem;              /* [16][30][32] */
+    float* wsm = smem + kP1Patch;  /* [16][5][5][8] */
+    const int tid = threadIdx.x;
+    for (int i = tid; i < kF1 * kK2 * kK2 * kF2P; i += kC2Threads) wsm[i] = w[i];
+
+    const int py = tid / kP2, px = tid - py * kP2;
+    const bool active = tid < kP2 * kP2;
+    for (long long patch = blockIdx.x; patch < n; patch += gridDim.x) {
+        const float4* src = reinterpret_cast<const float4*>(pool1 + patch * (long long)kP1Patch);
+        float4* dst4 = reinterpret_cast<float4*>(in);
+        for (int i = tid; i < kP1Patch / 4; i += kC2Threads) cp_async16(dst4 + i, src + i);
+        cp_async_wait_all();
+        __syncthreads();
+        if (active) {
+            float acc[2][2][kF2P];
+#pragma unroll
+            for (int f = 0; f < kF2P; ++f) {
+                const float b = bias[f];
+                acc[0][0][f] = b; acc[0][1][f] = b; acc[1][0][f] = b; acc[1][1][f] = b;
+            }
+            const float* p0 = in + (2 * py) * kP1W + 2 * px;
+#pragma unroll 1
+            for (int c = 0; c < kF1; ++c) {
+                const float* pc = p0 + c * kP1Plane;
+                const float4* wc = reinterpret_cast<const float4*>(wsm + c * kK2 * kK2 * kF2P);
+#pragma unroll
+                for (int ky = 0; ky < kK2; ++ky) {
+                    const float2* ra = reinterpret_cast<const float2*>(pc + ky * kP1W);
+                    const float2* rb = reinterpret_cast<const float2*>(pc + (ky + 1) * kP1W);
+                    const float2 a0 = ra[0], a1 = ra[1], a2 = ra[2];
+                    const float2 b0 = rb[0], b1 = rb[1], b2 = rb[2];
+                    const float a[6] = {a0.x, a0.y, a1.x, a1.y, a2.x, a2.y};
+                    const float b[6] = {b0.x, b0.y, b1.x, b1.y, b2.x, b2.y};
+#pragma unroll
+                    for (int kx = 0; kx < kK2; ++kx) {
+                        const float4 w0 = wc[(ky * kK2 + kx) * 2], w1 = wc[(ky * kK2 + kx) * 2 + 1];
+                        const float wv[kF2P] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+                        for (int ox = 0; ox < 2; ++ox)
+#pragma unroll
+                            for (int f = 0; f < kF2P; ++f) {
+                                acc[0][ox][f] = fmaf(a[ox + kx], wv[f], acc[0][ox][f]);
+                                acc[1][ox][f] = fmaf(b[ox + kx], wv[f], acc[1][ox][f]);
+                            }
+                    }
+                }
+            }
+            const bool row1 = (2 * py + 1) < kO2, col1 = (2 * px + 1) < kO2;
+            float* dst = pool2 + patch * (long long)kPool2Ld + py * kP2 + px;
+#pragma unroll
+            for (int f = 0; f < kF2; ++f) {
+                float m = acc[0][0][f];
+                if (col1) m = fmaxf(m, acc[0][1][f]);
+                if (row1) {
+                    m = fmaxf(m, acc[1][0][f]);
+                    if (col1) m = fmaxf(m, acc[1][1][f]);
+                }
+                dst[f * kP2 * kP2] = apply_act(m, act, slope ? slope[f] : 0.f);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+/* --------------------------------------------------------------------- fc ---- */
+/* Y[m][o] = act(bias[o] + sum_k X[m][k] * W[o][k]); K is a multiple of 4, rows 16-byte aligned */
+constexpr int kBM = 64, kBN = 64, kBK = 16, kFcPad = 4;
+
+__global__ void __launch_bounds__(256)
+fc_act_kernel(const float* __restrict__ X, int ldx, const float* __restrict__ W, int ldw,
+              const float* __restrict__ bias, const float* __restrict__ slope, int act,
+              float* __restrict__ Y, int ldy, int M, int N, int n_store, int K) {
+    __shared__ __align__(16) float Xs[kBK][kBM + kFcPad];
+    __shared__ __align__(16) float Ws[kBK][kBN + kFcPad];
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    const int m0 = blockIdx.x * kBM, n0 = blockIdx.y * kBN;
+    const int lrow = tid >> 2, lk = (tid & 3) * 4;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    for (int k0 = 0; k0 < K; k0 += kBK) {
+        float4 xv = make_float4(0.f, 0.f, 0.f, 0.f), wv = xv;
+        if (m0 + lrow < M && k0 + lk < K)
+            xv = *reinterpret_cast<const float4*>(X + (size_t)(m0 + lrow) * ldx + k0 + lk);
+        if (n0 + lrow < N && k0 + lk < K)
+            wv = __ldg(reinterpret_cast<const float4*>(W + (size_t)(n0 + lrow) * ldw + k0 + lk));
+        __syncthreads();
+        Xs[lk + 0][lrow] = xv.x; Xs[lk + 1][lrow] = xv.y; Xs[lk + 2][lrow] = xv.z; Xs[lk + 3][lrow] = xv.w;
+        Ws[lk + 0][lrow] = wv.x; Ws[lk + 1][lrow] = wv.y; Ws[lk + 2][lrow] = wv.z; Ws[lk + 3][lrow] = wv.w;
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < kBK; ++kk) {
+            const float4 a = *reinterpret_cast<const float4*>(&Xs[kk][ty * 4]);
+            const float4 b = *reinterpret_cast<const float4*>(&Ws[kk][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int m = m0 + ty * 4 + i;
+        if (m >= M) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int o = n0 + tx * 4 + j;
+            if (o < N) Y[(size_t)m * ldy + o] = apply_act(acc[i][j] + bias[o], act, slope ? slope[o] : 0.f);
+            else if (o < n_store) Y[(size_t)m * ldy + o] = 0.f; /* keep pad columns of an intermediate zero */
+        }
+    }
+}
+
+template <int CIN>
+int launch_conv1(pe_net* net, const float* d_patches, int patch_c, long long n) {
+    const size_t smem = (size_t)CIN * (kC1Plane + 64 * kF1) * sizeof(float);
+    static bool attr_done[16] = {};
+    if (!attr_done[net->device & 15]) {
+        PE_CUDA(cudaFuncSetAttribute(conv1_pool_act_kernel<CIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_done[net->device & 15] = true;
+    }
+    const int grid = (int)(n < net->num_sms ? n : net->num_sms);
+    const int vec_ok = ((reinterpret_cast<uintptr_t>(d_patches) & 15) == 0) && ((4096 * patch_c) % 4 == 0);
+    conv1_pool_act_kernel<CIN><<<grid, kC1Threads, smem, net->stream>>>(
+        d_patches, patch_c, net->d_slot, net->d_w1, net->d_b1, net->d_s1, net->act1,
+        net->pool1.as<float>(), n, vec_ok);
+    PE_LAUNCHED();
+    return PE_OK;
+}
+
+int dev_alloc_copy(float** dst, const std::vector<float>& src) {
+    if (*dst) { cudaFree(*dst); *dst = nullptr; }
+    PE_CUDA(cudaMalloc(dst, src.size() * sizeof(float)));
+    PE_CUDA(cudaMemcpy(*dst, src.data(), src.size() * sizeof(float), cudaMemcpyHostToDevice));
+    return PE_OK;
+}
+
+}  // namespace
+
+int net_upload_weights(pe_net* net) {
+    if (!net->weights_dirty) return PE_OK;
+    PE_CUDA(cudaSetDevice(net->device));
+    PE_CUDA(cudaStreamSynchronize(net->stream));
+    const int cin = net->cin;
+    {   /* conv1: Caffe [16][cin][8][8] -> [cin][8][8][16] */
+        const std::vector<float>& src = net->blobs[net->blob_w1];
+        std::vector<float> w((size_t)cin * 64 * kF1);
+        for (int f = 0; f < kF1; ++f)
+            for (int c = 0; c < cin; ++c)
+                for (int t = 0; t < 64; ++t) w[((size_t)c * 64 + t) * kF1 + f] = src[((size_t)f * cin + c) * 64 + t];
+        PE_CHECK(dev_alloc_copy(&net->d_w1, w));
+        PE_CHECK(dev_alloc_copy(&net->d_b1, net->blobs[net->blob_b1]));
+        if (net->blob_s1 >= 0) PE_CHECK(dev_alloc_copy(&net->d_s1, net->blobs[net->blob_s1]));
+    }
+    {   /* conv2: Caffe [7][16][5][5] -> [16][5][5][8] (8th filter zero) */
+        const std::vector<float>& src = net->blobs[net->blob_w2];
+        std::vector<float> w((size_t)kF1 * 25 * kF2P, 0.f), b(kF2P, 0.f), s(kF2P, 0.f);
+        for (int f = 0; f < kF2; ++f)
+            for (int c = 0; c < kF1; ++c)
+                for (int t = 0; t < 25; ++t) w[((size_t)c * 25 + t) * kF2P + f] = src[((size_t)f * kF1 + c) * 25 + t];
+        for (int f = 0; f < kF2; ++f) b[f] = net->blobs[net->blob_b2][f];
+        PE_CHECK(dev_alloc_copy(&net->d_w2, w));
+        PE_CHECK(dev_alloc_copy(&net->d_b2, b));
+        if (net->blob_s2 >= 0) {
+            for (int f = 0; f < kF2; ++f) s[f] = net->blobs[net->blob_s2][f];
+            PE_CHECK(dev_alloc_copy(&net->d_s2, s));
+        }
+    }
+    for (auto& fc : net->fcs) {
+        const std::vector<float>& src = net->blobs[fc.blob_w];
+        std::vector<float> w((size_t)fc.out * fc.ld_in, 0.f);
+        for (int o = 0; o < fc.out; ++o)
+            for (int i = 0; i < fc.in; ++i) w[(size_t)o * fc.ld_in + i] = src[(size_t)o * fc.in + i];
+        PE_CHECK(dev_alloc_copy(&fc.d_w, w));
+        PE_CHECK(dev_alloc_copy(&fc.d_b, net->blobs[fc.blob_b]));
+        if (fc.blob_slope >= 0) PE_CHECK(dev_alloc_copy(&fc.d_slope, net->blobs[fc.blob_slope]));
+    }
+    {
+        std::vector<int> slot(8, -1);
+        for (size_t i = 0; i < net->def.sel.size(); ++i) slot[net->def.sel[i]] = (int)i;
+        if (!net->d_slot) PE_CUDA(cudaMalloc(&net->d_slot, 8 * sizeof(int)));
+        PE_CUDA(cudaMemcpy(net->d_slot, slot.data(), 8 * sizeof(int), cudaMemcpyHostToDevice));
+    }
+    net->weights_dirty = false;
+    return PE_OK;
+}
+
+int net_reserve(pe_net* net, int64_t chunk) {
+    if (chunk <= net->chunk) return PE_OK;
+    PE_CUDA(cudaSetDevice(net->device));
+    PE_CUDA(cudaStreamSynchronize(net->stream));
+    /* zero-filled once: the zero borders of pool1 and the pad column of pool2 are never written */
+    net->pool1.release();
+    net->pool2.release();
+    PE_CHECK(net->pool1.reserve((size_t)chunk * kP1Patch * sizeof(float), true));
+    PE_CHECK(net->pool2.reserve((size_t)chunk * kPool2Ld * sizeof(float), true));
+    int max_w = 4;
+    for (auto& fc : net->fcs) max_w = fc.out > max_w ? fc.out : max_w;
+    max_w = (max_w + 3) & ~3;
+    PE_CHECK(net->fc_a.reserve((size_t)chunk * max_w * sizeof(float), true));
+    PE_CHECK(net->fc_b.reserve((size_t)chunk * max_w * sizeof(float), true));
+    net->chunk = chunk;
+    return PE_OK;
+}
+
+/* n patches resident on the device -> n x D descriptors (row stride ld_out) on the device */
+int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c, float* d_out,
+                    int ld_out) {
+    PE_CUDA(cudaSetDevice(net->device));
+    PE_CHECK(net_upload_weights(net));
+    if (n <= 0) return PE_OK;
+    const int64_t want = n < 4096 ? n : 4096;
+    if (net->chunk < want) PE_CHECK(net_reserve(net, want));
+    static bool c2_attr[16] = {};
+    const size_t smem2 = (size_t)(kP1Patch + kF1 * 25 * kF2P) * sizeof(float);
+    if (!c2_attr[net->device & 15]) {
+        PE_CUDA(cudaFuncSetAttribute(conv2_pool_act_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+        c2_attr[net->device & 15] = true;
+    }
+    for (int64_t first = 0; first < n; first += net->chunk) {
+        const long long m = (n - first < net->chunk) ? (n - first) : net->chunk;
+        const float* src = d_patches + (size_t)first * 4096 * patch_c;
+        switch (net->cin) {
+        case 1: PE_CHECK(launch_conv1<1>(net, src, patch_c, m)); break;
+        case 2: PE_CHECK(launch_conv1<2>(net, src, patch_c, m)); break;
+        case 3: PE_CHECK(launch_conv1<3>(net, src, patch_c, m)); break;
+        case 4: PE_CHECK(launch_conv1<4>(net, src, patch_c, m)); break;
+        case 5: PE_CHECK(launch_conv1<5>(net, src, patch_c, m)); break;
+        case 6: PE_CHECK(launch_conv1<6>(net, src, patch_c, m)); break;
+        case 7: PE_CHECK(launch_conv1<7>(net, src, patch_c, m)); break;
+        case 8: PE_CHECK(launch_conv1<8>(net, src, patch_c, m)); break;
+        default: set_error("conv1 input channels %d outside 1..8", net->cin); return PE_ERR_UNSUPPORTED;
+        }
+        const int grid2 = (int)(m < 3LL * net->num_sms ? m : 3LL * net->num_sms);
+        conv2_pool_act_kernel<<<grid2, kC2Threads, smem2, net->stream>>>(
+            net->pool1.as<float>(), net->d_w2, net->d_b2, net->d_s2, net->act2, net->pool2.as<float>(), m);
+        PE_LAUNCHED();
+        const float* x = net->pool2.as<float>();
+        int ldx = kPool2Ld;
+        for (size_t i = 0; i < net->fcs.size(); ++i) {
+            const FcPlan& fc = net->fcs[i];
+            const bool last = i + 1 == net->fcs.size();
+            float* y = last ? d_out + (size_t)first * ld_out : ((i & 1) ? net->fc_b.as<float>() : net->fc_a.as<float>());
+            const int ldy = last ? ld_out : ((fc.out + 3) & ~3);
+            dim3 grid((unsigned)((m + kBM - 1) / kBM), (unsigned)((fc.out + kBN - 1) / kBN));
+            fc_act_kernel<<<grid, 256, 0, net->stream>>>(x, ldx, fc.d_w, fc.ld_in, fc.d_b, fc.d_slope, fc.act, y,
+                                                         ldy, (int)m, fc.out, last ? fc.out : ldy, fc.ld_in);
+            PE_LAUNCHED();
+            x = y;
+            ldx = ldy;
+        }
+    }
+    return PE_OK;
+}
+
+}  // namespace pe

@@ -1,0 +1,544 @@
+/*
+ * knn.cu - brute-force k-nearest-neighbour matching of query descriptors against the
+ * template-descriptor DB on sm_100a.
+ *
+ * Replaces `DescriptorMatcher::create("BruteForce")` + `add(DBfeats)` + `knnMatch(DBtest, matches, k)`
+ * (reference src/networkevaluator.cpp:193-197, 263-267; src/networksolver.cpp:466-472), i.e.
+ * OpenCV BFMatcher(NORM_L2): dist = sqrt(sum (q-t)^2), k smallest ascending, ties -> lower index.
+ *
+ * L2 path, two kernels
+ *   knn_l2_scan     grid (query block, DB chunk).  A thread owns RQ queries (descriptors held in
+ *                   registers, pre-scaled by -2); the CTA streams its DB chunk through a
+ *                   cp.async double-buffered shared-memory tile and every template row is read
+ *                   by a warp-broadcast LDS.  Ranking value |t|^2 - 2 q.t (one FFMA per
+ *                   dimension); per-query sorted candidate lists of k+2 entries live in shared
+ *                   memory, only the admission threshold is in a register.
+ *   knn_select      one warp per query: recomputes the reference's exact fp32 expression
+ *                   sqrt(sum (q-t)^2) for every candidate of every chunk and extracts the k
+ *                   smallest by (distance, index).  Also merges per-shard lists after the NCCL
+ *                   all-gather (distances taken as given).
+ * Hamming path (new behaviour): same scan with XOR + POPC on packed codes; exact.
+ */
+#include <cfloat>
+#include <climits>
+
+#include "common.h"
+
+namespace pe {
+
+namespace {
+
+constexpr int kScanThreads = 128;
+constexpr int kTile = 256; /* templates per shared-memory tile */
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+/* sorted insert into the calling thread's list j (entries strided by RQ*threads in shared memory);
+ * strict '>' keeps the earlier (lower-index) entry first among equals.  Returns the new threshold. */
+template <typename T, int RQ>
+__device__ __noinline__ T list_insert(T* ld, int* li, int kc, int j, T d, int idx) {
+    const int stride = RQ * kScanThreads;
+    const int base = j * kScanThreads + threadIdx.x;
+    int p = kc - 1;
+    while (p > 0 && ld[(p - 1) * stride + base] > d) {
+        ld[p * stride + base] = ld[(p - 1) * stride + base];
+        li[p * stride + base] = li[(p - 1) * stride + base];
+        --p;
+    }
+    ld[p * stride + base] = d;
+    li[p * stride + base] = idx;
+    return ld[(kc - 1) * stride + base];
+}
+
+/* ---------------------------------------------------------------- L2 scan ---- */
+template <int DP, int RQ>
+__global__ void __launch_bounds__(kScanThreads)
+knn_l2_scan_kernel(const float* __restrict__ q, int nq, const float* __restrict__ db,
+                   const float* __restrict__ norm, long long t_local, long long chunk_len,
+                   int n_chunks, int kc, long long row_offset, float* __restrict__ cand_d,
+                   int* __restrict__ cand_i) {
+    extern __shared__ __align__(16) float smem[];
+    float* tile = smem;                                  /* [2][kTile][DP] */
+    float* tnorm = tile + 2 * kTile * DP;                /* [2][kTile] */
+    float* ld = tnorm + 2 * kTile;                       /* [kc][RQ][threads] */
+    int* li = reinterpret_cast<int*>(ld + kc * RQ * kScanThreads);
+    const int tid = threadIdx.x;
+    const int chunk = blockIdx.y;
+    const long long t_begin = chunk * chunk_len;
+    long long t_end = t_begin + chunk_len;
+    if (t_end > t_local) t_end = t_local;
+
+    float qr[RQ][DP];
+    float thr[RQ];
+    int qi[RQ];
+#pragma unroll
+    for (int j = 0; j < RQ; ++j) {
+        qi[j] = (blockIdx.x * RQ + j) * kScanThreads + tid;
+        const bool ok = qi[j] < nq;
+        thr[j] = ok ? INFINITY : -INFINITY; /* idle slots never admit a candidate */
+#pragma unroll
+        for (int d4 = 0; d4 < DP / 4; ++d4) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ok) v = __ldg(reinterpret_cast<const float4*>(q + (size_t)qi[j] * DP) + d4);
+            qr[j][4 * d4 + 0] = -2.f * v.x; qr[j][4 * d4 + 1] = -2.f * v.y;
+            qr[j][4 * d4 + 2] = -2.f * v.z; qr[j][4 * d4 + 3] = -2.f * v.w;
+        }
+        for (int p = 0; p < kc; ++p) {
+            ld[(p * RQ + j) * kScanThreads + tid] = INFINITY;
+            li[(p * RQ + j) * kScanThreads + tid] = -1;
+        }
+    }
+
+    const int n_tiles = (int)((t_end - t_begin + kTile - 1) / kTile);
+    auto issue = [&](int it) {
+        const long long t0 = t_begin + (long long)it * kTile;
+        const int valid = (int)((t_end - t0) < kTile ? (t_end - t0) : kTile);
+        float* dst = tile + (it & 1) * kTile * DP;
+        const float* src = db + (size_t)t0 * DP;
+        for (int i = tid; i < valid * (DP / 4); i += kScanThreads) cp_async16(dst + 4 * i, src + 4 * i);
+        float* ndst = tnorm + (it & 1) * kTile;
+        for (int i = tid; i < valid; i += kScanThreads) cp_async4(ndst + i, norm + t0 + i);
+    };
+    if (n_tiles > 0) issue(0);
+    cp_async_commit();
+    for (int it = 0; it < n_tiles; ++it) {
+        if (it + 1 < n_tiles) issue(it + 1);
+        cp_async_commit();
+        cp_async_wait<1>();
+        __syncthreads();
+        const long long t0 = t_begin + (long long)it * kTile;
+        const int valid = (int)((t_end - t0) < kTile ? (t_end - t0) : kTile);
+        const float* tl = tile + (it & 1) * kTile * DP;
+        const float* tn = tnorm + (it & 1) * kTile;
+#pragma unroll 2
+        for (int t = 0; t < valid; ++t) {
+            float tv[DP];
+#pragma unroll
+            for (int d4 = 0; d4 < DP / 4; ++d4) {
+                const float4 v = *reinterpret_cast<const float4*>(tl + t * DP + 4 * d4);
+                tv[4 * d4 + 0] = v.x; tv[4 * d4 + 1] = v.y; tv[4 * d4 + 2] = v.z; tv[4 * d4 + 3] = v.w;
+            }
+            const float n2 = tn[t];
+            float s[RQ];
+            bool any = false;
+#pragma unroll
+            for (int j = 0; j < RQ; ++j) {
+                float a = n2;
+#pragma unroll
+                for (int d = 0; d < DP; ++d) a = fmaf(qr[j][d], tv[d], a);
+                s[j] = a;
+                any |= a < thr[j];
+            }
+            if (any) {
+#pragma unroll
+                for (int j = 0; j < RQ; ++j)
+                    if (s[j] < thr[j]) thr[j] = list_insert<float, RQ>(ld, li, kc, j, s[j], (int)(t0 + t + row_offset));
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < RQ; ++j) {
+        if (qi[j] >= nq) continue;
+        const size_t o = ((size_t)qi[j] * n_chunks + chunk) * kc;
+        for (int p = 0; p < kc; ++p) {
+            cand_d[o + p] = ld[(p * RQ + j) * kScanThreads + tid];
+            cand_i[o + p] = li[(p * RQ + j) * kScanThreads + tid];
+        }
+    }
+}
+
+/* ----------------------------------------------------------- Hamming scan ---- */
+template <int W, int RQ>
+__global__ void __launch_bounds__(kScanThreads)
+knn_hamming_scan_kernel(const uint32_t* __restrict__ q, int nq, const uint32_t* __restrict__ db,
+                        long long t_local, long long chunk_len, int n_chunks, int kc,
+                        long long row_offset, int* __restrict__ cand_d, int* __restrict__ cand_i) {
+    extern __shared__ __align__(16) float smem[];
+    uint32_t* tile = reinterpret_cast<uint32_t*>(smem);          /* [2][kTile][W] */
+    int* ld = reinterpret_cast<int*>(tile + 2 * kTile * W);      /* [kc][RQ][threads] */
+    int* li = ld + kc * RQ * kScanThreads;
+    const int tid = threadIdx.x;
+    const int chunk = blockIdx.y;
+    const long long t_begin = chunk * chunk_len;
+    long long t_end = t_begin + chunk_len;
+    if (t_end > t_local) t_end = t_local;
+
+    uint32_t qr[RQ][W];
+    int thr[RQ], qi[RQ];
+#pragma unroll
+    for (int j = 0; j < RQ; ++j) {
+        qi[j] = (blockIdx.x * RQ + j) * kScanThreads + tid;
+        const bool ok = qi[j] < nq;
+        thr[j] = ok ? INT_MAX : INT_MIN;
+#pragma unroll
+        for (int w = 0; w < W; ++w) qr[j][w] = ok ? __ldg(q + (size_t)qi[j] * W + w) : 0u;
+        for (int p = 0; p < kc; ++p) {
+            ld[(p * RQ + j) * kScanThreads + tid] = INT_MAX;
+            li[(p * RQ + j) * kScanThreads + tid] = -1;
+        }
+    }
+    const int n_tiles = (int)((t_end - t_begin + kTile - 1) / kTile);
+    auto issue = [&](int it) {
+        const long long t0 = t_begin + (long long)it * kTile;
+        const int valid = (int)((t_end - t0) < kTile ? (t_end - t0) : kTile);
+        uint32_t* dst = tile + (it & 1) * kTile * W;
+        const uint32_t* src = db + (size_t)t0 * W;
+        for (int i = tid; i < valid * W; i += kScanThreads) cp_async4(dst + i, src + i);
+    };
+    if (n_tiles > 0) issue(0);
+    cp_async_commit();
+    for (int it = 0; it < n_tiles; ++it) {
+        if (it + 1 < n_tiles) issue(it + 1);
+        cp_async_commit();
+        cp_async_wait<1>();
+        __syncthreads();
+        const long long t0 = t_begin + (long long)it * kTile;
+        const int valid = (int)((t_end - t0) < kTile ? (t_end - t0) : kTile);
+        const uint32_t* tl = tile + (it & 1) * kTile * W;
+#pragma unroll 2
+        for (int t = 0; t < valid; ++t) {
+            uint32_t tv[W];
+#pragma unroll
+            for (int w = 0; w < W; ++w) tv[w] = tl[t * W + w];
+            int s[RQ];
+            bool any = false;
+#pragma unroll
+            for (int j = 0; j < RQ; ++j) {
+                int a = 0;
+#pragma unroll
+                for (int w = 0; w < W; ++w) a += __popc(qr[j][w] ^ tv[w]);
+                s[j] = a;
+                any |= a < thr[j];
+            }
+            if (any) {
+#pragma unroll
+                for (int j = 0; j < RQ; ++j)
+                    if (s[j] < thr[j]) thr[j] = list_insert<int, RQ>(ld, li, kc, j, s[j], (int)(t0 + t + row_offset));
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < RQ; ++j) {
+        if (qi[j] >= nq) continue;
+        const size_t o = ((size_t)qi[j] * n_chunks + chunk) * kc;
+        for (int p = 0; p < kc; ++p) {
+            cand_d[o + p] = ld[(p * RQ + j) * kScanThreads + tid];
+            cand_i[o + p] = li[(p * RQ + j) * kScanThreads + tid];
+        }
+    }
+}
+
+/* ------------------------------------------------------------------ select ---- */
+/* The reference's distance, restated operation for operation from the CPU oracle
+ * (oracle/oracle_match.c l2_sq): 8 partial sums over dims i%8, multiply and add rounded
+ * separately, fixed combine tree, then sqrt. */
+__device__ __forceinline__ float exact_l2(const float* __restrict__ a, const float* __restrict__ b, int dp) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int i = 0; i < dp; i += 4) {
+        const float4 x = *reinterpret_cast<const float4*>(a + i);
+        const float4 y = __ldg(reinterpret_cast<const float4*>(b + i));
+        const int l = i & 7;
+        const float d0 = __fsub_rn(x.x, y.x), d1 = __fsub_rn(x.y, y.y), d2 = __fsub_rn(x.z, y.z), d3 = __fsub_rn(x.w, y.w);
+        acc[l + 0] = __fadd_rn(acc[l + 0], __fmul_rn(d0, d0));
+        acc[l + 1] = __fadd_rn(acc[l + 1], __fmul_rn(d1, d1));
+        acc[l + 2] = __fadd_rn(acc[l + 2], __fmul_rn(d2, d2));
+        acc[l + 3] = __fadd_rn(acc[l + 3], __fmul_rn(d3, d3));
+    }
+    const float s = __fadd_rn(__fadd_rn(__fadd_rn(acc[0], acc[4]), __fadd_rn(acc[2], acc[6])),
+                              __fadd_rn(__fadd_rn(acc[1], acc[5]), __fadd_rn(acc[3], acc[7])));
+    return __fsqrt_rn(s);
+}
+
+template <typename T>
+__device__ __forceinline__ T big();
+template <>
+__device__ __forceinline__ float big<float>() { return INFINITY; }
+template <>
+__device__ __forceinline__ int big<int>() { return INT_MAX; }
+
+/* candidate (q, l, p) lives at q*stride_q + l*stride_l + p, l < n_lists, p < kc.
+ * REFINE: recompute the distance of each candidate from the DB rows (L2 only). */
+template <typename T, bool REFINE>
+__global__ void __launch_bounds__(32)
+knn_select_kernel(const T* __restrict__ cand_d, const int* __restrict__ cand_i, long long stride_q,
+                  long long stride_l, int n_lists, int kc, const float* __restrict__ q,
+                  const float* __restrict__ db, int dp, long long row_offset, int k,
+                  int* __restrict__ out_idx, T* __restrict__ out_dist) {
+    extern __shared__ __align__(16) float smem[];
+    const int n_cand = n_lists * kc;
+    float* sq = smem; /* REFINE: the query row (dp floats, keeps the lists 16-byte aligned) */
+    T* sd = reinterpret_cast<T*>(smem + (REFINE ? dp : 0));
+    int* si = reinterpret_cast<int*>(sd) + n_cand;
+    const int lane = threadIdx.x;
+    const long long qi = blockIdx.x;
+    if (REFINE) {
+        for (int d = lane; d < dp; d += 32) sq[d] = q[(size_t)qi * dp + d];
+        __syncwarp();
+    }
+    for (int c = lane; c < n_cand; c += 32) {
+        const int l = c / kc, p = c - l * kc;
+        const size_t at = (size_t)qi * stride_q + (size_t)l * stride_l + p;
+        const int idx = cand_i[at];
+        T d = big<T>();
+        if (idx >= 0) {
+            if (REFINE) d = (T)exact_l2(sq, db + (size_t)(idx - row_offset) * dp, dp);
+            else d = cand_d[at];
+        }
+        sd[c] = d;
+        si[c] = idx >= 0 ? idx : INT_MAX;
+    }
+    __syncwarp();
+    for (int r = 0; r < k; ++r) {
+        T bd = big<T>();
+        int bi = INT_MAX, bc = -1;
+        for (int c = lane; c < n_cand; c += 32) {
+            const T d = sd[c];
+            const int i = si[c];
+            if (d < bd || (d == bd && i < bi)) { bd = d; bi = i; bc = c; }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const T od = __shfl_xor_sync(0xffffffffu, bd, off);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+            const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
+            if (od < bd || (od == bd && oi < bi)) { bd = od; bi = oi; bc = oc; }
+        }
+        if (lane == 0) {
+            out_idx[(size_t)qi * k + r] = bi == INT_MAX ? -1 : bi;
+            out_dist[(size_t)qi * k + r] = bi == INT_MAX ? big<T>() : bd;
+            if (bc >= 0) { sd[bc] = big<T>(); si[bc] = INT_MAX; }
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void pad_rows_kernel(const float* __restrict__ src, int dim, float* __restrict__ dst, int dp, long long n) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n * dp) return;
+    const long long r = i / dp;
+    const int c = (int)(i - r * dp);
+    dst[i] = c < dim ? src[r * dim + c] : 0.f;
+}
+
+__global__ void row_norm_kernel(const float* __restrict__ x, int dp, float* __restrict__ norm, long long n) {
+    const long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    float s = 0.f;
+    for (int d = 0; d < dp; ++d) { const float v = x[r * dp + d]; s = fmaf(v, v, s); }
+    norm[r] = s;
+}
+
+int pad_dim(int dim) {
+    if (dim <= 4) return 4;
+    if (dim <= 16) return 16;
+    if (dim <= 64) return 64;
+    if (dim <= 128) return 128;
+    return -1;
+}
+
+struct ScanGeom {
+    int rq, q_blocks, n_chunks, kc;
+    long long chunk_len;
+    size_t smem;
+};
+
+ScanGeom plan_scan(const pe_db* db, long long nq, int k, bool hamming) {
+    ScanGeom g;
+    g.kc = hamming ? k : k + 2;
+    int rq_max;
+    if (hamming) rq_max = db->words <= 4 ? 8 : 4;
+    else rq_max = db->dim_pad <= 16 ? 8 : (db->dim_pad == 64 ? 2 : 1);
+    if (g.kc > 10 && rq_max > 4) rq_max = 4;
+    int rq = rq_max;
+    /* small query sets: fewer queries per thread so that lanes are not left idle */
+    while (rq > 1 && nq <= (long long)kScanThreads * (rq / 2)) rq /= 2;
+    if (!hamming && db->dim_pad <= 16 && rq == 2) rq = 1; /* instantiated: 1, 4, 8 */
+    if (hamming && rq == 2) rq = 1;
+    g.rq = rq;
+    g.q_blocks = (int)((nq + (long long)kScanThreads * rq - 1) / ((long long)kScanThreads * rq));
+    if (g.q_blocks < 1) g.q_blocks = 1;
+    /* about four CTAs per SM in flight over the whole grid; chunks are whole tiles */
+    long long want = (4LL * db->num_sms + g.q_blocks - 1) / g.q_blocks;
+    const long long tiles = (db->t_local + kTile - 1) / kTile;
+    if (want > tiles) want = tiles;
+    if (want < 1) want = 1;
+    const long long tiles_per_chunk = (tiles + want - 1) / want;
+    g.chunk_len = tiles_per_chunk * kTile;
+    g.n_chunks = (int)((db->t_local + g.chunk_len - 1) / g.chunk_len);
+    if (g.n_chunks < 1) g.n_chunks = 1;
+    const size_t lists = (size_t)2 * g.kc * rq * kScanThreads * 4;
+    if (hamming) g.smem = (size_t)2 * kTile * db->words * 4 + lists;
+    else g.smem = (size_t)2 * kTile * (db->dim_pad + 1) * 4 + lists;
+    return g;
+}
+
+template <int DP, int RQ>
+int launch_l2_scan(pe_db* db, const ScanGeom& g, const float* dq, int nq, float* cd, int* ci) {
+    PE_CUDA(cudaFuncSetAttribute(knn_l2_scan_kernel<DP, RQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
+    dim3 grid(g.q_blocks, g.n_chunks);
+    knn_l2_scan_kernel<DP, RQ><<<grid, kScanThreads, g.smem, db->stream>>>(
+        dq, nq, db->d_desc, db->d_norm, db->t_local, g.chunk_len, g.n_chunks, g.kc, db->row_offset, cd, ci);
+    PE_LAUNCHED();
+    return PE_OK;
+}
+
+template <int W, int RQ>
+int launch_ham_scan(pe_db* db, const ScanGeom& g, const uint32_t* dq, int nq, int* cd, int* ci) {
+    PE_CUDA(cudaFuncSetAttribute(knn_hamming_scan_kernel<W, RQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
+    dim3 grid(g.q_blocks, g.n_chunks);
+    knn_hamming_scan_kernel<W, RQ><<<grid, kScanThreads, g.smem, db->stream>>>(
+        dq, nq, db->d_codes, db->t_local, g.chunk_len, g.n_chunks, g.kc, db->row_offset, cd, ci);
+    PE_LAUNCHED();
+    return PE_OK;
+}
+
+}  // namespace
+
+/* local top-k of the shard held by `db` for nq device-resident queries (dense nq x dim) */
+int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist) {
+    PE_REQUIRE(!db->hamming, "pe_knn on a Hamming DB");
+    PE_REQUIRE(k >= 1 && k <= 16, "k=%d outside 1..16", k);
+    PE_REQUIRE(nq >= 0 && nq < (1LL << 31) / 16, "nq out of range");
+    PE_CUDA(cudaSetDevice(db->device));
+    if (nq == 0) return PE_OK;
+    const int dp = db->dim_pad;
+    const float* dq = d_queries;
+    if (dp != db->dim) {
+        PE_CHECK(db->q.reserve((size_t)nq * dp * sizeof(float)));
+        const long long tot = nq * dp;
+        pad_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, db->stream>>>(d_queries, db->dim, db->q.as<float>(), dp, nq);
+        PE_LAUNCHED();
+        dq = db->q.as<float>();
+    }
+    const ScanGeom g = plan_scan(db, nq, k, false);
+    const size_t n_cand = (size_t)nq * g.n_chunks * g.kc;
+    PE_CHECK(db->cand_d.reserve(n_cand * sizeof(float)));
+    PE_CHECK(db->cand_i.reserve(n_cand * sizeof(int)));
+    float* cd = db->cand_d.as<float>();
+    int* ci = db->cand_i.as<int>();
+    int st = PE_ERR_UNSUPPORTED;
+    if (db->t_local > 0) {
+#define L2_CASE(DPV, RQV) if (dp == DPV && g.rq == RQV) st = launch_l2_scan<DPV, RQV>(db, g, dq, (int)nq, cd, ci)
+        L2_CASE(4, 1); L2_CASE(4, 4); L2_CASE(4, 8);
+        L2_CASE(16, 1); L2_CASE(16, 4); L2_CASE(16, 8);
+        L2_CASE(64, 1); L2_CASE(64, 2);
+        L2_CASE(128, 1);
+#undef L2_CASE
+        if (st != PE_OK) {
+            if (st == PE_ERR_UNSUPPORTED) set_error("no L2 scan kernel for dim_pad=%d rq=%d", dp, g.rq);
+            return st;
+        }
+    } else {
+        PE_CUDA(cudaMemsetAsync(ci, 0xff, n_cand * sizeof(int), db->stream)); /* all -1: empty shard */
+    }
+    const size_t smem = (size_t)(2 * g.n_chunks * g.kc + dp) * 4;
+    PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
+    PE_CUDA(cudaFuncSetAttribute(knn_select_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    knn_select_kernel<float, true><<<(unsigned)nq, 32, smem, db->stream>>>(
+        cd, ci, (long long)g.n_chunks * g.kc, g.kc, g.n_chunks, g.kc, dq, db->d_desc, dp, db->row_offset, k,
+        d_out_idx, d_out_dist);
+    PE_LAUNCHED();
+    return PE_OK;
+}
+
+int knn_hamming_local(pe_db* db, const uint32_t* d_qcodes, int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist) {
+    PE_REQUIRE(db->hamming, "pe_knn_hamming on an L2 DB");
+    PE_REQUIRE(k >= 1 && k <= 16, "k=%d outside 1..16", k);
+    PE_REQUIRE(nq >= 0 && nq < (1LL << 31) / 16, "nq out of range");
+    PE_CUDA(cudaSetDevice(db->device));
+    if (nq == 0) return PE_OK;
+    const ScanGeom g = plan_scan(db, nq, k, true);
+    const size_t n_cand = (size_t)nq * g.n_chunks * g.kc;
+    PE_CHECK(db->cand_d.reserve(n_cand * sizeof(int)));
+    PE_CHECK(db->cand_i.reserve(n_cand * sizeof(int)));
+    int* cd = db->cand_d.as<int>();
+    int* ci = db->cand_i.as<int>();
+    int st = PE_ERR_UNSUPPORTED;
+    if (db->t_local > 0) {
+#define HAM_CASE(WV, RQV) if (db->words == WV && g.rq == RQV) st = launch_ham_scan<WV, RQV>(db, g, d_qcodes, (int)nq, cd, ci)
+        HAM_CASE(1, 1); HAM_CASE(1, 4); HAM_CASE(1, 8);
+        HAM_CASE(2, 1); HAM_CASE(2, 4); HAM_CASE(2, 8);
+        HAM_CASE(4, 1); HAM_CASE(4, 4); HAM_CASE(4, 8);
+        HAM_CASE(8, 1); HAM_CASE(8, 4);
+#undef HAM_CASE
+        if (st != PE_OK) {
+            if (st == PE_ERR_UNSUPPORTED) set_error("no Hamming scan kernel for words=%d rq=%d", db->words, g.rq);
+            return st;
+        }
+    } else {
+        PE_CUDA(cudaMemsetAsync(ci, 0xff, n_cand * sizeof(int), db->stream));
+    }
+    const size_t smem = (size_t)(2 * g.n_chunks * g.kc) * 4;
+    PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
+    PE_CUDA(cudaFuncSetAttribute(knn_select_kernel<int, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    knn_select_kernel<int, false><<<(unsigned)nq, 32, smem, db->stream>>>(
+        cd, ci, (long long)g.n_chunks * g.kc, g.kc, g.n_chunks, g.kc, nullptr, nullptr, 0, 0, k, d_out_idx, d_out_dist);
+    PE_LAUNCHED();
+    return PE_OK;
+}
+
+/* merge `n_lists` per-shard lists; list l of query q starts at l*stride_l + q*k (global indices, exact distances) */
+int knn_merge_f32(pe_db* db, const float* d_cd, const int* d_ci, long long stride_l, int n_lists, int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist) {
+    if (nq == 0) return PE_OK;
+    const size_t smem = (size_t)2 * n_lists * k * 4;
+    knn_select_kernel<float, false><<<(unsigned)nq, 32, smem, db->stream>>>(
+        d_cd, d_ci, k, stride_l, n_lists, k, nullptr, nullptr, 0, 0, k, d_out_idx, d_out_dist);
+    PE_LAUNCHED();
+    return PE_OK;
+}
+int knn_merge_i32(pe_db* db, const int* d_cd, const int* d_ci, long long stride_l, int n_lists, int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist) {
+    if (nq == 0) return PE_OK;
+    const size_t smem = (size_t)2 * n_lists * k * 4;
+    knn_select_kernel<int, false><<<(unsigned)nq, 32, smem, db->stream>>>(
+        d_cd, d_ci, k, stride_l, n_lists, k, nullptr, nullptr, 0, 0, k, d_out_idx, d_out_dist);
+    PE_LAUNCHED();
+    return PE_OK;
+}
+
+int db_set_descriptors(pe_db* db, const float* src, bool src_on_device) {
+    const int dp = pad_dim(db->dim);
+    if (dp < 0) { set_error("descriptor dim %d > 128 unsupported", db->dim); return PE_ERR_UNSUPPORTED; }
+    db->dim_pad = dp;
+    const size_t rows = db->t_local > 0 ? (size_t)db->t_local : 1;
+    PE_CUDA(cudaMalloc(&db->d_desc, rows * dp * sizeof(float)));
+    PE_CUDA(cudaMalloc(&db->d_norm, rows * sizeof(float)));
+    if (db->t_local == 0) return PE_OK;
+    const float* dsrc = src;
+    float* tmp = nullptr;
+    if (!src_on_device) {
+        if (dp == db->dim) {
+            PE_CUDA(cudaMemcpyAsync(db->d_desc, src, rows * dp * sizeof(float), cudaMemcpyHostToDevice, db->stream));
+            dsrc = nullptr;
+        } else {
+            PE_CUDA(cudaMalloc(&tmp, rows * db->dim * sizeof(float)));
+            PE_CUDA(cudaMemcpyAsync(tmp, src, rows * db->dim * sizeof(float), cudaMemcpyHostToDevice, db->stream));
+            dsrc = tmp;
+        }
+    }
+    if (dsrc) {
+        const long long tot = (long long)rows * dp;
+        pad_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, db->stream>>>(dsrc, db->dim, db->d_desc, dp, db->t_local);
+        PE_LAUNCHED();
+    }
+    row_norm_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, db->stream>>>(db->d_desc, dp, db->d_norm, db->t_local);
+    PE_LAUNCHED();
+    PE_CUDA(cudaStreamSynchronize(db->stream));
+    if (tmp) cudaFree(tmp);
+    return PE_OK;
+}
+
+}  // namespace pe

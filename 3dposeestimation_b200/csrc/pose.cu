@@ -1,0 +1,339 @@
+/*
+ * pose.cu - pose-error reductions over the kNN result on sm_100a.
+ *
+ * Replaces the per-query loops that follow knnMatch in the reference:
+ *   pose_err_kernel    networkEvaluator::computeHistogram body (src/networkevaluator.cpp:273-339):
+ *                      best same-class neighbour by angular error (Eigen angularDistance, or the
+ *                      elevation difference |acos(Rq22)-acos(Rk22)| for rotInv classes, :296-301),
+ *                      exact-match scan over the matched object's templates (:326-334),
+ *                      cumulative bins (:337-338).  One warp per query.
+ *   median_select      the sort + middle element of :349-350 as a 4-pass radix select.
+ *   confusion_kernel   computeConfusionMatrix body (:201-239).
+ *   bootstrap_kernel   networkSolver::computeKNN body (src/networksolver.cpp:474-504).
+ *   accuracy_kernel    computeKNNAccuracy (src/networkevaluator.cpp:153-175).
+ * acos is evaluated as the correctly rounded float of a double acos on both sides of the parity
+ * check (CPU oracle and here), so `<` comparisons between angles agree bit for bit.
+ */
+#include <cfloat>
+#include <cmath>
+
+#include "common.h"
+
+namespace pe {
+
+namespace {
+
+__device__ __forceinline__ float acos_cr(float x) { return __double2float_rn(acos((double)x)); }
+
+/* |a.b| clamped to 1, products and sums rounded separately in the order Eigen's dot() of a
+ * 4-vector evaluates them (oracle_match.c orc_angular_distance) */
+__device__ __forceinline__ float quat_absdot(const float* __restrict__ a, const float* __restrict__ b) {
+    float d = __fmul_rn(a[0], b[0]);
+    d = __fadd_rn(d, __fmul_rn(a[1], b[1]));
+    d = __fadd_rn(d, __fmul_rn(a[2], b[2]));
+    d = __fadd_rn(d, __fmul_rn(a[3], b[3]));
+    d = fabsf(d);
+    return d > 1.0f ? 1.0f : d;
+}
+
+__device__ __forceinline__ float rot22(const float* __restrict__ q) {
+    const float tx = __fmul_rn(2.0f, q[0]), ty = __fmul_rn(2.0f, q[1]);
+    const float txx = __fmul_rn(tx, q[0]), tyy = __fmul_rn(ty, q[1]);
+    return __fsub_rn(1.0f, __fadd_rn(txx, tyy));
+}
+
+/* `x*180.f/M_PI` as the reference writes it: float product, double division, narrowed to float */
+__device__ __forceinline__ float to_degrees(float rad) {
+    return __double2float_rn(__ddiv_rn((double)__fmul_rn(rad, 180.f), 3.14159265358979323846));
+}
+
+constexpr int kPoseWarps = 4;
+constexpr int kMaxBins = 16;
+
+__global__ void __launch_bounds__(kPoseWarps * 32)
+pose_err_kernel(const int* __restrict__ knn_idx, long long nq, int k, const float* __restrict__ q_labels,
+                const float* __restrict__ t_labels, long long t_total, int nr_tmpl_poses,
+                const int* __restrict__ rot_inv, int n_rot, const float* __restrict__ bins, int n_bins,
+                float* __restrict__ err_out, unsigned long long* __restrict__ counts,
+                double* __restrict__ sum_out) {
+    __shared__ unsigned int s_cnt[kMaxBins];
+    __shared__ double s_sum[kPoseWarps];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x < kMaxBins) s_cnt[threadIdx.x] = 0;
+    if (lane == 0) s_sum[warp] = 0.0;
+    __syncthreads();
+    const long long qi = (long long)blockIdx.x * kPoseWarps + warp;
+    if (qi < nq) {
+        const float* ql = q_labels + qi * 8;
+        const float qc = ql[0];
+        float qq[4] = {ql[1], ql[2], ql[3], ql[4]};
+        int cls = (int)qc;
+        const int inv = (cls >= 0 && cls < n_rot) ? rot_inv[cls] : 0;
+        /* lane nn < k scores neighbour nn */
+        float d = FLT_MAX;
+        int ti = -1;
+        if (lane < k) {
+            ti = knn_idx[qi * k + lane];
+            if (ti >= 0 && ti < t_total) {
+                const float* tl = t_labels + (long long)ti * 8;
+                if (tl[0] == qc) {
+                    if (inv == 0) {
+                        d = to_degrees(__fmul_rn(2.0f, acos_cr(quat_absdot(qq, tl + 1))));
+                    } else {
+                        d = to_degrees(fabsf(__fsub_rn(acos_cr(rot22(qq)), acos_cr(rot22(tl + 1)))));
+                        if (isnan(d)) d = FLT_MAX;
+                    }
+                }
+            }
+        }
+        /* `if (knn_dist >= best_dist) continue` with best_dist starting at FLT_MAX:
+         * smallest error wins, earlier neighbour on ties, FLT_MAX never wins */
+        float bd = d;
+        int bn = (d < FLT_MAX) ? lane : 64;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, bd, off);
+            const int on = __shfl_xor_sync(0xffffffffu, bn, off);
+            if (od < bd || (od == bd && on < bn)) { bd = od; bn = on; }
+        }
+        if (bn >= 64) { /* no same-class neighbour */
+            if (lane == 0) {
+                err_out[qi] = -1.f;
+                atomicAdd(&s_cnt[0], 1u);
+            }
+        } else {
+            const int best_t = __shfl_sync(0xffffffffu, ti, bn);
+            /* exact match: no template of the matched object is strictly closer */
+            const long long obj0 = (long long)(best_t / nr_tmpl_poses) * nr_tmpl_poses;
+            const float ref = quat_absdot(qq, t_labels + (long long)best_t * 8 + 1);
+            float mx = 0.f;
+            for (int p = lane; p < nr_tmpl_poses; p += 32) {
+                const long long t = obj0 + p;
+                if (t < t_total) mx = fmaxf(mx, quat_absdot(qq, t_labels + t * 8 + 1));
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+            if (lane == 0) {
+                const bool exact = !(mx > ref && acos_cr(mx) < acos_cr(ref));
+                err_out[qi] = bd;
+                if (exact) atomicAdd(&s_cnt[1], 1u);
+                for (int b = 2; b < n_bins; ++b)
+                    if (bd < bins[b]) atomicAdd(&s_cnt[b], 1u);
+                s_sum[warp] = (double)bd;
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < n_bins && s_cnt[threadIdx.x]) atomicAdd(&counts[threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int w = 0; w < kPoseWarps; ++w) s += s_sum[w];
+        if (s != 0.0) atomicAdd(sum_out, s);
+    }
+}
+
+/* element of rank (n_valid-1)/2 among the non-negative entries of err (radix select on the
+ * float bit patterns, which order like the floats for values >= 0); NaN when none */
+__global__ void __launch_bounds__(1024)
+median_select_kernel(const float* __restrict__ err, long long n, float* __restrict__ out) {
+    __shared__ unsigned int hist[256];
+    __shared__ unsigned int s_prefix, s_mask;
+    __shared__ unsigned long long s_rank, s_valid;
+    const int tid = threadIdx.x;
+    if (tid == 0) { s_valid = 0; s_prefix = 0; s_mask = 0; }
+    __syncthreads();
+    unsigned long long mine = 0;
+    for (long long i = tid; i < n; i += blockDim.x) mine += err[i] >= 0.f;
+    atomicAdd(&s_valid, mine);
+    __syncthreads();
+    if (s_valid == 0) {
+        if (tid == 0) *out = nanf("");
+        return;
+    }
+    if (tid == 0) s_rank = (s_valid - 1) / 2;
+    for (int pass = 3; pass >= 0; --pass) {
+        if (tid < 256) hist[tid] = 0;
+        __syncthreads();
+        const unsigned int prefix = s_prefix, mask = s_mask;
+        const int shift = pass * 8;
+        for (long long i = tid; i < n; i += blockDim.x) {
+            const float v = err[i];
+            if (!(v >= 0.f)) continue;
+            const unsigned int u = __float_as_uint(v);
+            if ((u & mask) == prefix) atomicAdd(&hist[(u >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            unsigned long long r = s_rank, cum = 0;
+            int b = 0;
+            for (; b < 256; ++b) {
+                if (cum + hist[b] > r) break;
+                cum += hist[b];
+            }
+            s_rank = r - cum;
+            s_prefix = prefix | ((unsigned int)b << shift);
+            s_mask = mask | (255u << shift);
+        }
+        __syncthreads();
+    }
+    if (tid == 0) *out = __uint_as_float(s_prefix);
+}
+
+__global__ void confusion_kernel(const int* __restrict__ knn_idx, long long nq, int k,
+                                 const float* __restrict__ q_labels, const float* __restrict__ t_labels,
+                                 long long t_total, const int* __restrict__ class_to_local, int n_classes,
+                                 int n_local, unsigned int* __restrict__ mat, int* __restrict__ bad) {
+    const long long qi = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (qi >= nq) return;
+    const float qc = q_labels[qi * 8];
+    int pick = -1;
+    for (int nn = 0; nn < k; ++nn) { /* first same-class neighbour wins */
+        const int ti = knn_idx[qi * k + nn];
+        if (ti >= 0 && ti < t_total && t_labels[(long long)ti * 8] == qc) { pick = ti; break; }
+    }
+    if (pick < 0) pick = knn_idx[qi * k]; /* else the 1st neighbour */
+    if (pick < 0 || pick >= t_total) return;
+    const int qcls = (int)qc, tcls = (int)t_labels[(long long)pick * 8];
+    if (qcls < 0 || qcls >= n_classes || tcls < 0 || tcls >= n_classes) { atomicExch(bad, 1); return; }
+    const int r = class_to_local[qcls], c = class_to_local[tcls];
+    if (r < 0 || r >= n_local || c < 0 || c >= n_local) { atomicExch(bad, 1); return; }
+    atomicAdd(&mat[r * n_local + c], 1u);
+}
+
+__global__ void bootstrap_kernel(const int* __restrict__ knn3, long long nq, int nr_query_poses,
+                                 int nr_tmpl_poses, int* __restrict__ out, int* __restrict__ out_len) {
+    const long long qi = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (qi >= nq) return;
+    const int query_object = (int)(qi / nr_query_poses);
+    int o[4] = {-1, -1, -1, -1};
+    int len = 0;
+    for (int nn = 0; nn < 3; ++nn) {
+        const int ti = knn3[qi * 3 + nn];
+        const int obj = ti / nr_tmpl_poses, pose = ti % nr_tmpl_poses;
+        if (nn == 0) { o[0] = obj; o[1] = pose; len = 2; }
+        else if (len < 4 && obj != query_object) { o[len] = obj; o[len + 1] = pose; len += 2; }
+    }
+    out[qi * 4 + 0] = o[0]; out[qi * 4 + 1] = o[1]; out[qi * 4 + 2] = o[2]; out[qi * 4 + 3] = o[3];
+    out_len[qi] = len;
+}
+
+__global__ void accuracy_kernel(const int* __restrict__ max_sim0, const int* __restrict__ boot, long long nq,
+                                int nr_query_poses, unsigned long long* __restrict__ counts) {
+    const long long qi = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    int intra = 0, inter = 0;
+    if (qi < nq) {
+        intra = max_sim0[qi] == boot[qi * 4 + 1];
+        inter = boot[qi * 4 + 0] == (int)(qi / nr_query_poses);
+    }
+    const unsigned bi = __ballot_sync(0xffffffffu, intra), be = __ballot_sync(0xffffffffu, inter);
+    if ((threadIdx.x & 31) == 0) {
+        if (bi) atomicAdd(&counts[0], (unsigned long long)__popc(bi));
+        if (be) atomicAdd(&counts[1], (unsigned long long)__popc(be));
+    }
+}
+
+}  // namespace
+
+/* all pointers device-resident; out_host: n_bins + 2 floats */
+int pose_histogram_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
+                       const int* rot_inv, int n_rot, const float* bins, int n_bins, float* out_host) {
+    PE_REQUIRE(db->d_labels != nullptr, "DB was created without labels");
+    PE_REQUIRE(n_bins >= 2 && n_bins <= kMaxBins, "n_bins=%d outside 2..%d", n_bins, kMaxBins);
+    PE_REQUIRE(k >= 1 && k <= 32, "k=%d outside 1..32", k);
+    PE_REQUIRE(db->poses_per_object > 0, "poses_per_object not set");
+    PE_CUDA(cudaSetDevice(db->device));
+    /* scratch: [counts: 16 x u64][sum: f64][median: f32 (+pad)][rot_inv: n_rot x i32][bins: 16 x f32][err: nq x f32] */
+    const size_t off_sum = kMaxBins * 8, off_med = off_sum + 8, off_rot = off_med + 8;
+    const size_t off_bins = off_rot + (((size_t)n_rot * 4 + 15) & ~(size_t)15);
+    const size_t off_err = off_bins + kMaxBins * 4;
+    PE_CHECK(db->scratch.reserve(off_err + (size_t)(nq > 0 ? nq : 1) * 4));
+    char* base = db->scratch.as<char>();
+    PE_CUDA(cudaMemsetAsync(base, 0, off_rot, db->stream));
+    if (n_rot > 0) PE_CUDA(cudaMemcpyAsync(base + off_rot, rot_inv, (size_t)n_rot * 4, cudaMemcpyHostToDevice, db->stream));
+    PE_CUDA(cudaMemcpyAsync(base + off_bins, bins, (size_t)n_bins * 4, cudaMemcpyHostToDevice, db->stream));
+    unsigned long long* d_counts = reinterpret_cast<unsigned long long*>(base);
+    double* d_sum = reinterpret_cast<double*>(base + off_sum);
+    float* d_med = reinterpret_cast<float*>(base + off_med);
+    float* d_err = reinterpret_cast<float*>(base + off_err);
+    if (nq > 0) {
+        pose_err_kernel<<<(unsigned)((nq + kPoseWarps - 1) / kPoseWarps), kPoseWarps * 32, 0, db->stream>>>(
+            d_knn_idx, nq, k, d_q_labels, db->d_labels, db->t_total, db->poses_per_object,
+            reinterpret_cast<const int*>(base + off_rot), n_rot, reinterpret_cast<const float*>(base + off_bins),
+            n_bins, d_err, d_counts, d_sum);
+        PE_LAUNCHED();
+    }
+    median_select_kernel<<<1, 1024, 0, db->stream>>>(d_err, nq, d_med);
+    PE_LAUNCHED();
+    unsigned long long h_counts[kMaxBins];
+    double h_sum = 0.0;
+    float h_med = 0.f;
+    PE_CUDA(cudaMemcpyAsync(h_counts, d_counts, sizeof(h_counts), cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaMemcpyAsync(&h_sum, d_sum, 8, cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaMemcpyAsync(&h_med, d_med, 4, cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaStreamSynchronize(db->stream));
+    /* normalisation of src/networkevaluator.cpp:342-346 */
+    const float total = (float)h_counts[0] + (float)h_counts[n_bins - 1];
+    for (int b = 0; b < n_bins; ++b) out_host[b] = (float)h_counts[b] / total;
+    out_host[n_bins] = (float)(h_sum / (double)nq);
+    out_host[n_bins + 1] = h_med;
+    return PE_OK;
+}
+
+int pose_confusion_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
+                       const int* class_to_local, int n_classes, int n_local, int nr_test_poses,
+                       float* out_host) {
+    PE_REQUIRE(db->d_labels != nullptr, "DB was created without labels");
+    PE_REQUIRE(n_classes > 0 && n_local > 0 && k >= 1, "bad confusion-matrix arguments");
+    PE_CUDA(cudaSetDevice(db->device));
+    const size_t n_mat = (size_t)n_local * n_local;
+    const size_t off_map = (n_mat * 4 + 16 + 15) & ~(size_t)15;
+    PE_CHECK(db->scratch.reserve(off_map + (size_t)n_classes * 4));
+    char* base = db->scratch.as<char>();
+    PE_CUDA(cudaMemsetAsync(base, 0, off_map, db->stream));
+    PE_CUDA(cudaMemcpyAsync(base + off_map, class_to_local, (size_t)n_classes * 4, cudaMemcpyHostToDevice, db->stream));
+    unsigned int* d_mat = reinterpret_cast<unsigned int*>(base);
+    int* d_bad = reinterpret_cast<int*>(base + n_mat * 4);
+    if (nq > 0) {
+        confusion_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, db->stream>>>(
+            d_knn_idx, nq, k, d_q_labels, db->d_labels, db->t_total, reinterpret_cast<const int*>(base + off_map),
+            n_classes, n_local, d_mat, d_bad);
+        PE_LAUNCHED();
+    }
+    std::vector<unsigned int> h(n_mat + 1);
+    PE_CUDA(cudaMemcpyAsync(h.data(), d_mat, (n_mat + 1) * 4, cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaStreamSynchronize(db->stream));
+    PE_REQUIRE(h[n_mat] == 0, "class label outside class_to_local");
+    for (size_t i = 0; i < n_mat; ++i) out_host[i] = (float)h[i] / (float)nr_test_poses; /* :242-244 */
+    return PE_OK;
+}
+
+int pose_bootstrap_dev(pe_db* db, const int* d_knn3, int64_t nq, int nr_query_poses, int* d_out, int* d_len) {
+    PE_REQUIRE(nr_query_poses > 0 && db->poses_per_object > 0, "pose counts not set");
+    PE_CUDA(cudaSetDevice(db->device));
+    if (nq == 0) return PE_OK;
+    bootstrap_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, db->stream>>>(d_knn3, nq, nr_query_poses,
+                                                                         db->poses_per_object, d_out, d_len);
+    PE_LAUNCHED();
+    return PE_OK;
+}
+
+int pose_accuracy_dev(pe_db* db, const int* d_max_sim0, const int* d_boot, int64_t nq, int nr_query_poses,
+                      float* intra_pct, float* inter_pct) {
+    PE_REQUIRE(nr_query_poses > 0, "nr_query_poses not set");
+    PE_CUDA(cudaSetDevice(db->device));
+    PE_CHECK(db->scratch2.reserve(16));
+    unsigned long long* d_c = db->scratch2.as<unsigned long long>();
+    PE_CUDA(cudaMemsetAsync(d_c, 0, 16, db->stream));
+    if (nq > 0) {
+        accuracy_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, db->stream>>>(d_max_sim0, d_boot, nq, nr_query_poses, d_c);
+        PE_LAUNCHED();
+    }
+    unsigned long long h[2];
+    PE_CUDA(cudaMemcpyAsync(h, d_c, 16, cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaStreamSynchronize(db->stream));
+    *intra_pct = (float)h[0] / (float)nq * 100; /* src/networkevaluator.cpp:173-174 */
+    *inter_pct = (float)h[1] / (float)nq * 100;
+    return PE_OK;
+}
+
+}  // namespace pe

@@ -136,6 +136,7 @@ PE_API int pe_synth_labels(uint64_t seed, int64_t first_index, int64_t n, int po
  * desc[32*w+j] > 0).  New behaviour: the reference never thresholds bin_ip2
  * (SURVEY 0); defined in SURVEY 7. */
 PE_API int pe_binarize(pe_net* net, const float* desc, int64_t n, int dim, uint32_t* bits);
+PE_API int pe_binarize_dev(pe_net* net, const float* d_desc, int64_t n, int dim, uint32_t* d_bits);
 
 /* ------------------------------------------------------------------ db --- */
 /* Replaces `matcher = DescriptorMatcher::create("BruteForce"); matcher->add(DBfeats)`
@@ -179,6 +180,10 @@ PE_API int pe_knn_hamming_dev(pe_db* db, const uint32_t* d_qcodes, int64_t nq, i
 PE_API int pe_histogram(pe_db* db, const int32_t* knn_idx, const float* q_labels, int64_t nq,
                         int k, const int* rot_inv, int n_rot, const float* bins, int n_bins,
                         float* out);
+/* same with knn_idx and q_labels resident on the DB's device (out stays a host pointer) */
+PE_API int pe_histogram_dev(pe_db* db, const int32_t* d_knn_idx, const float* d_q_labels, int64_t nq,
+                            int k, const int* rot_inv, int n_rot, const float* bins, int n_bins,
+                            float* out);
 /* body of computeConfusionMatrix after knnMatch (src/networkevaluator.cpp:199-245).
  * class_to_local[c] = local_index[models[c]] (:215-216); out: n_local x n_local,
  * row-normalised by nr_test_poses. */

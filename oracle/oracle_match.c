@@ -10,6 +10,9 @@
  *       scans templates in order and only replaces on strictly smaller).
  *   Eigen 3.x Quaternionf::angularDistance   - src/networkevaluator.cpp:297,331:
  *       2*acos(min(1,|a.b|))  (3.2 omits the clamp and returns NaN past 1; we clamp).
+ *       std::acos(float) is restated as the correctly rounded value (float)acos((double)x):
+ *       any libm acosf is within 1 ulp of it, and it is reproducible bit for bit on the GPU,
+ *       so the strict `<` of the exact-match scan (:331) agrees between oracle and CUDA.
  *   Eigen toRotationMatrix()(2,2)            - src/networkevaluator.cpp:299:
  *       tx=2x, ty=2y, txx=tx*x, tyy=ty*y, R22 = 1-(txx+tyy).
  * Own glue logic restated from src/networkevaluator.cpp:153-175,199-245,269-355 and
@@ -161,6 +164,8 @@ void orc_merge_topk_i32(const int32_t* idx, const int32_t* dist, int n_shards, i
 }
 
 /* ------------------------------------------------------------------ Eigen --- */
+static inline float acos_cr(float x) { return (float)acos((double)x); }
+
 float orc_angular_distance(const float* a, const float* b) {
     float d = a[0] * b[0];
     d = d + a[1] * b[1];
@@ -168,7 +173,7 @@ float orc_angular_distance(const float* a, const float* b) {
     d = d + a[3] * b[3];
     d = fabsf(d);
     if (d > 1.0f) d = 1.0f;
-    return 2.0f * acosf(d);
+    return 2.0f * acos_cr(d);
 }
 
 float orc_rot22(const float* q) {
@@ -210,7 +215,7 @@ void orc_histogram(const int32_t* knn_idx, int64_t nq, int k, const float* q_lab
             if (rot_inv[(int)ql[0]] == 0) {
                 d = to_degrees(orc_angular_distance(qquat, tl + 1)); /* :297 */
             } else {
-                d = to_degrees(fabsf(acosf(orc_rot22(qquat)) - acosf(orc_rot22(tl + 1)))); /* :299 */
+                d = to_degrees(fabsf(acos_cr(orc_rot22(qquat)) - acos_cr(orc_rot22(tl + 1)))); /* :299 */
                 if (isnan(d)) d = FLT_MAX;                                                 /* :300 */
             }
             if (d >= best) continue; /* :303 keeps the earlier neighbour on ties */

@@ -29,3 +29,17 @@ def po():
     from oracle import pyoracle
     pyoracle.build()
     return pyoracle
+
+
+@pytest.fixture(scope="session")
+def capi():
+    mod = importlib.import_module("3dposeestimation_b200.capi")
+    mod.build()
+    return mod
+
+
+@pytest.fixture(scope="session")
+def gpu(capi):
+    if capi.device_count() < 1:
+        pytest.fail("GPU test selected but no CUDA device is visible (there is no CPU fallback)")
+    return capi

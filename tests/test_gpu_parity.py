@@ -1,0 +1,382 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle and the committed golden
+vectors.  Everything here needs a B200: `pytest -m gpu`.
+
+Acceptance (BASELINE.json / SURVEY 8c):
+  descriptors   |a-b| <= 1e-4 * row max-abs (fp32)
+  L2 kNN        indices bit-exact except where the oracle's k/k+1 distance gap is < 1e-4 relative;
+                distances within 1e-6 relative (they restate the same fp32 expression)
+  Hamming       indices and distances bit-exact
+  histogram     bin fractions exact for identical indices, mean / median within 1e-3 degrees
+"""
+import numpy as np
+import pytest
+
+from tests import netdefs
+from tests.golden import make_golden as mg
+
+pytestmark = pytest.mark.gpu
+
+DESC_TOL = 1e-4
+BINS = np.array([-1, 0, 10, 20, 40, 180], np.float32)
+
+
+def rowscale_err(a, b):
+    scale = np.abs(b).max(axis=-1, keepdims=True) + 1e-30
+    return float((np.abs(a - b) / scale).max())
+
+
+def make_net(gpu, po, synth, name, seed):
+    ref = po.parse_prototxt(netdefs.prototxt(name))
+    blobs = synth.make_blobs(ref.blob_names, ref.blob_shapes, seed, mode=1)
+    net = gpu.Net(text=netdefs.prototxt(name))
+    net.set_blobs(blobs)
+    return net, po.OracleNet(ref, blobs), ref
+
+
+# ---------------------------------------------------------------------------- forward ---
+@pytest.mark.parametrize("vi,name", list(enumerate(netdefs.VARIANTS)))
+def test_forward_matches_oracle_and_golden(gpu, po, synth, golden, vi, name):
+    net, oracle, ref = make_net(gpu, po, synth, name, synth.BASE_SEED + vi)
+    # the three golden patches (torch fp32 / fp64 outputs committed in tests/golden)
+    patches = synth.make_patches(synth.BASE_SEED, 100 * vi, 3, ref.channels, 2)
+    d = net.compute_descriptors(patches)
+    assert d.shape == (3, ref.desc_dim)
+    assert rowscale_err(d, golden[f"fwd32_{name}"]) < DESC_TOL
+    assert rowscale_err(d.astype(np.float64), golden[f"fwd64_{name}"]) < DESC_TOL
+    # more patches than SMs, so the persistent CTAs loop, and an odd count
+    n = 333
+    big = synth.make_patches(synth.BASE_SEED + 1, 7 * vi, n, ref.channels, 9)
+    got = net.compute_descriptors(big)
+    want = oracle.forward(big)
+    assert rowscale_err(got, want) < DESC_TOL
+    # batch composition must not matter (src/networkevaluator.cpp:26-30: partial last batch)
+    again = np.concatenate([net.compute_descriptors(big[:5]), net.compute_descriptors(big[5:])])
+    assert np.array_equal(got, again)
+    assert net.compute_descriptors(big[:0]).shape == (0, ref.desc_dim)
+
+
+def test_forward_rejects_wrong_channel_count(gpu):
+    net = gpu.Net(named="manifold_rgbdnor_16")
+    net.fill(1, 1)
+    with pytest.raises(gpu.PoseError) as e:
+        net.compute_descriptors(np.zeros((2, 64, 64, 4), np.float32))
+    assert e.value.code == gpu.PE_ERR_INVALID
+
+
+def test_forward_device_entry_and_chunking(gpu, po, synth):
+    """device-resident patches, more than one 4096-patch chunk, unaligned tail"""
+    net, oracle, ref = make_net(gpu, po, synth, "manifold_rgbdnor_16", 99)
+    n = 4096 + 37
+    d_patches = gpu.DeviceArray((n, 64, 64, 7))
+    net.synth_patches_dev(synth.BASE_SEED, 1000, n, 50, d_patches)
+    d_out = gpu.DeviceArray((n, 16))
+    net.compute_descriptors_dev(d_patches, n, d_out)
+    net.sync()
+    got = d_out.to_host()
+    # device generator == numpy generator for the same sample indices
+    pick = np.array([0, 1, 4095, 4096, n - 1])
+    host_patches = np.concatenate([synth.make_patches(synth.BASE_SEED, 1000 + int(i), 1, 7, 50) for i in pick])
+    dev_patches = d_patches.to_host()[pick]
+    np.testing.assert_allclose(dev_patches, host_patches, rtol=0, atol=1e-6)
+    want = oracle.forward(dev_patches)
+    assert rowscale_err(got[pick], want) < DESC_TOL
+    # rows computed inside the big launch equal rows computed alone
+    alone = net.compute_descriptors(dev_patches)
+    assert np.array_equal(alone, got[pick])
+    assert np.isfinite(got).all()
+
+
+def test_weights_can_be_replaced(gpu, po, synth):
+    net, oracle, ref = make_net(gpu, po, synth, "manifold_rgbd_16", 5)
+    x = synth.make_patches(3, 0, 4, 7, 2)
+    a = net.compute_descriptors(x)
+    blobs2 = synth.make_blobs(ref.blob_names, ref.blob_shapes, 6, mode=1)
+    net.set_blobs(blobs2)
+    b = net.compute_descriptors(x)
+    assert rowscale_err(b, po.OracleNet(ref, blobs2).forward(x)) < DESC_TOL
+    assert not np.allclose(a, b)
+
+
+def test_binarize_matches_oracle(gpu, po):
+    rng = np.random.default_rng(5)
+    for dim in (128, 16, 3, 64, 40):
+        d = rng.standard_normal((77, dim)).astype(np.float32)
+        d[3, : min(dim, 5)] = 0.0          # exactly zero is not > 0
+        net = gpu.Net(named="manifold")
+        assert np.array_equal(net.binarize(d), po.binarize(d))
+
+
+# -------------------------------------------------------------------------------- kNN ---
+def check_knn(idx, dist, oi, od, gap, tol=1e-4):
+    """indices bit-exact except where the oracle's k/k+1 gap is below tol"""
+    assert idx.shape == oi.shape
+    finite = np.isfinite(od)
+    np.testing.assert_allclose(dist[finite], od[finite], rtol=2e-6, atol=1e-7)
+    assert np.array_equal(np.isfinite(dist), finite)
+    bad = (idx != oi).any(axis=1)
+    if bad.any():
+        # a row may differ only through near-ties: inner gaps or the k/k+1 gap below tol
+        inner = np.diff(od, axis=1) / np.maximum(od[:, 1:], 1e-30) if od.shape[1] > 1 else np.full((len(od), 1), np.inf)
+        near = (gap < tol) | (np.nan_to_num(inner, nan=np.inf).min(axis=1) < tol)
+        assert np.all(near[bad]), f"{bad.sum()} rows differ, {np.sum(bad & ~near)} of them without a near-tie"
+    return float(bad.mean())
+
+
+@pytest.mark.parametrize("dim", [16, 3, 64])
+def test_knn_l2_matches_cv2_golden(gpu, synth, golden, dim):
+    q, t = mg.knn_problem(synth.BASE_SEED + dim, 64, 512, dim)
+    t[100] = t[7]
+    t[300] = t[7]
+    q[5] = t[7]
+    db = gpu.TemplateDB(desc=t)
+    idx, dist = db.knn(q, 5)
+    gi, gd = golden[f"knn_idx_{dim}"], golden[f"knn_dist_{dim}"]
+    np.testing.assert_allclose(dist, gd, rtol=2e-6, atol=1e-7)
+    assert list(idx[5, :3]) == [7, 100, 300] and list(dist[5, :3]) == [0, 0, 0]
+    mism = idx != gi
+    assert np.all(np.abs(dist[mism] - gd[mism]) <= 2e-6 * np.abs(gd[mism])) and mism.sum() <= 2
+
+
+@pytest.mark.parametrize("dim,nq,nt,k", [(16, 1500, 19500, 1), (16, 700, 5000, 5), (16, 64, 333, 3), (3, 2000, 19500, 1),
+                                         (3, 300, 1000, 5), (64, 300, 3000, 3), (128, 200, 2500, 5), (16, 130, 70000, 16),
+                                         (16, 1, 1000, 1), (7, 50, 400, 2)])
+def test_knn_l2_matches_oracle(gpu, po, synth, dim, nq, nt, k):
+    _, t, _, _ = mg.eval_problem(synth.BASE_SEED + dim + k, 10, (nt + 9) // 10, 3, dim)
+    t = t[:nt]
+    rng = np.random.default_rng(nq)
+    q = t[rng.integers(0, nt, nq)] + 0.3 * rng.standard_normal((nq, dim)).astype(np.float32)
+    t[nt // 2] = t[3]                       # an exact duplicate row
+    q[0] = t[3]
+    db = gpu.TemplateDB(desc=t)
+    idx, dist = db.knn(q, k)
+    oi, od, gap = po.knn_l2(q, t, k, want_gap=True)
+    frac = check_knn(idx, dist, oi, od, gap)
+    assert frac < 0.01
+    assert idx[0, 0] == 3 and dist[0, 0] == 0
+    if k > 1:
+        assert idx[0, 1] == nt // 2 and dist[0, 1] == 0      # tie -> lower index first
+    assert np.all(np.diff(dist, axis=1) >= 0)
+
+
+def test_knn_l2_edge_cases(gpu, po):
+    rng = np.random.default_rng(0)
+    t = rng.standard_normal((3, 16)).astype(np.float32)
+    q = rng.standard_normal((2, 16)).astype(np.float32)
+    db = gpu.TemplateDB(desc=t)
+    idx, dist = db.knn(q, 5)                      # fewer templates than k -> -1 / inf padding
+    oi, od = po.knn_l2(q, t, 5)
+    assert np.array_equal(idx, oi) and np.array_equal(dist, od)
+    assert db.knn(q[:0], 1)[0].shape == (0, 1)
+    same = np.tile(t[:1], (40, 1))                # all rows identical: indices come out 0,1,2,...
+    idx, dist = gpu.TemplateDB(desc=same).knn(q[:1], 8)
+    assert list(idx[0]) == list(range(8)) and len(set(dist[0])) == 1
+    with pytest.raises(gpu.PoseError):
+        db.knn(q, 17)
+    with pytest.raises(gpu.PoseError):
+        db.knn_hamming(np.zeros((1, 4), np.uint32), 1)
+
+
+def test_knn_l2_clustered_descriptors(gpu, po):
+    """descriptors far from the origin and tightly clustered: the |t|^2-2qt ranking pass loses
+    precision there, the exact refine must still return the oracle's neighbours"""
+    rng = np.random.default_rng(11)
+    t = (5.0 + 0.01 * rng.standard_normal((20000, 16))).astype(np.float32)
+    q = (5.0 + 0.01 * rng.standard_normal((256, 16))).astype(np.float32)
+    idx, dist = gpu.TemplateDB(desc=t).knn(q, 3)
+    oi, od, gap = po.knn_l2(q, t, 3, want_gap=True)
+    assert check_knn(idx, dist, oi, od, gap) < 0.05
+
+
+def test_knn_hamming_matches_oracle_and_golden(gpu, po, synth, golden):
+    codes_t = (synth.uniform01(synth.BASE_SEED, 50, 512 * 4) * 2 ** 24).astype(np.uint32).reshape(512, 4)
+    codes_t = codes_t * np.uint32(257) ^ (codes_t >> np.uint32(3))
+    codes_q = codes_t[(np.arange(64) * 5) % 512] ^ (np.uint32(1) << (np.arange(64, dtype=np.uint32) % 32))[:, None]
+    idx, dist = gpu.TemplateDB(codes=codes_t).knn_hamming(codes_q, 5)
+    assert np.array_equal(dist, golden["ham_dist"]) and np.array_equal(idx[:, 0], golden["ham_idx"][:, 0])
+    oi, od = po.knn_hamming(codes_q, codes_t, 5)
+    assert np.array_equal(idx, oi) and np.array_equal(dist, od)
+    rng = np.random.default_rng(2)
+    for words, nq, nt, k in ((4, 1100, 30000, 5), (1, 300, 5000, 3), (2, 64, 999, 1), (8, 100, 3000, 4), (4, 5, 3, 4)):
+        t = rng.integers(0, 2 ** 32, (nt, words), dtype=np.uint64).astype(np.uint32)
+        if words == 1:
+            t &= np.uint32(0xFFFF)        # 16-bit codes: many equal distances, ties -> lower index
+        q = t[rng.integers(0, nt, nq)] ^ rng.integers(0, 8, (nq, words), dtype=np.uint64).astype(np.uint32)
+        idx, dist = gpu.TemplateDB(codes=t).knn_hamming(q, k)
+        oi, od = po.knn_hamming(q, t, k)
+        assert np.array_equal(idx, oi), (words, nq, nt, k)
+        assert np.array_equal(dist, od)
+
+
+def test_sharded_scan_plus_merge_equals_unsharded(gpu, po):
+    """three row shards scanned separately (global indices via row_offset), merged with the oracle's
+    merge == one unsharded scan.  (The NCCL all-gather itself is covered by bench.py --gpus N.)"""
+    rng = np.random.default_rng(3)
+    t = rng.standard_normal((3001, 16)).astype(np.float32)
+    t[2000] = t[10]
+    q = np.concatenate([rng.standard_normal((99, 16)).astype(np.float32), t[10:11]])
+    full_i, full_d = gpu.TemplateDB(desc=t).knn(q, 4)
+    bounds = [0, 1000, 1500, 3001]
+    ci, cd = [], []
+    for a, b in zip(bounds[:-1], bounds[1:]):
+        i, d = gpu.TemplateDB(desc=t[a:b], row_offset=a, t_total=3001).knn(q, 4)
+        assert i.min() >= a and i.max() < b
+        ci.append(i)
+        cd.append(d)
+    mi, md = po.merge_topk(np.stack(ci), np.stack(cd))
+    assert np.array_equal(mi, full_i) and np.array_equal(md, full_d)
+    # single-rank "sharded" entry point degenerates to the local scan
+    si, sd = gpu.TemplateDB(desc=t).knn_sharded(None, q, 4)
+    assert np.array_equal(si, full_i) and np.array_equal(sd, full_d)
+
+
+# ------------------------------------------------------------------- pose reductions ---
+@pytest.mark.parametrize("k", [1, 3, 5])
+def test_histogram_confusion_match_oracle_and_golden(gpu, po, synth, golden, k):
+    n_obj, nr_t, nr_q, dim = 6, 40, 15, 16
+    q, t, ql, tl = mg.eval_problem(synth.BASE_SEED, n_obj, nr_t, nr_q, dim)
+    rot_inv = np.array([0, 0, 1, 0, 2, 0], np.int32)
+    db = gpu.TemplateDB(desc=t, labels_all=tl, poses_per_object=nr_t)
+    idx, _ = db.knn(q, k)
+    assert np.array_equal(idx, golden[f"eval_idx_k{k}"])
+    h = db.histogram(idx, ql, rot_inv, BINS)
+    ho = po.histogram(idx, ql, tl, nr_t, rot_inv, BINS)
+    np.testing.assert_array_equal(h[:6], ho[:6])
+    np.testing.assert_allclose(h[6:], ho[6:], rtol=0, atol=1e-3)
+    np.testing.assert_allclose(h[:6], golden[f"eval_hist_k{k}"][:6], rtol=0, atol=1e-7)
+    np.testing.assert_allclose(h[6:], golden[f"eval_hist_k{k}"][6:], rtol=0, atol=1e-3)
+    c2l = np.arange(n_obj, dtype=np.int32)[::-1].copy()
+    cm = db.confusion(idx, ql, c2l, n_obj, nr_q)
+    assert np.array_equal(cm, golden[f"eval_conf_k{k}"])
+    assert np.array_equal(cm, po.confusion(idx, ql, tl, c2l, n_obj, nr_q))
+
+
+def test_histogram_larger_random_problem(gpu, po, synth):
+    """random neighbours (many misclassified, many non-exact), all rotInv kinds, big pose count"""
+    n_obj, nr_t, nr_q = 20, 700, 150
+    tl = synth.make_labels(77, n_obj, nr_t)
+    src = (np.arange(nr_q) * 13) % nr_t
+    ql = synth.perturb_labels(tl.reshape(n_obj, nr_t, 8)[:, src].reshape(-1, 8), 78, max_deg=25.0)
+    rot_inv = synth.rot_inv_pattern(n_obj)
+    rng = np.random.default_rng(9)
+    nq, k = n_obj * nr_q, 5
+    own = (np.repeat(np.arange(n_obj), nr_q) * nr_t)[:, None] + rng.integers(0, nr_t, (nq, k))
+    anyc = rng.integers(0, n_obj * nr_t, (nq, k))
+    idx = np.where(rng.random((nq, k)) < 0.5, own, anyc).astype(np.int32)
+    idx[::7, 0] = (np.repeat(np.arange(n_obj), nr_q) * nr_t + np.tile(src, n_obj))[::7]   # the true source template
+    db = gpu.TemplateDB(desc=np.zeros((4, 16), np.float32), labels_all=tl, poses_per_object=nr_t, t_total=n_obj * nr_t)
+    h = db.histogram(idx, ql, rot_inv, BINS)
+    ho, err = po.histogram(idx, ql, tl, nr_t, rot_inv, BINS, want_err=True)
+    np.testing.assert_array_equal(h[:6], ho[:6])
+    np.testing.assert_allclose(h[6:], ho[6:], rtol=0, atol=1e-3)
+    assert 0 < ho[0] < 1 and 0 < ho[1] < 1 and (err < 0).any()
+    c2l = rng.permutation(n_obj).astype(np.int32)
+    assert np.array_equal(db.confusion(idx, ql, c2l, n_obj, nr_q), po.confusion(idx, ql, tl, c2l, n_obj, nr_q))
+
+
+def test_histogram_edge_cases(gpu, po, synth):
+    tl = synth.make_labels(1, 2, 4)
+    ql = tl[[0, 5]].copy()
+    db = gpu.TemplateDB(desc=np.zeros((8, 16), np.float32), labels_all=tl, poses_per_object=4)
+    for idx in (np.array([[0], [1]], np.int32), np.array([[4], [1]], np.int32)):
+        h = db.histogram(idx, ql, np.zeros(2, np.int32), BINS)
+        ho = po.histogram(idx, ql, tl, 4, np.zeros(2, np.int32), BINS)
+        np.testing.assert_array_equal(h, ho)      # incl. NaN median when nobody matched
+    with pytest.raises(gpu.PoseError):
+        db.histogram(np.array([[0]], np.int32), ql[:1], np.zeros(0, np.int32), BINS)   # class without rotInv entry
+
+
+def test_bootstrap_and_accuracy_match_oracle(gpu, po, golden):
+    db = gpu.TemplateDB(desc=np.zeros((240, 16), np.float32), poses_per_object=40)
+    out, ln = db.knn_bootstrap(golden["eval_idx_k3"], 15)
+    assert np.array_equal(out, golden["eval_boot"]) and np.array_equal(ln, golden["eval_boot_len"])
+    rng = np.random.default_rng(4)
+    knn3 = rng.integers(0, 240, (900, 3)).astype(np.int32)
+    out, ln = db.knn_bootstrap(knn3, 150)
+    oo, ol = po.knn_bootstrap(knn3, 150, 40)
+    assert np.array_equal(out, oo) and np.array_equal(ln, ol)
+    ms = rng.integers(0, 40, 900).astype(np.int32)
+    ms[::3] = out[::3, 1]
+    assert db.knn_accuracy(ms, out, 150) == po.knn_accuracy(ms, out, 150)
+
+
+# ------------------------------------------------------- config 1 end to end ---
+def test_config1_manifold_15x1300_end_to_end(gpu, po, synth):
+    """BASELINE.json configs[0]: manifold.prototxt (C=4, D=3), 15 objects x 1300 templates, 15 x 600
+    queries, 1-NN + histogram: CUDA forward -> CUDA kNN -> CUDA histogram vs the oracle chain."""
+    n_obj, nr_t, nr_q = 15, 1300, 600
+    net, oracle, ref = make_net(gpu, po, synth, "manifold", synth.BASE_SEED)
+    nt, nq = n_obj * nr_t, n_obj * nr_q
+    d_p = gpu.DeviceArray((nt + nq, 64, 64, 4))
+    net.synth_patches_dev(synth.BASE_SEED, 0, nt, nr_t, d_p)
+    net.synth_patches_dev(synth.BASE_SEED + 1, 0, nq, nr_q, d_p, out_offset=nt)   # same classes, other pixels
+    d_d = gpu.DeviceArray((nt + nq, 3))
+    net.compute_descriptors_dev(d_p, nt + nq, d_d)
+    net.sync()
+    desc = d_d.to_host()
+    sub = np.r_[0:40, nt - 40:nt + 40, nt + nq - 40:nt + nq]
+    want = oracle.forward(d_p.to_host()[sub])
+    assert rowscale_err(desc[sub], want) < DESC_TOL
+    tl = synth.make_labels(synth.BASE_SEED, n_obj, nr_t)
+    src = (np.arange(nr_q) * 2) % nr_t
+    ql = synth.perturb_labels(tl.reshape(n_obj, nr_t, 8)[:, src].reshape(-1, 8), synth.BASE_SEED)
+    db = gpu.TemplateDB(desc=desc[:nt], labels_all=tl, poses_per_object=nr_t)
+    idx, dist = db.knn(desc[nt:], 1)
+    oi, od, gap = po.knn_l2(desc[nt:], desc[:nt], 1, want_gap=True)
+    excluded = check_knn(idx, dist, oi, od, gap)
+    assert excluded < 0.10          # >= 90 % agreement is the BASELINE.json target
+    rot_inv = np.array([0, 0, 1, 0, 0, 0, 2, 0, 0, 2, 2, 0, 0, 0, 0], np.int32)   # reference config.ini:10
+    h = db.histogram(idx, ql, rot_inv, BINS)
+    ho = po.histogram(idx, ql, tl, nr_t, rot_inv, BINS)
+    np.testing.assert_array_equal(h[:6], ho[:6])
+    np.testing.assert_allclose(h[6:], ho[6:], rtol=0, atol=1e-3)
+
+
+# --------------------------------------------------- full-size properties (1 M templates) ---
+def test_full_size_db_properties(gpu, synth):
+    """BASELINE.json 1M-template DB: properties that need no CPU pass over the DB"""
+    rng = np.random.default_rng(21)
+    nt, dim, nq = 1_000_200, 16, 4096
+    t = rng.standard_normal((nt, dim)).astype(np.float32)
+    db = gpu.TemplateDB(desc=t)
+    rows = rng.integers(0, nt, nq)
+    idx, dist = db.knn(t[rows], 1)
+    assert np.array_equal(idx[:, 0], rows) and np.all(dist == 0)          # every row is its own 1-NN
+    q = t[rows] + 0.05 * rng.standard_normal((nq, dim)).astype(np.float32)
+    idx5, dist5 = db.knn(q, 5)
+    assert np.all(np.diff(dist5, axis=1) >= 0)
+    # reported distances are the exact expression on the reported rows
+    ref = np.sqrt(((q[:, None, :].astype(np.float64) - t[idx5]) ** 2).sum(-1))
+    np.testing.assert_allclose(dist5, ref, rtol=1e-5)
+    # no unreported template is closer than the k-th reported one (checked on a query subset)
+    for qi in range(0, nq, 512):
+        d_all = np.sqrt(((t - q[qi]) ** 2).sum(1))
+        kth = np.partition(d_all, 4)[4]
+        assert abs(kth - dist5[qi, 4]) <= 1e-5 * kth
+    # sharding by rows does not change the answer
+    half = nt // 2
+    a_i, a_d = gpu.TemplateDB(desc=t[:half], t_total=nt).knn(q[:512], 5)
+    b_i, b_d = gpu.TemplateDB(desc=t[half:], row_offset=half, t_total=nt).knn(q[:512], 5)
+    both_i, both_d = np.concatenate([a_i, b_i], 1), np.concatenate([a_d, b_d], 1)
+    order = np.lexsort((both_i, both_d), axis=1) if False else np.argsort(both_d, axis=1, kind="stable")
+    merged = np.take_along_axis(both_i, order, 1)[:, :5]
+    assert np.array_equal(merged, idx5[:512])
+
+
+def test_full_size_hamming_properties(gpu):
+    rng = np.random.default_rng(22)
+    nt, nq = 1_000_200, 2048
+    t = rng.integers(0, 2 ** 32, (nt, 4), dtype=np.uint64).astype(np.uint32)
+    db = gpu.TemplateDB(codes=t)
+    rows = rng.integers(0, nt, nq)
+    flip = np.zeros((nq, 4), np.uint32)
+    flip[:, 1] = 1 << 7
+    idx, dist = db.knn_hamming(t[rows] ^ flip, 5)
+    assert np.array_equal(idx[:, 0], rows) and np.all(dist[:, 0] == 1)
+    assert np.all(np.diff(dist, axis=1) >= 0)
+    for qi in range(0, nq, 256):          # full brute-force check on a query subset
+        x = t ^ (t[rows[qi]] ^ flip[qi])
+        d_all = np.zeros(nt, np.int64)
+        for w in range(4):
+            d_all += np.array([bin(v).count("1") for v in range(256)], np.int64)[x[:, w].view(np.uint8).reshape(-1, 4)].sum(1)
+        order = np.argsort(d_all, kind="stable")[:5]
+        assert np.array_equal(order, idx[qi]) and np.array_equal(d_all[order], dist[qi])
