@@ -56,6 +56,11 @@ SIGNATURES = {
     "pe_timer_stop_db": (C.c_int, [vp, vp]),
     "pe_timer_elapsed_ms": (C.c_int, [vp, fp]),
     "pe_timer_destroy": (None, [vp]),
+    "pe_net_profile": (C.c_int, [vp, C.c_int]),
+    "pe_net_profile_read": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
+    "pe_db_profile": (C.c_int, [vp, C.c_int]),
+    "pe_db_profile_read": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
+    "pe_db_share_stream": (C.c_int, [vp, vp]),
     "pe_net_create_from_prototxt": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(vp)]),
     "pe_net_create_from_string": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(vp)]),
     "pe_net_create_named": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(vp)]),
@@ -98,6 +103,7 @@ SIGNATURES = {
     "pe_comm_info": (C.c_int, [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "pe_comm_allgather_f32": (C.c_int, [vp, vp, C.c_int64, vp]),
     "pe_comm_allreduce_sum_f64": (C.c_int, [vp, vp, C.c_int64]),
+    "pe_comm_allgather_f32_dev": (C.c_int, [vp, vp, vp, C.c_int64, vp]),
     "pe_knn_sharded": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
     "pe_knn_sharded_dev": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
     "pe_knn_hamming_sharded": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
@@ -309,6 +315,16 @@ class Net:
     def sync(self):
         check(lib().pe_net_sync(self.h))
 
+    def profile(self, enable: bool):
+        check(lib().pe_net_profile(self.h, int(enable)))
+
+    def profile_read(self):
+        """(ms per stage [conv1, conv2, fc], bracketed forward calls) since the last read"""
+        ms = (C.c_double * 3)()
+        calls = C.c_int64()
+        check(lib().pe_net_profile_read(self.h, ms, C.byref(calls)))
+        return list(ms), calls.value
+
     def synth_patches_dev(self, seed, first, n, poses_per_object, d_out, out_offset=0):
         ptr = d_out.offset(out_offset * 4096 * self.channels) if isinstance(d_out, DeviceArray) else d_out
         check(lib().pe_synth_patches_dev(self.h, seed, first, n, self.channels, poses_per_object, ptr))
@@ -369,6 +385,19 @@ class TemplateDB:
 
     def sync(self):
         check(lib().pe_db_sync(self.h))
+
+    def share_stream(self, net):
+        check(lib().pe_db_share_stream(self.h, net.h))
+
+    def profile(self, enable: bool):
+        check(lib().pe_db_profile(self.h, int(enable)))
+
+    def profile_read(self):
+        """(ms per stage [scan, select], bracketed kNN calls) since the last read"""
+        ms = (C.c_double * 2)()
+        calls = C.c_int64()
+        check(lib().pe_db_profile_read(self.h, ms, C.byref(calls)))
+        return list(ms), calls.value
 
     def knn(self, queries, k):
         """matcher->knnMatch(queries, matches, k): (idx nq x k, dist nq x k)"""
@@ -470,6 +499,9 @@ class Comm:
         out = np.empty((self.world, a.size), np.float32)
         check(lib().pe_comm_allgather_f32(self.h, _ptr(a), a.size, _ptr(out)))
         return out
+
+    def allgather_f32_dev(self, net, d_send, n, d_recv):
+        check(lib().pe_comm_allgather_f32_dev(self.h, net.h, d_send.ptr, n, d_recv.ptr))
 
     def allreduce_sum_f64(self, a):
         a = np.ascontiguousarray(a, np.float64).copy()

@@ -39,6 +39,34 @@ void DevBuf::release() {
     cap = 0;
 }
 
+int prof_mark(bool on, std::vector<cudaEvent_t>* events, cudaStream_t stream) {
+    if (!on) return PE_OK;
+    cudaEvent_t e;
+    PE_CUDA(cudaEventCreate(&e));
+    PE_CUDA(cudaEventRecord(e, stream));
+    events->push_back(e);
+    return PE_OK;
+}
+
+/* sums elapsed times of consecutive events in groups of `group`, destroys them */
+static int prof_collect(std::vector<cudaEvent_t>* events, int group, double* ms, int64_t* calls) {
+    for (int i = 0; i < group - 1; ++i) ms[i] = 0.0;
+    *calls = 0;
+    const size_t n_groups = events->size() / group;
+    for (size_t g = 0; g < n_groups; ++g) {
+        PE_CUDA(cudaEventSynchronize((*events)[g * group + group - 1]));
+        for (int i = 0; i + 1 < group; ++i) {
+            float t = 0.f;
+            PE_CUDA(cudaEventElapsedTime(&t, (*events)[g * group + i], (*events)[g * group + i + 1]));
+            ms[i] += t;
+        }
+        ++*calls;
+    }
+    for (cudaEvent_t e : *events) cudaEventDestroy(e);
+    events->clear();
+    return PE_OK;
+}
+
 static int set_device_checked(int device) {
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
@@ -264,6 +292,7 @@ void pe_net_destroy(pe_net* net) {
         cudaSetDevice(net->device);
         cudaStreamSynchronize(net->stream);
         cudaStreamSynchronize(net->copy_stream);
+        for (cudaEvent_t e : net->prof_events) cudaEventDestroy(e);
         for (float* p : {net->d_w1, net->d_b1, net->d_s1, net->d_w2, net->d_b2, net->d_s2})
             if (p) cudaFree(p);
         if (net->d_slot) cudaFree(net->d_slot);
@@ -449,6 +478,47 @@ int pe_compute_descriptors(pe_net* net, const float* patches_hwc, int64_t n, int
     return PE_OK;
 }
 
+int pe_net_profile(pe_net* net, int enable) {
+    PE_REQUIRE(net != nullptr, "null net");
+    PE_CHECK(net_ensure_device(net));
+    PE_CUDA(cudaStreamSynchronize(net->stream));
+    double ms[3];
+    int64_t calls;
+    PE_CHECK(prof_collect(&net->prof_events, 4, ms, &calls));
+    net->profile = enable != 0;
+    return PE_OK;
+}
+int pe_net_profile_read(pe_net* net, double ms[3], int64_t* calls) {
+    PE_REQUIRE(net && ms && calls, "null pointer");
+    PE_CHECK(net_ensure_device(net));
+    return prof_collect(&net->prof_events, 4, ms, calls);
+}
+int pe_db_profile(pe_db* db, int enable) {
+    PE_REQUIRE(db != nullptr, "null db");
+    PE_CUDA(cudaSetDevice(db->device));
+    PE_CUDA(cudaStreamSynchronize(db->stream));
+    double ms[2];
+    int64_t calls;
+    PE_CHECK(prof_collect(&db->prof_events, 3, ms, &calls));
+    db->profile = enable != 0;
+    return PE_OK;
+}
+int pe_db_profile_read(pe_db* db, double ms[2], int64_t* calls) {
+    PE_REQUIRE(db && ms && calls, "null pointer");
+    PE_CUDA(cudaSetDevice(db->device));
+    return prof_collect(&db->prof_events, 3, ms, calls);
+}
+int pe_db_share_stream(pe_db* db, pe_net* net) {
+    PE_REQUIRE(db && net, "null pointer");
+    PE_REQUIRE(db->device == net->device, "DB and net live on different devices");
+    PE_CHECK(net_ensure_device(net));
+    PE_CUDA(cudaStreamSynchronize(db->stream));
+    if (db->own_stream && db->stream) cudaStreamDestroy(db->stream);
+    db->stream = net->stream;
+    db->own_stream = false;
+    return PE_OK;
+}
+
 int pe_net_sync(pe_net* net) {
     PE_REQUIRE(net != nullptr, "null net");
     PE_CHECK(net_ensure_device(net));
@@ -596,7 +666,9 @@ int pe_db_create_hamming(const uint32_t* codes, int64_t t_local, int words_per_c
 void pe_db_destroy(pe_db* db) {
     if (!db) return;
     cudaSetDevice(db->device);
-    if (db->stream) cudaStreamSynchronize(db->stream);
+    if (db->stream && db->own_stream) cudaStreamSynchronize(db->stream);
+    else cudaDeviceSynchronize();
+    for (cudaEvent_t e : db->prof_events) cudaEventDestroy(e);
     if (db->d_desc) cudaFree(db->d_desc);
     if (db->d_norm) cudaFree(db->d_norm);
     if (db->d_codes) cudaFree(db->d_codes);
@@ -604,7 +676,7 @@ void pe_db_destroy(pe_db* db) {
     for (DevBuf* b : {&db->q, &db->q_in, &db->cand_d, &db->cand_i, &db->out_i, &db->out_d, &db->qlab, &db->knn_idx,
                       &db->scratch, &db->scratch2, &db->gather, &db->boot})
         b->release();
-    if (db->stream) cudaStreamDestroy(db->stream);
+    if (db->stream && db->own_stream) cudaStreamDestroy(db->stream);
     delete db;
 }
 int pe_db_info(const pe_db* db, int64_t* t_local, int64_t* t_total, int* dim, int* is_hamming) {

@@ -188,6 +188,15 @@ int pe_comm_allgather_f32(pe_comm* comm, const float* send, int64_t n, float* re
     return PE_OK;
 }
 
+int pe_comm_allgather_f32_dev(pe_comm* comm, pe_net* net, const float* d_send, int64_t n, float* d_recv) {
+    PE_REQUIRE(comm && net && n >= 0 && ((d_send && d_recv) || n == 0), "bad arguments");
+    PE_REQUIRE(comm->device == net->device, "communicator and net live on different devices");
+    if (n == 0) return PE_OK;
+    PE_CHECK(net_ensure_device(net));
+    PE_NCCL(g_nccl.AllGather(d_send, d_recv, (size_t)n, ncclFloat32, comm->comm, net->stream));
+    return PE_OK;
+}
+
 int pe_comm_allreduce_sum_f64(pe_comm* comm, double* buf, int64_t n) {
     PE_REQUIRE(comm && n >= 0 && (buf || n == 0), "bad arguments");
     if (n == 0) return PE_OK;

@@ -116,6 +116,9 @@ struct pe_net {
     float *d_w2 = nullptr, *d_b2 = nullptr, *d_s2 = nullptr; /* [16][5][5][8],  [8],  [8]  */
     int* d_slot = nullptr;            /* patch channel -> conv1 input slot or -1 */
 
+    bool profile = false;
+    std::vector<cudaEvent_t> prof_events; /* groups of 4: before conv1, after conv1, after conv2, after fcs */
+
     /* per-chunk activations (sized for `chunk` patches) and staging for the host entry point */
     int64_t chunk = 0;
     pe::DevBuf pool1, pool2, fc_a, fc_b, in_stage[2], out_stage;
@@ -124,6 +127,9 @@ struct pe_net {
 struct pe_db {
     int device = 0;
     cudaStream_t stream = nullptr;
+    bool own_stream = true;
+    bool profile = false;
+    std::vector<cudaEvent_t> prof_events; /* groups of 3: before scan, after scan, after select */
     int num_sms = 0;
     int64_t t_local = 0, t_total = 0, row_offset = 0;
     int dim = 0, dim_pad = 0;         /* descriptor dim and its multiple-of-4 padding */
@@ -138,6 +144,8 @@ struct pe_db {
 };
 
 namespace pe {
+/* records a profiling event on `stream` when `on` (appends to `events`) */
+int prof_mark(bool on, std::vector<cudaEvent_t>* events, cudaStream_t stream);
 int net_ensure_device(pe_net* net);
 /* forward.cu */
 int net_upload_weights(pe_net* net);

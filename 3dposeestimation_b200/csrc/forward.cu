@@ -406,6 +406,7 @@ int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c,
     for (int64_t first = 0; first < n; first += net->chunk) {
         const long long m = (n - first < net->chunk) ? (n - first) : net->chunk;
         const float* src = d_patches + (size_t)first * 4096 * patch_c;
+        PE_CHECK(prof_mark(net->profile, &net->prof_events, net->stream));
         switch (net->cin) {
         case 1: PE_CHECK(launch_conv1<1>(net, src, patch_c, m)); break;
         case 2: PE_CHECK(launch_conv1<2>(net, src, patch_c, m)); break;
@@ -417,10 +418,12 @@ int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c,
         case 8: PE_CHECK(launch_conv1<8>(net, src, patch_c, m)); break;
         default: set_error("conv1 input channels %d outside 1..8", net->cin); return PE_ERR_UNSUPPORTED;
         }
+        PE_CHECK(prof_mark(net->profile, &net->prof_events, net->stream));
         const int grid2 = (int)(m < 3LL * net->num_sms ? m : 3LL * net->num_sms);
         conv2_pool_act_kernel<<<grid2, kC2Threads, smem2, net->stream>>>(
             net->pool1.as<float>(), net->d_w2, net->d_b2, net->d_s2, net->act2, net->pool2.as<float>(), m);
         PE_LAUNCHED();
+        PE_CHECK(prof_mark(net->profile, &net->prof_events, net->stream));
         const float* x = net->pool2.as<float>();
         int ldx = kPool2Ld;
         for (size_t i = 0; i < net->fcs.size(); ++i) {
@@ -435,6 +438,7 @@ int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c,
             x = y;
             ldx = ldy;
         }
+        PE_CHECK(prof_mark(net->profile, &net->prof_events, net->stream));
     }
     return PE_OK;
 }

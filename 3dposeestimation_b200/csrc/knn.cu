@@ -431,6 +431,7 @@ int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* 
     float* cd = db->cand_d.as<float>();
     int* ci = db->cand_i.as<int>();
     int st = PE_ERR_UNSUPPORTED;
+    PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
     if (db->t_local > 0) {
 #define L2_CASE(DPV, RQV) if (dp == DPV && g.rq == RQV) st = launch_l2_scan<DPV, RQV>(db, g, dq, (int)nq, cd, ci)
         L2_CASE(4, 1); L2_CASE(4, 4); L2_CASE(4, 8);
@@ -445,6 +446,7 @@ int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* 
     } else {
         PE_CUDA(cudaMemsetAsync(ci, 0xff, n_cand * sizeof(int), db->stream)); /* all -1: empty shard */
     }
+    PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
     const size_t smem = (size_t)(2 * g.n_chunks * g.kc + dp) * 4;
     PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
     PE_CUDA(cudaFuncSetAttribute(knn_select_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -452,6 +454,7 @@ int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* 
         cd, ci, (long long)g.n_chunks * g.kc, g.kc, g.n_chunks, g.kc, dq, db->d_desc, dp, db->row_offset, k,
         d_out_idx, d_out_dist);
     PE_LAUNCHED();
+    PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
     return PE_OK;
 }
 
@@ -468,6 +471,7 @@ int knn_hamming_local(pe_db* db, const uint32_t* d_qcodes, int64_t nq, int k, in
     int* cd = db->cand_d.as<int>();
     int* ci = db->cand_i.as<int>();
     int st = PE_ERR_UNSUPPORTED;
+    PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
     if (db->t_local > 0) {
 #define HAM_CASE(WV, RQV) if (db->words == WV && g.rq == RQV) st = launch_ham_scan<WV, RQV>(db, g, d_qcodes, (int)nq, cd, ci)
         HAM_CASE(1, 1); HAM_CASE(1, 4); HAM_CASE(1, 8);
@@ -482,12 +486,14 @@ int knn_hamming_local(pe_db* db, const uint32_t* d_qcodes, int64_t nq, int k, in
     } else {
         PE_CUDA(cudaMemsetAsync(ci, 0xff, n_cand * sizeof(int), db->stream));
     }
+    PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
     const size_t smem = (size_t)(2 * g.n_chunks * g.kc) * 4;
     PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
     PE_CUDA(cudaFuncSetAttribute(knn_select_kernel<int, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     knn_select_kernel<int, false><<<(unsigned)nq, 32, smem, db->stream>>>(
         cd, ci, (long long)g.n_chunks * g.kc, g.kc, g.n_chunks, g.kc, nullptr, nullptr, 0, 0, k, d_out_idx, d_out_dist);
     PE_LAUNCHED();
+    PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
     return PE_OK;
 }
 

@@ -1,0 +1,325 @@
+#!/usr/bin/env python
+"""Bench of the evaluation hot path: descriptor forward + 1-NN against a 1 M-template DB.
+
+Workload (BASELINE.json configs[1]): manifold_rgbdnor_16 (64x64x7 patches ->
+16-d descriptors), batch 4096, 1-NN against 1,000,200 template descriptors (300 objects x 3,334).
+One step = one batch of 4096 patches per GPU through forward + kNN.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path
+  python bench.py --impl reference [...]                          # the reference's CPU path (oracle port)
+  torchrun --nproc-per-node N ... bench.py --gpus N ...           # one rank per GPU
+
+N > 1 (weak scaling): every rank forwards its own batch (no communication); the template DB is
+row-sharded, the ranks all-gather their query descriptors, scan their shard for all N*4096 queries,
+all-gather the per-shard candidates over NCCL and merge.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NET = "manifold_rgbdnor_16"
+BATCH = 4096
+N_OBJ, POSES = 300, 3334              # 1,000,200 templates
+K = 1
+SEED = 20240607
+MAC_PER_PATCH = {"conv1": 23288832, "conv2": 1750000, "fc": 302848 + 4096}
+FLOP_PER_PATCH = 2 * sum(MAC_PER_PATCH.values())          # 50,691,552
+BYTES_PER_PATCH = 7 * 64 * 64 * 4 + 16 * 4                # 114,752 compulsory HBM bytes
+METRIC = "descriptors+1-NN queries/sec (forward of 64x64x7 patches -> 16-d, 1-NN vs 1,000,200 templates)"
+UNIT = "patches/s"
+
+
+def load_peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return {"hbm_gbs": float(p["hbm_gbs"]), "bf16_tflops": float(p["bf16_tflops"]),
+                "bf16_tflops_sustained": float(p.get("bf16_tflops_sustained", p["bf16_tflops"])), "source": "measured"}
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks / throttle reasons during the timed region"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc = device, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.device), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except Exception:
+                continue
+            for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7), ("sw_power_cap", 8)):
+                if len(r) > col and r[col].lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------- CPU legs ---
+def cpu_arm(steps, warmup, budget_s, threads=0):
+    """the reference's CPU path restated (oracle port): Caffe-CPU style forward + BFMatcher L2 1-NN.
+    Each step is a bounded sample: n_f patches forwarded, n_q queries matched against the full
+    1,000,200 x 16 DB (random descriptors: the matcher's cost does not depend on the values)."""
+    from oracle import pyoracle as po
+    from tests import netdefs
+    synth = importlib.import_module("3dposeestimation_b200.synth")
+    ref = po.parse_prototxt(netdefs.prototxt(NET))
+    net = po.OracleNet(ref, synth.make_blobs(ref.blob_names, ref.blob_shapes, SEED, mode=1))
+    cores = po.num_threads() if threads <= 0 else threads
+    rng = np.random.default_rng(SEED)
+    db = rng.standard_normal((N_OBJ * POSES, 16)).astype(np.float32)
+    probe = synth.make_patches(SEED, 0, 8, 7, POSES)
+    t0 = time.perf_counter(); net.forward(np.repeat(probe, max(1, cores // 4), 0), threads); tf = (time.perf_counter() - t0) / (8 * max(1, cores // 4))
+    qprobe = db[:cores * 4] + 0.1
+    t0 = time.perf_counter(); po.knn_l2(qprobe, db, K, threads); tq = (time.perf_counter() - t0) / len(qprobe)
+    per_step = budget_s / max(1, steps + warmup)
+    n_f = int(min(BATCH, max(cores, 0.5 * per_step / tf)))
+    n_q = int(min(BATCH, max(cores, 0.5 * per_step / tq)))
+    patches = np.resize(probe, (n_f, 64, 64, 7)).copy()
+    patches += rng.random(patches.shape, dtype=np.float32) * 0.01
+    queries = db[rng.integers(0, len(db), n_q)] + 0.05 * rng.standard_normal((n_q, 16)).astype(np.float32)
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        net.forward(patches, threads)
+        t1 = time.perf_counter()
+        po.knn_l2(queries, db, K, threads)
+        t2 = time.perf_counter()
+        if it >= warmup:
+            times.append(((t1 - t0) / n_f, (t2 - t1) / n_q))
+    f = float(np.mean([a for a, _ in times])); q = float(np.mean([b for _, b in times]))
+    return {"value": 1.0 / (f + q), "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"per step: oracle forward of {n_f} patches + oracle 1-NN of {n_q} queries vs the full 1,000,200x16 DB "
+                      f"(random descriptors), {steps} steps; seconds/patch = forward/patch + knn/query",
+            "descriptors_per_s": 1.0 / f, "knn_queries_per_s": 1.0 / q, "ms_per_step_equiv": (f + q) * BATCH * 1e3}
+
+
+# ----------------------------------------------------------------------------- GPU arm ---
+def gpu_arm(args, rank, world, local_rank, dist):
+    capi = importlib.import_module("3dposeestimation_b200.capi")
+    if capi.device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device: the product has no CPU fallback")
+    dev = local_rank
+    peaks = load_peaks()
+    net = capi.Net(named=NET, device=dev)
+    net.fill(SEED, 1)
+    T = N_OBJ * POSES
+    # ---- setup (untimed): template descriptors of this rank's row shard, computed by the same forward
+    lo, hi = rank * T // world, (rank + 1) * T // world
+    d_db = capi.DeviceArray((hi - lo, 16), device=dev)
+    d_in = [capi.DeviceArray((BATCH, 64, 64, 7), device=dev) for _ in range(2)]   # 2 x 470 MB > L2 (126 MB)
+    for first in range(lo, hi, BATCH):
+        m = min(BATCH, hi - first)
+        net.synth_patches_dev(SEED, first, m, POSES, d_in[0])
+        net.compute_descriptors_dev(d_in[0], m, d_db, out_offset=first - lo)
+    net.sync()
+    labels = capi.synth_labels(SEED, 0, T, POSES)
+    db = capi.TemplateDB(d_desc=d_db, t_local=hi - lo, dim=16, row_offset=lo, t_total=T, labels_all=labels,
+                         poses_per_object=POSES, device=dev)
+    db.share_stream(net)
+    comm = None
+    if world > 1:
+        uid = [capi.Comm.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        comm = capi.Comm(rank, world, uid[0], dev)
+    # query batches: perturbed versions of template patches (other seed -> other pixels, same classes)
+    for b in range(2):
+        net.synth_patches_dev(SEED + 1 + b, (rank * 2 + b) * BATCH, BATCH, POSES, d_in[b])
+    nq_all = BATCH * world
+    d_desc = capi.DeviceArray((BATCH, 16), device=dev)
+    d_desc_all = capi.DeviceArray((nq_all, 16), device=dev) if world > 1 else d_desc
+    d_idx = capi.DeviceArray((nq_all, K), np.int32, device=dev)
+    d_dist = capi.DeviceArray((nq_all, K), np.float32, device=dev)
+
+    def step_device(i):
+        net.compute_descriptors_dev(d_in[i & 1], BATCH, d_desc)
+        if world > 1:   # every rank needs every query: all-gather the 4096x16 descriptors (262 KB per rank), same stream
+            comm.allgather_f32_dev(net, d_desc, BATCH * 16, d_desc_all)
+        db.knn_sharded_dev(comm, d_desc_all, nq_all, K, d_idx, d_dist)
+
+    def barrier():
+        net.sync()
+        if world > 1:
+            dist.barrier()
+
+    for i in range(args.warmup):
+        step_device(i)
+    barrier()
+    # ---- timed region 1: device-resident inputs (`value`), per-kernel events for the roofline
+    net.profile(True); db.profile(True)
+    sampler = ClockSampler(dev); sampler.start()
+    timer = capi.Timer(dev)
+    launches0 = capi.launch_count()
+    barrier()
+    t_wall = time.perf_counter()
+    timer.start(net)
+    for i in range(args.steps):
+        step_device(i)
+    timer.stop(net)
+    ms_dev = timer.elapsed_ms()
+    barrier()
+    t_wall = (time.perf_counter() - t_wall) * 1e3
+    launches = capi.launch_count() - launches0
+    clocks = sampler.stop()
+    net_ms, net_calls = net.profile_read()
+    db_ms, db_calls = db.profile_read()
+    net.profile(False); db.profile(False)
+    ms_total = ms_dev                                # forward, NCCL and kNN all run on the net's stream
+    if world > 1:
+        import torch
+        tt = torch.tensor([ms_total], dtype=torch.float64, device=f"cuda:{dev}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total = float(tt.item())
+
+    # ---- timed region 2: end to end through the public C ABI with HOST buffers (H2D + D2H inside)
+    h_in = [capi.pinned_empty((BATCH, 64, 64, 7)) for _ in range(2)]
+    for b in range(2):
+        capi.check(capi.lib().pe_memcpy_d2h(dev, h_in[b].ctypes.data, d_in[b].ptr, h_in[b].nbytes))
+
+    def step_host(i):
+        desc = net.compute_descriptors(h_in[i & 1])
+        if world > 1:
+            desc = comm.allgather_f32(desc).reshape(nq_all, 16)
+        return db.knn_sharded(comm, desc, K)
+
+    for i in range(max(1, min(args.warmup, 3))):
+        step_host(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        idx_h, dist_h = step_host(i)
+    barrier()
+    ms_e2e = (time.perf_counter() - t0) * 1e3
+    if world > 1:
+        tt = torch.tensor([ms_e2e], dtype=torch.float64, device=f"cuda:{dev}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_e2e = float(tt.item())
+    # sanity: the host path and the device path agree on the last batch
+    assert np.array_equal(idx_h, d_idx.to_host()), "host-API and device-API neighbours differ"
+
+    if rank != 0:
+        return None
+    cpu = cpu_arm(steps=2, warmup=1, budget_s=20.0) if world == 1 else None
+    conv1_ms = net_ms[0] / max(1, net_calls)
+    scan_ms = db_ms[0] / max(1, db_calls)
+    conv1_flops = 2.0 * MAC_PER_PATCH["conv1"] * BATCH
+    achieved_tf = conv1_flops / (conv1_ms * 1e-3) / 1e12 if conv1_ms > 0 else 0.0
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get("conv1_pool_act_bytes_per_launch")
+    except Exception:
+        pass
+    step_ms = ms_total / args.steps
+    out = {
+        "metric": METRIC, "value": BATCH * world / (step_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "configs[1]: manifold_rgbdnor_16 forward (64x64x7 -> 16-d) + 1-NN, batch 4096 per GPU, "
+                               "DB 1,000,200 templates (300 x 3,334) row-sharded over the GPUs",
+                   "net": NET, "batch_per_gpu": BATCH, "templates": T, "k": K, "seed": SEED,
+                   "l2_flush": "inputs alternate between two 470 MB batches (> 126 MB L2)",
+                   "parallelism": f"patches x{world} (no comm), DB rows /{world} + NCCL all-gather + merge" if world > 1 else "single GPU"},
+        "roofline": {"kernel": "conv1_pool_act_kernel<7>", "bound": "tensor", "achieved": achieved_tf,
+                     "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                     "frac": achieved_tf / peaks["bf16_tflops_sustained"], "traffic": traffic,
+                     "peak_source": f"{peaks['source']} bf16 sustained (kernel timed inside a long step)",
+                     "note": "fp32 SIMT kernel: the pipe that binds it is FP32 FMA (~74 TFLOP/s at 1965 MHz), see fp32_fma_frac; "
+                             "HBM side: achieved_hbm_gbs of the same kernel",
+                     "algorithmic_flops_per_launch": conv1_flops, "launch_ms": conv1_ms,
+                     "fp32_fma_frac": achieved_tf / 74.4,
+                     "achieved_hbm_gbs": BATCH * (BYTES_PER_PATCH + 16 * 30 * 32 * 4) / (conv1_ms * 1e-3) / 1e9 if conv1_ms > 0 else 0.0,
+                     "hbm_peak_gbs": peaks["hbm_gbs"]},
+        "kernels_ms_per_step": {"conv1_pool_act": conv1_ms, "conv2_pool_act": net_ms[1] / max(1, net_calls),
+                                "fc_act": net_ms[2] / max(1, net_calls), "knn_l2_scan": scan_ms,
+                                "knn_select": db_ms[1] / max(1, db_calls)},
+        "descriptors_per_s_forward_only": BATCH / (sum(net_ms) / max(1, net_calls) * 1e-3) if sum(net_ms) > 0 else None,
+        "knn_queries_per_s_knn_only": nq_all / (sum(db_ms) / max(1, db_calls) * 1e-3) if sum(db_ms) > 0 else None,
+        "knn_scan_tflops": 2.0 * 16 * nq_all * (hi - lo) / (scan_ms * 1e-3) / 1e12 if scan_ms > 0 else None,
+        "e2e": {"value": BATCH * world / (ms_e2e / args.steps * 1e-3), "unit": UNIT,
+                "h2d_bytes_per_step": int(BATCH * 4096 * 7 * 4 + nq_all * 16 * 4), "d2h_bytes_per_step": int(BATCH * 16 * 4 + nq_all * K * 8),
+                "ms_per_step": ms_e2e / args.steps,
+                "path": "pe_compute_descriptors(host patches) -> pe_knn_sharded(host descriptors) with pinned host buffers"},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "wall_ms_per_step": t_wall / args.steps,
+    }
+    if cpu:
+        out["cpu_baseline"] = cpu
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        r = cpu_arm(args.steps, args.warmup, budget_s=120.0)
+        line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step_equiv"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "configs[1]: manifold_rgbdnor_16 forward + 1-NN vs 1,000,200 templates, CPU path "
+                                       "(oracle port of Caffe-CPU forward + OpenCV BFMatcher; the reference itself needs "
+                                       "Caffe/OpenCV/Eigen and cannot be built here)", "net": NET, "templates": N_OBJ * POSES, "k": K},
+                "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line), flush=True)
+        return
+    dist = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    out = gpu_arm(args, rank, world, local_rank, dist)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

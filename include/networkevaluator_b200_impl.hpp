@@ -1,0 +1,232 @@
+/* networkevaluator_b200_impl.hpp - included by networkevaluator_b200.hpp; see the notes there. */
+#pragma once
+
+namespace sz {
+
+namespace detail {
+
+/* owns a pe_db for the duration of one evaluator call */
+struct DbGuard {
+    pe_db* db = nullptr;
+    ~DbGuard() { if (db) pe_db_destroy(db); }
+};
+
+inline std::vector<float> flatten_labels(const SampleSet& set) {
+    std::vector<float> out;
+    for (auto& obj : set)
+        for (auto& s : obj) out.insert(out.end(), s.label.ptr<float>(0), s.label.ptr<float>(0) + 8);
+    return out;
+}
+
+inline void check_rectangular(const SampleSet& set, const char* what) {
+    if (set.empty() || set[0].empty()) throw std::runtime_error(std::string(what) + " is empty");
+    for (auto& obj : set)
+        if (obj.size() != set[0].size())
+            throw std::runtime_error(std::string(what) + " must hold the same number of poses per object");
+}
+
+}  // namespace detail
+
+class networkEvaluator {
+public:
+    networkEvaluator() {}
+
+    /* src/networkevaluator.cpp:9-54.  Batching, the HWC->CHW staging copy and the forward are one
+     * call into the CUDA library; rows come back in sample order. */
+    static Mat computeDescriptors(Net& CNN, std::vector<Sample> samples) {
+        int batch, channels, height, width, desc_dim;
+        CNN.shape(&batch, &channels, &height, &width, &desc_dim);
+        Mat descs((int)samples.size(), desc_dim);
+        if (samples.empty()) return descs;
+        const size_t img = (size_t)height * width * channels;
+        std::vector<float> staging(samples.size() * img);
+        for (size_t i = 0; i < samples.size(); ++i) {
+            const Mat& patch = samples[i].data;
+            if (patch.rows != height || patch.cols != width || patch.channels() != channels)
+                throw std::runtime_error("computeDescriptors: patch shape does not match the net input");
+            std::memcpy(staging.data() + i * img, patch.ptr<float>(0), img * sizeof(float));
+        }
+        pe_check(pe_compute_descriptors(CNN.handle(), staging.data(), (int64_t)samples.size(), channels, descs.ptr<float>(0)));
+        return descs;
+    }
+
+    /* src/networkevaluator.cpp:153-175 (prints the two accuracies like the reference) */
+    static void computeKNNAccuracy(std::vector<std::vector<std::vector<int>>>& maxSimTmpl,
+                                   std::vector<std::vector<std::vector<int>>>& maxSimKNNTmpl) {
+        float intra, inter;
+        computeKNNAccuracy(maxSimTmpl, maxSimKNNTmpl, &intra, &inter);
+        std::cout << "Intra-class accuracy: " << intra << std::endl;
+        std::cout << "Inter-class accuracy: " << inter << std::endl;
+    }
+    static void computeKNNAccuracy(const std::vector<std::vector<std::vector<int>>>& maxSimTmpl,
+                                   const std::vector<std::vector<std::vector<int>>>& maxSimKNNTmpl, float* intra, float* inter) {
+        const int nr_objects = (int)maxSimTmpl.size();
+        const int nr_training_poses = (int)maxSimTmpl[0].size();
+        std::vector<int32_t> ms, boot;
+        for (int o = 0; o < nr_objects; ++o)
+            for (int p = 0; p < nr_training_poses; ++p) {
+                ms.push_back(maxSimTmpl[o][p][0]);
+                const std::vector<int>& b = maxSimKNNTmpl[o][p];
+                for (int j = 0; j < 4; ++j) boot.push_back(j < (int)b.size() ? b[j] : -1);
+            }
+        detail::DbGuard g;
+        const float zero[4] = {0, 0, 0, 0};
+        pe_check(pe_db_create(zero, 1, 4, 0, nullptr, 1, 1, 0, &g.db));
+        pe_check(pe_knn_accuracy(g.db, ms.data(), boot.data(), (int64_t)ms.size(), nr_training_poses, intra, inter));
+    }
+
+    /* src/networkevaluator.cpp:248-356 */
+    static std::vector<float> computeHistogram(Net& CNN, const SampleSet& template_set, const SampleSet& test_set,
+                                               std::vector<int> rotInv, std::vector<float> bins, int knn) {
+        detail::DbGuard g;
+        Mat DBtest;
+        std::vector<int32_t> idx = match(CNN, template_set, test_set, knn, &g, &DBtest);
+        const std::vector<float> ql = detail::flatten_labels(test_set);
+        std::vector<float> histo(bins.size() + 2);
+        pe_check(pe_histogram(g.db, idx.data(), ql.data(), DBtest.rows, knn, rotInv.data(), (int)rotInv.size(), bins.data(),
+                              (int)bins.size(), histo.data()));
+        return histo;
+    }
+
+    /* src/networkevaluator.cpp:178-246 */
+    static std::vector<std::vector<float>> computeConfusionMatrix(Net& CNN, const SampleSet& template_set,
+                                                                  const SampleSet& test_set, std::vector<std::string> models,
+                                                                  std::unordered_map<std::string, int> local_index, int knn) {
+        detail::DbGuard g;
+        Mat DBtest;
+        std::vector<int32_t> idx = match(CNN, template_set, test_set, knn, &g, &DBtest);
+        const std::vector<float> ql = detail::flatten_labels(test_set);
+        /* class label -> local_index[models[label]] (:215-216); models absent from local_index map to -1 */
+        std::vector<int> class_to_local(models.size(), -1);
+        for (size_t c = 0; c < models.size(); ++c) {
+            auto it = local_index.find(models[c]);
+            if (it != local_index.end()) class_to_local[c] = it->second;
+        }
+        const int n_local = (int)local_index.size();
+        std::vector<float> flat((size_t)n_local * n_local);
+        pe_check(pe_confusion(g.db, idx.data(), ql.data(), DBtest.rows, knn, class_to_local.data(), (int)class_to_local.size(),
+                              n_local, (int)test_set[0].size(), flat.data()));
+        std::vector<std::vector<float>> conf(n_local, std::vector<float>(n_local));
+        for (int r = 0; r < n_local; ++r)
+            for (int c = 0; c < n_local; ++c) conf[r][c] = flat[(size_t)r * n_local + c];
+        return conf;
+    }
+
+    /* src/networkevaluator.cpp:416-486: appends the "test" and "train" rows to <output_path>log<log_name> */
+    static void saveLog(Net& CNN, DatasetView& db, std::string config, int iter, float time) {
+        IniFile pt(config);
+        const int knn = pt.get<int>("output.kNN");
+        const std::vector<int> rotInv = to_array<int>(pt.get<std::string>("input.rotInv"));
+        (void)pt.get<int>("input.random_background"); /* read, unused: the fill is commented out at :434-446 */
+        const SampleSet& template_set = db.getTemplateSet();
+        const SampleSet& training_set = db.getTrainingSet();
+        const SampleSet& test_set = db.getTestSet();
+        const std::vector<float> bins = {-1, 0, 10, 20, 40, 180};
+        const std::vector<float> test_hist = computeHistogram(CNN, template_set, test_set, rotInv, bins, knn);
+        const std::vector<float> train_hist = computeHistogram(CNN, template_set, training_set, rotInv, bins, knn);
+
+        const std::string log_name = pt.get<std::string>("output.log_name");
+        const std::string output_path = pt.get<std::string>("paths.output_path");
+        const std::vector<std::string> used_models = to_array<std::string>(pt.get<std::string>("input.used_models"));
+        const size_t per_epoch = used_models.size() * training_set[0].size() / 60;
+        const int epoch = per_epoch ? (int)(iter / per_epoch) : 0;
+
+        std::ifstream check(output_path + "log" + log_name);
+        const bool need_header = !check.good() || check.peek() == std::ifstream::traits_type::eof();
+        std::ofstream log_file(output_path + "log" + log_name, std::ios::app);
+        if (!log_file) throw std::runtime_error("cannot write " + output_path + "log" + log_name);
+        if (need_header) {
+            log_file << "mod" << "\t" << "iter" << "\t" << "epoch" << "\t" << "time" << "\t";
+            for (size_t i = 0; i < bins.size(); ++i) log_file << "<" << bins[i] << "\t";
+            log_file << "mean" << "\t" << "median" << std::endl;
+        }
+        auto row = [&](const char* mod, const std::vector<float>& h) {
+            log_file << mod << "\t" << iter << "\t" << epoch << "\t" << time << "\t";
+            for (size_t i = 0; i < bins.size(); ++i) log_file << std::setprecision(3) << h[i] * 100 << "\t";
+            log_file << h[h.size() - 2] << "\t" << h.back() << std::endl;
+        };
+        row("test", test_hist);
+        row("train", train_hist);
+    }
+
+    /* src/networkevaluator.cpp:358-414: confusion matrix of the TRAINING set (:390) in percent */
+    static void saveConfusionMatrix(Net& CNN, DatasetView& db, std::string config) {
+        IniFile pt(config);
+        const int knn = pt.get<int>("output.kNN");
+        (void)pt.get<int>("input.random_background");
+        const std::vector<std::string> models = to_array<std::string>(pt.get<std::string>("input.models"));
+        const std::vector<std::string> used_models = to_array<std::string>(pt.get<std::string>("input.used_models"));
+        std::unordered_map<std::string, int> local_index;
+        for (size_t i = 0; i < used_models.size(); ++i) local_index[used_models[i]] = (int)i;
+        const std::vector<std::vector<float>> conf =
+            computeConfusionMatrix(CNN, db.getTemplateSet(), db.getTrainingSet(), models, local_index, knn);
+        const std::string log_name = pt.get<std::string>("output.log_name");
+        const std::string output_path = pt.get<std::string>("paths.output_path");
+        std::ofstream log_file(output_path + "cm" + log_name);
+        if (!log_file) throw std::runtime_error("cannot write " + output_path + "cm" + log_name);
+        for (size_t m = 0; m + 1 < used_models.size(); ++m) log_file << used_models[m] << "\t";
+        log_file << used_models.back() << std::endl;
+        for (size_t m = 0; m < used_models.size(); ++m) {
+            log_file << used_models[m] << "\t";
+            for (size_t v = 0; v + 1 < used_models.size(); ++v) log_file << std::setprecision(3) << conf[m][v] * 100 << "\t";
+            log_file << std::setprecision(3) << conf[m].back() * 100 << std::endl;
+        }
+    }
+
+    /* shared front half of computeHistogram / computeConfusionMatrix / computeKNN (:257-267):
+     * descriptors per object pushed into DBfeats / DBtest, BruteForce matcher, knnMatch */
+    static std::vector<int32_t> match(Net& CNN, const SampleSet& template_set, const SampleSet& query_set, int knn,
+                                      detail::DbGuard* g, Mat* DBquery) {
+        detail::check_rectangular(template_set, "template_set");
+        detail::check_rectangular(query_set, "query set");
+        if (query_set.size() != template_set.size()) throw std::runtime_error("template and query sets differ in object count");
+        Mat DBfeats;
+        for (size_t object = 0; object < template_set.size(); ++object) {
+            DBfeats.push_back(computeDescriptors(CNN, template_set[object]));
+            DBquery->push_back(computeDescriptors(CNN, query_set[object]));
+        }
+        const std::vector<float> tl = detail::flatten_labels(template_set);
+        pe_check(pe_db_create(DBfeats.ptr<float>(0), DBfeats.rows, DBfeats.cols, 0, tl.data(), DBfeats.rows,
+                              (int)template_set[0].size(), 0, &g->db));
+        std::vector<int32_t> idx((size_t)DBquery->rows * knn);
+        std::vector<float> dist((size_t)DBquery->rows * knn);
+        pe_check(pe_knn(g->db, DBquery->ptr<float>(0), DBquery->rows, knn, idx.data(), dist.data()));
+        return idx;
+    }
+};
+
+/* the evaluation-side member of networkSolver (include/networksolver.h:49-57) */
+class networkSolver {
+public:
+    networkSolver(const SampleSet& templates, const SampleSet& training, const SampleSet& test)
+        : template_set(templates), training_set(training), test_set(test) {
+        nr_objects = (unsigned)template_set.size();
+        nr_training_poses = (unsigned)training_set.front().size();
+        nr_template_poses = (unsigned)template_set.front().size();
+        nr_test_poses = (unsigned)test_set.front().size();
+    }
+
+    /* src/networksolver.cpp:456-505: k = 3 matcher over the training set -> maxSimKNNTmpl */
+    void computeKNN(Net& CNN) {
+        detail::DbGuard g;
+        Mat DBtraining;
+        const int knn = 3;
+        std::vector<int32_t> idx = networkEvaluator::match(CNN, template_set, training_set, knn, &g, &DBtraining);
+        std::vector<int32_t> out((size_t)DBtraining.rows * 4), len(DBtraining.rows);
+        pe_check(pe_knn_bootstrap(g.db, idx.data(), DBtraining.rows, (int)nr_training_poses, out.data(), len.data()));
+        maxSimKNNTmpl.assign(nr_objects, std::vector<std::vector<int>>(nr_training_poses, std::vector<int>()));
+        for (int linearId = 0; linearId < DBtraining.rows; ++linearId) {
+            std::vector<int>& v = maxSimKNNTmpl[linearId / nr_training_poses][linearId % nr_training_poses];
+            v.assign(out.begin() + (size_t)linearId * 4, out.begin() + (size_t)linearId * 4 + len[linearId]);
+        }
+    }
+
+    std::vector<std::vector<std::vector<int>>> maxSimKNNTmpl;
+    std::vector<int> rotInv;
+    unsigned int nr_objects, nr_training_poses, nr_template_poses, nr_test_poses;
+    const SampleSet &template_set, &training_set, &test_set;
+};
+
+}  // namespace sz
+
+typedef sz::networkEvaluator eval;

@@ -78,6 +78,16 @@ PE_API int pe_timer_stop_db(pe_timer* t, pe_db* db);
 PE_API int pe_timer_elapsed_ms(pe_timer* t, float* ms); /* synchronises on stop */
 PE_API void pe_timer_destroy(pe_timer* t);
 
+/* per-kernel device time (bench.py roofline): while enabled, every forward / kNN call brackets its
+ * kernels with CUDA events on the launching stream.  *_read synchronises, returns the accumulated
+ * milliseconds since the last read and the number of bracketed calls, and resets.
+ * net stages: [0] conv1+pool+act, [1] conv2+pool+act, [2] all InnerProducts.
+ * db stages:  [0] scan (L2 or Hamming), [1] select / refine (+ merge). */
+PE_API int pe_net_profile(pe_net* net, int enable);
+PE_API int pe_net_profile_read(pe_net* net, double ms[3], int64_t* calls);
+PE_API int pe_db_profile(pe_db* db, int enable);
+PE_API int pe_db_profile_read(pe_db* db, double ms[2], int64_t* calls);
+
 /* ----------------------------------------------------------------- net --- */
 /* Replaces `caffe::Net<float> testCNN(network_path + net_name + ".prototxt", caffe::TEST)`
  * (src/networksolver.cpp:286).  Parses the TEST-phase subset of a Caffe prototxt
@@ -158,6 +168,9 @@ PE_API void pe_db_destroy(pe_db* db);
 PE_API int pe_db_info(const pe_db* db, int64_t* t_local, int64_t* t_total, int* dim,
                       int* is_hamming);
 PE_API int pe_db_sync(pe_db* db);
+/* run the DB's kernels on the net's stream, so forward -> kNN needs no host synchronisation
+ * (the net must outlive the DB or be re-shared) */
+PE_API int pe_db_share_stream(pe_db* db, pe_net* net);
 
 /* matcher->knnMatch(queries, matches, k) (src/networkevaluator.cpp:197,267;
  * src/networksolver.cpp:472): L2 distance sqrt(sum (q-t)^2), k smallest
@@ -211,6 +224,9 @@ PE_API int pe_comm_info(const pe_comm* comm, int* rank, int* world);
 /* all-gather n floats per rank (host buffers; descriptor exchange) */
 PE_API int pe_comm_allgather_f32(pe_comm* comm, const float* send, int64_t n, float* recv);
 PE_API int pe_comm_allreduce_sum_f64(pe_comm* comm, double* buf, int64_t n);
+/* device-resident all-gather of n floats per rank, enqueued on the net's stream (descriptor
+ * exchange between the forward and the sharded kNN without a host round trip) */
+PE_API int pe_comm_allgather_f32_dev(pe_comm* comm, pe_net* net, const float* d_send, int64_t n, float* d_recv);
 /* kNN against a row-sharded DB: every rank passes the same nq queries, scans
  * its shard, candidates are all-gathered over NVLink and merged identically on
  * every rank (ties -> lower global index). */
