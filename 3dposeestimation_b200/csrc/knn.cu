@@ -63,16 +63,21 @@ __device__ __noinline__ T list_insert(T* ld, int* li, int kc, int j, T d, int id
 }
 
 /* ---------------------------------------------------------------- L2 scan ---- */
+/* templates per shared-memory tile of the L2 scan: 256 rows up to 16 dims, fewer for wide rows so that the
+ * double-buffered tile stays well under the 227 KB limit (dim 128: 2 x 64 x 129 x 4 B = 66 KB) */
+__host__ __device__ constexpr int l2_tile_rows(int dp) { return dp <= 16 ? 256 : (dp <= 64 ? 128 : 64); }
+
 template <int DP, int RQ>
 __global__ void __launch_bounds__(kScanThreads)
 knn_l2_scan_kernel(const float* __restrict__ q, int nq, const float* __restrict__ db,
                    const float* __restrict__ norm, long long t_local, long long chunk_len,
                    int n_chunks, int kc, long long row_offset, float* __restrict__ cand_d,
                    int* __restrict__ cand_i) {
+    constexpr int kT = l2_tile_rows(DP);
     extern __shared__ __align__(16) float smem[];
-    float* tile = smem;                                  /* [2][kTile][DP] */
-    float* tnorm = tile + 2 * kTile * DP;                /* [2][kTile] */
-    float* ld = tnorm + 2 * kTile;                       /* [kc][RQ][threads] */
+    float* tile = smem;                                  /* [2][kT][DP] */
+    float* tnorm = tile + 2 * kT * DP;                /* [2][kT] */
+    float* ld = tnorm + 2 * kT;                       /* [kc][RQ][threads] */
     int* li = reinterpret_cast<int*>(ld + kc * RQ * kScanThreads);
     const int tid = threadIdx.x;
     const int chunk = blockIdx.y;
@@ -101,14 +106,14 @@ knn_l2_scan_kernel(const float* __restrict__ q, int nq, const float* __restrict_
         }
     }
 
-    const int n_tiles = (int)((t_end - t_begin + kTile - 1) / kTile);
+    const int n_tiles = (int)((t_end - t_begin + kT - 1) / kT);
     auto issue = [&](int it) {
-        const long long t0 = t_begin + (long long)it * kTile;
-        const int valid = (int)((t_end - t0) < kTile ? (t_end - t0) : kTile);
-        float* dst = tile + (it & 1) * kTile * DP;
+        const long long t0 = t_begin + (long long)it * kT;
+        const int valid = (int)((t_end - t0) < kT ? (t_end - t0) : kT);
+        float* dst = tile + (it & 1) * kT * DP;
         const float* src = db + (size_t)t0 * DP;
         for (int i = tid; i < valid * (DP / 4); i += kScanThreads) cp_async16(dst + 4 * i, src + 4 * i);
-        float* ndst = tnorm + (it & 1) * kTile;
+        float* ndst = tnorm + (it & 1) * kT;
         for (int i = tid; i < valid; i += kScanThreads) cp_async4(ndst + i, norm + t0 + i);
     };
     if (n_tiles > 0) issue(0);
@@ -118,10 +123,10 @@ knn_l2_scan_kernel(const float* __restrict__ q, int nq, const float* __restrict_
         cp_async_commit();
         cp_async_wait<1>();
         __syncthreads();
-        const long long t0 = t_begin + (long long)it * kTile;
-        const int valid = (int)((t_end - t0) < kTile ? (t_end - t0) : kTile);
-        const float* tl = tile + (it & 1) * kTile * DP;
-        const float* tn = tnorm + (it & 1) * kTile;
+        const long long t0 = t_begin + (long long)it * kT;
+        const int valid = (int)((t_end - t0) < kT ? (t_end - t0) : kT);
+        const float* tl = tile + (it & 1) * kT * DP;
+        const float* tn = tnorm + (it & 1) * kT;
 #pragma unroll 2
         for (int t = 0; t < valid; ++t) {
             float tv[DP];
@@ -373,16 +378,17 @@ ScanGeom plan_scan(const pe_db* db, long long nq, int k, bool hamming) {
     if (g.q_blocks < 1) g.q_blocks = 1;
     /* about four CTAs per SM in flight over the whole grid; chunks are whole tiles */
     long long want = (4LL * db->num_sms + g.q_blocks - 1) / g.q_blocks;
-    const long long tiles = (db->t_local + kTile - 1) / kTile;
+    const int tile_rows = hamming ? kTile : l2_tile_rows(db->dim_pad);
+    const long long tiles = (db->t_local + tile_rows - 1) / tile_rows;
     if (want > tiles) want = tiles;
     if (want < 1) want = 1;
     const long long tiles_per_chunk = (tiles + want - 1) / want;
-    g.chunk_len = tiles_per_chunk * kTile;
+    g.chunk_len = tiles_per_chunk * tile_rows;
     g.n_chunks = (int)((db->t_local + g.chunk_len - 1) / g.chunk_len);
     if (g.n_chunks < 1) g.n_chunks = 1;
     const size_t lists = (size_t)2 * g.kc * rq * kScanThreads * 4;
     if (hamming) g.smem = (size_t)2 * kTile * db->words * 4 + lists;
-    else g.smem = (size_t)2 * kTile * (db->dim_pad + 1) * 4 + lists;
+    else g.smem = (size_t)2 * tile_rows * (db->dim_pad + 1) * 4 + lists;
     return g;
 }
 

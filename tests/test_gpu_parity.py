@@ -377,6 +377,6 @@ def test_full_size_hamming_properties(gpu):
         x = t ^ (t[rows[qi]] ^ flip[qi])
         d_all = np.zeros(nt, np.int64)
         for w in range(4):
-            d_all += np.array([bin(v).count("1") for v in range(256)], np.int64)[x[:, w].view(np.uint8).reshape(-1, 4)].sum(1)
+            d_all += np.array([bin(v).count("1") for v in range(256)], np.int64)[np.ascontiguousarray(x[:, w]).view(np.uint8).reshape(-1, 4)].sum(1)
         order = np.argsort(d_all, kind="stable")[:5]
         assert np.array_equal(order, idx[qi]) and np.array_equal(d_all[order], dist[qi])

@@ -1,0 +1,211 @@
+/*
+ * umma_probe.cu - development probe for the tcgen05 path (not part of the product library).
+ *   1. numerics: a 128-pixel x 16-filter x (8x8x8) implicit-GEMM convolution tile computed with
+ *      overlapping no-swizzle K-major descriptors straight out of an HWC8 fp16 image, checked on the host;
+ *   2. timing: cycles per tcgen05.mma (M=128, K=16, kind::f16, both operands in shared memory) for
+ *      N = 16..256, conv-like moving A windows;
+ *   3. timing: tcgen05.ld 32x32b.x32 throughput with 4 warps.
+ * Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I../3dposeestimation_b200/csrc umma_probe.cu -o umma_probe
+ */
+#include <cstdio>
+#include <cstdlib>
+#include <cmath>
+#include <vector>
+#include <cuda_runtime.h>
+#include "umma.cuh"
+
+using namespace pe::umma;
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); return 1; } } while (0)
+
+constexpr int kImgPix = 704;   /* 11 rows of 64 pixels, 8 fp16 channels each */
+constexpr int kTaps = 64;      /* 8 x 8 */
+
+/* ---- 1. numerics ------------------------------------------------------------------------------ */
+__global__ void __launch_bounds__(128) conv_tile_kernel(const __half* __restrict__ img, const __half* __restrict__ wgt,
+                                                        float* __restrict__ out, int* __restrict__ status) {
+    __shared__ __align__(128) __half s_img[kImgPix * 8];
+    __shared__ __align__(128) __half s_w[kTaps * 16 * 8];   /* [tap][n][8 ch] : chunk stride 256 B */
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < kImgPix * 8 / 8; i += 128) reinterpret_cast<uint4*>(s_img)[i] = reinterpret_cast<const uint4*>(img)[i];
+    for (int i = tid; i < kTaps * 16 * 8 / 8; i += 128) reinterpret_cast<uint4*>(s_w)[i] = reinterpret_cast<const uint4*>(wgt)[i];
+    fence_async_smem();
+    if (warp == 0) tmem_alloc<32>(&tmem_slot);
+    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = tmem_slot;
+    if (tid == 0) {
+        const uint32_t idesc = instr_desc(128, 16, FMT_F16, FMT_F16);
+        const uint64_t a0 = smem_desc(smem_u32(s_img), 16, 128);     /* LBO = 1 pixel, SBO = 8 pixels */
+        const uint64_t b0 = smem_desc(smem_u32(s_w), 256, 128);      /* LBO = next tap, SBO = next 8 filters */
+        uint32_t acc = 0;
+        for (int ky = 0; ky < 8; ++ky)
+            for (int kp = 0; kp < 4; ++kp) {       /* taps (ky, 2kp) and (ky, 2kp+1) */
+                mma_f16(tmem, desc_advance(a0, (ky * 64 + 2 * kp) * 16), desc_advance(b0, (ky * 8 + 2 * kp) * 256), idesc, acc);
+                acc = 1;
+            }
+        mma_commit(&bar);
+    }
+    const bool ok = mbar_wait(&bar, 0);
+    if (!ok && tid == 0) atomicExch(status, 1);
+    fence_after_sync();
+    if (ok) {
+        uint32_t r[16];
+        tmem_ld16(tmem + (static_cast<uint32_t>(warp * 32) << 16), r);
+        tmem_ld_wait();
+        for (int j = 0; j < 16; ++j) out[tid * 16 + j] = __uint_as_float(r[j]);
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<32>(tmem);
+}
+
+/* ---- 2. MMA issue-rate timing ------------------------------------------------------------------ */
+template <int N>
+__global__ void __launch_bounds__(128) mma_rate_kernel(int reps, int a_mode, long long* __restrict__ cycles, int* __restrict__ status) {
+    extern __shared__ __align__(128) unsigned char dyn[];
+    __half* s_a = reinterpret_cast<__half*>(dyn);                 /* 64 KB of zeros: an HWC8 image */
+    __half* s_b = reinterpret_cast<__half*>(dyn + 65536);         /* N x 16 fp16, [2 chunks][N][8] */
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < (65536 + N * 32) / 16; i += 128) reinterpret_cast<uint4*>(dyn)[i] = make_uint4(0, 0, 0, 0);
+    fence_async_smem();
+    if (warp == 0) tmem_alloc<256>(&tmem_slot);
+    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = tmem_slot;
+    long long t0 = 0, t1 = 0;
+    bool ok = true;
+    if (tid == 0) {
+        const uint32_t idesc = instr_desc(128, N, FMT_F16, FMT_F16);
+        const uint64_t a0 = smem_desc(smem_u32(s_a), 16, 128);
+        const uint64_t b0 = smem_desc(smem_u32(s_b), N * 16, 128);
+        t0 = clock64();
+        for (int r = 0; r < reps; ++r) {
+            /* a_mode 0: conv-like windows walking over the image; 1: always the same window */
+            const uint32_t off = a_mode == 0 ? static_cast<uint32_t>(((r & 7) * 64 + ((r >> 3) & 3) * 2 + ((r >> 5) & 15) * 128) * 16) : 0u;
+            mma_f16(tmem, desc_advance(a0, off), b0, idesc, r > 0);
+        }
+        mma_commit(&bar);
+        ok = mbar_wait(&bar, 0);
+        t1 = clock64();
+        cycles[0] = t1 - t0;
+        if (!ok) atomicExch(status, 2);
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<256>(tmem);
+}
+
+/* ---- 3. TMEM load throughput -------------------------------------------------------------------- */
+__global__ void __launch_bounds__(128) tmem_ld_rate_kernel(int reps, long long* __restrict__ cycles, float* __restrict__ sink) {
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    if (warp == 0) tmem_alloc<256>(&tmem_slot);
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = tmem_slot + (static_cast<uint32_t>(warp * 32) << 16);
+    float m = 0.f;
+    __syncthreads();
+    const long long t0 = clock64();
+    for (int r = 0; r < reps; ++r) {
+#pragma unroll
+        for (int c = 0; c < 256; c += 32) {
+            uint32_t v[32];
+            tmem_ld32(tmem + c, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) m = fminf(m, __uint_as_float(v[j]));
+        }
+    }
+    __syncthreads();
+    const long long t1 = clock64();
+    if (tid == 0) cycles[0] = t1 - t0;
+    sink[tid] = m;
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<256>(tmem_slot);
+}
+
+template <int N>
+int run_rate(int a_mode, long long* d_cycles, int* d_status) {
+    const int reps = 2048;
+    const size_t smem = 65536 + N * 32;
+    CK(cudaFuncSetAttribute(mma_rate_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    mma_rate_kernel<N><<<1, 128, smem>>>(reps, a_mode, d_cycles, d_status);
+    CK(cudaDeviceSynchronize());
+    mma_rate_kernel<N><<<1, 128, smem>>>(reps, a_mode, d_cycles, d_status);
+    CK(cudaDeviceSynchronize());
+    long long c = 0;
+    CK(cudaMemcpy(&c, d_cycles, sizeof(c), cudaMemcpyDeviceToHost));
+    printf("mma_rate N=%3d a_mode=%d: %.1f cycles/MMA (%lld cycles / %d)\n", N, a_mode, (double)c / reps, c, reps);
+    return 0;
+}
+
+int main() {
+    int* d_status;
+    CK(cudaMalloc(&d_status, sizeof(int)));
+    CK(cudaMemset(d_status, 0, sizeof(int)));
+    /* ---- numerics */
+    std::vector<__half> img(kImgPix * 8), wgt(kTaps * 16 * 8);
+    std::vector<float> imgf(kImgPix * 8), wf(kTaps * 16 * 8);
+    unsigned s = 12345u;
+    auto rnd = [&]() { s = s * 1664525u + 1013904223u; return ((s >> 8) & 0xFFFF) / 65536.0f - 0.5f; };
+    for (size_t i = 0; i < img.size(); ++i) { img[i] = __float2half_rn(rnd()); imgf[i] = __half2float(img[i]); }
+    for (size_t i = 0; i < wgt.size(); ++i) { wgt[i] = __float2half_rn(rnd() * 0.25f); wf[i] = __half2float(wgt[i]); }
+    __half *d_img, *d_w;
+    float* d_out;
+    CK(cudaMalloc(&d_img, img.size() * 2));
+    CK(cudaMalloc(&d_w, wgt.size() * 2));
+    CK(cudaMalloc(&d_out, 128 * 16 * 4));
+    CK(cudaMemcpy(d_img, img.data(), img.size() * 2, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_w, wgt.data(), wgt.size() * 2, cudaMemcpyHostToDevice));
+    conv_tile_kernel<<<1, 128>>>(d_img, d_w, d_out, d_status);
+    CK(cudaDeviceSynchronize());
+    std::vector<float> out(128 * 16);
+    CK(cudaMemcpy(out.data(), d_out, out.size() * 4, cudaMemcpyDeviceToHost));
+    int st = 0;
+    CK(cudaMemcpy(&st, d_status, sizeof(int), cudaMemcpyDeviceToHost));
+    double max_err = 0, max_ref = 0;
+    for (int m = 0; m < 128; ++m)
+        for (int n = 0; n < 16; ++n) {
+            double acc = 0;
+            for (int ky = 0; ky < 8; ++ky)
+                for (int kx = 0; kx < 8; ++kx)
+                    for (int c = 0; c < 8; ++c)
+                        acc += (double)imgf[(m + ky * 64 + kx) * 8 + c] * (double)wf[((ky * 8 + kx) * 16 + n) * 8 + c];
+            max_err = fmax(max_err, fabs(acc - out[m * 16 + n]));
+            max_ref = fmax(max_ref, fabs(acc));
+        }
+    printf("conv_tile: status=%d max_abs_err=%.3e max_ref=%.3e -> %s\n", st, max_err, max_ref, (st == 0 && max_err < 1e-4 * max_ref) ? "OK" : "MISMATCH");
+    /* ---- rates */
+    long long* d_cycles;
+    CK(cudaMalloc(&d_cycles, sizeof(long long)));
+    if (st == 0) {
+        for (int a_mode = 0; a_mode < 2; ++a_mode) {
+            if (run_rate<16>(a_mode, d_cycles, d_status)) return 1;
+            if (run_rate<32>(a_mode, d_cycles, d_status)) return 1;
+            if (run_rate<64>(a_mode, d_cycles, d_status)) return 1;
+            if (run_rate<128>(a_mode, d_cycles, d_status)) return 1;
+            if (run_rate<256>(a_mode, d_cycles, d_status)) return 1;
+        }
+        float* d_sink;
+        CK(cudaMalloc(&d_sink, 128 * 4));
+        tmem_ld_rate_kernel<<<1, 128>>>(256, d_cycles, d_sink);
+        CK(cudaDeviceSynchronize());
+        long long c = 0;
+        CK(cudaMemcpy(&c, d_cycles, sizeof(c), cudaMemcpyDeviceToHost));
+        printf("tmem_ld: %.1f cycles per 128x256 fp32 tile read by 4 warps (incl. 256 FMNMX/thread)\n", (double)c / 256);
+    }
+    CK(cudaMemcpy(&st, d_status, sizeof(int), cudaMemcpyDeviceToHost));
+    printf("final status=%d\n", st);
+    return 0;
+}
