@@ -42,6 +42,8 @@ SIGNATURES = {
     "pe_last_error": (C.c_char_p, []),
     "pe_device_count": (C.c_int, [C.POINTER(C.c_int)]),
     "pe_launch_count": (C.c_int64, []),
+    "pe_set_option": (C.c_int, [C.c_char_p, C.c_int]),
+    "pe_get_option": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
     "pe_host_alloc": (C.c_int, [C.POINTER(vp), C.c_size_t]),
     "pe_host_free": (C.c_int, [vp]),
     "pe_dev_alloc": (C.c_int, [C.c_int, C.POINTER(vp), C.c_size_t]),
@@ -148,6 +150,17 @@ def device_count() -> int:
 
 def launch_count() -> int:
     return int(lib().pe_launch_count())
+
+
+def set_option(name: str, value: int):
+    """process-wide switches: "knn_tensor", "forward_tensor" (1 = tcgen05 path, 0 = fp32 SIMT path)"""
+    check(lib().pe_set_option(name.encode(), int(value)))
+
+
+def get_option(name: str) -> int:
+    v = C.c_int(0)
+    check(lib().pe_get_option(name.encode(), C.byref(v)))
+    return v.value
 
 
 class DeviceArray:

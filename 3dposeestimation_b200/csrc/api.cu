@@ -13,6 +13,7 @@
 namespace pe {
 
 std::atomic<int64_t> g_launches{0};
+std::atomic<int> g_opt_knn_tensor{1}, g_opt_forward_tensor{1};
 static thread_local std::string t_error;
 
 void set_error(const char* fmt, ...) {
@@ -172,6 +173,22 @@ extern "C" {
 int pe_version(void) { return 100; }
 const char* pe_last_error(void) { return t_error.c_str(); }
 int64_t pe_launch_count(void) { return g_launches.load(); }
+int pe_set_option(const char* name, int value) {
+    PE_REQUIRE(name != nullptr, "null option name");
+    const std::string n(name);
+    if (n == "knn_tensor") { g_opt_knn_tensor.store(value); return PE_OK; }
+    if (n == "forward_tensor") { g_opt_forward_tensor.store(value); return PE_OK; }
+    set_error("unknown option '%s'", name);
+    return PE_ERR_INVALID;
+}
+int pe_get_option(const char* name, int* value) {
+    PE_REQUIRE(name && value, "null pointer");
+    const std::string n(name);
+    if (n == "knn_tensor") { *value = g_opt_knn_tensor.load(); return PE_OK; }
+    if (n == "forward_tensor") { *value = g_opt_forward_tensor.load(); return PE_OK; }
+    set_error("unknown option '%s'", name);
+    return PE_ERR_INVALID;
+}
 
 int pe_device_count(int* n) {
     PE_REQUIRE(n != nullptr, "null pointer");
@@ -673,6 +690,9 @@ void pe_db_destroy(pe_db* db) {
     if (db->d_norm) cudaFree(db->d_norm);
     if (db->d_codes) cudaFree(db->d_codes);
     if (db->d_labels) cudaFree(db->d_labels);
+    if (db->d_tc) cudaFree(db->d_tc);
+    if (db->d_tc_err) cudaFreeHost(db->d_tc_err);
+    db->tau.release();
     for (DevBuf* b : {&db->q, &db->q_in, &db->cand_d, &db->cand_i, &db->out_i, &db->out_d, &db->qlab, &db->knn_idx,
                       &db->scratch, &db->scratch2, &db->gather, &db->boot})
         b->release();
@@ -691,7 +711,7 @@ int pe_db_sync(pe_db* db) {
     PE_REQUIRE(db != nullptr, "null db");
     PE_CUDA(cudaSetDevice(db->device));
     PE_CUDA(cudaStreamSynchronize(db->stream));
-    return PE_OK;
+    return knn_tc_check(db);
 }
 
 int pe_knn_dev(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist) {
@@ -714,7 +734,7 @@ int pe_knn(pe_db* db, const float* queries, int64_t nq, int k, int32_t* out_idx,
     PE_CUDA(cudaMemcpyAsync(out_idx, db->out_i.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, db->stream));
     PE_CUDA(cudaMemcpyAsync(out_dist, db->out_d.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, db->stream));
     PE_CUDA(cudaStreamSynchronize(db->stream));
-    return PE_OK;
+    return knn_tc_check(db);
 }
 int pe_knn_hamming_dev(pe_db* db, const uint32_t* d_qcodes, int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist) {
     PE_REQUIRE(db != nullptr, "null db");

@@ -140,6 +140,13 @@ struct pe_db {
     float* d_norm = nullptr;          /* [t_local] squared norms */
     uint32_t* d_codes = nullptr;      /* [t_local][words] */
     float* d_labels = nullptr;        /* [t_total][8] or null */
+    /* tensor-core scan (knn_tc.cu): fp16 hi/lo/norm tiles of 128 templates, power-of-two scales */
+    bool tc_ready = false;
+    void* d_tc = nullptr;
+    int* d_tc_err = nullptr;
+    int tc_log2_st = 0, tc_log2_sn = 0;
+    float tc_center[16] = {};         /* DB mean the tensor tiles are centred on */
+    pe::DevBuf tau;                   /* [nq] shared admission thresholds of the tensor scan */
     pe::DevBuf q, q_in, cand_d, cand_i, out_i, out_d, qlab, knn_idx, scratch, scratch2, gather, boot;
 };
 
@@ -158,6 +165,15 @@ int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* 
 int knn_hamming_local(pe_db* db, const uint32_t* d_qcodes, int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist);
 int knn_merge_f32(pe_db* db, const float* d_cd, const int* d_ci, long long stride_l, int n_lists, int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist);
 int knn_merge_i32(pe_db* db, const int* d_cd, const int* d_ci, long long stride_l, int n_lists, int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist);
+/* knn_tc.cu */
+int knn_tc_prepare(pe_db* db);
+bool knn_tc_usable(const pe_db* db, int k);
+void knn_tc_plan(const pe_db* db, int64_t nq, int k, int* n_chunks, int* kc, int* tiles_per_chunk);
+int knn_tc_scan(pe_db* db, const float* d_q, int64_t nq, int k, int n_chunks, int kc, int tiles_per_chunk,
+                float* cand_d, int* cand_i);
+int knn_tc_check(pe_db* db);
+/* runtime switches (pe_set_option): tensor-core paths on/off */
+extern std::atomic<int> g_opt_knn_tensor, g_opt_forward_tensor;
 /* pose.cu */
 int pose_histogram_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
                        const int* rot_inv, int n_rot, const float* bins, int n_bins, float* out_host);

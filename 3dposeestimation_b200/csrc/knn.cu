@@ -430,7 +430,10 @@ int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* 
         PE_LAUNCHED();
         dq = db->q.as<float>();
     }
-    const ScanGeom g = plan_scan(db, nq, k, false);
+    ScanGeom g = plan_scan(db, nq, k, false);
+    const bool tensor = g_opt_knn_tensor.load() != 0 && knn_tc_usable(db, k);
+    int tc_tiles_per_chunk = 0;
+    if (tensor) knn_tc_plan(db, nq, k, &g.n_chunks, &g.kc, &tc_tiles_per_chunk);
     const size_t n_cand = (size_t)nq * g.n_chunks * g.kc;
     PE_CHECK(db->cand_d.reserve(n_cand * sizeof(float)));
     PE_CHECK(db->cand_i.reserve(n_cand * sizeof(int)));
@@ -438,7 +441,9 @@ int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* 
     int* ci = db->cand_i.as<int>();
     int st = PE_ERR_UNSUPPORTED;
     PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
-    if (db->t_local > 0) {
+    if (tensor) {
+        PE_CHECK(knn_tc_scan(db, dq, nq, k, g.n_chunks, g.kc, tc_tiles_per_chunk, cd, ci));
+    } else if (db->t_local > 0) {
 #define L2_CASE(DPV, RQV) if (dp == DPV && g.rq == RQV) st = launch_l2_scan<DPV, RQV>(db, g, dq, (int)nq, cd, ci)
         L2_CASE(4, 1); L2_CASE(4, 4); L2_CASE(4, 8);
         L2_CASE(16, 1); L2_CASE(16, 4); L2_CASE(16, 8);
@@ -550,7 +555,7 @@ int db_set_descriptors(pe_db* db, const float* src, bool src_on_device) {
     PE_LAUNCHED();
     PE_CUDA(cudaStreamSynchronize(db->stream));
     if (tmp) cudaFree(tmp);
-    return PE_OK;
+    return knn_tc_prepare(db);
 }
 
 }  // namespace pe

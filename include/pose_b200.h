@@ -58,6 +58,12 @@ PE_API int pe_device_count(int* n);
 /* number of kernels launched by this library in this process (bench "gpu_launches") */
 PE_API int64_t pe_launch_count(void);
 
+/* runtime switches (process-wide).  "knn_tensor" (default 1): L2 kNN scan on the tcgen05 tensor path for
+ * descriptors of up to 16 dimensions and k <= 5, 0 = fp32 SIMT scan.  "forward_tensor" (default 1): conv / FC
+ * layers on the tcgen05 split-fp16 path, 0 = fp32 SIMT kernels.  Both paths are CUDA; neither is a CPU fallback. */
+PE_API int pe_set_option(const char* name, int value);
+PE_API int pe_get_option(const char* name, int* value);
+
 /* pinned host memory + raw device memory helpers (harness plumbing) */
 PE_API int pe_host_alloc(void** p, size_t bytes);
 PE_API int pe_host_free(void* p);

@@ -107,6 +107,14 @@ def test_binarize_matches_oracle(gpu, po):
 
 
 # -------------------------------------------------------------------------------- kNN ---
+@pytest.fixture(params=[1, 0], ids=["tensor", "simt"])
+def knn_path(gpu, request):
+    """runs a test once with the tcgen05 scan (default) and once with the fp32 SIMT scan"""
+    gpu.set_option("knn_tensor", request.param)
+    yield request.param
+    gpu.set_option("knn_tensor", 1)
+
+
 def check_knn(idx, dist, oi, od, gap, tol=1e-4):
     """indices bit-exact except where the oracle's k/k+1 gap is below tol"""
     assert idx.shape == oi.shape
@@ -123,7 +131,7 @@ def check_knn(idx, dist, oi, od, gap, tol=1e-4):
 
 
 @pytest.mark.parametrize("dim", [16, 3, 64])
-def test_knn_l2_matches_cv2_golden(gpu, synth, golden, dim):
+def test_knn_l2_matches_cv2_golden(gpu, synth, golden, dim, knn_path):
     q, t = mg.knn_problem(synth.BASE_SEED + dim, 64, 512, dim)
     t[100] = t[7]
     t[300] = t[7]
@@ -140,7 +148,7 @@ def test_knn_l2_matches_cv2_golden(gpu, synth, golden, dim):
 @pytest.mark.parametrize("dim,nq,nt,k", [(16, 1500, 19500, 1), (16, 700, 5000, 5), (16, 64, 333, 3), (3, 2000, 19500, 1),
                                          (3, 300, 1000, 5), (64, 300, 3000, 3), (128, 200, 2500, 5), (16, 130, 70000, 16),
                                          (16, 1, 1000, 1), (7, 50, 400, 2)])
-def test_knn_l2_matches_oracle(gpu, po, synth, dim, nq, nt, k):
+def test_knn_l2_matches_oracle(gpu, po, synth, dim, nq, nt, k, knn_path):
     _, t, _, _ = mg.eval_problem(synth.BASE_SEED + dim + k, 10, (nt + 9) // 10, 3, dim)
     t = t[:nt]
     rng = np.random.default_rng(nq)
@@ -158,7 +166,7 @@ def test_knn_l2_matches_oracle(gpu, po, synth, dim, nq, nt, k):
     assert np.all(np.diff(dist, axis=1) >= 0)
 
 
-def test_knn_l2_edge_cases(gpu, po):
+def test_knn_l2_edge_cases(gpu, po, knn_path):
     rng = np.random.default_rng(0)
     t = rng.standard_normal((3, 16)).astype(np.float32)
     q = rng.standard_normal((2, 16)).astype(np.float32)
@@ -176,7 +184,7 @@ def test_knn_l2_edge_cases(gpu, po):
         db.knn_hamming(np.zeros((1, 4), np.uint32), 1)
 
 
-def test_knn_l2_clustered_descriptors(gpu, po):
+def test_knn_l2_clustered_descriptors(gpu, po, knn_path):
     """descriptors far from the origin and tightly clustered: the |t|^2-2qt ranking pass loses
     precision there, the exact refine must still return the oracle's neighbours"""
     rng = np.random.default_rng(11)
@@ -207,7 +215,7 @@ def test_knn_hamming_matches_oracle_and_golden(gpu, po, synth, golden):
         assert np.array_equal(dist, od)
 
 
-def test_sharded_scan_plus_merge_equals_unsharded(gpu, po):
+def test_sharded_scan_plus_merge_equals_unsharded(gpu, po, knn_path):
     """three row shards scanned separately (global indices via row_offset), merged with the oracle's
     merge == one unsharded scan.  (The NCCL all-gather itself is covered by bench.py --gpus N.)"""
     rng = np.random.default_rng(3)
@@ -332,7 +340,7 @@ def test_config1_manifold_15x1300_end_to_end(gpu, po, synth):
 
 
 # --------------------------------------------------- full-size properties (1 M templates) ---
-def test_full_size_db_properties(gpu, synth):
+def test_full_size_db_properties(gpu, synth, knn_path):
     """BASELINE.json 1M-template DB: properties that need no CPU pass over the DB"""
     rng = np.random.default_rng(21)
     nt, dim, nq = 1_000_200, 16, 4096
