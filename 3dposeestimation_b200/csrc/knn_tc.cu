@@ -13,12 +13,13 @@
  * with A = -2 s_q q (queries), B = s_t t (templates) and the last product adding s_q s_t |t|^2 from a
  * three-term fp16 split of the squared norm.
  *
- * Kernel (persistent, one CTA per SM, 192 threads):
+ * Kernel (persistent, one CTA per SM, 320 threads):
  *   warp 0      one lane streams 10 KB template tiles (128 rows: hi | lo | norm) with cp.async.bulk into an
  *               8-stage ring (mbarrier complete_tx)
  *   warp 1      one lane issues the MMAs: two query tiles (256 queries) x one template tile per stage,
  *               four 128-column accumulators in TMEM (double buffered), tcgen05.commit -> mbarriers
- *   warps 2-5   epilogue: tcgen05.ld 32 columns at a time, running minimum, and only when a value beats
+ *   warps 2-9   epilogue (four warps per query tile, one accumulator lane = one query per thread):
+ *               tcgen05.ld 32 columns at a time (double buffered), running minimum, and only when a value beats
  *               the query's admission threshold the sorted (k+2)-list in registers is updated.  The
  *               threshold is shared between the CTAs that scan different chunks for the same query
  *               through one float per query in global memory (atomicMin), so updates stay rare.
@@ -40,7 +41,7 @@ namespace {
 constexpr int kTcRows = 128;                 /* templates per tile / queries per query tile */
 constexpr int kTcTileBytes = 10240;          /* hi 4096 | lo 4096 | norm 2048 */
 constexpr int kTcStages = 8;
-constexpr int kTcThreads = 192;
+constexpr int kTcThreads = 320;        /* producer warp, MMA warp, 2 x 4 epilogue warps */
 constexpr int kAOpBytes = 10240;             /* per query tile: hi 4096 | lo 4096 | a_n 2048 */
 constexpr int kSmemA = 0;                                  /* 2 query tiles */
 constexpr int kSmemZero = kSmemA + 2 * kAOpBytes;          /* 2048 zero bytes: second K chunk of A_n */
@@ -219,7 +220,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
     if (tid == 0) {
         for (int s = 0; s < kTcStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         for (int b = 0; b < 4; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4); }
-        mbar_init(a_ready, 128);
+        mbar_init(a_ready, 256);
         *s_abort = 0;
         mbar_fence_init();
     }
@@ -286,41 +287,38 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
             }
         }
     } else {
-        /* ================= epilogue (warps 2..5, 128 threads = 128 accumulator lanes) ================= */
-        const int quarter = warp & 3;                 /* TMEM lanes this warp may read */
-        const int row = quarter * 32 + lane;          /* query row inside a query tile */
-        const int et = tid - 64;                      /* 0..127 */
+        /* ================= epilogue: warps 2..5 drain query tile 0, warps 6..9 query tile 1 ================= */
+        const int quarter = warp & 3;                 /* TMEM lanes this warp may read: 32 * (warp % 4) */
+        const int qt = (warp - 2) >> 2;               /* query tile of the pair */
+        const int row = quarter * 32 + lane;          /* query row inside the query tile */
         uint32_t g = 0;
-        CandList<KC> list[2];
+        CandList<KC> list;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             const int chunk = item / a.n_qpairs, qpair = item - chunk * a.n_qpairs;
             const int t0 = chunk * a.tiles_per_chunk;
             const int t1 = min(t0 + a.tiles_per_chunk, a.tiles_total);
-            /* ---- query operands: scale, split, store in the K-major core-matrix layout */
-            int qidx[2];
-            float qv[2][16];
-#pragma unroll
-            for (int qt = 0; qt < 2; ++qt) {
-                qidx[qt] = (qpair * 2 + qt) * kTcRows + row;
-                const bool ok = qidx[qt] < a.nq;
+            /* ---- query operands: centre, scale, split, store in the K-major core-matrix layout */
+            const int qidx = (qpair * 2 + qt) * kTcRows + row;
+            const bool q_ok = qidx < a.nq;
+            float qv[16];
+            {
                 float m = 0.f;
 #pragma unroll
                 for (int d4 = 0; d4 < 4; ++d4) {
                     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (ok && 4 * d4 < a.q_ld) v = __ldg(reinterpret_cast<const float4*>(a.q + (size_t)qidx[qt] * a.q_ld) + d4);
-                    if (ok && 4 * d4 < a.q_ld) {
+                    if (q_ok && 4 * d4 < a.q_ld) {
+                        v = __ldg(reinterpret_cast<const float4*>(a.q + (size_t)qidx * a.q_ld) + d4);
                         v.x -= a.ctr.c[4 * d4 + 0]; v.y -= a.ctr.c[4 * d4 + 1]; v.z -= a.ctr.c[4 * d4 + 2]; v.w -= a.ctr.c[4 * d4 + 3];
                     }
-                    qv[qt][4 * d4 + 0] = v.x; qv[qt][4 * d4 + 1] = v.y; qv[qt][4 * d4 + 2] = v.z; qv[qt][4 * d4 + 3] = v.w;
+                    qv[4 * d4 + 0] = v.x; qv[4 * d4 + 1] = v.y; qv[4 * d4 + 2] = v.z; qv[4 * d4 + 3] = v.w;
                     m = fmaxf(m, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
                 }
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
                 if (lane == 0) s_red[qt * 4 + quarter] = m;
             }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-#pragma unroll
-            for (int qt = 0; qt < 2; ++qt) {
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            {
                 const float m = fmaxf(fmaxf(s_red[qt * 4 + 0], s_red[qt * 4 + 1]), fmaxf(s_red[qt * 4 + 2], s_red[qt * 4 + 3]));
                 /* s_q = 2^eq with 2 * max|q| * s_q in [2^10, 2^11); a_n = s_q * s_t / s_n must stay a finite fp16 power of two */
                 int eq = (m > 0.f && isfinite(m)) ? 9 - ilogbf(m) : 0;
@@ -332,8 +330,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
 #pragma unroll
                 for (int d = 0; d < 16; d += 2) {
                     __half h0, l0, h1, l1;
-                    split_f16(-2.f * s_q * qv[qt][d], h0, l0);
-                    split_f16(-2.f * s_q * qv[qt][d + 1], h1, l1);
+                    split_f16(-2.f * s_q * qv[d], h0, l0);
+                    split_f16(-2.f * s_q * qv[d + 1], h1, l1);
                     hi[d / 2] = pack_h2(h0, h1);
                     lo[d / 2] = pack_h2(l0, l1);
                 }
@@ -343,71 +341,88 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                 op[256 + row] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
                 op[384 + row] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
                 op[512 + row] = make_uint4(pack_h2(an, an), pack_h2(an, __ushort_as_half(0)), 0u, 0u);
-                list[qt].reset();
+                list.reset();
             }
             fence_async_smem();
             mbar_arrive(a_ready);
-            asm volatile("bar.sync 1, 128;" ::: "memory");   /* s_red may be rewritten by the next item */
+            asm volatile("bar.sync 1, 256;" ::: "memory");   /* s_red may be rewritten by the next item */
 
-            float thr[2] = {INFINITY, INFINITY};              /* admission: v < thr */
+            float thr = INFINITY;                              /* k+2-th best of this chunk so far */
+            /* the CTAs that scan other chunks for this query publish their k+2-th best in tau: nothing above it
+             * can reach the final top-k.  Admission is v <= tau, i.e. v < nextup(tau); the value is refreshed one
+             * tile ahead so that the load never sits on the critical path (a stale tau is only more permissive). */
+            int tau_raw = q_ok ? __ldcg(a.tau + qidx) : 0x7F7F7F7F;
             for (int t = t0; t < t1 && !*s_abort; ++t, ++g) {
                 const int col0 = t * kTcRows;                 /* local template index of column 0 */
+                const int b = (g & 1) * 2 + qt;
+                const float tg = ord2f(tau_raw);
+                float tau_up = __int_as_float(tg >= 0.f ? __float_as_int(tg) + 1 : __float_as_int(tg) - 1);
+                if (tg == 0.f) tau_up = FLT_MIN;
+                if (q_ok) tau_raw = __ldcg(a.tau + qidx);     /* consumed by the next tile */
+                float th = fminf(thr, tau_up);
+                if (!mbar_wait(&tfull[b], (g >> 1) & 1)) { atomicExch(a.err, 5); *s_abort = 1; }
+                fence_after_sync();
+                const uint32_t tbase = tmem + b * 128 + (static_cast<uint32_t>(quarter * 32) << 16);
+                uint32_t v0[32], v1[32];
+                auto min32 = [](const uint32_t (&v)[32]) {
+                    float m8[8];
 #pragma unroll
-                for (int qt = 0; qt < 2; ++qt) {
-                    const int b = (g & 1) * 2 + qt;
-                    /* the other chunks' CTAs publish their k+2-th best: anything above it cannot be in the final top-k */
-                    float tau_up = INFINITY;
-                    if (qidx[qt] < a.nq) {
-                        const float tg = ord2f(__ldcg(a.tau + qidx[qt]));
-                        tau_up = tg < FLT_MAX ? __int_as_float(f2ord(tg) >= 0 ? __float_as_int(tg) + 1 : __float_as_int(tg) - 1) : INFINITY;
-                        if (tg == 0.f) tau_up = FLT_MIN;      /* next float above +-0 */
-                    }
-                    float th = fminf(thr[qt], tau_up);
-                    if (!mbar_wait(&tfull[b], (g >> 1) & 1)) { atomicExch(a.err, 5); *s_abort = 1; }
-                    fence_after_sync();
-                    const uint32_t tbase = tmem + b * 128 + (static_cast<uint32_t>(quarter * 32) << 16);
+                    for (int j = 0; j < 8; ++j)
+                        m8[j] = fminf(fminf(__uint_as_float(v[j]), __uint_as_float(v[j + 8])), fminf(__uint_as_float(v[j + 16]), __uint_as_float(v[j + 24])));
+                    return fminf(fminf(fminf(m8[0], m8[1]), fminf(m8[2], m8[3])), fminf(fminf(m8[4], m8[5]), fminf(m8[6], m8[7])));
+                };
+                /* hot path: four 32-column loads (next load in flight while the previous block is reduced) */
+                tmem_ld32(tbase, v0);
+                tmem_ld_wait();
+                tmem_ld32(tbase + 32, v1);
+                const float m0 = min32(v0);
+                tmem_ld_wait();
+                tmem_ld32(tbase + 64, v0);
+                const float m1 = min32(v1);
+                tmem_ld_wait();
+                tmem_ld32(tbase + 96, v1);
+                const float m2 = min32(v0);
+                tmem_ld_wait();
+                const float m3 = min32(v1);
+                const unsigned hit = (m0 < th ? 1u : 0u) | (m1 < th ? 2u : 0u) | (m2 < th ? 4u : 0u) | (m3 < th ? 8u : 0u);
+                const unsigned any = __reduce_or_sync(0xffffffffu, hit);
+                if (any) {
+                    /* rare path, one code instance: re-read the flagged 32-column blocks eight columns at a time */
+                    bool changed = false;
 #pragma unroll 1
-                    for (int blk = 0; blk < 4; ++blk) {
-                        uint32_t v[32];
-                        tmem_ld32(tbase + blk * 32, v);
+                    for (int sub = 0; sub < 16; ++sub) {
+                        if (!((any >> (sub >> 2)) & 1u)) continue;
+                        uint32_t w[8];
+                        tmem_ld8(tbase + sub * 8, w);
                         tmem_ld_wait();
-                        float m = __uint_as_float(v[0]);
 #pragma unroll
-                        for (int j = 1; j < 32; ++j) m = fminf(m, __uint_as_float(v[j]));
-                        if (__any_sync(0xffffffffu, m < th)) {
-                            if (m < th) {
-#pragma unroll
-                                for (int j = 0; j < 32; ++j) {
-                                    const float x = __uint_as_float(v[j]);
-                                    const int li = col0 + blk * 32 + j;
-                                    if (x < th && li < a.t_local) {
-                                        list[qt].insert(x, li);
-                                        thr[qt] = list[qt].d[KC - 1];
-                                        th = fminf(thr[qt], tau_up);
-                                    }
-                                }
-                                if (thr[qt] < INFINITY && qidx[qt] < a.nq) atomicMin(a.tau + qidx[qt], f2ord(thr[qt]));
+                        for (int j = 0; j < 8; ++j) {
+                            const float x = __uint_as_float(w[j]);
+                            const int li = col0 + sub * 8 + j;
+                            if (x < th && li < a.t_local) {
+                                list.insert(x, li);
+                                thr = list.d[KC - 1];
+                                th = fminf(thr, tau_up);
+                                changed = true;
                             }
-                            __syncwarp();
                         }
                     }
-                    fence_before_sync();
+                    if (changed && thr < INFINITY && q_ok) atomicMin(a.tau + qidx, f2ord(thr));
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&tempty[b]);
                 }
+                fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty[b]);
             }
             /* ---- this item's candidates: [query][chunk][KC], global template indices */
-#pragma unroll
-            for (int qt = 0; qt < 2; ++qt) {
-                if (qidx[qt] >= a.nq) continue;
-                const size_t o = ((size_t)qidx[qt] * a.n_chunks + chunk) * KC;
+            if (q_ok) {
+                const size_t o = ((size_t)qidx * a.n_chunks + chunk) * KC;
 #pragma unroll
                 for (int p = 0; p < KC; ++p) {
-                    a.cand_d[o + p] = list[qt].d[p];
-                    a.cand_i[o + p] = list[qt].i[p] >= 0 ? (int)(list[qt].i[p] + a.row_offset) : -1;
+                    a.cand_d[o + p] = list.d[p];
+                    a.cand_i[o + p] = list.i[p] >= 0 ? (int)(list.i[p] + a.row_offset) : -1;
                 }
             }
-            (void)et;
         }
     }
     fence_before_sync();
