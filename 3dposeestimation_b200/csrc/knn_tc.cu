@@ -13,12 +13,12 @@
  * with A = -2 s_q q (queries), B = s_t t (templates) and the last product adding s_q s_t |t|^2 from a
  * three-term fp16 split of the squared norm.
  *
- * Kernel (persistent, one CTA per SM, 320 threads):
+ * Kernel (persistent, one CTA per SM, 352 threads):
  *   warp 0      one lane streams 10 KB template tiles (128 rows: hi | lo | norm) with cp.async.bulk into an
  *               8-stage ring (mbarrier complete_tx)
- *   warp 1      one lane issues the MMAs: two query tiles (256 queries) x one template tile per stage,
- *               four 128-column accumulators in TMEM (double buffered), tcgen05.commit -> mbarriers
- *   warps 2-9   epilogue (four warps per query tile, one accumulator lane = one query per thread):
+ *   warps 1-2   one lane each issues the MMAs of one query tile (two tiles = 256 queries share every template
+ *               tile), four 128-column accumulators in TMEM (double buffered), tcgen05.commit -> mbarriers
+ *   warps 3-10  epilogue (four warps per query tile, one accumulator lane = one query per thread):
  *               tcgen05.ld 32 columns at a time (double buffered), running minimum, and only when a value beats
  *               the query's admission threshold the sorted (k+2)-list in registers is updated.  The
  *               threshold is shared between the CTAs that scan different chunks for the same query
@@ -27,6 +27,7 @@
 #include <cfloat>
 #include <climits>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.h"
@@ -41,12 +42,14 @@ namespace {
 constexpr int kTcRows = 128;                 /* templates per tile / queries per query tile */
 constexpr int kTcTileBytes = 10240;          /* hi 4096 | lo 4096 | norm 2048 */
 constexpr int kTcStages = 8;
-constexpr int kTcThreads = 320;        /* producer warp, MMA warp, 2 x 4 epilogue warps */
+constexpr int kTcThreads = 352;        /* producer warp, 2 MMA warps, 2 x 4 epilogue warps */
 constexpr int kAOpBytes = 10240;             /* per query tile: hi 4096 | lo 4096 | a_n 2048 */
 constexpr int kSmemA = 0;                                  /* 2 query tiles */
 constexpr int kSmemZero = kSmemA + 2 * kAOpBytes;          /* 2048 zero bytes: second K chunk of A_n */
 constexpr int kSmemB = kSmemZero + 2048;
-constexpr int kSmemBar = kSmemB + kTcStages * kTcTileBytes;
+constexpr int kSmemScratch = kSmemB + kTcStages * kTcTileBytes;   /* [32][256] floats: rare-path staging  */
+constexpr int kSmemList = kSmemScratch + 32 * 256 * 4;            /* [7][256] floats + [7][256] ints     */
+constexpr int kSmemBar = kSmemList + 2 * 7 * 256 * 4;
 constexpr int kSmemTotal = kSmemBar + 256;
 
 /* monotone float <-> int map so that atomicMin on ints orders floats (negative values included) */
@@ -180,45 +183,46 @@ struct TcArgs {
     float* cand_d;
     int* cand_i;
     int* err;
+    unsigned long long* dbg;   /* PE_TC_DEBUG: per-role cycle counters (null in production) */
 };
+#define TC_DBG_T0(var) long long var = 0; if (a.dbg) var = clock64()
+#define TC_DBG_ADD(slot, var) do { if (a.dbg) { const long long n_ = clock64(); dbg_acc[slot] += n_ - var; var = n_; } } while (0)
 
-template <int KC>
-struct CandList {
-    float d[KC];
-    int i[KC];
-    __device__ __forceinline__ void reset() {
-#pragma unroll
-        for (int p = 0; p < KC; ++p) { d[p] = INFINITY; i[p] = -1; }
+/* sorted insert into the calling thread's k+2 list (entries strided by 256 threads in shared memory); strict '>'
+ * keeps the earlier (lower-index) entry first among equals.  Returns the new k+2-th best.  Deliberately not
+ * inlined: it runs in about one warp-tile in six and must not bloat the hot loop's instruction footprint. */
+__device__ __noinline__ float tc_list_insert(float* ld, int* li, int kc, float v, int idx) {
+    int p = kc - 1;
+    while (p > 0 && ld[(p - 1) * 256] > v) {
+        ld[p * 256] = ld[(p - 1) * 256];
+        li[p * 256] = li[(p - 1) * 256];
+        --p;
     }
-    /* strict '<' on insertion keeps the earlier (lower-index) entry first among equals */
-    __device__ __forceinline__ void insert(float v, int idx) {
-#pragma unroll
-        for (int p = KC - 1; p >= 0; --p) {
-            const bool up = p > 0 && d[p - 1] > v;     /* entry p-1 moves down to p */
-            const bool here = d[p] > v && !up;         /* v lands at p */
-            if (p > 0 && up) { d[p] = d[p - 1]; i[p] = i[p - 1]; }
-            else if (here) { d[p] = v; i[p] = idx; }
-        }
-    }
-};
+    ld[p * 256] = v;
+    li[p * 256] = idx;
+    return ld[(kc - 1) * 256];
+}
 
 template <int KC>
 __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemBar);
     uint64_t* full = bars;                     /* [kTcStages] tile landed */
-    uint64_t* empty = bars + kTcStages;        /* [kTcStages] tile consumed by the MMAs */
+    uint64_t* empty = bars + kTcStages;        /* [kTcStages] tile consumed by both query tiles' MMAs */
     uint64_t* tfull = bars + 2 * kTcStages;    /* [4] accumulator ready */
     uint64_t* tempty = tfull + 4;              /* [4] accumulator drained */
     uint64_t* a_ready = tempty + 4;            /* query operands of the next item written */
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_ready + 1);
     volatile int* s_abort = reinterpret_cast<volatile int*>(tmem_slot + 1);
-    float* s_red = reinterpret_cast<float*>(tmem_slot + 2);   /* [8] query abs-max per epilogue warp x tile */
+    float* s_red = reinterpret_cast<float*>(tmem_slot + 2);   /* [8] query abs-max per epilogue warp */
+    float* s_scratch = reinterpret_cast<float*>(smem + kSmemScratch);   /* [32][256] rare-path staging */
+    float* s_ld = reinterpret_cast<float*>(smem + kSmemList);           /* [KC][256] candidate values */
+    int* s_li = reinterpret_cast<int*>(s_ld + KC * 256);                /* [KC][256] candidate rows   */
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int i = tid; i < 2048 / 16; i += kTcThreads) reinterpret_cast<uint4*>(smem + kSmemZero)[i] = make_uint4(0, 0, 0, 0);
     if (tid == 0) {
-        for (int s = 0; s < kTcStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int s = 0; s < kTcStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 2); }
         for (int b = 0; b < 4; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4); }
         mbar_init(a_ready, 256);
         *s_abort = 0;
@@ -248,51 +252,65 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                 }
             }
         }
-    } else if (warp == 1) {
-        /* ================= MMA issuer ================= */
+    } else if (warp <= 2) {
+        /* ================= MMA issuers: warp 1 feeds query tile 0, warp 2 query tile 1 ================= */
         if (lane == 0) {
+            const int qt = warp - 1;
             const uint32_t idesc = instr_desc(128, 128, FMT_F16, FMT_F16);
-            const uint32_t sA = smem_u32(smem + kSmemA), sB = smem_u32(smem + kSmemB), sZ = smem_u32(smem + kSmemZero);
+            const uint32_t sB = smem_u32(smem + kSmemB), sZ = smem_u32(smem + kSmemZero);
+            const uint32_t a_base = smem_u32(smem + kSmemA) + qt * kAOpBytes;
+            const uint64_t a_hi = smem_desc(a_base, 2048, 128), a_lo = smem_desc(a_base + 4096, 2048, 128);
+            const uint64_t a_n = smem_desc(a_base + 8192, sZ - (a_base + 8192), 128);
+            const uint64_t b_hi0 = smem_desc(sB, 2048, 128), b_lo0 = smem_desc(sB + 4096, 2048, 128);
+            const uint64_t b_n0 = smem_desc(sB + 8192, 0, 128);   /* chunk 1 aliases chunk 0: A_n's chunk 1 is zero */
             uint32_t g = 0, it = 0;
+            long long dbg_acc[4] = {0, 0, 0, 0};
+            TC_DBG_T0(tm);
             for (int item = blockIdx.x; item < n_items && !*s_abort; item += gridDim.x, ++it) {
                 const int chunk = item / a.n_qpairs;
                 const int t0 = chunk * a.tiles_per_chunk;
                 const int t1 = min(t0 + a.tiles_per_chunk, a.tiles_total);
                 if (!mbar_wait(a_ready, it & 1)) { atomicExch(a.err, 2); *s_abort = 1; break; }
                 fence_after_sync();
-                for (int t = t0; t < t1 && !*s_abort; ++t, ++g) {
+                for (int t = t0; t < t1; ++t, ++g) {
                     const int s = g % kTcStages;
+                    const int b = (g & 1) * 2 + qt;
+                    TC_DBG_ADD(2, tm);
+                    if (!mbar_wait(&tempty[b], ((g >> 1) & 1) ^ 1)) { atomicExch(a.err, 4); *s_abort = 1; break; }
+                    TC_DBG_ADD(1, tm);
                     if (!mbar_wait(&full[s], (g / kTcStages) & 1)) { atomicExch(a.err, 3); *s_abort = 1; break; }
                     fence_after_sync();
-                    const uint32_t b_base = sB + s * kTcTileBytes;
-                    const uint64_t b_hi = smem_desc(b_base, 2048, 128), b_lo = smem_desc(b_base + 4096, 2048, 128);
-                    const uint64_t b_n = smem_desc(b_base + 8192, 0, 128);   /* chunk 1 aliases chunk 0: A_n's chunk 1 is zero */
-#pragma unroll
-                    for (int qt = 0; qt < 2; ++qt) {
-                        const int b = (g & 1) * 2 + qt;
-                        if (!mbar_wait(&tempty[b], ((g >> 1) & 1) ^ 1)) { atomicExch(a.err, 4); *s_abort = 1; break; }
-                        fence_after_sync();
-                        const uint32_t a_base = sA + qt * kAOpBytes;
-                        const uint64_t a_hi = smem_desc(a_base, 2048, 128), a_lo = smem_desc(a_base + 4096, 2048, 128);
-                        const uint64_t a_n = smem_desc(a_base + 8192, sZ - (a_base + 8192), 128);
-                        const uint32_t d = tmem + b * 128;
-                        mma_f16(d, a_hi, b_hi, idesc, 0);
-                        mma_f16(d, a_hi, b_lo, idesc, 1);
-                        mma_f16(d, a_lo, b_hi, idesc, 1);
-                        mma_f16(d, a_n, b_n, idesc, 1);
-                        mma_commit(&tfull[b]);
-                    }
+                    TC_DBG_ADD(0, tm);
+                    const uint32_t off = static_cast<uint32_t>(s) * (kTcTileBytes >> 4);
+                    const uint32_t d = tmem + b * 128;
+                    mma_f16(d, a_hi, b_hi0 + off, idesc, 0);
+                    mma_f16(d, a_hi, b_lo0 + off, idesc, 1);
+                    mma_f16(d, a_lo, b_hi0 + off, idesc, 1);
+                    mma_f16(d, a_n, b_n0 + off, idesc, 1);
+                    mma_commit(&tfull[b]);
                     mma_commit(&empty[s]);
                 }
             }
+            if (a.dbg && qt == 0) {
+                TC_DBG_ADD(2, tm);
+                atomicAdd(a.dbg + 5, (unsigned long long)dbg_acc[0]);
+                atomicAdd(a.dbg + 6, (unsigned long long)dbg_acc[1]);
+                atomicAdd(a.dbg + 7, (unsigned long long)dbg_acc[2]);
+                atomicAdd(a.dbg + 8, (unsigned long long)g);
+            }
         }
     } else {
-        /* ================= epilogue: warps 2..5 drain query tile 0, warps 6..9 query tile 1 ================= */
+        /* ================= epilogue: warps 3..6 drain query tile 0, warps 7..10 query tile 1 ================= */
         const int quarter = warp & 3;                 /* TMEM lanes this warp may read: 32 * (warp % 4) */
-        const int qt = (warp - 2) >> 2;               /* query tile of the pair */
+        const int qt = (warp - 3) >> 2;               /* query tile of the pair */
         const int row = quarter * 32 + lane;          /* query row inside the query tile */
+        const int et = qt * 128 + row;                /* 0..255: this thread's column in the shared-memory lists */
+        float* my_ld = s_ld + et;
+        int* my_li = s_li + et;
+        float* my_scratch = s_scratch + et;
         uint32_t g = 0;
-        CandList<KC> list;
+        long long dbg_acc[5] = {0, 0, 0, 0, 0};
+        TC_DBG_T0(te);
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             const int chunk = item / a.n_qpairs, qpair = item - chunk * a.n_qpairs;
             const int t0 = chunk * a.tiles_per_chunk;
@@ -341,7 +359,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                 op[256 + row] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
                 op[384 + row] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
                 op[512 + row] = make_uint4(pack_h2(an, an), pack_h2(an, __ushort_as_half(0)), 0u, 0u);
-                list.reset();
+#pragma unroll
+                for (int p = 0; p < KC; ++p) { my_ld[p * 256] = INFINITY; my_li[p * 256] = -1; }
             }
             fence_async_smem();
             mbar_arrive(a_ready);
@@ -349,21 +368,27 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
 
             float thr = INFINITY;                              /* k+2-th best of this chunk so far */
             /* the CTAs that scan other chunks for this query publish their k+2-th best in tau: nothing above it
-             * can reach the final top-k.  Admission is v <= tau, i.e. v < nextup(tau); the value is refreshed one
-             * tile ahead so that the load never sits on the critical path (a stale tau is only more permissive). */
+             * can reach the final top-k.  Admission is v <= tau, i.e. v < nextup(tau).  tau is re-read every fourth
+             * tile and used from the following tile on (a stale tau is only more permissive). */
             int tau_raw = q_ok ? __ldcg(a.tau + qidx) : 0x7F7F7F7F;
-            for (int t = t0; t < t1 && !*s_abort; ++t, ++g) {
+            float tau_up = INFINITY;
+            for (int t = t0; t < t1; ++t, ++g) {
                 const int col0 = t * kTcRows;                 /* local template index of column 0 */
                 const int b = (g & 1) * 2 + qt;
-                const float tg = ord2f(tau_raw);
-                float tau_up = __int_as_float(tg >= 0.f ? __float_as_int(tg) + 1 : __float_as_int(tg) - 1);
-                if (tg == 0.f) tau_up = FLT_MIN;
-                if (q_ok) tau_raw = __ldcg(a.tau + qidx);     /* consumed by the next tile */
+                if ((g & 3) == 1) {
+                    const float tg = ord2f(tau_raw);
+                    tau_up = __int_as_float(tg >= 0.f ? __float_as_int(tg) + 1 : __float_as_int(tg) - 1);
+                    if (tg == 0.f) tau_up = FLT_MIN;
+                } else if ((g & 3) == 0 && q_ok) {
+                    tau_raw = __ldcg(a.tau + qidx);
+                }
                 float th = fminf(thr, tau_up);
-                if (!mbar_wait(&tfull[b], (g >> 1) & 1)) { atomicExch(a.err, 5); *s_abort = 1; }
+                TC_DBG_ADD(3, te);
+                if (!mbar_wait(&tfull[b], (g >> 1) & 1)) { atomicExch(a.err, 5); *s_abort = 1; break; }
                 fence_after_sync();
+                TC_DBG_ADD(0, te);
                 const uint32_t tbase = tmem + b * 128 + (static_cast<uint32_t>(quarter * 32) << 16);
-                uint32_t v0[32], v1[32];
+                uint32_t v0[32], v1[32], v2[32], v3[32];
                 auto min32 = [](const uint32_t (&v)[32]) {
                     float m8[8];
 #pragma unroll
@@ -371,37 +396,40 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                         m8[j] = fminf(fminf(__uint_as_float(v[j]), __uint_as_float(v[j + 8])), fminf(__uint_as_float(v[j + 16]), __uint_as_float(v[j + 24])));
                     return fminf(fminf(fminf(m8[0], m8[1]), fminf(m8[2], m8[3])), fminf(fminf(m8[4], m8[5]), fminf(m8[6], m8[7])));
                 };
-                /* hot path: four 32-column loads (next load in flight while the previous block is reduced) */
+                /* hot path: the whole 128-column accumulator row in one round trip (four loads in flight) */
                 tmem_ld32(tbase, v0);
-                tmem_ld_wait();
                 tmem_ld32(tbase + 32, v1);
-                const float m0 = min32(v0);
+                tmem_ld32(tbase + 64, v2);
+                tmem_ld32(tbase + 96, v3);
                 tmem_ld_wait();
-                tmem_ld32(tbase + 64, v0);
-                const float m1 = min32(v1);
-                tmem_ld_wait();
-                tmem_ld32(tbase + 96, v1);
-                const float m2 = min32(v0);
-                tmem_ld_wait();
-                const float m3 = min32(v1);
+                const float m0 = min32(v0), m1 = min32(v1), m2 = min32(v2), m3 = min32(v3);
                 const unsigned hit = (m0 < th ? 1u : 0u) | (m1 < th ? 2u : 0u) | (m2 < th ? 4u : 0u) | (m3 < th ? 8u : 0u);
                 const unsigned any = __reduce_or_sync(0xffffffffu, hit);
+                TC_DBG_ADD(1, te);
                 if (any) {
-                    /* rare path, one code instance: re-read the flagged 32-column blocks eight columns at a time */
+                    /* rare path, kept small (instruction cache): re-read a flagged 32-column block, park it in shared
+                     * memory, build the mask of admissible columns and insert those (usually one) */
+                    dbg_acc[4] += 1;
                     bool changed = false;
 #pragma unroll 1
-                    for (int sub = 0; sub < 16; ++sub) {
-                        if (!((any >> (sub >> 2)) & 1u)) continue;
-                        uint32_t w[8];
-                        tmem_ld8(tbase + sub * 8, w);
+                    for (int blk = 0; blk < 4; ++blk) {
+                        if (!((any >> blk) & 1u)) continue;
+                        uint32_t w[32];
+                        tmem_ld32(tbase + blk * 32, w);
                         tmem_ld_wait();
+                        unsigned mask = 0;
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float x = __uint_as_float(w[j]);
-                            const int li = col0 + sub * 8 + j;
+                        for (int j = 0; j < 32; ++j) {
+                            my_scratch[j * 256] = __uint_as_float(w[j]);
+                            mask |= (__uint_as_float(w[j]) < th ? 1u : 0u) << j;
+                        }
+                        while (mask) {
+                            const int j = __ffs(mask) - 1;
+                            mask &= mask - 1;
+                            const float x = my_scratch[j * 256];
+                            const int li = col0 + blk * 32 + j;
                             if (x < th && li < a.t_local) {
-                                list.insert(x, li);
-                                thr = list.d[KC - 1];
+                                thr = tc_list_insert(my_ld, my_li, KC, x, li);
                                 th = fminf(thr, tau_up);
                                 changed = true;
                             }
@@ -409,6 +437,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                     }
                     if (changed && thr < INFINITY && q_ok) atomicMin(a.tau + qidx, f2ord(thr));
                     __syncwarp();
+                    TC_DBG_ADD(2, te);
                 }
                 fence_before_sync();
                 __syncwarp();
@@ -419,10 +448,16 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                 const size_t o = ((size_t)qidx * a.n_chunks + chunk) * KC;
 #pragma unroll
                 for (int p = 0; p < KC; ++p) {
-                    a.cand_d[o + p] = list.d[p];
-                    a.cand_i[o + p] = list.i[p] >= 0 ? (int)(list.i[p] + a.row_offset) : -1;
+                    const int li = my_li[p * 256];
+                    a.cand_d[o + p] = my_ld[p * 256];
+                    a.cand_i[o + p] = li >= 0 ? (int)(li + a.row_offset) : -1;
                 }
             }
+        }
+        if (a.dbg && lane == 0) {
+            TC_DBG_ADD(3, te);
+            for (int j = 0; j < 5; ++j) atomicAdd(a.dbg + j, (unsigned long long)dbg_acc[j]);
+            atomicAdd(a.dbg + 9, (unsigned long long)g);
         }
     }
     fence_before_sync();
@@ -517,6 +552,14 @@ int knn_tc_scan(pe_db* db, const float* d_q, int64_t nq, int k, int n_chunks, in
     a.cand_d = cand_d;
     a.cand_i = cand_i;
     a.err = db->d_tc_err;
+    a.dbg = nullptr;
+    static const bool dbg_on = getenv("PE_TC_DEBUG") != nullptr;
+    unsigned long long* d_dbg = nullptr;
+    if (dbg_on) {
+        PE_CUDA(cudaMalloc(&d_dbg, 16 * sizeof(unsigned long long)));
+        PE_CUDA(cudaMemsetAsync(d_dbg, 0, 16 * sizeof(unsigned long long), db->stream));
+        a.dbg = d_dbg;
+    }
     const int items = a.n_chunks * a.n_qpairs;
     const int grid = items < db->num_sms ? items : db->num_sms;
     if (kc == 3) {
@@ -527,6 +570,16 @@ int knn_tc_scan(pe_db* db, const float* d_q, int64_t nq, int k, int n_chunks, in
         knn_tc_scan_kernel<7><<<grid, kTcThreads, kSmemTotal, db->stream>>>(a);
     }
     PE_LAUNCHED();
+    if (dbg_on) {
+        unsigned long long h[16];
+        PE_CUDA(cudaMemcpyAsync(h, d_dbg, sizeof(h), cudaMemcpyDeviceToHost, db->stream));
+        PE_CUDA(cudaStreamSynchronize(db->stream));
+        cudaFree(d_dbg);
+        const double ew = 8.0 * grid, tiles_e = h[9] > 0 ? (double)h[9] : 1.0, tiles_m = h[8] > 0 ? (double)h[8] : 1.0;
+        fprintf(stderr, "[tc dbg] grid %d items %d  epilogue per warp-tile: wait_tfull %.0f hot %.0f slow %.0f other %.0f cycles, slow entries %.3f/tile | "
+                        "mma per tile: wait_full %.0f wait_tempty %.0f issue %.0f (epi warps %.0f)\n", grid, items,
+                h[0] / tiles_e, h[1] / tiles_e, h[2] / tiles_e, h[3] / tiles_e, h[4] / tiles_e, h[5] / tiles_m, h[6] / tiles_m, h[7] / tiles_m, ew);
+    }
     return PE_OK;
 }
 

@@ -104,6 +104,128 @@ __global__ void __launch_bounds__(128) mma_rate_kernel(int reps, int a_mode, lon
     if (warp == 0) tmem_dealloc<256>(tmem);
 }
 
+/* ---- 2b. accumulator switching: `per` consecutive MMAs per accumulator, round-robin over nbuf accumulators,
+ *          a_lbo selects the A layout (16: overlapping pixels, 2048: chunk-major planes) ------------------- */
+template <int N>
+__global__ void __launch_bounds__(128) mma_switch_kernel(int reps, int per, int nbuf, int a_lbo, int fresh, long long* __restrict__ cycles, int* __restrict__ status) {
+    extern __shared__ __align__(128) unsigned char dyn[];
+    __half* s_a = reinterpret_cast<__half*>(dyn);
+    __half* s_b = reinterpret_cast<__half*>(dyn + 65536);
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < (65536 + N * 32) / 16; i += 128) reinterpret_cast<uint4*>(dyn)[i] = make_uint4(0, 0, 0, 0);
+    fence_async_smem();
+    if (warp == 0) tmem_alloc<512>(&tmem_slot);
+    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = tmem_slot;
+    if (tid == 0) {
+        const uint32_t idesc = instr_desc(128, N, FMT_F16, FMT_F16);
+        const uint64_t a0 = smem_desc(smem_u32(s_a), a_lbo, 128);
+        const uint64_t b0 = smem_desc(smem_u32(s_b), N * 16, 128);
+        const int lper = 31 - __clz(per);
+        const long long t0 = clock64();
+#pragma unroll 4
+        for (int r = 0; r < reps; ++r) {
+            /* per and nbuf are powers of two: no integer division on the issuing thread */
+            const int buf = (r >> lper) & (nbuf - 1);
+            mma_f16(tmem + buf * N, a0, b0, idesc, fresh ? (r & (per - 1)) != 0 : 1);
+        }
+        mma_commit(&bar);
+        const bool ok = mbar_wait(&bar, 0);
+        cycles[0] = clock64() - t0;
+        if (!ok) atomicExch(status, 3);
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<512>(tmem);
+}
+
+/* ---- 2c. contention: one thread issues MMAs (4 accumulators of 128 columns, round robin) while `nw` warps
+ *          read accumulators with tcgen05.ld.x32 + wait + 32 FMNMX, unsynchronised ------------------------- */
+__global__ void __launch_bounds__(320) contention_kernel(int mma_reps, int ld_reps, int nw, long long* __restrict__ cycles, float* __restrict__ sink, int* __restrict__ status) {
+    extern __shared__ __align__(128) unsigned char dyn[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int i = tid; i < (8192 + 128 * 32) / 16; i += 320) reinterpret_cast<uint4*>(dyn)[i] = make_uint4(0, 0, 0, 0);
+    fence_async_smem();
+    if (warp == 0) tmem_alloc<512>(&tmem_slot);
+    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = tmem_slot;
+    if (warp == 1) {
+        if (lane == 0 && mma_reps > 0) {
+            const uint32_t idesc = instr_desc(128, 128, FMT_F16, FMT_F16);
+            const uint64_t a0 = smem_desc(smem_u32(dyn), 2048, 128);
+            const uint64_t b0 = smem_desc(smem_u32(dyn + 8192), 2048, 128);
+            const long long t0 = clock64();
+#pragma unroll 4
+            for (int r = 0; r < mma_reps; ++r) mma_f16(tmem + ((r >> 2) & 3) * 128, a0, b0, idesc, (r & 3) != 0);
+            mma_commit(&bar);
+            const bool ok = mbar_wait(&bar, 0);
+            cycles[0] = clock64() - t0;
+            if (!ok) atomicExch(status, 4);
+        }
+    } else if (warp >= 2 && warp < 2 + nw) {
+        const uint32_t tb = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+        float m = 0.f;
+        const long long t0 = clock64();
+        for (int r = 0; r < ld_reps; ++r) {
+            const uint32_t base = tb + ((r + (warp >> 2)) & 3) * 128;
+#pragma unroll
+            for (int c = 0; c < 128; c += 32) {
+                uint32_t v[32];
+                tmem_ld32(base + c, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) m = fminf(m, __uint_as_float(v[j]));
+            }
+        }
+        const long long t1 = clock64();
+        if (lane == 0) cycles[warp] = t1 - t0;
+        sink[tid] = m;
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<512>(tmem);
+}
+
+int run_contention(int mma_reps, int ld_reps, int nw, long long* d_cycles, float* d_sink, int* d_status) {
+    const size_t smem = 8192 + 128 * 32;
+    CK(cudaMemset(d_cycles, 0, 16 * sizeof(long long)));
+    for (int i = 0; i < 2; ++i) {
+        contention_kernel<<<1, 320, smem>>>(mma_reps, ld_reps, nw, d_cycles, d_sink, d_status);
+        CK(cudaDeviceSynchronize());
+    }
+    long long c[16];
+    CK(cudaMemcpy(c, d_cycles, sizeof(c), cudaMemcpyDeviceToHost));
+    printf("contention mma_reps=%5d ld_reps=%4d nw=%d: %.1f cycles/MMA, %.1f cycles per 128x128 accumulator drain (warp 2), %.1f (warp %d)\n",
+           mma_reps, ld_reps, nw, mma_reps ? (double)c[0] / mma_reps : 0.0, ld_reps ? (double)c[2] / ld_reps : 0.0,
+           ld_reps ? (double)c[1 + nw] / ld_reps : 0.0, 1 + nw);
+    return 0;
+}
+
+template <int N>
+int run_switch(int per, int nbuf, int a_lbo, int fresh, long long* d_cycles, int* d_status) {
+    const int reps = 2048;
+    const size_t smem = 65536 + N * 32;
+    CK(cudaFuncSetAttribute(mma_switch_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    for (int i = 0; i < 2; ++i) {
+        mma_switch_kernel<N><<<1, 128, smem>>>(reps, per, nbuf, a_lbo, fresh, d_cycles, d_status);
+        CK(cudaDeviceSynchronize());
+    }
+    long long c = 0;
+    CK(cudaMemcpy(&c, d_cycles, sizeof(c), cudaMemcpyDeviceToHost));
+    printf("mma_switch N=%3d per=%2d nbuf=%d a_lbo=%4d fresh=%d: %.1f cycles/MMA\n", N, per, nbuf, a_lbo, fresh, (double)c / reps);
+    return 0;
+}
+
 /* ---- 3. TMEM load throughput -------------------------------------------------------------------- */
 __global__ void __launch_bounds__(128) tmem_ld_rate_kernel(int reps, long long* __restrict__ cycles, float* __restrict__ sink) {
     __shared__ uint32_t tmem_slot;
@@ -197,8 +319,26 @@ int main() {
             if (run_rate<128>(a_mode, d_cycles, d_status)) return 1;
             if (run_rate<256>(a_mode, d_cycles, d_status)) return 1;
         }
+        for (int a_lbo : {2048})
+            for (int per : {4})
+                if (run_switch<128>(per, 4, a_lbo, 1, d_cycles, d_status)) return 1;
+        if (run_switch<128>(4, 4, 2048, 0, d_cycles, d_status)) return 1;
+        if (run_switch<128>(4, 1, 2048, 1, d_cycles, d_status)) return 1;
+        if (run_switch<256>(4, 2, 2048, 1, d_cycles, d_status)) return 1;
+        if (run_switch<256>(1, 2, 2048, 1, d_cycles, d_status)) return 1;
+        if (run_switch<64>(4, 8, 2048, 1, d_cycles, d_status)) return 1;
+        if (run_switch<64>(1, 8, 2048, 1, d_cycles, d_status)) return 1;
         float* d_sink;
-        CK(cudaMalloc(&d_sink, 128 * 4));
+        CK(cudaMalloc(&d_sink, 320 * 4));
+        {
+            long long* d_c16;
+            CK(cudaMalloc(&d_c16, 16 * sizeof(long long)));
+            if (run_contention(4096, 0, 0, d_c16, d_sink, d_status)) return 1;
+            if (run_contention(0, 512, 4, d_c16, d_sink, d_status)) return 1;
+            if (run_contention(0, 512, 8, d_c16, d_sink, d_status)) return 1;
+            if (run_contention(8192, 512, 4, d_c16, d_sink, d_status)) return 1;
+            if (run_contention(16384, 512, 8, d_c16, d_sink, d_status)) return 1;
+        }
         tmem_ld_rate_kernel<<<1, 128>>>(256, d_cycles, d_sink);
         CK(cudaDeviceSynchronize());
         long long c = 0;
