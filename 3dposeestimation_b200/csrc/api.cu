@@ -313,6 +313,8 @@ void pe_net_destroy(pe_net* net) {
         for (float* p : {net->d_w1, net->d_b1, net->d_s1, net->d_w2, net->d_b2, net->d_s2})
             if (p) cudaFree(p);
         if (net->d_slot) cudaFree(net->d_slot);
+        if (net->d_z1) cudaFree(net->d_z1);
+        if (net->tc_err) cudaFreeHost(net->tc_err);
         for (auto& fc : net->fcs)
             for (float* p : {fc.d_w, fc.d_b, fc.d_slope})
                 if (p) cudaFree(p);
@@ -492,7 +494,7 @@ int pe_compute_descriptors(pe_net* net, const float* patches_hwc, int64_t n, int
     }
     PE_CUDA(cudaMemcpyAsync(out_desc, net->out_stage.p, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToHost, net->stream));
     PE_CUDA(cudaStreamSynchronize(net->stream));
-    return PE_OK;
+    return forward_tc_check(net);
 }
 
 int pe_net_profile(pe_net* net, int enable) {
@@ -540,7 +542,7 @@ int pe_net_sync(pe_net* net) {
     PE_REQUIRE(net != nullptr, "null net");
     PE_CHECK(net_ensure_device(net));
     PE_CUDA(cudaStreamSynchronize(net->stream));
-    return PE_OK;
+    return forward_tc_check(net);
 }
 
 int pe_synth_patches_dev(pe_net* net, uint64_t seed, int64_t first_index, int64_t n, int channels,

@@ -115,6 +115,11 @@ struct pe_net {
     float *d_w1 = nullptr, *d_b1 = nullptr, *d_s1 = nullptr; /* [cin][8][8][16], [16], [16] */
     float *d_w2 = nullptr, *d_b2 = nullptr, *d_s2 = nullptr; /* [16][5][5][8],  [8],  [8]  */
     int* d_slot = nullptr;            /* patch channel -> conv1 input slot or -1 */
+    /* tensor path (conv_tc.cu): Toeplitz fp16 hi/lo conv1 weights, output scale, pinned failure flag */
+    bool c1_tc_ready = false;
+    void* d_z1 = nullptr;
+    float c1_inv_scale = 1.f;
+    int* tc_err = nullptr;
 
     bool profile = false;
     std::vector<cudaEvent_t> prof_events; /* groups of 4: before conv1, after conv1, after conv2, after fcs */
@@ -159,6 +164,11 @@ int net_upload_weights(pe_net* net);
 int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c, float* d_out,
                     int ld_out);
 int net_reserve(pe_net* net, int64_t chunk);
+/* conv_tc.cu */
+int conv1_tc_prepare(pe_net* net);
+bool conv1_tc_usable(const pe_net* net, int patch_c, const void* d_patches);
+int conv1_tc_launch(pe_net* net, const float* d_patches, int patch_c, long long n);
+int forward_tc_check(pe_net* net);
 /* knn.cu */
 int db_set_descriptors(pe_db* db, const float* src, bool src_on_device);
 int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist);

@@ -1,0 +1,346 @@
+/*
+ * conv_tc.cu - conv1 + bias + max-pool + activation of the manifold nets on the tcgen05 tensor path.
+ *
+ * Replaces the first Convolution / Pooling / activation group that `CNN.Forward()` runs inside
+ * networkEvaluator::computeDescriptors (reference src/networkevaluator.cpp:33-48; layers conv1, pool1,
+ * relu1 of network/manifold*.prototxt, e.g. manifold_rgbdnor_16.prototxt:6-38): 16 filters of 8x8xC,
+ * stride 1, no padding, 2x2/2 MAX pooling with Caffe's ceil sizing (57 -> 29), then ReLU / ELU / PReLU.
+ *
+ * Formulation (implicit GEMM without im2col, see umma.cuh):
+ *   - the patch lives in shared memory as an fp16 HWC8 image (one pixel = 8 channel slots = 16 bytes = one
+ *     core-matrix row), split in two terms x ~= hi + lo.  A K-major no-swizzle descriptor with LBO = one pixel
+ *     and SBO = eight pixels makes 128 consecutive pixels the 128 rows of the A operand and (kx, kx+1) x 8
+ *     channels one K step, so the tensor core reads the sliding windows straight out of the image;
+ *   - with only 16 filters the MMA would be bound by its A reads, so N is widened to 128 with a Toeplitz
+ *     copy of the weights: column (j, f) of the accumulator is output row r + j, filter f, and a K step over
+ *     input row r + ky' uses weight row ky' - j (zero outside 0..7).  The Toeplitz operand is itself an
+ *     overlapping window over a short array of 256-byte weight slabs (SBO = 128, start = (14 - ky') slabs);
+ *   - image rows are stored in the order (y mod 8, y div 8) so that the two base rows r and r + 8 of a tile
+ *     are adjacent: one tile = 2 base rows x 64 pixels = 128 accumulator lanes = 16 output rows;
+ *   - fp32 accuracy: D = A_hi.B_hi + A_hi.B_lo + A_lo.B_hi in fp32 (TMEM), operands scaled by powers of two.
+ *   Per patch: 4 tiles x 15 input rows x 4 pixel pairs x 3 products = 720 MMAs of 128x128x16.
+ *
+ * Kernel (persistent, one CTA per SM, 416 threads): warp 0 issues the MMAs, warps 1-4 drain the accumulators
+ * (pool in registers / by shuffle, bias, activation, store), warps 5-12 stream the next patch in 16-row blocks
+ * (fp32 HWC -> fp16 hi/lo) as soon as a block's last reader tile has completed.
+ */
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+#include "common.h"
+#include "umma.cuh"
+
+namespace pe {
+
+using namespace umma;
+
+namespace {
+
+constexpr int kRowBytes = 1024;                    /* 64 pixels x 16 bytes */
+constexpr int kImgRows = 72;                       /* 64 image rows + 8 zero rows (base row 56 reads up to row 70) */
+constexpr int kImgBytes = kImgRows * kRowBytes;    /* per term */
+constexpr int kZSlabs = 127;                       /* 8 x (7 zero + 8 weight rows) + 7 zero slabs of 256 bytes */
+constexpr int kZBytes = kZSlabs * 256;             /* per term */
+constexpr int kZStride = 15 * 256;                 /* from the array of kx to the array of kx + 1 */
+constexpr int kOffImgHi = 0, kOffImgLo = kImgBytes;
+constexpr int kOffZHi = 2 * kImgBytes, kOffZLo = kOffZHi + kZBytes;
+constexpr int kOffMisc = kOffZLo + kZBytes;        /* bias[16] slope[16] barriers */
+constexpr int kC1TcSmem = kOffMisc + 512;
+constexpr int kC1TcThreads = 416;
+constexpr int kLog2Sx = 8;                         /* image scale 2^8: |x| <= 255 stays finite in fp16 */
+
+constexpr int kP1H = 30, kP1W = 32, kP1Plane = kP1H * kP1W, kP1Patch = 16 * kP1Plane;   /* as forward.cu */
+
+__device__ __forceinline__ int row_pos(int y) { return (y & 7) * 9 + (y >> 3); }
+
+__device__ __forceinline__ float act_apply(float v, int act, float slope) {
+    const float pos = fmaxf(v, 0.f), neg = fminf(v, 0.f);
+    if (act == PE_ACT_RELU) return pos;
+    if (act == PE_ACT_ELU) return pos + (expf(neg) - 1.0f);
+    if (act == PE_ACT_PRELU) return pos + slope * neg;
+    return v;
+}
+
+__device__ __forceinline__ uint32_t pack2(__half a, __half b) {
+    return static_cast<uint32_t>(__half_as_ushort(a)) | (static_cast<uint32_t>(__half_as_ushort(b)) << 16);
+}
+
+struct C1Args {
+    const float* patches;      /* [n][64][64][CP] fp32 */
+    long long n;
+    const uint4* ztoeplitz;    /* hi term then lo term, kZBytes each */
+    const float* bias;         /* [16] */
+    const float* slope;        /* [16] or null */
+    int act;
+    float inv_scale;           /* 1 / (s_x s_w) */
+    float* pool1;              /* [n][16][30][32] */
+    int* err;                  /* pinned flag: 1.. barrier time-out, 100 input magnitude above 255 */
+};
+
+template <int CP>
+__global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args a) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    float* s_bias = reinterpret_cast<float*>(smem + kOffMisc);
+    float* s_slope = s_bias + 16;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffMisc + 128);
+    uint64_t* img_full = bars;          /* [4] 16-row block converted (256 loader threads) */
+    uint64_t* img_empty = bars + 4;     /* [4] last reader tile of the block has completed */
+    uint64_t* acc_full = bars + 8;      /* [4] tile accumulated */
+    uint64_t* acc_empty = bars + 12;    /* [4] tile drained (4 epilogue warps) */
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+    volatile int* s_abort = reinterpret_cast<volatile int*>(tmem_slot + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    /* one-time: zero the image buffers (pad rows and the unused channel slot stay zero), load the Toeplitz weights */
+    for (int i = tid; i < 2 * kImgBytes / 16; i += kC1TcThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < 2 * kZBytes / 16; i += kC1TcThreads) reinterpret_cast<uint4*>(smem + kOffZHi)[i] = a.ztoeplitz[i];
+    if (tid < 16) {
+        s_bias[tid] = a.bias[tid];
+        s_slope[tid] = a.slope ? a.slope[tid] : 0.f;
+    }
+    if (tid == 0) {
+        for (int i = 0; i < 4; ++i) {
+            mbar_init(&img_full[i], 256);
+            mbar_init(&img_empty[i], 1);
+            mbar_init(&acc_full[i], 1);
+            mbar_init(&acc_empty[i], 4);
+        }
+        *s_abort = 0;
+        mbar_fence_init();
+    }
+    if (warp == 0) tmem_alloc<512>(tmem_slot);
+    fence_async_smem();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        /* ======================= MMA issuer ======================= */
+        if (lane == 0) {
+            const uint32_t idesc = instr_desc(128, 128, FMT_F16, FMT_F16);
+            const uint32_t s0 = smem_u32(smem);
+            const uint64_t a_hi = smem_desc(s0 + kOffImgHi, 16, 128), a_lo = smem_desc(s0 + kOffImgLo, 16, 128);
+            const uint64_t b_hi = smem_desc(s0 + kOffZHi, kZStride, 128), b_lo = smem_desc(s0 + kOffZLo, kZStride, 128);
+            uint32_t it = 0;
+            for (long long patch = blockIdx.x; patch < a.n && !*s_abort; patch += gridDim.x, ++it) {
+#pragma unroll 1
+                for (int t = 0; t < 4; ++t) {
+                    if (!mbar_wait(&acc_empty[t], (it & 1) ^ 1)) { atomicExch(a.err, 1); *s_abort = 1; break; }
+                    if (!mbar_wait(&img_full[t], it & 1)) { atomicExch(a.err, 2); *s_abort = 1; break; }
+                    if (t < 3 && !mbar_wait(&img_full[t + 1], it & 1)) { atomicExch(a.err, 3); *s_abort = 1; break; }
+                    fence_after_sync();
+                    const uint32_t d = tmem + t * 128;
+                    uint32_t acc = 0;
+#pragma unroll 1
+                    for (int ky = 0; ky < 15; ++ky) {
+                        const uint32_t a_row = static_cast<uint32_t>(row_pos(16 * t + ky)) * (kRowBytes >> 4);
+                        const uint32_t b_row = static_cast<uint32_t>(14 - ky) * (256 >> 4);
+#pragma unroll
+                        for (int p = 0; p < 4; ++p) {
+                            const uint32_t ao = a_row + p * 2, bo = b_row + p * 2 * (kZStride >> 4);
+                            mma_f16(d, a_hi + ao, b_hi + bo, idesc, acc);
+                            acc = 1;
+                            mma_f16(d, a_hi + ao, b_lo + bo, idesc, 1);
+                            mma_f16(d, a_lo + ao, b_hi + bo, idesc, 1);
+                        }
+                    }
+                    mma_commit(&img_empty[t]);
+                    mma_commit(&acc_full[t]);
+                }
+            }
+        }
+    } else if (warp <= 4) {
+        /* ======================= epilogue ======================= */
+        const int quarter = warp & 3;
+        const int m = quarter * 32 + lane;            /* accumulator lane */
+        const int grp = m >> 6, x = m & 63;
+        const int px = x >> 1;
+        const bool own_ok = x <= 56, other_ok = (x ^ 1) <= 56;
+        const int fsel = (x & 1) * 8;                 /* even lanes store filters 0..7, odd lanes 8..15 */
+        uint32_t it = 0;
+        for (long long patch = blockIdx.x; patch < a.n && !*s_abort; patch += gridDim.x, ++it) {
+            float* out = a.pool1 + patch * (long long)kP1Patch;
+#pragma unroll 1
+            for (int t = 0; t < 4; ++t) {
+                if (!mbar_wait(&acc_full[t], it & 1)) { atomicExch(a.err, 4); *s_abort = 1; break; }
+                fence_after_sync();
+                const uint32_t tbase = tmem + t * 128 + (static_cast<uint32_t>(quarter * 32) << 16);
+                const int r = 16 * t + 8 * grp;        /* base conv row of this lane */
+#pragma unroll 1
+                for (int half = 0; half < 2; ++half) {
+                    uint32_t v[2][32];
+                    tmem_ld32(tbase + half * 64, v[0]);
+                    tmem_ld32(tbase + half * 64 + 32, v[1]);
+                    tmem_ld_wait();
+                    if (half == 1) {       /* every column of the tile is in registers: hand the accumulator back */
+                        fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&acc_empty[t]);
+                    }
+#pragma unroll
+                    for (int j2 = 0; j2 < 2; ++j2) {
+                        const int ya = r + 4 * half + 2 * j2;   /* conv rows ya, ya + 1 -> pooled row ya / 2 */
+                        const int py = ya >> 1;
+                        const bool row_b = ya + 1 <= 56;
+#pragma unroll
+                        for (int f = 0; f < 16; ++f) {
+                            float c = __uint_as_float(v[j2][f]);
+                            if (row_b) c = fmaxf(c, __uint_as_float(v[j2][16 + f]));
+                            if (!own_ok) c = -FLT_MAX;
+                            const float o = __shfl_xor_sync(0xffffffffu, c, 1);
+                            if (other_ok) c = fmaxf(c, o);
+                            if ((f & 8) == fsel && ya <= 56 && px <= 28)
+                                out[f * kP1Plane + py * kP1W + px] = act_apply(fmaf(c, a.inv_scale, s_bias[f]), a.act, s_slope[f]);
+                        }
+                    }
+                }
+            }
+        }
+    } else {
+        /* ======================= loaders: fp32 HWC -> fp16 hi / lo HWC8, 16 rows at a time ======================= */
+        const int lt = tid - 160;                      /* 0..255: row (lt >> 4) of the block, pixels 4 * (lt & 15) .. +3 */
+        const int yr = lt >> 4, x0 = (lt & 15) * 4;
+        const float sx = static_cast<float>(1 << kLog2Sx);
+        float vmax = 0.f;
+        uint32_t it = 0;
+        for (long long patch = blockIdx.x; patch < a.n && !*s_abort; patch += gridDim.x, ++it) {
+            const float* src = a.patches + patch * (long long)(4096 * CP);
+#pragma unroll 1
+            for (int rb = 0; rb < 4; ++rb) {
+                const int y = rb * 16 + yr;
+                float val[4 * CP];
+                const float4* s4 = reinterpret_cast<const float4*>(src + (size_t)(y * 64 + x0) * CP);
+#pragma unroll
+                for (int i = 0; i < CP; ++i) {
+                    float4 q;
+                    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                                 : "=f"(q.x), "=f"(q.y), "=f"(q.z), "=f"(q.w) : "l"(s4 + i));
+                    val[4 * i + 0] = q.x; val[4 * i + 1] = q.y; val[4 * i + 2] = q.z; val[4 * i + 3] = q.w;
+                }
+                if (!mbar_wait(&img_empty[rb], (it & 1) ^ 1)) { atomicExch(a.err, 5); *s_abort = 1; break; }
+                unsigned char* dst = smem + row_pos(y) * kRowBytes + x0 * 16;
+#pragma unroll
+                for (int p = 0; p < 4; ++p) {
+                    uint32_t hi[4], lo[4];
+#pragma unroll
+                    for (int c2 = 0; c2 < 4; ++c2) {
+                        __half h[2], l[2];
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int ch = 2 * c2 + e;
+                            const float xv = ch < CP ? val[p * CP + (ch < CP ? ch : 0)] : 0.f;
+                            vmax = fmaxf(vmax, fabsf(xv));
+                            split_f16(xv * sx, h[e], l[e]);
+                        }
+                        hi[c2] = pack2(h[0], h[1]);
+                        lo[c2] = pack2(l[0], l[1]);
+                    }
+                    *reinterpret_cast<uint4*>(dst + kOffImgHi + p * 16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                    *reinterpret_cast<uint4*>(dst + kOffImgLo + p * 16) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                }
+                fence_async_smem();
+                mbar_arrive(&img_full[rb]);
+            }
+        }
+        if (!(vmax <= 255.f)) atomicExch(a.err, 100);   /* also catches NaN */
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<512>(tmem);
+}
+
+}  // namespace
+
+/* Toeplitz copy of the conv1 weights for the tensor kernel (see the header comment): per term (hi, lo) and per kx
+ * an array of 256-byte slabs [16 filters][8 patch channels]; slab 7 + (7 - ky) of array kx holds weight row ky.
+ * The Slice/Concat/Silence channel select (network/manifold_rgb_16.prototxt:6-33) is folded in here: a patch
+ * channel that the net drops gets zero weights, so the image is converted in patch channel order. */
+int conv1_tc_prepare(pe_net* net) {
+    net->c1_tc_ready = false;
+    const int cp = net->def.channels;
+    if (cp != 4 && cp != 7) return PE_OK;     /* loader instantiations; other counts use the SIMT kernel */
+    const std::vector<float>& w = net->blobs[net->blob_w1];   /* [16][cin][8][8] */
+    const int cin = net->cin;
+    float wmax = 0.f;
+    for (float v : w) wmax = std::fmax(wmax, std::fabs(v));
+    if (!(wmax > 0.f) || !std::isfinite(wmax)) return PE_OK;
+    const int log2_sw = 10 - std::ilogb(wmax);
+    const float sw = std::ldexp(1.f, log2_sw);
+    std::vector<int> slot_of(8, -1);
+    for (size_t s = 0; s < net->def.sel.size(); ++s) slot_of[net->def.sel[s]] = (int)s;
+    std::vector<uint16_t> z((size_t)2 * kZBytes / 2, 0);
+    for (int kx = 0; kx < 8; ++kx)
+        for (int ky = 0; ky < 8; ++ky)
+            for (int f = 0; f < 16; ++f)
+                for (int ch = 0; ch < cp; ++ch) {
+                    const int sl = slot_of[ch];
+                    if (sl < 0 || sl >= cin) continue;
+                    const float v = w[(((size_t)f * cin + sl) * 8 + ky) * 8 + kx] * sw;
+                    const __half h = __float2half_rn(v);
+                    const __half l = __float2half_rn(v - __half2float(h));
+                    const size_t slab = (size_t)kx * 15 + 7 + (7 - ky);
+                    const size_t at = slab * 128 + (size_t)f * 8 + ch;       /* in halves */
+                    uint16_t hb, lb;
+                    memcpy(&hb, &h, 2);
+                    memcpy(&lb, &l, 2);
+                    z[at] = hb;
+                    z[(size_t)kZBytes / 2 + at] = lb;
+                }
+    PE_CUDA(cudaSetDevice(net->device));
+    if (!net->d_z1) PE_CUDA(cudaMalloc(&net->d_z1, 2 * kZBytes));
+    PE_CUDA(cudaMemcpy(net->d_z1, z.data(), 2 * kZBytes, cudaMemcpyHostToDevice));
+    if (!net->tc_err) {
+        PE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&net->tc_err), sizeof(int), cudaHostAllocMapped));
+        *net->tc_err = 0;
+    }
+    net->c1_inv_scale = std::ldexp(1.f, -(log2_sw + kLog2Sx));
+    net->c1_tc_ready = true;
+    return PE_OK;
+}
+
+bool conv1_tc_usable(const pe_net* net, int patch_c, const void* d_patches) {
+    return g_opt_forward_tensor.load() != 0 && net->c1_tc_ready && patch_c == net->def.channels &&
+           (reinterpret_cast<uintptr_t>(d_patches) & 15) == 0;
+}
+
+int conv1_tc_launch(pe_net* net, const float* d_patches, int patch_c, long long n) {
+    C1Args a;
+    a.patches = d_patches;
+    a.n = n;
+    a.ztoeplitz = reinterpret_cast<const uint4*>(net->d_z1);
+    a.bias = net->d_b1;
+    a.slope = net->d_s1;
+    a.act = net->act1;
+    a.inv_scale = net->c1_inv_scale;
+    a.pool1 = net->pool1.as<float>();
+    a.err = net->tc_err;
+    const int grid = (int)(n < net->num_sms ? n : net->num_sms);
+    if (patch_c == 7) {
+        PE_CUDA(cudaFuncSetAttribute(conv1_tc_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, kC1TcSmem));
+        conv1_tc_kernel<7><<<grid, kC1TcThreads, kC1TcSmem, net->stream>>>(a);
+    } else {
+        PE_CUDA(cudaFuncSetAttribute(conv1_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kC1TcSmem));
+        conv1_tc_kernel<4><<<grid, kC1TcThreads, kC1TcSmem, net->stream>>>(a);
+    }
+    PE_LAUNCHED();
+    return PE_OK;
+}
+
+/* after a synchronisation: reports (and clears) a failure recorded by the tensor forward kernels */
+int forward_tc_check(pe_net* net) {
+    if (!net->tc_err) return PE_OK;
+    const int e = *reinterpret_cast<volatile int*>(net->tc_err);
+    if (e == 0) return PE_OK;
+    *net->tc_err = 0;
+    if (e == 100) {
+        set_error("tensor forward: an input value is not finite or exceeds 255 in magnitude (patches are expected in [-1, 1]: "
+                  "reference src/datasetmanager.cpp:327-343); use pe_set_option(\"forward_tensor\", 0) for such data");
+        return PE_ERR_INVALID;
+    }
+    set_error("tensor forward: pipeline barrier %d timed out", e);
+    return PE_ERR_CUDA;
+}
+
+}  // namespace pe

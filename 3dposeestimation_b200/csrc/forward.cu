@@ -367,6 +367,7 @@ int net_upload_weights(pe_net* net) {
         if (!net->d_slot) PE_CUDA(cudaMalloc(&net->d_slot, 8 * sizeof(int)));
         PE_CUDA(cudaMemcpy(net->d_slot, slot.data(), 8 * sizeof(int), cudaMemcpyHostToDevice));
     }
+    PE_CHECK(conv1_tc_prepare(net));
     net->weights_dirty = false;
     return PE_OK;
 }
@@ -407,6 +408,9 @@ int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c,
         const long long m = (n - first < net->chunk) ? (n - first) : net->chunk;
         const float* src = d_patches + (size_t)first * 4096 * patch_c;
         PE_CHECK(prof_mark(net->profile, &net->prof_events, net->stream));
+        if (conv1_tc_usable(net, patch_c, src)) {
+            PE_CHECK(conv1_tc_launch(net, src, patch_c, m));
+        } else
         switch (net->cin) {
         case 1: PE_CHECK(launch_conv1<1>(net, src, patch_c, m)); break;
         case 2: PE_CHECK(launch_conv1<2>(net, src, patch_c, m)); break;

@@ -34,8 +34,16 @@ def make_net(gpu, po, synth, name, seed):
 
 
 # ---------------------------------------------------------------------------- forward ---
+@pytest.fixture(params=[1, 0], ids=["tensor", "simt"])
+def fwd_path(gpu, request):
+    """runs a test once with the tcgen05 forward kernels (default) and once with the fp32 SIMT kernels"""
+    gpu.set_option("forward_tensor", request.param)
+    yield request.param
+    gpu.set_option("forward_tensor", 1)
+
+
 @pytest.mark.parametrize("vi,name", list(enumerate(netdefs.VARIANTS)))
-def test_forward_matches_oracle_and_golden(gpu, po, synth, golden, vi, name):
+def test_forward_matches_oracle_and_golden(gpu, po, synth, golden, vi, name, fwd_path):
     net, oracle, ref = make_net(gpu, po, synth, name, synth.BASE_SEED + vi)
     # the three golden patches (torch fp32 / fp64 outputs committed in tests/golden)
     patches = synth.make_patches(synth.BASE_SEED, 100 * vi, 3, ref.channels, 2)
@@ -63,7 +71,7 @@ def test_forward_rejects_wrong_channel_count(gpu):
     assert e.value.code == gpu.PE_ERR_INVALID
 
 
-def test_forward_device_entry_and_chunking(gpu, po, synth):
+def test_forward_device_entry_and_chunking(gpu, po, synth, fwd_path):
     """device-resident patches, more than one 4096-patch chunk, unaligned tail"""
     net, oracle, ref = make_net(gpu, po, synth, "manifold_rgbdnor_16", 99)
     n = 4096 + 37
@@ -86,7 +94,7 @@ def test_forward_device_entry_and_chunking(gpu, po, synth):
     assert np.isfinite(got).all()
 
 
-def test_weights_can_be_replaced(gpu, po, synth):
+def test_weights_can_be_replaced(gpu, po, synth, fwd_path):
     net, oracle, ref = make_net(gpu, po, synth, "manifold_rgbd_16", 5)
     x = synth.make_patches(3, 0, 4, 7, 2)
     a = net.compute_descriptors(x)
