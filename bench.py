@@ -138,7 +138,7 @@ def gpu_arm(args, rank, world, local_rank, dist):
     net.fill(SEED, 1)
     T = N_OBJ * POSES
     # ---- setup (untimed): template descriptors of this rank's row shard, computed by the same forward
-    lo, hi = rank * T // world, (rank + 1) * T // world
+    lo, hi = importlib.import_module("3dposeestimation_b200.sharding").shard_rows(rank, world, T)
     d_db = capi.DeviceArray((hi - lo, 16), device=dev)
     d_in = [capi.DeviceArray((BATCH, 64, 64, 7), device=dev) for _ in range(2)]   # 2 x 470 MB > L2 (126 MB)
     for first in range(lo, hi, BATCH):

@@ -96,6 +96,10 @@ public:
     pe_net* handle() const { return h_; }
     void fill(uint64_t seed, int mode) { pe_check(pe_net_fill(h_, seed, mode)); }
     void loadWeights(const std::string& path) { pe_check(pe_net_load_weights(h_, path.c_str())); }
+    /* learnable blobs in Caffe order (net.params()): stands in for CopyTrainedLayersFrom /
+     * ShareTrainedLayersWith (src/networksolver.cpp:307,377) */
+    int numBlobs() const { int n = 0; pe_check(pe_net_num_blobs(h_, &n)); return n; }
+    void setBlob(int blob, const float* data, int64_t count) { pe_check(pe_net_set_blob(h_, blob, data, count)); }
     /* CNN.input_blobs()[0] / output_blobs()[0] shapes (src/networkevaluator.cpp:11-19) */
     void shape(int* batch, int* channels, int* height, int* width, int* desc_dim) const {
         pe_check(pe_net_info(h_, batch, channels, height, width, desc_dim));
