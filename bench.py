@@ -237,9 +237,11 @@ def gpu_arm(args, rank, world, local_rank, dist):
     scan_ms = db_ms[0] / max(1, db_calls)
     conv1_flops = 2.0 * MAC_PER_PATCH["conv1"] * BATCH
     achieved_tf = conv1_flops / (conv1_ms * 1e-3) / 1e12 if conv1_ms > 0 else 0.0
+    fwd_tensor = capi.get_option("forward_tensor") != 0
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get("conv1_pool_act_bytes_per_launch")
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        traffic = tj.get("conv1_tc_bytes_per_launch" if fwd_tensor else "conv1_pool_act_bytes_per_launch")
     except Exception:
         pass
     step_ms = ms_total / args.steps
@@ -252,16 +254,21 @@ def gpu_arm(args, rank, world, local_rank, dist):
                    "net": NET, "batch_per_gpu": BATCH, "templates": T, "k": K, "seed": SEED,
                    "l2_flush": "inputs alternate between two 470 MB batches (> 126 MB L2)",
                    "parallelism": f"patches x{world} (no comm), DB rows /{world} + NCCL all-gather + merge" if world > 1 else "single GPU"},
-        "roofline": {"kernel": "conv1_pool_act_kernel<7>", "bound": "tensor", "achieved": achieved_tf,
+        "roofline": {"kernel": "conv1_tc_kernel<7>" if fwd_tensor else "conv1_pool_act_kernel<7>", "bound": "tensor", "achieved": achieved_tf,
                      "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
                      "frac": achieved_tf / peaks["bf16_tflops_sustained"], "traffic": traffic,
                      "peak_source": f"{peaks['source']} bf16 sustained (kernel timed inside a long step)",
-                     "note": "fp32 SIMT kernel: the pipe that binds it is FP32 FMA (~74 TFLOP/s at 1965 MHz), see fp32_fma_frac; "
-                             "HBM side: achieved_hbm_gbs of the same kernel",
+                     "note": ("tcgen05 split-fp16 implicit GEMM: achieved = ALGORITHMIC conv1 FLOPs (2 x 23,288,832 per patch) / launch time; "
+                              "the kernel executes 8.1x that in tensor FLOPs (x3 fp16 split for fp32 parity, x1.875 Toeplitz widening to N=128, "
+                              "x8/7 channel pad, x1.26 tile edges), see executed_tflops / executed_frac") if fwd_tensor else
+                             "fp32 SIMT kernel: the pipe that binds it is FP32 FMA (~74 TFLOP/s at 1965 MHz), see fp32_fma_frac",
                      "algorithmic_flops_per_launch": conv1_flops, "launch_ms": conv1_ms,
-                     "fp32_fma_frac": achieved_tf / 74.4,
+                     "executed_tflops": (720 * 2.0 * 128 * 128 * 16 * BATCH / (conv1_ms * 1e-3) / 1e12) if (fwd_tensor and conv1_ms > 0) else None,
+                     "executed_frac": (720 * 2.0 * 128 * 128 * 16 * BATCH / (conv1_ms * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"]) if (fwd_tensor and conv1_ms > 0) else None,
+                     "fp32_fma_frac": None if fwd_tensor else achieved_tf / 74.4,
                      "achieved_hbm_gbs": BATCH * (BYTES_PER_PATCH + 16 * 30 * 32 * 4) / (conv1_ms * 1e-3) / 1e9 if conv1_ms > 0 else 0.0,
                      "hbm_peak_gbs": peaks["hbm_gbs"]},
+        "paths": {"forward": "tcgen05" if fwd_tensor else "simt", "knn": "tcgen05" if capi.get_option("knn_tensor") else "simt"},
         "kernels_ms_per_step": {"conv1_pool_act": conv1_ms, "conv2_pool_act": net_ms[1] / max(1, net_calls),
                                 "fc_act": net_ms[2] / max(1, net_calls), "knn_l2_scan": scan_ms,
                                 "knn_select": db_ms[1] / max(1, db_calls)},

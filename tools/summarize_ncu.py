@@ -129,7 +129,9 @@ def main():
     tr = full(a.tag)
     tj = {"tag": a.tag, "dram_bytes_per_launch": tr, "ncu_us_per_launch_timed_region": per}
     for k, v in tr.items():
-        if "conv" in k and "1" in k:
+        if "conv1_tc" in k:
+            tj["conv1_tc_bytes_per_launch"] = v
+        elif "conv1_pool_act" in k:
             tj["conv1_pool_act_bytes_per_launch"] = v
         if "scan" in k:
             tj["knn_scan_bytes_per_launch"] = v
