@@ -316,8 +316,11 @@ void pe_net_destroy(pe_net* net) {
         if (net->d_z1) cudaFree(net->d_z1);
         if (net->tc_err) cudaFreeHost(net->tc_err);
         for (auto& fc : net->fcs)
+        {
             for (float* p : {fc.d_w, fc.d_b, fc.d_slope})
                 if (p) cudaFree(p);
+            if (fc.d_wp) cudaFree(fc.d_wp);
+        }
         net->pool1.release(); net->pool2.release(); net->fc_a.release(); net->fc_b.release();
         net->in_stage[0].release(); net->in_stage[1].release(); net->out_stage.release();
         for (int i = 0; i < 2; ++i) { cudaEventDestroy(net->ev_in[i]); cudaEventDestroy(net->ev_done[i]); }

@@ -94,6 +94,11 @@ struct FcPlan {
     float* d_w = nullptr;      /* [out][ld_in] */
     float* d_b = nullptr;      /* [out] */
     float* d_slope = nullptr;  /* [out] or null */
+    /* tensor path (fc_tc.cu): packed fp16 hi/lo weight blocks, K blocks of 64, output scale */
+    bool tc_ready = false;
+    void* d_wp = nullptr;
+    int k_blocks = 0;
+    float inv_scale = 1.f;
 };
 
 }  // namespace pe
@@ -169,6 +174,9 @@ int conv1_tc_prepare(pe_net* net);
 bool conv1_tc_usable(const pe_net* net, int patch_c, const void* d_patches);
 int conv1_tc_launch(pe_net* net, const float* d_patches, int patch_c, long long n);
 int forward_tc_check(pe_net* net);
+/* fc_tc.cu */
+int fc_tc_prepare(pe_net* net, FcPlan* fc);
+int fc_tc_launch(pe_net* net, const FcPlan& fc, const float* x, int ldx, float* y, int ldy, int n_store, int m);
 /* knn.cu */
 int db_set_descriptors(pe_db* db, const float* src, bool src_on_device);
 int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist);

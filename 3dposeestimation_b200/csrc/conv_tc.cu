@@ -334,9 +334,10 @@ int forward_tc_check(pe_net* net) {
     const int e = *reinterpret_cast<volatile int*>(net->tc_err);
     if (e == 0) return PE_OK;
     *net->tc_err = 0;
-    if (e == 100) {
-        set_error("tensor forward: an input value is not finite or exceeds 255 in magnitude (patches are expected in [-1, 1]: "
-                  "reference src/datasetmanager.cpp:327-343); use pe_set_option(\"forward_tensor\", 0) for such data");
+    if (e >= 100) {
+        set_error("tensor forward: %s is not finite or exceeds the fp16 split range (patches are expected in [-1, 1]: "
+                  "reference src/datasetmanager.cpp:327-343); use pe_set_option(\"forward_tensor\", 0) for such data",
+                  e == 100 ? "an input value (|x| > 255)" : "an activation (|x| > 4000)");
         return PE_ERR_INVALID;
     }
     set_error("tensor forward: pipeline barrier %d timed out", e);

@@ -360,6 +360,7 @@ int net_upload_weights(pe_net* net) {
         PE_CHECK(dev_alloc_copy(&fc.d_w, w));
         PE_CHECK(dev_alloc_copy(&fc.d_b, net->blobs[fc.blob_b]));
         if (fc.blob_slope >= 0) PE_CHECK(dev_alloc_copy(&fc.d_slope, net->blobs[fc.blob_slope]));
+        PE_CHECK(fc_tc_prepare(net, &fc));
     }
     {
         std::vector<int> slot(8, -1);
@@ -404,6 +405,7 @@ int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c,
         PE_CUDA(cudaFuncSetAttribute(conv2_pool_act_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
         c2_attr[net->device & 15] = true;
     }
+    const bool fwd_tensor = g_opt_forward_tensor.load() != 0;
     for (int64_t first = 0; first < n; first += net->chunk) {
         const long long m = (n - first < net->chunk) ? (n - first) : net->chunk;
         const float* src = d_patches + (size_t)first * 4096 * patch_c;
@@ -435,10 +437,14 @@ int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c,
             const bool last = i + 1 == net->fcs.size();
             float* y = last ? d_out + (size_t)first * ld_out : ((i & 1) ? net->fc_b.as<float>() : net->fc_a.as<float>());
             const int ldy = last ? ld_out : ((fc.out + 3) & ~3);
-            dim3 grid((unsigned)((m + kBM - 1) / kBM), (unsigned)((fc.out + kBN - 1) / kBN));
-            fc_act_kernel<<<grid, 256, 0, net->stream>>>(x, ldx, fc.d_w, fc.ld_in, fc.d_b, fc.d_slope, fc.act, y,
-                                                         ldy, (int)m, fc.out, last ? fc.out : ldy, fc.ld_in);
-            PE_LAUNCHED();
+            if (fwd_tensor && fc.tc_ready) {
+                PE_CHECK(fc_tc_launch(net, fc, x, ldx, y, ldy, last ? fc.out : ldy, (int)m));
+            } else {
+                dim3 grid((unsigned)((m + kBM - 1) / kBM), (unsigned)((fc.out + kBN - 1) / kBN));
+                fc_act_kernel<<<grid, 256, 0, net->stream>>>(x, ldx, fc.d_w, fc.ld_in, fc.d_b, fc.d_slope, fc.act, y,
+                                                             ldy, (int)m, fc.out, last ? fc.out : ldy, fc.ld_in);
+                PE_LAUNCHED();
+            }
             x = y;
             ldx = ldy;
         }
