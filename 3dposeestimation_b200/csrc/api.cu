@@ -314,6 +314,7 @@ void pe_net_destroy(pe_net* net) {
             if (p) cudaFree(p);
         if (net->d_slot) cudaFree(net->d_slot);
         if (net->d_z1) cudaFree(net->d_z1);
+        if (net->d_z2) cudaFree(net->d_z2);
         if (net->tc_err) cudaFreeHost(net->tc_err);
         for (auto& fc : net->fcs)
         {
@@ -321,7 +322,7 @@ void pe_net_destroy(pe_net* net) {
                 if (p) cudaFree(p);
             if (fc.d_wp) cudaFree(fc.d_wp);
         }
-        net->pool1.release(); net->pool2.release(); net->fc_a.release(); net->fc_b.release();
+        net->pool1.release(); net->p1_packed.release(); net->pool2.release(); net->fc_a.release(); net->fc_b.release();
         net->in_stage[0].release(); net->in_stage[1].release(); net->out_stage.release();
         for (int i = 0; i < 2; ++i) { cudaEventDestroy(net->ev_in[i]); cudaEventDestroy(net->ev_done[i]); }
         cudaStreamDestroy(net->stream);

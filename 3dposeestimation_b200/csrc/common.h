@@ -124,6 +124,9 @@ struct pe_net {
     bool c1_tc_ready = false;
     void* d_z1 = nullptr;
     float c1_inv_scale = 1.f;
+    bool c2_tc_ready = false;
+    void* d_z2 = nullptr;
+    float c2_inv_scale = 1.f;
     int* tc_err = nullptr;
 
     bool profile = false;
@@ -131,7 +134,7 @@ struct pe_net {
 
     /* per-chunk activations (sized for `chunk` patches) and staging for the host entry point */
     int64_t chunk = 0;
-    pe::DevBuf pool1, pool2, fc_a, fc_b, in_stage[2], out_stage;
+    pe::DevBuf pool1, p1_packed, pool2, fc_a, fc_b, in_stage[2], out_stage;
 };
 
 struct pe_db {
@@ -172,7 +175,10 @@ int net_reserve(pe_net* net, int64_t chunk);
 /* conv_tc.cu */
 int conv1_tc_prepare(pe_net* net);
 bool conv1_tc_usable(const pe_net* net, int patch_c, const void* d_patches);
-int conv1_tc_launch(pe_net* net, const float* d_patches, int patch_c, long long n);
+int conv1_tc_launch(pe_net* net, const float* d_patches, int patch_c, long long n, bool packed_out);
+int conv2_tc_prepare(pe_net* net);
+int conv2_tc_launch(pe_net* net, long long n);
+size_t conv_tc_p1_packed_bytes();
 int forward_tc_check(pe_net* net);
 /* fc_tc.cu */
 int fc_tc_prepare(pe_net* net, FcPlan* fc);

@@ -54,6 +54,14 @@ constexpr int kP1H = 30, kP1W = 32, kP1Plane = kP1H * kP1W, kP1Patch = 16 * kP1P
 
 __device__ __forceinline__ int row_pos(int y) { return (y & 7) * 9 + (y >> 3); }
 
+/* pool1 as conv2_tc reads it: 29 x 29 x 16 activations, fp16 hi / lo, two blocks of 8 channels, rows in
+ * (y mod 8, y div 8) order (40 row slots), 32 pixels per row, scaled by 2^4 */
+constexpr int kP1Rows = 40;
+constexpr int kP1PlaneBytes = kP1Rows * 512;             /* one term of one channel block */
+constexpr int kP1PackedBytes = 4 * kP1PlaneBytes;        /* hi: cblk0, cblk1; lo: cblk0, cblk1 = 81,920 B per patch */
+constexpr float kP1Scale = 16.f;
+__host__ __device__ __forceinline__ int p1_row_pos(int y) { return (y & 7) * 5 + (y >> 3); }
+
 __device__ __forceinline__ float act_apply(float v, int act, float slope) {
     const float pos = fmaxf(v, 0.f), neg = fminf(v, 0.f);
     if (act == PE_ACT_RELU) return pos;
@@ -74,7 +82,8 @@ struct C1Args {
     const float* slope;        /* [16] or null */
     int act;
     float inv_scale;           /* 1 / (s_x s_w) */
-    float* pool1;              /* [n][16][30][32] */
+    float* pool1;              /* [n][16][30][32] fp32 (SIMT conv2) */
+    unsigned char* p1_packed;  /* or, for conv2_tc: [n][hi,lo][2 channel blocks][40 rows][32 px][8 ch] fp16 */
     int* err;                  /* pinned flag: 1.. barrier time-out, 100 input magnitude above 255 */
 };
 
@@ -184,6 +193,7 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
                         const int ya = r + 4 * half + 2 * j2;   /* conv rows ya, ya + 1 -> pooled row ya / 2 */
                         const int py = ya >> 1;
                         const bool row_b = ya + 1 <= 56;
+                        float keep[8];                      /* this lane's 8 filters: 0..7 on even x, 8..15 on odd x */
 #pragma unroll
                         for (int f = 0; f < 16; ++f) {
                             float c = __uint_as_float(v[j2][f]);
@@ -191,8 +201,31 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
                             if (!own_ok) c = -FLT_MAX;
                             const float o = __shfl_xor_sync(0xffffffffu, c, 1);
                             if (other_ok) c = fmaxf(c, o);
-                            if ((f & 8) == fsel && ya <= 56 && px <= 28)
-                                out[f * kP1Plane + py * kP1W + px] = act_apply(fmaf(c, a.inv_scale, s_bias[f]), a.act, s_slope[f]);
+                            if ((f & 8) == fsel) keep[f & 7] = act_apply(fmaf(c, a.inv_scale, s_bias[f]), a.act, s_slope[f]);
+                        }
+                        if (ya <= 56 && px <= 28) {
+                            if (a.p1_packed) {
+                                /* conv2_tc's A operand: [term][channel block][row (y%8, y/8)][32 px][8 channels] fp16 */
+                                uint32_t hi[4], lo[4];
+                                float vm = 0.f;
+#pragma unroll
+                                for (int q = 0; q < 4; ++q) {
+                                    __half h0, l0, h1, l1;
+                                    vm = fmaxf(vm, fmaxf(fabsf(keep[2 * q]), fabsf(keep[2 * q + 1])));
+                                    split_f16(keep[2 * q] * kP1Scale, h0, l0);
+                                    split_f16(keep[2 * q + 1] * kP1Scale, h1, l1);
+                                    hi[q] = pack2(h0, h1);
+                                    lo[q] = pack2(l0, l1);
+                                }
+                                if (!(vm <= 4000.f)) atomicExch(a.err, 101);
+                                unsigned char* dst = a.p1_packed + patch * (long long)kP1PackedBytes +
+                                                     ((x & 1) * kP1Rows + p1_row_pos(py)) * 512 + px * 16;
+                                *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                                *reinterpret_cast<uint4*>(dst + 2 * kP1PlaneBytes) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                            } else {
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) out[(fsel + q) * kP1Plane + py * kP1W + px] = keep[q];
+                            }
                         }
                     }
                 }
@@ -251,6 +284,153 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
     if (warp == 0) tmem_dealloc<512>(tmem);
 }
 
+/* ------------------------------------------------------------------ conv2 ---- */
+/* conv2 (7 filters 5x5x16) + bias + pool (25 -> 13, ceil) + act on the same scheme: the A operand is the packed
+ * pool1 image (one 80 KB cp.async.bulk per patch, double buffered), a K step is (ky', kx) x 16 channels (the two
+ * 8-channel blocks are the two K chunks, LBO = one plane), N = 8 output rows x 8 filter slots = 64 through a
+ * Toeplitz window over 128-byte weight slabs, one 128-lane tile = base rows 0, 8, 16, 24 x 32 pixels.
+ * 12 x 5 x 3 = 180 MMAs (128x64x16) per patch. */
+constexpr int kZ2Slabs = 127, kZ2Bytes = kZ2Slabs * 128, kZ2Stride = 12 * 128;
+constexpr int kC2OffImg = 0;                                   /* 2 x kP1PackedBytes */
+constexpr int kC2OffZ = 2 * kP1PackedBytes;                    /* hi | lo */
+constexpr int kC2OffMisc = kC2OffZ + 2 * kZ2Bytes;
+constexpr int kC2TcSmem = kC2OffMisc + 256;
+constexpr int kC2TcThreads = 192;
+constexpr int kPool2Ld = 1184;
+
+struct C2Args {
+    const unsigned char* p1_packed;
+    long long n;
+    const uint4* ztoeplitz;    /* hi then lo, kZ2Bytes each */
+    const float* bias;         /* [8] */
+    const float* slope;        /* [8] or null */
+    int act;
+    float inv_scale;
+    float* pool2;              /* [n][1184] */
+    int* err;
+};
+
+__global__ void __launch_bounds__(kC2TcThreads, 1) conv2_tc_kernel(const C2Args a) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    float* s_bias = reinterpret_cast<float*>(smem + kC2OffMisc);
+    float* s_slope = s_bias + 8;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kC2OffMisc + 64);
+    uint64_t* img_full = bars;          /* [2] patch landed (tx bytes) */
+    uint64_t* img_empty = bars + 2;     /* [2] its MMAs have completed */
+    uint64_t* acc_full = bars + 4;      /* [2] */
+    uint64_t* acc_empty = bars + 6;     /* [2] four epilogue warps */
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+    volatile int* s_abort = reinterpret_cast<volatile int*>(tmem_slot + 1);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int i = tid; i < 2 * kZ2Bytes / 16; i += kC2TcThreads) reinterpret_cast<uint4*>(smem + kC2OffZ)[i] = a.ztoeplitz[i];
+    if (tid < 8) {
+        s_bias[tid] = a.bias[tid];
+        s_slope[tid] = a.slope ? a.slope[tid] : 0.f;
+    }
+    if (tid == 0) {
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&img_full[i], 1);
+            mbar_init(&img_empty[i], 1);
+            mbar_init(&acc_full[i], 1);
+            mbar_init(&acc_empty[i], 4);
+        }
+        *s_abort = 0;
+        mbar_fence_init();
+    }
+    if (warp == 0) tmem_alloc<128>(tmem_slot);
+    fence_async_smem();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (long long patch = blockIdx.x; patch < a.n && !*s_abort; patch += gridDim.x, ++it) {
+                const int s = it & 1;
+                if (!mbar_wait(&img_empty[s], ((it >> 1) & 1) ^ 1)) { atomicExch(a.err, 21); *s_abort = 1; break; }
+                mbar_expect_tx(&img_full[s], kP1PackedBytes);
+                bulk_g2s(smem + kC2OffImg + s * kP1PackedBytes, a.p1_packed + patch * (long long)kP1PackedBytes, kP1PackedBytes, &img_full[s]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = instr_desc(128, 64, FMT_F16, FMT_F16);
+            const uint32_t s0 = smem_u32(smem);
+            const uint64_t b_hi = smem_desc(s0 + kC2OffZ, kZ2Stride, 128), b_lo = smem_desc(s0 + kC2OffZ + kZ2Bytes, kZ2Stride, 128);
+            uint32_t it = 0;
+            for (long long patch = blockIdx.x; patch < a.n && !*s_abort; patch += gridDim.x, ++it) {
+                const int s = it & 1;
+                const uint32_t ph = (it >> 1) & 1;
+                if (!mbar_wait(&acc_empty[s], ph ^ 1)) { atomicExch(a.err, 22); *s_abort = 1; break; }
+                if (!mbar_wait(&img_full[s], ph)) { atomicExch(a.err, 23); *s_abort = 1; break; }
+                fence_after_sync();
+                const uint32_t img = s0 + kC2OffImg + s * kP1PackedBytes;
+                const uint64_t a_hi = smem_desc(img, kP1PlaneBytes, 128), a_lo = smem_desc(img + 2 * kP1PlaneBytes, kP1PlaneBytes, 128);
+                const uint32_t d = tmem + s * 64;
+                uint32_t acc = 0;
+#pragma unroll 1
+                for (int ky = 0; ky < 12; ++ky) {
+                    const uint32_t a_row = static_cast<uint32_t>(p1_row_pos(ky)) * (512 >> 4);
+                    const uint32_t b_row = static_cast<uint32_t>(11 - ky) * (128 >> 4);
+#pragma unroll
+                    for (int kx = 0; kx < 5; ++kx) {
+                        const uint32_t ao = a_row + kx, bo = b_row + kx * 2 * (kZ2Stride >> 4);
+                        mma_f16(d, a_hi + ao, b_hi + bo, idesc, acc);
+                        acc = 1;
+                        mma_f16(d, a_hi + ao, b_lo + bo, idesc, 1);
+                        mma_f16(d, a_lo + ao, b_hi + bo, idesc, 1);
+                    }
+                }
+                mma_commit(&img_empty[s]);
+                mma_commit(&acc_full[s]);
+            }
+        }
+    } else {
+        const int quarter = warp & 3;
+        const int m = quarter * 32 + lane;
+        const int g = m >> 5, x = m & 31;            /* base conv row 8g, pixel x */
+        const int px = x >> 1;
+        const bool own_ok = x <= 24, other_ok = (x ^ 1) <= 24;
+        const int fsel = (x & 1) * 4;                 /* even lanes store filters 0..3, odd lanes 4..6 */
+        uint32_t it = 0;
+        for (long long patch = blockIdx.x; patch < a.n && !*s_abort; patch += gridDim.x, ++it) {
+            const int s = it & 1;
+            if (!mbar_wait(&acc_full[s], (it >> 1) & 1)) { atomicExch(a.err, 24); *s_abort = 1; break; }
+            fence_after_sync();
+            const uint32_t tbase = tmem + s * 64 + (static_cast<uint32_t>(quarter * 32) << 16);
+            uint32_t v[2][32];
+            tmem_ld32(tbase, v[0]);
+            tmem_ld32(tbase + 32, v[1]);
+            tmem_ld_wait();
+            fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[s]);
+            float* out = a.pool2 + patch * (long long)kPool2Ld;
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) {
+                const int ya = 8 * g + 2 * jj;         /* conv rows ya, ya + 1 -> pooled row ya / 2 */
+                const int py = ya >> 1;
+                const bool row_b = ya + 1 <= 24;
+#pragma unroll
+                for (int f = 0; f < 7; ++f) {
+                    float c = __uint_as_float(v[jj >> 1][(jj & 1) * 16 + f]);
+                    if (row_b) c = fmaxf(c, __uint_as_float(v[jj >> 1][(jj & 1) * 16 + 8 + f]));
+                    if (!own_ok) c = -FLT_MAX;
+                    const float o = __shfl_xor_sync(0xffffffffu, c, 1);
+                    if (other_ok) c = fmaxf(c, o);
+                    if ((f & 4) == fsel && ya <= 24 && px <= 12)
+                        out[f * 169 + py * 13 + px] = act_apply(fmaf(c, a.inv_scale, s_bias[f]), a.act, s_slope[f]);
+                }
+            }
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<128>(tmem);
+}
+
 }  // namespace
 
 /* Toeplitz copy of the conv1 weights for the tensor kernel (see the header comment): per term (hi, lo) and per kx
@@ -300,12 +480,67 @@ int conv1_tc_prepare(pe_net* net) {
     return PE_OK;
 }
 
+/* Toeplitz copy of the conv2 weights [7][16][5][5]: per term, per (kx, channel block) an array of 128-byte slabs
+ * [8 filter slots][8 channels]; slab 7 + (4 - ky) of array 2 kx + cblk holds weight row ky */
+int conv2_tc_prepare(pe_net* net) {
+    net->c2_tc_ready = false;
+    if (!net->c1_tc_ready) return PE_OK;
+    const std::vector<float>& w = net->blobs[net->blob_w2];
+    float wmax = 0.f;
+    for (float v : w) wmax = std::fmax(wmax, std::fabs(v));
+    if (!(wmax > 0.f) || !std::isfinite(wmax)) return PE_OK;
+    const int log2_sw = 10 - std::ilogb(wmax);
+    const float sw = std::ldexp(1.f, log2_sw);
+    std::vector<uint16_t> z((size_t)2 * kZ2Bytes / 2, 0);
+    for (int kx = 0; kx < 5; ++kx)
+        for (int ky = 0; ky < 5; ++ky)
+            for (int f = 0; f < 7; ++f)
+                for (int c = 0; c < 16; ++c) {
+                    const float v = w[(((size_t)f * 16 + c) * 5 + ky) * 5 + kx] * sw;
+                    const __half h = __float2half_rn(v);
+                    const __half l = __float2half_rn(v - __half2float(h));
+                    uint16_t hb, lb;
+                    memcpy(&hb, &h, 2);
+                    memcpy(&lb, &l, 2);
+                    const size_t slab = (size_t)(kx * 2 + c / 8) * 12 + 7 + (4 - ky);
+                    const size_t at = slab * 64 + (size_t)f * 8 + (c % 8);
+                    z[at] = hb;
+                    z[(size_t)kZ2Bytes / 2 + at] = lb;
+                }
+    PE_CUDA(cudaSetDevice(net->device));
+    if (!net->d_z2) PE_CUDA(cudaMalloc(&net->d_z2, 2 * kZ2Bytes));
+    PE_CUDA(cudaMemcpy(net->d_z2, z.data(), 2 * kZ2Bytes, cudaMemcpyHostToDevice));
+    net->c2_inv_scale = std::ldexp(1.f, -(log2_sw + 4));      /* activations carry kP1Scale = 2^4 */
+    net->c2_tc_ready = true;
+    return PE_OK;
+}
+
+size_t conv_tc_p1_packed_bytes() { return (size_t)kP1PackedBytes; }
+
+int conv2_tc_launch(pe_net* net, long long n) {
+    C2Args a;
+    a.p1_packed = net->p1_packed.as<unsigned char>();
+    a.n = n;
+    a.ztoeplitz = reinterpret_cast<const uint4*>(net->d_z2);
+    a.bias = net->d_b2;
+    a.slope = net->d_s2;
+    a.act = net->act2;
+    a.inv_scale = net->c2_inv_scale;
+    a.pool2 = net->pool2.as<float>();
+    a.err = net->tc_err;
+    const int grid = (int)(n < net->num_sms ? n : net->num_sms);
+    PE_CUDA(cudaFuncSetAttribute(conv2_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kC2TcSmem));
+    conv2_tc_kernel<<<grid, kC2TcThreads, kC2TcSmem, net->stream>>>(a);
+    PE_LAUNCHED();
+    return PE_OK;
+}
+
 bool conv1_tc_usable(const pe_net* net, int patch_c, const void* d_patches) {
     return g_opt_forward_tensor.load() != 0 && net->c1_tc_ready && patch_c == net->def.channels &&
            (reinterpret_cast<uintptr_t>(d_patches) & 15) == 0;
 }
 
-int conv1_tc_launch(pe_net* net, const float* d_patches, int patch_c, long long n) {
+int conv1_tc_launch(pe_net* net, const float* d_patches, int patch_c, long long n, bool packed_out) {
     C1Args a;
     a.patches = d_patches;
     a.n = n;
@@ -315,6 +550,7 @@ int conv1_tc_launch(pe_net* net, const float* d_patches, int patch_c, long long 
     a.act = net->act1;
     a.inv_scale = net->c1_inv_scale;
     a.pool1 = net->pool1.as<float>();
+    a.p1_packed = packed_out ? net->p1_packed.as<unsigned char>() : nullptr;
     a.err = net->tc_err;
     const int grid = (int)(n < net->num_sms ? n : net->num_sms);
     if (patch_c == 7) {

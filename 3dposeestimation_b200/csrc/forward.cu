@@ -369,6 +369,7 @@ int net_upload_weights(pe_net* net) {
         PE_CUDA(cudaMemcpy(net->d_slot, slot.data(), 8 * sizeof(int), cudaMemcpyHostToDevice));
     }
     PE_CHECK(conv1_tc_prepare(net));
+    PE_CHECK(conv2_tc_prepare(net));
     net->weights_dirty = false;
     return PE_OK;
 }
@@ -379,8 +380,10 @@ int net_reserve(pe_net* net, int64_t chunk) {
     PE_CUDA(cudaStreamSynchronize(net->stream));
     /* zero-filled once: the zero borders of pool1 and the pad column of pool2 are never written */
     net->pool1.release();
+    net->p1_packed.release();
     net->pool2.release();
     PE_CHECK(net->pool1.reserve((size_t)chunk * kP1Patch * sizeof(float), true));
+    PE_CHECK(net->p1_packed.reserve((size_t)chunk * conv_tc_p1_packed_bytes(), true));
     PE_CHECK(net->pool2.reserve((size_t)chunk * kPool2Ld * sizeof(float), true));
     int max_w = 4;
     for (auto& fc : net->fcs) max_w = fc.out > max_w ? fc.out : max_w;
@@ -410,8 +413,10 @@ int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c,
         const long long m = (n - first < net->chunk) ? (n - first) : net->chunk;
         const float* src = d_patches + (size_t)first * 4096 * patch_c;
         PE_CHECK(prof_mark(net->profile, &net->prof_events, net->stream));
-        if (conv1_tc_usable(net, patch_c, src)) {
-            PE_CHECK(conv1_tc_launch(net, src, patch_c, m));
+        const bool c1_tc = conv1_tc_usable(net, patch_c, src);
+        const bool c2_tc = c1_tc && net->c2_tc_ready;
+        if (c1_tc) {
+            PE_CHECK(conv1_tc_launch(net, src, patch_c, m, c2_tc));
         } else
         switch (net->cin) {
         case 1: PE_CHECK(launch_conv1<1>(net, src, patch_c, m)); break;
@@ -425,10 +430,14 @@ int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c,
         default: set_error("conv1 input channels %d outside 1..8", net->cin); return PE_ERR_UNSUPPORTED;
         }
         PE_CHECK(prof_mark(net->profile, &net->prof_events, net->stream));
-        const int grid2 = (int)(m < 3LL * net->num_sms ? m : 3LL * net->num_sms);
-        conv2_pool_act_kernel<<<grid2, kC2Threads, smem2, net->stream>>>(
-            net->pool1.as<float>(), net->d_w2, net->d_b2, net->d_s2, net->act2, net->pool2.as<float>(), m);
-        PE_LAUNCHED();
+        if (c2_tc) {
+            PE_CHECK(conv2_tc_launch(net, m));
+        } else {
+            const int grid2 = (int)(m < 3LL * net->num_sms ? m : 3LL * net->num_sms);
+            conv2_pool_act_kernel<<<grid2, kC2Threads, smem2, net->stream>>>(
+                net->pool1.as<float>(), net->d_w2, net->d_b2, net->d_s2, net->act2, net->pool2.as<float>(), m);
+            PE_LAUNCHED();
+        }
         PE_CHECK(prof_mark(net->profile, &net->prof_events, net->stream));
         const float* x = net->pool2.as<float>();
         int ldx = kPool2Ld;
