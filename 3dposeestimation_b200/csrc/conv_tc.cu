@@ -20,9 +20,9 @@
  *   - fp32 accuracy: D = A_hi.B_hi + A_hi.B_lo + A_lo.B_hi in fp32 (TMEM), operands scaled by powers of two.
  *   Per patch: 4 tiles x 15 input rows x 4 pixel pairs x 3 products = 720 MMAs of 128x128x16.
  *
- * Kernel (persistent, one CTA per SM, 416 threads): warp 0 issues the MMAs, warps 1-4 drain the accumulators
- * (pool in registers / by shuffle, bias, activation, store), warps 5-12 stream the next patch in 16-row blocks
- * (fp32 HWC -> fp16 hi/lo) as soon as a block's last reader tile has completed.
+ * Kernel (persistent, one CTA per SM, 544 threads): warp 0 issues the MMAs, warps 1-8 drain the accumulators
+ * (two sets of four, alternate tiles: pool in registers / by shuffle, bias, activation, store), warps 9-16 stream
+ * the next patch in 16-row blocks (fp32 HWC -> fp16 hi/lo) as soon as a block's last reader tile has completed.
  */
 #include <cfloat>
 #include <cmath>
@@ -47,7 +47,7 @@ constexpr int kOffImgHi = 0, kOffImgLo = kImgBytes;
 constexpr int kOffZHi = 2 * kImgBytes, kOffZLo = kOffZHi + kZBytes;
 constexpr int kOffMisc = kOffZLo + kZBytes;        /* bias[16] slope[16] barriers */
 constexpr int kC1TcSmem = kOffMisc + 512;
-constexpr int kC1TcThreads = 416;
+constexpr int kC1TcThreads = 544;
 constexpr int kLog2Sx = 8;                         /* image scale 2^8: |x| <= 255 stays finite in fp16 */
 
 constexpr int kP1H = 30, kP1W = 32, kP1Plane = kP1H * kP1W, kP1Patch = 16 * kP1Plane;   /* as forward.cu */
@@ -160,19 +160,26 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
                 }
             }
         }
-    } else if (warp <= 4) {
-        /* ======================= epilogue ======================= */
-        const int quarter = warp & 3;
+    } else if (warp <= 8) {
+        /* ======================= epilogue: warps 1-4 drain tiles 0 and 2, warps 5-8 tiles 1 and 3 ======================= */
+        const int set = (warp - 1) >> 2;
+        const int quarter = warp & 3;                 /* the TMEM lane quarter this warp may read */
         const int m = quarter * 32 + lane;            /* accumulator lane */
         const int grp = m >> 6, x = m & 63;
         const int px = x >> 1;
+        const bool odd = (x & 1) != 0;                /* even lanes store filters 0..7, odd lanes 8..15 */
         const bool own_ok = x <= 56, other_ok = (x ^ 1) <= 56;
-        const int fsel = (x & 1) * 8;                 /* even lanes store filters 0..7, odd lanes 8..15 */
+        const int fsel = odd ? 8 : 0;
+        float bias_r[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) bias_r[q] = s_bias[fsel + q];
+        float amax = 0.f;
         uint32_t it = 0;
         for (long long patch = blockIdx.x; patch < a.n && !*s_abort; patch += gridDim.x, ++it) {
-            float* out = a.pool1 + patch * (long long)kP1Patch;
+            float* out = a.pool1 + patch * (long long)kP1Patch + fsel * kP1Plane + px;
+            unsigned char* outp = a.p1_packed + patch * (long long)kP1PackedBytes + (odd ? kP1PlaneBytes : 0) + px * 16;
 #pragma unroll 1
-            for (int t = 0; t < 4; ++t) {
+            for (int t = set; t < 4; t += 2) {
                 if (!mbar_wait(&acc_full[t], it & 1)) { atomicExch(a.err, 4); *s_abort = 1; break; }
                 fence_after_sync();
                 const uint32_t tbase = tmem + t * 128 + (static_cast<uint32_t>(quarter * 32) << 16);
@@ -193,47 +200,56 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
                         const int ya = r + 4 * half + 2 * j2;   /* conv rows ya, ya + 1 -> pooled row ya / 2 */
                         const int py = ya >> 1;
                         const bool row_b = ya + 1 <= 56;
-                        float keep[8];                      /* this lane's 8 filters: 0..7 on even x, 8..15 on odd x */
+                        /* pool in y inside the lane, then swap the half of the filters the neighbour keeps */
+                        float mine[8], send[8];
 #pragma unroll
-                        for (int f = 0; f < 16; ++f) {
-                            float c = __uint_as_float(v[j2][f]);
-                            if (row_b) c = fmaxf(c, __uint_as_float(v[j2][16 + f]));
-                            if (!own_ok) c = -FLT_MAX;
-                            const float o = __shfl_xor_sync(0xffffffffu, c, 1);
+                        for (int q = 0; q < 8; ++q) {
+                            float c0 = __uint_as_float(v[j2][q]), c1 = __uint_as_float(v[j2][8 + q]);
+                            if (row_b) {
+                                c0 = fmaxf(c0, __uint_as_float(v[j2][16 + q]));
+                                c1 = fmaxf(c1, __uint_as_float(v[j2][24 + q]));
+                            }
+                            mine[q] = odd ? c1 : c0;
+                            send[q] = odd ? c0 : c1;
+                        }
+                        float keep[8];
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const float o = __shfl_xor_sync(0xffffffffu, send[q], 1);
+                            float c = own_ok ? mine[q] : -FLT_MAX;
                             if (other_ok) c = fmaxf(c, o);
-                            if ((f & 8) == fsel) keep[f & 7] = act_apply(fmaf(c, a.inv_scale, s_bias[f]), a.act, s_slope[f]);
+                            const float sl = a.act == PE_ACT_PRELU ? s_slope[fsel + q] : 0.f;
+                            keep[q] = act_apply(fmaf(c, a.inv_scale, bias_r[q]), a.act, sl);
                         }
                         if (ya <= 56 && px <= 28) {
                             if (a.p1_packed) {
                                 /* conv2_tc's A operand: [term][channel block][row (y%8, y/8)][32 px][8 channels] fp16 */
                                 uint32_t hi[4], lo[4];
-                                float vm = 0.f;
 #pragma unroll
                                 for (int q = 0; q < 4; ++q) {
                                     __half h0, l0, h1, l1;
-                                    vm = fmaxf(vm, fmaxf(fabsf(keep[2 * q]), fabsf(keep[2 * q + 1])));
+                                    amax = fmaxf(amax, fmaxf(fabsf(keep[2 * q]), fabsf(keep[2 * q + 1])));
                                     split_f16(keep[2 * q] * kP1Scale, h0, l0);
                                     split_f16(keep[2 * q + 1] * kP1Scale, h1, l1);
                                     hi[q] = pack2(h0, h1);
                                     lo[q] = pack2(l0, l1);
                                 }
-                                if (!(vm <= 4000.f)) atomicExch(a.err, 101);
-                                unsigned char* dst = a.p1_packed + patch * (long long)kP1PackedBytes +
-                                                     ((x & 1) * kP1Rows + p1_row_pos(py)) * 512 + px * 16;
+                                unsigned char* dst = outp + p1_row_pos(py) * 512;
                                 *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
                                 *reinterpret_cast<uint4*>(dst + 2 * kP1PlaneBytes) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
                             } else {
 #pragma unroll
-                                for (int q = 0; q < 8; ++q) out[(fsel + q) * kP1Plane + py * kP1W + px] = keep[q];
+                                for (int q = 0; q < 8; ++q) out[q * kP1Plane + py * kP1W] = keep[q];
                             }
                         }
                     }
                 }
             }
         }
+        if (!(amax <= 4000.f)) atomicExch(a.err, 101);   /* packed activations must stay inside the fp16 split range */
     } else {
         /* ======================= loaders: fp32 HWC -> fp16 hi / lo HWC8, 16 rows at a time ======================= */
-        const int lt = tid - 160;                      /* 0..255: row (lt >> 4) of the block, pixels 4 * (lt & 15) .. +3 */
+        const int lt = tid - 288;                      /* 0..255: row (lt >> 4) of the block, pixels 4 * (lt & 15) .. +3 */
         const int yr = lt >> 4, x0 = (lt & 15) * 4;
         const float sx = static_cast<float>(1 << kLog2Sx);
         float vmax = 0.f;
@@ -252,7 +268,7 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
                                  : "=f"(q.x), "=f"(q.y), "=f"(q.z), "=f"(q.w) : "l"(s4 + i));
                     val[4 * i + 0] = q.x; val[4 * i + 1] = q.y; val[4 * i + 2] = q.z; val[4 * i + 3] = q.w;
                 }
-                if (!mbar_wait(&img_empty[rb], (it & 1) ^ 1)) { atomicExch(a.err, 5); *s_abort = 1; break; }
+                if (!mbar_wait_relaxed(&img_empty[rb], (it & 1) ^ 1)) { atomicExch(a.err, 5); *s_abort = 1; break; }
                 unsigned char* dst = smem + row_pos(y) * kRowBytes + x0 * 16;
 #pragma unroll
                 for (int p = 0; p < 4; ++p) {

@@ -133,6 +133,17 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, uint32
     return false;
 }
 
+/* the same for a role with slack (e.g. a loader that runs ahead): sleeps between polls so that its spinning
+ * does not take issue slots from the warps on the critical path */
+__device__ __forceinline__ bool mbar_wait_relaxed(uint64_t* bar, uint32_t parity, uint32_t ns = 256, uint32_t max_spins = (1u << 18)) {
+#pragma unroll 1
+    for (uint32_t i = 0; i < max_spins; ++i) {
+        if (mbar_try_wait(bar, parity)) return true;
+        __nanosleep(ns);
+    }
+    return false;
+}
+
 /* ------------------------------------------------------------ bulk copies --- */
 /* 1-D bulk async copy global -> shared (TMA engine, no tensor map); bytes % 16 == 0, both 16-byte aligned */
 __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
