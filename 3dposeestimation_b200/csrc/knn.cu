@@ -23,6 +23,7 @@
 #include <climits>
 
 #include "common.h"
+#include "knn_exact.cuh"
 
 namespace pe {
 
@@ -248,26 +249,6 @@ knn_hamming_scan_kernel(const uint32_t* __restrict__ q, int nq, const uint32_t* 
 }
 
 /* ------------------------------------------------------------------ select ---- */
-/* The reference's distance, restated operation for operation from the CPU oracle
- * (oracle/oracle_match.c l2_sq): 8 partial sums over dims i%8, multiply and add rounded
- * separately, fixed combine tree, then sqrt. */
-__device__ __forceinline__ float exact_l2(const float* __restrict__ a, const float* __restrict__ b, int dp) {
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int i = 0; i < dp; i += 4) {
-        const float4 x = *reinterpret_cast<const float4*>(a + i);
-        const float4 y = __ldg(reinterpret_cast<const float4*>(b + i));
-        const int l = i & 7;
-        const float d0 = __fsub_rn(x.x, y.x), d1 = __fsub_rn(x.y, y.y), d2 = __fsub_rn(x.z, y.z), d3 = __fsub_rn(x.w, y.w);
-        acc[l + 0] = __fadd_rn(acc[l + 0], __fmul_rn(d0, d0));
-        acc[l + 1] = __fadd_rn(acc[l + 1], __fmul_rn(d1, d1));
-        acc[l + 2] = __fadd_rn(acc[l + 2], __fmul_rn(d2, d2));
-        acc[l + 3] = __fadd_rn(acc[l + 3], __fmul_rn(d3, d3));
-    }
-    const float s = __fadd_rn(__fadd_rn(__fadd_rn(acc[0], acc[4]), __fadd_rn(acc[2], acc[6])),
-                              __fadd_rn(__fadd_rn(acc[1], acc[5]), __fadd_rn(acc[3], acc[7])));
-    return __fsqrt_rn(s);
-}
-
 template <typename T>
 __device__ __forceinline__ T big();
 template <>
@@ -458,13 +439,18 @@ int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* 
         PE_CUDA(cudaMemsetAsync(ci, 0xff, n_cand * sizeof(int), db->stream)); /* all -1: empty shard */
     }
     PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
-    const size_t smem = (size_t)(2 * g.n_chunks * g.kc + dp) * 4;
-    PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
-    PE_CUDA(cudaFuncSetAttribute(knn_select_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    knn_select_kernel<float, true><<<(unsigned)nq, 32, smem, db->stream>>>(
-        cd, ci, (long long)g.n_chunks * g.kc, g.kc, g.n_chunks, g.kc, dq, db->d_desc, dp, db->row_offset, k,
-        d_out_idx, d_out_dist);
-    PE_LAUNCHED();
+    if (tensor) {
+        /* the tensor scan emits 32-template blocks: exact pass over the best blocks */
+        PE_CHECK(knn_tc_select(db, cd, ci, g.n_chunks, g.kc, dq, nq, k, d_out_idx, d_out_dist));
+    } else {
+        const size_t smem = (size_t)(2 * g.n_chunks * g.kc + dp) * 4;
+        PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
+        PE_CUDA(cudaFuncSetAttribute(knn_select_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        knn_select_kernel<float, true><<<(unsigned)nq, 32, smem, db->stream>>>(
+            cd, ci, (long long)g.n_chunks * g.kc, g.kc, g.n_chunks, g.kc, dq, db->d_desc, dp, db->row_offset, k,
+            d_out_idx, d_out_dist);
+        PE_LAUNCHED();
+    }
     PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
     return PE_OK;
 }

@@ -1,0 +1,26 @@
+/* knn_exact.cuh - the matcher's exact fp32 distance, shared by the SIMT and the tensor candidate refinement. */
+#pragma once
+
+namespace pe {
+
+/* The reference's distance, restated operation for operation from the CPU oracle
+ * (oracle/oracle_match.c l2_sq): 8 partial sums over dims i%8, multiply and add rounded
+ * separately, fixed combine tree, then sqrt. */
+__device__ __forceinline__ float exact_l2(const float* __restrict__ a, const float* __restrict__ b, int dp) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int i = 0; i < dp; i += 4) {
+        const float4 x = *reinterpret_cast<const float4*>(a + i);
+        const float4 y = __ldg(reinterpret_cast<const float4*>(b + i));
+        const int l = i & 7;
+        const float d0 = __fsub_rn(x.x, y.x), d1 = __fsub_rn(x.y, y.y), d2 = __fsub_rn(x.z, y.z), d3 = __fsub_rn(x.w, y.w);
+        acc[l + 0] = __fadd_rn(acc[l + 0], __fmul_rn(d0, d0));
+        acc[l + 1] = __fadd_rn(acc[l + 1], __fmul_rn(d1, d1));
+        acc[l + 2] = __fadd_rn(acc[l + 2], __fmul_rn(d2, d2));
+        acc[l + 3] = __fadd_rn(acc[l + 3], __fmul_rn(d3, d3));
+    }
+    const float s = __fadd_rn(__fadd_rn(__fadd_rn(acc[0], acc[4]), __fadd_rn(acc[2], acc[6])),
+                              __fadd_rn(__fadd_rn(acc[1], acc[5]), __fadd_rn(acc[3], acc[7])));
+    return __fsqrt_rn(s);
+}
+
+}  // namespace pe

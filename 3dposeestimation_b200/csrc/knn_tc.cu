@@ -4,8 +4,9 @@
  * (reference src/networkevaluator.cpp:197,267; src/networksolver.cpp:472).
  *
  * The scan ranks templates by  R(q,t) = |t|^2 - 2 q.t  (same order as sqrt(sum (q-t)^2) for a fixed q)
- * and emits, per (query, DB chunk), the k+2 best candidates; knn_select_kernel (knn.cu) then recomputes
- * the reference's exact fp32 distance for every candidate and keeps the k smallest by (distance, index).
+ * and emits, per (query, DB chunk), the k+2 best 32-template blocks (keyed by their smallest R);
+ * knn_tc_select_kernel then recomputes the reference's exact fp32 distance for every template of the best
+ * blocks and keeps the k smallest by (distance, index).  The scan therefore never has to locate a column.
  *
  * Arithmetic: fp32 operands are split into two fp16 terms (x ~= hi + lo, 22 significant bits) after a
  * power-of-two scaling that keeps them in fp16's normal range; R is accumulated in fp32 in TMEM by
@@ -13,14 +14,15 @@
  * with A = -2 s_q q (queries), B = s_t t (templates) and the last product adding s_q s_t |t|^2 from a
  * three-term fp16 split of the squared norm.
  *
- * Kernel (persistent, one CTA per SM, 352 threads):
+ * Kernel (persistent, one CTA per SM, 608 threads):
  *   warp 0      one lane streams 10 KB template tiles (128 rows: hi | lo | norm) with cp.async.bulk into an
  *               8-stage ring (mbarrier complete_tx)
  *   warps 1-2   one lane each issues the MMAs of one query tile (two tiles = 256 queries share every template
  *               tile), four 128-column accumulators in TMEM (double buffered), tcgen05.commit -> mbarriers
- *   warps 3-10  epilogue (four warps per query tile, one accumulator lane = one query per thread):
- *               tcgen05.ld 32 columns at a time (double buffered), running minimum, and only when a value beats
- *               the query's admission threshold the sorted (k+2)-list in registers is updated.  The
+ *   warps 3-18  epilogue (per query tile two sets of four warps that drain alternate tiles; one accumulator lane =
+ *               one query per thread):
+ *               tcgen05.ld of the accumulator row, minimum of each 32-column block, and only when a block minimum
+ *               beats the query's admission threshold is the sorted (k+2)-list in shared memory updated.  The
  *               threshold is shared between the CTAs that scan different chunks for the same query
  *               through one float per query in global memory (atomicMin), so updates stay rare.
  */
@@ -31,6 +33,7 @@
 #include <cstring>
 
 #include "common.h"
+#include "knn_exact.cuh"
 #include "umma.cuh"
 
 namespace pe {
@@ -41,16 +44,18 @@ namespace {
 
 constexpr int kTcRows = 128;                 /* templates per tile / queries per query tile */
 constexpr int kTcTileBytes = 10240;          /* hi 4096 | lo 4096 | norm 2048 */
+constexpr int kTcBlock = 32;                 /* templates per candidate block */
+constexpr int kTcSelBlocks = 8;              /* candidate blocks re-ranked exactly per query */
 constexpr int kTcStages = 8;
-constexpr int kTcThreads = 352;        /* producer warp, 2 MMA warps, 2 x 4 epilogue warps */
+constexpr int kTcThreads = 608;               /* producer warp, 2 MMA warps, 2 x 2 x 4 epilogue warps */
+constexpr int kTcListCols = 512;              /* one list column per epilogue thread */
 constexpr int kAOpBytes = 10240;             /* per query tile: hi 4096 | lo 4096 | a_n 2048 */
 constexpr int kSmemA = 0;                                  /* 2 query tiles */
 constexpr int kSmemZero = kSmemA + 2 * kAOpBytes;          /* 2048 zero bytes: second K chunk of A_n */
 constexpr int kSmemB = kSmemZero + 2048;
-constexpr int kSmemScratch = kSmemB + kTcStages * kTcTileBytes;   /* [32][256] floats: rare-path staging  */
-constexpr int kSmemList = kSmemScratch + 32 * 256 * 4;            /* [7][256] floats + [7][256] ints     */
-constexpr int kSmemBar = kSmemList + 2 * 7 * 256 * 4;
-constexpr int kSmemTotal = kSmemBar + 256;
+constexpr int kSmemList = kSmemB + kTcStages * kTcTileBytes;      /* [7][512] floats + [7][512] ints     */
+constexpr int kSmemBar = kSmemList + 2 * 7 * kTcListCols * 4;
+constexpr int kSmemTotal = kSmemBar + 512;
 
 /* monotone float <-> int map so that atomicMin on ints orders floats (negative values included) */
 __device__ __forceinline__ int f2ord(float f) {
@@ -185,46 +190,59 @@ struct TcArgs {
     int* err;
     unsigned long long* dbg;   /* PE_TC_DEBUG: per-role cycle counters (null in production) */
 };
-#define TC_DBG_T0(var) long long var = 0; if (a.dbg) var = clock64()
-#define TC_DBG_ADD(slot, var) do { if (a.dbg) { const long long n_ = clock64(); dbg_acc[slot] += n_ - var; var = n_; } } while (0)
+#define TC_DBG_T0(var) long long var = 0; if (DBG) var = clock64()
+#define TC_DBG_ADD(slot, var) do { if (DBG) { const long long n_ = clock64(); dbg_acc[slot] += n_ - var; var = n_; } } while (0)
 
-/* sorted insert into the calling thread's k+2 list (entries strided by 256 threads in shared memory); strict '>'
- * keeps the earlier (lower-index) entry first among equals.  Returns the new k+2-th best.  Deliberately not
- * inlined: it runs in about one warp-tile in six and must not bloat the hot loop's instruction footprint. */
+/* sorted insert into the calling thread's k+2 list (entries strided by kTcListCols threads in shared memory);
+ * strict '>' keeps the earlier (lower-index) entry first among equals.  Returns the new k+2-th best.  Deliberately
+ * not inlined: it runs in about one warp-tile in six and must not bloat the hot loop's instruction footprint. */
 __device__ __noinline__ float tc_list_insert(float* ld, int* li, int kc, float v, int idx) {
     int p = kc - 1;
-    while (p > 0 && ld[(p - 1) * 256] > v) {
-        ld[p * 256] = ld[(p - 1) * 256];
-        li[p * 256] = li[(p - 1) * 256];
+    while (p > 0 && ld[(p - 1) * kTcListCols] > v) {
+        ld[p * kTcListCols] = ld[(p - 1) * kTcListCols];
+        li[p * kTcListCols] = li[(p - 1) * kTcListCols];
         --p;
     }
-    ld[p * 256] = v;
-    li[p * 256] = idx;
-    return ld[(kc - 1) * 256];
+    ld[p * kTcListCols] = v;
+    li[p * kTcListCols] = idx;
+    return ld[(kc - 1) * kTcListCols];
 }
 
-template <int KC>
+__device__ __forceinline__ float fmin3(float x, float y, float z) { return fminf(fminf(x, y), z); }   /* one FMNMX3 */
+
+/* minimum of 32 accumulator columns in 16 three-input instructions */
+__device__ __forceinline__ float tc_min32(const uint32_t (&v)[32]) {
+    float t[10];
+#pragma unroll
+    for (int i = 0; i < 10; ++i) t[i] = fmin3(__uint_as_float(v[3 * i]), __uint_as_float(v[3 * i + 1]), __uint_as_float(v[3 * i + 2]));
+    const float u0 = fmin3(t[0], t[1], t[2]), u1 = fmin3(t[3], t[4], t[5]), u2 = fmin3(t[6], t[7], t[8]);
+    const float u3 = fmin3(t[9], __uint_as_float(v[30]), __uint_as_float(v[31]));
+    return fminf(fmin3(u0, u1, u2), u3);
+}
+
+template <int KC, bool DBG>
 __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemBar);
     uint64_t* full = bars;                     /* [kTcStages] tile landed */
-    uint64_t* empty = bars + kTcStages;        /* [kTcStages] tile consumed by both query tiles' MMAs */
+    uint64_t* empty = bars + kTcStages;        /* [kTcStages] tile consumed by the MMAs of both query tiles */
     uint64_t* tfull = bars + 2 * kTcStages;    /* [4] accumulator ready */
     uint64_t* tempty = tfull + 4;              /* [4] accumulator drained */
     uint64_t* a_ready = tempty + 4;            /* query operands of the next item written */
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_ready + 1);
+    uint64_t* item_done = a_ready + 1;         /* every MMA of the item has completed (one commit per issuer) */
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(item_done + 1);
     volatile int* s_abort = reinterpret_cast<volatile int*>(tmem_slot + 1);
-    float* s_red = reinterpret_cast<float*>(tmem_slot + 2);   /* [8] query abs-max per epilogue warp */
-    float* s_scratch = reinterpret_cast<float*>(smem + kSmemScratch);   /* [32][256] rare-path staging */
-    float* s_ld = reinterpret_cast<float*>(smem + kSmemList);           /* [KC][256] candidate values */
-    int* s_li = reinterpret_cast<int*>(s_ld + KC * 256);                /* [KC][256] candidate rows   */
+    float* s_red = reinterpret_cast<float*>(tmem_slot + 2);   /* [8] query abs-max per operand warp */
+    float* s_ld = reinterpret_cast<float*>(smem + kSmemList);           /* [KC][512] candidate keys   */
+    int* s_li = reinterpret_cast<int*>(s_ld + KC * kTcListCols);        /* [KC][512] candidate blocks */
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int i = tid; i < 2048 / 16; i += kTcThreads) reinterpret_cast<uint4*>(smem + kSmemZero)[i] = make_uint4(0, 0, 0, 0);
     if (tid == 0) {
-        for (int s = 0; s < kTcStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 2); }
+        for (int s = 0; s < kTcStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         for (int b = 0; b < 4; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4); }
         mbar_init(a_ready, 256);
+        mbar_init(item_done, 2);
         *s_abort = 0;
         mbar_fence_init();
     }
@@ -253,73 +271,101 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
             }
         }
     } else if (warp <= 2) {
-        /* ================= MMA issuers: warp 1 feeds query tile 0, warp 2 query tile 1 ================= */
-        if (lane == 0) {
-            const int qt = warp - 1;
+        /* ================= MMA issuers: warp 1 issues the even tiles of the CTA's tile sequence, warp 2 the odd ones,
+         * each for both query tiles (8 MMAs per template tile), so the bookkeeping of one issuer runs under the MMAs
+         * of the other.  The whole warp runs the loop (warp-uniform operands), one elected lane issues. ============ */
+        {
+            const int set = warp - 1;
             const uint32_t idesc = instr_desc(128, 128, FMT_F16, FMT_F16);
             const uint32_t sB = smem_u32(smem + kSmemB), sZ = smem_u32(smem + kSmemZero);
-            const uint32_t a_base = smem_u32(smem + kSmemA) + qt * kAOpBytes;
-            const uint64_t a_hi = smem_desc(a_base, 2048, 128), a_lo = smem_desc(a_base + 4096, 2048, 128);
-            const uint64_t a_n = smem_desc(a_base + 8192, sZ - (a_base + 8192), 128);
+            const uint32_t a0 = smem_u32(smem + kSmemA), a1 = a0 + kAOpBytes;
+            const uint64_t a0_hi = smem_desc(a0, 2048, 128), a0_lo = smem_desc(a0 + 4096, 2048, 128);
+            const uint64_t a0_n = smem_desc(a0 + 8192, sZ - (a0 + 8192), 128);
+            const uint64_t a1_hi = smem_desc(a1, 2048, 128), a1_lo = smem_desc(a1 + 4096, 2048, 128);
+            const uint64_t a1_n = smem_desc(a1 + 8192, sZ - (a1 + 8192), 128);
             const uint64_t b_hi0 = smem_desc(sB, 2048, 128), b_lo0 = smem_desc(sB + 4096, 2048, 128);
             const uint64_t b_n0 = smem_desc(sB + 8192, 0, 128);   /* chunk 1 aliases chunk 0: A_n's chunk 1 is zero */
+            const uint32_t d0 = tmem + (set * 2) * 128, d1 = d0 + 128;
+            uint64_t* const tf0 = &tfull[set * 2], * const te0 = &tempty[set * 2];
             uint32_t g = 0, it = 0;
             long long dbg_acc[4] = {0, 0, 0, 0};
             TC_DBG_T0(tm);
-            for (int item = blockIdx.x; item < n_items && !*s_abort; item += gridDim.x, ++it) {
+            bool ok = true;
+            for (int item = blockIdx.x; item < n_items && ok && !*s_abort; item += gridDim.x, ++it) {
                 const int chunk = item / a.n_qpairs;
                 const int t0 = chunk * a.tiles_per_chunk;
                 const int t1 = min(t0 + a.tiles_per_chunk, a.tiles_total);
-                if (!mbar_wait(a_ready, it & 1)) { atomicExch(a.err, 2); *s_abort = 1; break; }
+                if (!mbar_wait(a_ready, it & 1)) { if (lane == 0) atomicExch(a.err, 2); ok = false; break; }
                 fence_after_sync();
-                for (int t = t0; t < t1; ++t, ++g) {
-                    const int s = g % kTcStages;
-                    const int b = (g & 1) * 2 + qt;
+                const uint32_t g_end = g + (uint32_t)(t1 - t0);
+#pragma unroll 1
+                for (uint32_t gi = g + ((g ^ (uint32_t)set) & 1u); gi < g_end; gi += 2) {
+                    const uint32_t s = gi & (kTcStages - 1);
+                    const uint32_t ph = (gi >> 1) & 1u;
                     TC_DBG_ADD(2, tm);
-                    if (!mbar_wait(&tempty[b], ((g >> 1) & 1) ^ 1)) { atomicExch(a.err, 4); *s_abort = 1; break; }
+                    if (!mbar_wait(te0, ph ^ 1u) || !mbar_wait(te0 + 1, ph ^ 1u)) { if (lane == 0) atomicExch(a.err, 4); ok = false; break; }
                     TC_DBG_ADD(1, tm);
-                    if (!mbar_wait(&full[s], (g / kTcStages) & 1)) { atomicExch(a.err, 3); *s_abort = 1; break; }
+                    if (!mbar_wait(&full[s], (gi / kTcStages) & 1u)) { if (lane == 0) atomicExch(a.err, 3); ok = false; break; }
                     fence_after_sync();
                     TC_DBG_ADD(0, tm);
-                    const uint32_t off = static_cast<uint32_t>(s) * (kTcTileBytes >> 4);
-                    const uint32_t d = tmem + b * 128;
-                    mma_f16(d, a_hi, b_hi0 + off, idesc, 0);
-                    mma_f16(d, a_hi, b_lo0 + off, idesc, 1);
-                    mma_f16(d, a_lo, b_hi0 + off, idesc, 1);
-                    mma_f16(d, a_n, b_n0 + off, idesc, 1);
-                    mma_commit(&tfull[b]);
-                    mma_commit(&empty[s]);
+                    const uint32_t off = s * (kTcTileBytes >> 4);
+                    if (elect_one()) {
+                        mma_f16(d0, a0_hi, b_hi0 + off, idesc, 0);
+                        mma_f16(d0, a0_hi, b_lo0 + off, idesc, 1);
+                        mma_f16(d0, a0_lo, b_hi0 + off, idesc, 1);
+                        mma_f16(d0, a0_n, b_n0 + off, idesc, 1);
+                        mma_commit(tf0);
+                        mma_f16(d1, a1_hi, b_hi0 + off, idesc, 0);
+                        mma_f16(d1, a1_hi, b_lo0 + off, idesc, 1);
+                        mma_f16(d1, a1_lo, b_hi0 + off, idesc, 1);
+                        mma_f16(d1, a1_n, b_n0 + off, idesc, 1);
+                        mma_commit(tf0 + 1);
+                        mma_commit(&empty[s]);
+                    }
+                    __syncwarp();
                 }
+                if (!ok) break;
+                /* the operand warps may rewrite the query tiles once both issuers' MMAs of this item are done */
+                if (elect_one()) mma_commit(item_done);
+                __syncwarp();
+                g = g_end;
             }
-            if (a.dbg && qt == 0) {
+            if (!ok) *s_abort = 1;
+            if (DBG && lane == 0) {
                 TC_DBG_ADD(2, tm);
                 atomicAdd(a.dbg + 5, (unsigned long long)dbg_acc[0]);
                 atomicAdd(a.dbg + 6, (unsigned long long)dbg_acc[1]);
                 atomicAdd(a.dbg + 7, (unsigned long long)dbg_acc[2]);
-                atomicAdd(a.dbg + 8, (unsigned long long)g);
+                if (set == 0) atomicAdd(a.dbg + 8, (unsigned long long)g);
             }
         }
     } else {
-        /* ================= epilogue: warps 3..6 drain query tile 0, warps 7..10 query tile 1 ================= */
+        /* ================= epilogue: 16 warps = 2 query tiles x 2 tile sets x 4 lane quarters.  Set 0 drains the
+         * even tiles of the CTA's tile sequence, set 1 the odd ones (each into its own list), so a warp has two tile
+         * periods for one accumulator and four warps per scheduler hide each other's TMEM and barrier latency. ===== */
+        const int ew = warp - 3;
         const int quarter = warp & 3;                 /* TMEM lanes this warp may read: 32 * (warp % 4) */
-        const int qt = (warp - 3) >> 2;               /* query tile of the pair */
+        const int qt = (ew >> 2) & 1;                 /* query tile of the pair */
+        const int set = ew >> 3;                      /* parity of the tiles this warp drains */
         const int row = quarter * 32 + lane;          /* query row inside the query tile */
-        const int et = qt * 128 + row;                /* 0..255: this thread's column in the shared-memory lists */
+        const int et = ew * 32 + lane;                /* 0..511: this thread's column in the shared-memory lists */
         float* my_ld = s_ld + et;
         int* my_li = s_li + et;
-        float* my_scratch = s_scratch + et;
-        uint32_t g = 0;
+        uint64_t* const my_tfull = &tfull[set * 2 + qt];
+        uint64_t* const my_tempty = &tempty[set * 2 + qt];
+        const uint32_t tbase = tmem + (set * 2 + qt) * 128 + (static_cast<uint32_t>(quarter * 32) << 16);
+        uint32_t g = 0, n_item = 0;
         long long dbg_acc[5] = {0, 0, 0, 0, 0};
         TC_DBG_T0(te);
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             const int chunk = item / a.n_qpairs, qpair = item - chunk * a.n_qpairs;
             const int t0 = chunk * a.tiles_per_chunk;
             const int t1 = min(t0 + a.tiles_per_chunk, a.tiles_total);
-            /* ---- query operands: centre, scale, split, store in the K-major core-matrix layout */
             const int qidx = (qpair * 2 + qt) * kTcRows + row;
             const bool q_ok = qidx < a.nq;
-            float qv[16];
-            {
+            if (set == 0) {
+                /* ---- query operands (256 threads): centre, scale, split, store in the K-major core-matrix layout */
+                float qv[16];
                 float m = 0.f;
 #pragma unroll
                 for (int d4 = 0; d4 < 4; ++d4) {
@@ -334,10 +380,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
                 if (lane == 0) s_red[qt * 4 + quarter] = m;
-            }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            {
-                const float m = fmaxf(fmaxf(s_red[qt * 4 + 0], s_red[qt * 4 + 1]), fmaxf(s_red[qt * 4 + 2], s_red[qt * 4 + 3]));
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                m = fmaxf(fmaxf(s_red[qt * 4 + 0], s_red[qt * 4 + 1]), fmaxf(s_red[qt * 4 + 2], s_red[qt * 4 + 3]));
                 /* s_q = 2^eq with 2 * max|q| * s_q in [2^10, 2^11); a_n = s_q * s_t / s_n must stay a finite fp16 power of two */
                 int eq = (m > 0.f && isfinite(m)) ? 9 - ilogbf(m) : 0;
                 int ea = eq + a.log2_st - a.log2_sn;
@@ -359,102 +403,114 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                 op[256 + row] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
                 op[384 + row] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
                 op[512 + row] = make_uint4(pack_h2(an, an), pack_h2(an, __ushort_as_half(0)), 0u, 0u);
-#pragma unroll
-                for (int p = 0; p < KC; ++p) { my_ld[p * 256] = INFINITY; my_li[p * 256] = -1; }
+                fence_async_smem();
+                mbar_arrive(a_ready);
+                asm volatile("bar.sync 1, 256;" ::: "memory");   /* s_red may be rewritten by the next item */
             }
-            fence_async_smem();
-            mbar_arrive(a_ready);
-            asm volatile("bar.sync 1, 256;" ::: "memory");   /* s_red may be rewritten by the next item */
+            /* the k+2 best blocks of this thread's tiles: in registers for k = 1, in shared memory otherwise */
+            float rk[KC <= 3 ? KC : 1];
+            int ri[KC <= 3 ? KC : 1];
+            if (KC <= 3) {
+#pragma unroll
+                for (int p = 0; p < (KC <= 3 ? KC : 1); ++p) { rk[p] = INFINITY; ri[p] = -1; }
+            } else {
+#pragma unroll
+                for (int p = 0; p < KC; ++p) { my_ld[p * kTcListCols] = INFINITY; my_li[p * kTcListCols] = -1; }
+            }
 
-            float thr = INFINITY;                              /* k+2-th best of this chunk so far */
-            /* the CTAs that scan other chunks for this query publish their k+2-th best in tau: nothing above it
-             * can reach the final top-k.  Admission is v <= tau, i.e. v < nextup(tau).  tau is re-read every fourth
-             * tile and used from the following tile on (a stale tau is only more permissive). */
-            int tau_raw = q_ok ? __ldcg(a.tau + qidx) : 0x7F7F7F7F;
+            float thr = INFINITY;                              /* k+2-th best of this list so far */
+            /* the warps that scan other tiles for this query publish their k+2-th best in tau: nothing above it can
+             * reach the final top-k.  Admission is v <= tau, i.e. v < nextup(tau).  tau is re-read every other
+             * drained tile and used from the following one on (a stale tau is only more permissive). */
+            int* const tau_p = a.tau + (q_ok ? qidx : 0);
+            int tau_raw = q_ok ? __ldcg(tau_p) : 0x7F7F7F7F;
             float tau_up = INFINITY;
-            for (int t = t0; t < t1; ++t, ++g) {
-                const int col0 = t * kTcRows;                 /* local template index of column 0 */
-                const int b = (g & 1) * 2 + qt;
-                if ((g & 3) == 1) {
+            const uint32_t g_end = g + (uint32_t)(t1 - t0);
+            const uint32_t g_first = g + ((g ^ (uint32_t)set) & 1u);               /* first tile of this set */
+            const int n_mine = g_first < g_end ? (int)((g_end - g_first + 1) >> 1) : 0;
+            int blk0 = (t0 + (int)(g_first - g)) * (kTcRows / kTcBlock);            /* local block id of columns 0..31 */
+            uint32_t ph = (g_first >> 1) & 1u;
+#pragma unroll 1
+            for (int i = 0; i < n_mine; ++i, blk0 += 2 * (kTcRows / kTcBlock), ph ^= 1u) {
+                if (i & 1) {
                     const float tg = ord2f(tau_raw);
                     tau_up = __int_as_float(tg >= 0.f ? __float_as_int(tg) + 1 : __float_as_int(tg) - 1);
                     if (tg == 0.f) tau_up = FLT_MIN;
-                } else if ((g & 3) == 0 && q_ok) {
-                    tau_raw = __ldcg(a.tau + qidx);
+                } else if (q_ok) {
+                    tau_raw = __ldcg(tau_p);
                 }
                 float th = fminf(thr, tau_up);
                 TC_DBG_ADD(3, te);
-                if (!mbar_wait(&tfull[b], (g >> 1) & 1)) { atomicExch(a.err, 5); *s_abort = 1; break; }
+                if (!mbar_wait(my_tfull, ph)) { atomicExch(a.err, 5); *s_abort = 1; break; }
                 fence_after_sync();
                 TC_DBG_ADD(0, te);
-                const uint32_t tbase = tmem + b * 128 + (static_cast<uint32_t>(quarter * 32) << 16);
-                uint32_t v0[32], v1[32], v2[32], v3[32];
-                auto min32 = [](const uint32_t (&v)[32]) {
-                    float m8[8];
-#pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        m8[j] = fminf(fminf(__uint_as_float(v[j]), __uint_as_float(v[j + 8])), fminf(__uint_as_float(v[j + 16]), __uint_as_float(v[j + 24])));
-                    return fminf(fminf(fminf(m8[0], m8[1]), fminf(m8[2], m8[3])), fminf(fminf(m8[4], m8[5]), fminf(m8[6], m8[7])));
-                };
-                /* hot path: the whole 128-column accumulator row in one round trip (four loads in flight) */
+                uint32_t v0[32], v1[32];
                 tmem_ld32(tbase, v0);
                 tmem_ld32(tbase + 32, v1);
-                tmem_ld32(tbase + 64, v2);
-                tmem_ld32(tbase + 96, v3);
                 tmem_ld_wait();
-                const float m0 = min32(v0), m1 = min32(v1), m2 = min32(v2), m3 = min32(v3);
-                const unsigned hit = (m0 < th ? 1u : 0u) | (m1 < th ? 2u : 0u) | (m2 < th ? 4u : 0u) | (m3 < th ? 8u : 0u);
-                const unsigned any = __reduce_or_sync(0xffffffffu, hit);
+                const float m0 = tc_min32(v0), m1 = tc_min32(v1);
+                tmem_ld32(tbase + 64, v0);
+                tmem_ld32(tbase + 96, v1);
+                tmem_ld_wait();
+                fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(my_tempty);     /* the accumulator goes back before anything else happens */
+                const float m2 = tc_min32(v0), m3 = tc_min32(v1);
+                const bool hit = fminf(fminf(m0, m1), fminf(m2, m3)) < th;
                 TC_DBG_ADD(1, te);
-                if (any) {
-                    /* rare path, kept small (instruction cache): re-read a flagged 32-column block, park it in shared
-                     * memory, build the mask of admissible columns and insert those (usually one) */
-                    dbg_acc[4] += 1;
-                    bool changed = false;
-#pragma unroll 1
-                    for (int blk = 0; blk < 4; ++blk) {
-                        if (!((any >> blk) & 1u)) continue;
-                        uint32_t w[32];
-                        tmem_ld32(tbase + blk * 32, w);
-                        tmem_ld_wait();
-                        unsigned mask = 0;
+                if (__any_sync(0xffffffffu, hit)) {
+                    /* rare path: a 32-template block enters the list with its minimum as the key; which template of
+                     * the block it was is found by the exact pass over the block (knn_tc_select_kernel) */
+                    if (DBG) dbg_acc[4] += 1;
+                    if (hit) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            my_scratch[j * 256] = __uint_as_float(w[j]);
-                            mask |= (__uint_as_float(w[j]) < th ? 1u : 0u) << j;
-                        }
-                        while (mask) {
-                            const int j = __ffs(mask) - 1;
-                            mask &= mask - 1;
-                            const float x = my_scratch[j * 256];
-                            const int li = col0 + blk * 32 + j;
-                            if (x < th && li < a.t_local) {
-                                thr = tc_list_insert(my_ld, my_li, KC, x, li);
+                        for (int j = 0; j < 4; ++j) {
+                            const float mj = j == 0 ? m0 : (j == 1 ? m1 : (j == 2 ? m2 : m3));
+                            if (mj < th) {
+                                if (KC <= 3) {
+                                    /* sorted insert, strict '>' keeps the earlier block first among equals */
+#pragma unroll
+                                    for (int p = (KC <= 3 ? KC : 1) - 1; p > 0; --p) {
+                                        const bool shift = rk[p - 1] > mj;
+                                        const bool here = !shift && rk[p] > mj;
+                                        ri[p] = shift ? ri[p - 1] : (here ? blk0 + j : ri[p]);
+                                        rk[p] = shift ? rk[p - 1] : (here ? mj : rk[p]);
+                                    }
+                                    if (rk[0] > mj) { rk[0] = mj; ri[0] = blk0 + j; }
+                                    thr = rk[(KC <= 3 ? KC : 1) - 1];
+                                } else {
+                                    thr = tc_list_insert(my_ld, my_li, KC, mj, blk0 + j);
+                                }
                                 th = fminf(thr, tau_up);
-                                changed = true;
                             }
                         }
+                        if (thr < INFINITY && q_ok) atomicMin(tau_p, f2ord(thr));
                     }
-                    if (changed && thr < INFINITY && q_ok) atomicMin(a.tau + qidx, f2ord(thr));
                     __syncwarp();
                     TC_DBG_ADD(2, te);
                 }
-                fence_before_sync();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&tempty[b]);
             }
-            /* ---- this item's candidates: [query][chunk][KC], global template indices */
+            /* the item's MMAs must have completed before the operand warps (set 0) overwrite the query tiles.  A parity
+             * wait on the other set's accumulator barrier would not do: that issuer may be more than one phase behind. */
+            if (set == 0 && !mbar_wait(item_done, n_item & 1u)) { atomicExch(a.err, 6); *s_abort = 1; }
+            ++n_item;
+            g = g_end;
+            /* ---- this item's candidates: [query][chunk][set][KC] (key, local 32-template block id or -1) */
             if (q_ok) {
-                const size_t o = ((size_t)qidx * a.n_chunks + chunk) * KC;
+                const size_t o = (((size_t)qidx * a.n_chunks + chunk) * 2 + set) * KC;
+                if (KC <= 3) {
 #pragma unroll
-                for (int p = 0; p < KC; ++p) {
-                    const int li = my_li[p * 256];
-                    a.cand_d[o + p] = my_ld[p * 256];
-                    a.cand_i[o + p] = li >= 0 ? (int)(li + a.row_offset) : -1;
+                    for (int p = 0; p < (KC <= 3 ? KC : 1); ++p) { a.cand_d[o + p] = rk[p]; a.cand_i[o + p] = ri[p]; }
+                } else {
+#pragma unroll
+                    for (int p = 0; p < KC; ++p) {
+                        a.cand_d[o + p] = my_ld[p * kTcListCols];
+                        a.cand_i[o + p] = my_li[p * kTcListCols];
+                    }
                 }
             }
         }
-        if (a.dbg && lane == 0) {
+        if (DBG && lane == 0) {
             TC_DBG_ADD(3, te);
             for (int j = 0; j < 5; ++j) atomicAdd(a.dbg + j, (unsigned long long)dbg_acc[j]);
             atomicAdd(a.dbg + 9, (unsigned long long)g);
@@ -463,6 +519,85 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
     fence_before_sync();
     __syncthreads();
     if (warp == 0) tmem_dealloc<512>(tmem);
+}
+
+/* ------------------------------------------------------------------ select ---- */
+/* One warp per query.  The scan left n_lists x kc (key, block) candidates; the kTcSelBlocks best blocks by
+ * (key, block id) are evaluated exactly -- the reference's fp32 sqrt(sum (q-t)^2) for each of their 32 templates --
+ * and the k smallest by (distance, index) are the answer, as BFMatcher::knnMatch orders them
+ * (reference src/networkevaluator.cpp:197; ties -> lower index). */
+__global__ void __launch_bounds__(32)
+knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ cand_i, int n_cand,
+                     const float* __restrict__ q, const float* __restrict__ db, int dp, long long t_local,
+                     long long row_offset, int k, int* __restrict__ out_idx, float* __restrict__ out_dist) {
+    extern __shared__ __align__(16) float sel_smem[];
+    float* sq = sel_smem;                                   /* [dp] */
+    float* sd = sel_smem + dp;                              /* [n_cand] keys */
+    int* si = reinterpret_cast<int*>(sd + n_cand);          /* [n_cand] block ids */
+    float* ed = reinterpret_cast<float*>(si + n_cand);      /* [kTcSelBlocks * 32] exact distances */
+    int* ei = reinterpret_cast<int*>(ed + kTcSelBlocks * kTcBlock);
+    const int lane = threadIdx.x;
+    const long long qi = blockIdx.x;
+    for (int d = lane; d < dp; d += 32) sq[d] = q[(size_t)qi * dp + d];
+    for (int c = lane; c < n_cand; c += 32) {
+        const int blk = cand_i[(size_t)qi * n_cand + c];
+        sd[c] = blk >= 0 ? cand_d[(size_t)qi * n_cand + c] : INFINITY;
+        si[c] = blk >= 0 ? blk : INT_MAX;
+    }
+    __syncwarp();
+    for (int r = 0; r < kTcSelBlocks; ++r) {
+        float bd = INFINITY;
+        int bi = INT_MAX, bc = -1;
+        for (int c = lane; c < n_cand; c += 32) {
+            const float d = sd[c];
+            const int i = si[c];
+            if (i != INT_MAX && (d < bd || (d == bd && i < bi) || bc < 0)) { bd = d; bi = i; bc = c; }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, bd, off);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+            const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
+            if (oc >= 0 && (bc < 0 || od < bd || (od == bd && oi < bi))) { bd = od; bi = oi; bc = oc; }
+        }
+        float d = INFINITY;
+        int idx = INT_MAX;
+        if (bc >= 0) {
+            const long long row = (long long)bi * kTcBlock + lane;
+            if (row < t_local) {
+                d = exact_l2(sq, db + (size_t)row * dp, dp);
+                idx = (int)row;
+            }
+        }
+        ed[r * kTcBlock + lane] = d;
+        ei[r * kTcBlock + lane] = idx;
+        __syncwarp();
+        if (lane == 0 && bc >= 0) si[bc] = INT_MAX;
+        __syncwarp();
+    }
+    for (int r = 0; r < k; ++r) {
+        float bd = INFINITY;
+        int bi = INT_MAX, bc = -1;
+#pragma unroll
+        for (int c = lane; c < kTcSelBlocks * kTcBlock; c += 32) {
+            const float d = ed[c];
+            const int i = ei[c];
+            if (i != INT_MAX && (bc < 0 || d < bd || (d == bd && i < bi))) { bd = d; bi = i; bc = c; }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, bd, off);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+            const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
+            if (oc >= 0 && (bc < 0 || od < bd || (od == bd && oi < bi))) { bd = od; bi = oi; bc = oc; }
+        }
+        if (lane == 0) {
+            out_idx[(size_t)qi * k + r] = bc >= 0 ? (int)(bi + row_offset) : -1;
+            out_dist[(size_t)qi * k + r] = bc >= 0 ? bd : INFINITY;
+            if (bc >= 0) ei[bc] = INT_MAX;
+        }
+        __syncwarp();
+    }
 }
 
 }  // namespace
@@ -517,8 +652,8 @@ int knn_tc_prepare(pe_db* db) {
 
 bool knn_tc_usable(const pe_db* db, int k) { return db->tc_ready && k + 2 <= 7; }
 
-/* plans the chunking; returns n_chunks and kc through the arguments */
-void knn_tc_plan(const pe_db* db, int64_t nq, int k, int* n_chunks, int* kc, int* tiles_per_chunk) {
+/* plans the chunking; returns the number of candidate lists per query (two per chunk: even and odd tiles) and kc */
+void knn_tc_plan(const pe_db* db, int64_t nq, int k, int* n_lists, int* kc, int* tiles_per_chunk) {
     const int n_qpairs = (int)((nq + 2 * kTcRows - 1) / (2 * kTcRows));
     const long long tiles = (db->t_local + kTcRows - 1) / kTcRows;
     long long c = (4LL * db->num_sms + n_qpairs - 1) / n_qpairs;
@@ -526,11 +661,11 @@ void knn_tc_plan(const pe_db* db, int64_t nq, int k, int* n_chunks, int* kc, int
     if (c > cmax) c = cmax;
     const long long tpc = (tiles + c - 1) / c;
     *tiles_per_chunk = (int)tpc;
-    *n_chunks = (int)((tiles + tpc - 1) / tpc);
+    *n_lists = 2 * (int)((tiles + tpc - 1) / tpc);
     *kc = k <= 1 ? 3 : 7;
 }
 
-int knn_tc_scan(pe_db* db, const float* d_q, int64_t nq, int k, int n_chunks, int kc, int tiles_per_chunk,
+int knn_tc_scan(pe_db* db, const float* d_q, int64_t nq, int k, int n_lists, int kc, int tiles_per_chunk,
                 float* cand_d, int* cand_i) {
     PE_CHECK(db->tau.reserve((size_t)nq * sizeof(int)));
     PE_CUDA(cudaMemsetAsync(db->tau.p, 0x7f, (size_t)nq * sizeof(int), db->stream));
@@ -543,7 +678,7 @@ int knn_tc_scan(pe_db* db, const float* d_q, int64_t nq, int k, int n_chunks, in
     a.row_offset = db->row_offset;
     a.tiles_total = (int)((db->t_local + kTcRows - 1) / kTcRows);
     a.tiles_per_chunk = tiles_per_chunk;
-    a.n_chunks = n_chunks;
+    a.n_chunks = n_lists / 2;
     a.n_qpairs = (int)((nq + 2 * kTcRows - 1) / (2 * kTcRows));
     a.log2_st = db->tc_log2_st;
     a.log2_sn = db->tc_log2_sn;
@@ -562,24 +697,36 @@ int knn_tc_scan(pe_db* db, const float* d_q, int64_t nq, int k, int n_chunks, in
     }
     const int items = a.n_chunks * a.n_qpairs;
     const int grid = items < db->num_sms ? items : db->num_sms;
-    if (kc == 3) {
-        PE_CUDA(cudaFuncSetAttribute(knn_tc_scan_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-        knn_tc_scan_kernel<3><<<grid, kTcThreads, kSmemTotal, db->stream>>>(a);
-    } else {
-        PE_CUDA(cudaFuncSetAttribute(knn_tc_scan_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-        knn_tc_scan_kernel<7><<<grid, kTcThreads, kSmemTotal, db->stream>>>(a);
-    }
+#define TC_LAUNCH(KCV, DBGV) do { \
+        PE_CUDA(cudaFuncSetAttribute(knn_tc_scan_kernel<KCV, DBGV>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal)); \
+        knn_tc_scan_kernel<KCV, DBGV><<<grid, kTcThreads, kSmemTotal, db->stream>>>(a); } while (0)
+    if (kc == 3) { if (dbg_on) TC_LAUNCH(3, true); else TC_LAUNCH(3, false); }
+    else { if (dbg_on) TC_LAUNCH(7, true); else TC_LAUNCH(7, false); }
+#undef TC_LAUNCH
     PE_LAUNCHED();
     if (dbg_on) {
         unsigned long long h[16];
         PE_CUDA(cudaMemcpyAsync(h, d_dbg, sizeof(h), cudaMemcpyDeviceToHost, db->stream));
         PE_CUDA(cudaStreamSynchronize(db->stream));
         cudaFree(d_dbg);
-        const double ew = 8.0 * grid, tiles_e = h[9] > 0 ? (double)h[9] : 1.0, tiles_m = h[8] > 0 ? (double)h[8] : 1.0;
+        const double ew = 16.0 * grid, tiles_e = h[9] > 0 ? (double)h[9] : 1.0, tiles_m = h[8] > 0 ? (double)h[8] : 1.0;
         fprintf(stderr, "[tc dbg] grid %d items %d  epilogue per warp-tile: wait_tfull %.0f hot %.0f slow %.0f other %.0f cycles, slow entries %.3f/tile | "
                         "mma per tile: wait_full %.0f wait_tempty %.0f issue %.0f (epi warps %.0f)\n", grid, items,
                 h[0] / tiles_e, h[1] / tiles_e, h[2] / tiles_e, h[3] / tiles_e, h[4] / tiles_e, h[5] / tiles_m, h[6] / tiles_m, h[7] / tiles_m, ew);
     }
+    return PE_OK;
+}
+
+/* exact re-ranking of the candidate blocks the scan produced: the local top-k of this shard */
+int knn_tc_select(pe_db* db, const float* cand_d, const int* cand_i, int n_lists, int kc, const float* d_q,
+                  int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist) {
+    const int n_cand = n_lists * kc;
+    const size_t smem = (size_t)(db->dim_pad + 2 * n_cand + 2 * kTcSelBlocks * kTcBlock) * 4;
+    PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
+    PE_CUDA(cudaFuncSetAttribute(knn_tc_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    knn_tc_select_kernel<<<(unsigned)nq, 32, smem, db->stream>>>(cand_d, cand_i, n_cand, d_q, db->d_desc, db->dim_pad,
+                                                                db->t_local, db->row_offset, k, d_out_idx, d_out_dist);
+    PE_LAUNCHED();
     return PE_OK;
 }
 

@@ -87,6 +87,21 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 
 /* -------------------------------------------------------------------- MMA --- */
 /* D[tmem] (+)= A[smem] * B[smem]; one thread issues for the CTA */
+/* one lane of a converged warp (elect.sync).  Issue tcgen05.mma / commit as
+ *     if (elect_one()) { mma_f16(...); ... }  __syncwarp();
+ * from code the WHOLE warp executes: the operands are then warp-uniform values (uniform registers) and ptxas emits a
+ * plain predicated UTCHMMA.  Inside an `if (lane == 0)` region it instead wraps every MMA in an
+ * ELECT / R2UR.BROADCAST / BRA.U.ANY loop that costs ~100 cycles per instruction. */
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 __device__ __forceinline__ void mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"

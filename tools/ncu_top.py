@@ -43,3 +43,8 @@ if len(sys.argv) > 6:
         o[0] += float(x[ci["# Samples"]] or 0); o[1] += float(x[ci["Instructions Executed"]] or 0)
     for k, v in sorted(ops.items(), key=lambda kv: -kv[1][0])[:25]:
         print(f"  {k:<12} samples {v[0]:>8.0f} exec {v[1]:>12.0f}")
+if len(sys.argv) > 7 and sys.argv[7] == "list":
+    for i in range(lo, hi):
+        x = rows[i]
+        top = sorted(((float(x[ci[k]] or 0), k) for k in stalls), reverse=True)[:2]
+        print(f'#{i:<5}{x[ci["# Samples"]]:>6} ex={x[ci["Instructions Executed"]]:>8} {x[ci["Source"]].strip()[:70]:<70} {[(int(a), b[6:]) for a, b in top if a > 0]}')

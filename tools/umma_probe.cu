@@ -211,6 +211,105 @@ int run_contention(int mma_reps, int ld_reps, int nw, long long* d_cycles, float
     return 0;
 }
 
+
+/* ---- 2d. drain variants: `nw` warps each read 128x128 accumulators (their lane quarter) and reduce every 32-column
+ *          block to its minimum; an optional MMA thread keeps the tensor pipe busy --------------------------- */
+__device__ __forceinline__ float probe_min32(const uint32_t (&v)[32]) {
+    float m8[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        m8[j] = fminf(fminf(__uint_as_float(v[j]), __uint_as_float(v[j + 8])), fminf(__uint_as_float(v[j + 16]), __uint_as_float(v[j + 24])));
+    return fminf(fminf(fminf(m8[0], m8[1]), fminf(m8[2], m8[3])), fminf(fminf(m8[4], m8[5]), fminf(m8[6], m8[7])));
+}
+template <int VARIANT>
+__global__ void __launch_bounds__(352) drain_kernel(int mma_reps, int ld_reps, int nw, long long* __restrict__ cycles, float* __restrict__ sink, int* __restrict__ status) {
+    extern __shared__ __align__(128) unsigned char dyn[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int i = tid; i < (8192 + 128 * 32) / 16; i += 352) reinterpret_cast<uint4*>(dyn)[i] = make_uint4(0, 0, 0, 0);
+    fence_async_smem();
+    if (warp == 0) tmem_alloc<512>(&tmem_slot);
+    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = tmem_slot;
+    if (warp == 1) {
+        if (lane == 0 && mma_reps > 0) {
+            const uint32_t idesc = instr_desc(128, 128, FMT_F16, FMT_F16);
+            const uint64_t a0 = smem_desc(smem_u32(dyn), 2048, 128);
+            const uint64_t b0 = smem_desc(smem_u32(dyn + 8192), 2048, 128);
+            const long long t0 = clock64();
+#pragma unroll 4
+            for (int r = 0; r < mma_reps; ++r) mma_f16(tmem + ((r >> 2) & 3) * 128, a0, b0, idesc, (r & 3) != 0);
+            mma_commit(&bar);
+            const bool ok = mbar_wait(&bar, 0);
+            cycles[0] = clock64() - t0;
+            if (!ok) atomicExch(status, 4);
+        }
+    } else if (warp >= 3 && warp < 3 + nw) {
+        const uint32_t tb = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+        float m = 0.f;
+        int hits = 0;
+        const long long t0 = clock64();
+#pragma unroll 1
+        for (int r = 0; r < ld_reps; ++r) {
+            const uint32_t base = tb + ((r + (warp >> 2)) & 3) * 128;
+            uint32_t v0[32], v1[32], v2[32], v3[32];
+            float m0, m1, m2, m3;
+            if (VARIANT == 0) {          /* serial: load, wait, reduce, four times */
+                tmem_ld32(base, v0); tmem_ld_wait(); m0 = probe_min32(v0);
+                tmem_ld32(base + 32, v1); tmem_ld_wait(); m1 = probe_min32(v1);
+                tmem_ld32(base + 64, v2); tmem_ld_wait(); m2 = probe_min32(v2);
+                tmem_ld32(base + 96, v3); tmem_ld_wait(); m3 = probe_min32(v3);
+            } else if (VARIANT == 1) {   /* four loads in flight, one wait */
+                tmem_ld32(base, v0); tmem_ld32(base + 32, v1); tmem_ld32(base + 64, v2); tmem_ld32(base + 96, v3);
+                tmem_ld_wait();
+                m0 = probe_min32(v0); m1 = probe_min32(v1); m2 = probe_min32(v2); m3 = probe_min32(v3);
+            } else if (VARIANT == 2) {   /* two and two, first half reduced under the second half's loads */
+                tmem_ld32(base, v0); tmem_ld32(base + 32, v1);
+                tmem_ld_wait();
+                tmem_ld32(base + 64, v2); tmem_ld32(base + 96, v3);
+                m0 = probe_min32(v0); m1 = probe_min32(v1);
+                tmem_ld_wait();
+                m2 = probe_min32(v2); m3 = probe_min32(v3);
+            } else {                     /* one at a time, each reduced under the next load */
+                tmem_ld32(base, v0); tmem_ld_wait();
+                tmem_ld32(base + 32, v1); m0 = probe_min32(v0); tmem_ld_wait();
+                tmem_ld32(base + 64, v2); m1 = probe_min32(v1); tmem_ld_wait();
+                tmem_ld32(base + 96, v3); m2 = probe_min32(v2); tmem_ld_wait();
+                m3 = probe_min32(v3);
+            }
+            const float mm = fminf(fminf(m0, m1), fminf(m2, m3));
+            if (__any_sync(0xffffffffu, mm < -1.f)) ++hits;
+            m = fminf(m, mm);
+        }
+        const long long t1 = clock64();
+        if (lane == 0) cycles[warp] = t1 - t0;
+        sink[tid] = m + hits;
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<512>(tmem);
+}
+
+template <int VARIANT>
+int run_drain(int mma_reps, int ld_reps, int nw, long long* d_cycles, float* d_sink, int* d_status) {
+    const size_t smem = 8192 + 128 * 32;
+    CK(cudaMemset(d_cycles, 0, 16 * sizeof(long long)));
+    for (int i = 0; i < 2; ++i) {
+        drain_kernel<VARIANT><<<1, 352, smem>>>(mma_reps, ld_reps, nw, d_cycles, d_sink, d_status);
+        CK(cudaDeviceSynchronize());
+    }
+    long long c[16];
+    CK(cudaMemcpy(c, d_cycles, sizeof(c), cudaMemcpyDeviceToHost));
+    printf("drain variant %d mma_reps=%5d ld_reps=%4d nw=%d: %.1f cycles/MMA, %.1f cycles per 128x128 drain (warp 3), %.1f (warp %d)\n",
+           VARIANT, mma_reps, ld_reps, nw, mma_reps ? (double)c[0] / mma_reps : 0.0, ld_reps ? (double)c[3] / ld_reps : 0.0,
+           ld_reps ? (double)c[2 + nw] / ld_reps : 0.0, 2 + nw);
+    return 0;
+}
+
 template <int N>
 int run_switch(int per, int nbuf, int a_lbo, int fresh, long long* d_cycles, int* d_status) {
     const int reps = 2048;
@@ -329,7 +428,7 @@ int main() {
         if (run_switch<64>(4, 8, 2048, 1, d_cycles, d_status)) return 1;
         if (run_switch<64>(1, 8, 2048, 1, d_cycles, d_status)) return 1;
         float* d_sink;
-        CK(cudaMalloc(&d_sink, 320 * 4));
+        CK(cudaMalloc(&d_sink, 352 * 4));
         {
             long long* d_c16;
             CK(cudaMalloc(&d_c16, 16 * sizeof(long long)));
@@ -338,6 +437,15 @@ int main() {
             if (run_contention(0, 512, 8, d_c16, d_sink, d_status)) return 1;
             if (run_contention(8192, 512, 4, d_c16, d_sink, d_status)) return 1;
             if (run_contention(16384, 512, 8, d_c16, d_sink, d_status)) return 1;
+            for (int nw : {1, 4, 8}) {
+                if (run_drain<0>(0, 512, nw, d_c16, d_sink, d_status)) return 1;
+                if (run_drain<1>(0, 512, nw, d_c16, d_sink, d_status)) return 1;
+                if (run_drain<2>(0, 512, nw, d_c16, d_sink, d_status)) return 1;
+                if (run_drain<3>(0, 512, nw, d_c16, d_sink, d_status)) return 1;
+            }
+            if (run_drain<1>(8 * 512, 512, 8, d_c16, d_sink, d_status)) return 1;
+            if (run_drain<2>(8 * 512, 512, 8, d_c16, d_sink, d_status)) return 1;
+            if (run_drain<3>(8 * 512, 512, 8, d_c16, d_sink, d_status)) return 1;
         }
         tmem_ld_rate_kernel<<<1, 128>>>(256, d_cycles, d_sink);
         CK(cudaDeviceSynchronize());
