@@ -107,6 +107,7 @@ SIGNATURES = {
     "pe_comm_allreduce_sum_f64": (C.c_int, [vp, vp, C.c_int64]),
     "pe_comm_allgather_f32_dev": (C.c_int, [vp, vp, vp, C.c_int64, vp]),
     "pe_knn_sharded": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "pe_match_patches": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_int, C.c_int, vp, vp, vp]),
     "pe_knn_sharded_dev": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
     "pe_knn_hamming_sharded": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
 }
@@ -442,6 +443,17 @@ class TemplateDB:
         dist = np.empty((nq, k), np.float32)
         check(lib().pe_knn_sharded(self.h, comm.h if comm else None, _ptr(q), nq, k, _ptr(idx), _ptr(dist)))
         return idx, dist
+
+    def match_patches(self, net, comm, patches, k, want_desc=False):
+        """fused computeKNN test pass (pe_match_patches): host patches (n, 64, 64, C) -> (idx, dist[, desc])"""
+        x = _f32(patches)
+        n, c = x.shape[0], x.shape[-1]
+        idx = np.empty((n, k), np.int32)
+        dist = np.empty((n, k), np.float32)
+        desc = np.empty((n, self.dim), np.float32) if want_desc else None
+        check(lib().pe_match_patches(net.h, self.h, comm.h if comm else None, _ptr(x), n, c, k, _ptr(idx), _ptr(dist),
+                                     _ptr(desc) if want_desc else None))
+        return (idx, dist, desc) if want_desc else (idx, dist)
 
     def knn_sharded_dev(self, comm, d_q, nq, k, d_idx, d_dist):
         check(lib().pe_knn_sharded_dev(self.h, comm.h if comm else None, d_q.ptr if isinstance(d_q, DeviceArray) else d_q,

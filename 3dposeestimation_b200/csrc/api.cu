@@ -700,8 +700,9 @@ void pe_db_destroy(pe_db* db) {
     if (db->d_tc_err) cudaFreeHost(db->d_tc_err);
     db->tau.release();
     for (DevBuf* b : {&db->q, &db->q_in, &db->cand_d, &db->cand_i, &db->out_i, &db->out_d, &db->qlab, &db->knn_idx,
-                      &db->scratch, &db->scratch2, &db->gather, &db->boot})
+                      &db->scratch, &db->scratch2, &db->gather, &db->boot, &db->m_q, &db->m_ci, &db->m_cd, &db->m_ri, &db->m_rd})
         b->release();
+    if (db->ev_match) cudaEventDestroy(db->ev_match);
     if (db->stream && db->own_stream) cudaStreamDestroy(db->stream);
     delete db;
 }

@@ -229,7 +229,84 @@ int pe_knn_sharded(pe_db* db, pe_comm* comm, const float* queries, int64_t nq, i
     PE_CUDA(cudaMemcpyAsync(out_idx, db->out_i.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, db->stream));
     PE_CUDA(cudaMemcpyAsync(out_dist, db->out_d.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, db->stream));
     PE_CUDA(cudaStreamSynchronize(db->stream));
-    return PE_OK;
+    return knn_tc_check(db);
+}
+
+/* Fused test pass of networkSolver::computeKNN / networkEvaluator::computeKNNAccuracy's first half
+ * (reference src/networksolver.cpp:456-472, src/networkevaluator.cpp:182-197): descriptors of n host patches, then
+ * their k nearest templates.  The batch is cut into 512-patch stages; the H2D copy of stage i+1 runs under the forward
+ * and the DB scan of stage i, so on a PCIe-bound box the call takes the copy time plus one stage.  With a
+ * communicator every rank must pass the same n; the DB is row-sharded and each stage's descriptors are all-gathered. */
+int pe_match_patches(pe_net* net, pe_db* db, pe_comm* comm, const float* patches_hwc, int64_t n, int patch_channels,
+                     int k, int32_t* out_idx, float* out_dist, float* out_desc) {
+    PE_REQUIRE(net && db, "null net / db");
+    PE_REQUIRE(!db->hamming, "pe_match_patches needs an L2 DB");
+    PE_REQUIRE(n >= 0 && k >= 1 && k <= 16, "bad n / k");
+    PE_REQUIRE(patch_channels == net->def.channels, "patches have %d channels, net input has %d", patch_channels, net->def.channels);
+    PE_REQUIRE(net->def.desc_dim == db->dim, "descriptor dim %d != DB dim %d", net->def.desc_dim, db->dim);
+    PE_REQUIRE(net->device == db->device && (!comm || comm->device == db->device), "net, DB and communicator must share a device");
+    PE_CHECK(net_ensure_device(net));
+    if (n == 0) return PE_OK;
+    PE_REQUIRE(patches_hwc && out_idx && out_dist, "null pointer");
+    const int world = comm ? comm->world : 1, rank = comm ? comm->rank : 0;
+    const int D = net->def.desc_dim;
+    const size_t patch_floats = (size_t)4096 * patch_channels;
+    const int64_t sub = 512;
+    const int64_t stage_n = n < sub ? n : sub;
+    PE_CHECK(net->in_stage[0].reserve(stage_n * patch_floats * sizeof(float)));
+    if (n > sub) PE_CHECK(net->in_stage[1].reserve(stage_n * patch_floats * sizeof(float)));
+    PE_CHECK(net->out_stage.reserve((size_t)n * D * sizeof(float)));
+    PE_CHECK(db->m_ri.reserve((size_t)n * k * 4));
+    PE_CHECK(db->m_rd.reserve((size_t)n * k * 4));
+    if (world > 1) {
+        PE_CHECK(db->m_q.reserve((size_t)world * stage_n * D * 4));
+        PE_CHECK(db->m_ci.reserve((size_t)world * stage_n * k * 4));
+        PE_CHECK(db->m_cd.reserve((size_t)world * stage_n * k * 4));
+    }
+    if (!db->ev_match) PE_CUDA(cudaEventCreateWithFlags(&db->ev_match, cudaEventDisableTiming));
+    const bool two_streams = db->stream != net->stream;
+    int it = 0;
+    for (int64_t first = 0; first < n; first += sub, ++it) {
+        const int64_t m = n - first < sub ? n - first : sub;
+        const int b = it & 1;
+        if (it >= 2) PE_CUDA(cudaStreamWaitEvent(net->copy_stream, net->ev_done[b], 0));
+        PE_CUDA(cudaMemcpyAsync(net->in_stage[b].p, patches_hwc + first * patch_floats, m * patch_floats * sizeof(float),
+                                cudaMemcpyHostToDevice, net->copy_stream));
+        PE_CUDA(cudaEventRecord(net->ev_in[b], net->copy_stream));
+        PE_CUDA(cudaStreamWaitEvent(net->stream, net->ev_in[b], 0));
+        float* d_desc = net->out_stage.as<float>() + (size_t)first * D;
+        PE_CHECK(net_forward_dev(net, net->in_stage[b].as<float>(), m, patch_channels, d_desc, D));
+        PE_CUDA(cudaEventRecord(net->ev_done[b], net->stream));
+        const float* d_q = d_desc;
+        if (world > 1) {
+            PE_NCCL(g_nccl.AllGather(d_desc, db->m_q.p, (size_t)m * D, ncclFloat32, comm->comm, net->stream));
+            d_q = db->m_q.as<float>();
+        }
+        if (two_streams) {
+            PE_CUDA(cudaEventRecord(db->ev_match, net->stream));
+            PE_CUDA(cudaStreamWaitEvent(db->stream, db->ev_match, 0));
+        }
+        int32_t* r_i = db->m_ri.as<int32_t>() + (size_t)first * k;
+        float* r_d = db->m_rd.as<float>() + (size_t)first * k;
+        if (world > 1) {
+            PE_CHECK(sharded_knn<float>(db, comm, d_q, world * m, k, db->m_ci.as<int32_t>(), db->m_cd.as<float>(), false));
+            PE_CUDA(cudaMemcpyAsync(r_i, db->m_ci.as<int32_t>() + (size_t)rank * m * k, (size_t)m * k * 4, cudaMemcpyDeviceToDevice, db->stream));
+            PE_CUDA(cudaMemcpyAsync(r_d, db->m_cd.as<float>() + (size_t)rank * m * k, (size_t)m * k * 4, cudaMemcpyDeviceToDevice, db->stream));
+            if (two_streams) {   /* the next stage's all-gather reuses m_q: it must not overtake this scan */
+                PE_CUDA(cudaEventRecord(db->ev_match, db->stream));
+                PE_CUDA(cudaStreamWaitEvent(net->stream, db->ev_match, 0));
+            }
+        } else {
+            PE_CHECK(knn_l2_local(db, d_q, m, k, r_i, r_d));
+        }
+    }
+    PE_CUDA(cudaMemcpyAsync(out_idx, db->m_ri.p, (size_t)n * k * 4, cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaMemcpyAsync(out_dist, db->m_rd.p, (size_t)n * k * 4, cudaMemcpyDeviceToHost, db->stream));
+    if (out_desc) PE_CUDA(cudaMemcpyAsync(out_desc, net->out_stage.p, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaStreamSynchronize(db->stream));
+    PE_CUDA(cudaStreamSynchronize(net->stream));
+    PE_CHECK(forward_tc_check(net));
+    return knn_tc_check(db);
 }
 
 int pe_knn_hamming_sharded(pe_db* db, pe_comm* comm, const uint32_t* qcodes, int64_t nq, int k, int32_t* out_idx,

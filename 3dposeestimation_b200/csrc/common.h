@@ -161,6 +161,8 @@ struct pe_db {
     float tc_center[16] = {};         /* DB mean the tensor tiles are centred on */
     pe::DevBuf tau;                   /* [nq] shared admission thresholds of the tensor scan */
     pe::DevBuf q, q_in, cand_d, cand_i, out_i, out_d, qlab, knn_idx, scratch, scratch2, gather, boot;
+    pe::DevBuf m_q, m_ci, m_cd, m_ri, m_rd;   /* pe_match_patches: gathered chunk queries, chunk and final results */
+    cudaEvent_t ev_match = nullptr;           /* forward of a chunk finished (net stream -> DB stream) */
 };
 
 namespace pe {

@@ -126,40 +126,47 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
     const uint32_t tmem = *tmem_slot;
 
     if (warp == 0) {
-        /* ======================= MMA issuer ======================= */
-        if (lane == 0) {
-            const uint32_t idesc = instr_desc(128, 128, FMT_F16, FMT_F16);
-            const uint32_t s0 = smem_u32(smem);
-            const uint64_t a_hi = smem_desc(s0 + kOffImgHi, 16, 128), a_lo = smem_desc(s0 + kOffImgLo, 16, 128);
-            const uint64_t b_hi = smem_desc(s0 + kOffZHi, kZStride, 128), b_lo = smem_desc(s0 + kOffZLo, kZStride, 128);
-            uint32_t it = 0;
-            for (long long patch = blockIdx.x; patch < a.n && !*s_abort; patch += gridDim.x, ++it) {
+        /* ======================= MMA issuer: the whole warp runs the loops (warp-uniform operands), one elected lane
+         * issues ======================= */
+        const uint32_t idesc = instr_desc(128, 128, FMT_F16, FMT_F16);
+        const uint32_t s0 = smem_u32(smem);
+        const uint64_t a_hi = smem_desc(s0 + kOffImgHi, 16, 128), a_lo = smem_desc(s0 + kOffImgLo, 16, 128);
+        const uint64_t b_hi = smem_desc(s0 + kOffZHi, kZStride, 128), b_lo = smem_desc(s0 + kOffZLo, kZStride, 128);
+        uint32_t it = 0;
+        bool ok = true;
+        for (long long patch = blockIdx.x; patch < a.n && ok && !*s_abort; patch += gridDim.x, ++it) {
 #pragma unroll 1
-                for (int t = 0; t < 4; ++t) {
-                    if (!mbar_wait(&acc_empty[t], (it & 1) ^ 1)) { atomicExch(a.err, 1); *s_abort = 1; break; }
-                    if (!mbar_wait(&img_full[t], it & 1)) { atomicExch(a.err, 2); *s_abort = 1; break; }
-                    if (t < 3 && !mbar_wait(&img_full[t + 1], it & 1)) { atomicExch(a.err, 3); *s_abort = 1; break; }
-                    fence_after_sync();
-                    const uint32_t d = tmem + t * 128;
-                    uint32_t acc = 0;
+            for (int t = 0; t < 4; ++t) {
+                int e = 0;
+                if (!mbar_wait(&acc_empty[t], (it & 1) ^ 1)) e = 1;
+                else if (!mbar_wait(&img_full[t], it & 1)) e = 2;
+                else if (t < 3 && !mbar_wait(&img_full[t + 1], it & 1)) e = 3;
+                if (e) { if (lane == 0) atomicExch(a.err, e); ok = false; break; }
+                fence_after_sync();
+                const uint32_t d = tmem + t * 128;
 #pragma unroll 1
-                    for (int ky = 0; ky < 15; ++ky) {
-                        const uint32_t a_row = static_cast<uint32_t>(row_pos(16 * t + ky)) * (kRowBytes >> 4);
-                        const uint32_t b_row = static_cast<uint32_t>(14 - ky) * (256 >> 4);
+                for (int ky = 0; ky < 15; ++ky) {
+                    const uint32_t a_row = static_cast<uint32_t>(row_pos(16 * t + ky)) * (kRowBytes >> 4);
+                    const uint32_t b_row = static_cast<uint32_t>(14 - ky) * (256 >> 4);
+                    if (elect_one()) {
 #pragma unroll
                         for (int p = 0; p < 4; ++p) {
                             const uint32_t ao = a_row + p * 2, bo = b_row + p * 2 * (kZStride >> 4);
-                            mma_f16(d, a_hi + ao, b_hi + bo, idesc, acc);
-                            acc = 1;
+                            mma_f16(d, a_hi + ao, b_hi + bo, idesc, (ky | p) != 0);
                             mma_f16(d, a_hi + ao, b_lo + bo, idesc, 1);
                             mma_f16(d, a_lo + ao, b_hi + bo, idesc, 1);
                         }
                     }
+                    __syncwarp();
+                }
+                if (elect_one()) {
                     mma_commit(&img_empty[t]);
                     mma_commit(&acc_full[t]);
                 }
+                __syncwarp();
             }
         }
+        if (!ok) *s_abort = 1;
     } else if (warp <= 8) {
         /* ======================= epilogue: warps 1-4 drain tiles 0 and 2, warps 5-8 tiles 1 and 3 ======================= */
         const int set = (warp - 1) >> 2;
@@ -371,38 +378,43 @@ __global__ void __launch_bounds__(kC2TcThreads, 1) conv2_tc_kernel(const C2Args 
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            const uint32_t idesc = instr_desc(128, 64, FMT_F16, FMT_F16);
-            const uint32_t s0 = smem_u32(smem);
-            const uint64_t b_hi = smem_desc(s0 + kC2OffZ, kZ2Stride, 128), b_lo = smem_desc(s0 + kC2OffZ + kZ2Bytes, kZ2Stride, 128);
-            uint32_t it = 0;
-            for (long long patch = blockIdx.x; patch < a.n && !*s_abort; patch += gridDim.x, ++it) {
-                const int s = it & 1;
-                const uint32_t ph = (it >> 1) & 1;
-                if (!mbar_wait(&acc_empty[s], ph ^ 1)) { atomicExch(a.err, 22); *s_abort = 1; break; }
-                if (!mbar_wait(&img_full[s], ph)) { atomicExch(a.err, 23); *s_abort = 1; break; }
-                fence_after_sync();
-                const uint32_t img = s0 + kC2OffImg + s * kP1PackedBytes;
-                const uint64_t a_hi = smem_desc(img, kP1PlaneBytes, 128), a_lo = smem_desc(img + 2 * kP1PlaneBytes, kP1PlaneBytes, 128);
-                const uint32_t d = tmem + s * 64;
-                uint32_t acc = 0;
+        /* MMA issuer: whole warp, one elected lane issues (see conv1) */
+        const uint32_t idesc = instr_desc(128, 64, FMT_F16, FMT_F16);
+        const uint32_t s0 = smem_u32(smem);
+        const uint64_t b_hi = smem_desc(s0 + kC2OffZ, kZ2Stride, 128), b_lo = smem_desc(s0 + kC2OffZ + kZ2Bytes, kZ2Stride, 128);
+        uint32_t it = 0;
+        bool ok = true;
+        for (long long patch = blockIdx.x; patch < a.n && ok && !*s_abort; patch += gridDim.x, ++it) {
+            const int s = it & 1;
+            const uint32_t ph = (it >> 1) & 1;
+            if (!mbar_wait(&acc_empty[s], ph ^ 1)) { if (lane == 0) atomicExch(a.err, 22); ok = false; break; }
+            if (!mbar_wait(&img_full[s], ph)) { if (lane == 0) atomicExch(a.err, 23); ok = false; break; }
+            fence_after_sync();
+            const uint32_t img = s0 + kC2OffImg + s * kP1PackedBytes;
+            const uint64_t a_hi = smem_desc(img, kP1PlaneBytes, 128), a_lo = smem_desc(img + 2 * kP1PlaneBytes, kP1PlaneBytes, 128);
+            const uint32_t d = tmem + s * 64;
 #pragma unroll 1
-                for (int ky = 0; ky < 12; ++ky) {
-                    const uint32_t a_row = static_cast<uint32_t>(p1_row_pos(ky)) * (512 >> 4);
-                    const uint32_t b_row = static_cast<uint32_t>(11 - ky) * (128 >> 4);
+            for (int ky = 0; ky < 12; ++ky) {
+                const uint32_t a_row = static_cast<uint32_t>(p1_row_pos(ky)) * (512 >> 4);
+                const uint32_t b_row = static_cast<uint32_t>(11 - ky) * (128 >> 4);
+                if (elect_one()) {
 #pragma unroll
                     for (int kx = 0; kx < 5; ++kx) {
                         const uint32_t ao = a_row + kx, bo = b_row + kx * 2 * (kZ2Stride >> 4);
-                        mma_f16(d, a_hi + ao, b_hi + bo, idesc, acc);
-                        acc = 1;
+                        mma_f16(d, a_hi + ao, b_hi + bo, idesc, (ky | kx) != 0);
                         mma_f16(d, a_hi + ao, b_lo + bo, idesc, 1);
                         mma_f16(d, a_lo + ao, b_hi + bo, idesc, 1);
                     }
                 }
+                __syncwarp();
+            }
+            if (elect_one()) {
                 mma_commit(&img_empty[s]);
                 mma_commit(&acc_full[s]);
             }
+            __syncwarp();
         }
+        if (!ok) *s_abort = 1;
     } else {
         const int quarter = warp & 3;
         const int m = quarter * 32 + lane;

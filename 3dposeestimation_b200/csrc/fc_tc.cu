@@ -91,29 +91,31 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            const uint32_t idesc = instr_desc(128, n_mma, FMT_F16, FMT_F16);
-            uint32_t acc = 0;
-            for (int kb = 0; kb < a.k_blocks; ++kb) {
-                const int s = kb % kFcStages;
-                if (!mbar_wait(&full_a[s], (kb / kFcStages) & 1)) { atomicExch(a.err, 12); break; }
-                if (!mbar_wait(&full_b[s], (kb / kFcStages) & 1)) { atomicExch(a.err, 13); break; }
-                fence_after_sync();
-                const uint32_t base = smem_u32(smem + s * kFcStageBytes);
-                const uint64_t a_hi = smem_desc(base, 2048, 128), a_lo = smem_desc(base + kFcTerm, 2048, 128);
-                const uint64_t b_hi = smem_desc(base + 2 * kFcTerm, 2048, 128), b_lo = smem_desc(base + 3 * kFcTerm, 2048, 128);
+        /* the whole warp runs the loop (warp-uniform operands), one elected lane issues */
+        const uint32_t idesc = instr_desc(128, n_mma, FMT_F16, FMT_F16);
+        bool ok = true;
+        for (int kb = 0; kb < a.k_blocks; ++kb) {
+            const int s = kb % kFcStages;
+            if (!mbar_wait(&full_a[s], (kb / kFcStages) & 1)) { if (lane == 0) atomicExch(a.err, 12); ok = false; break; }
+            if (!mbar_wait(&full_b[s], (kb / kFcStages) & 1)) { if (lane == 0) atomicExch(a.err, 13); ok = false; break; }
+            fence_after_sync();
+            const uint32_t base = smem_u32(smem + s * kFcStageBytes);
+            const uint64_t a_hi = smem_desc(base, 2048, 128), a_lo = smem_desc(base + kFcTerm, 2048, 128);
+            const uint64_t b_hi = smem_desc(base + 2 * kFcTerm, 2048, 128), b_lo = smem_desc(base + 3 * kFcTerm, 2048, 128);
+            if (elect_one()) {
 #pragma unroll
                 for (int ks = 0; ks < 4; ++ks) {
                     const uint32_t o = ks * 2 * (2048 >> 4);
-                    mma_f16(tmem, a_hi + o, b_hi + o, idesc, acc);
-                    acc = 1;
+                    mma_f16(tmem, a_hi + o, b_hi + o, idesc, (kb | ks) != 0);
                     mma_f16(tmem, a_hi + o, b_lo + o, idesc, 1);
                     mma_f16(tmem, a_lo + o, b_hi + o, idesc, 1);
                 }
                 mma_commit(&empty[s]);
             }
-            mma_commit(acc_full);
+            __syncwarp();
         }
+        if (ok && elect_one()) mma_commit(acc_full);
+        __syncwarp();
     } else {
         /* ---- loaders: thread r converts row m0 + r, one K block at a time ---- */
         const int r = (warp & 3) * 32 + lane;     /* = the TMEM lane this thread may read in the epilogue */

@@ -181,16 +181,32 @@ public:
         detail::check_rectangular(query_set, "query set");
         if (query_set.size() != template_set.size()) throw std::runtime_error("template and query sets differ in object count");
         Mat DBfeats;
-        for (size_t object = 0; object < template_set.size(); ++object) {
+        for (size_t object = 0; object < template_set.size(); ++object)
             DBfeats.push_back(computeDescriptors(CNN, template_set[object]));
-            DBquery->push_back(computeDescriptors(CNN, query_set[object]));
-        }
         const std::vector<float> tl = detail::flatten_labels(template_set);
         pe_check(pe_db_create(DBfeats.ptr<float>(0), DBfeats.rows, DBfeats.cols, 0, tl.data(), DBfeats.rows,
                               (int)template_set[0].size(), 0, &g->db));
-        std::vector<int32_t> idx((size_t)DBquery->rows * knn);
-        std::vector<float> dist((size_t)DBquery->rows * knn);
-        pe_check(pe_knn(g->db, DBquery->ptr<float>(0), DBquery->rows, knn, idx.data(), dist.data()));
+        /* the query side (DBtest.push_back(computeDescriptors(...)) per object, then knnMatch) as one fused call:
+         * the patches of all objects in object order, descriptors and neighbours back together */
+        int batch, channels, height, width, desc_dim;
+        CNN.shape(&batch, &channels, &height, &width, &desc_dim);
+        const size_t img = (size_t)height * width * channels;
+        size_t nq = 0;
+        for (const std::vector<Sample>& obj : query_set) nq += obj.size();
+        std::vector<float> staging(nq * img);
+        size_t at = 0;
+        for (const std::vector<Sample>& obj : query_set)
+            for (const Sample& smp : obj) {
+                if (smp.data.rows != height || smp.data.cols != width || smp.data.ch != channels)
+                    throw std::runtime_error("match: patch shape does not match the net input");
+                std::memcpy(staging.data() + at * img, smp.data.buf.data(), img * sizeof(float));
+                ++at;
+            }
+        *DBquery = Mat((int)nq, desc_dim);
+        std::vector<int32_t> idx(nq * knn);
+        std::vector<float> dist(nq * knn);
+        pe_check(pe_match_patches(CNN.handle(), g->db, nullptr, staging.data(), (int64_t)nq, channels, knn, idx.data(),
+                                  dist.data(), DBquery->ptr<float>(0)));
         return idx;
     }
 };

@@ -240,6 +240,14 @@ PE_API int pe_knn_sharded(pe_db* db, pe_comm* comm, const float* queries, int64_
                           int32_t* out_idx, float* out_dist);
 PE_API int pe_knn_sharded_dev(pe_db* db, pe_comm* comm, const float* d_queries, int64_t nq, int k,
                               int32_t* d_out_idx, float* d_out_dist);
+/* Fused test pass: descriptors of n HOST patches and their k nearest templates in one call, i.e. what
+ * networkSolver::computeKNN (reference src/networksolver.cpp:456-472) and the first half of
+ * networkEvaluator::computeKNNAccuracy (src/networkevaluator.cpp:182-197) do with CNN.Forward + knnMatch.
+ * The batch is staged in 512-patch pieces so that the host->device copy overlaps the forward and the scan.
+ * comm may be null (unsharded DB); with a communicator every rank passes its own n patches (same n on all
+ * ranks) and gets its own n x k results.  out_desc (n x dim) may be null. */
+PE_API int pe_match_patches(pe_net* net, pe_db* db, pe_comm* comm, const float* patches_hwc, int64_t n,
+                            int patch_channels, int k, int32_t* out_idx, float* out_dist, float* out_desc);
 PE_API int pe_knn_hamming_sharded(pe_db* db, pe_comm* comm, const uint32_t* qcodes, int64_t nq,
                                   int k, int32_t* out_idx, int32_t* out_dist);
 

@@ -347,6 +347,31 @@ def test_config1_manifold_15x1300_end_to_end(gpu, po, synth):
     np.testing.assert_allclose(h[6:], ho[6:], rtol=0, atol=1e-3)
 
 
+def test_match_patches_equals_forward_then_knn(gpu, po, synth, knn_path):
+    """pe_match_patches (fused computeKNN test pass, 512-patch stages) == compute_descriptors + knn on the same data,
+    bit for bit, and agrees with the oracle chain on a subset"""
+    net, oracle, ref = make_net(gpu, po, synth, "manifold_rgbdnor_16", 5)
+    nt, nq = 2600, 1300                                      # 3 stages, ragged tail
+    d_p = gpu.DeviceArray((nt + nq, 64, 64, 7))
+    net.synth_patches_dev(synth.BASE_SEED, 0, nt, 130, d_p)
+    net.synth_patches_dev(synth.BASE_SEED + 1, 0, nq, 65, d_p, out_offset=nt)
+    patches = d_p.to_host()
+    tdesc = net.compute_descriptors(patches[:nt])
+    db = gpu.TemplateDB(desc=tdesc)
+    for k in (1, 3):
+        idx, dist, desc = db.match_patches(net, None, patches[nt:], k, want_desc=True)
+        desc2 = net.compute_descriptors(patches[nt:])
+        idx2, dist2 = db.knn(desc2, k)
+        assert np.array_equal(desc, desc2) and np.array_equal(idx, idx2) and np.array_equal(dist, dist2)
+    sub = np.r_[0:16, 600:616, nq - 16:nq]
+    want = oracle.forward(patches[nt:][sub])
+    assert rowscale_err(desc[sub], want) < DESC_TOL
+    oi, od, gap = po.knn_l2(desc[sub], tdesc, 3, want_gap=True)
+    assert check_knn(idx[sub], dist[sub], oi, od, gap) < 0.10
+    e_i, e_d = db.match_patches(net, None, patches[:0], 1)
+    assert e_i.shape == (0, 1) and e_d.shape == (0, 1)
+
+
 # --------------------------------------------------- full-size properties (1 M templates) ---
 def test_full_size_db_properties(gpu, synth, knn_path):
     """BASELINE.json 1M-template DB: properties that need no CPU pass over the DB"""
