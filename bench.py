@@ -49,43 +49,87 @@ def load_peaks():
 
 
 class ClockSampler:
-    """samples nvidia-smi clocks / throttle reasons during the timed region"""
+    """SM clocks / throttle reasons DURING the timed region.  Two sources run from before the warm-up to after the timed
+    steps: the recipe's `nvidia-smi --query-gpu=... -lms` line, and an NVML poll every ~2 ms from a thread (the timed
+    region of a default run lasts only some tens of milliseconds).  Only samples whose arrival time falls between
+    mark_begin() and mark_end() are reported."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, device):
-        self.device, self.rows, self.proc = device, [], None
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        ids = [x for x in vis.split(",") if x.strip().isdigit()]
+        self.device = int(ids[device]) if device < len(ids) else device
+        self.smi_rows, self.nvml_rows, self.proc, self.stop_flag = [], [], None, False
+        self.t0 = self.t1 = None
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.device), "-lms", "100"], stdout=subprocess.PIPE, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
+                                          "-i", str(self.device), "-lms", "20"], stdout=subprocess.PIPE, text=True)
+            self.t_smi = threading.Thread(target=self._read_smi, daemon=True)
+            self.t_smi.start()
         except Exception:
             self.proc = None
+        self.t_nvml = threading.Thread(target=self._poll_nvml, daemon=True)
+        self.t_nvml.start()
 
-    def _read(self):
+    def _read_smi(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.smi_rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
+
+    def _poll_nvml(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.device)
+            mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            names = (("hw_slowdown", pynvml.nvmlClocksEventReasonHwSlowdown), ("hw_thermal_slowdown", pynvml.nvmlClocksEventReasonHwThermalSlowdown),
+                     ("sw_thermal_slowdown", pynvml.nvmlClocksEventReasonSwThermalSlowdown), ("sw_power_cap", pynvml.nvmlClocksEventReasonSwPowerCap))
+            while not self.stop_flag:
+                clk = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                try:
+                    mask = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    mask = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.nvml_rows.append((time.perf_counter(), float(clk), float(mx), [n for n, bit in names if mask & bit]))
+                time.sleep(0.002)
+        except Exception:
+            pass
+
+    def mark_begin(self):
+        self.t0 = time.perf_counter()
+
+    def mark_end(self):
+        self.t1 = time.perf_counter()
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.12)
-        self.proc.terminate()
-        self.t.join(timeout=2)
-        sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        time.sleep(0.05)
+        self.stop_flag = True
+        if self.proc:
+            self.proc.terminate()
+            self.t_smi.join(timeout=2)
+        self.t_nvml.join(timeout=2)
+        t0, t1 = self.t0 or 0.0, self.t1 or float("inf")
+        sm, mx, reasons, n_smi, n_nvml = [], [], set(), 0, 0
+        for t, r in self.smi_rows:
+            if not (t0 <= t <= t1 + 0.02):      # a row printed just after the region was sampled inside it
+                continue
             try:
-                sm.append(float(r[1])); mx.append(float(r[2]))
+                sm.append(float(r[1])); mx.append(float(r[2])); n_smi += 1
             except Exception:
                 continue
             for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7), ("sw_power_cap", 8)):
                 if len(r) > col and r[col].lower().startswith("active"):
                     reasons.add(name)
+        for t, clk, m, rs in self.nvml_rows:
+            if t0 <= t <= t1:
+                sm.append(clk); mx.append(m); n_nvml += 1
+                reasons.update(rs)
+        if not sm and not self.proc and not self.nvml_rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "samples": 0, "reasons": ["nvidia-smi / NVML unavailable"]}
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "samples_nvidia_smi": n_smi, "samples_nvml": n_nvml, "reasons": sorted(reasons)}
 
 
 # ----------------------------------------------------------------------------- CPU legs ---
@@ -127,12 +171,27 @@ def cpu_arm(steps, warmup, budget_s, threads=0):
             "descriptors_per_s": 1.0 / f, "knn_queries_per_s": 1.0 / q, "ms_per_step_equiv": (f + q) * BATCH * 1e3}
 
 
+def bind_to_gpu_numa_node(device):
+    """best effort: run this rank (and first-touch its pinned host buffers) on the CPUs closest to its GPU, so that the
+    470 MB per step of host patches do not cross the socket interconnect on their way to PCIe"""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = [x for x in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if x.strip().isdigit()]
+        h = pynvml.nvmlDeviceGetHandleByIndex(int(vis[device]) if device < len(vis) else device)
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        return True
+    except Exception:
+        return False
+
+
 # ----------------------------------------------------------------------------- GPU arm ---
 def gpu_arm(args, rank, world, local_rank, dist):
     capi = importlib.import_module("3dposeestimation_b200.capi")
     if capi.device_count() < 1:
         raise RuntimeError("bench.py needs a CUDA device: the product has no CPU fallback")
     dev = local_rank
+    bind_to_gpu_numa_node(dev)
     peaks = load_peaks()
     net = capi.Net(named=NET, device=dev)
     net.fill(SEED, 1)
@@ -175,15 +234,16 @@ def gpu_arm(args, rank, world, local_rank, dist):
         if world > 1:
             dist.barrier()
 
+    sampler = ClockSampler(dev); sampler.start()     # up and sampling well before the timed region
     for i in range(args.warmup):
         step_device(i)
     barrier()
     # ---- timed region 1: device-resident inputs (`value`), per-kernel events for the roofline
     net.profile(True); db.profile(True)
-    sampler = ClockSampler(dev); sampler.start()
     timer = capi.Timer(dev)
     launches0 = capi.launch_count()
     barrier()
+    sampler.mark_begin()
     t_wall = time.perf_counter()
     timer.start(net)
     for i in range(args.steps):
@@ -191,6 +251,7 @@ def gpu_arm(args, rank, world, local_rank, dist):
     timer.stop(net)
     ms_dev = timer.elapsed_ms()
     barrier()
+    sampler.mark_end()
     t_wall = (time.perf_counter() - t_wall) * 1e3
     launches = capi.launch_count() - launches0
     clocks = sampler.stop()
@@ -265,7 +326,7 @@ def gpu_arm(args, rank, world, local_rank, dist):
                      "executed_tflops": (720 * 2.0 * 128 * 128 * 16 * BATCH / (conv1_ms * 1e-3) / 1e12) if (fwd_tensor and conv1_ms > 0) else None,
                      "executed_frac": (720 * 2.0 * 128 * 128 * 16 * BATCH / (conv1_ms * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"]) if (fwd_tensor and conv1_ms > 0) else None,
                      "fp32_fma_frac": None if fwd_tensor else achieved_tf / 74.4,
-                     "achieved_hbm_gbs": BATCH * (BYTES_PER_PATCH + 16 * 30 * 32 * 4) / (conv1_ms * 1e-3) / 1e9 if conv1_ms > 0 else 0.0,
+                     "achieved_hbm_gbs": BATCH * (7 * 64 * 64 * 4 + (81920 if fwd_tensor else 16 * 30 * 32 * 4)) / (conv1_ms * 1e-3) / 1e9 if conv1_ms > 0 else 0.0,
                      "hbm_peak_gbs": peaks["hbm_gbs"]},
         "paths": {"forward": "tcgen05" if fwd_tensor else "simt", "knn": "tcgen05" if capi.get_option("knn_tensor") else "simt"},
         "kernels_ms_per_step": {"conv1_pool_act": conv1_ms, "conv2_pool_act": net_ms[1] / max(1, net_calls),

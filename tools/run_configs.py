@@ -1,0 +1,149 @@
+#!/usr/bin/env python
+"""Throughput of the BASELINE.json configurations other than the bench.py headline (configs[1]):
+
+  python tools/run_configs.py --config 1            # manifold.prototxt (C=4, D=3), 15 x 1,300 templates, 9,000 queries, 1-NN
+  python tools/run_configs.py --config 4            # manifold_rgbdnor_16_bin: forward + sign bits + Hamming k-NN vs 1,000,200 codes
+  python tools/run_configs.py --config 5            # rgbdnor_16, 1,000,200 templates, k = 5 + angular-error histogram
+  torchrun --nproc-per-node N tools/run_configs.py --config 3   # 125 x 10,000 templates row-sharded over N GPUs (also 5)
+
+Inputs are the seeded synthetic patches of the bench (device generator), resident in HBM; times are CUDA events on
+the launching stream, max over ranks; one JSON line per configuration on rank 0.  Parity for the same configurations
+is the job of tests/test_gpu_parity.py - this tool only measures."""
+import argparse
+import importlib
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+SEED = 20240607
+BINS = np.array([-1, 0, 10, 20, 40, 180], np.float32)
+
+CONFIGS = {
+    1: dict(net="manifold", c=4, d=3, n_obj=15, poses=1300, q_poses=600, batch=9000, k=1, hamming=False, hist=True),
+    3: dict(net="manifold_rgbdnor_16", c=7, d=16, n_obj=125, poses=10000, q_poses=None, batch=4096, k=1, hamming=False, hist=False),
+    4: dict(net="manifold_rgbdnor_16_bin", c=7, d=128, n_obj=300, poses=3334, q_poses=None, batch=4096, k=5, hamming=True, hist=False),
+    5: dict(net="manifold_rgbdnor_16", c=7, d=16, n_obj=300, poses=3334, q_poses=None, batch=4096, k=5, hamming=False, hist=True),
+}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", type=int, required=True, choices=sorted(CONFIGS))
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=2)
+    a = ap.parse_args()
+    cfg = CONFIGS[a.config]
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    dev = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(dev)
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{dev}"))
+    capi = importlib.import_module("3dposeestimation_b200.capi")
+    shard_rows = importlib.import_module("3dposeestimation_b200.sharding").shard_rows
+    net = capi.Net(named=cfg["net"], device=dev)
+    net.fill(SEED, 1)
+    C, D, B, K = cfg["c"], cfg["d"], cfg["batch"], cfg["k"]
+    T = cfg["n_obj"] * cfg["poses"]
+    lo, hi = shard_rows(rank, world, T)
+    chunk = 4096
+    d_in = capi.DeviceArray((max(B, chunk), 64, 64, C), device=dev)
+    d_db = capi.DeviceArray((hi - lo, D), device=dev)
+    for first in range(lo, hi, chunk):                      # untimed: template descriptors of this rank's rows
+        m = min(chunk, hi - first)
+        net.synth_patches_dev(SEED, first, m, cfg["poses"], d_in)
+        net.compute_descriptors_dev(d_in, m, d_db, out_offset=first - lo)
+    net.sync()
+    labels = capi.synth_labels(SEED, 0, T, cfg["poses"])
+    comm = None
+    if world > 1:
+        uid = [capi.Comm.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        comm = capi.Comm(rank, world, uid[0], dev)
+    if cfg["hamming"]:
+        words = D // 32
+        d_codes = capi.DeviceArray((hi - lo, words), np.uint32, device=dev)
+        net.binarize_dev(d_db, hi - lo, D, d_codes)
+        net.sync()
+        db = capi.TemplateDB(codes=d_codes.to_host(), labels_all=labels, poses_per_object=cfg["poses"], row_offset=lo, t_total=T, device=dev)
+    else:
+        db = capi.TemplateDB(d_desc=d_db, t_local=hi - lo, dim=D, row_offset=lo, t_total=T, labels_all=labels,
+                             poses_per_object=cfg["poses"], device=dev)
+    db.share_stream(net)
+    qp = cfg["q_poses"] or cfg["poses"]
+    net.synth_patches_dev(SEED + 1, rank * B, B, qp, d_in)                       # this rank's query patches
+    q_labels = capi.synth_labels(SEED + 1, rank * B, B, qp) if cfg["hist"] else None
+    nq_all = B * world
+    d_desc = capi.DeviceArray((B, D), device=dev)
+    d_all = capi.DeviceArray((nq_all, D), device=dev) if world > 1 else d_desc
+    d_idx = capi.DeviceArray((nq_all, K), np.int32, device=dev)
+    d_dist = capi.DeviceArray((nq_all, K), np.int32 if cfg["hamming"] else np.float32, device=dev)
+    d_bits = capi.DeviceArray((nq_all, max(1, D // 32)), np.uint32, device=dev) if cfg["hamming"] else None
+
+    def forward():
+        net.compute_descriptors_dev(d_in, B, d_desc)
+        if world > 1:
+            comm.allgather_f32_dev(net, d_desc, B * D, d_all)
+
+    def match():
+        if cfg["hamming"]:
+            net.binarize_dev(d_all, nq_all, D, d_bits)
+            if world > 1:
+                raise SystemExit("config 4 is measured on one GPU (the sharded Hamming entry takes host codes)")
+            db.knn_hamming_dev(d_bits, nq_all, K, d_idx, d_dist)
+        else:
+            db.knn_sharded_dev(comm, d_all, nq_all, K, d_idx, d_dist)
+
+    def timed(fn):
+        for _ in range(a.warmup):
+            fn()
+        net.sync()
+        if world > 1:
+            dist.barrier()
+        t = capi.Timer(dev)
+        t.start(net)
+        for _ in range(a.steps):
+            fn()
+        t.stop(net)
+        ms = t.elapsed_ms() / a.steps
+        if world > 1:
+            import torch
+            tt = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{dev}")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms = float(tt.item())
+        return ms
+
+    ms_f = timed(forward)
+    ms_m = timed(match)
+    ms_both = timed(lambda: (forward(), match()))
+    out = {"config": a.config, "net": cfg["net"], "n_gpus": world, "templates": T, "batch_per_gpu": B, "k": K,
+           "matcher": "hamming" if cfg["hamming"] else "l2", "descriptors_per_s": B * world / (ms_f * 1e-3),
+           "knn_queries_per_s": nq_all / (ms_m * 1e-3), "patches_per_s_forward_plus_knn": B * world / (ms_both * 1e-3),
+           "ms_forward": ms_f, "ms_knn": ms_m, "ms_step": ms_both,
+           "paths": {"forward": "tcgen05" if capi.get_option("forward_tensor") else "simt",
+                     "knn": "simt xor+popc" if cfg["hamming"] else ("tcgen05" if capi.get_option("knn_tensor") and D <= 16 and K <= 5 else "simt")}}
+    if cfg["hist"] and world == 1:
+        rot_inv = np.zeros(cfg["n_obj"], np.int32)
+        d_ql = capi.DeviceArray.from_host(q_labels, device=dev)
+        t = capi.Timer(dev)
+        t.start(net)
+        h = db.histogram_dev(d_idx, d_ql, nq_all, K, rot_inv, BINS)
+        t.stop(net)
+        out["ms_histogram"] = t.elapsed_ms()
+        out["histogram"] = [float(x) for x in h]
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
