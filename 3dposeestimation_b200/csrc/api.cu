@@ -683,6 +683,8 @@ int pe_db_create_hamming(const uint32_t* codes, int64_t t_local, int words_per_c
         pe_db_destroy(db);
         return PE_ERR_CUDA;
     }
+    const int st = knn_tc_prepare(db);      /* +-1 tensor tiles of the codes (32 / 64 / 128 bit) */
+    if (st != PE_OK) { pe_db_destroy(db); return st; }
     *out = db;
     return PE_OK;
 }

@@ -195,10 +195,12 @@ int knn_merge_i32(pe_db* db, const int* d_cd, const int* d_ci, long long stride_
 int knn_tc_prepare(pe_db* db);
 bool knn_tc_usable(const pe_db* db, int k);
 void knn_tc_plan(const pe_db* db, int64_t nq, int k, int* n_chunks, int* kc, int* tiles_per_chunk);
-int knn_tc_scan(pe_db* db, const float* d_q, int64_t nq, int k, int n_chunks, int kc, int tiles_per_chunk,
+int knn_tc_scan(pe_db* db, const void* d_q, int64_t nq, int k, int n_lists, int kc, int tiles_per_chunk,
                 float* cand_d, int* cand_i);
 int knn_tc_select(pe_db* db, const float* cand_d, const int* cand_i, int n_chunks, int kc, const float* d_q,
                   int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist);
+int knn_tc_select_hamming(pe_db* db, const float* cand_d, const int* cand_i, int n_lists, int kc, const uint32_t* d_q,
+                          int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist);
 int knn_tc_check(pe_db* db);
 /* runtime switches (pe_set_option): tensor-core paths on/off */
 extern std::atomic<int> g_opt_knn_tensor, g_opt_forward_tensor;

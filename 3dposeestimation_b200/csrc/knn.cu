@@ -461,7 +461,10 @@ int knn_hamming_local(pe_db* db, const uint32_t* d_qcodes, int64_t nq, int k, in
     PE_REQUIRE(nq >= 0 && nq < (1LL << 31) / 16, "nq out of range");
     PE_CUDA(cudaSetDevice(db->device));
     if (nq == 0) return PE_OK;
-    const ScanGeom g = plan_scan(db, nq, k, true);
+    ScanGeom g = plan_scan(db, nq, k, true);
+    const bool tensor = g_opt_knn_tensor.load() != 0 && knn_tc_usable(db, k);
+    int tc_tiles_per_chunk = 0;
+    if (tensor) knn_tc_plan(db, nq, k, &g.n_chunks, &g.kc, &tc_tiles_per_chunk);
     const size_t n_cand = (size_t)nq * g.n_chunks * g.kc;
     PE_CHECK(db->cand_d.reserve(n_cand * sizeof(int)));
     PE_CHECK(db->cand_i.reserve(n_cand * sizeof(int)));
@@ -469,6 +472,14 @@ int knn_hamming_local(pe_db* db, const uint32_t* d_qcodes, int64_t nq, int k, in
     int* ci = db->cand_i.as<int>();
     int st = PE_ERR_UNSUPPORTED;
     PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
+    if (tensor) {
+        /* -dot of the +-1 expansions on the tensor pipe (exact integers in fp32), 32-code candidate blocks */
+        PE_CHECK(knn_tc_scan(db, d_qcodes, nq, k, g.n_chunks, g.kc, tc_tiles_per_chunk, db->cand_d.as<float>(), ci));
+        PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
+        PE_CHECK(knn_tc_select_hamming(db, db->cand_d.as<float>(), ci, g.n_chunks, g.kc, d_qcodes, nq, k, d_out_idx, d_out_dist));
+        PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
+        return PE_OK;
+    }
     if (db->t_local > 0) {
 #define HAM_CASE(WV, RQV) if (db->words == WV && g.rq == RQV) st = launch_ham_scan<WV, RQV>(db, g, d_qcodes, (int)nq, cd, ci)
         HAM_CASE(1, 1); HAM_CASE(1, 4); HAM_CASE(1, 8);

@@ -50,12 +50,18 @@ constexpr int kTcStages = 8;
 constexpr int kTcThreads = 608;               /* producer warp, 2 MMA warps, 2 x 2 x 4 epilogue warps */
 constexpr int kTcListCols = 512;              /* one list column per epilogue thread */
 constexpr int kAOpBytes = 10240;             /* per query tile: hi 4096 | lo 4096 | a_n 2048 */
-constexpr int kSmemA = 0;                                  /* 2 query tiles */
-constexpr int kSmemZero = kSmemA + 2 * kAOpBytes;          /* 2048 zero bytes: second K chunk of A_n */
-constexpr int kSmemB = kSmemZero + 2048;
-constexpr int kSmemList = kSmemB + kTcStages * kTcTileBytes;      /* [7][512] floats + [7][512] ints     */
-constexpr int kSmemBar = kSmemList + 2 * 7 * kTcListCols * 4;
-constexpr int kSmemTotal = kSmemBar + 512;
+constexpr int kHamBytes = 16384;             /* Hamming: per tile up to 4 K-steps of [2 chunks][128 rows][16 x e4m3] */
+/* shared-memory layout; MODE 0 = L2 (split fp16), MODE 1 = Hamming (+-1 as e4m3) */
+template <int MODE> struct TcLayout {
+    static constexpr int a_bytes = MODE ? kHamBytes : kAOpBytes;            /* one query tile */
+    static constexpr int stage_bytes = MODE ? kHamBytes : kTcTileBytes;     /* one template tile */
+    static constexpr int off_a = 0;                                          /* 2 query tiles */
+    static constexpr int off_zero = 2 * a_bytes;                             /* L2: 2048 zero bytes, second K chunk of A_n */
+    static constexpr int off_b = off_zero + (MODE ? 0 : 2048);
+    static constexpr int off_list = off_b + kTcStages * stage_bytes;         /* [7][512] floats + [7][512] ints */
+    static constexpr int off_bar = off_list + 2 * 7 * kTcListCols * 4;
+    static constexpr int total = off_bar + 512;
+};
 
 /* monotone float <-> int map so that atomicMin on ints orders floats (negative values included) */
 __device__ __forceinline__ int f2ord(float f) {
@@ -175,10 +181,42 @@ __global__ void tc_pack_db_kernel(const float* __restrict__ desc, int ld, long l
     base[384 + i] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
 }
 
+/* 16 code bits -> 16 e4m3 bytes: byte i = base with its sign flipped when bit i is set (base 0xB8.. = -1: bit -> +-1;
+ * base 0x38.. = +1: bit -> -(+-1)) */
+__device__ __forceinline__ uint4 tc_expand16(uint32_t bits, uint32_t base) {
+    uint32_t w[4];
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+        const uint32_t nib = (bits >> (4 * n)) & 0xFu;
+        w[n] = base ^ (((nib * 0x00204081u) & 0x01010101u) << 7);
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+/* codes: [t][words] u32.  out tile j (128 rows): [2 * words chunks][128 rows][16 bytes].  Rows past t_local repeat the
+ * last real row, so the minimum of a partly filled block is that of its real rows; blocks with no real row are
+ * skipped by the scan (n_blocks). */
+__global__ void tc_pack_codes_kernel(const uint32_t* __restrict__ codes, int words, long long t_local, uint4* __restrict__ out) {
+    const long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long tiles = (t_local + kTcRows - 1) / kTcRows;
+    if (r >= tiles * kTcRows) return;
+    const long long tile = r / kTcRows;
+    const int i = (int)(r - tile * kTcRows);
+    const long long src = r < t_local ? r : t_local - 1;
+    uint4* base = out + tile * ((size_t)words * 4096 / 16);
+    for (int w = 0; w < words; ++w) {
+        const uint32_t code = codes[src * words + w];
+        base[(2 * w) * 128 + i] = tc_expand16(code & 0xFFFFu, 0xB8B8B8B8u);
+        base[(2 * w + 1) * 128 + i] = tc_expand16(code >> 16, 0xB8B8B8B8u);
+    }
+}
+
 /* ------------------------------------------------------------------- scan ---- */
 struct TcArgs {
-    const float* q;            /* [nq][q_ld], q_ld = 4 or 16 (zero padded) */
-    int nq, q_ld;
+    const float* q;            /* L2: [nq][q_ld], q_ld = 4 or 16 (zero padded) */
+    const uint32_t* qcodes;    /* Hamming: [nq][words] */
+    int nq, q_ld, words;
+    int n_blocks;              /* 32-template blocks that hold at least one real row */
     const uint4* db;           /* packed tiles */
     long long t_local, row_offset;
     int tiles_total, tiles_per_chunk, n_chunks, n_qpairs;
@@ -220,10 +258,11 @@ __device__ __forceinline__ float tc_min32(const uint32_t (&v)[32]) {
     return fminf(fmin3(u0, u1, u2), u3);
 }
 
-template <int KC, bool DBG>
+template <int KC, bool DBG, int MODE>
 __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemBar);
+    using L = TcLayout<MODE>;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::off_bar);
     uint64_t* full = bars;                     /* [kTcStages] tile landed */
     uint64_t* empty = bars + kTcStages;        /* [kTcStages] tile consumed by the MMAs of both query tiles */
     uint64_t* tfull = bars + 2 * kTcStages;    /* [4] accumulator ready */
@@ -233,11 +272,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(item_done + 1);
     volatile int* s_abort = reinterpret_cast<volatile int*>(tmem_slot + 1);
     float* s_red = reinterpret_cast<float*>(tmem_slot + 2);   /* [8] query abs-max per operand warp */
-    float* s_ld = reinterpret_cast<float*>(smem + kSmemList);           /* [KC][512] candidate keys   */
+    float* s_ld = reinterpret_cast<float*>(smem + L::off_list);           /* [KC][512] candidate keys   */
     int* s_li = reinterpret_cast<int*>(s_ld + KC * kTcListCols);        /* [KC][512] candidate blocks */
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    for (int i = tid; i < 2048 / 16; i += kTcThreads) reinterpret_cast<uint4*>(smem + kSmemZero)[i] = make_uint4(0, 0, 0, 0);
+    if (MODE == 0)
+        for (int i = tid; i < 2048 / 16; i += kTcThreads) reinterpret_cast<uint4*>(smem + L::off_zero)[i] = make_uint4(0, 0, 0, 0);
     if (tid == 0) {
         for (int s = 0; s < kTcStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         for (int b = 0; b < 4; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4); }
@@ -258,6 +298,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
         /* ================= producer ================= */
         if (lane == 0) {
             uint32_t g = 0;
+            const uint32_t tile_bytes = MODE ? (uint32_t)a.words * 4096u : (uint32_t)kTcTileBytes;
             for (int item = blockIdx.x; item < n_items && !*s_abort; item += gridDim.x) {
                 const int chunk = item / a.n_qpairs;
                 const int t0 = chunk * a.tiles_per_chunk;
@@ -265,8 +306,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                 for (int t = t0; t < t1; ++t, ++g) {
                     const int s = g % kTcStages;
                     if (!mbar_wait(&empty[s], ((g / kTcStages) & 1) ^ 1)) { atomicExch(a.err, 1); *s_abort = 1; break; }
-                    mbar_expect_tx(&full[s], kTcTileBytes);
-                    bulk_g2s(smem + kSmemB + s * kTcTileBytes, a.db + (size_t)t * (kTcTileBytes / 16), kTcTileBytes, &full[s]);
+                    mbar_expect_tx(&full[s], tile_bytes);
+                    bulk_g2s(smem + L::off_b + s * L::stage_bytes, a.db + (size_t)t * (tile_bytes / 16), tile_bytes, &full[s]);
                 }
             }
         }
@@ -277,14 +318,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
         {
             const int set = warp - 1;
             const uint32_t idesc = instr_desc(128, 128, FMT_F16, FMT_F16);
-            const uint32_t sB = smem_u32(smem + kSmemB), sZ = smem_u32(smem + kSmemZero);
-            const uint32_t a0 = smem_u32(smem + kSmemA), a1 = a0 + kAOpBytes;
+            const uint32_t sB = smem_u32(smem + L::off_b), sZ = smem_u32(smem + L::off_zero);
+            const uint32_t a0 = smem_u32(smem + L::off_a), a1 = a0 + L::a_bytes;
+            /* L2: hi | lo | norm terms of a tile.  Hamming: K step j of a tile is the two 16-byte chunks at j * 4096 */
             const uint64_t a0_hi = smem_desc(a0, 2048, 128), a0_lo = smem_desc(a0 + 4096, 2048, 128);
-            const uint64_t a0_n = smem_desc(a0 + 8192, sZ - (a0 + 8192), 128);
+            const uint64_t a0_n = smem_desc(a0 + 8192, MODE ? 2048 : sZ - (a0 + 8192), 128);
             const uint64_t a1_hi = smem_desc(a1, 2048, 128), a1_lo = smem_desc(a1 + 4096, 2048, 128);
-            const uint64_t a1_n = smem_desc(a1 + 8192, sZ - (a1 + 8192), 128);
+            const uint64_t a1_n = smem_desc(a1 + 8192, MODE ? 2048 : sZ - (a1 + 8192), 128);
             const uint64_t b_hi0 = smem_desc(sB, 2048, 128), b_lo0 = smem_desc(sB + 4096, 2048, 128);
-            const uint64_t b_n0 = smem_desc(sB + 8192, 0, 128);   /* chunk 1 aliases chunk 0: A_n's chunk 1 is zero */
+            const uint64_t b_n0 = smem_desc(sB + 8192, MODE ? 2048 : 0, 128);   /* L2: chunk 1 aliases chunk 0, A_n's chunk 1 is zero */
             const uint32_t d0 = tmem + (set * 2) * 128, d1 = d0 + 128;
             uint64_t* const tf0 = &tfull[set * 2], * const te0 = &tempty[set * 2];
             uint32_t g = 0, it = 0;
@@ -308,17 +350,24 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                     if (!mbar_wait(&full[s], (gi / kTcStages) & 1u)) { if (lane == 0) atomicExch(a.err, 3); ok = false; break; }
                     fence_after_sync();
                     TC_DBG_ADD(0, tm);
-                    const uint32_t off = s * (kTcTileBytes >> 4);
+                    const uint32_t off = s * (L::stage_bytes >> 4);
                     if (elect_one()) {
-                        mma_f16(d0, a0_hi, b_hi0 + off, idesc, 0);
-                        mma_f16(d0, a0_hi, b_lo0 + off, idesc, 1);
-                        mma_f16(d0, a0_lo, b_hi0 + off, idesc, 1);
-                        mma_f16(d0, a0_n, b_n0 + off, idesc, 1);
-                        mma_commit(tf0);
-                        mma_f16(d1, a1_hi, b_hi0 + off, idesc, 0);
-                        mma_f16(d1, a1_hi, b_lo0 + off, idesc, 1);
-                        mma_f16(d1, a1_lo, b_hi0 + off, idesc, 1);
-                        mma_f16(d1, a1_n, b_n0 + off, idesc, 1);
+                        if (MODE == 0) {
+                            mma_f16(d0, a0_hi, b_hi0 + off, idesc, 0);
+                            mma_f16(d0, a0_hi, b_lo0 + off, idesc, 1);
+                            mma_f16(d0, a0_lo, b_hi0 + off, idesc, 1);
+                            mma_f16(d0, a0_n, b_n0 + off, idesc, 1);
+                            mma_commit(tf0);
+                            mma_f16(d1, a1_hi, b_hi0 + off, idesc, 0);
+                            mma_f16(d1, a1_hi, b_lo0 + off, idesc, 1);
+                            mma_f16(d1, a1_lo, b_hi0 + off, idesc, 1);
+                            mma_f16(d1, a1_n, b_n0 + off, idesc, 1);
+                        } else {
+                            /* -dot of the +-1 expansions, 32 bits per MMA: R = 2 * hamming - bits */
+                            for (int j = 0; j < a.words; ++j) mma_f8(d0, a0_hi + j * 256, b_hi0 + off + j * 256, idesc, j > 0);
+                            mma_commit(tf0);
+                            for (int j = 0; j < a.words; ++j) mma_f8(d1, a1_hi + j * 256, b_hi0 + off + j * 256, idesc, j > 0);
+                        }
                         mma_commit(tf0 + 1);
                         mma_commit(&empty[s]);
                     }
@@ -363,7 +412,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
             const int t1 = min(t0 + a.tiles_per_chunk, a.tiles_total);
             const int qidx = (qpair * 2 + qt) * kTcRows + row;
             const bool q_ok = qidx < a.nq;
-            if (set == 0) {
+            if (set == 0 && MODE == 0) {
                 /* ---- query operands (256 threads): centre, scale, split, store in the K-major core-matrix layout */
                 float qv[16];
                 float m = 0.f;
@@ -397,7 +446,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                     hi[d / 2] = pack_h2(h0, h1);
                     lo[d / 2] = pack_h2(l0, l1);
                 }
-                uint4* op = reinterpret_cast<uint4*>(smem + kSmemA + qt * kAOpBytes);
+                uint4* op = reinterpret_cast<uint4*>(smem + L::off_a + qt * L::a_bytes);
                 op[0 + row] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
                 op[128 + row] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
                 op[256 + row] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
@@ -406,6 +455,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                 fence_async_smem();
                 mbar_arrive(a_ready);
                 asm volatile("bar.sync 1, 256;" ::: "memory");   /* s_red may be rewritten by the next item */
+            }
+            if (set == 0 && MODE == 1) {
+                /* ---- query operands, Hamming: bit b of the code -> -(+-1) as e4m3 (0x38 = +1, 0xB8 = -1), 16 bits per
+                 * 16-byte core-matrix row, K chunk c = bits 16c .. 16c+15 */
+                uint4* op = reinterpret_cast<uint4*>(smem + L::off_a + qt * L::a_bytes);
+                for (int w = 0; w < a.words; ++w) {
+                    const uint32_t code = q_ok ? __ldg(a.qcodes + (size_t)qidx * a.words + w) : 0u;
+                    op[(2 * w) * 128 + row] = tc_expand16(code & 0xFFFFu, 0x38383838u);
+                    op[(2 * w + 1) * 128 + row] = tc_expand16(code >> 16, 0x38383838u);
+                }
+                fence_async_smem();
+                mbar_arrive(a_ready);
             }
             /* the k+2 best blocks of this thread's tiles: in registers for k = 1, in shared memory otherwise */
             float rk[KC <= 3 ? KC : 1];
@@ -466,7 +527,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             const float mj = j == 0 ? m0 : (j == 1 ? m1 : (j == 2 ? m2 : m3));
-                            if (mj < th) {
+                            if (mj < th && blk0 + j < a.n_blocks) {
                                 if (KC <= 3) {
                                     /* sorted insert, strict '>' keeps the earlier block first among equals */
 #pragma unroll
@@ -600,12 +661,103 @@ knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ c
     }
 }
 
+/* Hamming twin of knn_tc_select_kernel: exact XOR + POPC distance over the 32 codes of each of the best blocks.  With
+ * integer keys the block order (key, id) is exact, and a block holding one of the k nearest (ties -> lower row) is
+ * preceded by at most k - 1 others, so the first 8 blocks contain the answer for k <= 5. */
+__global__ void __launch_bounds__(32)
+knn_tc_select_hamming_kernel(const float* __restrict__ cand_d, const int* __restrict__ cand_i, int n_cand,
+                             const uint32_t* __restrict__ q, const uint32_t* __restrict__ codes, int words, long long t_local,
+                             long long row_offset, int k, int* __restrict__ out_idx, int* __restrict__ out_dist) {
+    extern __shared__ __align__(16) float sel_smem[];
+    float* sd = sel_smem;                                   /* [n_cand] keys */
+    int* si = reinterpret_cast<int*>(sd + n_cand);          /* [n_cand] block ids */
+    int* ed = si + n_cand;                                  /* [kTcSelBlocks * 32] exact distances */
+    int* ei = ed + kTcSelBlocks * kTcBlock;
+    const int lane = threadIdx.x;
+    const long long qi = blockIdx.x;
+    uint32_t qc[8];
+    for (int w = 0; w < words; ++w) qc[w] = q[(size_t)qi * words + w];
+    for (int c = lane; c < n_cand; c += 32) {
+        const int blk = cand_i[(size_t)qi * n_cand + c];
+        sd[c] = blk >= 0 ? cand_d[(size_t)qi * n_cand + c] : INFINITY;
+        si[c] = blk >= 0 ? blk : INT_MAX;
+    }
+    __syncwarp();
+    for (int r = 0; r < kTcSelBlocks; ++r) {
+        float bd = INFINITY;
+        int bi = INT_MAX, bc = -1;
+        for (int c = lane; c < n_cand; c += 32) {
+            const float d = sd[c];
+            const int i = si[c];
+            if (i != INT_MAX && (bc < 0 || d < bd || (d == bd && i < bi))) { bd = d; bi = i; bc = c; }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, bd, off);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+            const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
+            if (oc >= 0 && (bc < 0 || od < bd || (od == bd && oi < bi))) { bd = od; bi = oi; bc = oc; }
+        }
+        int d = INT_MAX, idx = INT_MAX;
+        if (bc >= 0) {
+            const long long row = (long long)bi * kTcBlock + lane;
+            if (row < t_local) {
+                d = 0;
+                for (int w = 0; w < words; ++w) d += __popc(qc[w] ^ __ldg(codes + (size_t)row * words + w));
+                idx = (int)row;
+            }
+        }
+        ed[r * kTcBlock + lane] = d;
+        ei[r * kTcBlock + lane] = idx;
+        __syncwarp();
+        if (lane == 0 && bc >= 0) si[bc] = INT_MAX;
+        __syncwarp();
+    }
+    for (int r = 0; r < k; ++r) {
+        int bd = INT_MAX, bi = INT_MAX, bc = -1;
+#pragma unroll
+        for (int c = lane; c < kTcSelBlocks * kTcBlock; c += 32) {
+            const int d = ed[c], i = ei[c];
+            if (i != INT_MAX && (bc < 0 || d < bd || (d == bd && i < bi))) { bd = d; bi = i; bc = c; }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const int od = __shfl_xor_sync(0xffffffffu, bd, off);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+            const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
+            if (oc >= 0 && (bc < 0 || od < bd || (od == bd && oi < bi))) { bd = od; bi = oi; bc = oc; }
+        }
+        if (lane == 0) {
+            out_idx[(size_t)qi * k + r] = bc >= 0 ? (int)(bi + row_offset) : -1;
+            out_dist[(size_t)qi * k + r] = bc >= 0 ? bd : INT_MAX;
+            if (bc >= 0) ei[bc] = INT_MAX;
+        }
+        __syncwarp();
+    }
+}
+
 }  // namespace
 
 /* packs the (already padded, normed) fp32 DB of `db` into tensor tiles; called once per DB */
 int knn_tc_prepare(pe_db* db) {
     db->tc_ready = false;
-    if (db->hamming || (db->dim_pad != 16 && db->dim_pad != 4) || db->t_local <= 0) return PE_OK;
+    if (db->t_local <= 0) return PE_OK;
+    if (db->hamming) {
+        /* +-1 (e4m3) tiles of the packed codes: 32, 64 or 128 bits -> 1, 2 or 4 K steps of 32 */
+        if (db->words != 1 && db->words != 2 && db->words != 4) return PE_OK;
+        PE_CUDA(cudaSetDevice(db->device));
+        const long long tiles = (db->t_local + kTcRows - 1) / kTcRows;
+        PE_CUDA(cudaMalloc(&db->d_tc, (size_t)tiles * db->words * 4096));
+        tc_pack_codes_kernel<<<(unsigned)((tiles * kTcRows + 255) / 256), 256, 0, db->stream>>>(
+            db->d_codes, db->words, db->t_local, reinterpret_cast<uint4*>(db->d_tc));
+        PE_LAUNCHED();
+        PE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&db->d_tc_err), sizeof(int), cudaHostAllocMapped));
+        *db->d_tc_err = 0;
+        PE_CUDA(cudaStreamSynchronize(db->stream));
+        db->tc_ready = true;
+        return PE_OK;
+    }
+    if ((db->dim_pad != 16 && db->dim_pad != 4)) return PE_OK;
     PE_CUDA(cudaSetDevice(db->device));
     const int ld = db->dim_pad;
     void* d_tmp = nullptr;
@@ -652,6 +804,7 @@ int knn_tc_prepare(pe_db* db) {
 
 bool knn_tc_usable(const pe_db* db, int k) { return db->tc_ready && k + 2 <= 7; }
 
+
 /* plans the chunking; returns the number of candidate lists per query (two per chunk: even and odd tiles) and kc */
 void knn_tc_plan(const pe_db* db, int64_t nq, int k, int* n_lists, int* kc, int* tiles_per_chunk) {
     const int n_qpairs = (int)((nq + 2 * kTcRows - 1) / (2 * kTcRows));
@@ -665,14 +818,17 @@ void knn_tc_plan(const pe_db* db, int64_t nq, int k, int* n_lists, int* kc, int*
     *kc = k <= 1 ? 3 : 7;
 }
 
-int knn_tc_scan(pe_db* db, const float* d_q, int64_t nq, int k, int n_lists, int kc, int tiles_per_chunk,
+int knn_tc_scan(pe_db* db, const void* d_q, int64_t nq, int k, int n_lists, int kc, int tiles_per_chunk,
                 float* cand_d, int* cand_i) {
     PE_CHECK(db->tau.reserve((size_t)nq * sizeof(int)));
     PE_CUDA(cudaMemsetAsync(db->tau.p, 0x7f, (size_t)nq * sizeof(int), db->stream));
     TcArgs a;
-    a.q = d_q;
+    a.q = db->hamming ? nullptr : static_cast<const float*>(d_q);
+    a.qcodes = db->hamming ? static_cast<const uint32_t*>(d_q) : nullptr;
     a.nq = (int)nq;
     a.q_ld = db->dim_pad;
+    a.words = db->words;
+    a.n_blocks = (int)((db->t_local + kTcBlock - 1) / kTcBlock);
     a.db = reinterpret_cast<const uint4*>(db->d_tc);
     a.t_local = db->t_local;
     a.row_offset = db->row_offset;
@@ -690,21 +846,23 @@ int knn_tc_scan(pe_db* db, const float* d_q, int64_t nq, int k, int n_lists, int
     a.dbg = nullptr;
     static const bool dbg_on = getenv("PE_TC_DEBUG") != nullptr;
     unsigned long long* d_dbg = nullptr;
-    if (dbg_on) {
+    if (dbg_on && !db->hamming) {
         PE_CUDA(cudaMalloc(&d_dbg, 16 * sizeof(unsigned long long)));
         PE_CUDA(cudaMemsetAsync(d_dbg, 0, 16 * sizeof(unsigned long long), db->stream));
         a.dbg = d_dbg;
     }
     const int items = a.n_chunks * a.n_qpairs;
     const int grid = items < db->num_sms ? items : db->num_sms;
-#define TC_LAUNCH(KCV, DBGV) do { \
-        PE_CUDA(cudaFuncSetAttribute(knn_tc_scan_kernel<KCV, DBGV>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal)); \
-        knn_tc_scan_kernel<KCV, DBGV><<<grid, kTcThreads, kSmemTotal, db->stream>>>(a); } while (0)
-    if (kc == 3) { if (dbg_on) TC_LAUNCH(3, true); else TC_LAUNCH(3, false); }
-    else { if (dbg_on) TC_LAUNCH(7, true); else TC_LAUNCH(7, false); }
+#define TC_LAUNCH(KCV, DBGV, MODEV) do { \
+        PE_CUDA(cudaFuncSetAttribute(knn_tc_scan_kernel<KCV, DBGV, MODEV>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcLayout<MODEV>::total)); \
+        knn_tc_scan_kernel<KCV, DBGV, MODEV><<<grid, kTcThreads, TcLayout<MODEV>::total, db->stream>>>(a); } while (0)
+    if (db->hamming) {
+        if (kc == 3) TC_LAUNCH(3, false, 1); else TC_LAUNCH(7, false, 1);
+    } else if (kc == 3) { if (dbg_on) TC_LAUNCH(3, true, 0); else TC_LAUNCH(3, false, 0); }
+    else { if (dbg_on) TC_LAUNCH(7, true, 0); else TC_LAUNCH(7, false, 0); }
 #undef TC_LAUNCH
     PE_LAUNCHED();
-    if (dbg_on) {
+    if (dbg_on && !db->hamming) {
         unsigned long long h[16];
         PE_CUDA(cudaMemcpyAsync(h, d_dbg, sizeof(h), cudaMemcpyDeviceToHost, db->stream));
         PE_CUDA(cudaStreamSynchronize(db->stream));
@@ -726,6 +884,18 @@ int knn_tc_select(pe_db* db, const float* cand_d, const int* cand_i, int n_lists
     PE_CUDA(cudaFuncSetAttribute(knn_tc_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     knn_tc_select_kernel<<<(unsigned)nq, 32, smem, db->stream>>>(cand_d, cand_i, n_cand, d_q, db->d_desc, db->dim_pad,
                                                                 db->t_local, db->row_offset, k, d_out_idx, d_out_dist);
+    PE_LAUNCHED();
+    return PE_OK;
+}
+
+int knn_tc_select_hamming(pe_db* db, const float* cand_d, const int* cand_i, int n_lists, int kc, const uint32_t* d_q,
+                          int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist) {
+    const int n_cand = n_lists * kc;
+    const size_t smem = (size_t)(2 * n_cand + 2 * kTcSelBlocks * kTcBlock) * 4;
+    PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
+    PE_CUDA(cudaFuncSetAttribute(knn_tc_select_hamming_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    knn_tc_select_hamming_kernel<<<(unsigned)nq, 32, smem, db->stream>>>(cand_d, cand_i, n_cand, d_q, db->d_codes, db->words,
+                                                                        db->t_local, db->row_offset, k, d_out_idx, d_out_dist);
     PE_LAUNCHED();
     return PE_OK;
 }

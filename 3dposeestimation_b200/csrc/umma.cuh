@@ -86,7 +86,6 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 /* -------------------------------------------------------------------- MMA --- */
-/* D[tmem] (+)= A[smem] * B[smem]; one thread issues for the CTA */
 /* one lane of a converged warp (elect.sync).  Issue tcgen05.mma / commit as
  *     if (elect_one()) { mma_f16(...); ... }  __syncwarp();
  * from code the WHOLE warp executes: the operands are then warp-uniform values (uniform registers) and ptxas emits a
@@ -102,10 +101,19 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+/* D[tmem] (+)= A[smem] * B[smem]; one thread issues for the CTA */
 __device__ __forceinline__ void mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+/* kind::f8f6f4 with 8-bit operands (E4M3 = format code 0, the same instruction-descriptor bits as FMT_F16): K = 32 per
+ * instruction, a core-matrix row is 16 bytes = 16 elements */
+__device__ __forceinline__ void mma_f8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {

@@ -203,7 +203,7 @@ def test_knn_l2_clustered_descriptors(gpu, po, knn_path):
     assert check_knn(idx, dist, oi, od, gap) < 0.05
 
 
-def test_knn_hamming_matches_oracle_and_golden(gpu, po, synth, golden):
+def test_knn_hamming_matches_oracle_and_golden(gpu, po, synth, golden, knn_path):
     codes_t = (synth.uniform01(synth.BASE_SEED, 50, 512 * 4) * 2 ** 24).astype(np.uint32).reshape(512, 4)
     codes_t = codes_t * np.uint32(257) ^ (codes_t >> np.uint32(3))
     codes_q = codes_t[(np.arange(64) * 5) % 512] ^ (np.uint32(1) << (np.arange(64, dtype=np.uint32) % 32))[:, None]
@@ -212,7 +212,8 @@ def test_knn_hamming_matches_oracle_and_golden(gpu, po, synth, golden):
     oi, od = po.knn_hamming(codes_q, codes_t, 5)
     assert np.array_equal(idx, oi) and np.array_equal(dist, od)
     rng = np.random.default_rng(2)
-    for words, nq, nt, k in ((4, 1100, 30000, 5), (1, 300, 5000, 3), (2, 64, 999, 1), (8, 100, 3000, 4), (4, 5, 3, 4)):
+    for words, nq, nt, k in ((4, 1100, 30000, 5), (1, 300, 5000, 3), (2, 64, 999, 1), (8, 100, 3000, 4), (4, 5, 3, 4), (4, 700, 40001, 2),
+                             (1, 513, 70000, 5)):
         t = rng.integers(0, 2 ** 32, (nt, words), dtype=np.uint64).astype(np.uint32)
         if words == 1:
             t &= np.uint32(0xFFFF)        # 16-bit codes: many equal distances, ties -> lower index
@@ -403,7 +404,7 @@ def test_full_size_db_properties(gpu, synth, knn_path):
     assert np.array_equal(merged, idx5[:512])
 
 
-def test_full_size_hamming_properties(gpu):
+def test_full_size_hamming_properties(gpu, knn_path):
     rng = np.random.default_rng(22)
     nt, nq = 1_000_200, 2048
     t = rng.integers(0, 2 ** 32, (nt, 4), dtype=np.uint64).astype(np.uint32)

@@ -128,7 +128,8 @@ def main():
            "knn_queries_per_s": nq_all / (ms_m * 1e-3), "patches_per_s_forward_plus_knn": B * world / (ms_both * 1e-3),
            "ms_forward": ms_f, "ms_knn": ms_m, "ms_step": ms_both,
            "paths": {"forward": "tcgen05" if capi.get_option("forward_tensor") else "simt",
-                     "knn": "simt xor+popc" if cfg["hamming"] else ("tcgen05" if capi.get_option("knn_tensor") and D <= 16 and K <= 5 else "simt")}}
+                     "knn": ("tcgen05 +-1 e4m3" if capi.get_option("knn_tensor") and D <= 128 and K <= 5 else "simt xor+popc") if cfg["hamming"]
+                     else ("tcgen05" if capi.get_option("knn_tensor") and D <= 16 and K <= 5 else "simt")}}
     if cfg["hist"] and world == 1:
         rot_inv = np.zeros(cfg["n_obj"], np.int32)
         d_ql = capi.DeviceArray.from_host(q_labels, device=dev)
