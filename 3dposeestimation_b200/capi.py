@@ -110,6 +110,12 @@ SIGNATURES = {
     "pe_match_patches": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_int, C.c_int, vp, vp, vp]),
     "pe_knn_sharded_dev": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
     "pe_knn_hamming_sharded": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "pe_depth2normals": (C.c_int, [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, vp]),
+    "pe_depth2normals_dev": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, vp]),
+    "pe_sample_patches": (C.c_int, [C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int64, C.c_float, C.c_float,
+                                    C.c_float, vp, vp]),
+    "pe_sample_patches_dev": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int64, C.c_float,
+                                        C.c_float, C.c_float, vp, vp]),
 }
 
 
@@ -502,6 +508,40 @@ class TemplateDB:
         intra, inter = C.c_float(), C.c_float()
         check(lib().pe_knn_accuracy(self.h, _ptr(m), _ptr(b), m.size, nr_query_poses, C.byref(intra), C.byref(inter)))
         return intra.value, inter.value
+
+
+# ------------------------------------------------------------------ patch extraction ---
+def depth2normals(depth, fx, fy, ox=0.0, oy=0.0, device=0):
+    """depth2normals (src/helper.cpp:53-103) on [n_frames, rows, cols] (or [rows, cols]) f32 depth -> normals [..., 3]"""
+    d = _f32(depth)
+    d3 = d.reshape((-1,) + d.shape[-2:])
+    out = np.empty(d3.shape + (3,), np.float32)
+    check(lib().pe_depth2normals(device, _ptr(d3), d3.shape[0], d3.shape[1], d3.shape[2], fx, fy, ox, oy, _ptr(out)))
+    return out.reshape(d.shape + (3,))
+
+
+def sample_patches(color, depth, centers_xy, z, fx, fy, m=0.2, normals=None, frame_of=None, device=0):
+    """samplePatchWithScale (src/datasetmanager.cpp:299-346) for n patches from host frames:
+    color [F, rows, cols, 3] u8, depth [F, rows, cols] f32 -> (patches [n, 64, 64, 7] f32, status [n])"""
+    col = np.ascontiguousarray(color, np.uint8)
+    dep = _f32(depth)
+    ctr, zz = _i32(centers_xy).reshape(-1, 2), _f32(z).reshape(-1)
+    nor = None if normals is None else _f32(normals)
+    fr = None if frame_of is None else _i32(frame_of)
+    n = ctr.shape[0]
+    out = np.empty((n, 64, 64, 7), np.float32)
+    status = np.empty(n, np.int32)
+    check(lib().pe_sample_patches(device, _ptr(col), _ptr(dep), _ptr(nor), dep.shape[0], dep.shape[1], dep.shape[2], _ptr(fr),
+                                  _ptr(ctr), _ptr(zz), n, fx, fy, m, _ptr(out), _ptr(status)))
+    return out, status
+
+
+def sample_patches_dev(net, d_color, d_depth, d_normals, n_frames, rows, cols, d_frame_of, d_centers, d_z, n, fx, fy, m, d_out,
+                       d_status=None, device=0):
+    """device-resident variant on the net's stream: the output feeds Net.compute_descriptors_dev directly"""
+    p = lambda a: None if a is None else a.ptr
+    check(lib().pe_sample_patches_dev(net.h if net is not None else None, device, p(d_color), p(d_depth), p(d_normals), n_frames, rows,
+                                      cols, p(d_frame_of), p(d_centers), p(d_z), n, fx, fy, m, p(d_out), p(d_status)))
 
 
 class Comm:

@@ -219,6 +219,32 @@ PE_API int pe_knn_bootstrap(pe_db* db, const int32_t* knn3_idx, int64_t nq, int 
 PE_API int pe_knn_accuracy(pe_db* db, const int32_t* max_sim_tmpl0, const int32_t* bootstrap,
                            int64_t nq, int nr_query_poses, float* intra_pct, float* inter_pct);
 
+/* ------------------------------------------------ patch extraction --- */
+/* The producer side of computeDescriptors on the device: frames -> 64x64x7 patches in the layout
+ * pe_compute_descriptors[_dev] consumes.  `net` (may be null) only supplies the stream / device for the _dev variants,
+ * so that extraction and forward queue up without a host round trip; with net == null `device` and the default
+ * stream are used.
+ *
+ * depth2normals (reference src/helper.cpp:53-103, include/helper.h:73-75): depth [n_frames][rows][cols] f32 metres ->
+ * normals [n_frames][rows][cols][3] f32, zero where the reference leaves them zero. */
+PE_API int pe_depth2normals(int device, const float* depth, int n_frames, int rows, int cols, float fx, float fy,
+                            float ox, float oy, float* normals);
+PE_API int pe_depth2normals_dev(pe_net* net, int device, const float* d_depth, int n_frames, int rows, int cols,
+                                float fx, float fy, float ox, float oy, float* d_normals);
+/* datasetManager::samplePatchWithScale (reference src/datasetmanager.cpp:299-346) for n patches: colour
+ * [n_frames][rows][cols][3] u8 BGR, depth as above, normals as above or null (then computed on the fly for the pixels
+ * the patch touches), frame_of[n] or null (patch i from frame i), centers_xy[n][2] (projected centroid, pixels),
+ * z[n] (centroid depth, metres), fx / fy of the camera, m = metric cut size (0.2 in the reference) ->
+ * out_patches [n][64][64][7] f32 {B,G,R,depth,nx,ny,nz}; status[n] (may be null): 0 ok, 1 = the cut rectangle does
+ * not fit the frame (the reference asserts there; here the patch is zero-filled). */
+PE_API int pe_sample_patches(int device, const uint8_t* color, const float* depth, const float* normals, int n_frames,
+                             int rows, int cols, const int32_t* frame_of, const int32_t* centers_xy, const float* z,
+                             int64_t n, float fx, float fy, float m, float* out_patches, int32_t* status);
+PE_API int pe_sample_patches_dev(pe_net* net, int device, const uint8_t* d_color, const float* d_depth,
+                                 const float* d_normals, int n_frames, int rows, int cols, const int32_t* d_frame_of,
+                                 const int32_t* d_centers_xy, const float* d_z, int64_t n, float fx, float fy, float m,
+                                 float* d_out_patches, int32_t* d_status);
+
 /* ----------------------------------------------------------- multi-GPU --- */
 /* One process per GPU.  Rank 0 calls pe_comm_unique_id, the harness ships the
  * 128 bytes to all ranks, every rank calls pe_comm_create.  New: the reference

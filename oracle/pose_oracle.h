@@ -88,6 +88,14 @@ void orc_knn_bootstrap(const int32_t* knn3_idx, int64_t nq, int nr_query_poses,
 void orc_knn_accuracy(const int32_t* max_sim_tmpl0, const int32_t* bootstrap, int64_t nq,
                       int nr_query_poses, float* intra_pct, float* inter_pct);
 
+/* patch extraction (oracle_patch.c): depth2normals src/helper.cpp:53-103, samplePatchWithScale
+ * src/datasetmanager.cpp:299-346 with cv::resize restated */
+void orc_depth2normals(const float* dep, int rows, int cols, float fx, float fy, float ox, float oy, float* nor);
+int orc_patch_rect(int rows, int cols, int center_x, int center_y, float z, float fx, float fy, float m,
+                   int* x, int* y, int* w, int* h);
+int orc_sample_patch(const uint8_t* color, const float* depth, const float* normals, int rows, int cols,
+                     int center_x, int center_y, float z, float fx, float fy, float m, float* out /* 64x64x7 */);
+
 int orc_num_threads(void);
 
 #ifdef __cplusplus

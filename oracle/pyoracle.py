@@ -74,6 +74,13 @@ def lib():
         L.orc_knn_bootstrap.argtypes = [ip, C.c_int64, C.c_int, C.c_int, ip, ip]
         L.orc_knn_accuracy.restype = None
         L.orc_knn_accuracy.argtypes = [ip, ip, C.c_int64, C.c_int, fp, fp]
+        L.orc_depth2normals.restype = None
+        L.orc_depth2normals.argtypes = [fp, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, fp]
+        L.orc_patch_rect.restype = C.c_int
+        L.orc_patch_rect.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, ip, ip, ip, ip]
+        L.orc_sample_patch.restype = C.c_int
+        L.orc_sample_patch.argtypes = [C.POINTER(C.c_uint8), fp, fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
+                                       C.c_float, C.c_float, fp]
         L.orc_num_threads.restype = C.c_int
         _lib = L
     return _lib
@@ -362,6 +369,31 @@ def knn_accuracy(max_sim_tmpl0, bootstrap, nr_query_poses):
     intra, inter = C.c_float(), C.c_float()
     lib().orc_knn_accuracy(_p(m, C.c_int32), _p(b, C.c_int32), m.size, nr_query_poses, C.byref(intra), C.byref(inter))
     return intra.value, inter.value
+
+
+# ------------------------------------------------------------------ patch extraction ---
+def depth2normals(depth, fx, fy, ox=0.0, oy=0.0):
+    """src/helper.cpp:53-103 on one rows x cols f32 depth map -> rows x cols x 3 normals"""
+    d = _f32(depth)
+    out = np.empty(d.shape + (3,), np.float32)
+    lib().orc_depth2normals(_p(d, C.c_float), d.shape[0], d.shape[1], fx, fy, ox, oy, _p(out, C.c_float))
+    return out
+
+
+def patch_rect(rows, cols, cx, cy, z, fx, fy, m=0.2):
+    v = [C.c_int32() for _ in range(4)]
+    ok = lib().orc_patch_rect(rows, cols, int(cx), int(cy), z, fx, fy, m, *[C.byref(x) for x in v])
+    return bool(ok), tuple(x.value for x in v)
+
+
+def sample_patch(color_u8, depth, normals, cx, cy, z, fx, fy, m=0.2):
+    """samplePatchWithScale (src/datasetmanager.cpp:299-346) -> 64 x 64 x 7 f32, or None where its asserts fail"""
+    c = np.ascontiguousarray(color_u8, np.uint8)
+    d, n = _f32(depth), _f32(normals)
+    out = np.empty((64, 64, 7), np.float32)
+    st = lib().orc_sample_patch(_p(c, C.c_uint8), _p(d, C.c_float), _p(n, C.c_float), d.shape[0], d.shape[1], int(cx), int(cy),
+                                z, fx, fy, m, _p(out, C.c_float))
+    return out if st == 0 else None
 
 
 def num_threads():

@@ -1,0 +1,31 @@
+"""Seeded synthetic RGB-D frames for the patch-extraction tests (numpy only; shared by tests/golden/make_golden_patch.py,
+the CPU oracle tests and the GPU parity tests).  A frame is a tilted background plane with a sphere and a box in front
+of it, a rectangle of missing depth (zeros, as a real sensor gives), and smooth random colour."""
+import numpy as np
+
+CAM = dict(fx=572.4114, fy=573.57043, ox=325.2611, oy=242.04899)     # LineMOD intrinsics (640 x 480)
+
+
+def make_frame(seed, rows=480, cols=640):
+    rng = np.random.default_rng(seed)
+    sx, sy = cols / 640.0, rows / 480.0
+    yy, xx = np.mgrid[0:rows, 0:cols].astype(np.float32)
+    depth = (1.2 + 0.0005 / sx * (xx - cols / 2) + 0.0003 / sy * (yy - rows / 2)).astype(np.float32)
+    cx, cy, rad = cols * (0.4 + 0.2 * rng.random()), rows * (0.4 + 0.2 * rng.random()), 0.17 * rows
+    r2 = (xx - cx) ** 2 + (yy - cy) ** 2
+    sphere = 0.85 - 0.25 * np.sqrt(np.maximum(0, rad * rad - r2)) / rad
+    depth = np.where(r2 < rad * rad, sphere, depth).astype(np.float32)
+    bx, by = int(cols * 0.72), int(rows * 0.2)
+    depth[by:by + rows // 5, bx:bx + cols // 6] = 0.95
+    depth[rows // 8:rows // 8 + rows // 16, cols // 10:cols // 10 + cols // 12] = 0.0       # sensor holes
+    depth += (rng.random((rows, cols)).astype(np.float32) - 0.5) * 0.002                      # sensor noise
+    depth[depth < 0.01] = 0.0
+    color = rng.integers(0, 256, (rows // 8 + 2, cols // 8 + 2, 3)).astype(np.float32)
+    color = np.kron(color, np.ones((8, 8, 1), np.float32))[:rows, :cols]                      # blocky texture
+    color = np.clip(color + 20 * np.sin(xx / 7.0)[..., None], 0, 255).astype(np.uint8)
+    return color, depth.astype(np.float32), (int(cx), int(cy))
+
+
+def cam_for(rows, cols):
+    """intrinsics scaled to a smaller frame"""
+    return dict(fx=CAM["fx"] * cols / 640.0, fy=CAM["fy"] * rows / 480.0, ox=CAM["ox"] * cols / 640.0, oy=CAM["oy"] * rows / 480.0)
