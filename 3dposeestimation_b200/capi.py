@@ -116,6 +116,10 @@ SIGNATURES = {
                                     C.c_float, vp, vp]),
     "pe_sample_patches_dev": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int64, C.c_float,
                                         C.c_float, C.c_float, vp, vp]),
+    "pe_sphere_views": (C.c_int, [C.c_int, vp, vp, C.c_int, vp, C.c_int64, C.POINTER(C.c_int64)]),
+    "pe_render_views": (C.c_int, [C.c_int, vp, vp, C.c_int, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, vp]),
+    "pe_render_views_dev": (C.c_int, [vp, C.c_int, vp, vp, C.c_int, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
+                                      vp, vp]),
 }
 
 
@@ -542,6 +546,36 @@ def sample_patches_dev(net, d_color, d_depth, d_normals, n_frames, rows, cols, d
     p = lambda a: None if a is None else a.ptr
     check(lib().pe_sample_patches_dev(net.h if net is not None else None, device, p(d_color), p(d_depth), p(d_normals), n_frames, rows,
                                       cols, p(d_frame_of), p(d_centers), p(d_z), n, fx, fy, m, p(d_out), p(d_status)))
+
+
+# ------------------------------------------------------------------ template renderer ---
+def sphere_views(depth, scale, rotation, skip_lower_hemi=True):
+    """SphereRenderer::createViews' poses (src/sphere.cpp:69-94): scale / rotation = (first, step, last) -> [n, 3, 4]"""
+    sc, ro = _f32(scale), _f32(rotation)
+    n = C.c_int64()
+    check(lib().pe_sphere_views(depth, _ptr(sc), _ptr(ro), int(skip_lower_hemi), None, 0, C.byref(n)))
+    out = np.empty((n.value, 3, 4), np.float32)
+    check(lib().pe_sphere_views(depth, _ptr(sc), _ptr(ro), int(skip_lower_hemi), _ptr(out), n.value, C.byref(n)))
+    return out
+
+
+def render_views(vertices, colors, faces, cam4, poses, rows=480, cols=640, z_near=0.001, z_far=4.0, device=0):
+    """Painter::paint for a batch of poses of one mesh -> (BGR u8 [n, rows, cols, 3], depth f32 [n, rows, cols])"""
+    v, c, f = _f32(vertices), _f32(colors), _i32(faces)
+    k, p = _f32(cam4), _f32(poses).reshape(-1, 12)
+    n = p.shape[0]
+    col = np.empty((n, rows, cols, 3), np.uint8)
+    dep = np.empty((n, rows, cols), np.float32)
+    check(lib().pe_render_views(device, _ptr(v), _ptr(c), v.shape[0], _ptr(f), f.shape[0], _ptr(k), _ptr(p), n, rows, cols, z_near, z_far,
+                                _ptr(col), _ptr(dep)))
+    return col, dep
+
+
+def render_views_dev(net, d_vertices, d_colors, n_vertices, d_faces, n_faces, cam4, d_poses, n_views, rows, cols, d_color, d_depth,
+                     z_near=0.001, z_far=4.0, device=0):
+    k = _f32(cam4)
+    check(lib().pe_render_views_dev(net.h if net is not None else None, device, d_vertices.ptr, d_colors.ptr, n_vertices, d_faces.ptr,
+                                    n_faces, _ptr(k), d_poses.ptr, n_views, rows, cols, z_near, z_far, d_color.ptr, d_depth.ptr))
 
 
 class Comm:

@@ -245,6 +245,25 @@ PE_API int pe_sample_patches_dev(pe_net* net, int device, const uint8_t* d_color
                                  const int32_t* d_centers_xy, const float* d_z, int64_t n, float fx, float fy, float m,
                                  float* d_out_patches, int32_t* d_status);
 
+/* ------------------------------------------------ template renderer --- */
+/* SphereRenderer::createViews' pose list (reference src/sphere.cpp:27-35,69-94,134-226), host only: icosahedron
+ * subdivided `sphere_depth` times in the reference's vertex order, lower hemisphere optionally skipped, for every
+ * distance in scale3 = {first, step, last} (metres) and in-plane rotation in rot3 = {first, step, last} (degrees) one
+ * row-major 3x4 [R|t].  out_poses may be null to query the count. */
+PE_API int pe_sphere_views(int sphere_depth, const float* scale3, const float* rot3, int skip_lower_hemi,
+                           float* out_poses, int64_t cap, int64_t* n_views);
+/* Painter::paint with RealWorldCamera + Model (reference src/painter.cpp:86-110,186-194,231-248,
+ * src/model.cpp:29-54) as a CUDA rasteriser, for n_views poses of one mesh: vertices [n_vertices][3], colors
+ * [n_vertices][3] RGB in [0,1], faces [n_faces][3], cam4 = {fx, fy, ox, oy}, z_near / z_far (0.001 / 4.0 in the
+ * reference) -> out_color [n_views][rows][cols][3] u8 BGR (black background), out_depth [n_views][rows][cols] f32
+ * metres (0 = background): the frame layout pe_sample_patches reads.  OpenGL itself is unavailable on this box. */
+PE_API int pe_render_views(int device, const float* vertices, const float* colors, int n_vertices, const int32_t* faces,
+                           int n_faces, const float* cam4, const float* poses, int n_views, int rows, int cols,
+                           float z_near, float z_far, uint8_t* out_color, float* out_depth);
+PE_API int pe_render_views_dev(pe_net* net, int device, const float* d_vertices, const float* d_colors, int n_vertices,
+                               const int32_t* d_faces, int n_faces, const float* cam4, const float* d_poses, int n_views,
+                               int rows, int cols, float z_near, float z_far, uint8_t* d_out_color, float* d_out_depth);
+
 /* ----------------------------------------------------------- multi-GPU --- */
 /* One process per GPU.  Rank 0 calls pe_comm_unique_id, the harness ships the
  * 128 bytes to all ranks, every rank calls pe_comm_create.  New: the reference

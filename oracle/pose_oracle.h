@@ -96,6 +96,13 @@ int orc_patch_rect(int rows, int cols, int center_x, int center_y, float z, floa
 int orc_sample_patch(const uint8_t* color, const float* depth, const float* normals, int rows, int cols,
                      int center_x, int center_y, float z, float fx, float fy, float m, float* out /* 64x64x7 */);
 
+/* template renderer (oracle_render.c): view sphere src/sphere.cpp:27-35,134-226; Painter / RealWorldCamera / Model
+ * pipeline maths src/painter.cpp:86-110,186-194,231-248, src/model.cpp:29-54.  PARITY UNPINNED (OpenGL unavailable). */
+int orc_init_sphere(int depth, float* out_xyz, int cap);
+void orc_view_pose(const float* vertex, float scale, float angle_deg, float* out_rt /* row-major 3x4 */);
+void orc_render(const float* vertices, const float* colors, int nv, const int32_t* faces, int nf, const float* cam /* fx fy ox oy */,
+                const float* rt, int rows, int cols, float z_near, float z_far, uint8_t* out_color /* BGR */, float* out_depth);
+
 int orc_num_threads(void);
 
 #ifdef __cplusplus

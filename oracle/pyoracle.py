@@ -81,6 +81,12 @@ def lib():
         L.orc_sample_patch.restype = C.c_int
         L.orc_sample_patch.argtypes = [C.POINTER(C.c_uint8), fp, fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
                                        C.c_float, C.c_float, fp]
+        L.orc_init_sphere.restype = C.c_int
+        L.orc_init_sphere.argtypes = [C.c_int, fp, C.c_int]
+        L.orc_view_pose.restype = None
+        L.orc_view_pose.argtypes = [fp, C.c_float, C.c_float, fp]
+        L.orc_render.restype = None
+        L.orc_render.argtypes = [fp, fp, C.c_int, ip, C.c_int, fp, fp, C.c_int, C.c_int, C.c_float, C.c_float, C.POINTER(C.c_uint8), fp]
         L.orc_num_threads.restype = C.c_int
         _lib = L
     return _lib
@@ -394,6 +400,52 @@ def sample_patch(color_u8, depth, normals, cx, cy, z, fx, fy, m=0.2):
     st = lib().orc_sample_patch(_p(c, C.c_uint8), _p(d, C.c_float), _p(n, C.c_float), d.shape[0], d.shape[1], int(cx), int(cy),
                                 z, fx, fy, m, _p(out, C.c_float))
     return out if st == 0 else None
+
+
+# ------------------------------------------------------------------ template renderer ---
+def init_sphere(depth):
+    """SphereRenderer::initSphere (src/sphere.cpp:186-226) -> [n, 3] unit vectors in the reference's order"""
+    cap = 10 * 4 ** depth + 2
+    out = np.empty((cap, 3), np.float32)
+    n = lib().orc_init_sphere(depth, _p(out, C.c_float), cap)
+    return out[:n].copy()
+
+
+def view_pose(vertex, scale, angle_deg):
+    """SphereRenderer::createTransformation -> row-major 3x4 [R|t]"""
+    v = _f32(vertex)
+    out = np.empty((3, 4), np.float32)
+    lib().orc_view_pose(_p(v, C.c_float), scale, angle_deg, _p(out, C.c_float))
+    return out
+
+
+def sphere_views(depth, scale, rotation, skip_lower_hemi=True):
+    """the pose list of SphereRenderer::createViews (src/sphere.cpp:69-94): scale / rotation = (first, step, last)"""
+    f32 = np.float32
+    def frange(a):
+        out, i = [], f32(a[0])
+        while i <= f32(a[2]):
+            out.append(float(i)); i = f32(i + f32(a[1]))
+        return out
+    poses = []
+    for sc in frange(scale):
+        for pos in init_sphere(depth):
+            if pos[2] < 0 and skip_lower_hemi:
+                continue
+            for rot in frange(rotation):
+                poses.append(view_pose(pos, sc, rot))
+    return np.stack(poses) if poses else np.zeros((0, 3, 4), np.float32)
+
+
+def render(vertices, colors, faces, cam, rt, rows=480, cols=640, z_near=0.001, z_far=4.0):
+    """Painter::paint with RealWorldCamera + Model -> (BGR u8 [rows, cols, 3], depth f32 [rows, cols], 0 = background)"""
+    v, c, f = _f32(vertices), _f32(colors), _i32(faces)
+    k, p = _f32(cam), _f32(rt)
+    col = np.empty((rows, cols, 3), np.uint8)
+    dep = np.empty((rows, cols), np.float32)
+    lib().orc_render(_p(v, C.c_float), _p(c, C.c_float), v.shape[0], _p(f, C.c_int32), f.shape[0], _p(k, C.c_float), _p(p, C.c_float),
+                     rows, cols, z_near, z_far, _p(col, C.c_uint8), _p(dep, C.c_float))
+    return col, dep
 
 
 def num_threads():

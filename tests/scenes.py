@@ -29,3 +29,34 @@ def make_frame(seed, rows=480, cols=640):
 def cam_for(rows, cols):
     """intrinsics scaled to a smaller frame"""
     return dict(fx=CAM["fx"] * cols / 640.0, fy=CAM["fy"] * rows / 480.0, ox=CAM["ox"] * cols / 640.0, oy=CAM["oy"] * rows / 480.0)
+
+
+# ------------------------------------------------------------------ meshes for the renderer tests ---
+def icosphere(level, radius=1.0):
+    """(vertices [n, 3], faces [m, 3]) of a subdivided icosahedron (its own subdivision: shared midpoints by dictionary)"""
+    t = (1.0 + 5.0 ** 0.5) / 2.0
+    v = [(-1, t, 0), (1, t, 0), (-1, -t, 0), (1, -t, 0), (0, -1, t), (0, 1, t), (0, -1, -t), (0, 1, -t), (t, 0, -1), (t, 0, 1), (-t, 0, -1), (-t, 0, 1)]
+    v = [np.array(p, np.float64) / np.linalg.norm(p) for p in v]
+    f = [(0, 11, 5), (0, 5, 1), (0, 1, 7), (0, 7, 10), (0, 10, 11), (1, 5, 9), (5, 11, 4), (11, 10, 2), (10, 7, 6), (7, 1, 8),
+         (3, 9, 4), (3, 4, 2), (3, 2, 6), (3, 6, 8), (3, 8, 9), (4, 9, 5), (2, 4, 11), (6, 2, 10), (8, 6, 7), (9, 8, 1)]
+    for _ in range(level):
+        cache, nf = {}, []
+        def mid(a, b):
+            key = (min(a, b), max(a, b))
+            if key not in cache:
+                m = v[a] + v[b]
+                v.append(m / np.linalg.norm(m))
+                cache[key] = len(v) - 1
+            return cache[key]
+        for a, b, c in f:
+            ab, bc, ca = mid(a, b), mid(b, c), mid(c, a)
+            nf += [(a, ab, ca), (b, bc, ab), (c, ca, bc), (ab, bc, ca)]
+        f = nf
+    return (np.array(v) * radius).astype(np.float32), np.array(f, np.int32)
+
+
+def cube(half=0.05):
+    v = np.array([[x, y, z] for x in (-half, half) for y in (-half, half) for z in (-half, half)], np.float32)
+    f = np.array([[0, 1, 3], [0, 3, 2], [4, 6, 7], [4, 7, 5], [0, 4, 5], [0, 5, 1], [2, 3, 7], [2, 7, 6], [0, 2, 6], [0, 6, 4], [1, 5, 7], [1, 7, 3]], np.int32)
+    c = (v / (2 * half) + 0.5).astype(np.float32)            # colour = position in the unit cube
+    return v, c, f
