@@ -116,6 +116,10 @@ SIGNATURES = {
                                     C.c_float, vp, vp]),
     "pe_sample_patches_dev": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int64, C.c_float,
                                         C.c_float, C.c_float, vp, vp]),
+    "pe_samples_write": (C.c_int, [C.c_char_p, vp, vp, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "pe_samples_info": (C.c_int, [C.c_char_p, C.POINTER(C.c_int64), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                  C.POINTER(C.c_int)]),
+    "pe_samples_read": (C.c_int, [C.c_char_p, C.c_int64, C.c_int64, vp, vp]),
     "pe_sphere_views": (C.c_int, [C.c_int, vp, vp, C.c_int, vp, C.c_int64, C.POINTER(C.c_int64)]),
     "pe_render_views": (C.c_int, [C.c_int, vp, vp, C.c_int, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, vp]),
     "pe_render_views_dev": (C.c_int, [vp, C.c_int, vp, vp, C.c_int, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
@@ -576,6 +580,30 @@ def render_views_dev(net, d_vertices, d_colors, n_vertices, d_faces, n_faces, ca
     k = _f32(cam4)
     check(lib().pe_render_views_dev(net.h if net is not None else None, device, d_vertices.ptr, d_colors.ptr, n_vertices, d_faces.ptr,
                                     n_faces, _ptr(k), d_poses.ptr, n_views, rows, cols, z_near, z_far, d_color.ptr, d_depth.ptr))
+
+
+# ------------------------------------------------------------------ sample-set files ---
+def samples_write(path, data_hwc, labels):
+    """hdf5Handler::write (src/hdf5handler.cpp:71-132) into a flat PESS0001 file: data [n, H, W, C], labels [n, L]"""
+    d, l = _f32(data_hwc), _f32(labels)
+    n, hh, ww, cc = d.shape
+    check(lib().pe_samples_write(os.fsencode(path), _ptr(d), _ptr(l), n, cc, hh, ww, l.shape[1] if l.ndim == 2 else 0))
+
+
+def samples_info(path):
+    n, c, hh, ww, ld = C.c_int64(), C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    check(lib().pe_samples_info(os.fsencode(path), C.byref(n), C.byref(c), C.byref(hh), C.byref(ww), C.byref(ld)))
+    return {"n": n.value, "channels": c.value, "height": hh.value, "width": ww.value, "label_dim": ld.value}
+
+
+def samples_read(path, first=0, count=None):
+    """hdf5Handler::read (src/hdf5handler.cpp:11-69) -> (data [count, H, W, C], labels [count, L])"""
+    i = samples_info(path)
+    count = i["n"] - first if count is None else count
+    d = np.empty((count, i["height"], i["width"], i["channels"]), np.float32)
+    l = np.empty((count, i["label_dim"]), np.float32)
+    check(lib().pe_samples_read(os.fsencode(path), first, count, _ptr(d), _ptr(l)))
+    return d, l
 
 
 class Comm:

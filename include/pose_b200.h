@@ -264,6 +264,17 @@ PE_API int pe_render_views_dev(pe_net* net, int device, const float* d_vertices,
                                const int32_t* d_faces, int n_faces, const float* cam4, const float* d_poses, int n_views,
                                int rows, int cols, float z_near, float z_far, uint8_t* d_out_color, float* d_out_depth);
 
+/* ------------------------------------------------ on-disk sample sets --- */
+/* hdf5Handler::write / read (reference src/hdf5handler.cpp:11-132) without HDF5: one flat little-endian file holding
+ * the same two arrays as the reference's datasets - "data" [n][C][H][W] f32 and "label" [n][label_dim] f32 - behind a
+ * 32-byte header ("PESS0001", int64 n, int32 C, H, W, label_dim).  The calls take / return HWC patches (Sample.data);
+ * the HWC <-> CHW transposes of the reference are inside.  tools/h5_to_pess.py converts a reference .h5 file,
+ * tools/caffemodel_to_pew.py a trained .caffemodel into the weight file pe_net_load_weights reads. */
+PE_API int pe_samples_write(const char* path, const float* data_hwc, const float* labels, int64_t n, int channels,
+                            int height, int width, int label_dim);
+PE_API int pe_samples_info(const char* path, int64_t* n, int* channels, int* height, int* width, int* label_dim);
+PE_API int pe_samples_read(const char* path, int64_t first, int64_t count, float* out_data_hwc, float* out_labels);
+
 /* ----------------------------------------------------------- multi-GPU --- */
 /* One process per GPU.  Rank 0 calls pe_comm_unique_id, the harness ships the
  * 128 bytes to all ranks, every rank calls pe_comm_create.  New: the reference
