@@ -120,6 +120,18 @@ SIGNATURES = {
     "pe_samples_info": (C.c_int, [C.c_char_p, C.POINTER(C.c_int64), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
                                   C.POINTER(C.c_int)]),
     "pe_samples_read": (C.c_int, [C.c_char_p, C.c_int64, C.c_int64, vp, vp]),
+    "pe_miner_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.POINTER(vp)]),
+    "pe_miner_destroy": (None, [vp]),
+    "pe_miner_pools_dev": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp)]),
+    "pe_miner_sync": (C.c_int, [vp]),
+    "pe_miner_share_stream": (C.c_int, [vp, vp]),
+    "pe_miner_set_hard_negatives": (C.c_int, [vp, vp, vp]),
+    "pe_miner_max_sim": (C.c_int, [vp, vp]),
+    "pe_miner_compute_knn": (C.c_int, [vp, vp, vp, vp]),
+    "pe_miner_set_knn": (C.c_int, [vp, vp, vp]),
+    "pe_miner_build_batch": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int, vp, vp]),
+    "pe_miner_build_batch_dev": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int, vp, vp]),
+    "pe_miner_flags": (C.c_int, [vp, C.c_int, vp]),
     "pe_sphere_views": (C.c_int, [C.c_int, vp, vp, C.c_int, vp, C.c_int64, C.POINTER(C.c_int64)]),
     "pe_render_views": (C.c_int, [C.c_int, vp, vp, C.c_int, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, vp]),
     "pe_render_views_dev": (C.c_int, [vp, C.c_int, vp, vp, C.c_int, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
@@ -516,6 +528,94 @@ class TemplateDB:
         intra, inter = C.c_float(), C.c_float()
         check(lib().pe_knn_accuracy(self.h, _ptr(m), _ptr(b), m.size, nr_query_poses, C.byref(intra), C.byref(inter)))
         return intra.value, inter.value
+
+
+# ----------------------------------------------------------------------- triplet miner ---
+class Miner:
+    """networkSolver's batch builder (reference src/networksolver.cpp:52-186, 456-505) over device-resident sample sets:
+    tmpl / train patches [n_objects * poses, 64, 64, C] (or None: pools allocated, filled in place through pools()),
+    labels [n_objects * poses, 8], rot_inv per used object."""
+
+    def __init__(self, tmpl_patches, tmpl_labels, train_patches, train_labels, n_objects, rot_inv, inplane=True, channels=None,
+                 device=0):
+        tl, ql = _f32(tmpl_labels).reshape(-1, 8), _f32(train_labels).reshape(-1, 8)
+        tp = _f32(tmpl_patches) if tmpl_patches is not None else None
+        qp = _f32(train_patches) if train_patches is not None else None
+        self.channels = int(channels if channels is not None else tp.shape[-1])
+        self.n_objects, self.n_tmpl, self.n_train = n_objects, tl.shape[0] // n_objects, ql.shape[0] // n_objects
+        ri = _i32(rot_inv)
+        assert ri.size == n_objects
+        h = vp()
+        check(lib().pe_miner_create(device, self.channels, n_objects, self.n_tmpl, self.n_train, _ptr(tp) if tp is not None else None,
+                                    _ptr(tl), _ptr(qp) if qp is not None else None, _ptr(ql), _ptr(ri), int(bool(inplane)), C.byref(h)))
+        self.h = h.value
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().pe_miner_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def pools(self):
+        a, b = vp(), vp()
+        check(lib().pe_miner_pools_dev(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def sync(self):
+        check(lib().pe_miner_sync(self.h))
+
+    def share_stream(self, net):
+        check(lib().pe_miner_share_stream(self.h, net.h))
+
+    def set_hard_negatives(self, patches, offsets):
+        if offsets is None:
+            check(lib().pe_miner_set_hard_negatives(self.h, None, None))
+            return
+        o = np.ascontiguousarray(offsets, np.int64)
+        p = _f32(patches)
+        check(lib().pe_miner_set_hard_negatives(self.h, _ptr(p), _ptr(o)))
+
+    def max_sim(self):
+        out = np.empty((self.n_objects * self.n_train, 2), np.int32)
+        check(lib().pe_miner_max_sim(self.h, _ptr(out)))
+        return out
+
+    def compute_knn(self, net):
+        nq = self.n_objects * self.n_train
+        t, ln = np.empty((nq, 4), np.int32), np.empty(nq, np.int32)
+        check(lib().pe_miner_compute_knn(self.h, net.h, _ptr(t), _ptr(ln)))
+        return t, ln
+
+    def set_knn(self, table, length):
+        if table is None:
+            check(lib().pe_miner_set_knn(self.h, None, None))
+            return
+        t, ln = _i32(table), _i32(length)
+        check(lib().pe_miner_set_knn(self.h, _ptr(t), _ptr(ln)))
+
+    def build_batch(self, batch_size, it, seed, triplet_size=5, random_background=0, want_batch=True):
+        n = batch_size // triplet_size if triplet_size > 0 else 0
+        batch = np.empty((n * 5, self.channels, 64, 64), np.float32) if want_batch else None
+        idx = np.empty((n, 5), np.int32)
+        check(lib().pe_miner_build_batch(self.h, batch_size, triplet_size, it, seed, random_background,
+                                         _ptr(batch) if want_batch else None, _ptr(idx)))
+        return batch, idx
+
+    def build_batch_dev(self, batch_size, it, seed, d_batch, d_idx=None, triplet_size=5, random_background=0):
+        check(lib().pe_miner_build_batch_dev(self.h, batch_size, triplet_size, it, seed, random_background,
+                                             d_batch.ptr if isinstance(d_batch, DeviceArray) else d_batch,
+                                             d_idx.ptr if isinstance(d_idx, DeviceArray) else d_idx))
+
+    def flags(self, n_triplets):
+        out = np.empty(n_triplets, np.int32)
+        check(lib().pe_miner_flags(self.h, n_triplets, _ptr(out)))
+        return out
 
 
 # ------------------------------------------------------------------ patch extraction ---

@@ -275,6 +275,51 @@ PE_API int pe_samples_write(const char* path, const float* data_hwc, const float
 PE_API int pe_samples_info(const char* path, int64_t* n, int* channels, int* height, int* width, int* label_dim);
 PE_API int pe_samples_read(const char* path, int64_t first, int64_t count, float* out_data_hwc, float* out_labels);
 
+/* ------------------------------------------------ triplet miner --- */
+/* The training-side consumer of the k-NN: networkSolver's view of the dataset (template_set, training_set, rotInv,
+ * inplane; reference include/networksolver.h:60-75) with both sample sets resident on the device.
+ * Patches are HWC [n_objects * poses][64][64][channels] f32 in object-major order (template_set[object][pose]), labels
+ * [n_objects * poses][8] = {class, quaternion xyzw, translation}; rot_inv[object] = rotInv[model_index[used_models[
+ * object]]].  A null patch pointer leaves that pool allocated but unfilled (see pe_miner_pools_dev). */
+typedef struct pe_miner pe_miner;
+PE_API int pe_miner_create(int device, int channels, int n_objects, int nr_template_poses, int nr_training_poses,
+                           const float* tmpl_patches_hwc, const float* tmpl_labels, const float* train_patches_hwc,
+                           const float* train_labels, const int* rot_inv, int inplane, pe_miner** out);
+PE_API void pe_miner_destroy(pe_miner* m);
+/* device addresses of the two pools, for producers that write them in place (pe_render_views_dev ->
+ * pe_sample_patches_dev) */
+PE_API int pe_miner_pools_dev(pe_miner* m, float** d_tmpl_patches, float** d_train_patches);
+PE_API int pe_miner_sync(pe_miner* m);
+/* queue the miner's kernels on the net's stream (as pe_db_share_stream); the net must outlive the miner */
+PE_API int pe_miner_share_stream(pe_miner* m, pe_net* net);
+/* datasetManager::getHardNegatives (used at src/networksolver.cpp:60,95-100): patches of all objects back to back,
+ * offsets[n_objects + 1] the prefix offsets per object; offsets == null removes them */
+PE_API int pe_miner_set_hard_negatives(pe_miner* m, const float* patches_hwc, const int64_t* offsets);
+/* datasetManager::computeMaxSimTmpl / computeMaxSimTmplInplane (src/datasetmanager.cpp:687-783):
+ * out [n_objects * nr_training_poses][2] = maxSimTmpl[object][pose][0..1]; -1 where the reference would push an
+ * uninitialised int.  out may be null (the table stays on the device for pe_miner_build_batch). */
+PE_API int pe_miner_max_sim(pe_miner* m, int32_t* out);
+/* networkSolver::computeKNN (src/networksolver.cpp:456-505) over the resident pools: forward of both sets, k = 3
+ * matcher, maxSimKNNTmpl; switches `bootstrapping` on as trainNet does after it (:308-309,332-333).
+ * out_table [nq][4] / out_len [nq] as pe_knn_bootstrap, both may be null. */
+PE_API int pe_miner_compute_knn(pe_miner* m, pe_net* net, int32_t* out_table, int32_t* out_len);
+/* the same table from the host (pe_knn_bootstrap's output); table == null switches bootstrapping off */
+PE_API int pe_miner_set_knn(pe_miner* m, const int32_t* table, const int32_t* len);
+/* networkSolver::buildBatch + the batch_caffe fill (src/networksolver.cpp:32-40,52-186).
+ * out_batch: [batch_size / 5 * 5][channels][64][64] f32 (Caffe layout; anchor, puller, pusher0, pusher1, pusher2 per
+ * triplet); out_idx: [batch_size / 5][5] = anchor as training linear index, the others as template linear indices, a
+ * hard negative as ~(index into the negative pool).  Either may be null.  The reference draws from
+ * std::random_device; here draw j of triplet linearId is a hash of (seed, linearId, j), so a call is reproducible and
+ * the caller varies `seed` per epoch.  random_background: 0, or 1 = bgfill::randomColorFill on the anchor
+ * (src/bgfill.cpp:136-158; 7-channel patches); shapes / fractals / real backgrounds return PE_ERR_INVALID.
+ * A rejection loop the reference would never leave fails with PE_ERR_INVALID. */
+PE_API int pe_miner_build_batch(pe_miner* m, int batch_size, int triplet_size, int iter, uint64_t seed,
+                                int random_background, float* out_batch, int32_t* out_idx);
+/* asynchronous on the miner's stream, outputs on the device; check pe_miner_flags afterwards */
+PE_API int pe_miner_build_batch_dev(pe_miner* m, int batch_size, int triplet_size, int iter, uint64_t seed,
+                                    int random_background, float* d_out_batch, int32_t* d_out_idx);
+PE_API int pe_miner_flags(pe_miner* m, int n_triplets, int32_t* out_flags);
+
 /* ----------------------------------------------------------- multi-GPU --- */
 /* One process per GPU.  Rank 0 calls pe_comm_unique_id, the harness ships the
  * 128 bytes to all ranks, every rank calls pe_comm_create.  New: the reference

@@ -103,6 +103,22 @@ void orc_view_pose(const float* vertex, float scale, float angle_deg, float* out
 void orc_render(const float* vertices, const float* colors, int nv, const int32_t* faces, int nf, const float* cam /* fx fy ox oy */,
                 const float* rt, int rows, int cols, float z_near, float z_far, uint8_t* out_color /* BGR */, float* out_depth);
 
+/* triplet miner (oracle_miner.c): computeMaxSimTmpl[Inplane] src/datasetmanager.cpp:687-783, buildBatch
+ * src/networksolver.cpp:52-186, Caffe batch layout :32-40, randomColorFill src/bgfill.cpp:136-158 */
+#define ORC_MAX_DRAWS 4096
+uint64_t orc_miner_key(uint64_t seed, uint64_t linear_id);
+uint64_t orc_miner_draw(uint64_t key, uint64_t j);
+float orc_elevation(const float* label);
+void orc_max_sim_tmpl(const float* tmpl_labels, const float* train_labels, int n_objects, int nr_template_poses,
+                      int nr_training_poses, int inplane, int32_t* out /* [n_objects * nr_training_poses][2] */);
+void orc_triplet_indices(const float* tmpl_labels, const int32_t* max_sim, const int32_t* knn_table, const int32_t* knn_len,
+                         const int* rot_inv, const int64_t* neg_offsets, int n_objects, int nr_template_poses,
+                         int nr_training_poses, int batch_size, int triplet_size, int iter, uint64_t seed,
+                         int32_t* out_idx /* [batch_size / triplet_size][5] */, int32_t* out_flag);
+void orc_gather_batch(const float* tmpl_pool, const float* train_pool, const float* neg_pool, const int32_t* idx,
+                      int n_triplets, int channels, int64_t first_linear_id, uint64_t seed, int random_background,
+                      float* out /* [n_triplets * 5][C][64][64] */);
+
 int orc_num_threads(void);
 
 #ifdef __cplusplus

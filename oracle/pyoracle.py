@@ -87,6 +87,16 @@ def lib():
         L.orc_view_pose.argtypes = [fp, C.c_float, C.c_float, fp]
         L.orc_render.restype = None
         L.orc_render.argtypes = [fp, fp, C.c_int, ip, C.c_int, fp, fp, C.c_int, C.c_int, C.c_float, C.c_float, C.POINTER(C.c_uint8), fp]
+        i64p = C.POINTER(C.c_int64)
+        L.orc_max_sim_tmpl.restype = None
+        L.orc_max_sim_tmpl.argtypes = [fp, fp, C.c_int, C.c_int, C.c_int, C.c_int, ip]
+        L.orc_triplet_indices.restype = None
+        L.orc_triplet_indices.argtypes = [fp, ip, ip, ip, ip, i64p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                          C.c_uint64, ip, ip]
+        L.orc_gather_batch.restype = None
+        L.orc_gather_batch.argtypes = [fp, fp, fp, ip, C.c_int, C.c_int, C.c_int64, C.c_uint64, C.c_int, fp]
+        L.orc_elevation.restype = C.c_float
+        L.orc_elevation.argtypes = [fp]
         L.orc_num_threads.restype = C.c_int
         _lib = L
     return _lib
@@ -446,6 +456,52 @@ def render(vertices, colors, faces, cam, rt, rows=480, cols=640, z_near=0.001, z
     lib().orc_render(_p(v, C.c_float), _p(c, C.c_float), v.shape[0], _p(f, C.c_int32), f.shape[0], _p(k, C.c_float), _p(p, C.c_float),
                      rows, cols, z_near, z_far, _p(col, C.c_uint8), _p(dep, C.c_float))
     return col, dep
+
+
+# ----------------------------------------------------------------------- triplet miner ---
+def max_sim_tmpl(tmpl_labels, train_labels, n_objects, inplane):
+    """datasetManager::computeMaxSimTmpl[Inplane] (src/datasetmanager.cpp:687-783) -> [n_objects * n_train, 2]"""
+    tl, ql = _f32(tmpl_labels).reshape(-1, 8), _f32(train_labels).reshape(-1, 8)
+    n_t, n_q = tl.shape[0] // n_objects, ql.shape[0] // n_objects
+    out = np.empty((n_objects * n_q, 2), np.int32)
+    lib().orc_max_sim_tmpl(_p(tl, C.c_float), _p(ql, C.c_float), n_objects, n_t, n_q, int(bool(inplane)), _p(out, C.c_int32))
+    return out
+
+
+def elevation(label):
+    l = _f32(label)
+    return lib().orc_elevation(_p(l, C.c_float))
+
+
+def triplet_indices(tmpl_labels, max_sim, knn_table, knn_len, rot_inv, neg_offsets, n_objects, nr_training_poses, batch_size,
+                    triplet_size, it, seed):
+    """networkSolver::buildBatch's index selection (src/networksolver.cpp:52-186) -> ([n_triplets, 5], flags)"""
+    tl = _f32(tmpl_labels).reshape(-1, 8)
+    n_t = tl.shape[0] // n_objects
+    ms = _i32(max_sim)
+    kt = _i32(knn_table) if knn_table is not None else None
+    kl = _i32(knn_len) if knn_len is not None else None
+    ri = _i32(rot_inv)
+    no = np.ascontiguousarray(neg_offsets, np.int64) if neg_offsets is not None else None
+    n = batch_size // triplet_size
+    out, flag = np.empty((n, 5), np.int32), np.empty(n, np.int32)
+    lib().orc_triplet_indices(_p(tl, C.c_float), _p(ms, C.c_int32), _p(kt, C.c_int32) if kt is not None else None,
+                              _p(kl, C.c_int32) if kl is not None else None, _p(ri, C.c_int32),
+                              _p(no, C.c_int64) if no is not None else None, n_objects, n_t, nr_training_poses, batch_size,
+                              triplet_size, it, seed, _p(out, C.c_int32), _p(flag, C.c_int32))
+    return out, flag
+
+
+def gather_batch(tmpl_pool, train_pool, neg_pool, idx, first_linear_id, seed, random_background=0):
+    """the batch_caffe fill of buildBatchQueue (src/networksolver.cpp:32-40) -> [n_triplets * 5, C, 64, 64]"""
+    tp, qp = _f32(tmpl_pool), _f32(train_pool)
+    npool = _f32(neg_pool) if neg_pool is not None else None
+    ix = _i32(idx)
+    ch = tp.shape[-1]
+    out = np.empty((ix.shape[0] * 5, ch, 64, 64), np.float32)
+    lib().orc_gather_batch(_p(tp, C.c_float), _p(qp, C.c_float), _p(npool, C.c_float) if npool is not None else None,
+                           _p(ix, C.c_int32), ix.shape[0], ch, first_linear_id, seed, random_background, _p(out, C.c_float))
+    return out
 
 
 def num_threads():
