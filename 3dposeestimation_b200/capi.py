@@ -152,6 +152,40 @@ def lib():
     return _lib
 
 
+_host_lib = None
+HOST_SIGNATURES = {
+    "pe_host_last_error": (C.c_char_p, []),
+    "pe_host_compute_descriptors": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, vp]),
+    "pe_host_compute_histogram": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, vp]),
+    "pe_host_compute_confusion": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, C.c_char_p, C.c_char_p, C.c_int, vp]),
+    "pe_host_compute_knn": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
+    "pe_host_save_logs": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_char_p, C.c_int, C.c_float]),
+    "pe_host_build_batch": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, vp, C.c_int, vp, vp, C.c_int, C.c_int,
+                                      C.c_uint64, C.c_int, vp, vp, vp, vp]),
+}
+
+
+def host_lib():
+    """libpose_b200_host.so: flat-array doors into the C++ mirror of networkEvaluator / networkSolver
+    (include/networkevaluator_b200.hpp), for tests that drive it the way a C++ caller of the reference would"""
+    global _host_lib
+    if _host_lib is None:
+        lib()
+        if not os.path.exists(HOST_LIB_PATH):
+            raise PoseError(PE_ERR_CUDA, f"{HOST_LIB_PATH} is not built (run __graft_entry__.build())")
+        L = C.CDLL(HOST_LIB_PATH)
+        for name, (res, args) in HOST_SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _host_lib = L
+    return _host_lib
+
+
+def host_check(code: int):
+    if code != 0:
+        raise PoseError(code, (host_lib().pe_host_last_error() or b"").decode())
+
+
 def check(code: int):
     if code != PE_OK:
         raise PoseError(code, lib().pe_last_error().decode(errors="replace"))

@@ -127,3 +127,42 @@ HOST_API int pe_host_save_logs(pe_net* net, const float* t_patches, const float*
         sz::networkEvaluator::saveConfusionMatrix(cnn, db, config_path);
     });
 }
+
+/* networkSolver::buildBatch / buildBatchQueue's batch_caffe through the mirror: knn_table (nq x 4, -1 padded) + knn_len
+ * switch bootstrapping on; out_batch [batch_size / 5 * 5][channels][64][64], out_triplets [batch_size / 5][5],
+ * out_max_sim [n_obj * nr_q][2]; also returns the vector<Sample> form's data in out_samples_hwc when non-null */
+HOST_API int pe_host_build_batch(const float* t_patches, const float* t_labels, int n_obj, int nr_t, const float* q_patches,
+                                 const float* q_labels, int nr_q, int channels, const int* rot_inv, int inplane,
+                                 const int* knn_table, const int* knn_len, int batch_size, int iter, uint64_t seed,
+                                 int random_background, float* out_batch, int* out_triplets, int* out_max_sim,
+                                 float* out_samples_hwc) {
+    return guarded([&] {
+        const sz::SampleSet ts = make_set(t_patches, t_labels, n_obj, nr_t, channels);
+        const sz::SampleSet qs = make_set(q_patches, q_labels, n_obj, nr_q, channels);
+        sz::networkSolver solver(ts, qs, qs, std::vector<int>(rot_inv, rot_inv + n_obj), inplane != 0);
+        solver.seed = seed;
+        solver.random_background = random_background;
+        if (knn_table) {
+            solver.maxSimKNNTmpl.assign(n_obj, std::vector<std::vector<int>>(nr_q));
+            for (int q = 0; q < n_obj * nr_q; ++q)
+                solver.maxSimKNNTmpl[q / nr_q][q % nr_q].assign(knn_table + (size_t)q * 4, knn_table + (size_t)q * 4 + knn_len[q]);
+            solver.bootstrapping = true;
+        }
+        const std::vector<float> b = solver.buildBatchCaffe(batch_size, 5, iter);
+        std::memcpy(out_batch, b.data(), b.size() * sizeof(float));
+        std::memcpy(out_triplets, solver.last_triplets.data(), solver.last_triplets.size() * sizeof(int));
+        for (int q = 0; q < n_obj * nr_q; ++q) {
+            out_max_sim[q * 2] = solver.maxSimTmpl[q / nr_q][q % nr_q][0];
+            out_max_sim[q * 2 + 1] = solver.maxSimTmpl[q / nr_q][q % nr_q][1];
+        }
+        if (out_samples_hwc) {
+            sz::networkSolver again(ts, qs, qs, std::vector<int>(rot_inv, rot_inv + n_obj), inplane != 0);
+            again.seed = seed;
+            again.maxSimKNNTmpl = solver.maxSimKNNTmpl;
+            again.bootstrapping = solver.bootstrapping;
+            const std::vector<sz::Sample> v = again.buildBatch(batch_size, 5, iter);
+            const size_t img = (size_t)64 * 64 * channels;
+            for (size_t i = 0; i < v.size(); ++i) std::memcpy(out_samples_hwc + i * img, v[i].data.buf.data(), img * sizeof(float));
+        }
+    });
+}

@@ -211,36 +211,158 @@ public:
     }
 };
 
-/* the evaluation-side member of networkSolver (include/networksolver.h:49-57) */
+/* the evaluation-side member of networkSolver (include/networksolver.h:49-57) and its batch builder (:38-43) */
 class networkSolver {
 public:
-    networkSolver(const SampleSet& templates, const SampleSet& training, const SampleSet& test)
-        : template_set(templates), training_set(training), test_set(test) {
+    /* rot_inv_per_object[object] = rotInv[model_index[used_models[object]]] (src/networksolver.cpp:78); `inplane`
+     * selects computeMaxSimTmplInplane over computeMaxSimTmpl as datasetManager does (src/datasetmanager.cpp:683-684) */
+    networkSolver(const SampleSet& templates, const SampleSet& training, const SampleSet& test,
+                  std::vector<int> rot_inv_per_object = {}, bool inplane = true, int device = 0)
+        : rotInv(std::move(rot_inv_per_object)), template_set(templates), training_set(training), test_set(test),
+          inplane_(inplane), device_(device) {
+        detail::check_rectangular(template_set, "template_set");
+        detail::check_rectangular(training_set, "training_set");
         nr_objects = (unsigned)template_set.size();
         nr_training_poses = (unsigned)training_set.front().size();
         nr_template_poses = (unsigned)template_set.front().size();
-        nr_test_poses = (unsigned)test_set.front().size();
+        nr_test_poses = test_set.empty() ? 0u : (unsigned)test_set.front().size();
+        if (rotInv.empty()) rotInv.assign(nr_objects, 0);
+        if (rotInv.size() != nr_objects) throw std::runtime_error("rotInv must hold one entry per used object");
     }
+    networkSolver(const networkSolver&) = delete;
+    networkSolver& operator=(const networkSolver&) = delete;
+    ~networkSolver() { if (miner_) pe_miner_destroy(miner_); }
 
-    /* src/networksolver.cpp:456-505: k = 3 matcher over the training set -> maxSimKNNTmpl */
+    /* src/networksolver.cpp:456-505: k = 3 matcher over the training set -> maxSimKNNTmpl; both sets stay on the
+     * device between calls.  As in trainNet (:308-309,332-333) the caller sets `bootstrapping` afterwards. */
     void computeKNN(Net& CNN) {
-        detail::DbGuard g;
-        Mat DBtraining;
-        const int knn = 3;
-        std::vector<int32_t> idx = networkEvaluator::match(CNN, template_set, training_set, knn, &g, &DBtraining);
-        std::vector<int32_t> out((size_t)DBtraining.rows * 4), len(DBtraining.rows);
-        pe_check(pe_knn_bootstrap(g.db, idx.data(), DBtraining.rows, (int)nr_training_poses, out.data(), len.data()));
+        ensureMiner();
+        const size_t nq = (size_t)nr_objects * nr_training_poses;
+        std::vector<int32_t> out(nq * 4), len(nq);
+        pe_check(pe_miner_compute_knn(miner_, CNN.handle(), out.data(), len.data()));
         maxSimKNNTmpl.assign(nr_objects, std::vector<std::vector<int>>(nr_training_poses, std::vector<int>()));
-        for (int linearId = 0; linearId < DBtraining.rows; ++linearId) {
+        for (size_t linearId = 0; linearId < nq; ++linearId) {
             std::vector<int>& v = maxSimKNNTmpl[linearId / nr_training_poses][linearId % nr_training_poses];
-            v.assign(out.begin() + (size_t)linearId * 4, out.begin() + (size_t)linearId * 4 + len[linearId]);
+            v.assign(out.begin() + linearId * 4, out.begin() + linearId * 4 + len[linearId]);
         }
+        knn_on_device_ = true;
     }
 
+    /* datasetManager::getHardNegatives as buildBatch reads it (:60,95-100): one (possibly empty) list per used object */
+    void setHardNegatives(const std::vector<std::vector<Sample>>& negs) {
+        ensureMiner();
+        if (negs.size() != nr_objects) throw std::runtime_error("hard negatives: one list per used object");
+        std::vector<int64_t> off(nr_objects + 1, 0);
+        std::vector<float> flat;
+        for (size_t o = 0; o < nr_objects; ++o) {
+            off[o + 1] = off[o] + (int64_t)negs[o].size();
+            for (const Sample& smp : negs[o]) flat.insert(flat.end(), smp.data.buf.begin(), smp.data.buf.end());
+        }
+        hard_negs_ = negs;
+        pe_check(pe_miner_set_hard_negatives(miner_, flat.data(), off.data()));
+    }
+
+    /* the batch_caffe buffer buildBatchQueue pushes (src/networksolver.cpp:12-50) / trainNet fills (:353-368):
+     * [batch_size / 5 * 5][channels][64][64].  Every call draws with a fresh seed (the reference draws from
+     * std::random_device); `seed` makes a run repeatable. */
+    std::vector<float> buildBatchCaffe(int batch_size, unsigned int triplet_size, int iter) {
+        ensureMiner();
+        syncBootstrapping();
+        const size_t n_triplets = triplet_size ? (size_t)batch_size / triplet_size : 0;
+        std::vector<float> batch_caffe(n_triplets * 5 * img_, 0.f);
+        last_triplets.assign(n_triplets * 5, 0);
+        pe_check(pe_miner_build_batch(miner_, batch_size, (int)triplet_size, iter, seed + batches_built_++, random_background,
+                                      batch_caffe.data(), last_triplets.data()));
+        return batch_caffe;
+    }
+
+    /* src/networksolver.cpp:52-186 with the reference's return type: anchor, puller, pusher0-2 per triplet (the
+     * selection runs on the device, the Samples are copied from the host sets; no background fill here) */
+    std::vector<Sample> buildBatch(int batch_size, unsigned int triplet_size, int iter) {
+        ensureMiner();
+        syncBootstrapping();
+        const size_t n_triplets = triplet_size ? (size_t)batch_size / triplet_size : 0;
+        last_triplets.assign(n_triplets * 5, 0);
+        pe_check(pe_miner_build_batch(miner_, batch_size, (int)triplet_size, iter, seed + batches_built_++, 0, nullptr,
+                                      last_triplets.data()));
+        std::vector<Sample> batch;
+        batch.reserve(n_triplets * 5);
+        for (size_t t = 0; t < n_triplets; ++t)
+            for (int slot = 0; slot < 5; ++slot) {
+                const int32_t id = last_triplets[t * 5 + slot];
+                Sample smp;
+                if (slot == 0) smp.copySample(training_set[id / nr_training_poses][id % nr_training_poses]);
+                else if (id >= 0) smp.copySample(template_set[id / nr_template_poses][id % nr_template_poses]);
+                else smp.copySample(negSample(~id));
+                batch.push_back(std::move(smp));
+            }
+        return batch;
+    }
+
+    std::vector<std::vector<std::vector<int>>> maxSimTmpl;      /* db.getMaxSimTmpl() (filled with the first batch) */
     std::vector<std::vector<std::vector<int>>> maxSimKNNTmpl;
+    std::vector<int32_t> last_triplets;                         /* [n_triplets][5] indices of the last batch */
     std::vector<int> rotInv;
+    bool bootstrapping = false;
+    int random_background = 0;
+    uint64_t seed = 0x5eed;
     unsigned int nr_objects, nr_training_poses, nr_template_poses, nr_test_poses;
     const SampleSet &template_set, &training_set, &test_set;
+
+private:
+    static std::vector<float> flatten_patches(const SampleSet& set, size_t img) {
+        std::vector<float> out;
+        out.reserve(set.size() * set[0].size() * img);
+        for (auto& obj : set)
+            for (auto& smp : obj) {
+                if (smp.data.buf.size() != img) throw std::runtime_error("samples differ in patch size");
+                out.insert(out.end(), smp.data.buf.begin(), smp.data.buf.end());
+            }
+        return out;
+    }
+    void ensureMiner() {
+        if (miner_) return;
+        const Mat& first = template_set[0][0].data;
+        if (first.rows != 64 || first.cols != 64) throw std::runtime_error("patches must be 64x64");
+        img_ = (size_t)64 * 64 * first.ch;
+        const std::vector<float> tp = flatten_patches(template_set, img_), qp = flatten_patches(training_set, img_);
+        const std::vector<float> tl = detail::flatten_labels(template_set), ql = detail::flatten_labels(training_set);
+        pe_check(pe_miner_create(device_, first.ch, (int)nr_objects, (int)nr_template_poses, (int)nr_training_poses, tp.data(),
+                                 tl.data(), qp.data(), ql.data(), rotInv.data(), inplane_ ? 1 : 0, &miner_));
+        std::vector<int32_t> ms((size_t)nr_objects * nr_training_poses * 2);
+        pe_check(pe_miner_max_sim(miner_, ms.data()));
+        maxSimTmpl.assign(nr_objects, std::vector<std::vector<int>>(nr_training_poses));
+        for (size_t q = 0; q < ms.size() / 2; ++q)
+            maxSimTmpl[q / nr_training_poses][q % nr_training_poses] = {ms[q * 2], ms[q * 2 + 1]};
+    }
+    /* `bootstrapping` is a plain member in the reference: follow it, and push a table the caller filled by hand */
+    void syncBootstrapping() {
+        if (!bootstrapping) { pe_check(pe_miner_set_knn(miner_, nullptr, nullptr)); knn_on_device_ = false; return; }
+        if (knn_on_device_) return;
+        const size_t nq = (size_t)nr_objects * nr_training_poses;
+        if (maxSimKNNTmpl.size() != nr_objects) throw std::runtime_error("bootstrapping without maxSimKNNTmpl (call computeKNN)");
+        std::vector<int32_t> table(nq * 4, -1), len(nq);
+        for (size_t q = 0; q < nq; ++q) {
+            const std::vector<int>& v = maxSimKNNTmpl[q / nr_training_poses][q % nr_training_poses];
+            len[q] = (int32_t)v.size();
+            for (size_t j = 0; j < v.size() && j < 4; ++j) table[q * 4 + j] = v[j];
+        }
+        pe_check(pe_miner_set_knn(miner_, table.data(), len.data()));
+        knn_on_device_ = true;
+    }
+    const Sample& negSample(int64_t linear) const {
+        for (const std::vector<Sample>& list : hard_negs_) {
+            if (linear < (int64_t)list.size()) return list[linear];
+            linear -= (int64_t)list.size();
+        }
+        throw std::runtime_error("hard negative index out of range");
+    }
+    pe_miner* miner_ = nullptr;
+    std::vector<std::vector<Sample>> hard_negs_;
+    bool inplane_, knn_on_device_ = false;
+    int device_;
+    size_t img_ = 0;
+    uint64_t batches_built_ = 0;
 };
 
 }  // namespace sz

@@ -28,6 +28,27 @@ def test_library_exports_every_declared_symbol(capi):
     assert lib.pe_version() == 100
 
 
+def test_host_mirror_library_loads_and_exports_its_doors(capi):
+    """libpose_b200_host.so (the compiled C++ mirror of networkEvaluator / networkSolver) links and loads without a GPU"""
+    src = open(os.path.join(ROOT, "3dposeestimation_b200", "csrc", "host_cabi.cpp")).read()
+    doors = re.findall(r"HOST_API\s+[\w\s\*]+?\b(pe_host_\w+)\s*\(", src)
+    assert set(doors) == set(capi.HOST_SIGNATURES) and len(doors) >= 7
+    H = capi.host_lib()
+    for n in doors:
+        assert hasattr(H, n)
+    # no device here: the mirror reports the library's error instead of computing anything on the host
+    if capi.device_count() == 0:
+        z = np.zeros((2, 64, 64, 7), np.float32)
+        lab = np.zeros((2, 8), np.float32)
+        rot = np.zeros(2, np.int32)
+        out = np.zeros((10, 7, 64, 64), np.float32)
+        idx, ms = np.zeros((2, 5), np.int32), np.zeros((2, 2), np.int32)
+        vp = lambda a: a.ctypes.data_as(capi.vp)
+        code = H.pe_host_build_batch(vp(z), vp(lab), 2, 1, vp(z), vp(lab), 1, 7, vp(rot), 1, None, None, 10, 0, 1, 0, vp(out), vp(idx),
+                                     vp(ms), None)
+        assert code != 0 and b"pose_b200" in H.pe_host_last_error()
+
+
 def test_header_cites_reference_interfaces():
     text = open(os.path.join(ROOT, "include", "pose_b200.h")).read()
     for cite in ("src/networkevaluator.cpp:9-54", "src/networkevaluator.cpp:269-355", "src/networkevaluator.cpp:199-245",
