@@ -6,6 +6,11 @@
  */
 #include "../../include/networkevaluator_b200.hpp"
 
+#include <csignal>
+#include <cstdlib>
+#include <execinfo.h>
+#include <unistd.h>
+
 namespace {
 
 thread_local std::string g_err;
@@ -47,6 +52,21 @@ int guarded(F&& f) {
 }  // namespace
 
 #define HOST_API extern "C" __attribute__((visibility("default")))
+
+/* PE_HOST_BACKTRACE=1: print the native stack on SIGSEGV (debugging aid for callers that load the library into an
+ * interpreter) */
+namespace {
+void on_segv(int) {
+    void* bt[64];
+    const int n = backtrace(bt, 64);
+    backtrace_symbols_fd(bt, n, 2);
+    _exit(139);
+}
+__attribute__((constructor)) void install_backtrace() {
+    const char* e = std::getenv("PE_HOST_BACKTRACE");
+    if (e && *e == '1') std::signal(SIGSEGV, on_segv);
+}
+}  // namespace
 
 HOST_API const char* pe_host_last_error() { return g_err.c_str(); }
 

@@ -50,10 +50,12 @@ def test_compute_descriptors_and_histogram_and_confusion(gpu, po, world):
                                                    _p(BINS), len(BINS), knn, _p(hist)))
         np.testing.assert_array_equal(hist, db.histogram(idx, ql, rot_inv, BINS))
         np.testing.assert_allclose(hist, po.histogram(idx, ql, tl, N_T, rot_inv, BINS), rtol=0, atol=1e-6)
-        cm = np.empty((2, 2), np.float32)
-        gpu.host_check(H.pe_host_compute_confusion(net.h, _p(tp), _p(tl), N_OBJ, N_T, _p(qp), _p(ql), N_Q, 7, b"ape, bowl, cam",
-                                                   b"ape,cam", knn, _p(cm)))
-        np.testing.assert_array_equal(cm, db.confusion(idx, ql, np.array([0, -1, 1], np.int32), 2, N_Q))
+        cm = np.empty((3, 3), np.float32)
+        gpu.host_check(H.pe_host_compute_confusion(net.h, _p(tp), _p(tl), N_OBJ, N_T, _p(qp), _p(ql), N_Q, 7, b"ape, bowl, cam, duck",
+                                                   b"cam,ape,bowl", knn, _p(cm)))
+        np.testing.assert_array_equal(cm, db.confusion(idx, ql, np.array([1, 2, 0, -1], np.int32), 3, N_Q))
+        np.testing.assert_array_equal(cm, po.confusion(idx, ql, tl, np.array([1, 2, 0, -1], np.int32), 3, N_Q))
+        assert abs(float(cm.sum()) - 3.0) < 1e-5
 
 
 def test_solver_compute_knn_and_accuracy(gpu, po, world):
