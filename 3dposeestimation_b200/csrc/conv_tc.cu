@@ -9,20 +9,24 @@
  * Formulation (implicit GEMM without im2col, see umma.cuh):
  *   - the patch lives in shared memory as an fp16 HWC8 image (one pixel = 8 channel slots = 16 bytes = one
  *     core-matrix row), split in two terms x ~= hi + lo.  A K-major no-swizzle descriptor with LBO = one pixel
- *     and SBO = eight pixels makes 128 consecutive pixels the 128 rows of the A operand and (kx, kx+1) x 8
- *     channels one K step, so the tensor core reads the sliding windows straight out of the image;
- *   - with only 16 filters the MMA would be bound by its A reads, so N is widened to 128 with a Toeplitz
- *     copy of the weights: column (j, f) of the accumulator is output row r + j, filter f, and a K step over
- *     input row r + ky' uses weight row ky' - j (zero outside 0..7).  The Toeplitz operand is itself an
- *     overlapping window over a short array of 256-byte weight slabs (SBO = 128, start = (14 - ky') slabs);
- *   - image rows are stored in the order (y mod 8, y div 8) so that the two base rows r and r + 8 of a tile
- *     are adjacent: one tile = 2 base rows x 64 pixels = 128 accumulator lanes = 16 output rows;
- *   - fp32 accuracy: D = A_hi.B_hi + A_hi.B_lo + A_lo.B_hi in fp32 (TMEM), operands scaled by powers of two.
- *   Per patch: 4 tiles x 15 input rows x 4 pixel pairs x 3 products = 720 MMAs of 128x128x16.
+ *     and SBO = eight pixels turns 256 consecutive pixels into the 256 rows of the B operand and (kx, kx+1) x 8
+ *     channels into one K step, so the tensor core reads the sliding windows straight out of the image;
+ *   - image rows are stored in the order (y mod 8, y div 8), so the four base rows r, r + 8, r + 16, r + 24 of a
+ *     tile are adjacent: one B window = 4 base rows x 64 pixels = 256 accumulator columns;
+ *   - the A operand is a Toeplitz copy of the weights: accumulator lane (j, f) is output row r + j, filter f, and a
+ *     K step over input row r + ky' uses weight row ky' - j (zero outside 0..7).  The Toeplitz operand is itself an
+ *     overlapping window over a short array of 256-byte weight slabs (SBO = 128, start = (14 - ky') slabs).  With
+ *     16 filters alone M would be 16; eight row offsets fill the 128 lanes at the price of 15 K rows per 8 useful;
+ *   - fp32 accuracy: D = Z_hi.X_hi + Z_lo.X_hi + Z_hi.X_lo in fp32 (TMEM), operands scaled by powers of two.
+ *   Per patch: 2 tiles (conv rows 0..31, 32..63) x 15 input rows x 4 pixel pairs x 3 products = 360 MMAs of
+ *   128x256x16, 128 cycles each: the tensor pipe is the bound (ncu: 96 % active).  Which operand slides matters:
+ *   with the image as the 128-row A operand and N = 128 (720 MMAs) an MMA took 78 cycles instead of 64, because
+ *   shared memory had to deliver 8 KB per 64 cycles and three of four windows are misaligned; at N = 256 the
+ *   operand traffic per cycle is lower and the misalignment disappears behind the math.
  *
- * Kernel (persistent, one CTA per SM, 544 threads): warp 0 issues the MMAs, warps 1-8 drain the accumulators
- * (two sets of four, alternate tiles: pool in registers / by shuffle, bias, activation, store), warps 9-16 stream
- * the next patch in 16-row blocks (fp32 HWC -> fp16 hi/lo) as soon as a block's last reader tile has completed.
+ * Kernel (persistent, one CTA per SM, 544 threads): warp 0 issues the MMAs, warps 1-4 / 5-8 drain the accumulator
+ * of tile 0 / 1 (pool x in registers, pool y by one shuffle, bias, activation, fp16 hi / lo store), warps 9-16
+ * stream the next patch in 16-row blocks (fp32 HWC -> fp16 hi/lo) as soon as a block's last reader tile has completed.
  */
 #include <cfloat>
 #include <cmath>
@@ -127,40 +131,48 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
 
     if (warp == 0) {
         /* ======================= MMA issuer: the whole warp runs the loops (warp-uniform operands), one elected lane
-         * issues ======================= */
-        const uint32_t idesc = instr_desc(128, 128, FMT_F16, FMT_F16);
+         * issues.  A = Toeplitz weight window (128 rows = 8 output-row offsets x 16 filters), B = 256 consecutive
+         * pixels of the image = base rows r, r + 8, r + 16, r + 24 (adjacent in the (y mod 8, y div 8) order) ===== */
+        const uint32_t idesc = instr_desc(128, 256, FMT_F16, FMT_F16);
         const uint32_t s0 = smem_u32(smem);
-        const uint64_t a_hi = smem_desc(s0 + kOffImgHi, 16, 128), a_lo = smem_desc(s0 + kOffImgLo, 16, 128);
-        const uint64_t b_hi = smem_desc(s0 + kOffZHi, kZStride, 128), b_lo = smem_desc(s0 + kOffZLo, kZStride, 128);
+        const uint64_t i_hi = smem_desc(s0 + kOffImgHi, 16, 128), i_lo = smem_desc(s0 + kOffImgLo, 16, 128);
+        const uint64_t z_hi = smem_desc(s0 + kOffZHi, kZStride, 128), z_lo = smem_desc(s0 + kOffZLo, kZStride, 128);
         uint32_t it = 0;
         bool ok = true;
         for (long long patch = blockIdx.x; patch < a.n && ok && !*s_abort; patch += gridDim.x, ++it) {
 #pragma unroll 1
-            for (int t = 0; t < 4; ++t) {
+            for (int t = 0; t < 2; ++t) {
+                /* tile 0 reads image rows 0..38 (16-row blocks 0, 1 and, from ky' = 8 on, 2), tile 1 rows 32..70 */
                 int e = 0;
                 if (!mbar_wait(&acc_empty[t], (it & 1) ^ 1)) e = 1;
-                else if (!mbar_wait(&img_full[t], it & 1)) e = 2;
-                else if (t < 3 && !mbar_wait(&img_full[t + 1], it & 1)) e = 3;
+                else if (!mbar_wait(&img_full[2 * t], it & 1)) e = 2;
+                else if (!mbar_wait(&img_full[2 * t + 1], it & 1)) e = 3;
                 if (e) { if (lane == 0) atomicExch(a.err, e); ok = false; break; }
                 fence_after_sync();
-                const uint32_t d = tmem + t * 128;
+                const uint32_t d = tmem + t * 256;
 #pragma unroll 1
                 for (int ky = 0; ky < 15; ++ky) {
-                    const uint32_t a_row = static_cast<uint32_t>(row_pos(16 * t + ky)) * (kRowBytes >> 4);
-                    const uint32_t b_row = static_cast<uint32_t>(14 - ky) * (256 >> 4);
+                    if (t == 0 && ky == 8) {
+                        if (!mbar_wait(&img_full[2], it & 1)) { if (lane == 0) atomicExch(a.err, 6); ok = false; break; }
+                        fence_after_sync();
+                    }
+                    const uint32_t i_row = static_cast<uint32_t>(row_pos(32 * t + ky)) * (kRowBytes >> 4);
+                    const uint32_t z_row = static_cast<uint32_t>(14 - ky) * (256 >> 4);
                     if (elect_one()) {
 #pragma unroll
                         for (int p = 0; p < 4; ++p) {
-                            const uint32_t ao = a_row + p * 2, bo = b_row + p * 2 * (kZStride >> 4);
-                            mma_f16(d, a_hi + ao, b_hi + bo, idesc, (ky | p) != 0);
-                            mma_f16(d, a_hi + ao, b_lo + bo, idesc, 1);
-                            mma_f16(d, a_lo + ao, b_hi + bo, idesc, 1);
+                            const uint32_t io = i_row + p * 2, zo = z_row + p * 2 * (kZStride >> 4);
+                            mma_f16(d, z_hi + zo, i_hi + io, idesc, (ky | p) != 0);
+                            mma_f16(d, z_lo + zo, i_hi + io, idesc, 1);
+                            mma_f16(d, z_hi + zo, i_lo + io, idesc, 1);
                         }
                     }
                     __syncwarp();
                 }
+                if (!ok) break;
                 if (elect_one()) {
-                    mma_commit(&img_empty[t]);
+                    mma_commit(&img_empty[2 * t]);
+                    mma_commit(&img_empty[2 * t + 1]);
                     mma_commit(&acc_full[t]);
                 }
                 __syncwarp();
@@ -168,85 +180,64 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
         }
         if (!ok) *s_abort = 1;
     } else if (warp <= 8) {
-        /* ======================= epilogue: warps 1-4 drain tiles 0 and 2, warps 5-8 tiles 1 and 3 ======================= */
-        const int set = (warp - 1) >> 2;
+        /* ======================= epilogue: warps 1-4 drain tile 0 (conv rows 0..31), warps 5-8 tile 1 (32..63).
+         * Accumulator lane = (row offset j, filter f), column = (base row b, x).  Lanes j = 2q and 2q + 1 of a pool
+         * window sit 16 apart in the same warp: pool x inside the thread, y by one shuffle, then the even-j lane keeps
+         * the even pooled columns and the odd-j lane the odd ones, so one store instruction fills whole 32-byte
+         * sectors of the packed image ======================= */
+        const int t = (warp - 1) >> 2;
         const int quarter = warp & 3;                 /* the TMEM lane quarter this warp may read */
         const int m = quarter * 32 + lane;            /* accumulator lane */
-        const int grp = m >> 6, x = m & 63;
-        const int px = x >> 1;
-        const bool odd = (x & 1) != 0;                /* even lanes store filters 0..7, odd lanes 8..15 */
-        const bool own_ok = x <= 56, other_ok = (x ^ 1) <= 56;
-        const int fsel = odd ? 8 : 0;
-        float bias_r[8];
-#pragma unroll
-        for (int q = 0; q < 8; ++q) bias_r[q] = s_bias[fsel + q];
+        const int f = m & 15, jpar = (m >> 4) & 1;
+        const float bias = s_bias[f];
+        const float slope = a.act == PE_ACT_PRELU ? s_slope[f] : 0.f;
+        int n_b = 0;                                  /* base rows of this tile with a valid conv row for this warp */
+        for (int b = 0; b < 4; ++b) n_b += (32 * t + 8 * b + 2 * quarter) <= 56;
         float amax = 0.f;
         uint32_t it = 0;
         for (long long patch = blockIdx.x; patch < a.n && !*s_abort; patch += gridDim.x, ++it) {
-            float* out = a.pool1 + patch * (long long)kP1Patch + fsel * kP1Plane + px;
-            unsigned char* outp = a.p1_packed + patch * (long long)kP1PackedBytes + (odd ? kP1PlaneBytes : 0) + px * 16;
+            float* out = a.pool1 + patch * (long long)kP1Patch + f * kP1Plane;
+            unsigned char* outp = a.p1_packed + patch * (long long)kP1PackedBytes + (f >> 3) * kP1PlaneBytes + (f & 7) * 2;
+            if (!mbar_wait(&acc_full[t], it & 1)) { atomicExch(a.err, 4); *s_abort = 1; break; }
+            fence_after_sync();
+            const uint32_t tbase = tmem + t * 256 + (static_cast<uint32_t>(quarter * 32) << 16);
 #pragma unroll 1
-            for (int t = set; t < 4; t += 2) {
-                if (!mbar_wait(&acc_full[t], it & 1)) { atomicExch(a.err, 4); *s_abort = 1; break; }
-                fence_after_sync();
-                const uint32_t tbase = tmem + t * 128 + (static_cast<uint32_t>(quarter * 32) << 16);
-                const int r = 16 * t + 8 * grp;        /* base conv row of this lane */
-#pragma unroll 1
-                for (int half = 0; half < 2; ++half) {
-                    uint32_t v[2][32];
-                    tmem_ld32(tbase + half * 64, v[0]);
-                    tmem_ld32(tbase + half * 64 + 32, v[1]);
+            for (int b = 0; b < n_b; ++b) {
+                const int ye = 32 * t + 8 * b + 2 * quarter;          /* conv rows ye (even-j lanes) and ye + 1 */
+                const int py = ye >> 1;
+                const bool row_o_ok = ye + 1 <= 56;
+                const bool own_ok = jpar ? row_o_ok : true, oth_ok = jpar ? true : row_o_ok;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t v[32];
+                    tmem_ld32(tbase + b * 64 + h * 32, v);
                     tmem_ld_wait();
-                    if (half == 1) {       /* every column of the tile is in registers: hand the accumulator back */
+                    if (b == n_b - 1 && h == 1) {  /* every column this warp needs is in registers: hand the accumulator back */
                         fence_before_sync();
                         __syncwarp();
                         if (lane == 0) mbar_arrive(&acc_empty[t]);
                     }
 #pragma unroll
-                    for (int j2 = 0; j2 < 2; ++j2) {
-                        const int ya = r + 4 * half + 2 * j2;   /* conv rows ya, ya + 1 -> pooled row ya / 2 */
-                        const int py = ya >> 1;
-                        const bool row_b = ya + 1 <= 56;
-                        /* pool in y inside the lane, then swap the half of the filters the neighbour keeps */
-                        float mine[8], send[8];
-#pragma unroll
-                        for (int q = 0; q < 8; ++q) {
-                            float c0 = __uint_as_float(v[j2][q]), c1 = __uint_as_float(v[j2][8 + q]);
-                            if (row_b) {
-                                c0 = fmaxf(c0, __uint_as_float(v[j2][16 + q]));
-                                c1 = fmaxf(c1, __uint_as_float(v[j2][24 + q]));
-                            }
-                            mine[q] = odd ? c1 : c0;
-                            send[q] = odd ? c0 : c1;
-                        }
-                        float keep[8];
-#pragma unroll
-                        for (int q = 0; q < 8; ++q) {
-                            const float o = __shfl_xor_sync(0xffffffffu, send[q], 1);
-                            float c = own_ok ? mine[q] : -FLT_MAX;
-                            if (other_ok) c = fmaxf(c, o);
-                            const float sl = a.act == PE_ACT_PRELU ? s_slope[fsel + q] : 0.f;
-                            keep[q] = act_apply(fmaf(c, a.inv_scale, bias_r[q]), a.act, sl);
-                        }
-                        if (ya <= 56 && px <= 28) {
+                    for (int i2 = 0; i2 < 8; ++i2) {
+                        const int x0 = 32 * h + 4 * i2;                 /* pooled columns x0 / 2 and x0 / 2 + 1 */
+                        const float m0 = x0 + 1 <= 56 ? fmaxf(__uint_as_float(v[4 * i2]), __uint_as_float(v[4 * i2 + 1])) : __uint_as_float(v[4 * i2]);
+                        const float m1 = x0 + 3 <= 56 ? fmaxf(__uint_as_float(v[4 * i2 + 2]), __uint_as_float(v[4 * i2 + 3])) : __uint_as_float(v[4 * i2 + 2]);
+                        const float o = __shfl_xor_sync(0xffffffffu, jpar ? m0 : m1, 16);
+                        float c = own_ok ? (jpar ? m1 : m0) : -FLT_MAX;
+                        if (oth_ok) c = fmaxf(c, o);
+                        const int px = 16 * h + 2 * i2 + jpar;
+                        const float keep = act_apply(fmaf(c, a.inv_scale, bias), a.act, slope);
+                        if (px <= 28) {
                             if (a.p1_packed) {
                                 /* conv2_tc's A operand: [term][channel block][row (y%8, y/8)][32 px][8 channels] fp16 */
-                                uint32_t hi[4], lo[4];
-#pragma unroll
-                                for (int q = 0; q < 4; ++q) {
-                                    __half h0, l0, h1, l1;
-                                    amax = fmaxf(amax, fmaxf(fabsf(keep[2 * q]), fabsf(keep[2 * q + 1])));
-                                    split_f16(keep[2 * q] * kP1Scale, h0, l0);
-                                    split_f16(keep[2 * q + 1] * kP1Scale, h1, l1);
-                                    hi[q] = pack2(h0, h1);
-                                    lo[q] = pack2(l0, l1);
-                                }
-                                unsigned char* dst = outp + p1_row_pos(py) * 512;
-                                *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                                *reinterpret_cast<uint4*>(dst + 2 * kP1PlaneBytes) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                                __half hi, lo;
+                                amax = fmaxf(amax, fabsf(keep));
+                                split_f16(keep * kP1Scale, hi, lo);
+                                unsigned char* dst = outp + p1_row_pos(py) * 512 + px * 16;
+                                *reinterpret_cast<__half*>(dst) = hi;
+                                *reinterpret_cast<__half*>(dst + 2 * kP1PlaneBytes) = lo;
                             } else {
-#pragma unroll
-                                for (int q = 0; q < 8; ++q) out[q * kP1Plane + py * kP1W] = keep[q];
+                                out[py * kP1W + px] = keep;
                             }
                         }
                     }

@@ -319,12 +319,12 @@ def gpu_arm(args, rank, world, local_rank, dist):
                      "frac": achieved_tf / peaks["bf16_tflops_sustained"], "traffic": traffic,
                      "peak_source": f"{peaks['source']} bf16 sustained (kernel timed inside a long step)",
                      "note": ("tcgen05 split-fp16 implicit GEMM: achieved = ALGORITHMIC conv1 FLOPs (2 x 23,288,832 per patch) / launch time; "
-                              "the kernel executes 8.1x that in tensor FLOPs (x3 fp16 split for fp32 parity, x1.875 Toeplitz widening to N=128, "
+                              "the kernel executes 8.1x that in tensor FLOPs (x3 fp16 split for fp32 parity, x1.875 Toeplitz widening of the 16 filters to 128 accumulator lanes, "
                               "x8/7 channel pad, x1.26 tile edges), see executed_tflops / executed_frac") if fwd_tensor else
                              "fp32 SIMT kernel: the pipe that binds it is FP32 FMA (~74 TFLOP/s at 1965 MHz), see fp32_fma_frac",
                      "algorithmic_flops_per_launch": conv1_flops, "launch_ms": conv1_ms,
-                     "executed_tflops": (720 * 2.0 * 128 * 128 * 16 * BATCH / (conv1_ms * 1e-3) / 1e12) if (fwd_tensor and conv1_ms > 0) else None,
-                     "executed_frac": (720 * 2.0 * 128 * 128 * 16 * BATCH / (conv1_ms * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"]) if (fwd_tensor and conv1_ms > 0) else None,
+                     "executed_tflops": (360 * 2.0 * 128 * 256 * 16 * BATCH / (conv1_ms * 1e-3) / 1e12) if (fwd_tensor and conv1_ms > 0) else None,
+                     "executed_frac": (360 * 2.0 * 128 * 256 * 16 * BATCH / (conv1_ms * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"]) if (fwd_tensor and conv1_ms > 0) else None,
                      "fp32_fma_frac": None if fwd_tensor else achieved_tf / 74.4,
                      "achieved_hbm_gbs": BATCH * (7 * 64 * 64 * 4 + (81920 if fwd_tensor else 16 * 30 * 32 * 4)) / (conv1_ms * 1e-3) / 1e9 if conv1_ms > 0 else 0.0,
                      "hbm_peak_gbs": peaks["hbm_gbs"]},

@@ -356,6 +356,129 @@ __global__ void __launch_bounds__(128) tmem_ld_rate_kernel(int reps, long long* 
     if (warp == 0) tmem_dealloc<256>(tmem_slot);
 }
 
+/* ---- 2c. roles swapped: A = 128 weight rows (aligned), B = N consecutive pixels of the HWC8 image (sliding, 32-byte
+ *          misaligned windows).  b_mode 0: conv-like windows, 1: always the same aligned window -------------- */
+template <int N>
+__global__ void __launch_bounds__(128) mma_rate_swap_kernel(int reps, int b_mode, int a_var, long long* __restrict__ cycles, int* __restrict__ status) {
+    extern __shared__ __align__(128) unsigned char dyn[];
+    __half* s_img = reinterpret_cast<__half*>(dyn);               /* 64 KB of zeros: an HWC8 image */
+    __half* s_w = reinterpret_cast<__half*>(dyn + 65536);         /* 8 x (128 x 16 fp16, [2 chunks][128][8]) */
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < (65536 + 8 * 4096) / 16; i += 128) reinterpret_cast<uint4*>(dyn)[i] = make_uint4(0, 0, 0, 0);
+    fence_async_smem();
+    if (warp == 0) tmem_alloc<512>(&tmem_slot);
+    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = tmem_slot;
+    if (tid == 0) {
+        const uint32_t idesc = instr_desc(128, N, FMT_F16, FMT_F16);
+        const uint64_t a0 = smem_desc(smem_u32(s_w), 128 * 16, 128);
+        const uint64_t b0 = smem_desc(smem_u32(s_img), 16, 128);
+        const long long t0 = clock64();
+        for (int r = 0; r < reps; ++r) {
+            const uint32_t off = b_mode == 0 ? static_cast<uint32_t>(((r & 7) * 64 + ((r >> 3) & 3) * 2 + ((r >> 5) & 15) * 128) * 16) : 0u;
+            const uint32_t aoff = a_var > 0 ? static_cast<uint32_t>(((r >> (a_var - 1)) & 7) << 12) : 0u;   /* a_var 1: new A every MMA, 2: every 2, 3: every 4 */
+            mma_f16(tmem + ((r >> 7) & 1) * N, desc_advance(a0, aoff), desc_advance(b0, off), idesc, (r & 127) > 0);
+        }
+        mma_commit(&bar);
+        const bool ok = mbar_wait(&bar, 0);
+        cycles[0] = clock64() - t0;
+        if (!ok) atomicExch(status, 2);
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<512>(tmem);
+}
+
+template <int N>
+int run_rate_swap(int b_mode, int a_var, long long* d_cycles, int* d_status) {
+    const int reps = 2048;
+    const size_t smem = 65536 + 8 * 4096;
+    CK(cudaFuncSetAttribute(mma_rate_swap_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    for (int i = 0; i < 2; ++i) {
+        mma_rate_swap_kernel<N><<<1, 128, smem>>>(reps, b_mode, a_var, d_cycles, d_status);
+        CK(cudaDeviceSynchronize());
+    }
+    long long c = 0;
+    CK(cudaMemcpy(&c, d_cycles, sizeof(c), cudaMemcpyDeviceToHost));
+    printf("mma_rate_swap (A = weights, B = image window) N=%3d b_mode=%d a_var=%d: %.1f cycles/MMA\n", N, b_mode, a_var, (double)c / reps);
+    return 0;
+}
+
+/* ---- 2d. the conv1 issue pattern (A = Toeplitz weight windows, B = 256-pixel image windows, three split products),
+ *          with parts of the address pattern frozen by `flags`: 1 A always the hi array, 2 B always the hi image,
+ *          4 p = 0 only (aligned image windows), 8 ky = 0 only, 16 A window fixed, 32 p advances the A window only ---- */
+__global__ void __launch_bounds__(128) mma_conv_pattern_kernel(int tiles, int flags, long long* __restrict__ cycles, int* __restrict__ status) {
+    extern __shared__ __align__(1024) unsigned char dyn[];
+    constexpr int kImg = 72 * 1024, kZ = 127 * 256, kZStride = 15 * 256;
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < (2 * kImg + 2 * kZ) / 16; i += 128) reinterpret_cast<uint4*>(dyn)[i] = make_uint4(0, 0, 0, 0);
+    fence_async_smem();
+    if (warp == 0) tmem_alloc<512>(&tmem_slot);
+    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = tmem_slot;
+    if (warp == 0) {
+        const uint32_t idesc = instr_desc(128, 256, FMT_F16, FMT_F16);
+        const uint32_t s0 = smem_u32(dyn);
+        const uint64_t i_hi = smem_desc(s0, 16, 128), i_lo = (flags & 2) ? i_hi : smem_desc(s0 + kImg, 16, 128);
+        const uint64_t z_hi = smem_desc(s0 + 2 * kImg, kZStride, 128), z_lo = (flags & 1) ? z_hi : smem_desc(s0 + 2 * kImg + kZ, kZStride, 128);
+        const long long t0 = clock64();
+        for (int t = 0; t < tiles; ++t) {
+            const uint32_t d = tmem + (t & 1) * 256;
+#pragma unroll 1
+            for (int ky = 0; ky < 15; ++ky) {
+                const int kye = (flags & 8) ? 0 : ky;
+                const int y = 32 * (t & 1) + kye;
+                const uint32_t i_row = static_cast<uint32_t>((y & 7) * 9 + (y >> 3)) * 64;
+                const uint32_t z_row = (flags & 16) ? 0u : static_cast<uint32_t>(14 - kye) * 16;
+                if (elect_one()) {
+#pragma unroll
+                    for (int p = 0; p < 4; ++p) {
+                        const uint32_t io = i_row + ((flags & (4 | 32)) ? 0 : p * 2), zo = z_row + ((flags & 16) ? 0 : p * 2 * (kZStride >> 4));
+                        mma_f16(d, z_hi + zo, i_hi + io, idesc, (ky | p) != 0);
+                        mma_f16(d, z_lo + zo, i_hi + io, idesc, 1);
+                        mma_f16(d, z_hi + zo, i_lo + io, idesc, 1);
+                    }
+                }
+                __syncwarp();
+            }
+        }
+        if (elect_one()) mma_commit(&bar);
+        __syncwarp();
+        const bool ok = mbar_wait(&bar, 0);
+        if (tid == 0) {
+            cycles[0] = clock64() - t0;
+            if (!ok) atomicExch(status, 2);
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<512>(tmem);
+}
+
+int run_conv_pattern(int flags, long long* d_cycles, int* d_status) {
+    const int tiles = 16;
+    const size_t smem = 2 * 72 * 1024 + 2 * 127 * 256;
+    CK(cudaFuncSetAttribute(mma_conv_pattern_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    for (int i = 0; i < 2; ++i) {
+        mma_conv_pattern_kernel<<<1, 128, smem>>>(tiles, flags, d_cycles, d_status);
+        CK(cudaDeviceSynchronize());
+    }
+    long long c = 0;
+    CK(cudaMemcpy(&c, d_cycles, sizeof(c), cudaMemcpyDeviceToHost));
+    printf("conv1 pattern flags=%2d: %.1f cycles/MMA (128x256x16)\n", flags, (double)c / (tiles * 180));
+    return 0;
+}
+
 template <int N>
 int run_rate(int a_mode, long long* d_cycles, int* d_status) {
     const int reps = 2048;
@@ -417,6 +540,14 @@ int main() {
             if (run_rate<64>(a_mode, d_cycles, d_status)) return 1;
             if (run_rate<128>(a_mode, d_cycles, d_status)) return 1;
             if (run_rate<256>(a_mode, d_cycles, d_status)) return 1;
+        }
+        for (int flags : {0, 1, 2, 3, 4, 8, 16, 32, 4 | 16, 1 | 2 | 4 | 8 | 16})
+            if (run_conv_pattern(flags, d_cycles, d_status)) return 1;
+        for (int b_mode = 0; b_mode < 1; ++b_mode) {
+            for (int a_var : {0, 1, 2, 3}) {
+                if (run_rate_swap<128>(b_mode, a_var, d_cycles, d_status)) return 1;
+                if (run_rate_swap<256>(b_mode, a_var, d_cycles, d_status)) return 1;
+            }
         }
         for (int a_lbo : {2048})
             for (int per : {4})
