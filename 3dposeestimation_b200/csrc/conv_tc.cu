@@ -304,10 +304,10 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
  * 8-channel blocks are the two K chunks, LBO = one plane), N = 8 output rows x 8 filter slots = 64 through a
  * Toeplitz window over 128-byte weight slabs, one 128-lane tile = base rows 0, 8, 16, 24 x 32 pixels.
  * 12 x 5 x 3 = 180 MMAs (128x64x16) per patch. */
-constexpr int kZ2Slabs = 127, kZ2Bytes = kZ2Slabs * 128, kZ2Stride = 12 * 128;
+constexpr int kZ2Slabs = 127, kZ2Bytes = kZ2Slabs * 256, kZ2Stride = 12 * 256;   /* a slab = [hi 8 x 8][lo 8 x 8] halves */
 constexpr int kC2OffImg = 0;                                   /* 2 x kP1PackedBytes */
-constexpr int kC2OffZ = 2 * kP1PackedBytes;                    /* hi | lo */
-constexpr int kC2OffMisc = kC2OffZ + 2 * kZ2Bytes;
+constexpr int kC2OffZ = 2 * kP1PackedBytes;
+constexpr int kC2OffMisc = kC2OffZ + kZ2Bytes;
 constexpr int kC2TcSmem = kC2OffMisc + 256;
 constexpr int kC2TcThreads = 192;
 constexpr int kPool2Ld = 1184;
@@ -315,7 +315,7 @@ constexpr int kPool2Ld = 1184;
 struct C2Args {
     const unsigned char* p1_packed;
     long long n;
-    const uint4* ztoeplitz;    /* hi then lo, kZ2Bytes each */
+    const uint4* ztoeplitz;    /* kZ2Bytes: hi and lo slabs interleaved */
     const float* bias;         /* [8] */
     const float* slope;        /* [8] or null */
     int act;
@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(kC2TcThreads, 1) conv2_tc_kernel(const C2Args 
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
     volatile int* s_abort = reinterpret_cast<volatile int*>(tmem_slot + 1);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    for (int i = tid; i < 2 * kZ2Bytes / 16; i += kC2TcThreads) reinterpret_cast<uint4*>(smem + kC2OffZ)[i] = a.ztoeplitz[i];
+    for (int i = tid; i < kZ2Bytes / 16; i += kC2TcThreads) reinterpret_cast<uint4*>(smem + kC2OffZ)[i] = a.ztoeplitz[i];
     if (tid < 8) {
         s_bias[tid] = a.bias[tid];
         s_slope[tid] = a.slope ? a.slope[tid] : 0.f;
@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(kC2TcThreads, 1) conv2_tc_kernel(const C2Args 
         *s_abort = 0;
         mbar_fence_init();
     }
-    if (warp == 0) tmem_alloc<128>(tmem_slot);
+    if (warp == 0) tmem_alloc<256>(tmem_slot);
     fence_async_smem();
     fence_before_sync();
     __syncthreads();
@@ -370,9 +370,9 @@ __global__ void __launch_bounds__(kC2TcThreads, 1) conv2_tc_kernel(const C2Args 
         }
     } else if (warp == 1) {
         /* MMA issuer: whole warp, one elected lane issues (see conv1) */
-        const uint32_t idesc = instr_desc(128, 64, FMT_F16, FMT_F16);
+        const uint32_t idesc = instr_desc(128, 128, FMT_F16, FMT_F16);
         const uint32_t s0 = smem_u32(smem);
-        const uint64_t b_hi = smem_desc(s0 + kC2OffZ, kZ2Stride, 128), b_lo = smem_desc(s0 + kC2OffZ + kZ2Bytes, kZ2Stride, 128);
+        const uint64_t b_cat = smem_desc(s0 + kC2OffZ, kZ2Stride, 128);
         uint32_t it = 0;
         bool ok = true;
         for (long long patch = blockIdx.x; patch < a.n && ok && !*s_abort; patch += gridDim.x, ++it) {
@@ -383,18 +383,17 @@ __global__ void __launch_bounds__(kC2TcThreads, 1) conv2_tc_kernel(const C2Args 
             fence_after_sync();
             const uint32_t img = s0 + kC2OffImg + s * kP1PackedBytes;
             const uint64_t a_hi = smem_desc(img, kP1PlaneBytes, 128), a_lo = smem_desc(img + 2 * kP1PlaneBytes, kP1PlaneBytes, 128);
-            const uint32_t d = tmem + s * 64;
+            const uint32_t d = tmem + s * 128;
 #pragma unroll 1
             for (int ky = 0; ky < 12; ++ky) {
                 const uint32_t a_row = static_cast<uint32_t>(p1_row_pos(ky)) * (512 >> 4);
-                const uint32_t b_row = static_cast<uint32_t>(11 - ky) * (128 >> 4);
+                const uint32_t b_row = static_cast<uint32_t>(11 - ky) * (256 >> 4);
                 if (elect_one()) {
 #pragma unroll
                     for (int kx = 0; kx < 5; ++kx) {
                         const uint32_t ao = a_row + kx, bo = b_row + kx * 2 * (kZ2Stride >> 4);
-                        mma_f16(d, a_hi + ao, b_hi + bo, idesc, (ky | kx) != 0);
-                        mma_f16(d, a_hi + ao, b_lo + bo, idesc, 1);
-                        mma_f16(d, a_lo + ao, b_hi + bo, idesc, 1);
+                        mma_f16(d, a_hi + ao, b_cat + bo, idesc, (ky | kx) != 0);
+                        mma_f16(d, a_lo + ao, b_cat + bo, idesc, 1);
                     }
                 }
                 __syncwarp();
@@ -418,11 +417,28 @@ __global__ void __launch_bounds__(kC2TcThreads, 1) conv2_tc_kernel(const C2Args 
             const int s = it & 1;
             if (!mbar_wait(&acc_full[s], (it >> 1) & 1)) { atomicExch(a.err, 24); *s_abort = 1; break; }
             fence_after_sync();
-            const uint32_t tbase = tmem + s * 64 + (static_cast<uint32_t>(quarter * 32) << 16);
+            const uint32_t tbase = tmem + s * 128 + (static_cast<uint32_t>(quarter * 32) << 16);
+            /* columns (row offset j, term, filter slot): the hi and lo weight slabs alternate, their sums are the result */
             uint32_t v[2][32];
-            tmem_ld32(tbase, v[0]);
-            tmem_ld32(tbase + 32, v[1]);
-            tmem_ld_wait();
+            {
+                uint32_t w[2][32];
+                tmem_ld32(tbase, w[0]);
+                tmem_ld32(tbase + 32, w[1]);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+#pragma unroll
+                    for (int q = 0; q < 8; ++q)
+                        v[0][j * 8 + q] = __float_as_uint(__uint_as_float(w[j >> 1][(j & 1) * 16 + q]) + __uint_as_float(w[j >> 1][(j & 1) * 16 + 8 + q]));
+                tmem_ld32(tbase + 64, w[0]);
+                tmem_ld32(tbase + 96, w[1]);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+#pragma unroll
+                    for (int q = 0; q < 8; ++q)
+                        v[1][j * 8 + q] = __float_as_uint(__uint_as_float(w[j >> 1][(j & 1) * 16 + q]) + __uint_as_float(w[j >> 1][(j & 1) * 16 + 8 + q]));
+            }
             fence_before_sync();
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_empty[s]);
@@ -447,7 +463,7 @@ __global__ void __launch_bounds__(kC2TcThreads, 1) conv2_tc_kernel(const C2Args 
     }
     fence_before_sync();
     __syncthreads();
-    if (warp == 0) tmem_dealloc<128>(tmem);
+    if (warp == 0) tmem_dealloc<256>(tmem);
 }
 
 }  // namespace
@@ -510,7 +526,7 @@ int conv2_tc_prepare(pe_net* net) {
     if (!(wmax > 0.f) || !std::isfinite(wmax)) return PE_OK;
     const int log2_sw = 10 - std::ilogb(wmax);
     const float sw = std::ldexp(1.f, log2_sw);
-    std::vector<uint16_t> z((size_t)2 * kZ2Bytes / 2, 0);
+    std::vector<uint16_t> z((size_t)kZ2Bytes / 2, 0);
     for (int kx = 0; kx < 5; ++kx)
         for (int ky = 0; ky < 5; ++ky)
             for (int f = 0; f < 7; ++f)
@@ -522,13 +538,13 @@ int conv2_tc_prepare(pe_net* net) {
                     memcpy(&hb, &h, 2);
                     memcpy(&lb, &l, 2);
                     const size_t slab = (size_t)(kx * 2 + c / 8) * 12 + 7 + (4 - ky);
-                    const size_t at = slab * 64 + (size_t)f * 8 + (c % 8);
+                    const size_t at = slab * 128 + (size_t)f * 8 + (c % 8);      /* in halves: hi rows, then the 8 lo rows */
                     z[at] = hb;
-                    z[(size_t)kZ2Bytes / 2 + at] = lb;
+                    z[at + 64] = lb;
                 }
     PE_CUDA(cudaSetDevice(net->device));
-    if (!net->d_z2) PE_CUDA(cudaMalloc(&net->d_z2, 2 * kZ2Bytes));
-    PE_CUDA(cudaMemcpy(net->d_z2, z.data(), 2 * kZ2Bytes, cudaMemcpyHostToDevice));
+    if (!net->d_z2) PE_CUDA(cudaMalloc(&net->d_z2, kZ2Bytes));
+    PE_CUDA(cudaMemcpy(net->d_z2, z.data(), kZ2Bytes, cudaMemcpyHostToDevice));
     net->c2_inv_scale = std::ldexp(1.f, -(log2_sw + 4));      /* activations carry kP1Scale = 2^4 */
     net->c2_tc_ready = true;
     return PE_OK;
