@@ -345,11 +345,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                     const uint32_t s = gi & (kTcStages - 1);
                     const uint32_t ph = (gi >> 1) & 1u;
                     TC_DBG_ADD(2, tm);
-                    if (!mbar_wait(te0, ph ^ 1u) || !mbar_wait(te0 + 1, ph ^ 1u)) { if (lane == 0) atomicExch(a.err, 4); ok = false; break; }
-                    TC_DBG_ADD(1, tm);
                     if (!mbar_wait(&full[s], (gi / kTcStages) & 1u)) { if (lane == 0) atomicExch(a.err, 3); ok = false; break; }
-                    fence_after_sync();
                     TC_DBG_ADD(0, tm);
+                    /* the two accumulators of the set are handed back half a tile apart: issue for each as soon as it is
+                     * free instead of waiting for both */
+                    if (!mbar_wait(te0, ph ^ 1u)) { if (lane == 0) atomicExch(a.err, 4); ok = false; break; }
+                    fence_after_sync();
+                    TC_DBG_ADD(1, tm);
                     const uint32_t off = s * (L::stage_bytes >> 4);
                     if (elect_one()) {
                         if (MODE == 0) {
@@ -357,15 +359,24 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                             mma_f16(d0, a0_hi, b_lo0 + off, idesc, 1);
                             mma_f16(d0, a0_lo, b_hi0 + off, idesc, 1);
                             mma_f16(d0, a0_n, b_n0 + off, idesc, 1);
-                            mma_commit(tf0);
+                        } else {
+                            /* -dot of the +-1 expansions, 32 bits per MMA: R = 2 * hamming - bits */
+                            for (int j = 0; j < a.words; ++j) mma_f8(d0, a0_hi + j * 256, b_hi0 + off + j * 256, idesc, j > 0);
+                        }
+                        mma_commit(tf0);
+                    }
+                    __syncwarp();
+                    TC_DBG_ADD(2, tm);
+                    if (!mbar_wait(te0 + 1, ph ^ 1u)) { if (lane == 0) atomicExch(a.err, 4); ok = false; break; }
+                    fence_after_sync();
+                    TC_DBG_ADD(1, tm);
+                    if (elect_one()) {
+                        if (MODE == 0) {
                             mma_f16(d1, a1_hi, b_hi0 + off, idesc, 0);
                             mma_f16(d1, a1_hi, b_lo0 + off, idesc, 1);
                             mma_f16(d1, a1_lo, b_hi0 + off, idesc, 1);
                             mma_f16(d1, a1_n, b_n0 + off, idesc, 1);
                         } else {
-                            /* -dot of the +-1 expansions, 32 bits per MMA: R = 2 * hamming - bits */
-                            for (int j = 0; j < a.words; ++j) mma_f8(d0, a0_hi + j * 256, b_hi0 + off + j * 256, idesc, j > 0);
-                            mma_commit(tf0);
                             for (int j = 0; j < a.words; ++j) mma_f8(d1, a1_hi + j * 256, b_hi0 + off + j * 256, idesc, j > 0);
                         }
                         mma_commit(tf0 + 1);
