@@ -30,7 +30,10 @@
  */
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+
+#include <cuda_fp8.h>
 
 #include "common.h"
 #include "umma.cuh"
@@ -53,6 +56,12 @@ constexpr int kOffMisc = kOffZLo + kZBytes;        /* bias[16] slope[16] barrier
 constexpr int kC1TcSmem = kOffMisc + 512;
 constexpr int kC1TcThreads = 544;
 constexpr int kLog2Sx = 8;                         /* image scale 2^8: |x| <= 255 stays finite in fp16 */
+/* fp8 cross terms (F8 kernels): per pixel 16 bytes [x8: e4m3(x s_x 2^-4) x 8 ch | lo8: e4m3((x s_x - hi) 2^6) x 8 ch]
+ * against weight slabs [lo_w8: e4m3((w s_w - hi_w) 2^4) | w8: e4m3(w s_w 2^-6)], so one kind::f8f6f4 MMA (K = 32 =
+ * two pixels x 16 slots) adds hi_x.lo_w + lo_x.w at the scale s_x s_w of the fp16 hi.hi product.  With |w s_w| < 2^11
+ * and |x| <= 28: |x8| <= 448, |lo8| <= 128, |lo_w8| <= 8, |w8| < 32 - all inside e4m3's finite range */
+constexpr int kF8XDown = 4, kF8LoUp = 6;
+constexpr float kF8MaxInput = 28.f;
 
 constexpr int kP1H = 30, kP1W = 32, kP1Plane = kP1H * kP1W, kP1Patch = 16 * kP1Plane;   /* as forward.cu */
 
@@ -89,9 +98,11 @@ struct C1Args {
     float* pool1;              /* [n][16][30][32] fp32 (SIMT conv2) */
     unsigned char* p1_packed;  /* or, for conv2_tc: [n][hi,lo][2 channel blocks][40 rows][32 px][8 ch] fp16 */
     int* err;                  /* pinned flag: 1.. barrier time-out, 100 input magnitude above 255 */
+    int dbg;                   /* PE_C1_DBG experiments (results are wrong when set): 1 no stores, 2 no shuffles, 4 loaders do not
+                                  store after the first patch, 8 no MMAs, 16 no global loads after the first patch */
 };
 
-template <int CP>
+template <int CP, bool F8, bool PACKED>
 __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args a) {
     extern __shared__ __align__(1024) unsigned char smem[];
     float* s_bias = reinterpret_cast<float*>(smem + kOffMisc);
@@ -107,7 +118,11 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     /* one-time: zero the image buffers (pad rows and the unused channel slot stay zero), load the Toeplitz weights */
     for (int i = tid; i < 2 * kImgBytes / 16; i += kC1TcThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
-    for (int i = tid; i < 2 * kZBytes / 16; i += kC1TcThreads) reinterpret_cast<uint4*>(smem + kOffZHi)[i] = a.ztoeplitz[i];
+    /* second weight buffer: the fp16 lo term, or (F8) the e4m3 [lo_w | w] slabs that follow it in ztoeplitz */
+    for (int i = tid; i < kZBytes / 16; i += kC1TcThreads) {
+        reinterpret_cast<uint4*>(smem + kOffZHi)[i] = a.ztoeplitz[i];
+        reinterpret_cast<uint4*>(smem + kOffZLo)[i] = a.ztoeplitz[(F8 ? 2 : 1) * (kZBytes / 16) + i];
+    }
     if (tid < 16) {
         s_bias[tid] = a.bias[tid];
         s_slope[tid] = a.slope ? a.slope[tid] : 0.f;
@@ -158,13 +173,17 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
                     }
                     const uint32_t i_row = static_cast<uint32_t>(row_pos(32 * t + ky)) * (kRowBytes >> 4);
                     const uint32_t z_row = static_cast<uint32_t>(14 - ky) * (256 >> 4);
-                    if (elect_one()) {
+                    if (!(a.dbg & 8) && elect_one()) {
 #pragma unroll
                         for (int p = 0; p < 4; ++p) {
                             const uint32_t io = i_row + p * 2, zo = z_row + p * 2 * (kZStride >> 4);
                             mma_f16(d, z_hi + zo, i_hi + io, idesc, (ky | p) != 0);
-                            mma_f16(d, z_lo + zo, i_hi + io, idesc, 1);
-                            mma_f16(d, z_hi + zo, i_lo + io, idesc, 1);
+                            if (F8) {
+                                mma_f8(d, z_lo + zo, i_lo + io, idesc, 1);     /* hi_x.lo_w + lo_x.w in e4m3, K = 32 */
+                            } else {
+                                mma_f16(d, z_lo + zo, i_hi + io, idesc, 1);
+                                mma_f16(d, z_hi + zo, i_lo + io, idesc, 1);
+                            }
                         }
                     }
                     __syncwarp();
@@ -191,64 +210,130 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
         const int f = m & 15, jpar = (m >> 4) & 1;
         const float bias = s_bias[f];
         const float slope = a.act == PE_ACT_PRELU ? s_slope[f] : 0.f;
+        const int fodd = f & 1;
+        const bool is_elu = a.act == PE_ACT_ELU;
+        const bool is_lin = a.act != PE_ACT_RELU && a.act != PE_ACT_ELU && a.act != PE_ACT_PRELU;
         int n_b = 0;                                  /* base rows of this tile with a valid conv row for this warp */
         for (int b = 0; b < 4; ++b) n_b += (32 * t + 8 * b + 2 * quarter) <= 56;
         float amax = 0.f;
+        uint32_t sink = 0;
         uint32_t it = 0;
         for (long long patch = blockIdx.x; patch < a.n && !*s_abort; patch += gridDim.x, ++it) {
             float* out = a.pool1 + patch * (long long)kP1Patch + f * kP1Plane;
-            unsigned char* outp = a.p1_packed + patch * (long long)kP1PackedBytes + (f >> 3) * kP1PlaneBytes + (f & 7) * 2;
+            unsigned char* outp = a.p1_packed + ((a.dbg & 128) ? (long long)blockIdx.x : patch) * (long long)kP1PackedBytes + (f >> 3) * kP1PlaneBytes + (f & 6) * 2;
             if (!mbar_wait(&acc_full[t], it & 1)) { atomicExch(a.err, 4); *s_abort = 1; break; }
             fence_after_sync();
             const uint32_t tbase = tmem + t * 256 + (static_cast<uint32_t>(quarter * 32) << 16);
+            /* one 16-column group (base row b, quarter g) of this thread's accumulator lane: pool x in the thread, send the
+             * partner lane its half, pool y, bias, activation, store.  Under the tensor pipe's operand traffic every
+             * shuffle / store spends ~150 cycles in the memory-instruction queue, so the four shuffles and the eight
+             * stores of a group are issued back to back (row pointer + immediate offsets, no per-store address) */
+            auto drain = [&](const uint32_t (&v)[16], int g, bool own_ok, bool oth_ok, unsigned char* rowp, float* rowf) {
+                float mine[4], snd[4], oth[4], keep[4];
+#pragma unroll
+                for (int i2 = 0; i2 < 4; ++i2) {
+                    const int x0 = 16 * g + 4 * i2;                 /* pooled columns x0 / 2 and x0 / 2 + 1 */
+                    const float m0 = x0 + 1 <= 56 ? fmaxf(__uint_as_float(v[4 * i2]), __uint_as_float(v[4 * i2 + 1])) : __uint_as_float(v[4 * i2]);
+                    const float m1 = x0 + 3 <= 56 ? fmaxf(__uint_as_float(v[4 * i2 + 2]), __uint_as_float(v[4 * i2 + 3])) : __uint_as_float(v[4 * i2 + 2]);
+                    mine[i2] = jpar ? m1 : m0;
+                    snd[i2] = jpar ? m0 : m1;
+                }
+#pragma unroll
+                for (int i2 = 0; i2 < 4; ++i2) oth[i2] = (a.dbg & 2) ? snd[i2] : __shfl_xor_sync(0xffffffffu, snd[i2], 16);
+#pragma unroll
+                for (int i2 = 0; i2 < 4; ++i2) {
+                    float c = own_ok ? mine[i2] : -FLT_MAX;
+                    if (oth_ok) c = fmaxf(c, oth[i2]);
+                    /* branch-free activation: ReLU / PReLU = pos + slope neg (slope 0 for ReLU), ELU = pos + (e^neg - 1) */
+                    const float y = fmaf(c, a.inv_scale, bias);
+                    const float pos = fmaxf(y, 0.f), neg = fminf(y, 0.f);
+                    const float tail = is_elu ? expf(neg) - 1.0f : slope * neg;
+                    keep[i2] = is_lin ? y : pos + tail;
+                }
+                if (a.dbg & 1) return;
+                if (PACKED) {
+                    /* conv2_tc's A operand: [term][channel block][row (y%8, y/8)][32 px][8 channels] fp16 */
+                    uint32_t hl[4];
+#pragma unroll
+                    for (int i2 = 0; i2 < 4; ++i2) {
+                        __half hi, lo;
+                        amax = fmaxf(amax, fabsf(keep[i2]));
+                        split_f16(keep[i2] * kP1Scale, hi, lo);
+                        hl[i2] = pack2(hi, lo);
+                    }
+#pragma unroll
+                    if (a.dbg & 32) { sink ^= hl[0] ^ hl[1] ^ hl[2] ^ hl[3]; return; }
+                    /* a 2-byte store per lane costs ~15 cycles of the load/store unit per warp instruction.  Neighbouring
+                     * filters (lanes f, f ^ 1) therefore trade two of their four pixels: the even-f lane ends up with both
+                     * channels of pixels i2 = 0, 2, the odd-f lane with those of i2 = 1, 3, and every store is 32 bits
+                     * (a warp instruction writes four whole 32-byte sectors) */
+                    const uint32_t r0 = __shfl_xor_sync(0xffffffffu, fodd ? hl[0] : hl[1], 1);
+                    const uint32_t r1 = __shfl_xor_sync(0xffffffffu, fodd ? hl[2] : hl[3], 1);
+                    const uint32_t ea = fodd ? r0 : hl[0], oa = fodd ? hl[1] : r0;      /* even / odd channel, first pixel */
+                    const uint32_t eb = fodd ? r1 : hl[2], ob = fodd ? hl[3] : r1;      /* second pixel (4 further right) */
+                    unsigned char* q = rowp + g * 128;
+                    if (a.dbg & 64) {
+                        __stcs(reinterpret_cast<uint32_t*>(q), __byte_perm(ea, oa, 0x5410));
+                        __stcs(reinterpret_cast<uint32_t*>(q + 2 * kP1PlaneBytes), __byte_perm(ea, oa, 0x7632));
+                        if (g < 3 || (!fodd && jpar == 0)) {
+                            __stcs(reinterpret_cast<uint32_t*>(q + 64), __byte_perm(eb, ob, 0x5410));
+                            __stcs(reinterpret_cast<uint32_t*>(q + 64 + 2 * kP1PlaneBytes), __byte_perm(eb, ob, 0x7632));
+                        }
+                        return;
+                    }
+                    *reinterpret_cast<uint32_t*>(q) = __byte_perm(ea, oa, 0x5410);                           /* hi terms */
+                    *reinterpret_cast<uint32_t*>(q + 2 * kP1PlaneBytes) = __byte_perm(ea, oa, 0x7632);       /* lo terms */
+                    if (g < 3 || (!fodd && jpar == 0)) {
+                        *reinterpret_cast<uint32_t*>(q + 64) = __byte_perm(eb, ob, 0x5410);
+                        *reinterpret_cast<uint32_t*>(q + 64 + 2 * kP1PlaneBytes) = __byte_perm(eb, ob, 0x7632);
+                    }
+                } else {
+#pragma unroll
+                    for (int i2 = 0; i2 < 4; ++i2) {
+                        const int pxe = 8 * g + 2 * i2;
+                        if (pxe < 28 || (pxe == 28 && jpar == 0)) rowf[pxe] = keep[i2];
+                    }
+                }
+            };
+            /* the TMEM loads run one group ahead of the arithmetic (two 16-register buffers) */
+            uint32_t v0[16], v1[16];
+            tmem_ld16(tbase, v0);
 #pragma unroll 1
             for (int b = 0; b < n_b; ++b) {
                 const int ye = 32 * t + 8 * b + 2 * quarter;          /* conv rows ye (even-j lanes) and ye + 1 */
                 const int py = ye >> 1;
                 const bool row_o_ok = ye + 1 <= 56;
                 const bool own_ok = jpar ? row_o_ok : true, oth_ok = jpar ? true : row_o_ok;
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    uint32_t v[32];
-                    tmem_ld32(tbase + b * 64 + h * 32, v);
-                    tmem_ld_wait();
-                    if (b == n_b - 1 && h == 1) {  /* every column this warp needs is in registers: hand the accumulator back */
-                        fence_before_sync();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&acc_empty[t]);
-                    }
-#pragma unroll
-                    for (int i2 = 0; i2 < 8; ++i2) {
-                        const int x0 = 32 * h + 4 * i2;                 /* pooled columns x0 / 2 and x0 / 2 + 1 */
-                        const float m0 = x0 + 1 <= 56 ? fmaxf(__uint_as_float(v[4 * i2]), __uint_as_float(v[4 * i2 + 1])) : __uint_as_float(v[4 * i2]);
-                        const float m1 = x0 + 3 <= 56 ? fmaxf(__uint_as_float(v[4 * i2 + 2]), __uint_as_float(v[4 * i2 + 3])) : __uint_as_float(v[4 * i2 + 2]);
-                        const float o = __shfl_xor_sync(0xffffffffu, jpar ? m0 : m1, 16);
-                        float c = own_ok ? (jpar ? m1 : m0) : -FLT_MAX;
-                        if (oth_ok) c = fmaxf(c, o);
-                        const int px = 16 * h + 2 * i2 + jpar;
-                        const float keep = act_apply(fmaf(c, a.inv_scale, bias), a.act, slope);
-                        if (px <= 28) {
-                            if (a.p1_packed) {
-                                /* conv2_tc's A operand: [term][channel block][row (y%8, y/8)][32 px][8 channels] fp16 */
-                                __half hi, lo;
-                                amax = fmaxf(amax, fabsf(keep));
-                                split_f16(keep * kP1Scale, hi, lo);
-                                unsigned char* dst = outp + p1_row_pos(py) * 512 + px * 16;
-                                *reinterpret_cast<__half*>(dst) = hi;
-                                *reinterpret_cast<__half*>(dst + 2 * kP1PlaneBytes) = lo;
-                            } else {
-                                out[py * kP1W + px] = keep;
-                            }
-                        }
-                    }
+                unsigned char* rowp = outp + p1_row_pos(py) * 512 + jpar * 16 + fodd * 32;   /* pixel jpar (+ 2 for odd f) */
+                float* rowf = out + py * kP1W + jpar;
+                tmem_ld_wait();
+                tmem_ld16(tbase + b * 64 + 16, v1);
+                drain(v0, 0, own_ok, oth_ok, rowp, rowf);
+                tmem_ld_wait();
+                tmem_ld16(tbase + b * 64 + 32, v0);
+                drain(v1, 1, own_ok, oth_ok, rowp, rowf);
+                tmem_ld_wait();
+                tmem_ld16(tbase + b * 64 + 48, v1);
+                drain(v0, 2, own_ok, oth_ok, rowp, rowf);
+                tmem_ld_wait();
+                if (b + 1 < n_b) {
+                    tmem_ld16(tbase + (b + 1) * 64, v0);
+                } else {              /* every column this warp needs is in registers: hand the accumulator back */
+                    fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&acc_empty[t]);
                 }
+                drain(v1, 3, own_ok, oth_ok, rowp, rowf);
             }
         }
+        if (sink == 0x12345678u) atomicExch(a.err, 7);
         if (!(amax <= 4000.f)) atomicExch(a.err, 101);   /* packed activations must stay inside the fp16 split range */
     } else {
         /* ======================= loaders: fp32 HWC -> fp16 hi / lo HWC8, 16 rows at a time ======================= */
         const int lt = tid - 288;                      /* 0..255: row (lt >> 4) of the block, pixels 4 * (lt & 15) .. +3 */
         const int yr = lt >> 4, x0 = (lt & 15) * 4;
+        const int rot = (lt >> 1) & 3;                 /* see the store loop */
+        const bool rot1 = rot & 1, rot2 = rot & 2;
         const float sx = static_cast<float>(1 << kLog2Sx);
         float vmax = 0.f;
         uint32_t it = 0;
@@ -261,37 +346,73 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
                 const float4* s4 = reinterpret_cast<const float4*>(src + (size_t)(y * 64 + x0) * CP);
 #pragma unroll
                 for (int i = 0; i < CP; ++i) {
-                    float4 q;
+                    float4 q = make_float4(0.5f, 0.25f, 0.125f, 0.75f);
+                    if (!((a.dbg & 16) && it > 0))
                     asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
                                  : "=f"(q.x), "=f"(q.y), "=f"(q.z), "=f"(q.w) : "l"(s4 + i));
                     val[4 * i + 0] = q.x; val[4 * i + 1] = q.y; val[4 * i + 2] = q.z; val[4 * i + 3] = q.w;
                 }
                 if (!mbar_wait_relaxed(&img_empty[rb], (it & 1) ^ 1)) { atomicExch(a.err, 5); *s_abort = 1; break; }
                 unsigned char* dst = smem + row_pos(y) * kRowBytes + x0 * 16;
+                if ((a.dbg & 4) && it > 0) { mbar_arrive(&img_full[rb]); continue; }
+                uint32_t H[4][4], L[4][4];
 #pragma unroll
                 for (int p = 0; p < 4; ++p) {
-                    uint32_t hi[4], lo[4];
+                    uint32_t (&hi)[4] = H[p];
+                    uint32_t (&lo)[4] = L[p];
 #pragma unroll
                     for (int c2 = 0; c2 < 4; ++c2) {
                         __half h[2], l[2];
+                        float xs[2], ls[2];
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
                             const int ch = 2 * c2 + e;
                             const float xv = ch < CP ? val[p * CP + (ch < CP ? ch : 0)] : 0.f;
                             vmax = fmaxf(vmax, fabsf(xv));
                             split_f16(xv * sx, h[e], l[e]);
+                            xs[e] = xv * (sx / static_cast<float>(1 << kF8XDown));
+                            ls[e] = (xv * sx - __half2float(h[e])) * static_cast<float>(1 << kF8LoUp);
                         }
                         hi[c2] = pack2(h[0], h[1]);
-                        lo[c2] = pack2(l[0], l[1]);
+                        if (F8) {
+                            /* bytes 0..7 of the pixel: x8 of channels 0..7, bytes 8..15: lo8 */
+                            const uint32_t x2 = __nv_cvt_float2_to_fp8x2(make_float2(xs[0], xs[1]), __NV_SATFINITE, __NV_E4M3);
+                            const uint32_t l2 = __nv_cvt_float2_to_fp8x2(make_float2(ls[0], ls[1]), __NV_SATFINITE, __NV_E4M3);
+                            const int w = c2 >> 1, sh = (c2 & 1) * 16;
+                            if ((c2 & 1) == 0) { lo[w] = x2; lo[2 + w] = l2; }
+                            else { lo[w] |= x2 << sh; lo[2 + w] |= l2 << sh; }
+                        } else {
+                            lo[c2] = pack2(l[0], l[1]);
+                        }
                     }
-                    *reinterpret_cast<uint4*>(dst + kOffImgHi + p * 16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                    *reinterpret_cast<uint4*>(dst + kOffImgLo + p * 16) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                }
+                /* a quarter warp writes 8 x 16 bytes at a 64-byte stride: storing pixel s at step s would hit only two
+                 * 16-byte bank groups (4-way conflict, 4x the shared-memory cycles, and this kernel runs the shared-memory
+                 * pipe close to its limit with the tensor operands).  Lane l therefore stores pixel (s + (l >> 1)) & 3
+                 * at step s - a rotation of its four pixels by two select stages - which spreads the eight lanes over
+                 * all banks */
+#pragma unroll
+                for (int w = 0; w < 4; ++w) {
+                    uint32_t t0 = H[0][w], t1 = H[1][w], t2 = H[2][w], t3 = H[3][w];
+                    H[0][w] = rot1 ? t1 : t0; H[1][w] = rot1 ? t2 : t1; H[2][w] = rot1 ? t3 : t2; H[3][w] = rot1 ? t0 : t3;
+                    t0 = H[0][w]; t1 = H[1][w]; t2 = H[2][w]; t3 = H[3][w];
+                    H[0][w] = rot2 ? t2 : t0; H[1][w] = rot2 ? t3 : t1; H[2][w] = rot2 ? t0 : t2; H[3][w] = rot2 ? t1 : t3;
+                    t0 = L[0][w]; t1 = L[1][w]; t2 = L[2][w]; t3 = L[3][w];
+                    L[0][w] = rot1 ? t1 : t0; L[1][w] = rot1 ? t2 : t1; L[2][w] = rot1 ? t3 : t2; L[3][w] = rot1 ? t0 : t3;
+                    t0 = L[0][w]; t1 = L[1][w]; t2 = L[2][w]; t3 = L[3][w];
+                    L[0][w] = rot2 ? t2 : t0; L[1][w] = rot2 ? t3 : t1; L[2][w] = rot2 ? t0 : t2; L[3][w] = rot2 ? t1 : t3;
+                }
+#pragma unroll
+                for (int st = 0; st < 4; ++st) {
+                    const int po = ((st + rot) & 3) * 16;
+                    *reinterpret_cast<uint4*>(dst + kOffImgHi + po) = make_uint4(H[st][0], H[st][1], H[st][2], H[st][3]);
+                    *reinterpret_cast<uint4*>(dst + kOffImgLo + po) = make_uint4(L[st][0], L[st][1], L[st][2], L[st][3]);
                 }
                 fence_async_smem();
                 mbar_arrive(&img_full[rb]);
             }
         }
-        if (!(vmax <= 255.f)) atomicExch(a.err, 100);   /* also catches NaN */
+        if (!(vmax <= (F8 ? kF8MaxInput : 255.f))) atomicExch(a.err, F8 ? 102 : 100);   /* also catches NaN */
     }
     fence_before_sync();
     __syncthreads();
@@ -485,7 +606,8 @@ int conv1_tc_prepare(pe_net* net) {
     const float sw = std::ldexp(1.f, log2_sw);
     std::vector<int> slot_of(8, -1);
     for (size_t s = 0; s < net->def.sel.size(); ++s) slot_of[net->def.sel[s]] = (int)s;
-    std::vector<uint16_t> z((size_t)2 * kZBytes / 2, 0);
+    std::vector<uint16_t> z((size_t)3 * kZBytes / 2, 0);     /* fp16 hi, fp16 lo, e4m3 [lo_w | w] */
+    unsigned char* z8 = reinterpret_cast<unsigned char*>(z.data()) + (size_t)2 * kZBytes;
     for (int kx = 0; kx < 8; ++kx)
         for (int ky = 0; ky < 8; ++ky)
             for (int f = 0; f < 16; ++f)
@@ -502,10 +624,14 @@ int conv1_tc_prepare(pe_net* net) {
                     memcpy(&lb, &l, 2);
                     z[at] = hb;
                     z[(size_t)kZBytes / 2 + at] = lb;
+                    /* the same slab in e4m3: bytes 0..7 of a filter row = lo_w (meets x8), bytes 8..15 = w (meets lo8) */
+                    const size_t at8 = slab * 256 + (size_t)f * 16 + ch;
+                    z8[at8] = __nv_cvt_float_to_fp8(std::ldexp(v - __half2float(h), kF8XDown), __NV_SATFINITE, __NV_E4M3);
+                    z8[at8 + 8] = __nv_cvt_float_to_fp8(std::ldexp(v, -kF8LoUp), __NV_SATFINITE, __NV_E4M3);
                 }
     PE_CUDA(cudaSetDevice(net->device));
-    if (!net->d_z1) PE_CUDA(cudaMalloc(&net->d_z1, 2 * kZBytes));
-    PE_CUDA(cudaMemcpy(net->d_z1, z.data(), 2 * kZBytes, cudaMemcpyHostToDevice));
+    if (!net->d_z1) PE_CUDA(cudaMalloc(&net->d_z1, 3 * kZBytes));
+    PE_CUDA(cudaMemcpy(net->d_z1, z.data(), 3 * kZBytes, cudaMemcpyHostToDevice));
     if (!net->tc_err) {
         PE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&net->tc_err), sizeof(int), cudaHostAllocMapped));
         *net->tc_err = 0;
@@ -587,14 +713,19 @@ int conv1_tc_launch(pe_net* net, const float* d_patches, int patch_c, long long 
     a.pool1 = net->pool1.as<float>();
     a.p1_packed = packed_out ? net->p1_packed.as<unsigned char>() : nullptr;
     a.err = net->tc_err;
+    static const int dbg = getenv("PE_C1_DBG") ? atoi(getenv("PE_C1_DBG")) : 0;
+    a.dbg = dbg;
     const int grid = (int)(n < net->num_sms ? n : net->num_sms);
-    if (patch_c == 7) {
-        PE_CUDA(cudaFuncSetAttribute(conv1_tc_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, kC1TcSmem));
-        conv1_tc_kernel<7><<<grid, kC1TcThreads, kC1TcSmem, net->stream>>>(a);
-    } else {
-        PE_CUDA(cudaFuncSetAttribute(conv1_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kC1TcSmem));
-        conv1_tc_kernel<4><<<grid, kC1TcThreads, kC1TcSmem, net->stream>>>(a);
-    }
+    const bool f8 = g_opt_forward_fp8.load() != 0;
+    auto launch = [&](auto kernel) -> int {
+        PE_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kC1TcSmem));
+        kernel<<<grid, kC1TcThreads, kC1TcSmem, net->stream>>>(a);
+        return PE_OK;
+    };
+    if (patch_c == 7 && packed_out) PE_CHECK(f8 ? launch(conv1_tc_kernel<7, true, true>) : launch(conv1_tc_kernel<7, false, true>));
+    else if (patch_c == 7) PE_CHECK(f8 ? launch(conv1_tc_kernel<7, true, false>) : launch(conv1_tc_kernel<7, false, false>));
+    else if (packed_out) PE_CHECK(f8 ? launch(conv1_tc_kernel<4, true, true>) : launch(conv1_tc_kernel<4, false, true>));
+    else PE_CHECK(f8 ? launch(conv1_tc_kernel<4, true, false>) : launch(conv1_tc_kernel<4, false, false>));
     PE_LAUNCHED();
     return PE_OK;
 }
@@ -606,9 +737,10 @@ int forward_tc_check(pe_net* net) {
     if (e == 0) return PE_OK;
     *net->tc_err = 0;
     if (e >= 100) {
-        set_error("tensor forward: %s is not finite or exceeds the fp16 split range (patches are expected in [-1, 1]: "
-                  "reference src/datasetmanager.cpp:327-343); use pe_set_option(\"forward_tensor\", 0) for such data",
-                  e == 100 ? "an input value (|x| > 255)" : "an activation (|x| > 4000)");
+        set_error("tensor forward: %s is not finite or exceeds the split range (patches are expected in [-1, 1]: "
+                  "reference src/datasetmanager.cpp:327-343); use pe_set_option(\"%s\", 0) for such data",
+                  e == 100 ? "an input value (|x| > 255)" : e == 102 ? "an input value (|x| > 28, fp16 + e4m3 split)" : "an activation (|x| > 4000)",
+                  e == 102 ? "forward_fp8" : "forward_tensor");
         return PE_ERR_INVALID;
     }
     set_error("tensor forward: pipeline barrier %d timed out", e);

@@ -288,7 +288,8 @@ def gpu_arm(args, rank, world, local_rank, dist):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ms_e2e = float(tt.item())
     # sanity: the host path and the device path agree on the last batch
-    assert np.array_equal(idx_h, d_idx.to_host()[rank * BATCH:(rank + 1) * BATCH]), "host-API and device-API neighbours differ"
+    if not os.environ.get("PE_C1_DBG"):     # kernel ablation runs (tools/c1_dbg.sh) compute garbage on purpose
+        assert np.array_equal(idx_h, d_idx.to_host()[rank * BATCH:(rank + 1) * BATCH]), "host-API and device-API neighbours differ"
 
     if rank != 0:
         return None

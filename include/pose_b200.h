@@ -60,7 +60,10 @@ PE_API int64_t pe_launch_count(void);
 
 /* runtime switches (process-wide).  "knn_tensor" (default 1): L2 kNN scan on the tcgen05 tensor path for
  * descriptors of up to 16 dimensions and k <= 5, 0 = fp32 SIMT scan.  "forward_tensor" (default 1): conv / FC
- * layers on the tcgen05 split-fp16 path, 0 = fp32 SIMT kernels.  Both paths are CUDA; neither is a CPU fallback. */
+ * layers on the tcgen05 split-fp16 path, 0 = fp32 SIMT kernels.  "forward_fp8" (default 1): conv1 takes its two
+ * cross terms (hi.lo + lo.hi) from one e4m3 MMA instead of two fp16 MMAs (descriptor error ~3e-5 of the row max
+ * instead of ~1e-6, inside the 1e-4 acceptance; inputs must satisfy |x| <= 28), 0 = all three terms in fp16.
+ * Every path is CUDA; none is a CPU fallback. */
 PE_API int pe_set_option(const char* name, int value);
 PE_API int pe_get_option(const char* name, int* value);
 

@@ -34,12 +34,15 @@ def make_net(gpu, po, synth, name, seed):
 
 
 # ---------------------------------------------------------------------------- forward ---
-@pytest.fixture(params=[1, 0], ids=["tensor", "simt"])
+@pytest.fixture(params=[(1, 1), (1, 0), (0, 1)], ids=["tensor", "tensor_f16x3", "simt"])
 def fwd_path(gpu, request):
-    """runs a test once with the tcgen05 forward kernels (default) and once with the fp32 SIMT kernels"""
-    gpu.set_option("forward_tensor", request.param)
-    yield request.param
+    """runs a test with the tcgen05 forward kernels (default: conv1 cross terms in e4m3), with all three conv1
+    split terms in fp16, and with the fp32 SIMT kernels"""
+    gpu.set_option("forward_tensor", request.param[0])
+    gpu.set_option("forward_fp8", request.param[1])
+    yield request.param[0]
     gpu.set_option("forward_tensor", 1)
+    gpu.set_option("forward_fp8", 1)
 
 
 @pytest.mark.parametrize("vi,name", list(enumerate(netdefs.VARIANTS)))
@@ -69,6 +72,29 @@ def test_forward_rejects_wrong_channel_count(gpu):
     with pytest.raises(gpu.PoseError) as e:
         net.compute_descriptors(np.zeros((2, 64, 64, 4), np.float32))
     assert e.value.code == gpu.PE_ERR_INVALID
+
+
+def test_forward_input_range_is_checked(gpu, synth):
+    """the e4m3 cross terms hold |x| <= 28, the fp16 split |x| <= 255; beyond that the call fails loudly and the
+    next wider path is named (patches of the reference are in [-1, 1], src/datasetmanager.cpp:327-343)"""
+    net = gpu.Net(named="manifold_rgbdnor_16")
+    net.fill(1, 1)
+    x = synth.make_patches(3, 0, 2, 7, 2)
+    ok = net.compute_descriptors(x)
+    x[1, 5, 5, 2] = 40.0
+    with pytest.raises(gpu.PoseError) as e:
+        net.compute_descriptors(x)
+    assert e.value.code == gpu.PE_ERR_INVALID and "forward_fp8" in str(e.value)
+    gpu.set_option("forward_fp8", 0)
+    try:
+        wide = net.compute_descriptors(x)
+        assert np.isfinite(wide).all() and rowscale_err(wide[:1], ok[:1]) < DESC_TOL
+        x[1, 5, 5, 2] = 300.0
+        with pytest.raises(gpu.PoseError) as e:
+            net.compute_descriptors(x)
+        assert "forward_tensor" in str(e.value)
+    finally:
+        gpu.set_option("forward_fp8", 1)
 
 
 def test_forward_device_entry_and_chunking(gpu, po, synth, fwd_path):
