@@ -299,6 +299,8 @@ def gpu_arm(args, rank, world, local_rank, dist):
     conv1_flops = 2.0 * MAC_PER_PATCH["conv1"] * BATCH
     achieved_tf = conv1_flops / (conv1_ms * 1e-3) / 1e12 if conv1_ms > 0 else 0.0
     fwd_tensor = capi.get_option("forward_tensor") != 0
+    fwd_fp8 = capi.get_option("forward_fp8") != 0
+    n_mma = 240 if fwd_fp8 else 360           # per patch: 2 tiles x 15 input rows x 4 pixel pairs x (fp16 hi.hi + e4m3 cross | 3 fp16)
     traffic = None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
@@ -315,21 +317,22 @@ def gpu_arm(args, rank, world, local_rank, dist):
                    "net": NET, "batch_per_gpu": BATCH, "templates": T, "k": K, "seed": SEED,
                    "l2_flush": "inputs alternate between two 470 MB batches (> 126 MB L2)",
                    "parallelism": f"patches x{world} (no comm), DB rows /{world} + NCCL all-gather + merge" if world > 1 else "single GPU"},
-        "roofline": {"kernel": "conv1_tc_kernel<7>" if fwd_tensor else "conv1_pool_act_kernel<7>", "bound": "tensor", "achieved": achieved_tf,
+        "roofline": {"kernel": ("conv1_tc_kernel<7, e4m3 cross terms>" if fwd_fp8 else "conv1_tc_kernel<7, fp16 x3>") if fwd_tensor else "conv1_pool_act_kernel<7>", "bound": "tensor", "achieved": achieved_tf,
                      "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
                      "frac": achieved_tf / peaks["bf16_tflops_sustained"], "traffic": traffic,
                      "peak_source": f"{peaks['source']} bf16 sustained (kernel timed inside a long step)",
-                     "note": ("tcgen05 split-fp16 implicit GEMM: achieved = ALGORITHMIC conv1 FLOPs (2 x 23,288,832 per patch) / launch time; "
-                              "the kernel executes 8.1x that in tensor FLOPs (x3 fp16 split for fp32 parity, x1.875 Toeplitz widening of the 16 filters to 128 accumulator lanes, "
-                              "x8/7 channel pad, x1.26 tile edges), see executed_tflops / executed_frac") if fwd_tensor else
+                     "note": ("tcgen05 split-precision implicit GEMM: achieved = ALGORITHMIC conv1 FLOPs (2 x 23,288,832 per patch) / launch time; "
+                              f"the kernel occupies the tensor pipe for {n_mma} MMA slots of 128x256x16-fp16 size per patch = {n_mma * 2 * 128 * 256 * 16 / (2.0 * MAC_PER_PATCH['conv1']):.1f}x the algorithmic FLOPs "
+                              "(" + ("x2: fp16 hi.hi + one e4m3 K=32 MMA for both cross terms" if fwd_fp8 else "x3 fp16 split") + " for fp32 parity, x1.875 Toeplitz widening of the 16 filters "
+                              "to 128 accumulator lanes, x8/7 channel pad, x1.26 tile edges), see executed_tflops / executed_frac (fp16-equivalent pipe work)") if fwd_tensor else
                              "fp32 SIMT kernel: the pipe that binds it is FP32 FMA (~74 TFLOP/s at 1965 MHz), see fp32_fma_frac",
                      "algorithmic_flops_per_launch": conv1_flops, "launch_ms": conv1_ms,
-                     "executed_tflops": (360 * 2.0 * 128 * 256 * 16 * BATCH / (conv1_ms * 1e-3) / 1e12) if (fwd_tensor and conv1_ms > 0) else None,
-                     "executed_frac": (360 * 2.0 * 128 * 256 * 16 * BATCH / (conv1_ms * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"]) if (fwd_tensor and conv1_ms > 0) else None,
+                     "executed_tflops": (n_mma * 2.0 * 128 * 256 * 16 * BATCH / (conv1_ms * 1e-3) / 1e12) if (fwd_tensor and conv1_ms > 0) else None,
+                     "executed_frac": (n_mma * 2.0 * 128 * 256 * 16 * BATCH / (conv1_ms * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"]) if (fwd_tensor and conv1_ms > 0) else None,
                      "fp32_fma_frac": None if fwd_tensor else achieved_tf / 74.4,
                      "achieved_hbm_gbs": BATCH * (7 * 64 * 64 * 4 + (81920 if fwd_tensor else 16 * 30 * 32 * 4)) / (conv1_ms * 1e-3) / 1e9 if conv1_ms > 0 else 0.0,
                      "hbm_peak_gbs": peaks["hbm_gbs"]},
-        "paths": {"forward": "tcgen05" if fwd_tensor else "simt", "knn": "tcgen05" if capi.get_option("knn_tensor") else "simt"},
+        "paths": {"forward": ("tcgen05 (conv1 cross terms e4m3)" if fwd_fp8 else "tcgen05") if fwd_tensor else "simt", "knn": "tcgen05" if capi.get_option("knn_tensor") else "simt"},
         "kernels_ms_per_step": {"conv1_pool_act": conv1_ms, "conv2_pool_act": net_ms[1] / max(1, net_calls),
                                 "fc_act": net_ms[2] / max(1, net_calls), "knn_l2_scan": scan_ms,
                                 "knn_select": db_ms[1] / max(1, db_calls)},
