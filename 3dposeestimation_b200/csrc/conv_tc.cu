@@ -17,16 +17,21 @@
  *     K step over input row r + ky' uses weight row ky' - j (zero outside 0..7).  The Toeplitz operand is itself an
  *     overlapping window over a short array of 256-byte weight slabs (SBO = 128, start = (14 - ky') slabs).  With
  *     16 filters alone M would be 16; eight row offsets fill the 128 lanes at the price of 15 K rows per 8 useful;
- *   - fp32 accuracy: D = Z_hi.X_hi + Z_lo.X_hi + Z_hi.X_lo in fp32 (TMEM), operands scaled by powers of two.
- *   Per patch: 2 tiles (conv rows 0..31, 32..63) x 15 input rows x 4 pixel pairs x 3 products = 360 MMAs of
- *   128x256x16, 128 cycles each: the tensor pipe is the bound (ncu: 96 % active).  Which operand slides matters:
+ *   - fp32 accuracy: D = Z_hi.X_hi + Z_lo.X_hi + Z_hi.X_lo in fp32 (TMEM), operands scaled by powers of two.  The two
+ *     cross terms are ~2^-11 of the product; with F8 (default, pe_set_option("forward_fp8")) they come from ONE
+ *     kind::f8f6f4 MMA over e4m3 copies ([x | lo_x] per pixel against [lo_w | w] per filter row, K = 32), which costs
+ *     the same 128 cycles as an fp16 MMA and leaves descriptors within ~3e-5 of the row max (fp16 x3: ~1e-6).
+ *   Per patch: 2 tiles (conv rows 0..31, 32..63) x 15 input rows x 4 pixel pairs x (2 | 3) products = 240 | 360
+ *   MMAs of 128x256, 128 cycles each: the tensor pipe is the bound (ncu: 95 % active).  Which operand slides matters:
  *   with the image as the 128-row A operand and N = 128 (720 MMAs) an MMA took 78 cycles instead of 64, because
  *   shared memory had to deliver 8 KB per 64 cycles and three of four windows are misaligned; at N = 256 the
  *   operand traffic per cycle is lower and the misalignment disappears behind the math.
  *
  * Kernel (persistent, one CTA per SM, 544 threads): warp 0 issues the MMAs, warps 1-4 / 5-8 drain the accumulator
- * of tile 0 / 1 (pool x in registers, pool y by one shuffle, bias, activation, fp16 hi / lo store), warps 9-16
- * stream the next patch in 16-row blocks (fp32 HWC -> fp16 hi/lo) as soon as a block's last reader tile has completed.
+ * of tile 0 / 1 (TMEM loads one 16-column group ahead, pool x in registers, pool y by one shuffle, bias, activation,
+ * fp16 hi / lo split, 32-bit stores after a pixel trade between neighbouring filters), warps 9-16 stream the next
+ * patch in 16-row blocks (fp32 HWC -> fp16 hi + fp16 lo | e4m3 pair, L1-allocating loads, bank-conflict-free stores)
+ * as soon as a block's last reader tile has completed.
  */
 #include <cfloat>
 #include <cmath>
