@@ -820,9 +820,18 @@ bool knn_tc_usable(const pe_db* db, int k) { return db->tc_ready && k + 2 <= 7; 
 void knn_tc_plan(const pe_db* db, int64_t nq, int k, int* n_lists, int* kc, int* tiles_per_chunk) {
     const int n_qpairs = (int)((nq + 2 * kTcRows - 1) / (2 * kTcRows));
     const long long tiles = (db->t_local + kTcRows - 1) / kTcRows;
-    long long c = (4LL * db->num_sms + n_qpairs - 1) / n_qpairs;
+    /* items = chunks x query pairs are dealt round-robin to num_sms persistent CTAs: pick the chunk count whose makespan
+     * ceil(items / CTAs) x (tiles per chunk + a fixed per-item cost of ~8 tile times) is smallest, among 2..8 items per CTA
+     * (the first guess, 4 items per CTA rounded up, left a fifth round with a few items at 2 GPUs: 5 rounds for 4.1) */
     const long long cmax = tiles / 32 > 0 ? tiles / 32 : 1;
-    if (c > cmax) c = cmax;
+    long long c = 1, best = -1;
+    for (long long cc = 1; cc <= cmax; ++cc) {
+        const long long items = cc * n_qpairs;
+        if (items > 8LL * db->num_sms && cc > 1) break;
+        const long long rounds = (items + db->num_sms - 1) / db->num_sms;
+        const long long cost = rounds * ((tiles + cc - 1) / cc + 8);
+        if (best < 0 || cost < best) { best = cost; c = cc; }
+    }
     const long long tpc = (tiles + c - 1) / c;
     *tiles_per_chunk = (int)tpc;
     *n_lists = 2 * (int)((tiles + tpc - 1) / tpc);
