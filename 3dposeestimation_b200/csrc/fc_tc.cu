@@ -29,7 +29,7 @@ constexpr int kFcTerm = 8 * 2048;                  /* one term of one operand bl
 constexpr int kFcStageBytes = 4 * kFcTerm;         /* A hi | A lo | B hi | B lo */
 constexpr int kFcOffBar = kFcStages * kFcStageBytes;
 constexpr int kFcSmem = kFcOffBar + 256;
-constexpr int kFcThreads = 192;                    /* warp 0 weight copies, warp 1 MMA, warps 2-5 loaders + epilogue */
+constexpr int kFcThreads = 320;                    /* warp 0 weight copies, warp 1 MMA, warps 2-9 loaders + epilogue */
 constexpr int kLog2SxFc = 4;                       /* activation scale 2^4: |x| < 4094 */
 
 __device__ __forceinline__ float fc_act(float v, int act, float slope) {
@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
     int n_mma = a.N - n0;
     n_mma = n_mma >= 128 ? 128 : ((n_mma + 15) & ~15);
     if (tid == 0) {
-        for (int s = 0; s < kFcStages; ++s) { mbar_init(&full_a[s], 128); mbar_init(&full_b[s], 1); mbar_init(&empty[s], 1); }
+        for (int s = 0; s < kFcStages; ++s) { mbar_init(&full_a[s], 256); mbar_init(&full_b[s], 1); mbar_init(&empty[s], 1); }
         mbar_init(acc_full, 1);
         mbar_fence_init();
     }
@@ -117,27 +117,31 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
         if (ok && elect_one()) mma_commit(acc_full);
         __syncwarp();
     } else {
-        /* ---- loaders: thread r converts row m0 + r, one K block at a time ---- */
+        /* ---- loaders: two threads per row m0 + r (k halves of 32), one K block at a time.  The loads of block kb + 1 are
+         * in flight while block kb is converted (two register buffers): a row is 4.7 KB away from the next one, so every
+         * load is its own pair of cache lines and its latency would otherwise be paid 19 times in a row ---- */
         const int r = (warp & 3) * 32 + lane;     /* = the TMEM lane this thread may read in the epilogue */
+        const int half = (warp - 2) >> 2;
         const int m = m0 + r;
         const bool row_ok = m < a.M;
         const float sx = static_cast<float>(1 << kLog2SxFc);
-        const float* xrow = a.x + (size_t)(row_ok ? m : 0) * a.ldx;
+        const float* xrow = a.x + (size_t)(row_ok ? m : 0) * a.ldx + 32 * half;
         float vmax = 0.f;
         bool ok = true;
-        for (int kb = 0; kb < a.k_blocks && ok; ++kb) {
-            const int s = kb % kFcStages;
-            float4 v[16];
+        auto load = [&](float4 (&v)[8], int kb) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const int k = kb * kFcKB + 4 * i;
-                v[i] = (row_ok && k < a.K) ? *reinterpret_cast<const float4*>(xrow + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = 0; i < 8; ++i) {
+                const int k = kb * kFcKB + 32 * half + 4 * i;
+                v[i] = (row_ok && k < a.K) ? *reinterpret_cast<const float4*>(xrow + kb * kFcKB + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
-            if (!mbar_wait(&empty[s], ((kb / kFcStages) & 1) ^ 1)) { atomicExch(a.err, 14); ok = false; break; }
-            uint4* dst_hi = reinterpret_cast<uint4*>(smem + s * kFcStageBytes) + r;
+        };
+        auto convert = [&](const float4 (&v)[8], int kb) {
+            const int s = kb % kFcStages;
+            if (!mbar_wait(&empty[s], ((kb / kFcStages) & 1) ^ 1)) { atomicExch(a.err, 14); ok = false; return; }
+            uint4* dst_hi = reinterpret_cast<uint4*>(smem + s * kFcStageBytes) + (4 * half) * 128 + r;
             uint4* dst_lo = dst_hi + kFcTerm / 16;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
+            for (int c = 0; c < 4; ++c) {
                 const float e[8] = {v[2 * c].x, v[2 * c].y, v[2 * c].z, v[2 * c].w, v[2 * c + 1].x, v[2 * c + 1].y, v[2 * c + 1].z, v[2 * c + 1].w};
                 uint32_t hi[4], lo[4];
 #pragma unroll
@@ -154,6 +158,17 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
             }
             fence_async_smem();
             mbar_arrive(&full_a[s]);
+        };
+        float4 va[8], vb[8];
+        load(va, 0);
+#pragma unroll 1
+        for (int kb = 0; kb < a.k_blocks && ok; kb += 2) {
+            if (kb + 1 < a.k_blocks) load(vb, kb + 1);
+            convert(va, kb);
+            if (kb + 1 < a.k_blocks && ok) {
+                if (kb + 2 < a.k_blocks) load(va, kb + 2);
+                convert(vb, kb + 1);
+            }
         }
         if (!(vmax <= 4000.f)) atomicExch(a.err, 101);
         /* ---- epilogue: accumulator row r -> bias, activation, store ---- */
@@ -161,7 +176,8 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
             fence_after_sync();
             const uint32_t tbase = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
             float* yrow = a.y + (size_t)(row_ok ? m : 0) * a.ldy + n0;
-            for (int c0 = 0; c0 < n_mma; c0 += 16) {
+            const int groups = n_mma / 16, g_split = (groups + 1) / 2;
+            for (int c0 = (half ? g_split : 0) * 16; c0 < (half ? groups : g_split) * 16; c0 += 16) {
                 uint32_t w[16];
                 tmem_ld16(tbase + c0, w);
                 tmem_ld_wait();
