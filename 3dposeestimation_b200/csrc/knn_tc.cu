@@ -598,18 +598,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
  * (key, block id) are evaluated exactly -- the reference's fp32 sqrt(sum (q-t)^2) for each of their 32 templates --
  * and the k smallest by (distance, index) are the answer, as BFMatcher::knnMatch orders them
  * (reference src/networkevaluator.cpp:197; ties -> lower index). */
-__global__ void __launch_bounds__(32)
+constexpr int kTcSelWarps = 4;               /* queries (warps) per CTA of the L2 select kernel */
+__global__ void __launch_bounds__(32 * kTcSelWarps)
 knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ cand_i, int n_cand,
                      const float* __restrict__ q, const float* __restrict__ db, int dp, long long t_local,
-                     long long row_offset, int k, int* __restrict__ out_idx, float* __restrict__ out_dist) {
-    extern __shared__ __align__(16) float sel_smem[];
+                     long long row_offset, int k, int n_sel, long long nq, int* __restrict__ out_idx, float* __restrict__ out_dist) {
+    extern __shared__ __align__(16) float sel_smem_all[];
+    /* one warp per query, kTcSelWarps independent queries per CTA (32-thread CTAs cap an SM at 32 resident warps, and
+     * this kernel is a chain of dependent reductions and random row reads: it lives on resident warps) */
+    float* sel_smem = sel_smem_all + (size_t)(threadIdx.x >> 5) * (dp + 2 * n_cand + 2 * kTcSelBlocks * kTcBlock);
     float* sq = sel_smem;                                   /* [dp] */
     float* sd = sel_smem + dp;                              /* [n_cand] keys */
     int* si = reinterpret_cast<int*>(sd + n_cand);          /* [n_cand] block ids */
     float* ed = reinterpret_cast<float*>(si + n_cand);      /* [kTcSelBlocks * 32] exact distances */
     int* ei = reinterpret_cast<int*>(ed + kTcSelBlocks * kTcBlock);
-    const int lane = threadIdx.x;
-    const long long qi = blockIdx.x;
+    const int lane = threadIdx.x & 31;
+    const long long qi = (long long)blockIdx.x * kTcSelWarps + (threadIdx.x >> 5);
+    if (qi >= nq) return;
     for (int d = lane; d < dp; d += 32) sq[d] = q[(size_t)qi * dp + d];
     for (int c = lane; c < n_cand; c += 32) {
         const int blk = cand_i[(size_t)qi * n_cand + c];
@@ -617,7 +622,7 @@ knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ c
         si[c] = blk >= 0 ? blk : INT_MAX;
     }
     __syncwarp();
-    for (int r = 0; r < kTcSelBlocks; ++r) {
+    for (int r = 0; r < n_sel; ++r) {
         float bd = INFINITY;
         int bi = INT_MAX, bc = -1;
         for (int c = lane; c < n_cand; c += 32) {
@@ -651,7 +656,7 @@ knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ c
         float bd = INFINITY;
         int bi = INT_MAX, bc = -1;
 #pragma unroll
-        for (int c = lane; c < kTcSelBlocks * kTcBlock; c += 32) {
+        for (int c = lane; c < n_sel * kTcBlock; c += 32) {
             const float d = ed[c];
             const int i = ei[c];
             if (i != INT_MAX && (bc < 0 || d < bd || (d == bd && i < bi))) { bd = d; bi = i; bc = c; }
@@ -899,11 +904,14 @@ int knn_tc_scan(pe_db* db, const void* d_q, int64_t nq, int k, int n_lists, int 
 int knn_tc_select(pe_db* db, const float* cand_d, const int* cand_i, int n_lists, int kc, const float* d_q,
                   int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist) {
     const int n_cand = n_lists * kc;
-    const size_t smem = (size_t)(db->dim_pad + 2 * n_cand + 2 * kTcSelBlocks * kTcBlock) * 4;
+    const size_t smem = (size_t)kTcSelWarps * (db->dim_pad + 2 * n_cand + 2 * kTcSelBlocks * kTcBlock) * 4;
     PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
     PE_CUDA(cudaFuncSetAttribute(knn_tc_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    knn_tc_select_kernel<<<(unsigned)nq, 32, smem, db->stream>>>(cand_d, cand_i, n_cand, d_q, db->d_desc, db->dim_pad,
-                                                                db->t_local, db->row_offset, k, d_out_idx, d_out_dist);
+    /* blocks re-ranked exactly: a block holding one of the k nearest is preceded only by blocks whose key lies within the
+     * split's ~2^-22 of it, so k + 3 keeps the margin the k + 2 list entries have (8 for k = 5, 4 for k = 1) */
+    const int n_sel = k + 3 < kTcSelBlocks ? k + 3 : kTcSelBlocks;
+    knn_tc_select_kernel<<<(unsigned)((nq + kTcSelWarps - 1) / kTcSelWarps), 32 * kTcSelWarps, smem, db->stream>>>(
+        cand_d, cand_i, n_cand, d_q, db->d_desc, db->dim_pad, db->t_local, db->row_offset, k, n_sel, (long long)nq, d_out_idx, d_out_dist);
     PE_LAUNCHED();
     return PE_OK;
 }
