@@ -1,0 +1,95 @@
+"""CPU emulation of conv1's split arithmetic (csrc/conv_tc.cu): fp16 hi.hi on the tensor pipe plus ONE e4m3 MMA for both
+cross terms (forward_fp8, the default), against the all-fp16 three-term split and plain fp16.  The GPU tests hold the
+kernels to 1e-4 of the row max; this test pins the error budget of the scheme itself with the same scales and operand
+formats, so a change of the scales or formats that eats the margin fails here, without a GPU.
+
+Reference semantics: conv1 / pool1 / act of network/manifold*.prototxt as run by CNN.Forward()
+(reference src/networkevaluator.cpp:44-48); fp64 torch is the yardstick."""
+import importlib
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+import torch.nn.functional as F  # noqa: E402
+
+from oracle import pyoracle as po  # noqa: E402
+from tests import netdefs  # noqa: E402
+
+synth = importlib.import_module("3dposeestimation_b200.synth")
+
+LOG2_SX, X_DOWN, LO_UP = 8, 4, 6          # kLog2Sx, kF8XDown, kF8LoUp of conv_tc.cu
+
+
+def _e4m3(t):
+    return t.to(torch.float32).clamp(-448, 448).to(torch.float8_e4m3fn).to(torch.float64)
+
+
+def _f16(t):
+    return t.to(torch.float32).to(torch.float16).to(torch.float64)
+
+
+def _forward(net, blobs, x, conv1):
+    first = True
+    y = x
+    for kind, _, a, b, b0, b1 in net.layers:
+        if kind == po.CONV:
+            w, bias = torch.from_numpy(blobs[b0]).double(), torch.from_numpy(blobs[b1]).double()
+            y = conv1(y, w, bias) if first else F.conv2d(y, w, bias)
+            first = False
+        elif kind == po.POOL:
+            y = F.max_pool2d(y, a, b, ceil_mode=True)
+        elif kind == po.ACT:
+            y = F.relu(y) if a == 1 else (F.elu(y) if a == 2 else F.prelu(y, torch.from_numpy(blobs[b0]).double()))
+        else:
+            y = F.linear(y.flatten(1), torch.from_numpy(blobs[b0]).double(), torch.from_numpy(blobs[b1]).double())
+    return y
+
+
+def _scales(w):
+    wmax = float(w.abs().max())
+    return 2.0 ** LOG2_SX, 2.0 ** (10 - int(np.floor(np.log2(wmax))))     # conv1_tc_prepare: |w s_w| in [2^10, 2^11)
+
+
+def conv1_fp16_e4m3(y, w, bias):
+    sx, sw = _scales(w)
+    X, W = y * sx, w * sw
+    Xh, Wh = _f16(X), _f16(W)
+    x8, lo8 = _e4m3(X * 2.0 ** -X_DOWN), _e4m3((X - Xh) * 2.0 ** LO_UP)
+    lw8, w8 = _e4m3((W - Wh) * 2.0 ** X_DOWN), _e4m3(W * 2.0 ** -LO_UP)
+    # every operand must sit inside e4m3's finite range (no saturation) for inputs in [-1, 1]
+    for t in (x8, lo8, lw8, w8):
+        assert float(t.abs().max()) < 448
+    return (F.conv2d(Xh, Wh) + F.conv2d(x8, lw8) + F.conv2d(lo8, w8)) / (sx * sw) + bias.view(1, -1, 1, 1)
+
+
+def conv1_fp16x3(y, w, bias):
+    sx, sw = _scales(w)
+    X, W = y * sx, w * sw
+    Xh, Wh = _f16(X), _f16(W)
+    Xl, Wl = _f16(X - Xh), _f16(W - Wh)
+    return (F.conv2d(Xh, Wh) + F.conv2d(Xh, Wl) + F.conv2d(Xl, Wh)) / (sx * sw) + bias.view(1, -1, 1, 1)
+
+
+def conv1_fp16x1(y, w, bias):
+    sx, sw = _scales(w)
+    return F.conv2d(_f16(y * sx), _f16(w * sw)) / (sx * sw) + bias.view(1, -1, 1, 1)
+
+
+@pytest.mark.parametrize("name", ["manifold", "manifold_rgbd_16", "manifold_rgbdnor_16", "manifold_rgbdnor_16_bin"])
+def test_conv1_split_error_budget(name):
+    torch.set_num_threads(4)
+    net = po.parse_prototxt(netdefs.prototxt(name))
+    blobs = synth.make_blobs(net.blob_names, net.blob_shapes, synth.BASE_SEED, mode=1)
+    patches = synth.make_patches(synth.BASE_SEED, 0, 48, net.channels, 16)
+    x = torch.from_numpy(patches).double().permute(0, 3, 1, 2)[:, net.sel]
+    ref = _forward(net, blobs, x, lambda y, w, b: F.conv2d(y, w, b))
+
+    def err(fn):
+        out = _forward(net, blobs, x, fn)
+        return float(((out - ref).abs().amax(1) / ref.abs().amax(1)).max())
+
+    e8, e3, e1 = err(conv1_fp16_e4m3), err(conv1_fp16x3), err(conv1_fp16x1)
+    assert e3 < 2e-6                      # three fp16 terms: fp32-class
+    assert e8 < 5e-5                      # fp16 + e4m3 cross terms: inside the 1e-4 acceptance with a factor 2
+    assert e1 > 1e-4                      # one fp16 product alone would not pass: the cross terms are needed
