@@ -231,19 +231,54 @@ struct TcArgs {
 #define TC_DBG_T0(var) long long var = 0; if (DBG) var = clock64()
 #define TC_DBG_ADD(slot, var) do { if (DBG) { const long long n_ = clock64(); dbg_acc[slot] += n_ - var; var = n_; } } while (0)
 
-/* sorted insert into the calling thread's k+2 list (entries strided by kTcListCols threads in shared memory);
- * strict '>' keeps the earlier (lower-index) entry first among equals.  Returns the new k+2-th best.  Deliberately
- * not inlined: it runs in about one warp-tile in six and must not bloat the hot loop's instruction footprint. */
-__device__ __noinline__ float tc_list_insert(float* ld, int* li, int kc, float v, int idx) {
-    int p = kc - 1;
-    while (p > 0 && ld[(p - 1) * kTcListCols] > v) {
-        ld[p * kTcListCols] = ld[(p - 1) * kTcListCols];
-        li[p * kTcListCols] = li[(p - 1) * kTcListCols];
-        --p;
+/* insert into the calling thread's k+2 list (entries strided by kTcListCols threads in shared memory): the new entry
+ * replaces the worst one - largest key, among equal keys the largest block id, so the earlier (lower-index) block
+ * stays as a strict '>' in a sorted insert would have it.  The list is NOT kept sorted (the select kernel ranks all
+ * candidates anyway): all entries are read at once, one is written, i.e. two shared-memory round trips where the
+ * shifting insert made up to a dozen dependent ones (~1,800 cycles per entry under the tensor pipe's operand traffic).
+ * The four 32-template blocks of a drained tile go through ONE load / store of the list.  Returns the new k+2-th best =
+ * the largest key left.  Deliberately not inlined: it runs in about one warp-tile in six and must not bloat the hot
+ * loop's instruction footprint. */
+__device__ __noinline__ float tc_list_insert4(float* ld, int* li, float tau_up, float m0, float m1, float m2, float m3,
+                                             int blk0, int n_blocks) {
+    float key[7];
+    int id[7];
+#pragma unroll
+    for (int p = 0; p < 7; ++p) {
+        key[p] = ld[p * kTcListCols];
+        id[p] = li[p * kTcListCols];
     }
-    ld[p * kTcListCols] = v;
-    li[p * kTcListCols] = idx;
-    return ld[(kc - 1) * kTcListCols];
+    float thr = key[0];
+#pragma unroll
+    for (int p = 1; p < 7; ++p) thr = fmaxf(thr, key[p]);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float mj = j == 0 ? m0 : (j == 1 ? m1 : (j == 2 ? m2 : m3));
+        if (mj < fminf(thr, tau_up) && blk0 + j < n_blocks) {
+            float wk = key[0];
+            int wi = id[0], wp = 0;
+#pragma unroll
+            for (int p = 1; p < 7; ++p) {
+                const bool worse = key[p] > wk || (key[p] == wk && id[p] > wi);
+                wk = worse ? key[p] : wk;
+                wi = worse ? id[p] : wi;
+                wp = worse ? p : wp;
+            }
+            thr = mj;
+#pragma unroll
+            for (int p = 0; p < 7; ++p) {
+                key[p] = p == wp ? mj : key[p];
+                id[p] = p == wp ? blk0 + j : id[p];
+                thr = fmaxf(thr, key[p]);
+            }
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < 7; ++p) {
+        ld[p * kTcListCols] = key[p];
+        li[p * kTcListCols] = id[p];
+    }
+    return thr;
 }
 
 __device__ __forceinline__ float fmin3(float x, float y, float z) { return fminf(fminf(x, y), z); }   /* one FMNMX3 */
@@ -535,11 +570,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                      * the block it was is found by the exact pass over the block (knn_tc_select_kernel) */
                     if (DBG) dbg_acc[4] += 1;
                     if (hit) {
+                        if (KC <= 3) {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const float mj = j == 0 ? m0 : (j == 1 ? m1 : (j == 2 ? m2 : m3));
-                            if (mj < th && blk0 + j < a.n_blocks) {
-                                if (KC <= 3) {
+                            for (int j = 0; j < 4; ++j) {
+                                const float mj = j == 0 ? m0 : (j == 1 ? m1 : (j == 2 ? m2 : m3));
+                                if (mj < th && blk0 + j < a.n_blocks) {
                                     /* sorted insert, strict '>' keeps the earlier block first among equals */
 #pragma unroll
                                     for (int p = (KC <= 3 ? KC : 1) - 1; p > 0; --p) {
@@ -550,11 +585,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                                     }
                                     if (rk[0] > mj) { rk[0] = mj; ri[0] = blk0 + j; }
                                     thr = rk[(KC <= 3 ? KC : 1) - 1];
-                                } else {
-                                    thr = tc_list_insert(my_ld, my_li, KC, mj, blk0 + j);
+                                    th = fminf(thr, tau_up);
                                 }
-                                th = fminf(thr, tau_up);
                             }
+                        } else {
+                            thr = tc_list_insert4(my_ld, my_li, tau_up, m0, m1, m2, m3, blk0, a.n_blocks);
+                            th = fminf(thr, tau_up);
                         }
                         if (thr < INFINITY && q_ok) atomicMin(tau_p, f2ord(thr));
                     }
