@@ -103,6 +103,7 @@ SIGNATURES = {
     "pe_comm_create": (C.c_int, [C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(vp)]),
     "pe_comm_destroy": (None, [vp]),
     "pe_comm_info": (C.c_int, [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "pe_comm_p2p": (C.c_int, [vp, C.POINTER(C.c_int)]),
     "pe_comm_allgather_f32": (C.c_int, [vp, vp, C.c_int64, vp]),
     "pe_comm_allreduce_sum_f64": (C.c_int, [vp, vp, C.c_int64]),
     "pe_comm_allgather_f32_dev": (C.c_int, [vp, vp, vp, C.c_int64, vp]),
@@ -754,6 +755,12 @@ class Comm:
         check(lib().pe_comm_create(rank, world, uid, device, C.byref(h)))
         self.h = h.value
         self.rank, self.world = rank, world
+
+    def p2p_active(self) -> bool:
+        """True when the all-gathers run as one peer-memory kernel (raises if one of them timed out)"""
+        v = C.c_int(0)
+        check(lib().pe_comm_p2p(self.h, C.byref(v)))
+        return bool(v.value)
 
     def allgather_f32(self, a):
         a = _f32(a).reshape(-1)

@@ -13,7 +13,7 @@
 namespace pe {
 
 std::atomic<int64_t> g_launches{0};
-std::atomic<int> g_opt_knn_tensor{1}, g_opt_forward_tensor{1}, g_opt_forward_fp8{1};
+std::atomic<int> g_opt_knn_tensor{1}, g_opt_forward_tensor{1}, g_opt_forward_fp8{1}, g_opt_p2p{0};
 static thread_local std::string t_error;
 
 void set_error(const char* fmt, ...) {
@@ -179,6 +179,7 @@ int pe_set_option(const char* name, int value) {
     if (n == "knn_tensor") { g_opt_knn_tensor.store(value); return PE_OK; }
     if (n == "forward_tensor") { g_opt_forward_tensor.store(value); return PE_OK; }
     if (n == "forward_fp8") { g_opt_forward_fp8.store(value); return PE_OK; }
+    if (n == "p2p") { g_opt_p2p.store(value); return PE_OK; }
     set_error("unknown option '%s'", name);
     return PE_ERR_INVALID;
 }
@@ -188,6 +189,7 @@ int pe_get_option(const char* name, int* value) {
     if (n == "knn_tensor") { *value = g_opt_knn_tensor.load(); return PE_OK; }
     if (n == "forward_tensor") { *value = g_opt_forward_tensor.load(); return PE_OK; }
     if (n == "forward_fp8") { *value = g_opt_forward_fp8.load(); return PE_OK; }
+    if (n == "p2p") { *value = g_opt_p2p.load(); return PE_OK; }
     set_error("unknown option '%s'", name);
     return PE_ERR_INVALID;
 }

@@ -13,8 +13,10 @@
 #include <dlfcn.h>
 #include <nccl.h>
 
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <vector>
 
 #include "common.h"
 
@@ -73,14 +75,109 @@ int nccl_load() {
 
 using namespace pe;
 
+/* Peer window (NVLink / NVSwitch peer memory): every rank owns [flags | 2 parities x world slots x kWinSlot bytes] in its
+ * HBM and maps the windows of all peers (CUDA IPC).  An all-gather is then ONE kernel per rank: push my block into
+ * slot[rank] of every peer with 16-byte stores over NVLink, publish the call's epoch in every peer's flag word,
+ * wait for the epochs of all peers in my own flags, copy my window out.  The messages of this path are 0.26 - 1.3 MB
+ * per rank: latency bound, which is where a single kernel beats a collective library call. */
+constexpr size_t kWinSlot = 2u << 20;         /* bytes per rank and call */
+constexpr size_t kWinFlags = 4096;
+constexpr int kWinMaxWorld = 16;
+
+struct PeerWin {
+    unsigned char* base[kWinMaxWorld];        /* base[r] = rank r's window as mapped here */
+};
+
 struct pe_comm {
     int rank = 0, world = 1, device = 0;
     ncclComm_t comm = nullptr;
     cudaStream_t stream = nullptr;
     pe::DevBuf send, recv;
+    bool p2p = false;                         /* all ranks mapped all windows */
+    unsigned char* win = nullptr;             /* my window */
+    PeerWin peers{};
+    unsigned int* done = nullptr;             /* CTA counter of the push phase */
+    unsigned int epoch = 0;                   /* calls so far: identical on every rank */
+    int* p2p_err = nullptr;                   /* mapped host flag: a flag wait timed out */
 };
 
+namespace pe_p2p {
+
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+/* grid <= number of SMs (all CTAs resident: the waiting phase must not keep a pushing CTA off the machine) */
+__global__ void __launch_bounds__(256) p2p_allgather_kernel(PeerWin peers, int rank, int world, unsigned int epoch,
+                                                            const uint4* __restrict__ send, size_t n16, uint4* __restrict__ recv,
+                                                            unsigned int* done, int* err) {
+    const size_t slot16 = kWinSlot / 16;
+    const size_t par_off = kWinFlags / 16 + (size_t)(epoch & 1u) * world * slot16;
+    /* 1. push: my block -> slot[rank] of every window (my own included) */
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = tid; i < n16 * world; i += nth) {          /* one (peer, 16 bytes) store per thread and step */
+        const size_t r = i / n16, j = i - r * n16;
+        reinterpret_cast<uint4*>(peers.base[r])[par_off + (size_t)rank * slot16 + j] = send[j];
+    }
+    __threadfence_system();
+    __syncthreads();
+    /* 2. the last CTA to finish publishes the epoch in flag[rank] of every window */
+    __shared__ bool last;
+    if (threadIdx.x == 0) {
+        last = atomicAdd(done, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last) {
+        if (threadIdx.x == 0) *done = 0;
+        __threadfence_system();
+        if ((int)threadIdx.x < world) st_release_sys(reinterpret_cast<unsigned int*>(peers.base[threadIdx.x]) + rank, epoch);
+    }
+    /* 3. wait for every rank's epoch in my flags (bounded: a missing peer becomes an error, not a hung GPU) */
+    if ((int)threadIdx.x < world) {
+        const unsigned int* f = reinterpret_cast<const unsigned int*>(peers.base[rank]) + threadIdx.x;
+        bool ok = false;
+        for (unsigned int spin = 0; spin < (1u << 24); ++spin) {
+            if ((int)(ld_acquire_sys(f) - epoch) >= 0) { ok = true; break; }
+            if (spin > 64) __nanosleep(32);
+        }
+        if (!ok) atomicExch(err, 1);
+    }
+    __syncthreads();
+    /* 4. my window -> recv (rank-major, n16 per rank) */
+    const uint4* w = reinterpret_cast<const uint4*>(peers.base[rank]) + par_off;
+    for (size_t i = tid; i < n16 * world; i += nth) {
+        const size_t r = i / n16, j = i - r * n16;
+        recv[i] = __ldcg(w + r * slot16 + j);      /* L2: the lines were written by peers */
+    }
+}
+
+}  // namespace pe_p2p
+using pe_p2p::p2p_allgather_kernel;
+
 namespace {
+
+/* all-gather of `bytes` per rank on `stream`: the peer-window kernel when it applies, NCCL otherwise */
+int comm_allgather(pe_comm* comm, const void* d_send, void* d_recv, size_t bytes, cudaStream_t stream, int num_sms) {
+    if (comm->p2p && g_opt_p2p.load() != 0 && bytes % 16 == 0 && bytes <= kWinSlot &&
+        (reinterpret_cast<uintptr_t>(d_send) & 15) == 0 && (reinterpret_cast<uintptr_t>(d_recv) & 15) == 0) {
+        ++comm->epoch;
+        size_t ctas = (bytes / 16 * comm->world + 255) / 256;
+        if (ctas > (size_t)num_sms) ctas = num_sms;
+        if (ctas < 1) ctas = 1;
+        p2p_allgather_kernel<<<(unsigned)ctas, 256, 0, stream>>>(comm->peers, comm->rank, comm->world, comm->epoch,
+                                                               static_cast<const uint4*>(d_send), bytes / 16, static_cast<uint4*>(d_recv),
+                                                               comm->done, comm->p2p_err);
+        PE_LAUNCHED();
+        return PE_OK;
+    }
+    PE_NCCL(g_nccl.AllGather(d_send, d_recv, bytes, ncclInt8, comm->comm, stream));
+    return PE_OK;
+}
 
 /* local top-k -> all-gather of [idx block | dist block] per rank -> merge.  T is float or int. */
 template <typename T>
@@ -104,7 +201,7 @@ int sharded_knn(pe_db* db, pe_comm* comm, const void* d_queries, int64_t nq, int
         PE_CHECK(knn_hamming_local(db, static_cast<const uint32_t*>(d_queries), nq, k, send, send + block));
     else
         PE_CHECK(knn_l2_local(db, static_cast<const float*>(d_queries), nq, k, send, reinterpret_cast<float*>(send + block)));
-    PE_NCCL(g_nccl.AllGather(send, recv, 2 * block, ncclInt32, comm->comm, db->stream));
+    PE_CHECK(comm_allgather(comm, send, recv, 2 * block * 4, db->stream, db->num_sms));
     /* candidate (q, shard, p): idx at shard*2*block + q*k + p, dist `block` entries further */
     if (hamming)
         return knn_merge_i32(db, recv + block, recv, 2 * (long long)block, world, nq, k, d_out_idx, reinterpret_cast<int32_t*>(d_out_dist));
@@ -154,6 +251,72 @@ int pe_comm_create(int rank, int world, const char* id128, int device, pe_comm**
         set_error("cudaStreamCreate failed");
         return PE_ERR_CUDA;
     }
+    /* peer windows: allocate, exchange the IPC handles through NCCL, map.  Any failure on any rank leaves every rank on
+     * the NCCL all-gather (the outcome is agreed with an all-reduce), it is not an error. */
+    if (world > 1 && world <= kWinMaxWorld && getenv("PE_NO_P2P") == nullptr) {
+        const size_t win_bytes = kWinFlags + 2 * (size_t)world * kWinSlot;
+        int ok = 1;
+        cudaIpcMemHandle_t mine;
+        memset(&mine, 0, sizeof(mine));
+        if (cudaMalloc(reinterpret_cast<void**>(&c->win), win_bytes) != cudaSuccess) { ok = 0; c->win = nullptr; }
+        if (ok && cudaMemset(c->win, 0, kWinFlags) != cudaSuccess) ok = 0;
+        if (ok && cudaIpcGetMemHandle(&mine, c->win) != cudaSuccess) ok = 0;
+        if (ok && cudaMalloc(reinterpret_cast<void**>(&c->done), 4) != cudaSuccess) ok = 0;
+        if (ok && cudaMemset(c->done, 0, 4) != cudaSuccess) ok = 0;
+        if (ok && cudaHostAlloc(reinterpret_cast<void**>(&c->p2p_err), sizeof(int), cudaHostAllocMapped) != cudaSuccess) ok = 0;
+        if (ok) *c->p2p_err = 0;
+        cudaGetLastError();
+        /* [handle 64 B | ok 4 B | pad] per rank */
+        constexpr size_t rec = 128;
+        std::vector<unsigned char> h_all((size_t)world * rec, 0), h_me(rec, 0);
+        memcpy(h_me.data(), &mine, sizeof(mine));
+        memcpy(h_me.data() + 64, &ok, 4);
+        unsigned char* d_x = nullptr;
+        bool exchanged = false;
+        if (cudaMalloc(reinterpret_cast<void**>(&d_x), (size_t)(world + 1) * rec) == cudaSuccess) {
+            if (cudaMemcpy(d_x, h_me.data(), rec, cudaMemcpyHostToDevice) == cudaSuccess &&
+                g_nccl.AllGather(d_x, d_x + rec, rec, ncclInt8, c->comm, c->stream) == ncclSuccess &&
+                cudaStreamSynchronize(c->stream) == cudaSuccess &&
+                cudaMemcpy(h_all.data(), d_x + rec, (size_t)world * rec, cudaMemcpyDeviceToHost) == cudaSuccess)
+                exchanged = true;
+        }
+        int all_ok = exchanged ? 1 : 0;
+        for (int r = 0; r < world && all_ok; ++r) {
+            int okr = 0;
+            memcpy(&okr, h_all.data() + (size_t)r * rec + 64, 4);
+            if (!okr) all_ok = 0;
+        }
+        if (all_ok) {
+            for (int r = 0; r < world; ++r) {
+                if (r == rank) { c->peers.base[r] = c->win; continue; }
+                cudaIpcMemHandle_t hnd;
+                memcpy(&hnd, h_all.data() + (size_t)r * rec, sizeof(hnd));
+                void* ptr = nullptr;
+                if (cudaIpcOpenMemHandle(&ptr, hnd, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { all_ok = 0; cudaGetLastError(); break; }
+                c->peers.base[r] = static_cast<unsigned char*>(ptr);
+            }
+        }
+        /* second agreement round: did everybody map everything? */
+        int agreed = 0;
+        if (exchanged) {
+            memset(h_me.data(), 0, rec);
+            memcpy(h_me.data(), &all_ok, 4);
+            if (cudaMemcpy(d_x, h_me.data(), rec, cudaMemcpyHostToDevice) == cudaSuccess &&
+                g_nccl.AllGather(d_x, d_x + rec, rec, ncclInt8, c->comm, c->stream) == ncclSuccess &&
+                cudaStreamSynchronize(c->stream) == cudaSuccess &&
+                cudaMemcpy(h_all.data(), d_x + rec, (size_t)world * rec, cudaMemcpyDeviceToHost) == cudaSuccess) {
+                agreed = 1;
+                for (int r = 0; r < world; ++r) {
+                    int okr = 0;
+                    memcpy(&okr, h_all.data() + (size_t)r * rec, 4);
+                    if (!okr) agreed = 0;
+                }
+            }
+        }
+        if (d_x) cudaFree(d_x);
+        cudaGetLastError();
+        c->p2p = agreed != 0;
+    }
     *out = c;
     return PE_OK;
 }
@@ -162,6 +325,13 @@ void pe_comm_destroy(pe_comm* comm) {
     if (!comm) return;
     cudaSetDevice(comm->device);
     if (comm->stream) { cudaStreamSynchronize(comm->stream); cudaStreamDestroy(comm->stream); }
+    cudaDeviceSynchronize();
+    for (int r = 0; r < comm->world && r < kWinMaxWorld; ++r)
+        if (r != comm->rank && comm->peers.base[r]) cudaIpcCloseMemHandle(comm->peers.base[r]);
+    if (comm->win) cudaFree(comm->win);
+    if (comm->done) cudaFree(comm->done);
+    if (comm->p2p_err) cudaFreeHost(comm->p2p_err);
+    cudaGetLastError();
     comm->send.release();
     comm->recv.release();
     if (comm->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm->comm);
@@ -172,6 +342,16 @@ int pe_comm_info(const pe_comm* comm, int* rank, int* world) {
     PE_REQUIRE(comm != nullptr, "null comm");
     if (rank) *rank = comm->rank;
     if (world) *world = comm->world;
+    return PE_OK;
+}
+
+int pe_comm_p2p(const pe_comm* comm, int* active) {
+    PE_REQUIRE(comm != nullptr, "null comm");
+    if (active) *active = comm->p2p && g_opt_p2p.load() != 0 ? 1 : 0;
+    if (comm->p2p_err && *reinterpret_cast<volatile int*>(comm->p2p_err) != 0) {
+        set_error("peer-window all-gather: a rank did not publish its epoch in time");
+        return PE_ERR_NCCL;
+    }
     return PE_OK;
 }
 
@@ -193,8 +373,7 @@ int pe_comm_allgather_f32_dev(pe_comm* comm, pe_net* net, const float* d_send, i
     PE_REQUIRE(comm->device == net->device, "communicator and net live on different devices");
     if (n == 0) return PE_OK;
     PE_CHECK(net_ensure_device(net));
-    PE_NCCL(g_nccl.AllGather(d_send, d_recv, (size_t)n, ncclFloat32, comm->comm, net->stream));
-    return PE_OK;
+    return comm_allgather(comm, d_send, d_recv, (size_t)n * 4, net->stream, net->num_sms);
 }
 
 int pe_comm_allreduce_sum_f64(pe_comm* comm, double* buf, int64_t n) {

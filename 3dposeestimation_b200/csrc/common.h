@@ -203,7 +203,7 @@ int knn_tc_select_hamming(pe_db* db, const float* cand_d, const int* cand_i, int
                           int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist);
 int knn_tc_check(pe_db* db);
 /* runtime switches (pe_set_option): tensor-core paths on/off */
-extern std::atomic<int> g_opt_knn_tensor, g_opt_forward_tensor, g_opt_forward_fp8;
+extern std::atomic<int> g_opt_knn_tensor, g_opt_forward_tensor, g_opt_forward_fp8, g_opt_p2p;
 /* pose.cu */
 int pose_histogram_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
                        const int* rot_inv, int n_rot, const float* bins, int n_bins, float* out_host);

@@ -316,7 +316,8 @@ def gpu_arm(args, rank, world, local_rank, dist):
                                "DB 1,000,200 templates (300 x 3,334) row-sharded over the GPUs",
                    "net": NET, "batch_per_gpu": BATCH, "templates": T, "k": K, "seed": SEED,
                    "l2_flush": "inputs alternate between two 470 MB batches (> 126 MB L2)",
-                   "parallelism": f"patches x{world} (no comm), DB rows /{world} + NCCL all-gather + merge" if world > 1 else "single GPU"},
+                   "parallelism": (f"patches x{world} (no comm), DB rows /{world} + all-gather "
+                                   f"({'one peer-memory kernel over NVLink (CUDA IPC windows)' if comm.p2p_active() else 'NCCL'}) + merge") if world > 1 else "single GPU"},
         "roofline": {"kernel": ("conv1_tc_kernel<7, e4m3 cross terms>" if fwd_fp8 else "conv1_tc_kernel<7, fp16 x3>") if fwd_tensor else "conv1_pool_act_kernel<7>", "bound": "tensor", "achieved": achieved_tf,
                      "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
                      "frac": achieved_tf / peaks["bf16_tflops_sustained"], "traffic": traffic,

@@ -331,6 +331,12 @@ PE_API int pe_comm_unique_id(char* id128);
 PE_API int pe_comm_create(int rank, int world, const char* id128, int device, pe_comm** out);
 PE_API void pe_comm_destroy(pe_comm* comm);
 PE_API int pe_comm_info(const pe_comm* comm, int* rank, int* world);
+/* *active = 1 when every rank mapped every peer's window (CUDA IPC over NVLink) AND pe_set_option("p2p", 1) selected the
+ * peer-memory all-gather (one kernel: push to every peer's window, publish the epoch, wait, copy out) instead of the
+ * NCCL call.  Default 0: measured on B200 (tools/p2p_check.py, 262 KB per rank) the kernel takes 15 us at 2 GPUs and
+ * 21 us at 8 against 12 and 23 us for ncclAllGather - a tie, so NCCL stays the default.  PE_NO_P2P=1 skips the window
+ * set-up.  Also returns PE_ERR_NCCL when an earlier peer-window all-gather timed out waiting for a rank. */
+PE_API int pe_comm_p2p(const pe_comm* comm, int* active);
 /* all-gather n floats per rank (host buffers; descriptor exchange) */
 PE_API int pe_comm_allgather_f32(pe_comm* comm, const float* send, int64_t n, float* recv);
 PE_API int pe_comm_allreduce_sum_f64(pe_comm* comm, double* buf, int64_t n);
