@@ -103,6 +103,7 @@ SIGNATURES = {
     "pe_comm_create": (C.c_int, [C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(vp)]),
     "pe_comm_destroy": (None, [vp]),
     "pe_comm_info": (C.c_int, [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "pe_net_fp8_state": (C.c_int, [vp, C.POINTER(C.c_int)]),
     "pe_comm_p2p": (C.c_int, [vp, C.POINTER(C.c_int)]),
     "pe_comm_allgather_f32": (C.c_int, [vp, vp, C.c_int64, vp]),
     "pe_comm_allreduce_sum_f64": (C.c_int, [vp, vp, C.c_int64]),
@@ -389,6 +390,12 @@ class Net:
 
     def sync(self):
         check(lib().pe_net_sync(self.h))
+
+    def fp8_state(self) -> int:
+        """conv1 cross terms of the current weights: 0 not decided yet, 1 e4m3, 2 fp16 (pe_net_fp8_state)"""
+        v = C.c_int(0)
+        check(lib().pe_net_fp8_state(self.h, C.byref(v)))
+        return v.value
 
     def profile(self, enable: bool):
         check(lib().pe_net_profile(self.h, int(enable)))

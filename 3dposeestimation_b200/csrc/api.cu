@@ -13,7 +13,7 @@
 namespace pe {
 
 std::atomic<int64_t> g_launches{0};
-std::atomic<int> g_opt_knn_tensor{1}, g_opt_forward_tensor{1}, g_opt_forward_fp8{1}, g_opt_p2p{0};
+std::atomic<int> g_opt_knn_tensor{1}, g_opt_forward_tensor{1}, g_opt_forward_fp8{1}, g_opt_p2p{0}, g_opt_conv2_tensor{1};
 static thread_local std::string t_error;
 
 void set_error(const char* fmt, ...) {
@@ -180,6 +180,7 @@ int pe_set_option(const char* name, int value) {
     if (n == "forward_tensor") { g_opt_forward_tensor.store(value); return PE_OK; }
     if (n == "forward_fp8") { g_opt_forward_fp8.store(value); return PE_OK; }
     if (n == "p2p") { g_opt_p2p.store(value); return PE_OK; }
+    if (n == "conv2_tensor") { g_opt_conv2_tensor.store(value); return PE_OK; }
     set_error("unknown option '%s'", name);
     return PE_ERR_INVALID;
 }
@@ -190,6 +191,7 @@ int pe_get_option(const char* name, int* value) {
     if (n == "forward_tensor") { *value = g_opt_forward_tensor.load(); return PE_OK; }
     if (n == "forward_fp8") { *value = g_opt_forward_fp8.load(); return PE_OK; }
     if (n == "p2p") { *value = g_opt_p2p.load(); return PE_OK; }
+    if (n == "conv2_tensor") { *value = g_opt_conv2_tensor.load(); return PE_OK; }
     set_error("unknown option '%s'", name);
     return PE_ERR_INVALID;
 }
@@ -335,6 +337,13 @@ void pe_net_destroy(pe_net* net) {
     delete net;
 }
 
+int pe_net_fp8_state(const pe_net* net, int* state) {
+    PE_REQUIRE(net && state, "null pointer");
+    const int opt = g_opt_forward_fp8.load();
+    *state = opt >= 2 ? 1 : (opt == 0 ? 2 : net->fp8_state);
+    return PE_OK;
+}
+
 int pe_net_info(const pe_net* net, int* batch, int* channels, int* height, int* width, int* desc_dim) {
     PE_REQUIRE(net != nullptr, "null net");
     if (batch) *batch = net->def.batch;
@@ -390,6 +399,7 @@ int pe_net_set_blob(pe_net* net, int blob, const float* host, int64_t count) {
                net->blobs[blob].size(), (long long)count);
     memcpy(net->blobs[blob].data(), host, (size_t)count * sizeof(float));
     net->weights_dirty = true;
+    net->fp8_state = 0;
     return PE_OK;
 }
 int pe_net_get_blob(const pe_net* net, int blob, float* host, int64_t count) {
@@ -419,6 +429,7 @@ int pe_net_fill(pe_net* net, uint64_t seed, int mode) {
         }
     }
     net->weights_dirty = true;
+    net->fp8_state = 0;
     return PE_OK;
 }
 int pe_net_save_weights(const pe_net* net, const char* path) {
@@ -457,6 +468,7 @@ int pe_net_load_weights(pe_net* net, const char* path) {
     }
     net->blobs.swap(tmp);
     net->weights_dirty = true;
+    net->fp8_state = 0;
     return PE_OK;
 }
 

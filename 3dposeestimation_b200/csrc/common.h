@@ -122,6 +122,7 @@ struct pe_net {
     int* d_slot = nullptr;            /* patch channel -> conv1 input slot or -1 */
     /* tensor path (conv_tc.cu): Toeplitz fp16 hi/lo conv1 weights, output scale, pinned failure flag */
     bool c1_tc_ready = false;
+    int fp8_state = 0;         /* conv1 cross terms for these weights: 0 not calibrated yet, 1 e4m3, 2 fp16 (see net_forward_dev) */
     void* d_z1 = nullptr;
     float c1_inv_scale = 1.f;
     bool c2_tc_ready = false;
@@ -203,7 +204,7 @@ int knn_tc_select_hamming(pe_db* db, const float* cand_d, const int* cand_i, int
                           int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist);
 int knn_tc_check(pe_db* db);
 /* runtime switches (pe_set_option): tensor-core paths on/off */
-extern std::atomic<int> g_opt_knn_tensor, g_opt_forward_tensor, g_opt_forward_fp8, g_opt_p2p;
+extern std::atomic<int> g_opt_knn_tensor, g_opt_forward_tensor, g_opt_forward_fp8, g_opt_p2p, g_opt_conv2_tensor;
 /* pose.cu */
 int pose_histogram_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
                        const int* rot_inv, int n_rot, const float* bins, int n_bins, float* out_host);

@@ -648,6 +648,7 @@ int conv1_tc_prepare(pe_net* net) {
         *net->tc_err = 0;
     }
     net->c1_inv_scale = std::ldexp(1.f, -(log2_sw + kLog2Sx));
+    net->fp8_state = 0;                       /* new weights: the e4m3 cross terms are re-qualified on the next batch */
     net->c1_tc_ready = true;
     return PE_OK;
 }
@@ -727,7 +728,9 @@ int conv1_tc_launch(pe_net* net, const float* d_patches, int patch_c, long long 
     static const int dbg = getenv("PE_C1_DBG") ? atoi(getenv("PE_C1_DBG")) : 0;
     a.dbg = dbg;
     const int grid = (int)(n < net->num_sms ? n : net->num_sms);
-    const bool f8 = g_opt_forward_fp8.load() != 0;
+    /* forward_fp8: 0 never, 2 always, 1 (default) where the calibration of net_forward_dev qualified these weights */
+    const int opt8 = g_opt_forward_fp8.load();
+    const bool f8 = opt8 >= 2 || (opt8 == 1 && net->fp8_state == 1);
     auto launch = [&](auto kernel) -> int {
         PE_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kC1TcSmem));
         kernel<<<grid, kC1TcThreads, kC1TcSmem, net->stream>>>(a);

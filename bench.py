@@ -299,7 +299,7 @@ def gpu_arm(args, rank, world, local_rank, dist):
     conv1_flops = 2.0 * MAC_PER_PATCH["conv1"] * BATCH
     achieved_tf = conv1_flops / (conv1_ms * 1e-3) / 1e12 if conv1_ms > 0 else 0.0
     fwd_tensor = capi.get_option("forward_tensor") != 0
-    fwd_fp8 = capi.get_option("forward_fp8") != 0
+    fwd_fp8 = net.fp8_state() == 1            # forward_fp8 = 1: qualified per set of weights on the first batch
     n_mma = 240 if fwd_fp8 else 360           # per patch: 2 tiles x 15 input rows x 4 pixel pairs x (fp16 hi.hi + e4m3 cross | 3 fp16)
     traffic = None
     try:

@@ -60,11 +60,17 @@ PE_API int64_t pe_launch_count(void);
 
 /* runtime switches (process-wide).  "knn_tensor" (default 1): L2 kNN scan on the tcgen05 tensor path for
  * descriptors of up to 16 dimensions and k <= 5, 0 = fp32 SIMT scan.  "forward_tensor" (default 1): conv / FC
- * layers on the tcgen05 split-fp16 path, 0 = fp32 SIMT kernels.  "forward_fp8" (default 1): conv1 takes its two
- * cross terms (hi.lo + lo.hi) from one e4m3 MMA instead of two fp16 MMAs (descriptor error ~3e-5 of the row max
- * instead of ~1e-6, inside the 1e-4 acceptance; inputs must satisfy |x| <= 28), 0 = all three terms in fp16.
- * Every path is CUDA; none is a CPU fallback. */
+ * layers on the tcgen05 split-fp16 path, 0 = fp32 SIMT kernels.  "forward_fp8": conv1 takes its two cross terms
+ * (hi.lo + lo.hi) from one e4m3 MMA instead of two fp16 MMAs (conv1 1.45x faster; descriptor error ~1-3e-5 of the row
+ * max instead of ~1e-6 on the 16-d nets, but up to 1.5e-4 where the last layers cancel, e.g. manifold.prototxt with
+ * D = 3; inputs must satisfy |x| <= 28).  1 (default) = per set of weights, decided on the first batch of >= 64
+ * patches: it is forwarded both ways (<= 256 patches) and e4m3 is kept only if it stays within 3e-5 of the all-fp16
+ * split there (pe_net_fp8_state reports the outcome); 0 = never; 2 = always (out-of-range input: PE_ERR_INVALID).
+ * "conv2_tensor" (default 1): 0 pairs the tensor conv1 with the fp32 SIMT conv2 (conv1 then writes fp32 pool1 instead
+ * of the packed fp16 image; a test switch).  Every path is CUDA; none is a CPU fallback. */
 PE_API int pe_set_option(const char* name, int value);
+/* conv1 cross terms of this net's current weights: 0 not decided yet (all-fp16 until then), 1 e4m3, 2 fp16 */
+PE_API int pe_net_fp8_state(const pe_net* net, int* state);
 PE_API int pe_get_option(const char* name, int* value);
 
 /* pinned host memory + raw device memory helpers (harness plumbing) */

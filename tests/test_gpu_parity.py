@@ -82,9 +82,17 @@ def test_forward_input_range_is_checked(gpu, synth):
     x = synth.make_patches(3, 0, 2, 7, 2)
     ok = net.compute_descriptors(x)
     x[1, 5, 5, 2] = 40.0
-    with pytest.raises(gpu.PoseError) as e:
-        net.compute_descriptors(x)
-    assert e.value.code == gpu.PE_ERR_INVALID and "forward_fp8" in str(e.value)
+    gpu.set_option("forward_fp8", 2)          # e4m3 cross terms forced
+    try:
+        with pytest.raises(gpu.PoseError) as e:
+            net.compute_descriptors(x)
+        assert e.value.code == gpu.PE_ERR_INVALID and "forward_fp8" in str(e.value)
+    finally:
+        gpu.set_option("forward_fp8", 1)
+    # default (qualified per set of weights): a first batch beyond the e4m3 range keeps the all-fp16 split, no error
+    big = np.concatenate([synth.make_patches(3, 0, 70, 7, 2), x])
+    big[3, 9, 9, 1] = 40.0
+    assert np.isfinite(net.compute_descriptors(big)).all() and net.fp8_state() == 2
     gpu.set_option("forward_fp8", 0)
     try:
         wide = net.compute_descriptors(x)
@@ -95,6 +103,30 @@ def test_forward_input_range_is_checked(gpu, synth):
         assert "forward_tensor" in str(e.value)
     finally:
         gpu.set_option("forward_fp8", 1)
+
+
+def test_e4m3_cross_terms_are_qualified_per_weights(gpu, po, synth):
+    """forward_fp8 = 1: the 16-d net keeps the e4m3 cross terms, manifold.prototxt (D = 3, cancelling last layers:
+    1.5e-4 with e4m3 on these patches) falls back to the all-fp16 split; either way the descriptors hold the
+    acceptance, also with the fp32 SIMT conv2 behind the tensor conv1 (fp32 pool1 output of conv1_tc)"""
+    for name, seed, state in (("manifold_rgbdnor_16", 3, 1), ("manifold", 4, 2)):
+        net, oracle, ref = make_net(gpu, po, synth, name, seed)
+        x = synth.make_patches(synth.BASE_SEED + 2, 11, 160, ref.channels, 7)
+        want = oracle.forward(x)
+        assert net.fp8_state() == 0
+        assert rowscale_err(net.compute_descriptors(x), want) < DESC_TOL
+        assert net.fp8_state() == state
+        gpu.set_option("conv2_tensor", 0)
+        try:
+            for f8 in (1, 0, 2) if state == 1 else (1, 0):
+                gpu.set_option("forward_fp8", f8)
+                assert rowscale_err(net.compute_descriptors(x), want) < DESC_TOL
+        finally:
+            gpu.set_option("conv2_tensor", 1)
+            gpu.set_option("forward_fp8", 1)
+        # new weights are qualified again
+        net.set_blobs(synth.make_blobs(ref.blob_names, ref.blob_shapes, seed + 100, mode=1))
+        assert net.fp8_state() == 0
 
 
 def test_forward_device_entry_and_chunking(gpu, po, synth, fwd_path):
