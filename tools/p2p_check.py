@@ -24,7 +24,8 @@ lo, hi = sharding.shard_rows(rank, world, T)
 shard = capi.TemplateDB(desc=t[lo:hi], row_offset=lo, t_total=T, device=local)
 full = capi.TemplateDB(desc=t, device=local) if rank == 0 else None
 ok = True
-active = comm.p2p_active()
+capi.set_option("p2p", 1)
+active = comm.p2p_active()          # windows mapped on every rank (with the option on)
 for nq, k in ((1, 1), (257, 3), (4096, 1), (8192, 5), (4099, 5)):
     q = (t[rng.integers(0, T, nq)] + 0.05 * rng.standard_normal((nq, D))).astype(np.float32)
     res = {}
@@ -58,6 +59,7 @@ flags = [None] * world
 dist.all_gather_object(flags, ok)
 if rank == 0:
     print(f"p2p_check world={world} peer_windows={active} all_equal={all(flags)} allgather 262 KB/rank: peer kernel {times[1]:.1f} us, NCCL {times[0]:.1f} us")
+capi.set_option("p2p", 0)
 comm.close()
 dist.destroy_process_group()
 sys.exit(0 if all(flags) else 1)
