@@ -112,6 +112,10 @@ SIGNATURES = {
     "pe_match_patches": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_int, C.c_int, vp, vp, vp]),
     "pe_knn_sharded_dev": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
     "pe_knn_hamming_sharded": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "pe_knn_hamming_sharded_dev": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "pe_match_patches_dev": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_int, C.c_int, vp, vp, vp]),
+    "pe_histogram_sharded_dev": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_int, vp, C.c_int, vp, C.c_int, vp]),
+    "pe_confusion_sharded_dev": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp]),
     "pe_depth2normals": (C.c_int, [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, vp]),
     "pe_depth2normals_dev": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, vp]),
     "pe_sample_patches": (C.c_int, [C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int64, C.c_float, C.c_float,
@@ -522,6 +526,31 @@ class TemplateDB:
         check(lib().pe_match_patches(net.h, self.h, comm.h if comm else None, _ptr(x), n, c, k, _ptr(idx), _ptr(dist),
                                      _ptr(desc) if want_desc else None))
         return (idx, dist, desc) if want_desc else (idx, dist)
+
+    def match_patches_dev(self, net, comm, d_patches, n, k, d_idx, d_dist, d_desc=None, patch_offset=0):
+        """pe_match_patches_dev: device patches -> neighbours of this rank's patches; asynchronous, forward on the net's
+        stream, exchange + scan + merge on the DB's stream (sync() completes it)"""
+        src = d_patches.offset(patch_offset * 4096 * net.channels) if isinstance(d_patches, DeviceArray) else d_patches
+        check(lib().pe_match_patches_dev(net.h, self.h, comm.h if comm else None, src, n, net.channels, k, d_idx.ptr, d_dist.ptr,
+                                         d_desc.ptr if d_desc is not None else None))
+
+    def knn_hamming_sharded_dev(self, comm, d_q, nq, k, d_idx, d_dist):
+        check(lib().pe_knn_hamming_sharded_dev(self.h, comm.h if comm else None, d_q.ptr, nq, k, d_idx.ptr, d_dist.ptr))
+
+    def histogram_sharded_dev(self, comm, d_idx, d_qlabels, nq_local, k, rot_inv, bins):
+        """histogram of the query set split over the ranks (every rank passes its own nq_local queries)"""
+        rot, bn = _i32(rot_inv), _f32(bins)
+        out = np.empty(bn.size + 2, np.float32)
+        check(lib().pe_histogram_sharded_dev(self.h, comm.h if comm else None, d_idx.ptr, d_qlabels.ptr, nq_local, k, _ptr(rot),
+                                             rot.size, _ptr(bn), bn.size, _ptr(out)))
+        return out
+
+    def confusion_sharded_dev(self, comm, d_idx, d_qlabels, nq_local, k, class_to_local, n_local, nr_test_poses):
+        c2l = _i32(class_to_local)
+        out = np.empty((n_local, n_local), np.float32)
+        check(lib().pe_confusion_sharded_dev(self.h, comm.h if comm else None, d_idx.ptr, d_qlabels.ptr, nq_local, k, _ptr(c2l),
+                                             c2l.size, n_local, nr_test_poses, _ptr(out)))
+        return out
 
     def knn_sharded_dev(self, comm, d_q, nq, k, d_idx, d_dist):
         check(lib().pe_knn_sharded_dev(self.h, comm.h if comm else None, d_q.ptr if isinstance(d_q, DeviceArray) else d_q,

@@ -13,7 +13,7 @@
 namespace pe {
 
 std::atomic<int64_t> g_launches{0};
-std::atomic<int> g_opt_knn_tensor{1}, g_opt_forward_tensor{1}, g_opt_forward_fp8{1}, g_opt_p2p{0}, g_opt_conv2_tensor{1};
+std::atomic<int> g_opt_knn_tensor{1}, g_opt_forward_tensor{1}, g_opt_forward_fp8{0}, g_opt_p2p{0}, g_opt_conv2_tensor{1}, g_opt_knn_certify{1};
 static thread_local std::string t_error;
 
 void set_error(const char* fmt, ...) {
@@ -181,6 +181,7 @@ int pe_set_option(const char* name, int value) {
     if (n == "forward_fp8") { g_opt_forward_fp8.store(value); return PE_OK; }
     if (n == "p2p") { g_opt_p2p.store(value); return PE_OK; }
     if (n == "conv2_tensor") { g_opt_conv2_tensor.store(value); return PE_OK; }
+    if (n == "knn_certify") { g_opt_knn_certify.store(value); return PE_OK; }
     set_error("unknown option '%s'", name);
     return PE_ERR_INVALID;
 }
@@ -192,6 +193,7 @@ int pe_get_option(const char* name, int* value) {
     if (n == "forward_fp8") { *value = g_opt_forward_fp8.load(); return PE_OK; }
     if (n == "p2p") { *value = g_opt_p2p.load(); return PE_OK; }
     if (n == "conv2_tensor") { *value = g_opt_conv2_tensor.load(); return PE_OK; }
+    if (n == "knn_certify") { *value = g_opt_knn_certify.load(); return PE_OK; }
     set_error("unknown option '%s'", name);
     return PE_ERR_INVALID;
 }
@@ -484,14 +486,7 @@ int pe_compute_descriptors_dev(pe_net* net, const float* d_patches_hwc, int64_t 
     return net_forward_dev(net, d_patches_hwc, n, patch_channels, d_out_desc, net->def.desc_dim);
 }
 
-int pe_compute_descriptors(pe_net* net, const float* patches_hwc, int64_t n, int patch_channels, float* out_desc) {
-    PE_REQUIRE(net != nullptr, "null net");
-    PE_REQUIRE(n >= 0, "negative sample count");
-    PE_REQUIRE(patch_channels == net->def.channels, "patches have %d channels, net input has %d",
-               patch_channels, net->def.channels);
-    PE_CHECK(net_ensure_device(net));
-    if (n == 0) return PE_OK;
-    PE_REQUIRE(patches_hwc && out_desc, "null pointer");
+static int compute_descriptors_once(pe_net* net, const float* patches_hwc, int64_t n, int patch_channels, float* out_desc) {
     const int D = net->def.desc_dim;
     const size_t patch_floats = (size_t)4096 * patch_channels;
     const int64_t sub = 1024; /* patches per H2D stage: copy of stage i+1 overlaps compute of stage i */
@@ -515,6 +510,21 @@ int pe_compute_descriptors(pe_net* net, const float* patches_hwc, int64_t n, int
     PE_CUDA(cudaMemcpyAsync(out_desc, net->out_stage.p, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToHost, net->stream));
     PE_CUDA(cudaStreamSynchronize(net->stream));
     return forward_tc_check(net);
+}
+
+int pe_compute_descriptors(pe_net* net, const float* patches_hwc, int64_t n, int patch_channels, float* out_desc) {
+    PE_REQUIRE(net != nullptr, "null net");
+    PE_REQUIRE(n >= 0, "negative sample count");
+    PE_REQUIRE(patch_channels == net->def.channels, "patches have %d channels, net input has %d",
+               patch_channels, net->def.channels);
+    PE_CHECK(net_ensure_device(net));
+    if (n == 0) return PE_OK;
+    PE_REQUIRE(patches_hwc && out_desc, "null pointer");
+    /* PE_RETRY_FP16: opt-in e4m3 cross terms (forward_fp8 = 1) met an input beyond their range; the net has switched
+     * to the all-fp16 split, the batch is forwarded again */
+    int st = compute_descriptors_once(net, patches_hwc, n, patch_channels, out_desc);
+    if (st == PE_RETRY_FP16) st = compute_descriptors_once(net, patches_hwc, n, patch_channels, out_desc);
+    return st == PE_RETRY_FP16 ? PE_ERR_INVALID : st;
 }
 
 int pe_net_profile(pe_net* net, int enable) {
@@ -562,7 +572,8 @@ int pe_net_sync(pe_net* net) {
     PE_REQUIRE(net != nullptr, "null net");
     PE_CHECK(net_ensure_device(net));
     PE_CUDA(cudaStreamSynchronize(net->stream));
-    return forward_tc_check(net);
+    const int st = forward_tc_check(net);
+    return st == PE_RETRY_FP16 ? PE_ERR_INVALID : st;   /* device entry points cannot replay the caller's batch */
 }
 
 int pe_synth_patches_dev(pe_net* net, uint64_t seed, int64_t first_index, int64_t n, int channels,
@@ -721,6 +732,10 @@ void pe_db_destroy(pe_db* db) {
                       &db->scratch, &db->scratch2, &db->gather, &db->boot, &db->m_q, &db->m_ci, &db->m_cd, &db->m_ri, &db->m_rd})
         b->release();
     if (db->ev_match) cudaEventDestroy(db->ev_match);
+    for (int i = 0; i < 2; ++i) {
+        db->m_desc[i].release();
+        if (db->ev_free[i]) cudaEventDestroy(db->ev_free[i]);
+    }
     if (db->stream && db->own_stream) cudaStreamDestroy(db->stream);
     delete db;
 }
@@ -736,6 +751,7 @@ int pe_db_sync(pe_db* db) {
     PE_REQUIRE(db != nullptr, "null db");
     PE_CUDA(cudaSetDevice(db->device));
     PE_CUDA(cudaStreamSynchronize(db->stream));
+    PE_CHECK(comm_check(db->last_comm));
     return knn_tc_check(db);
 }
 

@@ -179,20 +179,27 @@ int comm_allgather(pe_comm* comm, const void* d_send, void* d_recv, size_t bytes
     return PE_OK;
 }
 
-/* local top-k -> all-gather of [idx block | dist block] per rank -> merge.  T is float or int. */
+/* local top-k -> all-gather of [idx block | dist block] per rank -> merge.  T is float or int.
+ * Every rank scans its shard for all nq queries; the merged neighbours are written for queries
+ * [q_first, q_first + q_count) only (q_count < 0: all of them), which is what a rank that owns a slice of the query
+ * batch needs (pe_match_patches*). */
 template <typename T>
 int sharded_knn(pe_db* db, pe_comm* comm, const void* d_queries, int64_t nq, int k, int32_t* d_out_idx, T* d_out_dist,
-                bool hamming) {
+                bool hamming, int64_t q_first = 0, int64_t q_count = -1) {
     PE_REQUIRE(db != nullptr, "null db");
     PE_REQUIRE(nq >= 0 && k >= 1 && k <= 16, "bad k / nq");
     if (nq == 0) return PE_OK;
+    if (q_count < 0) { q_first = 0; q_count = nq; }
     const int world = comm ? comm->world : 1;
     if (world == 1) {
-        return hamming ? knn_hamming_local(db, static_cast<const uint32_t*>(d_queries), nq, k, d_out_idx, reinterpret_cast<int32_t*>(d_out_dist))
-                       : knn_l2_local(db, static_cast<const float*>(d_queries), nq, k, d_out_idx, reinterpret_cast<float*>(d_out_dist));
+        const size_t row = hamming ? (size_t)db->words : (size_t)db->dim;
+        const void* q = static_cast<const char*>(d_queries) + (size_t)q_first * row * 4;
+        return hamming ? knn_hamming_local(db, static_cast<const uint32_t*>(q), q_count, k, d_out_idx, reinterpret_cast<int32_t*>(d_out_dist))
+                       : knn_l2_local(db, static_cast<const float*>(q), q_count, k, d_out_idx, reinterpret_cast<float*>(d_out_dist));
     }
     PE_REQUIRE(comm->device == db->device, "communicator and DB live on different devices");
     PE_CUDA(cudaSetDevice(db->device));
+    db->last_comm = comm;
     const size_t block = (size_t)nq * k; /* entries per rank and per half */
     PE_CHECK(db->gather.reserve((size_t)(world + 1) * 2 * block * 4));
     int32_t* send = db->gather.as<int32_t>();          /* [idx block | dist block] of this rank */
@@ -203,13 +210,40 @@ int sharded_knn(pe_db* db, pe_comm* comm, const void* d_queries, int64_t nq, int
         PE_CHECK(knn_l2_local(db, static_cast<const float*>(d_queries), nq, k, send, reinterpret_cast<float*>(send + block)));
     PE_CHECK(comm_allgather(comm, send, recv, 2 * block * 4, db->stream, db->num_sms));
     /* candidate (q, shard, p): idx at shard*2*block + q*k + p, dist `block` entries further */
+    const int32_t* ci = recv + (size_t)q_first * k;
     if (hamming)
-        return knn_merge_i32(db, recv + block, recv, 2 * (long long)block, world, nq, k, d_out_idx, reinterpret_cast<int32_t*>(d_out_dist));
-    return knn_merge_f32(db, reinterpret_cast<const float*>(recv + block), recv, 2 * (long long)block, world, nq, k, d_out_idx,
+        return knn_merge_i32(db, ci + block, ci, 2 * (long long)block, world, q_count, k, d_out_idx, reinterpret_cast<int32_t*>(d_out_dist));
+    return knn_merge_f32(db, reinterpret_cast<const float*>(ci + block), ci, 2 * (long long)block, world, q_count, k, d_out_idx,
                          reinterpret_cast<float*>(d_out_dist));
 }
 
+/* one stage of the fused test pass on the DB's stream: descriptors of this rank's m patches (already queued on the
+ * net's stream, `ready` recorded behind them) -> [all-gather ->] scan -> select [-> all-gather -> merge] -> the m x k
+ * neighbours of this rank's patches.  Both collectives run on the DB's stream. */
+int match_stage(pe_net* net, pe_db* db, pe_comm* comm, const float* d_desc, int64_t m, int k, int32_t* r_i, float* r_d) {
+    const int world = comm ? comm->world : 1, rank = comm ? comm->rank : 0;
+    const int D = db->dim;
+    if (db->stream != net->stream) {
+        PE_CUDA(cudaEventRecord(db->ev_match, net->stream));
+        PE_CUDA(cudaStreamWaitEvent(db->stream, db->ev_match, 0));
+    }
+    if (world == 1) return knn_l2_local(db, d_desc, m, k, r_i, r_d);
+    PE_CHECK(db->m_q.reserve((size_t)world * m * D * 4));
+    PE_CHECK(comm_allgather(comm, d_desc, db->m_q.p, (size_t)m * D * 4, db->stream, db->num_sms));
+    return sharded_knn<float>(db, comm, db->m_q.p, world * m, k, r_i, r_d, false, rank * m, m);
+}
+
 }  // namespace
+
+namespace pe {
+int comm_check(pe_comm* comm) {
+    if (!comm || !comm->p2p_err) return PE_OK;
+    if (*reinterpret_cast<volatile int*>(comm->p2p_err) == 0) return PE_OK;
+    *comm->p2p_err = 0;
+    set_error("peer-window all-gather: a rank did not publish its epoch in time (results of the call are invalid)");
+    return PE_ERR_NCCL;
+}
+}  // namespace pe
 
 extern "C" {
 
@@ -373,7 +407,10 @@ int pe_comm_allgather_f32_dev(pe_comm* comm, pe_net* net, const float* d_send, i
     PE_REQUIRE(comm->device == net->device, "communicator and net live on different devices");
     if (n == 0) return PE_OK;
     PE_CHECK(net_ensure_device(net));
-    return comm_allgather(comm, d_send, d_recv, (size_t)n * 4, net->stream, net->num_sms);
+    /* always NCCL: the peer-window protocol (epochs, window parity) is only sound for all-gathers that follow each other on
+     * ONE stream, and that stream is the DB's (matcher exchanges); this call runs on the net's */
+    PE_NCCL(g_nccl.AllGather(d_send, d_recv, (size_t)n, ncclFloat32, comm->comm, net->stream));
+    return PE_OK;
 }
 
 int pe_comm_allreduce_sum_f64(pe_comm* comm, double* buf, int64_t n) {
@@ -408,6 +445,7 @@ int pe_knn_sharded(pe_db* db, pe_comm* comm, const float* queries, int64_t nq, i
     PE_CUDA(cudaMemcpyAsync(out_idx, db->out_i.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, db->stream));
     PE_CUDA(cudaMemcpyAsync(out_dist, db->out_d.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, db->stream));
     PE_CUDA(cudaStreamSynchronize(db->stream));
+    PE_CHECK(comm_check(comm));
     return knn_tc_check(db);
 }
 
@@ -416,6 +454,42 @@ int pe_knn_sharded(pe_db* db, pe_comm* comm, const float* queries, int64_t nq, i
  * their k nearest templates.  The batch is cut into 512-patch stages; the H2D copy of stage i+1 runs under the forward
  * and the DB scan of stage i, so on a PCIe-bound box the call takes the copy time plus one stage.  With a
  * communicator every rank must pass the same n; the DB is row-sharded and each stage's descriptors are all-gathered. */
+static int match_patches_once(pe_net* net, pe_db* db, pe_comm* comm, const float* patches_hwc, int64_t n, int patch_channels,
+                              int k, int32_t* out_idx, float* out_dist, float* out_desc) {
+    const int D = net->def.desc_dim;
+    const size_t patch_floats = (size_t)4096 * patch_channels;
+    const int64_t sub = 512;
+    const int64_t stage_n = n < sub ? n : sub;
+    PE_CHECK(net->in_stage[0].reserve(stage_n * patch_floats * sizeof(float)));
+    if (n > sub) PE_CHECK(net->in_stage[1].reserve(stage_n * patch_floats * sizeof(float)));
+    PE_CHECK(net->out_stage.reserve((size_t)n * D * sizeof(float)));
+    PE_CHECK(db->m_ri.reserve((size_t)n * k * 4));
+    PE_CHECK(db->m_rd.reserve((size_t)n * k * 4));
+    if (!db->ev_match) PE_CUDA(cudaEventCreateWithFlags(&db->ev_match, cudaEventDisableTiming));
+    int it = 0;
+    for (int64_t first = 0; first < n; first += sub, ++it) {
+        const int64_t m = n - first < sub ? n - first : sub;
+        const int b = it & 1;
+        if (it >= 2) PE_CUDA(cudaStreamWaitEvent(net->copy_stream, net->ev_done[b], 0));
+        PE_CUDA(cudaMemcpyAsync(net->in_stage[b].p, patches_hwc + first * patch_floats, m * patch_floats * sizeof(float),
+                                cudaMemcpyHostToDevice, net->copy_stream));
+        PE_CUDA(cudaEventRecord(net->ev_in[b], net->copy_stream));
+        PE_CUDA(cudaStreamWaitEvent(net->stream, net->ev_in[b], 0));
+        float* d_desc = net->out_stage.as<float>() + (size_t)first * D;       /* every stage has its own rows: no reuse hazard */
+        PE_CHECK(net_forward_dev(net, net->in_stage[b].as<float>(), m, patch_channels, d_desc, D));
+        PE_CUDA(cudaEventRecord(net->ev_done[b], net->stream));
+        PE_CHECK(match_stage(net, db, comm, d_desc, m, k, db->m_ri.as<int32_t>() + (size_t)first * k, db->m_rd.as<float>() + (size_t)first * k));
+    }
+    PE_CUDA(cudaMemcpyAsync(out_idx, db->m_ri.p, (size_t)n * k * 4, cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaMemcpyAsync(out_dist, db->m_rd.p, (size_t)n * k * 4, cudaMemcpyDeviceToHost, db->stream));
+    if (out_desc) PE_CUDA(cudaMemcpyAsync(out_desc, net->out_stage.p, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaStreamSynchronize(db->stream));
+    PE_CUDA(cudaStreamSynchronize(net->stream));
+    PE_CHECK(forward_tc_check(net));
+    PE_CHECK(comm_check(comm));
+    return knn_tc_check(db);
+}
+
 int pe_match_patches(pe_net* net, pe_db* db, pe_comm* comm, const float* patches_hwc, int64_t n, int patch_channels,
                      int k, int32_t* out_idx, float* out_dist, float* out_desc) {
     PE_REQUIRE(net && db, "null net / db");
@@ -427,65 +501,93 @@ int pe_match_patches(pe_net* net, pe_db* db, pe_comm* comm, const float* patches
     PE_CHECK(net_ensure_device(net));
     if (n == 0) return PE_OK;
     PE_REQUIRE(patches_hwc && out_idx && out_dist, "null pointer");
-    const int world = comm ? comm->world : 1, rank = comm ? comm->rank : 0;
+    int st = match_patches_once(net, db, comm, patches_hwc, n, patch_channels, k, out_idx, out_dist, out_desc);
+    /* opt-in e4m3 cross terms withdrawn by an out-of-range batch (every rank sees its own patches, so a rank may replay
+     * alone only without a communicator; with one the error is reported) */
+    if (st == PE_RETRY_FP16 && !comm) st = match_patches_once(net, db, comm, patches_hwc, n, patch_channels, k, out_idx, out_dist, out_desc);
+    return st == PE_RETRY_FP16 ? PE_ERR_INVALID : st;
+}
+
+int pe_match_patches_dev(pe_net* net, pe_db* db, pe_comm* comm, const float* d_patches_hwc, int64_t n, int patch_channels,
+                         int k, int32_t* d_out_idx, float* d_out_dist, float* d_out_desc) {
+    PE_REQUIRE(net && db, "null net / db");
+    PE_REQUIRE(!db->hamming, "pe_match_patches_dev needs an L2 DB");
+    PE_REQUIRE(n >= 0 && k >= 1 && k <= 16, "bad n / k");
+    PE_REQUIRE(patch_channels == net->def.channels, "patches have %d channels, net input has %d", patch_channels, net->def.channels);
+    PE_REQUIRE(net->def.desc_dim == db->dim, "descriptor dim %d != DB dim %d", net->def.desc_dim, db->dim);
+    PE_REQUIRE(net->device == db->device && (!comm || comm->device == db->device), "net, DB and communicator must share a device");
+    PE_CHECK(net_ensure_device(net));
+    if (n == 0) return PE_OK;
+    PE_REQUIRE(d_patches_hwc && d_out_idx && d_out_dist, "null pointer");
     const int D = net->def.desc_dim;
-    const size_t patch_floats = (size_t)4096 * patch_channels;
-    const int64_t sub = 512;
-    const int64_t stage_n = n < sub ? n : sub;
-    PE_CHECK(net->in_stage[0].reserve(stage_n * patch_floats * sizeof(float)));
-    if (n > sub) PE_CHECK(net->in_stage[1].reserve(stage_n * patch_floats * sizeof(float)));
-    PE_CHECK(net->out_stage.reserve((size_t)n * D * sizeof(float)));
-    PE_CHECK(db->m_ri.reserve((size_t)n * k * 4));
-    PE_CHECK(db->m_rd.reserve((size_t)n * k * 4));
-    if (world > 1) {
-        PE_CHECK(db->m_q.reserve((size_t)world * stage_n * D * 4));
-        PE_CHECK(db->m_ci.reserve((size_t)world * stage_n * k * 4));
-        PE_CHECK(db->m_cd.reserve((size_t)world * stage_n * k * 4));
-    }
     if (!db->ev_match) PE_CUDA(cudaEventCreateWithFlags(&db->ev_match, cudaEventDisableTiming));
+    for (int i = 0; i < 2; ++i)
+        if (!db->ev_free[i]) PE_CUDA(cudaEventCreateWithFlags(&db->ev_free[i], cudaEventDisableTiming));
+    const int b = (int)(db->match_calls++ & 1);
     const bool two_streams = db->stream != net->stream;
-    int it = 0;
-    for (int64_t first = 0; first < n; first += sub, ++it) {
-        const int64_t m = n - first < sub ? n - first : sub;
-        const int b = it & 1;
-        if (it >= 2) PE_CUDA(cudaStreamWaitEvent(net->copy_stream, net->ev_done[b], 0));
-        PE_CUDA(cudaMemcpyAsync(net->in_stage[b].p, patches_hwc + first * patch_floats, m * patch_floats * sizeof(float),
-                                cudaMemcpyHostToDevice, net->copy_stream));
-        PE_CUDA(cudaEventRecord(net->ev_in[b], net->copy_stream));
-        PE_CUDA(cudaStreamWaitEvent(net->stream, net->ev_in[b], 0));
-        float* d_desc = net->out_stage.as<float>() + (size_t)first * D;
-        PE_CHECK(net_forward_dev(net, net->in_stage[b].as<float>(), m, patch_channels, d_desc, D));
-        PE_CUDA(cudaEventRecord(net->ev_done[b], net->stream));
-        const float* d_q = d_desc;
-        if (world > 1) {
-            PE_NCCL(g_nccl.AllGather(d_desc, db->m_q.p, (size_t)m * D, ncclFloat32, comm->comm, net->stream));
-            d_q = db->m_q.as<float>();
-        }
-        if (two_streams) {
-            PE_CUDA(cudaEventRecord(db->ev_match, net->stream));
-            PE_CUDA(cudaStreamWaitEvent(db->stream, db->ev_match, 0));
-        }
-        int32_t* r_i = db->m_ri.as<int32_t>() + (size_t)first * k;
-        float* r_d = db->m_rd.as<float>() + (size_t)first * k;
-        if (world > 1) {
-            PE_CHECK(sharded_knn<float>(db, comm, d_q, world * m, k, db->m_ci.as<int32_t>(), db->m_cd.as<float>(), false));
-            PE_CUDA(cudaMemcpyAsync(r_i, db->m_ci.as<int32_t>() + (size_t)rank * m * k, (size_t)m * k * 4, cudaMemcpyDeviceToDevice, db->stream));
-            PE_CUDA(cudaMemcpyAsync(r_d, db->m_cd.as<float>() + (size_t)rank * m * k, (size_t)m * k * 4, cudaMemcpyDeviceToDevice, db->stream));
-            if (two_streams) {   /* the next stage's all-gather reuses m_q: it must not overtake this scan */
-                PE_CUDA(cudaEventRecord(db->ev_match, db->stream));
-                PE_CUDA(cudaStreamWaitEvent(net->stream, db->ev_match, 0));
-            }
-        } else {
-            PE_CHECK(knn_l2_local(db, d_q, m, k, r_i, r_d));
-        }
+    if (db->m_desc[b].cap < (size_t)n * D * 4) {
+        /* growing a buffer frees it: nothing queued may still read the old one */
+        PE_CUDA(cudaStreamSynchronize(db->stream));
+        PE_CHECK(db->m_desc[b].reserve((size_t)n * D * 4));
+    } else if (two_streams) {
+        PE_CUDA(cudaStreamWaitEvent(net->stream, db->ev_free[b], 0));   /* the call before last has finished reading buffer b */
     }
-    PE_CUDA(cudaMemcpyAsync(out_idx, db->m_ri.p, (size_t)n * k * 4, cudaMemcpyDeviceToHost, db->stream));
-    PE_CUDA(cudaMemcpyAsync(out_dist, db->m_rd.p, (size_t)n * k * 4, cudaMemcpyDeviceToHost, db->stream));
-    if (out_desc) PE_CUDA(cudaMemcpyAsync(out_desc, net->out_stage.p, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToHost, db->stream));
-    PE_CUDA(cudaStreamSynchronize(db->stream));
-    PE_CUDA(cudaStreamSynchronize(net->stream));
-    PE_CHECK(forward_tc_check(net));
-    return knn_tc_check(db);
+    float* d_desc = db->m_desc[b].as<float>();
+    PE_CHECK(net_forward_dev(net, d_patches_hwc, n, patch_channels, d_desc, D));
+    PE_CHECK(match_stage(net, db, comm, d_desc, n, k, d_out_idx, d_out_dist));
+    if (d_out_desc) PE_CUDA(cudaMemcpyAsync(d_out_desc, d_desc, (size_t)n * D * 4, cudaMemcpyDeviceToDevice, db->stream));
+    PE_CUDA(cudaEventRecord(db->ev_free[b], db->stream));
+    /* per-kernel profiling brackets kernels with events on their own stream: keep the two streams from overlapping
+     * while it is on, so that a bracket never includes time spent waiting for the other stream's CTAs to leave the SMs */
+    if (two_streams && (net->profile || db->profile)) PE_CUDA(cudaStreamWaitEvent(net->stream, db->ev_free[b], 0));
+    return PE_OK;
+}
+
+int pe_knn_hamming_sharded_dev(pe_db* db, pe_comm* comm, const uint32_t* d_qcodes, int64_t nq, int k, int32_t* d_out_idx,
+                               int32_t* d_out_dist) {
+    PE_REQUIRE(db && db->hamming, "need a Hamming DB");
+    PE_REQUIRE(nq == 0 || (d_qcodes && d_out_idx && d_out_dist), "null pointer");
+    return sharded_knn<int32_t>(db, comm, d_qcodes, nq, k, d_out_idx, d_out_dist, true);
+}
+
+/* computeHistogram's body over a query set that is split across the ranks (every rank passes its own nq_local queries
+ * with their merged global neighbours): bin counts and the error sum are all-reduced, the per-query errors all-gathered
+ * for the median, so every rank returns the histogram of the whole set (reference src/networkevaluator.cpp:269-355). */
+int pe_histogram_sharded_dev(pe_db* db, pe_comm* comm, const int32_t* d_knn_idx, const float* d_q_labels, int64_t nq_local,
+                             int k, const int* rot_inv, int n_rot, const float* bins, int n_bins, float* out) {
+    PE_REQUIRE(db && bins && out && (rot_inv || n_rot == 0), "null pointer");
+    PE_REQUIRE(nq_local >= 0 && (nq_local == 0 || (d_knn_idx && d_q_labels)), "null pointer");
+    const int world = comm ? comm->world : 1;
+    if (world == 1) return pose_histogram_dev(db, d_knn_idx, d_q_labels, nq_local, k, rot_inv, n_rot, bins, n_bins, out);
+    PE_REQUIRE(comm->device == db->device, "communicator and DB live on different devices");
+    db->last_comm = comm;
+    unsigned long long* d_counts = nullptr;
+    double* d_sum = nullptr;
+    float *d_med = nullptr, *d_err = nullptr;
+    /* err: [own nq_local | gathered world x nq_local] */
+    PE_CHECK(pose_hist_local(db, d_knn_idx, d_q_labels, nq_local, k, rot_inv, n_rot, bins, n_bins, (world + 1) * (nq_local > 0 ? nq_local : 1),
+                             &d_counts, &d_sum, &d_med, &d_err));
+    PE_NCCL(g_nccl.AllReduce(d_counts, d_counts, 16, ncclUint64, ncclSum, comm->comm, db->stream));
+    PE_NCCL(g_nccl.AllReduce(d_sum, d_sum, 1, ncclFloat64, ncclSum, comm->comm, db->stream));
+    float* d_all = d_err + (nq_local > 0 ? nq_local : 1);
+    if (nq_local > 0) PE_NCCL(g_nccl.AllGather(d_err, d_all, (size_t)nq_local, ncclFloat32, comm->comm, db->stream));
+    return pose_hist_finish(db, d_counts, d_sum, d_med, d_all, world * nq_local, world * nq_local, n_bins, out);
+}
+
+/* computeConfusionMatrix's body over a query set split across the ranks: counts all-reduced
+ * (reference src/networkevaluator.cpp:199-245) */
+int pe_confusion_sharded_dev(pe_db* db, pe_comm* comm, const int32_t* d_knn_idx, const float* d_q_labels, int64_t nq_local,
+                             int k, const int* class_to_local, int n_classes, int n_local, int nr_test_poses, float* out) {
+    PE_REQUIRE(db && class_to_local && out, "null pointer");
+    PE_REQUIRE(nq_local >= 0 && (nq_local == 0 || (d_knn_idx && d_q_labels)), "null pointer");
+    PE_REQUIRE(k >= 1 && k <= 32, "k=%d outside 1..32", k);
+    unsigned int* d_mat = nullptr;
+    PE_CHECK(pose_confusion_local(db, d_knn_idx, d_q_labels, nq_local, k, class_to_local, n_classes, n_local, &d_mat));
+    if (comm && comm->world > 1) {
+        PE_REQUIRE(comm->device == db->device, "communicator and DB live on different devices");
+        PE_NCCL(g_nccl.AllReduce(d_mat, d_mat, (size_t)n_local * n_local + 1, ncclUint32, ncclSum, comm->comm, db->stream));
+    }
+    return pose_confusion_finish(db, d_mat, n_local, nr_test_poses, out);
 }
 
 int pe_knn_hamming_sharded(pe_db* db, pe_comm* comm, const uint32_t* qcodes, int64_t nq, int k, int32_t* out_idx,
@@ -503,7 +605,8 @@ int pe_knn_hamming_sharded(pe_db* db, pe_comm* comm, const uint32_t* qcodes, int
     PE_CUDA(cudaMemcpyAsync(out_idx, db->out_i.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, db->stream));
     PE_CUDA(cudaMemcpyAsync(out_dist, db->out_d.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, db->stream));
     PE_CUDA(cudaStreamSynchronize(db->stream));
-    return PE_OK;
+    PE_CHECK(comm_check(comm));
+    return knn_tc_check(db);
 }
 
 }  // extern "C"

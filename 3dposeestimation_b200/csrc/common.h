@@ -45,6 +45,10 @@ inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_
         }                                                                                      \
     } while (0)
 
+/* internal status (never crosses the C ABI): the opt-in e4m3 cross terms (forward_fp8 = 1) met an input beyond their
+ * range, the net has switched to the all-fp16 split and the call should be replayed */
+#define PE_RETRY_FP16 100
+
 /* after a kernel launch: catches launch-configuration errors and counts the launch */
 #define PE_LAUNCHED()                                                                          \
     do {                                                                                       \
@@ -123,6 +127,8 @@ struct pe_net {
     /* tensor path (conv_tc.cu): Toeplitz fp16 hi/lo conv1 weights, output scale, pinned failure flag */
     bool c1_tc_ready = false;
     int fp8_state = 0;         /* conv1 cross terms for these weights: 0 not calibrated yet, 1 e4m3, 2 fp16 (see net_forward_dev) */
+    int fp8_calls = 0;         /* forward calls since the last qualification (forward_fp8 = 1 re-qualifies every 32nd) */
+    bool fp8_busy = false;     /* inside the qualification's own forwards */
     void* d_z1 = nullptr;
     float c1_inv_scale = 1.f;
     bool c2_tc_ready = false;
@@ -164,6 +170,12 @@ struct pe_db {
     pe::DevBuf q, q_in, cand_d, cand_i, out_i, out_d, qlab, knn_idx, scratch, scratch2, gather, boot;
     pe::DevBuf m_q, m_ci, m_cd, m_ri, m_rd;   /* pe_match_patches: gathered chunk queries, chunk and final results */
     cudaEvent_t ev_match = nullptr;           /* forward of a chunk finished (net stream -> DB stream) */
+    /* pe_match_patches_dev: two descriptor buffers so that call i + 1's forward (net stream) runs under call i's
+     * exchange + scan + merge (DB stream); ev_free[b] = the last reader of buffer b has finished */
+    pe::DevBuf m_desc[2];
+    cudaEvent_t ev_free[2] = {nullptr, nullptr};
+    int64_t match_calls = 0;
+    struct pe_comm* last_comm = nullptr;      /* communicator of the last sharded call (pe_db_sync reports its failures) */
 };
 
 namespace pe {
@@ -203,14 +215,24 @@ int knn_tc_select(pe_db* db, const float* cand_d, const int* cand_i, int n_chunk
 int knn_tc_select_hamming(pe_db* db, const float* cand_d, const int* cand_i, int n_lists, int kc, const uint32_t* d_q,
                           int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist);
 int knn_tc_check(pe_db* db);
+/* comm.cu: after a synchronisation, reports (and clears) a peer-window all-gather that timed out */
+int comm_check(struct pe_comm* comm);
 /* runtime switches (pe_set_option): tensor-core paths on/off */
-extern std::atomic<int> g_opt_knn_tensor, g_opt_forward_tensor, g_opt_forward_fp8, g_opt_p2p, g_opt_conv2_tensor;
+extern std::atomic<int> g_opt_knn_tensor, g_opt_forward_tensor, g_opt_forward_fp8, g_opt_p2p, g_opt_conv2_tensor, g_opt_knn_certify;
 /* pose.cu */
 int pose_histogram_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
                        const int* rot_inv, int n_rot, const float* bins, int n_bins, float* out_host);
 int pose_confusion_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
                        const int* class_to_local, int n_classes, int n_local, int nr_test_poses,
                        float* out_host);
+int pose_hist_local(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k, const int* rot_inv, int n_rot,
+                    const float* bins, int n_bins, int64_t err_cap, unsigned long long** d_counts_out, double** d_sum_out,
+                    float** d_med_out, float** d_err_out);
+int pose_hist_finish(pe_db* db, const unsigned long long* d_counts, const double* d_sum, float* d_med, const float* d_err,
+                     int64_t n_err, int64_t nq_total, int n_bins, float* out_host);
+int pose_confusion_local(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k, const int* class_to_local,
+                         int n_classes, int n_local, unsigned int** d_mat_out);
+int pose_confusion_finish(pe_db* db, const unsigned int* d_mat, int n_local, int nr_test_poses, float* out_host);
 int pose_bootstrap_dev(pe_db* db, const int* d_knn3, int64_t nq, int nr_query_poses, int* d_out, int* d_len);
 int pose_accuracy_dev(pe_db* db, const int* d_max_sim0, const int* d_boot, int64_t nq, int nr_query_poses,
                       float* intra_pct, float* inter_pct);

@@ -153,7 +153,10 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
         /* ======================= MMA issuer: the whole warp runs the loops (warp-uniform operands), one elected lane
          * issues.  A = Toeplitz weight window (128 rows = 8 output-row offsets x 16 filters), B = 256 consecutive
          * pixels of the image = base rows r, r + 8, r + 16, r + 24 (adjacent in the (y mod 8, y div 8) order) ===== */
-        const uint32_t idesc = instr_desc(128, 256, FMT_F16, FMT_F16);
+        const uint32_t idesc256 = instr_desc(128, 256, FMT_F16, FMT_F16);
+        /* tile 1, input rows ky' >= 8: base row 56 (columns 192..255) only feeds conv row 56 = row offset 0, whose weight
+         * rows end at ky' = 7, so these steps run on 192 columns (-5.8 % of the patch's tensor-pipe time) */
+        const uint32_t idesc192 = instr_desc(128, 192, FMT_F16, FMT_F16);
         const uint32_t s0 = smem_u32(smem);
         const uint64_t i_hi = smem_desc(s0 + kOffImgHi, 16, 128), i_lo = smem_desc(s0 + kOffImgLo, 16, 128);
         const uint64_t z_hi = smem_desc(s0 + kOffZHi, kZStride, 128), z_lo = smem_desc(s0 + kOffZLo, kZStride, 128);
@@ -178,6 +181,7 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
                     }
                     const uint32_t i_row = static_cast<uint32_t>(row_pos(32 * t + ky)) * (kRowBytes >> 4);
                     const uint32_t z_row = static_cast<uint32_t>(14 - ky) * (256 >> 4);
+                    const uint32_t idesc = (t == 1 && ky >= 8) ? idesc192 : idesc256;
                     if (!(a.dbg & 8) && elect_one()) {
 #pragma unroll
                         for (int p = 0; p < 4; ++p) {
@@ -750,6 +754,14 @@ int forward_tc_check(pe_net* net) {
     const int e = *reinterpret_cast<volatile int*>(net->tc_err);
     if (e == 0) return PE_OK;
     *net->tc_err = 0;
+    if (e == 102 && g_opt_forward_fp8.load() == 1) {
+        /* qualified e4m3 cross terms (opt-in) and a later batch beyond |x| = 28: the qualification is withdrawn for
+         * these weights; host entry points replay the batch on the fp16 split, device entry points report it */
+        net->fp8_state = 2;
+        set_error("tensor forward: an input value exceeds 28 with the e4m3 cross terms active (forward_fp8 = 1); the net now "
+                  "uses the all-fp16 split - run the batch again");
+        return PE_RETRY_FP16;
+    }
     if (e >= 100) {
         set_error("tensor forward: %s is not finite or exceeds the split range (patches are expected in [-1, 1]: "
                   "reference src/datasetmanager.cpp:327-343); use pe_set_option(\"%s\", 0) for such data",

@@ -404,13 +404,14 @@ int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c,
     if (n <= 0) return PE_OK;
     const int64_t want = n < 4096 ? n : 4096;
     if (net->chunk < want) PE_CHECK(net_reserve(net, want));
-    /* forward_fp8 = 1 (default): conv1's e4m3 cross terms cost ~3e-5 of the descriptor's row max on the 16-d nets but
-     * more where the last layers cancel (manifold.prototxt, D = 3: 1.5e-4 on some patches), so they are qualified per
-     * set of weights: the first batch of >= 64 patches is forwarded both ways (at most 256 patches) and the e4m3 variant
-     * is kept only if it stays within 3e-5 of the all-fp16 split there; out-of-range inputs (|x| > 28) also keep fp16.
-     * Until then (small first calls) the all-fp16 split is used. */
-    if (g_opt_forward_tensor.load() != 0 && g_opt_forward_fp8.load() == 1 && net->fp8_state == 0 && n >= 64 &&
-        conv1_tc_usable(net, patch_c, d_patches)) {
+    /* forward_fp8 = 1 (opt-in; the default 0 keeps all three conv1 split products in fp16): conv1's e4m3 cross terms cost
+     * ~3e-5 of the descriptor's row max on the 16-d nets but more where the last layers cancel (manifold.prototxt, D = 3:
+     * 1.5e-4 on some patches), so they are qualified per set of weights AND re-qualified as the data moves on: the first
+     * batch of >= 64 patches, and every 32nd such batch after it, is forwarded both ways (at most 256 patches) and the
+     * e4m3 variant is kept only while it stays within 3e-5 of the all-fp16 split; out-of-range inputs (|x| > 28) also
+     * select fp16.  Until the first qualification (small first calls) the all-fp16 split is used. */
+    if (g_opt_forward_tensor.load() != 0 && g_opt_forward_fp8.load() == 1 && !net->fp8_busy && n >= 64 &&
+        (net->fp8_state == 0 || (net->fp8_state == 1 && ++net->fp8_calls >= 32)) && conv1_tc_usable(net, patch_c, d_patches)) {
         const int64_t m = n < 256 ? n : 256;
         const int d = net->def.desc_dim;
         float* d_tmp = nullptr;
@@ -418,13 +419,15 @@ int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c,
         std::vector<float> h((size_t)2 * m * d);
         const bool prof = net->profile;
         net->profile = false;
+        net->fp8_busy = true;
+        net->fp8_calls = 0;
         int rc = PE_OK, decided = 2;
         net->fp8_state = 2;
         rc = net_forward_dev(net, d_patches, m, patch_c, d_tmp + (size_t)m * d, d);
         if (rc == PE_OK) { net->fp8_state = 1; rc = net_forward_dev(net, d_patches, m, patch_c, d_tmp, d); }
         if (rc == PE_OK && cudaStreamSynchronize(net->stream) != cudaSuccess) rc = PE_ERR_CUDA;
         if (rc == PE_OK && net->tc_err && *reinterpret_cast<volatile int*>(net->tc_err) == 102) {
-            *net->tc_err = 0;                 /* inputs beyond the e4m3 range: not an error in auto mode */
+            *net->tc_err = 0;                 /* inputs beyond the e4m3 range: not an error in this mode */
         } else if (rc == PE_OK && cudaMemcpy(h.data(), d_tmp, h.size() * sizeof(float), cudaMemcpyDeviceToHost) == cudaSuccess) {
             float worst = 0.f;
             for (int64_t r = 0; r < m; ++r) {
@@ -443,6 +446,7 @@ int net_forward_dev(pe_net* net, const float* d_patches, int64_t n, int patch_c,
         cudaFree(d_tmp);
         cudaGetLastError();
         net->profile = prof;
+        net->fp8_busy = false;
         net->fp8_state = decided;
         if (rc != PE_OK) return rc;
     }

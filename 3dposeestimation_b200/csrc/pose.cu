@@ -17,6 +17,8 @@
 #include <cfloat>
 #include <cmath>
 
+#include <vector>
+
 #include "common.h"
 
 namespace pe {
@@ -234,26 +236,28 @@ __global__ void accuracy_kernel(const int* __restrict__ max_sim0, const int* __r
 
 }  // namespace
 
-/* all pointers device-resident; out_host: n_bins + 2 floats */
-int pose_histogram_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
-                       const int* rot_inv, int n_rot, const float* bins, int n_bins, float* out_host) {
+/* first half of the histogram: per-query errors, bin counts and the error sum of nq queries, left on the device in
+ * db->scratch ([counts: 16 x u64][sum: f64][median: f32 (+pad)][rot_inv][bins][err: err_cap x f32]); err_cap >= nq leaves
+ * room for the errors of other ranks (sharded evaluation) */
+int pose_hist_local(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k, const int* rot_inv, int n_rot,
+                    const float* bins, int n_bins, int64_t err_cap, unsigned long long** d_counts_out, double** d_sum_out,
+                    float** d_med_out, float** d_err_out) {
     PE_REQUIRE(db->d_labels != nullptr, "DB was created without labels");
     PE_REQUIRE(n_bins >= 2 && n_bins <= kMaxBins, "n_bins=%d outside 2..%d", n_bins, kMaxBins);
     PE_REQUIRE(k >= 1 && k <= 32, "k=%d outside 1..32", k);
     PE_REQUIRE(db->poses_per_object > 0, "poses_per_object not set");
     PE_CUDA(cudaSetDevice(db->device));
-    /* scratch: [counts: 16 x u64][sum: f64][median: f32 (+pad)][rot_inv: n_rot x i32][bins: 16 x f32][err: nq x f32] */
     const size_t off_sum = kMaxBins * 8, off_med = off_sum + 8, off_rot = off_med + 8;
     const size_t off_bins = off_rot + (((size_t)n_rot * 4 + 15) & ~(size_t)15);
     const size_t off_err = off_bins + kMaxBins * 4;
-    PE_CHECK(db->scratch.reserve(off_err + (size_t)(nq > 0 ? nq : 1) * 4));
+    if (err_cap < nq) err_cap = nq;
+    PE_CHECK(db->scratch.reserve(off_err + (size_t)(err_cap > 0 ? err_cap : 1) * 4));
     char* base = db->scratch.as<char>();
     PE_CUDA(cudaMemsetAsync(base, 0, off_rot, db->stream));
     if (n_rot > 0) PE_CUDA(cudaMemcpyAsync(base + off_rot, rot_inv, (size_t)n_rot * 4, cudaMemcpyHostToDevice, db->stream));
     PE_CUDA(cudaMemcpyAsync(base + off_bins, bins, (size_t)n_bins * 4, cudaMemcpyHostToDevice, db->stream));
     unsigned long long* d_counts = reinterpret_cast<unsigned long long*>(base);
     double* d_sum = reinterpret_cast<double*>(base + off_sum);
-    float* d_med = reinterpret_cast<float*>(base + off_med);
     float* d_err = reinterpret_cast<float*>(base + off_err);
     if (nq > 0) {
         pose_err_kernel<<<(unsigned)((nq + kPoseWarps - 1) / kPoseWarps), kPoseWarps * 32, 0, db->stream>>>(
@@ -262,7 +266,18 @@ int pose_histogram_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels,
             n_bins, d_err, d_counts, d_sum);
         PE_LAUNCHED();
     }
-    median_select_kernel<<<1, 1024, 0, db->stream>>>(d_err, nq, d_med);
+    *d_counts_out = d_counts;
+    *d_sum_out = d_sum;
+    *d_med_out = reinterpret_cast<float*>(base + off_med);
+    *d_err_out = d_err;
+    return PE_OK;
+}
+
+/* second half: median over n_err per-query errors (entries < 0 = "no same-class neighbour" are skipped), then the
+ * normalisation of src/networkevaluator.cpp:342-350 over nq_total queries */
+int pose_hist_finish(pe_db* db, const unsigned long long* d_counts, const double* d_sum, float* d_med, const float* d_err,
+                     int64_t n_err, int64_t nq_total, int n_bins, float* out_host) {
+    median_select_kernel<<<1, 1024, 0, db->stream>>>(d_err, n_err, d_med);
     PE_LAUNCHED();
     unsigned long long h_counts[kMaxBins];
     double h_sum = 0.0;
@@ -274,14 +289,24 @@ int pose_histogram_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels,
     /* normalisation of src/networkevaluator.cpp:342-346 */
     const float total = (float)h_counts[0] + (float)h_counts[n_bins - 1];
     for (int b = 0; b < n_bins; ++b) out_host[b] = (float)h_counts[b] / total;
-    out_host[n_bins] = (float)(h_sum / (double)nq);
+    out_host[n_bins] = (float)(h_sum / (double)nq_total);
     out_host[n_bins + 1] = h_med;
     return PE_OK;
 }
 
-int pose_confusion_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
-                       const int* class_to_local, int n_classes, int n_local, int nr_test_poses,
-                       float* out_host) {
+/* all pointers device-resident; out_host: n_bins + 2 floats */
+int pose_histogram_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
+                       const int* rot_inv, int n_rot, const float* bins, int n_bins, float* out_host) {
+    unsigned long long* d_counts = nullptr;
+    double* d_sum = nullptr;
+    float *d_med = nullptr, *d_err = nullptr;
+    PE_CHECK(pose_hist_local(db, d_knn_idx, d_q_labels, nq, k, rot_inv, n_rot, bins, n_bins, nq, &d_counts, &d_sum, &d_med, &d_err));
+    return pose_hist_finish(db, d_counts, d_sum, d_med, d_err, nq, nq, n_bins, out_host);
+}
+
+/* confusion counts of nq queries, left on the device: db->scratch = [n_local^2 x u32][bad flag][class map] */
+int pose_confusion_local(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k, const int* class_to_local,
+                         int n_classes, int n_local, unsigned int** d_mat_out) {
     PE_REQUIRE(db->d_labels != nullptr, "DB was created without labels");
     PE_REQUIRE(n_classes > 0 && n_local > 0 && k >= 1, "bad confusion-matrix arguments");
     PE_CUDA(cudaSetDevice(db->device));
@@ -299,12 +324,27 @@ int pose_confusion_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels,
             n_classes, n_local, d_mat, d_bad);
         PE_LAUNCHED();
     }
+    *d_mat_out = d_mat;
+    return PE_OK;
+}
+
+/* counts (+ the bad flag behind them) -> row-normalised matrix (src/networkevaluator.cpp:242-244) */
+int pose_confusion_finish(pe_db* db, const unsigned int* d_mat, int n_local, int nr_test_poses, float* out_host) {
+    const size_t n_mat = (size_t)n_local * n_local;
     std::vector<unsigned int> h(n_mat + 1);
     PE_CUDA(cudaMemcpyAsync(h.data(), d_mat, (n_mat + 1) * 4, cudaMemcpyDeviceToHost, db->stream));
     PE_CUDA(cudaStreamSynchronize(db->stream));
     PE_REQUIRE(h[n_mat] == 0, "class label outside class_to_local");
-    for (size_t i = 0; i < n_mat; ++i) out_host[i] = (float)h[i] / (float)nr_test_poses; /* :242-244 */
+    for (size_t i = 0; i < n_mat; ++i) out_host[i] = (float)h[i] / (float)nr_test_poses;
     return PE_OK;
+}
+
+int pose_confusion_dev(pe_db* db, const int* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
+                       const int* class_to_local, int n_classes, int n_local, int nr_test_poses,
+                       float* out_host) {
+    unsigned int* d_mat = nullptr;
+    PE_CHECK(pose_confusion_local(db, d_knn_idx, d_q_labels, nq, k, class_to_local, n_classes, n_local, &d_mat));
+    return pose_confusion_finish(db, d_mat, n_local, nr_test_poses, out_host);
 }
 
 int pose_bootstrap_dev(pe_db* db, const int* d_knn3, int64_t nq, int nr_query_poses, int* d_out, int* d_len) {

@@ -58,16 +58,22 @@ PE_API int pe_device_count(int* n);
 /* number of kernels launched by this library in this process (bench "gpu_launches") */
 PE_API int64_t pe_launch_count(void);
 
-/* runtime switches (process-wide).  "knn_tensor" (default 1): L2 kNN scan on the tcgen05 tensor path for
- * descriptors of up to 16 dimensions and k <= 5, 0 = fp32 SIMT scan.  "forward_tensor" (default 1): conv / FC
- * layers on the tcgen05 split-fp16 path, 0 = fp32 SIMT kernels.  "forward_fp8": conv1 takes its two cross terms
- * (hi.lo + lo.hi) from one e4m3 MMA instead of two fp16 MMAs (conv1 1.45x faster; descriptor error ~1-3e-5 of the row
- * max instead of ~1e-6 on the 16-d nets, but up to 1.5e-4 where the last layers cancel, e.g. manifold.prototxt with
- * D = 3; inputs must satisfy |x| <= 28).  1 (default) = per set of weights, decided on the first batch of >= 64
- * patches: it is forwarded both ways (<= 256 patches) and e4m3 is kept only if it stays within 3e-5 of the all-fp16
- * split there (pe_net_fp8_state reports the outcome); 0 = never; 2 = always (out-of-range input: PE_ERR_INVALID).
+/* runtime switches (process-wide).  "knn_tensor" (default 1): L2 / Hamming kNN scan on the tcgen05 tensor path (descriptors of
+ * up to 128 dimensions, k <= 16, where its shared-memory plan fits), 0 = fp32 SIMT scan.  "forward_tensor" (default 1):
+ * conv / FC layers on the tcgen05 split-fp16 path (three fp16 products per term, fp32 accumulate: descriptors within
+ * ~1e-6 of the row max of the fp32 reference), 0 = fp32 SIMT kernels.
+ * "forward_fp8" (default 0 = off, OPT-IN): conv1 takes its two cross terms (hi.lo + lo.hi) from one e4m3 MMA instead of
+ * two fp16 MMAs - conv1 1.45x faster, but the descriptor error grows from ~1e-6 to 1-3e-5 of the row max on the 16-d
+ * nets and up to 1.5e-4 where the last layers cancel (manifold.prototxt, D = 3), and inputs must satisfy |x| <= 28.
+ * 1 = qualified per set of weights and re-qualified every 32nd batch: a batch of >= 64 patches is forwarded both ways
+ * (<= 256 patches) and e4m3 is kept only while it stays within 3e-5 of the all-fp16 split (pe_net_fp8_state reports the
+ * outcome; an out-of-range batch withdraws the qualification, host entry points replay it on fp16); 2 = always
+ * (out-of-range input: PE_ERR_INVALID).
  * "conv2_tensor" (default 1): 0 pairs the tensor conv1 with the fp32 SIMT conv2 (conv1 then writes fp32 pool1 instead
- * of the packed fp16 image; a test switch).  Every path is CUDA; none is a CPU fallback. */
+ * of the packed fp16 image; a test switch).  "knn_certify" (default 1): the L2 matcher proves per query that no
+ * unexamined template can beat the reported k-th neighbour (error bound of the split-precision scan) and re-scans the
+ * queries it cannot prove with the direct fp32 (q-t)^2 expression; 0 skips the proof (round-1 behaviour).
+ * Every path is CUDA; none is a CPU fallback. */
 PE_API int pe_set_option(const char* name, int value);
 /* conv1 cross terms of this net's current weights: 0 not decided yet (all-fp16 until then), 1 e4m3, 2 fp16 */
 PE_API int pe_net_fp8_state(const pe_net* net, int* state);
@@ -341,13 +347,15 @@ PE_API int pe_comm_info(const pe_comm* comm, int* rank, int* world);
  * peer-memory all-gather (one kernel: push to every peer's window, publish the epoch, wait, copy out) instead of the
  * NCCL call.  Default 0: measured on B200 (tools/p2p_check.py, 262 KB per rank) the kernel takes 15 us at 2 GPUs and
  * 21 us at 8 against 12 and 23 us for ncclAllGather - a tie, so NCCL stays the default.  PE_NO_P2P=1 skips the window
- * set-up.  Also returns PE_ERR_NCCL when an earlier peer-window all-gather timed out waiting for a rank. */
+ * set-up.  A peer-window all-gather that timed out waiting for a rank makes the sharded entry point that issued it (or the
+ * pe_db_sync that completes it) return PE_ERR_NCCL; so does this call. */
 PE_API int pe_comm_p2p(const pe_comm* comm, int* active);
 /* all-gather n floats per rank (host buffers; descriptor exchange) */
 PE_API int pe_comm_allgather_f32(pe_comm* comm, const float* send, int64_t n, float* recv);
 PE_API int pe_comm_allreduce_sum_f64(pe_comm* comm, double* buf, int64_t n);
 /* device-resident all-gather of n floats per rank, enqueued on the net's stream (descriptor
- * exchange between the forward and the sharded kNN without a host round trip) */
+ * exchange between the forward and the sharded kNN without a host round trip); always NCCL - the
+ * peer-window kernel serves the matcher's exchanges on the DB's stream only */
 PE_API int pe_comm_allgather_f32_dev(pe_comm* comm, pe_net* net, const float* d_send, int64_t n, float* d_recv);
 /* kNN against a row-sharded DB: every rank passes the same nq queries, scans
  * its shard, candidates are all-gathered over NVLink and merged identically on
@@ -366,6 +374,27 @@ PE_API int pe_match_patches(pe_net* net, pe_db* db, pe_comm* comm, const float* 
                             int patch_channels, int k, int32_t* out_idx, float* out_dist, float* out_desc);
 PE_API int pe_knn_hamming_sharded(pe_db* db, pe_comm* comm, const uint32_t* qcodes, int64_t nq,
                                   int k, int32_t* out_idx, int32_t* out_dist);
+PE_API int pe_knn_hamming_sharded_dev(pe_db* db, pe_comm* comm, const uint32_t* d_qcodes, int64_t nq,
+                                      int k, int32_t* d_out_idx, int32_t* d_out_dist);
+/* Device-resident, asynchronous twin of pe_match_patches, pipelined over two streams: the forward of the n patches is
+ * queued on the net's stream, [all-gather of the descriptors ->] scan -> select [-> all-gather of the candidates ->
+ * merge] on the DB's stream behind it (event-ordered, two internal descriptor buffers), so the NEXT call's forward runs
+ * under THIS call's collectives and matcher tail.  d_out_idx / d_out_dist: n x k neighbours of this rank's
+ * patches; d_out_desc (n x dim) may be null.  Results are complete after pe_db_sync(db); pe_net_sync(net) reports
+ * forward errors.  Outputs of consecutive calls must not alias while both are in flight.  With pe_db_share_stream the
+ * call degenerates to one stream (no overlap). */
+PE_API int pe_match_patches_dev(pe_net* net, pe_db* db, pe_comm* comm, const float* d_patches_hwc, int64_t n,
+                                int patch_channels, int k, int32_t* d_out_idx, float* d_out_dist, float* d_out_desc);
+/* computeHistogram / computeConfusionMatrix bodies (reference src/networkevaluator.cpp:269-355, 199-245) over a query
+ * set that is split across the ranks: every rank passes its own nq_local queries (same count on every rank) with their
+ * merged global neighbours; bin counts / the error sum / the confusion counts are all-reduced and the per-query errors
+ * all-gathered for the median, so every rank returns the result of the whole set.  comm == null: single rank. */
+PE_API int pe_histogram_sharded_dev(pe_db* db, pe_comm* comm, const int32_t* d_knn_idx, const float* d_q_labels,
+                                    int64_t nq_local, int k, const int* rot_inv, int n_rot, const float* bins,
+                                    int n_bins, float* out);
+PE_API int pe_confusion_sharded_dev(pe_db* db, pe_comm* comm, const int32_t* d_knn_idx, const float* d_q_labels,
+                                    int64_t nq_local, int k, const int* class_to_local, int n_classes, int n_local,
+                                    int nr_test_poses, float* out);
 
 #ifdef __cplusplus
 }

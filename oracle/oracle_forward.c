@@ -280,3 +280,163 @@ int orc_forward_stage(const orc_layer* layers, int n_layers, const float* const*
     free(a); free(b); free(pad);
     return cnt;
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * The same forward in the FORM Caffe-CPU runs it (the "reference-faithful" timing baseline of SURVEY 8d): per sample
+ * im2col + SGEMM for the convolutions (caffe/layers/base_conv_layer.cpp: conv_im2col_cpu + caffe_cpu_gemm), one
+ * batched SGEMM per InnerProduct (inner_product_layer.cpp: gemm(NoTrans, Trans)), bias added by a rank-1 update as
+ * Caffe's bias multiplier does, single-threaded like a stock Caffe-CPU build with a serial BLAS.  No BLAS library is
+ * installed here, so the SGEMM is a hand-blocked AVX2/FMA micro-kernel (4 x 16 register tile).  Same arithmetic as
+ * orc_forward up to the summation order (tests hold the two within 1e-5 of the row max).
+ * --------------------------------------------------------------------------------------------- */
+#include <immintrin.h>
+
+/* C[M][N] = A[M][K] * B[K][N] (row-major, C overwritten) */
+static void sgemm_nn(int M, int N, int K, const float* A, const float* B, float* C) {
+    for (int i0 = 0; i0 < M; i0 += 4) {
+        const int mi = M - i0 < 4 ? M - i0 : 4;
+        int j0 = 0;
+        for (; j0 + 16 <= N; j0 += 16) {
+            __m256 acc[4][2];
+            for (int i = 0; i < 4; ++i) { acc[i][0] = _mm256_setzero_ps(); acc[i][1] = _mm256_setzero_ps(); }
+            for (int k = 0; k < K; ++k) {
+                const __m256 b0 = _mm256_loadu_ps(B + (size_t)k * N + j0), b1 = _mm256_loadu_ps(B + (size_t)k * N + j0 + 8);
+                for (int i = 0; i < mi; ++i) {
+                    const __m256 a = _mm256_broadcast_ss(A + (size_t)(i0 + i) * K + k);
+                    acc[i][0] = _mm256_fmadd_ps(a, b0, acc[i][0]);
+                    acc[i][1] = _mm256_fmadd_ps(a, b1, acc[i][1]);
+                }
+            }
+            for (int i = 0; i < mi; ++i) {
+                _mm256_storeu_ps(C + (size_t)(i0 + i) * N + j0, acc[i][0]);
+                _mm256_storeu_ps(C + (size_t)(i0 + i) * N + j0 + 8, acc[i][1]);
+            }
+        }
+        for (; j0 < N; ++j0)
+            for (int i = 0; i < mi; ++i) {
+                float s = 0.f;
+                for (int k = 0; k < K; ++k) s += A[(size_t)(i0 + i) * K + k] * B[(size_t)k * N + j0];
+                C[(size_t)(i0 + i) * N + j0] = s;
+            }
+    }
+}
+
+static float hsum8(__m256 v) {
+    __m128 lo = _mm256_castps256_ps128(v), hi = _mm256_extractf128_ps(v, 1);
+    lo = _mm_add_ps(lo, hi);
+    lo = _mm_hadd_ps(lo, lo);
+    lo = _mm_hadd_ps(lo, lo);
+    return _mm_cvtss_f32(lo);
+}
+
+/* C[M][N] = A[M][K] * B[N][K]^T (InnerProduct over a batch: A = bottom, B = weights) */
+static void sgemm_nt(int M, int N, int K, const float* A, const float* B, float* C) {
+    for (int i0 = 0; i0 < M; i0 += 4)
+        for (int j0 = 0; j0 < N; j0 += 2) {
+            const int mi = M - i0 < 4 ? M - i0 : 4, nj = N - j0 < 2 ? N - j0 : 2;
+            __m256 acc[4][2];
+            for (int i = 0; i < 4; ++i) { acc[i][0] = _mm256_setzero_ps(); acc[i][1] = _mm256_setzero_ps(); }
+            int k = 0;
+            for (; k + 8 <= K; k += 8) {
+                const __m256 b0 = _mm256_loadu_ps(B + (size_t)j0 * K + k);
+                const __m256 b1 = nj > 1 ? _mm256_loadu_ps(B + (size_t)(j0 + 1) * K + k) : _mm256_setzero_ps();
+                for (int i = 0; i < mi; ++i) {
+                    const __m256 a = _mm256_loadu_ps(A + (size_t)(i0 + i) * K + k);
+                    acc[i][0] = _mm256_fmadd_ps(a, b0, acc[i][0]);
+                    acc[i][1] = _mm256_fmadd_ps(a, b1, acc[i][1]);
+                }
+            }
+            for (int i = 0; i < mi; ++i)
+                for (int j = 0; j < nj; ++j) {
+                    float s = hsum8(acc[i][j]);
+                    for (int kk = k; kk < K; ++kk) s += A[(size_t)(i0 + i) * K + kk] * B[(size_t)(j0 + j) * K + kk];
+                    C[(size_t)(i0 + i) * N + j0 + j] = s;
+                }
+        }
+}
+
+/* caffe/util/im2col.cpp im2col_cpu for stride 1, pad 0: col[(c*k + ky)*k + kx][y*OW + x] = in[c][y+ky][x+kx] */
+static void im2col(const float* in, shape3 s, int k, float* col) {
+    const int OH = s.h - k + 1, OW = s.w - k + 1;
+    for (int c = 0; c < s.c; ++c)
+        for (int ky = 0; ky < k; ++ky)
+            for (int kx = 0; kx < k; ++kx) {
+                float* dst = col + ((size_t)(c * k + ky) * k + kx) * OH * OW;
+                for (int y = 0; y < OH; ++y)
+                    memcpy(dst + (size_t)y * OW, in + ((size_t)c * s.h + y + ky) * s.w + kx, sizeof(float) * OW);
+            }
+}
+
+int orc_forward_im2col(const orc_layer* layers, int n_layers, const float* const* blobs, const int* sel, int n_sel, int h,
+                       int w, const float* patches_hwc, int64_t n, int patch_c, int batch, float* out) {
+    shape3 in = {n_sel, h, w}, fin;
+    for (int c = 0; c < n_sel; ++c)
+        if (sel[c] < 0 || sel[c] >= patch_c) return -1;
+    const size_t mx = max_activation(layers, n_layers, in, &fin);
+    if (!mx || batch < 1) return -1;
+    const int D = fin.c * fin.h * fin.w;
+    /* largest im2col buffer over the conv layers */
+    size_t col_n = 1;
+    {
+        shape3 cur = in;
+        for (int i = 0; i < n_layers; ++i) {
+            shape3 nx;
+            layer_out_shape(&layers[i], cur, &nx);
+            if (layers[i].kind == ORC_CONV) {
+                const size_t need = (size_t)cur.c * layers[i].b * layers[i].b * nx.h * nx.w;
+                if (need > col_n) col_n = need;
+            }
+            cur = nx;
+        }
+    }
+    float* a = (float*)malloc(sizeof(float) * mx * batch);
+    float* b = (float*)malloc(sizeof(float) * mx * batch);
+    float* col = (float*)malloc(sizeof(float) * col_n);
+    if (!a || !b || !col) { free(a); free(b); free(col); return -1; }
+    for (int64_t first = 0; first < n; first += batch) {
+        const int m = (int)(n - first < batch ? n - first : batch);
+        shape3 cur = in;
+        size_t cnt = (size_t)cur.c * cur.h * cur.w;
+        /* the staging copy of src/networkevaluator.cpp:33-42: HWC -> CHW (+ channel select) for the whole batch */
+        for (int s = 0; s < m; ++s) {
+            const float* patch = patches_hwc + (size_t)(first + s) * h * w * patch_c;
+            for (int c = 0; c < n_sel; ++c)
+                for (int i = 0; i < h * w; ++i) a[(size_t)s * cnt + (size_t)c * h * w + i] = patch[(size_t)i * patch_c + sel[c]];
+        }
+        float *src = a, *dst = b;
+        for (int li = 0; li < n_layers; ++li) {
+            const orc_layer* L = &layers[li];
+            shape3 nx;
+            if (layer_out_shape(L, cur, &nx)) { free(a); free(b); free(col); return -1; }
+            const size_t ncnt = (size_t)nx.c * nx.h * nx.w;
+            if (L->kind == ORC_CONV) {
+                const int K = cur.c * L->b * L->b, N = nx.h * nx.w;
+                for (int s = 0; s < m; ++s) {
+                    im2col(src + (size_t)s * cnt, cur, L->b, col);
+                    float* o = dst + (size_t)s * ncnt;
+                    sgemm_nn(L->a, N, K, blobs[L->blob0], col, o);
+                    for (int f = 0; f < L->a; ++f) {
+                        const float bf = blobs[L->blob1][f];
+                        for (int i = 0; i < N; ++i) o[(size_t)f * N + i] += bf;
+                    }
+                }
+                float* t = src; src = dst; dst = t;
+            } else if (L->kind == ORC_POOL) {
+                for (int s = 0; s < m; ++s) pool_forward(src + (size_t)s * cnt, cur, L->a, L->b, dst + (size_t)s * ncnt);
+                float* t = src; src = dst; dst = t;
+            } else if (L->kind == ORC_ACT) {
+                for (int s = 0; s < m; ++s) act_forward(src + (size_t)s * cnt, cur, L->a, L->blob0 >= 0 ? blobs[L->blob0] : 0);
+            } else if (L->kind == ORC_FC) {
+                sgemm_nt(m, L->a, (int)cnt, src, blobs[L->blob0], dst);
+                for (int s = 0; s < m; ++s)
+                    for (int o = 0; o < L->a; ++o) dst[(size_t)s * L->a + o] += blobs[L->blob1][o];
+                float* t = src; src = dst; dst = t;
+            } else { free(a); free(b); free(col); return -1; }
+            cur = nx;
+            cnt = ncnt;
+        }
+        memcpy(out + (size_t)first * D, src, sizeof(float) * (size_t)m * D);
+    }
+    free(a); free(b); free(col);
+    return D;
+}

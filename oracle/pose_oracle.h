@@ -42,6 +42,12 @@ int orc_forward(const orc_layer* layers, int n_layers, const float* const* blobs
                 const int* sel, int n_sel, int h, int w,
                 const float* patches_hwc, int64_t n, int patch_c, float* out, int threads);
 
+/* the same forward in the form Caffe-CPU executes it: per-sample im2col + SGEMM convolutions, batched SGEMM
+ * InnerProducts, `batch` samples per pass (the prototxt's input N), single-threaded - the "reference-faithful"
+ * timing baseline of SURVEY 8(d); equal to orc_forward up to the summation order */
+int orc_forward_im2col(const orc_layer* layers, int n_layers, const float* const* blobs, const int* sel, int n_sel, int h,
+                       int w, const float* patches_hwc, int64_t n, int patch_c, int batch, float* out);
+
 /* also return intermediate activations of ONE patch (debug / layer-wise parity):
  * stage index s = output of layer s; buf must hold max activation size; returns count. */
 int orc_forward_stage(const orc_layer* layers, int n_layers, const float* const* blobs,

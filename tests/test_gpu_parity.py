@@ -1,28 +1,31 @@
 """Parity of the CUDA path (through the C ABI) against the CPU oracle and the committed golden
 vectors.  Everything here needs a B200: `pytest -m gpu`.
 
-Acceptance (BASELINE.json / SURVEY 8c):
-  descriptors   |a-b| <= 1e-4 * row max-abs (fp32)
+Acceptance (BASELINE.json / SURVEY 8c; metrics in 3dposeestimation_b200/parity.py):
+  descriptors   row-scaled: |a-b| <= 1e-4 * row max-abs (fp32), every element; AND element-relative (SURVEY 8c verbatim:
+                |a-b| <= 1e-4 * max(|a|,|b|,eps_row)): >= 99 % of the elements for the default (fp16 x3) and SIMT paths -
+                two fp32 CPU forms of the oracle that differ only in summation order reach 99.5-99.8 % -
+                and >= 90 % (BASELINE.json's agreement target) for the opt-in e4m3 cross terms
   L2 kNN        indices bit-exact except where the oracle's k/k+1 distance gap is < 1e-4 relative;
                 distances within 1e-6 relative (they restate the same fp32 expression)
   Hamming       indices and distances bit-exact
   histogram     bin fractions exact for identical indices, mean / median within 1e-3 degrees
 """
+import importlib
+
 import numpy as np
 import pytest
 
 from tests import netdefs
 from tests.golden import make_golden as mg
 
+parity = importlib.import_module("3dposeestimation_b200.parity")
+rowscale_err, elementrel = parity.rowscale_err, parity.elementrel
+
 pytestmark = pytest.mark.gpu
 
 DESC_TOL = 1e-4
 BINS = np.array([-1, 0, 10, 20, 40, 180], np.float32)
-
-
-def rowscale_err(a, b):
-    scale = np.abs(b).max(axis=-1, keepdims=True) + 1e-30
-    return float((np.abs(a - b) / scale).max())
 
 
 def make_net(gpu, po, synth, name, seed):
@@ -34,15 +37,15 @@ def make_net(gpu, po, synth, name, seed):
 
 
 # ---------------------------------------------------------------------------- forward ---
-@pytest.fixture(params=[(1, 1), (1, 0), (0, 1)], ids=["tensor", "tensor_f16x3", "simt"])
+@pytest.fixture(params=[(1, 0), (1, 1), (0, 0)], ids=["tensor", "tensor_e4m3_optin", "simt"])
 def fwd_path(gpu, request):
-    """runs a test with the tcgen05 forward kernels (default: conv1 cross terms in e4m3), with all three conv1
-    split terms in fp16, and with the fp32 SIMT kernels"""
+    """runs a test with the tcgen05 forward kernels (default: all three conv1 split terms in fp16), with the opt-in
+    e4m3 cross terms (qualified per set of weights), and with the fp32 SIMT kernels"""
     gpu.set_option("forward_tensor", request.param[0])
     gpu.set_option("forward_fp8", request.param[1])
-    yield request.param[0]
+    yield request.param
     gpu.set_option("forward_tensor", 1)
-    gpu.set_option("forward_fp8", 1)
+    gpu.set_option("forward_fp8", 0)
 
 
 @pytest.mark.parametrize("vi,name", list(enumerate(netdefs.VARIANTS)))
@@ -60,6 +63,8 @@ def test_forward_matches_oracle_and_golden(gpu, po, synth, golden, vi, name, fwd
     got = net.compute_descriptors(big)
     want = oracle.forward(big)
     assert rowscale_err(got, want) < DESC_TOL
+    frac, _, _ = elementrel(got, want)
+    assert frac >= (0.90 if fwd_path[1] else 0.99), frac
     # batch composition must not matter (src/networkevaluator.cpp:26-30: partial last batch)
     again = np.concatenate([net.compute_descriptors(big[:5]), net.compute_descriptors(big[5:])])
     assert np.array_equal(got, again)
@@ -74,59 +79,82 @@ def test_forward_rejects_wrong_channel_count(gpu):
     assert e.value.code == gpu.PE_ERR_INVALID
 
 
-def test_forward_input_range_is_checked(gpu, synth):
-    """the e4m3 cross terms hold |x| <= 28, the fp16 split |x| <= 255; beyond that the call fails loudly and the
+def test_forward_input_range_is_checked(gpu, po, synth):
+    """the fp16 split holds |x| <= 255, the opt-in e4m3 cross terms |x| <= 28; beyond that the call fails loudly and the
     next wider path is named (patches of the reference are in [-1, 1], src/datasetmanager.cpp:327-343)"""
     net = gpu.Net(named="manifold_rgbdnor_16")
     net.fill(1, 1)
     x = synth.make_patches(3, 0, 2, 7, 2)
     ok = net.compute_descriptors(x)
     x[1, 5, 5, 2] = 40.0
+    assert gpu.get_option("forward_fp8") == 0       # the default never uses e4m3
+    wide = net.compute_descriptors(x)
+    assert np.isfinite(wide).all() and rowscale_err(wide[:1], ok[:1]) < DESC_TOL
     gpu.set_option("forward_fp8", 2)          # e4m3 cross terms forced
     try:
         with pytest.raises(gpu.PoseError) as e:
             net.compute_descriptors(x)
         assert e.value.code == gpu.PE_ERR_INVALID and "forward_fp8" in str(e.value)
-    finally:
+        # qualified mode: a first batch beyond the e4m3 range keeps the all-fp16 split, no error
         gpu.set_option("forward_fp8", 1)
-    # default (qualified per set of weights): a first batch beyond the e4m3 range keeps the all-fp16 split, no error
-    big = np.concatenate([synth.make_patches(3, 0, 70, 7, 2), x])
-    big[3, 9, 9, 1] = 40.0
-    assert np.isfinite(net.compute_descriptors(big)).all() and net.fp8_state() == 2
-    gpu.set_option("forward_fp8", 0)
-    try:
-        wide = net.compute_descriptors(x)
-        assert np.isfinite(wide).all() and rowscale_err(wide[:1], ok[:1]) < DESC_TOL
-        x[1, 5, 5, 2] = 300.0
-        with pytest.raises(gpu.PoseError) as e:
-            net.compute_descriptors(x)
-        assert "forward_tensor" in str(e.value)
+        big = np.concatenate([synth.make_patches(3, 0, 70, 7, 2), x])
+        big[3, 9, 9, 1] = 40.0
+        assert np.isfinite(net.compute_descriptors(big)).all() and net.fp8_state() == 2
+        # qualified on in-range data, then an out-of-range batch: the qualification is withdrawn and the host entry
+        # point replays the batch on the fp16 split instead of failing (ADVICE r1)
+        net, _, _ = make_net(gpu, po, synth, "manifold_rgbdnor_16", 3)     # weights that qualify (see the next test)
+        good = synth.make_patches(3, 0, 80, 7, 2)
+        want = net.compute_descriptors(good)
+        assert net.fp8_state() == 1
+        bad = good.copy()
+        bad[7, 1, 1, 0] = 40.0
+        got = net.compute_descriptors(bad)
+        assert net.fp8_state() == 2 and np.isfinite(got).all()
+        keep = np.arange(80) != 7
+        assert rowscale_err(got[keep], want[keep]) < DESC_TOL
     finally:
-        gpu.set_option("forward_fp8", 1)
+        gpu.set_option("forward_fp8", 0)
+    x[1, 5, 5, 2] = 300.0
+    with pytest.raises(gpu.PoseError) as e:
+        net.compute_descriptors(x)
+    assert "forward_tensor" in str(e.value)
+    x[1, 5, 5, 2] = np.nan
+    with pytest.raises(gpu.PoseError):
+        net.compute_descriptors(x)
 
 
 def test_e4m3_cross_terms_are_qualified_per_weights(gpu, po, synth):
-    """forward_fp8 = 1: the 16-d net keeps the e4m3 cross terms, manifold.prototxt (D = 3, cancelling last layers:
-    1.5e-4 with e4m3 on these patches) falls back to the all-fp16 split; either way the descriptors hold the
-    acceptance, also with the fp32 SIMT conv2 behind the tensor conv1 (fp32 pool1 output of conv1_tc)"""
-    for name, seed, state in (("manifold_rgbdnor_16", 3, 1), ("manifold", 4, 2)):
-        net, oracle, ref = make_net(gpu, po, synth, name, seed)
-        x = synth.make_patches(synth.BASE_SEED + 2, 11, 160, ref.channels, 7)
-        want = oracle.forward(x)
-        assert net.fp8_state() == 0
-        assert rowscale_err(net.compute_descriptors(x), want) < DESC_TOL
-        assert net.fp8_state() == state
-        gpu.set_option("conv2_tensor", 0)
-        try:
-            for f8 in (1, 0, 2) if state == 1 else (1, 0):
-                gpu.set_option("forward_fp8", f8)
-                assert rowscale_err(net.compute_descriptors(x), want) < DESC_TOL
-        finally:
-            gpu.set_option("conv2_tensor", 1)
-            gpu.set_option("forward_fp8", 1)
-        # new weights are qualified again
-        net.set_blobs(synth.make_blobs(ref.blob_names, ref.blob_shapes, seed + 100, mode=1))
-        assert net.fp8_state() == 0
+    """forward_fp8 = 1 (opt-in): the 16-d net keeps the e4m3 cross terms, manifold.prototxt (D = 3, cancelling last
+    layers: 1.5e-4 with e4m3 on these patches) falls back to the all-fp16 split; either way the descriptors hold the
+    acceptance, also with the fp32 SIMT conv2 behind the tensor conv1 (fp32 pool1 output of conv1_tc); the qualification
+    is repeated every 32nd batch"""
+    gpu.set_option("forward_fp8", 1)
+    try:
+        for name, seed, state in (("manifold_rgbdnor_16", 3, 1), ("manifold", 4, 2)):
+            net, oracle, ref = make_net(gpu, po, synth, name, seed)
+            x = synth.make_patches(synth.BASE_SEED + 2, 11, 160, ref.channels, 7)
+            want = oracle.forward(x)
+            assert net.fp8_state() == 0
+            assert rowscale_err(net.compute_descriptors(x), want) < DESC_TOL
+            assert net.fp8_state() == state
+            gpu.set_option("conv2_tensor", 0)
+            try:
+                for f8 in (1, 0, 2) if state == 1 else (1, 0):
+                    gpu.set_option("forward_fp8", f8)
+                    assert rowscale_err(net.compute_descriptors(x), want) < DESC_TOL
+            finally:
+                gpu.set_option("conv2_tensor", 1)
+                gpu.set_option("forward_fp8", 1)
+            if state == 1:      # 40 more batches cross the re-qualification point; results stay the same
+                first = net.compute_descriptors(x[:64])
+                for _ in range(40):
+                    assert np.array_equal(net.compute_descriptors(x[:64]), first)
+                assert net.fp8_state() == 1
+            # new weights are qualified again
+            net.set_blobs(synth.make_blobs(ref.blob_names, ref.blob_shapes, seed + 100, mode=1))
+            assert net.fp8_state() == 0
+    finally:
+        gpu.set_option("forward_fp8", 0)
 
 
 def test_forward_device_entry_and_chunking(gpu, po, synth, fwd_path):
@@ -429,6 +457,74 @@ def test_match_patches_equals_forward_then_knn(gpu, po, synth, knn_path):
     assert check_knn(idx[sub], dist[sub], oi, od, gap) < 0.10
     e_i, e_d = db.match_patches(net, None, patches[:0], 1)
     assert e_i.shape == (0, 1) and e_d.shape == (0, 1)
+
+
+def test_match_patches_dev_pipeline(gpu, po, synth, knn_path):
+    """pe_match_patches_dev: device patches, forward on the net's stream and the matcher on the DB's stream, several
+    calls queued back to back with alternating buffers (call i + 1's forward overlaps call i's scan) == forward + kNN,
+    bit for bit; also with the DB sharing the net's stream, with per-kernel profiling on (serialised), and with a batch
+    that grows between calls"""
+    net, oracle, ref = make_net(gpu, po, synth, "manifold_rgbdnor_16", 5)
+    nt = 3000
+    d_t = gpu.DeviceArray((nt, 64, 64, 7))
+    net.synth_patches_dev(synth.BASE_SEED, 0, nt, 150, d_t)
+    d_td = gpu.DeviceArray((nt, 16))
+    net.compute_descriptors_dev(d_t, nt, d_td)
+    net.sync()
+    tdesc = d_td.to_host()
+    sizes = [300, 300, 700, 700, 64, 1]
+    d_p = [gpu.DeviceArray((n, 64, 64, 7)) for n in sizes]
+    for c, n in enumerate(sizes):
+        net.synth_patches_dev(synth.BASE_SEED + 1 + c, 1000 * c, n, 75, d_p[c])
+    net.sync()
+    want = []
+    db_ref = gpu.TemplateDB(desc=tdesc)
+    for c, n in enumerate(sizes):
+        desc = net.compute_descriptors(d_p[c].to_host())
+        want.append((desc,) + db_ref.knn(desc, 3))
+    for shared, prof in ((False, False), (True, False), (False, True)):
+        db = gpu.TemplateDB(desc=tdesc)
+        if shared:
+            db.share_stream(net)
+        net.profile(prof); db.profile(prof)
+        outs = [(gpu.DeviceArray((n, 3), np.int32), gpu.DeviceArray((n, 3), np.float32), gpu.DeviceArray((n, 16))) for n in sizes]
+        for c, n in enumerate(sizes):
+            db.match_patches_dev(net, None, d_p[c], n, 3, outs[c][0], outs[c][1], outs[c][2] if c % 2 == 0 else None)
+        net.sync(); db.sync()
+        net.profile(False); db.profile(False)
+        for c in range(len(sizes)):
+            assert np.array_equal(outs[c][0].to_host(), want[c][1]) and np.array_equal(outs[c][1].to_host(), want[c][2]), (shared, prof, c)
+            if c % 2 == 0:
+                assert np.array_equal(outs[c][2].to_host(), want[c][0])
+    assert rowscale_err(want[0][0][:16], oracle.forward(d_p[0].to_host()[:16])) < DESC_TOL
+
+
+def test_sharded_entry_points_degenerate_without_a_communicator(gpu, po, synth):
+    """pe_histogram_sharded_dev / pe_confusion_sharded_dev / pe_knn_hamming_sharded_dev with comm == null are the
+    single-rank calls (the multi-rank side: tools/p2p_check.py under torchrun, tests/test_sharding_gloo.py on CPU)"""
+    n_obj, nr_t, nr_q, k = 6, 40, 15, 3
+    q, t, ql, tl = mg.eval_problem(synth.BASE_SEED, n_obj, nr_t, nr_q, 16)
+    rot_inv = np.array([0, 0, 1, 0, 2, 0], np.int32)
+    db = gpu.TemplateDB(desc=t, labels_all=tl, poses_per_object=nr_t)
+    idx, _ = db.knn(q, k)
+    d_i, d_l = gpu.DeviceArray.from_host(idx), gpu.DeviceArray.from_host(ql)
+    h = db.histogram_sharded_dev(None, d_i, d_l, len(idx), k, rot_inv, BINS)
+    np.testing.assert_array_equal(h, db.histogram(idx, ql, rot_inv, BINS))
+    ho = po.histogram(idx, ql, tl, nr_t, rot_inv, BINS)
+    np.testing.assert_array_equal(h[:6], ho[:6])
+    c2l = np.arange(n_obj, dtype=np.int32)[::-1].copy()
+    cm = db.confusion_sharded_dev(None, d_i, d_l, len(idx), k, c2l, n_obj, nr_q)
+    assert np.array_equal(cm, po.confusion(idx, ql, tl, c2l, n_obj, nr_q))
+    rng = np.random.default_rng(8)
+    codes = rng.integers(0, 2 ** 32, (5000, 4), dtype=np.uint64).astype(np.uint32)
+    qc = codes[:300] ^ np.uint32(5)
+    hdb = gpu.TemplateDB(codes=codes)
+    d_q = gpu.DeviceArray.from_host(qc)
+    d_oi, d_od = gpu.DeviceArray((300, 4), np.int32), gpu.DeviceArray((300, 4), np.int32)
+    hdb.knn_hamming_sharded_dev(None, d_q, 300, 4, d_oi, d_od)
+    hdb.sync()
+    oi, od = po.knn_hamming(qc, codes, 4)
+    assert np.array_equal(d_oi.to_host(), oi) and np.array_equal(d_od.to_host(), od)
 
 
 # --------------------------------------------------- full-size properties (1 M templates) ---

@@ -190,3 +190,33 @@ def test_emitted_prototxt_equals_reference_file(po, name):
     assert a.sel == b.sel and a.desc_dim == b.desc_dim
     assert a.describe() == b.describe()
     assert a.blob_names == b.blob_names and a.blob_shapes == b.blob_shapes
+
+
+def test_im2col_sgemm_form_equals_direct_form(po, synth):
+    """the single-thread im2col + SGEMM forward (the form Caffe-CPU runs, used as the "reference-faithful" timing
+    baseline) equals the direct-convolution oracle up to the summation order, partial last batch included"""
+    from tests import netdefs
+    import importlib
+    parity = importlib.import_module("3dposeestimation_b200.parity")
+    for vi, name in enumerate(netdefs.VARIANTS):
+        ref = po.parse_prototxt(netdefs.prototxt(name))
+        net = po.OracleNet(ref, synth.make_blobs(ref.blob_names, ref.blob_shapes, synth.BASE_SEED + vi, mode=1))
+        x = synth.make_patches(synth.BASE_SEED + 1, 7 * vi, 7, ref.channels, 3)
+        a, b = net.forward(x), net.forward_im2col(x, batch=3)
+        assert parity.rowscale_err(b, a) < 1e-5
+        # two exact fp32 evaluation orders: the element-relative reading of SURVEY 8(c) is met by most, not all, elements
+        assert parity.elementrel(b, a)[0] > 0.95
+
+
+def test_parity_metrics():
+    import importlib
+    parity = importlib.import_module("3dposeestimation_b200.parity")
+    b = np.array([[1.0, 1e-3, 0.0, -2.0]])
+    a = b + np.array([[1e-5, 1e-6, 1e-9, 1e-3]])
+    assert abs(parity.rowscale_err(a, b) - 5e-4) < 1e-9
+    frac, rows, worst = parity.elementrel(a, b)
+    # elements: 1e-5 rel ok; 1e-3 rel bad; |0 - 1e-9| vs eps_row 2e-4 -> 5e-6 ok; 5e-4 rel bad
+    assert frac == 0.5 and rows == 0.0 and abs(worst - 1e-3) < 1e-6
+    same, unexplained = parity.knn_agreement(np.array([[1], [2], [3]]), np.array([[1], [5], [6]]), np.array([[1.0], [1.0], [1.0]]),
+                                             np.array([0.5, 1e-6, 0.5]))
+    assert abs(same - 1 / 3) < 1e-12 and abs(unexplained - 1 / 3) < 1e-12

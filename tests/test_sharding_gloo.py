@@ -66,3 +66,42 @@ def test_two_gloo_ranks_match_unsharded_oracle(po, tmp_path, k):
     port = _free_port()
     mp.spawn(_worker, args=(2, port, 1501, 64, k, 16, str(tmp_path)), nprocs=2, join=True)
     assert open(tmp_path / "result.txt").read() == "1"
+
+
+def _hist_worker(rank, world, port, out_dir):
+    """the sharded-evaluation protocol of pe_histogram_sharded_dev on CPU: every rank reduces its slice of the queries,
+    bins / sums are combined, per-query errors gathered for the median == one unsharded pass"""
+    import torch.distributed as dist
+    from oracle import pyoracle as po
+    synth = importlib.import_module("3dposeestimation_b200.synth")
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    n_obj, nr_t, nr_q, k = 6, 50, 20, 3
+    tl = synth.make_labels(5, n_obj, nr_t)
+    src = (np.arange(nr_q) * 3) % nr_t
+    ql = synth.perturb_labels(tl.reshape(n_obj, nr_t, 8)[:, src].reshape(-1, 8), 6, max_deg=30.0)
+    rng = np.random.default_rng(3)
+    nq = n_obj * nr_q
+    own = (np.repeat(np.arange(n_obj), nr_q) * nr_t)[:, None] + rng.integers(0, nr_t, (nq, k))
+    idx = np.where(rng.random((nq, k)) < 0.6, own, rng.integers(0, n_obj * nr_t, (nq, k))).astype(np.int32)
+    rot = synth.rot_inv_pattern(n_obj)
+    bins = np.array([-1, 0, 10, 20, 40, 180], np.float32)
+    lo, hi = rank * nq // world, (rank + 1) * nq // world
+    h_r, e_r = po.histogram(idx[lo:hi], ql[lo:hi], tl, nr_t, rot, bins, want_err=True)
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (h_r, e_r))
+    merged = sharding.merge_histograms([g[0] for g in gathered], [g[1] for g in gathered], bins)
+    want = po.histogram(idx, ql, tl, nr_t, rot, bins)
+    ok = bool(np.array_equal(merged[:6], want[:6]) and np.allclose(merged[6:], want[6:], atol=1e-4))
+    if rank == 0:
+        with open(os.path.join(out_dir, "hist.txt"), "w") as f:
+            f.write("1" if ok else f"0 {merged} {want}")
+    dist.destroy_process_group()
+
+
+def test_two_gloo_ranks_sharded_histogram_equals_unsharded(po, tmp_path):
+    import torch.multiprocessing as mp
+    port = _free_port()
+    mp.spawn(_hist_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    assert open(tmp_path / "hist.txt").read() == "1"

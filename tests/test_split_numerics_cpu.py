@@ -1,5 +1,5 @@
 """CPU emulation of conv1's split arithmetic (csrc/conv_tc.cu): fp16 hi.hi on the tensor pipe plus ONE e4m3 MMA for both
-cross terms (forward_fp8, the default), against the all-fp16 three-term split and plain fp16.  The GPU tests hold the
+cross terms (forward_fp8 = 1 / 2, opt-in), against the all-fp16 three-term split and plain fp16.  The GPU tests hold the
 kernels to 1e-4 of the row max; this test pins the error budget of the scheme itself with the same scales and operand
 formats, so a change of the scales or formats that eats the margin fails here, without a GPU.
 

@@ -3,8 +3,9 @@
 
   python tools/run_configs.py --config 1            # manifold.prototxt (C=4, D=3), 15 x 1,300 templates, 9,000 queries, 1-NN
   python tools/run_configs.py --config 4            # manifold_rgbdnor_16_bin: forward + sign bits + Hamming k-NN vs 1,000,200 codes
-  python tools/run_configs.py --config 5            # rgbdnor_16, 1,000,200 templates, k = 5 + angular-error histogram
-  torchrun --nproc-per-node N tools/run_configs.py --config 3   # 125 x 10,000 templates row-sharded over N GPUs (also 5)
+  python tools/run_configs.py --config 5            # rgbdnor_16, 1,000,200 templates, 30,000 queries, k = 5 + angular-error histogram
+  python tools/run_configs.py --config 6            # rgbdnor_16_bin float descriptors (D = 128), L2 k-NN vs 1,000,200 rows (tensor scan)
+  torchrun --nproc-per-node N tools/run_configs.py --config 3   # 125 x 10,000 templates row-sharded over N GPUs (also 4, 5, 6)
 
 Inputs are the seeded synthetic patches of the bench (device generator), resident in HBM; times are CUDA events on
 the launching stream, max over ranks; one JSON line per configuration on rank 0.  Parity for the same configurations
@@ -26,7 +27,11 @@ CONFIGS = {
     1: dict(net="manifold", c=4, d=3, n_obj=15, poses=1300, q_poses=600, batch=9000, k=1, hamming=False, hist=True),
     3: dict(net="manifold_rgbdnor_16", c=7, d=16, n_obj=125, poses=10000, q_poses=None, batch=4096, k=1, hamming=False, hist=False),
     4: dict(net="manifold_rgbdnor_16_bin", c=7, d=128, n_obj=300, poses=3334, q_poses=None, batch=4096, k=5, hamming=True, hist=False),
-    5: dict(net="manifold_rgbdnor_16", c=7, d=16, n_obj=300, poses=3334, q_poses=None, batch=4096, k=5, hamming=False, hist=True),
+    # Q = 30,000 (300 x 100) queries in total, split over the ranks (the same query set at every N, so the
+    # histogram of an N-GPU run must equal the single-GPU one), rotInv 80 / 10 / 10 %
+    5: dict(net="manifold_rgbdnor_16", c=7, d=16, n_obj=300, poses=3334, q_poses=100, batch=30000, k=5, hamming=False, hist=True, split=True),
+    # the float bin_ip2 descriptors the reference's evaluator L2-matches (networkevaluator.cpp:195,265): D = 128
+    6: dict(net="manifold_rgbdnor_16_bin", c=7, d=128, n_obj=300, poses=3334, q_poses=None, batch=4096, k=1, hamming=False, hist=False),
 }
 
 
@@ -47,10 +52,14 @@ def main():
         torch.cuda.set_device(dev)
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{dev}"))
     capi = importlib.import_module("3dposeestimation_b200.capi")
+    synth = importlib.import_module("3dposeestimation_b200.synth")
     shard_rows = importlib.import_module("3dposeestimation_b200.sharding").shard_rows
     net = capi.Net(named=cfg["net"], device=dev)
     net.fill(SEED, 1)
     C, D, B, K = cfg["c"], cfg["d"], cfg["batch"], cfg["k"]
+    if cfg.get("split"):                                    # a fixed query set split over the ranks
+        assert B % world == 0
+        B //= world
     T = cfg["n_obj"] * cfg["poses"]
     lo, hi = shard_rows(rank, world, T)
     chunk = 4096
@@ -72,14 +81,18 @@ def main():
         d_codes = capi.DeviceArray((hi - lo, words), np.uint32, device=dev)
         net.binarize_dev(d_db, hi - lo, D, d_codes)
         net.sync()
-        db = capi.TemplateDB(codes=d_codes.to_host(), labels_all=labels, poses_per_object=cfg["poses"], row_offset=lo, t_total=T, device=dev)
+        db = capi.TemplateDB(codes=d_codes, labels_all=labels, poses_per_object=cfg["poses"], row_offset=lo, t_total=T, device=dev)
     else:
         db = capi.TemplateDB(d_desc=d_db, t_local=hi - lo, dim=D, row_offset=lo, t_total=T, labels_all=labels,
                              poses_per_object=cfg["poses"], device=dev)
     db.share_stream(net)
     qp = cfg["q_poses"] or cfg["poses"]
     net.synth_patches_dev(SEED + 1, rank * B, B, qp, d_in)                       # this rank's query patches
-    q_labels = capi.synth_labels(SEED + 1, rank * B, B, qp) if cfg["hist"] else None
+    q_labels = None
+    if cfg["hist"]:     # query poses = template poses of the same class perturbed by <= 15 degrees
+        ids = np.arange(B * world)                          # the whole query set on every rank: identical at every N
+        src = (ids // qp) * cfg["poses"] + ((ids % qp) * 7) % cfg["poses"]
+        q_labels = np.ascontiguousarray(synth.perturb_labels(labels[src], SEED + 1)[rank * B:(rank + 1) * B])
     nq_all = B * world
     d_desc = capi.DeviceArray((B, D), device=dev)
     d_all = capi.DeviceArray((nq_all, D), device=dev) if world > 1 else d_desc
@@ -95,9 +108,7 @@ def main():
     def match():
         if cfg["hamming"]:
             net.binarize_dev(d_all, nq_all, D, d_bits)
-            if world > 1:
-                raise SystemExit("config 4 is measured on one GPU (the sharded Hamming entry takes host codes)")
-            db.knn_hamming_dev(d_bits, nq_all, K, d_idx, d_dist)
+            db.knn_hamming_sharded_dev(comm, d_bits, nq_all, K, d_idx, d_dist)
         else:
             db.knn_sharded_dev(comm, d_all, nq_all, K, d_idx, d_dist)
 
@@ -129,16 +140,23 @@ def main():
            "ms_forward": ms_f, "ms_knn": ms_m, "ms_step": ms_both,
            "paths": {"forward": "tcgen05" if capi.get_option("forward_tensor") else "simt",
                      "knn": ("tcgen05 +-1 e4m3" if capi.get_option("knn_tensor") and D <= 128 and K <= 5 else "simt xor+popc") if cfg["hamming"]
-                     else ("tcgen05" if capi.get_option("knn_tensor") and D <= 16 and K <= 5 else "simt")}}
-    if cfg["hist"] and world == 1:
-        rot_inv = np.zeros(cfg["n_obj"], np.int32)
+                     else ("tcgen05" if capi.get_option("knn_tensor") and D <= 128 and K <= 16 else "simt")}}
+    if cfg["hist"]:
+        # computeHistogram's body over the whole query set: every rank reduces its own slice of the merged neighbours,
+        # bins / sum all-reduced, per-query errors all-gathered for the median (pe_histogram_sharded_dev)
+        rot_inv = synth.rot_inv_pattern(cfg["n_obj"])                    # 80 % / 10 % / 10 % as config.ini:10
         d_ql = capi.DeviceArray.from_host(q_labels, device=dev)
+        d_own = capi.DeviceArray((B, K), np.int32, device=dev)
+        capi.check(capi.lib().pe_memcpy_h2d(dev, d_own.ptr, np.ascontiguousarray(d_idx.to_host()[rank * B:(rank + 1) * B]).ctypes.data, B * K * 4))
+        net.sync()
         t = capi.Timer(dev)
-        t.start(net)
-        h = db.histogram_dev(d_idx, d_ql, nq_all, K, rot_inv, BINS)
-        t.stop(net)
+        t.start(db)
+        h = db.histogram_sharded_dev(comm, d_own, d_ql, B, K, rot_inv, BINS)
+        t.stop(db)
         out["ms_histogram"] = t.elapsed_ms()
         out["histogram"] = [float(x) for x in h]
+        out["histogram_queries"] = B * world
+        out["rot_inv"] = "0 / 1 / 2 for 80 / 10 / 10 % of the classes (synth.rot_inv_pattern)"
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
