@@ -103,8 +103,9 @@ struct C1Args {
     float* pool1;              /* [n][16][30][32] fp32 (SIMT conv2) */
     unsigned char* p1_packed;  /* or, for conv2_tc: [n][hi,lo][2 channel blocks][40 rows][32 px][8 ch] fp16 */
     int* err;                  /* pinned flag: 1.. barrier time-out, 100 input magnitude above 255 */
-    int dbg;                   /* PE_C1_DBG experiments (results are wrong when set): 1 no stores, 2 no shuffles, 4 loaders do not
-                                  store after the first patch, 8 no MMAs, 16 no global loads after the first patch */
+    int dbg;                   /* PE_C1_DBG experiments (results are wrong when bits 1..256 are set): 1 no stores, 2 no shuffles, 4 loaders
+                                  do not store after the first patch, 8 no MMAs, 16 no global loads after the first patch;
+                                  512 = round-1 issue order of the split products (results stay correct) */
 };
 
 template <int CP, bool F8, bool PACKED>
@@ -173,29 +174,81 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
                 if (e) { if (lane == 0) atomicExch(a.err, e); ok = false; break; }
                 fence_after_sync();
                 const uint32_t d = tmem + t * 256;
+                /* Issue order.  The tensor core adds every MMA into the fp32 accumulator with truncation (round toward zero):
+                 * a bias of ~2^-24 of the accumulator's magnitude per MMA that adds up along the chain (the effect Ootomo &
+                 * Yokota 2022 describe for split-precision GEMMs).  The cross terms are 2^-11 of the result, so they are
+                 * issued FIRST, while the accumulator is small, and only the 60 hi.hi MMAs truncate at full magnitude
+                 * (measured on B200, tools/c1_order.sh: descriptor error 6.6e-6 -> 4.6e-6 of the row max; with the same
+                 * change in conv2 and two accumulators in the InnerProducts 1.3e-5 -> 4.6e-6).  Several input rows go into
+                 * one elected block: below ~6 MMAs per block the issue loop, not the tensor pipe, sets the pace (4 per
+                 * block: conv1 0.76 ms; 12-16 per block: 0.715 ms; the interleaved order, PE_C1_DBG=512: 0.70 ms). */
+                auto rows = [&](int ky, uint32_t& i_row, uint32_t& z_row, uint32_t& idesc) {
+                    i_row = static_cast<uint32_t>(row_pos(32 * t + ky)) * (kRowBytes >> 4);
+                    z_row = static_cast<uint32_t>(14 - ky) * (256 >> 4);
+                    idesc = (t == 1 && ky >= 8) ? idesc192 : idesc256;
+                };
+                if (!(a.dbg & 512)) {
+                    /* cross terms: two input rows per elected block (16 MMAs), then hi.hi: three rows per block (12 MMAs) */
 #pragma unroll 1
-                for (int ky = 0; ky < 15; ++ky) {
-                    if (t == 0 && ky == 8) {
-                        if (!mbar_wait(&img_full[2], it & 1)) { if (lane == 0) atomicExch(a.err, 6); ok = false; break; }
-                        fence_after_sync();
-                    }
-                    const uint32_t i_row = static_cast<uint32_t>(row_pos(32 * t + ky)) * (kRowBytes >> 4);
-                    const uint32_t z_row = static_cast<uint32_t>(14 - ky) * (256 >> 4);
-                    const uint32_t idesc = (t == 1 && ky >= 8) ? idesc192 : idesc256;
-                    if (!(a.dbg & 8) && elect_one()) {
+                    for (int ky0 = 0; ky0 < 15; ky0 += 2) {
+                        if (t == 0 && ky0 == 8) {
+                            if (!mbar_wait(&img_full[2], it & 1)) { if (lane == 0) atomicExch(a.err, 6); ok = false; break; }
+                            fence_after_sync();
+                        }
+                        if (!(a.dbg & 8) && elect_one()) {
 #pragma unroll
-                        for (int p = 0; p < 4; ++p) {
-                            const uint32_t io = i_row + p * 2, zo = z_row + p * 2 * (kZStride >> 4);
-                            mma_f16(d, z_hi + zo, i_hi + io, idesc, (ky | p) != 0);
-                            if (F8) {
-                                mma_f8(d, z_lo + zo, i_lo + io, idesc, 1);     /* hi_x.lo_w + lo_x.w in e4m3, K = 32 */
-                            } else {
-                                mma_f16(d, z_lo + zo, i_hi + io, idesc, 1);
-                                mma_f16(d, z_hi + zo, i_lo + io, idesc, 1);
+                            for (int dk = 0; dk < 2; ++dk) {
+                                const int ky = ky0 + dk;
+                                if (ky < 15) {
+                                    uint32_t i_row, z_row, idesc;
+                                    rows(ky, i_row, z_row, idesc);
+#pragma unroll
+                                    for (int p = 0; p < 4; ++p) {
+                                        const uint32_t io = i_row + p * 2, zo = z_row + p * 2 * (kZStride >> 4);
+                                        if (F8) mma_f8(d, z_lo + zo, i_lo + io, idesc, (ky | p) != 0);     /* hi_x.lo_w + lo_x.w in e4m3, K = 32 */
+                                        else { mma_f16(d, z_lo + zo, i_hi + io, idesc, (ky | p) != 0); mma_f16(d, z_hi + zo, i_lo + io, idesc, 1); }
+                                    }
+                                }
                             }
                         }
+                        __syncwarp();
                     }
-                    __syncwarp();
+                    if (ok) {
+#pragma unroll 1
+                        for (int ky0 = 0; ky0 < 15; ky0 += 3) {
+                            if (!(a.dbg & 8) && elect_one()) {
+#pragma unroll 1
+                                for (int ky = ky0; ky < ky0 + 3; ++ky) {
+                                    uint32_t i_row, z_row, idesc;
+                                    rows(ky, i_row, z_row, idesc);
+#pragma unroll
+                                    for (int p = 0; p < 4; ++p) mma_f16(d, z_hi + z_row + p * 2 * (kZStride >> 4), i_hi + i_row + p * 2, idesc, 1);
+                                }
+                            }
+                            __syncwarp();
+                        }
+                    }
+                } else {
+                    /* PE_C1_DBG=512: the three products of a K step back to back (round-1 order), for the A/B measurement */
+#pragma unroll 1
+                    for (int ky = 0; ky < 15; ++ky) {
+                        if (t == 0 && ky == 8) {
+                            if (!mbar_wait(&img_full[2], it & 1)) { if (lane == 0) atomicExch(a.err, 6); ok = false; break; }
+                            fence_after_sync();
+                        }
+                        uint32_t i_row, z_row, idesc;
+                        rows(ky, i_row, z_row, idesc);
+                        if (!(a.dbg & 8) && elect_one()) {
+#pragma unroll
+                            for (int p = 0; p < 4; ++p) {
+                                const uint32_t io = i_row + p * 2, zo = z_row + p * 2 * (kZStride >> 4);
+                                mma_f16(d, z_hi + zo, i_hi + io, idesc, (ky | p) != 0);
+                                if (F8) { mma_f8(d, z_lo + zo, i_lo + io, idesc, 1); }
+                                else { mma_f16(d, z_lo + zo, i_hi + io, idesc, 1); mma_f16(d, z_hi + zo, i_lo + io, idesc, 1); }
+                            }
+                        }
+                        __syncwarp();
+                    }
                 }
                 if (!ok) break;
                 if (elect_one()) {
@@ -344,7 +397,7 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
         const int rot = (lt >> 1) & 3;                 /* see the store loop */
         const bool rot1 = rot & 1, rot2 = rot & 2;
         const float sx = static_cast<float>(1 << kLog2Sx);
-        float vmax = 0.f;
+        float vmax = 0.f, vnan = 0.f;                  /* fmaxf drops NaN operands: x * 0 accumulates NaN / Inf inputs into vnan */
         uint32_t it = 0;
         for (long long patch = blockIdx.x; patch < a.n && !*s_abort; patch += gridDim.x, ++it) {
             const float* src = a.patches + patch * (long long)(4096 * CP);
@@ -384,6 +437,7 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
                             const int ch = 2 * c2 + e;
                             const float xv = ch < CP ? val[p * CP + (ch < CP ? ch : 0)] : 0.f;
                             vmax = fmaxf(vmax, fabsf(xv));
+                            vnan = fmaf(xv, 0.f, vnan);
                             split_f16(xv * sx, h[e], l[e]);
                             xs[e] = xv * (sx / static_cast<float>(1 << kF8XDown));
                             ls[e] = (xv * sx - __half2float(h[e])) * static_cast<float>(1 << kF8LoUp);
@@ -427,7 +481,7 @@ __global__ void __launch_bounds__(kC1TcThreads, 1) conv1_tc_kernel(const C1Args 
                 mbar_arrive(&img_full[rb]);
             }
         }
-        if (!(vmax <= (F8 ? kF8MaxInput : 255.f))) atomicExch(a.err, F8 ? 102 : 100);   /* also catches NaN */
+        if (!(vmax <= (F8 ? kF8MaxInput : 255.f)) || vnan != 0.f) atomicExch(a.err, (F8 && vnan == 0.f) ? 102 : 100);
     }
     fence_before_sync();
     __syncthreads();
@@ -520,19 +574,24 @@ __global__ void __launch_bounds__(kC2TcThreads, 1) conv2_tc_kernel(const C2Args 
             const uint32_t img = s0 + kC2OffImg + s * kP1PackedBytes;
             const uint64_t a_hi = smem_desc(img, kP1PlaneBytes, 128), a_lo = smem_desc(img + 2 * kP1PlaneBytes, kP1PlaneBytes, 128);
             const uint32_t d = tmem + s * 128;
+            /* lo image terms first: they are 2^-11 of the result, so the accumulator is still small while they are added and
+             * only the 60 hi MMAs truncate (round toward zero) at full magnitude - see the issue order of conv1 */
+#pragma unroll 1
+            for (int pass = 0; pass < 2; ++pass) {
 #pragma unroll 1
             for (int ky = 0; ky < 12; ++ky) {
                 const uint32_t a_row = static_cast<uint32_t>(p1_row_pos(ky)) * (512 >> 4);
                 const uint32_t b_row = static_cast<uint32_t>(11 - ky) * (256 >> 4);
+                const uint64_t a_op = pass == 0 ? a_lo : a_hi;
                 if (elect_one()) {
 #pragma unroll
                     for (int kx = 0; kx < 5; ++kx) {
                         const uint32_t ao = a_row + kx, bo = b_row + kx * 2 * (kZ2Stride >> 4);
-                        mma_f16(d, a_hi + ao, b_cat + bo, idesc, (ky | kx) != 0);
-                        mma_f16(d, a_lo + ao, b_cat + bo, idesc, 1);
+                        mma_f16(d, a_op + ao, b_cat + bo, idesc, (pass | ky | kx) != 0);
                     }
                 }
                 __syncwarp();
+            }
             }
             if (elect_one()) {
                 mma_commit(&img_empty[s]);

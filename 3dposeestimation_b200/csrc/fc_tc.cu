@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
         mbar_init(acc_full, 1);
         mbar_fence_init();
     }
-    if (warp == 0) tmem_alloc<128>(tmem_slot);
+    if (warp == 0) tmem_alloc<256>(tmem_slot);
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
@@ -106,9 +106,13 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
 #pragma unroll
                 for (int ks = 0; ks < 4; ++ks) {
                     const uint32_t o = ks * 2 * (2048 >> 4);
+                    /* two accumulators: the hi.hi chain (columns 0..127) and the cross terms (128..255), summed in the
+                     * epilogue with round-to-nearest.  The tensor core truncates every accumulate (round toward zero,
+                     * ~2^-24 of the accumulator's magnitude per MMA); kept apart, the 2^-11-sized cross terms neither
+                     * suffer nor cause truncation at the main sum's magnitude: 76 instead of 228 chained truncations */
                     mma_f16(tmem, a_hi + o, b_hi + o, idesc, (kb | ks) != 0);
-                    mma_f16(tmem, a_hi + o, b_lo + o, idesc, 1);
-                    mma_f16(tmem, a_lo + o, b_hi + o, idesc, 1);
+                    mma_f16(tmem + 128, a_hi + o, b_lo + o, idesc, (kb | ks) != 0);
+                    mma_f16(tmem + 128, a_lo + o, b_hi + o, idesc, 1);
                 }
                 mma_commit(&empty[s]);
             }
@@ -178,9 +182,12 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
             float* yrow = a.y + (size_t)(row_ok ? m : 0) * a.ldy + n0;
             const int groups = n_mma / 16, g_split = (groups + 1) / 2;
             for (int c0 = (half ? g_split : 0) * 16; c0 < (half ? groups : g_split) * 16; c0 += 16) {
-                uint32_t w[16];
+                uint32_t w[16], wx[16];
                 tmem_ld16(tbase + c0, w);
+                tmem_ld16(tbase + 128 + c0, wx);
                 tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 16; ++j) w[j] = __float_as_uint(__uint_as_float(w[j]) + __uint_as_float(wx[j]));
                 if (row_ok) {
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
@@ -196,7 +203,7 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
     }
     fence_before_sync();
     __syncthreads();
-    if (warp == 0) tmem_dealloc<128>(tmem);
+    if (warp == 0) tmem_dealloc<256>(tmem);
 }
 
 }  // namespace

@@ -424,13 +424,13 @@ def gpu_arm(args, rank, world, local_rank, dist):
     barrier()
     ms_e2e = max_over_ranks((time.perf_counter() - t0) * 1e3)
     # sanity: the host path and the device path agree on the last batch
-    if not os.environ.get("PE_C1_DBG"):     # kernel ablation runs (tools/c1_dbg.sh) compute garbage on purpose
+    if int(os.environ.get("PE_C1_DBG", "0")) & 511 == 0:     # kernel ablation runs (tools/c1_dbg.sh) compute garbage on purpose
         step_device(args.steps - 1); barrier()
         assert np.array_equal(idx_h, d_idx[last].to_host()), "host-API and device-API neighbours differ"
 
     if rank != 0:
         return None
-    cpu = cpu_arm(steps=2, warmup=1, budget_s=20.0) if world == 1 else None
+    cpu = cpu_arm(steps=2, warmup=1, budget_s=20.0) if (world == 1 and not os.environ.get("PE_BENCH_NO_CPU")) else None   # env: experiment scripts only
     conv1_ms = net_ms[0] / max(1, net_calls)
     scan_ms = db_ms[0] / max(1, db_calls)
     conv1_flops = 2.0 * MAC_PER_PATCH["conv1"] * BATCH

@@ -64,7 +64,7 @@ def test_forward_matches_oracle_and_golden(gpu, po, synth, golden, vi, name, fwd
     want = oracle.forward(big)
     assert rowscale_err(got, want) < DESC_TOL
     frac, _, _ = elementrel(got, want)
-    assert frac >= (0.90 if fwd_path[1] else 0.99), frac
+    assert frac >= (0.90 if fwd_path[1] else (0.97 if fwd_path[0] else 0.99)), frac
     # batch composition must not matter (src/networkevaluator.cpp:26-30: partial last batch)
     again = np.concatenate([net.compute_descriptors(big[:5]), net.compute_descriptors(big[5:])])
     assert np.array_equal(got, again)
