@@ -91,6 +91,7 @@ SIGNATURES = {
     "pe_db_info": (C.c_int, [vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "pe_db_sync": (C.c_int, [vp]),
     "pe_knn": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp, vp]),
+    "pe_db_knn_flagged": (C.c_int, [vp, C.POINTER(C.c_int64)]),
     "pe_knn_dev": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp, vp]),
     "pe_knn_hamming": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp, vp]),
     "pe_knn_hamming_dev": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp, vp]),
@@ -493,6 +494,12 @@ class TemplateDB:
         dist = np.empty((nq, k), np.float32)
         check(lib().pe_knn(self.h, _ptr(q), nq, k, _ptr(idx), _ptr(dist)))
         return idx, dist
+
+    def knn_flagged(self) -> int:
+        """queries of the last L2 kNN call that the certificate could not prove (re-scanned exactly)"""
+        n = C.c_int64(0)
+        check(lib().pe_db_knn_flagged(self.h, C.byref(n)))
+        return n.value
 
     def knn_dev(self, d_q, nq, k, d_idx, d_dist):
         check(lib().pe_knn_dev(self.h, d_q.ptr if isinstance(d_q, DeviceArray) else d_q, nq, k, d_idx.ptr, d_dist.ptr))

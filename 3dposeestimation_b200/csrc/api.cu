@@ -726,6 +726,9 @@ void pe_db_destroy(pe_db* db) {
     if (db->d_codes) cudaFree(db->d_codes);
     if (db->d_labels) cudaFree(db->d_labels);
     if (db->d_tc) cudaFree(db->d_tc);
+    if (db->d_center) cudaFree(db->d_center);
+    if (db->d_norm_c) cudaFree(db->d_norm_c);
+    for (DevBuf* b : {&db->key_scale, &db->flag, &db->fb_d, &db->fb_i, &db->fb_done}) b->release();
     if (db->d_tc_err) cudaFreeHost(db->d_tc_err);
     db->tau.release();
     for (DevBuf* b : {&db->q, &db->q_in, &db->cand_d, &db->cand_i, &db->out_i, &db->out_d, &db->qlab, &db->knn_idx,
@@ -753,6 +756,18 @@ int pe_db_sync(pe_db* db) {
     PE_CUDA(cudaStreamSynchronize(db->stream));
     PE_CHECK(comm_check(db->last_comm));
     return knn_tc_check(db);
+}
+
+int pe_db_knn_flagged(pe_db* db, int64_t* n) {
+    PE_REQUIRE(db && n, "null pointer");
+    *n = 0;
+    if (!db->flag.p) return PE_OK;
+    PE_CUDA(cudaSetDevice(db->device));
+    int h = 0;
+    PE_CUDA(cudaMemcpyAsync(&h, db->flag.p, sizeof(int), cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaStreamSynchronize(db->stream));
+    *n = h;
+    return PE_OK;
 }
 
 int pe_knn_dev(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist) {

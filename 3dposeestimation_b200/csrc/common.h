@@ -165,8 +165,18 @@ struct pe_db {
     void* d_tc = nullptr;
     int* d_tc_err = nullptr;
     int tc_log2_st = 0, tc_log2_sn = 0;
-    float tc_center[16] = {};         /* DB mean the tensor tiles are centred on */
+    /* L2 is translation invariant: both scans rank on descriptors centred on the DB mean, so that the cancellation in
+     * |t|^2 - 2 q.t is measured against the spread of the DB, not its distance from the origin */
+    float center[128] = {};           /* DB mean (host copy) */
+    float* d_center = nullptr;        /* [128] the same on the device */
+    float* d_norm_c = nullptr;        /* [t_local] squared norms of the centred rows (SIMT scan) */
+    float max_abs_c = 0.f, max_norm2_c = 0.f;   /* max |t-c| over elements, max |t-c|^2 over rows */
     pe::DevBuf tau;                   /* [nq] shared admission thresholds of the tensor scan */
+    pe::DevBuf key_scale;             /* [nq] 1 / (s_q s_t): tensor-scan keys -> squared-distance units */
+    /* exactness certificate of the L2 matcher: [0] number of queries the select pass could not prove, [1] calls, [4..]
+     * their ids; fb_*: per (query, DB chunk) partial top-k of the direct (q-t)^2 re-scan and its arrival counters */
+    pe::DevBuf flag, fb_d, fb_i, fb_done;
+    long long flagged_total = 0, certified_calls = 0;   /* read back lazily by pe_db_knn_stats */
     pe::DevBuf q, q_in, cand_d, cand_i, out_i, out_d, qlab, knn_idx, scratch, scratch2, gather, boot;
     pe::DevBuf m_q, m_ci, m_cd, m_ri, m_rd;   /* pe_match_patches: gathered chunk queries, chunk and final results */
     cudaEvent_t ev_match = nullptr;           /* forward of a chunk finished (net stream -> DB stream) */
@@ -211,7 +221,10 @@ void knn_tc_plan(const pe_db* db, int64_t nq, int k, int* n_chunks, int* kc, int
 int knn_tc_scan(pe_db* db, const void* d_q, int64_t nq, int k, int n_lists, int kc, int tiles_per_chunk,
                 float* cand_d, int* cand_i);
 int knn_tc_select(pe_db* db, const float* cand_d, const int* cand_i, int n_chunks, int kc, const float* d_q,
-                  int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist);
+                  int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist, int* d_flag);
+/* knn.cu: DB mean, centred norms and spread (called once per L2 DB); direct (q-t)^2 re-scan of the flagged queries */
+int knn_center_stats(pe_db* db);
+int knn_exact_fallback(pe_db* db, const int* d_flag, const float* d_q, int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist);
 int knn_tc_select_hamming(pe_db* db, const float* cand_d, const int* cand_i, int n_lists, int kc, const uint32_t* d_q,
                           int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist);
 int knn_tc_check(pe_db* db);

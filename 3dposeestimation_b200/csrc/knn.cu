@@ -21,6 +21,8 @@
  */
 #include <cfloat>
 #include <climits>
+#include <cmath>
+#include <cstring>
 
 #include "common.h"
 #include "knn_exact.cuh"
@@ -71,7 +73,7 @@ __host__ __device__ constexpr int l2_tile_rows(int dp) { return dp <= 16 ? 256 :
 template <int DP, int RQ>
 __global__ void __launch_bounds__(kScanThreads)
 knn_l2_scan_kernel(const float* __restrict__ q, int nq, const float* __restrict__ db,
-                   const float* __restrict__ norm, long long t_local, long long chunk_len,
+                   const float* __restrict__ norm, const float* __restrict__ ctr, long long t_local, long long chunk_len,
                    int n_chunks, int kc, long long row_offset, float* __restrict__ cand_d,
                    int* __restrict__ cand_i) {
     constexpr int kT = l2_tile_rows(DP);
@@ -97,7 +99,11 @@ knn_l2_scan_kernel(const float* __restrict__ q, int nq, const float* __restrict_
 #pragma unroll
         for (int d4 = 0; d4 < DP / 4; ++d4) {
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ok) v = __ldg(reinterpret_cast<const float4*>(q + (size_t)qi[j] * DP) + d4);
+            if (ok) {      /* centred on the DB mean, like the rows and their norms (L2 is translation invariant) */
+                const float4 c = __ldg(reinterpret_cast<const float4*>(ctr) + d4);
+                v = __ldg(reinterpret_cast<const float4*>(q + (size_t)qi[j] * DP) + d4);
+                v.x -= c.x; v.y -= c.y; v.z -= c.z; v.w -= c.w;
+            }
             qr[j][4 * d4 + 0] = -2.f * v.x; qr[j][4 * d4 + 1] = -2.f * v.y;
             qr[j][4 * d4 + 2] = -2.f * v.z; qr[j][4 * d4 + 3] = -2.f * v.w;
         }
@@ -126,8 +132,16 @@ knn_l2_scan_kernel(const float* __restrict__ q, int nq, const float* __restrict_
         __syncthreads();
         const long long t0 = t_begin + (long long)it * kT;
         const int valid = (int)((t_end - t0) < kT ? (t_end - t0) : kT);
-        const float* tl = tile + (it & 1) * kT * DP;
+        float* tl = tile + (it & 1) * kT * DP;
         const float* tn = tnorm + (it & 1) * kT;
+        /* centre the landed rows in place: valid x DP subtractions per tile against RQ x valid x DP FMAs per thread */
+        for (int i = tid; i < valid * (DP / 4); i += kScanThreads) {
+            float4 v = reinterpret_cast<float4*>(tl)[i];
+            const float4 c = __ldg(reinterpret_cast<const float4*>(ctr) + (i % (DP / 4)));
+            v.x -= c.x; v.y -= c.y; v.z -= c.z; v.w -= c.w;
+            reinterpret_cast<float4*>(tl)[i] = v;
+        }
+        __syncthreads();
 #pragma unroll 2
         for (int t = 0; t < valid; ++t) {
             float tv[DP];
@@ -263,7 +277,8 @@ __global__ void __launch_bounds__(32)
 knn_select_kernel(const T* __restrict__ cand_d, const int* __restrict__ cand_i, long long stride_q,
                   long long stride_l, int n_lists, int kc, const float* __restrict__ q,
                   const float* __restrict__ db, int dp, long long row_offset, int k,
-                  int* __restrict__ out_idx, T* __restrict__ out_dist) {
+                  int* __restrict__ out_idx, T* __restrict__ out_dist,
+                  const float* __restrict__ ctr = nullptr, float max_norm2 = 0.f, int* __restrict__ flag = nullptr) {
     extern __shared__ __align__(16) float smem[];
     const int n_cand = n_lists * kc;
     float* sq = smem; /* REFINE: the query row (dp floats, keeps the lists 16-byte aligned) */
@@ -271,8 +286,13 @@ knn_select_kernel(const T* __restrict__ cand_d, const int* __restrict__ cand_i, 
     int* si = reinterpret_cast<int*>(sd) + n_cand;
     const int lane = threadIdx.x;
     const long long qi = blockIdx.x;
+    float qn2 = 0.f, b_key = INFINITY;          /* certificate (REFINE && flag): |q - c|^2, smallest key a list dropped */
     if (REFINE) {
-        for (int d = lane; d < dp; d += 32) sq[d] = q[(size_t)qi * dp + d];
+        for (int d = lane; d < dp; d += 32) {
+            const float v = q[(size_t)qi * dp + d];
+            sq[d] = v;
+            if (flag) { const float c = v - ctr[d]; qn2 = fmaf(c, c, qn2); }
+        }
         __syncwarp();
     }
     for (int c = lane; c < n_cand; c += 32) {
@@ -281,13 +301,18 @@ knn_select_kernel(const T* __restrict__ cand_d, const int* __restrict__ cand_i, 
         const int idx = cand_i[at];
         T d = big<T>();
         if (idx >= 0) {
-            if (REFINE) d = (T)exact_l2(sq, db + (size_t)(idx - row_offset) * dp, dp);
-            else d = cand_d[at];
+            if (REFINE) {
+                d = (T)exact_l2(sq, db + (size_t)(idx - row_offset) * dp, dp);
+                /* a full list (sorted ascending) dropped only templates whose key was >= its last entry */
+                if (flag && p == kc - 1) b_key = fminf(b_key, (float)cand_d[at]);
+            } else d = cand_d[at];
         }
         sd[c] = d;
         si[c] = idx >= 0 ? idx : INT_MAX;
     }
     __syncwarp();
+    T d_kth = big<T>();
+    bool have_k = true;
     for (int r = 0; r < k; ++r) {
         T bd = big<T>();
         int bi = INT_MAX, bc = -1;
@@ -303,12 +328,34 @@ knn_select_kernel(const T* __restrict__ cand_d, const int* __restrict__ cand_i, 
             const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
             if (od < bd || (od == bd && oi < bi)) { bd = od; bi = oi; bc = oc; }
         }
+        if (bi == INT_MAX) have_k = false; else d_kth = bd;
         if (lane == 0) {
             out_idx[(size_t)qi * k + r] = bi == INT_MAX ? -1 : bi;
             out_dist[(size_t)qi * k + r] = bi == INT_MAX ? big<T>() : bd;
             if (bc >= 0) { sd[bc] = big<T>(); si[bc] = INT_MAX; }
         }
         __syncwarp();
+    }
+    if (REFINE && flag) {
+        /* Certificate of the SIMT scan (same argument as knn_tc_select_kernel): its keys are |t'|^2 - 2 q'.t' evaluated
+         * as one fp32 FMA chain of dp + 1 terms, error <= (dp + 2) 2^-23 (T^2 + 2 |q'| T); every template a chunk's list
+         * dropped has a key >= that list's last entry, so its d^2 >= |q'|^2 + min over lists - eps */
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            qn2 += __shfl_xor_sync(0xffffffffu, qn2, off);
+            b_key = fminf(b_key, __shfl_xor_sync(0xffffffffu, b_key, off));
+        }
+        bool proven = true;
+        if (b_key < INFINITY) {
+            const float qn = sqrtf(qn2), tmax = sqrtf(max_norm2);
+            const float eps = (float)(dp + 2) * 1.1920929e-7f * (max_norm2 + 2.f * qn * tmax) + 1.9073486328125e-6f * qn2;
+            const float dk = (float)d_kth;
+            proven = have_k && dk * dk * 1.000002f < qn2 + b_key - eps;
+        }
+        if (!proven && lane == 0) {
+            const int slot = atomicAdd(flag, 1);
+            flag[4 + slot] = (int)qi;
+        }
     }
 }
 
@@ -326,6 +373,147 @@ __global__ void row_norm_kernel(const float* __restrict__ x, int dp, float* __re
     float s = 0.f;
     for (int d = 0; d < dp; ++d) { const float v = x[r * dp + d]; s = fmaf(v, v, s); }
     norm[r] = s;
+}
+
+/* ------------------------------------------------- DB mean / centred statistics ---- */
+/* column sums of the padded DB in double (fp32 partials flushed every 64 rows); one launch, dp <= 128 columns:
+ * thread (row lane, column) with blockDim = (dp, 1024 / dp rows) */
+__global__ void center_sum_kernel(const float* __restrict__ desc, int dp, long long t_local, double* __restrict__ sum) {
+    const int col = threadIdx.x % dp, lane_r = threadIdx.x / dp, rows_per_block = blockDim.x / dp;
+    double tot = 0.0;
+    float acc = 0.f;
+    int n = 0;
+    for (long long r = (long long)blockIdx.x * rows_per_block + lane_r; r < t_local; r += (long long)gridDim.x * rows_per_block) {
+        acc += desc[r * dp + col];
+        if (++n == 64) { tot += acc; acc = 0.f; n = 0; }
+    }
+    tot += acc;
+    atomicAdd(sum + col, tot);
+}
+
+/* centred squared norms + out[0] = max |t-c| over elements, out[1] = max |t-c|^2 over rows (bit patterns of floats >= 0) */
+__global__ void center_stats_kernel(const float* __restrict__ desc, int dp, long long t_local, const float* __restrict__ ctr,
+                                    float* __restrict__ norm_c, unsigned* __restrict__ out) {
+    float m = 0.f, mn = 0.f;
+    for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < t_local; r += (long long)gridDim.x * blockDim.x) {
+        float n = 0.f;
+        for (int d = 0; d < dp; ++d) {
+            const float v = desc[r * dp + d] - ctr[d];
+            m = fmaxf(m, fabsf(v));
+            n = fmaf(v, v, n);
+        }
+        norm_c[r] = n;
+        mn = fmaxf(mn, n);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        mn = fmaxf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (isfinite(m)) atomicMax(out, __float_as_uint(m));
+        if (isfinite(mn)) atomicMax(out + 1, __float_as_uint(mn));
+    }
+}
+
+/* --------------------------------------------- exact re-scan of unproven queries ---- */
+/* The matcher's last resort and its ground truth: for every flagged query the reference's own expression
+ * sqrt(sum (q-t)^2) over ALL rows of the shard (no ranking shortcut), k smallest by (distance, row).
+ * grid (slots, chunks): CTA (x, y) serves flagged queries x, x + gridDim.x, ... on row chunk y; each thread keeps a sorted
+ * top-k of its rows (row order ascending: a strict '<' keeps the lower row among equals), the CTA merges them in shared
+ * memory, writes its chunk's k best, and the last chunk to arrive (counter per query) merges the chunks and writes the result. */
+constexpr int kFbThreads = 256, kFbChunks = 16, kFbMaxK = 16;
+
+__device__ void fb_block_topk(float* s_d, int* s_i, int n, int k, float* out_d, int* out_i) {
+    /* warp 0: k rounds of (distance, row) argmin over n shared-memory entries */
+    const int lane = threadIdx.x & 31;
+    if (threadIdx.x >= 32) return;
+    for (int r = 0; r < k; ++r) {
+        float bd = INFINITY;
+        int bi = INT_MAX, bc = -1;
+        for (int c = lane; c < n; c += 32) {
+            const float d = s_d[c];
+            const int i = s_i[c];
+            if (i != INT_MAX && (bc < 0 || d < bd || (d == bd && i < bi))) { bd = d; bi = i; bc = c; }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, bd, off);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+            const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
+            if (oc >= 0 && (bc < 0 || od < bd || (od == bd && oi < bi))) { bd = od; bi = oi; bc = oc; }
+        }
+        if (lane == 0) {
+            out_d[r] = bc >= 0 ? bd : INFINITY;
+            out_i[r] = bc >= 0 ? bi : INT_MAX;
+            if (bc >= 0) s_i[bc] = INT_MAX;
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(kFbThreads)
+knn_exact_fallback_kernel(const int* __restrict__ flag, const float* __restrict__ q, int dp, const float* __restrict__ db,
+                          long long t_local, long long row_offset, int k, float* __restrict__ part_d, int* __restrict__ part_i,
+                          unsigned* __restrict__ done, int* __restrict__ out_idx, float* __restrict__ out_dist) {
+    extern __shared__ __align__(16) float fb_smem[];
+    float* sq = fb_smem;                                        /* [dp] */
+    float* s_d = fb_smem + dp;                                  /* [kFbThreads * k] */
+    int* s_i = reinterpret_cast<int*>(s_d + kFbThreads * k);
+    __shared__ float r_d[kFbMaxK];
+    __shared__ int r_i[kFbMaxK];
+    __shared__ bool s_last;
+    const int count = flag[0];
+    const int chunk = blockIdx.y;
+    const long long rows_per = (t_local + kFbChunks - 1) / kFbChunks;
+    const long long r0 = chunk * rows_per, r1 = (r0 + rows_per < t_local) ? r0 + rows_per : t_local;
+    for (int f = blockIdx.x; f < count; f += gridDim.x) {
+        const int qi = flag[4 + f];
+        __syncthreads();
+        for (int d = threadIdx.x; d < dp; d += kFbThreads) sq[d] = q[(size_t)qi * dp + d];
+        __syncthreads();
+        float bd[kFbMaxK];
+        int bi[kFbMaxK];
+#pragma unroll
+        for (int p = 0; p < kFbMaxK; ++p) { bd[p] = INFINITY; bi[p] = INT_MAX; }
+        for (long long r = r0 + threadIdx.x; r < r1; r += kFbThreads) {
+            const float d = exact_l2(sq, db + (size_t)r * dp, dp);
+            if (d < bd[k - 1]) {
+                int p = k - 1;
+                while (p > 0 && d < bd[p - 1]) { bd[p] = bd[p - 1]; bi[p] = bi[p - 1]; --p; }
+                bd[p] = d;
+                bi[p] = (int)r;
+            }
+        }
+        for (int p = 0; p < k; ++p) { s_d[threadIdx.x * k + p] = bd[p]; s_i[threadIdx.x * k + p] = bi[p]; }
+        __syncthreads();
+        fb_block_topk(s_d, s_i, kFbThreads * k, k, r_d, r_i);
+        __syncthreads();
+        if (threadIdx.x < k) {
+            part_d[((size_t)f * kFbChunks + chunk) * k + threadIdx.x] = r_d[threadIdx.x];
+            part_i[((size_t)f * kFbChunks + chunk) * k + threadIdx.x] = r_i[threadIdx.x];
+        }
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) s_last = atomicAdd(done + f, 1u) == kFbChunks - 1;
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            for (int c = threadIdx.x; c < kFbChunks * k; c += kFbThreads) {
+                s_d[c] = __ldcg(part_d + (size_t)f * kFbChunks * k + c);
+                s_i[c] = __ldcg(part_i + (size_t)f * kFbChunks * k + c);
+            }
+            __syncthreads();
+            fb_block_topk(s_d, s_i, kFbChunks * k, k, r_d, r_i);
+            __syncthreads();
+            if (threadIdx.x < k) {
+                const bool ok = r_i[threadIdx.x] != INT_MAX;
+                out_idx[(size_t)qi * k + threadIdx.x] = ok ? (int)(r_i[threadIdx.x] + row_offset) : -1;
+                out_dist[(size_t)qi * k + threadIdx.x] = ok ? r_d[threadIdx.x] : INFINITY;
+            }
+            if (threadIdx.x == 0) done[f] = 0;                  /* ready for the next call */
+        }
+    }
 }
 
 int pad_dim(int dim) {
@@ -378,7 +566,7 @@ int launch_l2_scan(pe_db* db, const ScanGeom& g, const float* dq, int nq, float*
     PE_CUDA(cudaFuncSetAttribute(knn_l2_scan_kernel<DP, RQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
     dim3 grid(g.q_blocks, g.n_chunks);
     knn_l2_scan_kernel<DP, RQ><<<grid, kScanThreads, g.smem, db->stream>>>(
-        dq, nq, db->d_desc, db->d_norm, db->t_local, g.chunk_len, g.n_chunks, g.kc, db->row_offset, cd, ci);
+        dq, nq, db->d_desc, db->d_norm_c, db->d_center, db->t_local, g.chunk_len, g.n_chunks, g.kc, db->row_offset, cd, ci);
     PE_LAUNCHED();
     return PE_OK;
 }
@@ -421,6 +609,15 @@ int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* 
     float* cd = db->cand_d.as<float>();
     int* ci = db->cand_i.as<int>();
     int st = PE_ERR_UNSUPPORTED;
+    /* exactness certificate (pe_set_option("knn_certify")): the select pass lists the queries it cannot prove */
+    int* d_flag = nullptr;
+    if (g_opt_knn_certify.load() != 0 && db->t_local > 0 && db->d_center) {
+        PE_CHECK(db->flag.reserve((size_t)(nq + 4) * sizeof(int)));
+        d_flag = db->flag.as<int>();
+        PE_CUDA(cudaMemsetAsync(d_flag, 0, 4 * sizeof(int), db->stream));
+    } else if (db->flag.p) {
+        PE_CUDA(cudaMemsetAsync(db->flag.p, 0, 4 * sizeof(int), db->stream));
+    }
     PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
     if (tensor) {
         PE_CHECK(knn_tc_scan(db, dq, nq, k, g.n_chunks, g.kc, tc_tiles_per_chunk, cd, ci));
@@ -441,17 +638,75 @@ int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* 
     PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
     if (tensor) {
         /* the tensor scan emits 32-template blocks: exact pass over the best blocks */
-        PE_CHECK(knn_tc_select(db, cd, ci, g.n_chunks, g.kc, dq, nq, k, d_out_idx, d_out_dist));
+        PE_CHECK(knn_tc_select(db, cd, ci, g.n_chunks, g.kc, dq, nq, k, d_out_idx, d_out_dist, d_flag));
     } else {
         const size_t smem = (size_t)(2 * g.n_chunks * g.kc + dp) * 4;
         PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
         PE_CUDA(cudaFuncSetAttribute(knn_select_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         knn_select_kernel<float, true><<<(unsigned)nq, 32, smem, db->stream>>>(
             cd, ci, (long long)g.n_chunks * g.kc, g.kc, g.n_chunks, g.kc, dq, db->d_desc, dp, db->row_offset, k,
-            d_out_idx, d_out_dist);
+            d_out_idx, d_out_dist, db->d_center, db->max_norm2_c, db->t_local > 0 ? d_flag : nullptr);
         PE_LAUNCHED();
     }
+    if (d_flag) PE_CHECK(knn_exact_fallback(db, d_flag, dq, nq, k, d_out_idx, d_out_dist));
     PE_CHECK(prof_mark(db->profile, &db->prof_events, db->stream));
+    return PE_OK;
+}
+
+/* re-scan of the queries listed in d_flag with the direct expression; a no-op (one early-exit launch) when none is */
+int knn_exact_fallback(pe_db* db, const int* d_flag, const float* d_q, int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist) {
+    const int slots = (int)(nq < 4 * (int64_t)db->num_sms / kFbChunks + 1 ? nq : 4 * (int64_t)db->num_sms / kFbChunks + 1);
+    const size_t part = (size_t)nq * kFbChunks * k;
+    PE_CHECK(db->fb_d.reserve(part * sizeof(float)));
+    PE_CHECK(db->fb_i.reserve(part * sizeof(int)));
+    if (db->fb_done.cap < (size_t)nq * sizeof(unsigned)) PE_CHECK(db->fb_done.reserve((size_t)nq * sizeof(unsigned), true));
+    const size_t smem = (size_t)(db->dim_pad + 2 * kFbThreads * k) * 4;
+    PE_CUDA(cudaFuncSetAttribute(knn_exact_fallback_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)(slots > 0 ? slots : 1), kFbChunks);
+    knn_exact_fallback_kernel<<<grid, kFbThreads, smem, db->stream>>>(d_flag, d_q, db->dim_pad, db->d_desc, db->t_local, db->row_offset, k,
+                                                                      db->fb_d.as<float>(), db->fb_i.as<int>(), db->fb_done.as<unsigned>(),
+                                                                      d_out_idx, d_out_dist);
+    PE_LAUNCHED();
+    /* statistics: flagged queries accumulate in flag[1..2] on the device (read by pe_db_knn_stats) */
+    return PE_OK;
+}
+
+/* DB mean, centred norms and spread of an L2 DB (after db->d_desc is in place) */
+int knn_center_stats(pe_db* db) {
+    const int dp = db->dim_pad;
+    PE_CUDA(cudaSetDevice(db->device));
+    if (!db->d_center) PE_CUDA(cudaMalloc(&db->d_center, 128 * sizeof(float)));
+    if (!db->d_norm_c) PE_CUDA(cudaMalloc(&db->d_norm_c, (size_t)(db->t_local > 0 ? db->t_local : 1) * sizeof(float)));
+    for (int d = 0; d < 128; ++d) db->center[d] = 0.f;
+    db->max_abs_c = db->max_norm2_c = 0.f;
+    if (db->t_local > 0) {
+        void* d_tmp = nullptr;
+        PE_CUDA(cudaMalloc(&d_tmp, 128 * sizeof(double) + 2 * sizeof(unsigned)));
+        double* d_sum = reinterpret_cast<double*>(d_tmp);
+        unsigned* d_max = reinterpret_cast<unsigned*>(d_sum + 128);
+        PE_CUDA(cudaMemsetAsync(d_tmp, 0, 128 * sizeof(double) + 2 * sizeof(unsigned), db->stream));
+        center_sum_kernel<<<2 * db->num_sms, 1024, 0, db->stream>>>(db->d_desc, dp, db->t_local, d_sum);
+        PE_LAUNCHED();
+        double h_sum[128];
+        PE_CUDA(cudaMemcpyAsync(h_sum, d_sum, sizeof(h_sum), cudaMemcpyDeviceToHost, db->stream));
+        PE_CUDA(cudaStreamSynchronize(db->stream));
+        for (int d = 0; d < dp; ++d) {
+            const double m = h_sum[d] / (double)db->t_local;
+            db->center[d] = std::isfinite(m) ? (float)m : 0.f;
+        }
+        PE_CUDA(cudaMemcpyAsync(db->d_center, db->center, sizeof(db->center), cudaMemcpyHostToDevice, db->stream));
+        center_stats_kernel<<<2 * db->num_sms, 256, 0, db->stream>>>(db->d_desc, dp, db->t_local, db->d_center, db->d_norm_c, d_max);
+        PE_LAUNCHED();
+        unsigned h[2];
+        PE_CUDA(cudaMemcpyAsync(h, d_max, sizeof(h), cudaMemcpyDeviceToHost, db->stream));
+        PE_CUDA(cudaStreamSynchronize(db->stream));
+        cudaFree(d_tmp);
+        memcpy(&db->max_abs_c, &h[0], 4);
+        memcpy(&db->max_norm2_c, &h[1], 4);
+    } else {
+        PE_CUDA(cudaMemcpyAsync(db->d_center, db->center, sizeof(db->center), cudaMemcpyHostToDevice, db->stream));
+        PE_CUDA(cudaStreamSynchronize(db->stream));
+    }
     return PE_OK;
 }
 
@@ -552,6 +807,7 @@ int db_set_descriptors(pe_db* db, const float* src, bool src_on_device) {
     PE_LAUNCHED();
     PE_CUDA(cudaStreamSynchronize(db->stream));
     if (tmp) cudaFree(tmp);
+    PE_CHECK(knn_center_stats(db));
     return knn_tc_prepare(db);
 }
 

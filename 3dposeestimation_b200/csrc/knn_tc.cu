@@ -1,7 +1,9 @@
 /*
  * knn_tc.cu - tcgen05 (5th-gen tensor core) scan of the brute-force L2 matcher for descriptors of
- * up to 16 dimensions: the hot loop of `matcher->knnMatch(DBtest, matches, knn)`
- * (reference src/networkevaluator.cpp:197,267; src/networksolver.cpp:472).
+ * up to 128 dimensions and k <= 16: the hot loop of `matcher->knnMatch(DBtest, matches, knn)`
+ * (reference src/networkevaluator.cpp:197,267; src/networksolver.cpp:472) - the 16-d nets, the 64-d
+ * manifold_wang (network/manifold_wang.prototxt:104) and the 128 float outputs of bin_ip2
+ * (network/manifold_rgbdnor_16_bin.prototxt:142-154) alike.
  *
  * The scan ranks templates by  R(q,t) = |t|^2 - 2 q.t  (same order as sqrt(sum (q-t)^2) for a fixed q)
  * and emits, per (query, DB chunk), the k+2 best 32-template blocks (keyed by their smallest R);
@@ -12,7 +14,14 @@
  * power-of-two scaling that keeps them in fp16's normal range; R is accumulated in fp32 in TMEM by
  *     D  = A_hi.B_hi + A_hi.B_lo + A_lo.B_hi + A_n.B_n          (4 x tcgen05.mma, M=128 N=128 K=16)
  * with A = -2 s_q q (queries), B = s_t t (templates) and the last product adding s_q s_t |t|^2 from a
- * three-term fp16 split of the squared norm.
+ * three-term fp16 split of the squared norm.  Descriptors wider than 16 dimensions run dim/16 K chunks
+ * (3 MMAs each) into the same accumulator; a template tile then travels through the shared-memory ring
+ * as dim/16 stages of 8 KB (hi | lo of one chunk; the first also carries the 2 KB norm term).
+ *
+ * Certificate: knn_tc_select_kernel proves per query that no template outside the re-ranked blocks can
+ * beat the reported k-th neighbour (rigorous error bound of the split arithmetic, see the kernel) and
+ * flags the queries it cannot prove; those are re-scanned with the direct fp32 (q-t)^2 expression
+ * (knn.cu knn_exact_fallback), so the result never depends on the precision of the ranking pass.
  *
  * Kernel (persistent, one CTA per SM, 608 threads):
  *   warp 0      one lane streams 10 KB template tiles (128 rows: hi | lo | norm) with cp.async.bulk into an
@@ -43,25 +52,45 @@ using namespace umma;
 namespace {
 
 constexpr int kTcRows = 128;                 /* templates per tile / queries per query tile */
-constexpr int kTcTileBytes = 10240;          /* hi 4096 | lo 4096 | norm 2048 */
+constexpr int kTcChunkBytes = 8192;          /* one 16-dim K chunk of a tile: hi 4096 | lo 4096 */
+constexpr int kTcStageBytes = 10240;         /* ring stage: a chunk + the 2048-byte norm term (first chunk of a tile only) */
 constexpr int kTcBlock = 32;                 /* templates per candidate block */
-constexpr int kTcSelBlocks = 8;              /* candidate blocks re-ranked exactly per query */
-constexpr int kTcStages = 8;
+constexpr int kTcMaxSel = 19;                /* candidate blocks re-ranked exactly per query: k + 3, k <= 16 */
+constexpr int kTcMaxStages = 8;
 constexpr int kTcThreads = 608;               /* producer warp, 2 MMA warps, 2 x 2 x 4 epilogue warps */
 constexpr int kTcListCols = 512;              /* one list column per epilogue thread */
-constexpr int kAOpBytes = 10240;             /* per query tile: hi 4096 | lo 4096 | a_n 2048 */
 constexpr int kHamBytes = 16384;             /* Hamming: per tile up to 4 K-steps of [2 chunks][128 rows][16 x e4m3] */
-/* shared-memory layout; MODE 0 = L2 (split fp16), MODE 1 = Hamming (+-1 as e4m3) */
-template <int MODE> struct TcLayout {
-    static constexpr int a_bytes = MODE ? kHamBytes : kAOpBytes;            /* one query tile */
-    static constexpr int stage_bytes = MODE ? kHamBytes : kTcTileBytes;     /* one template tile */
-    static constexpr int off_a = 0;                                          /* 2 query tiles */
-    static constexpr int off_zero = 2 * a_bytes;                             /* L2: 2048 zero bytes, second K chunk of A_n */
-    static constexpr int off_b = off_zero + (MODE ? 0 : 2048);
-    static constexpr int off_list = off_b + kTcStages * stage_bytes;         /* [7][512] floats + [7][512] ints */
-    static constexpr int off_bar = off_list + 2 * 7 * kTcListCols * 4;
-    static constexpr int total = off_bar + 512;
+constexpr int kTcSmemMax = 232448;           /* 227 KB of dynamic shared memory per CTA on sm_100 */
+
+/* shared-memory plan of one launch (bytes); MODE 0 = L2 (split fp16), MODE 1 = Hamming (+-1 as e4m3) */
+struct TcPlan {
+    int nch;           /* L2: K chunks of 16 dims per tile (dim_pad / 16, at least 1); Hamming: 1 */
+    int stages;        /* ring stages (one K chunk each) */
+    int stage_bytes;
+    int a_bytes;       /* one query tile: nch x (hi | lo) + the a_n term */
+    int off_zero;      /* L2: 2048 zero bytes, second K chunk of A_n */
+    int off_b, off_list, off_bar, total;
 };
+
+/* false when even two ring stages do not fit (e.g. D = 128 with k + 2 = 18 list entries still fits: 2 stages) */
+bool tc_make_plan(bool hamming, int dim_pad, int kc, TcPlan* p) {
+    p->nch = hamming ? 1 : (dim_pad > 16 ? dim_pad / 16 : 1);
+    p->a_bytes = hamming ? kHamBytes : p->nch * kTcChunkBytes + 2048;
+    p->stage_bytes = hamming ? kHamBytes : kTcStageBytes;
+    p->off_zero = 2 * p->a_bytes;
+    p->off_b = p->off_zero + (hamming ? 0 : 2048);
+    const int list_bytes = kc > 3 ? 2 * kc * kTcListCols * 4 : 0;
+    const int avail = kTcSmemMax - 512 - p->off_b - list_bytes;
+    p->stages = avail / p->stage_bytes;
+    if (p->stages > kTcMaxStages) p->stages = kTcMaxStages;
+    if (p->stages < 2) return false;
+    p->off_list = p->off_b + p->stages * p->stage_bytes;
+    p->off_bar = p->off_list + list_bytes;
+    p->total = p->off_bar + 512;
+    return true;
+}
+
+int tc_kc_for(int k) { return k <= 1 ? 3 : (k <= 5 ? 7 : 18); }
 
 /* monotone float <-> int map so that atomicMin on ints orders floats (negative values included) */
 __device__ __forceinline__ int f2ord(float f) {
@@ -75,93 +104,48 @@ __device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
 }
 
 /* ------------------------------------------------------------------ DB pack ---- */
-/* The L2 distance is translation invariant, so the scan works on descriptors centred on the DB mean c:
- * |t-c| and |q-c| are what the cancellation in |t|^2 - 2 q.t is measured against, not the distance of the
- * cluster from the origin. */
-__global__ void tc_mean_kernel(const float* __restrict__ desc, int ld, long long t_local, double* __restrict__ sum16) {
-    __shared__ double red[16][8];
-    float acc[16];
-#pragma unroll
-    for (int d = 0; d < 16; ++d) acc[d] = 0.f;
-    double tot[16];
-#pragma unroll
-    for (int d = 0; d < 16; ++d) tot[d] = 0.0;
-    int n = 0;
-    for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < t_local; r += (long long)gridDim.x * blockDim.x) {
-#pragma unroll
-        for (int d = 0; d < 16; ++d) acc[d] += d < ld ? desc[r * ld + d] : 0.f;
-        if (++n == 64) {   /* flush the fp32 partials into doubles before they lose bits */
-#pragma unroll
-            for (int d = 0; d < 16; ++d) { tot[d] += acc[d]; acc[d] = 0.f; }
-            n = 0;
-        }
-    }
-#pragma unroll
-    for (int d = 0; d < 16; ++d) {
-        double v = tot[d] + acc[d];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if ((threadIdx.x & 31) == 0) red[d][threadIdx.x >> 5] = v;
-    }
-    __syncthreads();
-    if (threadIdx.x < 16) {
-        double v = 0.0;
-        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) v += red[threadIdx.x][w];
-        atomicAdd(sum16 + threadIdx.x, v);
-    }
-}
-
-struct TcCenter { float c[16]; };
-
-/* out[0] = max |t-c| over all elements, out[1] = max |t-c|^2 over rows (as uint bit patterns of non-negative floats) */
-__global__ void tc_stats_kernel(const float* __restrict__ desc, int ld, long long t_local, const TcCenter ctr, unsigned* __restrict__ out) {
-    float m = 0.f, mn = 0.f;
-    for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < t_local; r += (long long)gridDim.x * blockDim.x) {
-        float n = 0.f;
-#pragma unroll
-        for (int d = 0; d < 16; ++d) {
-            const float v = d < ld ? desc[r * ld + d] - ctr.c[d] : 0.f;
-            m = fmaxf(m, fabsf(v));
-            n = fmaf(v, v, n);
-        }
-        mn = fmaxf(mn, n);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-        mn = fmaxf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-    }
-    if ((threadIdx.x & 31) == 0) {
-        if (isfinite(m)) atomicMax(out, __float_as_uint(m));
-        if (isfinite(mn)) atomicMax(out + 1, __float_as_uint(mn));
-    }
-}
-
-/* desc: [t][ld] fp32 (ld = 4 or 16, zero padded).  out tile j (128 rows): hi[2][128][8] lo[2][128][8] n[128][8] halves */
-__global__ void tc_pack_db_kernel(const float* __restrict__ desc, int ld, long long t_local, const TcCenter ctr,
+/* desc: [t][ld] fp32 (ld = 4, 16, 64 or 128, zero padded), ctr: the DB mean (knn.cu knn_center_stats).
+ * out tile j (128 rows): [chunk 0: hi[2][128][8] | lo[2][128][8] | n[128][8]] [chunk c >= 1: hi | lo] halves, chunk c =
+ * dims 16c .. 16c + 15 of the centred, scaled rows */
+__global__ void tc_pack_db_kernel(const float* __restrict__ desc, int ld, int nch, long long t_local, const float* __restrict__ ctr,
                                   float s_t, float s_n, uint4* __restrict__ out) {
     const long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     const long long tiles = (t_local + kTcRows - 1) / kTcRows;
     if (r >= tiles * kTcRows) return;
     const long long tile = r / kTcRows;
     const int i = (int)(r - tile * kTcRows);
-    uint4* base = out + tile * (kTcTileBytes / 16);
-    uint32_t hi[8], lo[8];
+    const size_t tile16 = (size_t)(nch * kTcChunkBytes + 2048) / 16;
+    uint4* base = out + tile * tile16;
+    float nrm = 0.f;
+    for (int c = 0; c < nch; ++c) {
+        uint32_t hi[8], lo[8];
+        if (r < t_local) {
+            float v[16];
+#pragma unroll
+            for (int d = 0; d < 16; ++d) {
+                const int dd = 16 * c + d;
+                v[d] = dd < ld ? desc[r * ld + dd] - ctr[dd] : 0.f;
+                nrm = fmaf(v[d], v[d], nrm);
+            }
+#pragma unroll
+            for (int d = 0; d < 16; d += 2) {
+                __half h0, l0, h1, l1;
+                split_f16(v[d] * s_t, h0, l0);
+                split_f16(v[d + 1] * s_t, h1, l1);
+                hi[d / 2] = pack_h2(h0, h1);
+                lo[d / 2] = pack_h2(l0, l1);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) hi[j] = lo[j] = 0u;
+        }
+        uint4* cb = base + (c == 0 ? 0 : (kTcStageBytes + (size_t)(c - 1) * kTcChunkBytes) / 16);
+        cb[0 + i] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        cb[128 + i] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+        cb[256 + i] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        cb[384 + i] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+    }
     if (r < t_local) {
-        float v[16], nrm = 0.f;
-#pragma unroll
-        for (int d = 0; d < 16; ++d) {
-            v[d] = d < ld ? desc[r * ld + d] - ctr.c[d] : 0.f;
-            nrm = fmaf(v[d], v[d], nrm);
-        }
-#pragma unroll
-        for (int d = 0; d < 16; d += 2) {
-            __half h0, l0, h1, l1;
-            split_f16(v[d] * s_t, h0, l0);
-            split_f16(v[d + 1] * s_t, h1, l1);
-            hi[d / 2] = pack_h2(h0, h1);
-            lo[d / 2] = pack_h2(l0, l1);
-        }
         const float n = nrm * s_n;
         const __half n1 = __float2half_rn(n);
         const float r1 = n - __half2float(n1);
@@ -170,15 +154,9 @@ __global__ void tc_pack_db_kernel(const float* __restrict__ desc, int ld, long l
         base[512 + i] = make_uint4(pack_h2(n1, n2), pack_h2(n3, __ushort_as_half(0)), 0u, 0u);
     } else {
         /* padding rows: zero vector, largest norm term; the epilogue also rejects them by index */
-#pragma unroll
-        for (int j = 0; j < 8; ++j) hi[j] = lo[j] = 0u;
         const __half big = __ushort_as_half(0x7BFF); /* 65504 */
         base[512 + i] = make_uint4(pack_h2(big, big), pack_h2(big, __ushort_as_half(0)), 0u, 0u);
     }
-    base[0 + i] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-    base[128 + i] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-    base[256 + i] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-    base[384 + i] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
 }
 
 /* 16 code bits -> 16 e4m3 bytes: byte i = base with its sign flipped when bit i is set (base 0xB8.. = -1: bit -> +-1;
@@ -222,7 +200,9 @@ struct TcArgs {
     int tiles_total, tiles_per_chunk, n_chunks, n_qpairs;
     int log2_st, log2_sn;      /* s_t = 2^log2_st, s_n = s_t * 2^-c = 2^log2_sn  (norm term scale) */
     int* tau;                  /* [nq] shared admission thresholds (ordered-int floats) */
-    TcCenter ctr;              /* DB mean: queries are centred the same way as the packed templates */
+    const float* ctr;          /* [128] DB mean: queries are centred the same way as the packed templates */
+    float* key_scale;          /* [nq] 1 / (s_q s_t): what a key must be multiplied with to become |t'|^2 - 2 q'.t' */
+    TcPlan plan;
     float* cand_d;
     int* cand_i;
     int* err;
@@ -233,24 +213,25 @@ struct TcArgs {
 
 /* insert into the calling thread's k+2 list (entries strided by kTcListCols threads in shared memory): the new entry
  * replaces the worst one - largest key, among equal keys the largest block id, so the earlier (lower-index) block
- * stays as a strict '>' in a sorted insert would have it.  The list is NOT kept sorted (the select kernel ranks all
+ * stays as a strict '>' in a sorted insert would have it (KC = 7 for k <= 5, 18 for k <= 16).  The list is NOT kept sorted (the select kernel ranks all
  * candidates anyway): all entries are read at once, one is written, i.e. two shared-memory round trips where the
  * shifting insert made up to a dozen dependent ones (~1,800 cycles per entry under the tensor pipe's operand traffic).
  * The four 32-template blocks of a drained tile go through ONE load / store of the list.  Returns the new k+2-th best =
  * the largest key left.  Deliberately not inlined: it runs in about one warp-tile in six and must not bloat the hot
  * loop's instruction footprint. */
+template <int KC>
 __device__ __noinline__ float tc_list_insert4(float* ld, int* li, float tau_up, float m0, float m1, float m2, float m3,
                                              int blk0, int n_blocks) {
-    float key[7];
-    int id[7];
+    float key[KC];
+    int id[KC];
 #pragma unroll
-    for (int p = 0; p < 7; ++p) {
+    for (int p = 0; p < KC; ++p) {
         key[p] = ld[p * kTcListCols];
         id[p] = li[p * kTcListCols];
     }
     float thr = key[0];
 #pragma unroll
-    for (int p = 1; p < 7; ++p) thr = fmaxf(thr, key[p]);
+    for (int p = 1; p < KC; ++p) thr = fmaxf(thr, key[p]);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         const float mj = j == 0 ? m0 : (j == 1 ? m1 : (j == 2 ? m2 : m3));
@@ -258,7 +239,7 @@ __device__ __noinline__ float tc_list_insert4(float* ld, int* li, float tau_up, 
             float wk = key[0];
             int wi = id[0], wp = 0;
 #pragma unroll
-            for (int p = 1; p < 7; ++p) {
+            for (int p = 1; p < KC; ++p) {
                 const bool worse = key[p] > wk || (key[p] == wk && id[p] > wi);
                 wk = worse ? key[p] : wk;
                 wi = worse ? id[p] : wi;
@@ -266,7 +247,7 @@ __device__ __noinline__ float tc_list_insert4(float* ld, int* li, float tau_up, 
             }
             thr = mj;
 #pragma unroll
-            for (int p = 0; p < 7; ++p) {
+            for (int p = 0; p < KC; ++p) {
                 key[p] = p == wp ? mj : key[p];
                 id[p] = p == wp ? blk0 + j : id[p];
                 thr = fmaxf(thr, key[p]);
@@ -274,7 +255,7 @@ __device__ __noinline__ float tc_list_insert4(float* ld, int* li, float tau_up, 
         }
     }
 #pragma unroll
-    for (int p = 0; p < 7; ++p) {
+    for (int p = 0; p < KC; ++p) {
         ld[p * kTcListCols] = key[p];
         li[p * kTcListCols] = id[p];
     }
@@ -293,31 +274,38 @@ __device__ __forceinline__ float tc_min32(const uint32_t (&v)[32]) {
     return fminf(fmin3(u0, u1, u2), u3);
 }
 
-template <int KC, bool DBG, int MODE>
+/* FAST: one K chunk per tile and a full ring of 8 stages (descriptors of up to 16 dimensions, all Hamming widths with
+ * k <= 5): chunk count and ring size are compile-time constants and both issuers run.  Otherwise (wider descriptors,
+ * shorter rings) ONE issuer walks the tiles in order: a parity wait on a ring barrier is only sound while the waiter is at
+ * most one phase away from the barrier, which two issuers that work on different tiles cannot guarantee once a tile spans
+ * several stages - and with dim / 16 x 3 MMAs per chunk the tensor pipe, not the issue bookkeeping, is the bound there. */
+template <int KC, bool DBG, int MODE, bool FAST>
 __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    using L = TcLayout<MODE>;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::off_bar);
-    uint64_t* full = bars;                     /* [kTcStages] tile landed */
-    uint64_t* empty = bars + kTcStages;        /* [kTcStages] tile consumed by the MMAs of both query tiles */
-    uint64_t* tfull = bars + 2 * kTcStages;    /* [4] accumulator ready */
+    const TcPlan& L = a.plan;
+    const int n_stages = FAST ? kTcMaxStages : L.stages, nch = FAST ? 1 : L.nch;
+    const bool single = !FAST;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
+    uint64_t* full = bars;                     /* [kTcMaxStages] chunk landed */
+    uint64_t* empty = bars + kTcMaxStages;     /* [kTcMaxStages] chunk consumed by the MMAs of both query tiles */
+    uint64_t* tfull = bars + 2 * kTcMaxStages; /* [4] accumulator ready */
     uint64_t* tempty = tfull + 4;              /* [4] accumulator drained */
     uint64_t* a_ready = tempty + 4;            /* query operands of the next item written */
     uint64_t* item_done = a_ready + 1;         /* every MMA of the item has completed (one commit per issuer) */
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(item_done + 1);
     volatile int* s_abort = reinterpret_cast<volatile int*>(tmem_slot + 1);
     float* s_red = reinterpret_cast<float*>(tmem_slot + 2);   /* [8] query abs-max per operand warp */
-    float* s_ld = reinterpret_cast<float*>(smem + L::off_list);           /* [KC][512] candidate keys   */
+    float* s_ld = reinterpret_cast<float*>(smem + L.off_list);          /* [KC][512] candidate keys (KC > 3) */
     int* s_li = reinterpret_cast<int*>(s_ld + KC * kTcListCols);        /* [KC][512] candidate blocks */
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (MODE == 0)
-        for (int i = tid; i < 2048 / 16; i += kTcThreads) reinterpret_cast<uint4*>(smem + L::off_zero)[i] = make_uint4(0, 0, 0, 0);
+        for (int i = tid; i < 2048 / 16; i += kTcThreads) reinterpret_cast<uint4*>(smem + L.off_zero)[i] = make_uint4(0, 0, 0, 0);
     if (tid == 0) {
-        for (int s = 0; s < kTcStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int s = 0; s < kTcMaxStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         for (int b = 0; b < 4; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4); }
         mbar_init(a_ready, 256);
-        mbar_init(item_done, 2);
+        mbar_init(item_done, single ? 1 : 2);
         *s_abort = 0;
         mbar_fence_init();
     }
@@ -330,41 +318,48 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
     const int n_items = a.n_chunks * a.n_qpairs;
 
     if (warp == 0) {
-        /* ================= producer ================= */
+        /* ================= producer: one ring stage per K chunk of a template tile ================= */
         if (lane == 0) {
-            uint32_t g = 0;
-            const uint32_t tile_bytes = MODE ? (uint32_t)a.words * 4096u : (uint32_t)kTcTileBytes;
-            for (int item = blockIdx.x; item < n_items && !*s_abort; item += gridDim.x) {
+            uint32_t g = 0;                                   /* stages issued so far */
+            const uint32_t ham_bytes = (uint32_t)a.words * 4096u;
+            const size_t tile16 = MODE ? ham_bytes / 16 : (size_t)(nch * kTcChunkBytes + 2048) / 16;
+            bool ok = true;
+            for (int item = blockIdx.x; item < n_items && ok && !*s_abort; item += gridDim.x) {
                 const int chunk = item / a.n_qpairs;
                 const int t0 = chunk * a.tiles_per_chunk;
                 const int t1 = min(t0 + a.tiles_per_chunk, a.tiles_total);
-                for (int t = t0; t < t1; ++t, ++g) {
-                    const int s = g % kTcStages;
-                    if (!mbar_wait(&empty[s], ((g / kTcStages) & 1) ^ 1)) { atomicExch(a.err, 1); *s_abort = 1; break; }
-                    mbar_expect_tx(&full[s], tile_bytes);
-                    bulk_g2s(smem + L::off_b + s * L::stage_bytes, a.db + (size_t)t * (tile_bytes / 16), tile_bytes, &full[s]);
+                for (int t = t0; t < t1 && ok; ++t) {
+                    for (int c = 0; c < nch; ++c, ++g) {
+                        const uint32_t s = g % (uint32_t)n_stages;
+                        if (!mbar_wait(&empty[s], ((g / (uint32_t)n_stages) & 1u) ^ 1u)) { atomicExch(a.err, 1); *s_abort = 1; ok = false; break; }
+                        const uint32_t bytes = MODE ? ham_bytes : (c == 0 ? (uint32_t)kTcStageBytes : (uint32_t)kTcChunkBytes);
+                        const size_t off16 = MODE || c == 0 ? 0 : (kTcStageBytes + (size_t)(c - 1) * kTcChunkBytes) / 16;
+                        mbar_expect_tx(&full[s], bytes);
+                        bulk_g2s(smem + L.off_b + s * L.stage_bytes, a.db + (size_t)t * tile16 + off16, bytes, &full[s]);
+                    }
                 }
             }
         }
     } else if (warp <= 2) {
         /* ================= MMA issuers: warp 1 issues the even tiles of the CTA's tile sequence, warp 2 the odd ones,
-         * each for both query tiles (8 MMAs per template tile), so the bookkeeping of one issuer runs under the MMAs
-         * of the other.  The whole warp runs the loop (warp-uniform operands), one elected lane issues. ============ */
-        {
+         * each for both query tiles, so the bookkeeping of one issuer runs under the MMAs of the other.  The whole warp
+         * runs the loop (warp-uniform operands), one elected lane issues.  A tile of a D-dim DB is D/16 K chunks; chunk
+         * c adds hi.hi + hi.lo + lo.hi of dims 16c..16c+15 (and, with c = 0, the norm term) to BOTH accumulators of the
+         * set, then releases its ring stage; the accumulators are committed behind the last chunk. ============ */
+        if (!(single && warp == 2)) {
             const int set = warp - 1;
             const uint32_t idesc = instr_desc(128, 128, FMT_F16, FMT_F16);
-            const uint32_t sB = smem_u32(smem + L::off_b), sZ = smem_u32(smem + L::off_zero);
-            const uint32_t a0 = smem_u32(smem + L::off_a), a1 = a0 + L::a_bytes;
-            /* L2: hi | lo | norm terms of a tile.  Hamming: K step j of a tile is the two 16-byte chunks at j * 4096 */
+            const uint32_t sB = smem_u32(smem + L.off_b), sZ = smem_u32(smem + L.off_zero);
+            const uint32_t a0 = smem_u32(smem), a1 = a0 + L.a_bytes;
+            const uint32_t an_off = (uint32_t)nch * kTcChunkBytes;     /* a_n behind the chunks of a query tile */
+            /* L2: hi | lo of a chunk, norm term.  Hamming: K step j of a tile is the two 16-byte chunks at j * 4096 */
             const uint64_t a0_hi = smem_desc(a0, 2048, 128), a0_lo = smem_desc(a0 + 4096, 2048, 128);
-            const uint64_t a0_n = smem_desc(a0 + 8192, MODE ? 2048 : sZ - (a0 + 8192), 128);
+            const uint64_t a0_n = smem_desc(a0 + an_off, MODE ? 2048 : sZ - (a0 + an_off), 128);
             const uint64_t a1_hi = smem_desc(a1, 2048, 128), a1_lo = smem_desc(a1 + 4096, 2048, 128);
-            const uint64_t a1_n = smem_desc(a1 + 8192, MODE ? 2048 : sZ - (a1 + 8192), 128);
+            const uint64_t a1_n = smem_desc(a1 + an_off, MODE ? 2048 : sZ - (a1 + an_off), 128);
             const uint64_t b_hi0 = smem_desc(sB, 2048, 128), b_lo0 = smem_desc(sB + 4096, 2048, 128);
             const uint64_t b_n0 = smem_desc(sB + 8192, MODE ? 2048 : 0, 128);   /* L2: chunk 1 aliases chunk 0, A_n's chunk 1 is zero */
-            const uint32_t d0 = tmem + (set * 2) * 128, d1 = d0 + 128;
-            uint64_t* const tf0 = &tfull[set * 2], * const te0 = &tempty[set * 2];
-            uint32_t g = 0, it = 0;
+            uint32_t g = 0, it = 0;                          /* g: tiles of the CTA's sequence so far */
             long long dbg_acc[4] = {0, 0, 0, 0};
             TC_DBG_T0(tm);
             bool ok = true;
@@ -376,48 +371,57 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                 fence_after_sync();
                 const uint32_t g_end = g + (uint32_t)(t1 - t0);
 #pragma unroll 1
-                for (uint32_t gi = g + ((g ^ (uint32_t)set) & 1u); gi < g_end; gi += 2) {
-                    const uint32_t s = gi & (kTcStages - 1);
+                for (uint32_t gi = single ? g : g + ((g ^ (uint32_t)set) & 1u); gi < g_end && ok; gi += single ? 1 : 2) {
                     const uint32_t ph = (gi >> 1) & 1u;
-                    TC_DBG_ADD(2, tm);
-                    if (!mbar_wait(&full[s], (gi / kTcStages) & 1u)) { if (lane == 0) atomicExch(a.err, 3); ok = false; break; }
-                    TC_DBG_ADD(0, tm);
-                    /* the two accumulators of the set are handed back half a tile apart: issue for each as soon as it is
-                     * free instead of waiting for both */
-                    if (!mbar_wait(te0, ph ^ 1u)) { if (lane == 0) atomicExch(a.err, 4); ok = false; break; }
-                    fence_after_sync();
-                    TC_DBG_ADD(1, tm);
-                    const uint32_t off = s * (L::stage_bytes >> 4);
-                    if (elect_one()) {
-                        if (MODE == 0) {
-                            mma_f16(d0, a0_hi, b_hi0 + off, idesc, 0);
-                            mma_f16(d0, a0_hi, b_lo0 + off, idesc, 1);
-                            mma_f16(d0, a0_lo, b_hi0 + off, idesc, 1);
-                            mma_f16(d0, a0_n, b_n0 + off, idesc, 1);
-                        } else {
-                            /* -dot of the +-1 expansions, 32 bits per MMA: R = 2 * hamming - bits */
-                            for (int j = 0; j < a.words; ++j) mma_f8(d0, a0_hi + j * 256, b_hi0 + off + j * 256, idesc, j > 0);
+                    const uint32_t aset = single ? (gi & 1u) : (uint32_t)set;       /* accumulator pair = tile parity */
+                    const uint32_t d0 = tmem + (aset * 2) * 128, d1 = d0 + 128;
+                    uint64_t* const tf0 = &tfull[aset * 2], * const te0 = &tempty[aset * 2];
+#pragma unroll 1
+                    for (int c = 0; c < nch; ++c) {
+                        const uint32_t gc = gi * (uint32_t)nch + (uint32_t)c;
+                        const uint32_t s = gc % (uint32_t)n_stages;
+                        const bool first = c == 0, last = c == nch - 1;
+                        TC_DBG_ADD(2, tm);
+                        if (!mbar_wait(&full[s], (gc / (uint32_t)n_stages) & 1u)) { if (lane == 0) atomicExch(a.err, 3); ok = false; break; }
+                        TC_DBG_ADD(0, tm);
+                        /* the two accumulators of the set are handed back half a tile apart: issue for each as soon as it is
+                         * free instead of waiting for both */
+                        if (first && !mbar_wait(te0, ph ^ 1u)) { if (lane == 0) atomicExch(a.err, 4); ok = false; break; }
+                        fence_after_sync();
+                        TC_DBG_ADD(1, tm);
+                        const uint32_t off = s * ((uint32_t)L.stage_bytes >> 4);
+                        const uint32_t ao = (uint32_t)c * (kTcChunkBytes >> 4);
+                        if (elect_one()) {
+                            if (MODE == 0) {
+                                mma_f16(d0, a0_hi + ao, b_hi0 + off, idesc, first ? 0u : 1u);
+                                mma_f16(d0, a0_hi + ao, b_lo0 + off, idesc, 1);
+                                mma_f16(d0, a0_lo + ao, b_hi0 + off, idesc, 1);
+                                if (first) mma_f16(d0, a0_n, b_n0 + off, idesc, 1);
+                            } else {
+                                /* -dot of the +-1 expansions, 32 bits per MMA: R = 2 * hamming - bits */
+                                for (int j = 0; j < a.words; ++j) mma_f8(d0, a0_hi + j * 256, b_hi0 + off + j * 256, idesc, j > 0);
+                            }
+                            if (last) mma_commit(tf0);
                         }
-                        mma_commit(tf0);
-                    }
-                    __syncwarp();
-                    TC_DBG_ADD(2, tm);
-                    if (!mbar_wait(te0 + 1, ph ^ 1u)) { if (lane == 0) atomicExch(a.err, 4); ok = false; break; }
-                    fence_after_sync();
-                    TC_DBG_ADD(1, tm);
-                    if (elect_one()) {
-                        if (MODE == 0) {
-                            mma_f16(d1, a1_hi, b_hi0 + off, idesc, 0);
-                            mma_f16(d1, a1_hi, b_lo0 + off, idesc, 1);
-                            mma_f16(d1, a1_lo, b_hi0 + off, idesc, 1);
-                            mma_f16(d1, a1_n, b_n0 + off, idesc, 1);
-                        } else {
-                            for (int j = 0; j < a.words; ++j) mma_f8(d1, a1_hi + j * 256, b_hi0 + off + j * 256, idesc, j > 0);
+                        __syncwarp();
+                        TC_DBG_ADD(2, tm);
+                        if (first && !mbar_wait(te0 + 1, ph ^ 1u)) { if (lane == 0) atomicExch(a.err, 4); ok = false; break; }
+                        fence_after_sync();
+                        TC_DBG_ADD(1, tm);
+                        if (elect_one()) {
+                            if (MODE == 0) {
+                                mma_f16(d1, a1_hi + ao, b_hi0 + off, idesc, first ? 0u : 1u);
+                                mma_f16(d1, a1_hi + ao, b_lo0 + off, idesc, 1);
+                                mma_f16(d1, a1_lo + ao, b_hi0 + off, idesc, 1);
+                                if (first) mma_f16(d1, a1_n, b_n0 + off, idesc, 1);
+                            } else {
+                                for (int j = 0; j < a.words; ++j) mma_f8(d1, a1_hi + j * 256, b_hi0 + off + j * 256, idesc, j > 0);
+                            }
+                            if (last) mma_commit(tf0 + 1);
+                            mma_commit(&empty[s]);
                         }
-                        mma_commit(tf0 + 1);
-                        mma_commit(&empty[s]);
+                        __syncwarp();
                     }
-                    __syncwarp();
                 }
                 if (!ok) break;
                 /* the operand warps may rewrite the query tiles once both issuers' MMAs of this item are done */
@@ -459,19 +463,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
             const int qidx = (qpair * 2 + qt) * kTcRows + row;
             const bool q_ok = qidx < a.nq;
             if (set == 0 && MODE == 0) {
-                /* ---- query operands (256 threads): centre, scale, split, store in the K-major core-matrix layout */
-                float qv[16];
+                /* ---- query operands (256 threads): centre, scale, split, store in the K-major core-matrix layout.  Two
+                 * passes over the query row (it stays in L1): the tile's abs-max first, then one 16-dim chunk at a time */
+                const float4* q4 = reinterpret_cast<const float4*>(a.q + (size_t)(q_ok ? qidx : 0) * a.q_ld);
+                const float4* c4 = reinterpret_cast<const float4*>(a.ctr);
+                const int n4 = a.q_ld >> 2;
                 float m = 0.f;
-#pragma unroll
-                for (int d4 = 0; d4 < 4; ++d4) {
-                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (q_ok && 4 * d4 < a.q_ld) {
-                        v = __ldg(reinterpret_cast<const float4*>(a.q + (size_t)qidx * a.q_ld) + d4);
-                        v.x -= a.ctr.c[4 * d4 + 0]; v.y -= a.ctr.c[4 * d4 + 1]; v.z -= a.ctr.c[4 * d4 + 2]; v.w -= a.ctr.c[4 * d4 + 3];
+                if (q_ok)
+                    for (int d4 = 0; d4 < n4; ++d4) {
+                        const float4 v = __ldg(q4 + d4), c = __ldg(c4 + d4);
+                        m = fmaxf(m, fmaxf(fmaxf(fabsf(v.x - c.x), fabsf(v.y - c.y)), fmaxf(fabsf(v.z - c.z), fabsf(v.w - c.w))));
                     }
-                    qv[4 * d4 + 0] = v.x; qv[4 * d4 + 1] = v.y; qv[4 * d4 + 2] = v.z; qv[4 * d4 + 3] = v.w;
-                    m = fmaxf(m, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
-                }
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
                 if (lane == 0) s_red[qt * 4 + quarter] = m;
@@ -483,21 +485,37 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                 if (ea > 15) { eq -= ea - 15; ea = 15; }
                 const float s_q = ldexpf(1.f, eq);
                 const __half an = ea < -24 ? __ushort_as_half(0) : __float2half_rn(ldexpf(1.f, ea));
-                uint32_t hi[8], lo[8];
+                if (q_ok && chunk == 0) a.key_scale[qidx] = ldexpf(1.f, -(eq + a.log2_st));
+                uint4* op = reinterpret_cast<uint4*>(smem + qt * L.a_bytes);
+#pragma unroll 1
+                for (int c = 0; c < nch; ++c) {
+                    float qv[16];
 #pragma unroll
-                for (int d = 0; d < 16; d += 2) {
-                    __half h0, l0, h1, l1;
-                    split_f16(-2.f * s_q * qv[d], h0, l0);
-                    split_f16(-2.f * s_q * qv[d + 1], h1, l1);
-                    hi[d / 2] = pack_h2(h0, h1);
-                    lo[d / 2] = pack_h2(l0, l1);
+                    for (int d4 = 0; d4 < 4; ++d4) {
+                        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (q_ok && 4 * c + d4 < n4) {
+                            const float4 cc = __ldg(c4 + 4 * c + d4);
+                            v = __ldg(q4 + 4 * c + d4);
+                            v.x -= cc.x; v.y -= cc.y; v.z -= cc.z; v.w -= cc.w;
+                        }
+                        qv[4 * d4 + 0] = v.x; qv[4 * d4 + 1] = v.y; qv[4 * d4 + 2] = v.z; qv[4 * d4 + 3] = v.w;
+                    }
+                    uint32_t hi[8], lo[8];
+#pragma unroll
+                    for (int d = 0; d < 16; d += 2) {
+                        __half h0, l0, h1, l1;
+                        split_f16(-2.f * s_q * qv[d], h0, l0);
+                        split_f16(-2.f * s_q * qv[d + 1], h1, l1);
+                        hi[d / 2] = pack_h2(h0, h1);
+                        lo[d / 2] = pack_h2(l0, l1);
+                    }
+                    uint4* oc = op + c * (kTcChunkBytes / 16);
+                    oc[0 + row] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                    oc[128 + row] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+                    oc[256 + row] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                    oc[384 + row] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
                 }
-                uint4* op = reinterpret_cast<uint4*>(smem + L::off_a + qt * L::a_bytes);
-                op[0 + row] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                op[128 + row] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-                op[256 + row] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                op[384 + row] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
-                op[512 + row] = make_uint4(pack_h2(an, an), pack_h2(an, __ushort_as_half(0)), 0u, 0u);
+                op[nch * (kTcChunkBytes / 16) + row] = make_uint4(pack_h2(an, an), pack_h2(an, __ushort_as_half(0)), 0u, 0u);
                 fence_async_smem();
                 mbar_arrive(a_ready);
                 asm volatile("bar.sync 1, 256;" ::: "memory");   /* s_red may be rewritten by the next item */
@@ -505,7 +523,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
             if (set == 0 && MODE == 1) {
                 /* ---- query operands, Hamming: bit b of the code -> -(+-1) as e4m3 (0x38 = +1, 0xB8 = -1), 16 bits per
                  * 16-byte core-matrix row, K chunk c = bits 16c .. 16c+15 */
-                uint4* op = reinterpret_cast<uint4*>(smem + L::off_a + qt * L::a_bytes);
+                uint4* op = reinterpret_cast<uint4*>(smem + qt * L.a_bytes);
                 for (int w = 0; w < a.words; ++w) {
                     const uint32_t code = q_ok ? __ldg(a.qcodes + (size_t)qidx * a.words + w) : 0u;
                     op[(2 * w) * 128 + row] = tc_expand16(code & 0xFFFFu, 0x38383838u);
@@ -589,7 +607,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
                                 }
                             }
                         } else {
-                            thr = tc_list_insert4(my_ld, my_li, tau_up, m0, m1, m2, m3, blk0, a.n_blocks);
+                            thr = tc_list_insert4<KC>(my_ld, my_li, tau_up, m0, m1, m2, m3, blk0, a.n_blocks);
                             th = fminf(thr, tau_up);
                         }
                         if (thr < INFINITY && q_ok) atomicMin(tau_p, f2ord(thr));
@@ -630,35 +648,61 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn_tc_scan_kernel(const TcArgs
 }
 
 /* ------------------------------------------------------------------ select ---- */
-/* One warp per query.  The scan left n_lists x kc (key, block) candidates; the kTcSelBlocks best blocks by
+/* One warp per query.  The scan left n_lists x kc (key, block) candidates; the n_sel best blocks by
  * (key, block id) are evaluated exactly -- the reference's fp32 sqrt(sum (q-t)^2) for each of their 32 templates --
  * and the k smallest by (distance, index) are the answer, as BFMatcher::knnMatch orders them
- * (reference src/networkevaluator.cpp:197; ties -> lower index). */
+ * (reference src/networkevaluator.cpp:197; ties -> lower index).
+ *
+ * Certificate (flag != null).  Every block outside the re-ranked ones has a scan key >= B:
+ *   - a candidate that was not re-ranked has a key >= the (n_sel + 1)-th smallest candidate key;
+ *   - a block that is in no list was rejected or evicted while some list of this query held kc keys <= its own (own
+ *     list's threshold, or the shared threshold tau = another list's kc-th best), and list entries are only ever
+ *     replaced by smaller keys: its key is >= K*, the kc-th smallest candidate key.
+ * A scan key is s_q s_t (|t'|^2 - 2 q'.t') (primes: centred on the DB mean) up to the error of the arithmetic: each
+ * operand is a two-term fp16 split (residual <= 2^-22 relative), the lo.lo product is dropped, the tensor core
+ * accumulates the <= 8 x 3 + 1 products of a tile with truncation (<= 2^-23 of the running magnitude each), the
+ * three-term norm split is exact to 2^-33:  |key / (s_q s_t) - R| <= 2^-17 |q'| T + 2^-19 T^2  with T = max |t'| over
+ * the DB (a factor >= 4 above the worst case of the terms just listed).  So every template that was not re-ranked has
+ * d^2 >= |q'|^2 + B / (s_q s_t) - eps, and the reported k-th neighbour is proven whenever its exact d_k^2 lies below
+ * that.  Queries that cannot be proven (near-ties at the list boundary, or a DB whose spread T^2 is > ~1e5 x the
+ * neighbour distances, e.g. tight far-apart clusters) are appended to flag[] and re-scanned with the direct expression. */
 constexpr int kTcSelWarps = 4;               /* queries (warps) per CTA of the L2 select kernel */
 __global__ void __launch_bounds__(32 * kTcSelWarps)
-knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ cand_i, int n_cand,
+knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ cand_i, int n_cand, int kc,
                      const float* __restrict__ q, const float* __restrict__ db, int dp, long long t_local,
-                     long long row_offset, int k, int n_sel, long long nq, int* __restrict__ out_idx, float* __restrict__ out_dist) {
+                     long long row_offset, int k, int n_sel, long long nq, const float* __restrict__ key_scale,
+                     const float* __restrict__ ctr, float max_norm2, int* __restrict__ flag,
+                     int* __restrict__ out_idx, float* __restrict__ out_dist) {
     extern __shared__ __align__(16) float sel_smem_all[];
     /* one warp per query, kTcSelWarps independent queries per CTA (32-thread CTAs cap an SM at 32 resident warps, and
      * this kernel is a chain of dependent reductions and random row reads: it lives on resident warps) */
-    float* sel_smem = sel_smem_all + (size_t)(threadIdx.x >> 5) * (dp + 2 * n_cand + 2 * kTcSelBlocks * kTcBlock);
+    float* sel_smem = sel_smem_all + (size_t)(threadIdx.x >> 5) * (dp + 2 * n_cand + 2 * n_sel * kTcBlock);
     float* sq = sel_smem;                                   /* [dp] */
     float* sd = sel_smem + dp;                              /* [n_cand] keys */
     int* si = reinterpret_cast<int*>(sd + n_cand);          /* [n_cand] block ids */
-    float* ed = reinterpret_cast<float*>(si + n_cand);      /* [kTcSelBlocks * 32] exact distances */
-    int* ei = reinterpret_cast<int*>(ed + kTcSelBlocks * kTcBlock);
+    float* ed = reinterpret_cast<float*>(si + n_cand);      /* [n_sel * 32] exact distances */
+    int* ei = reinterpret_cast<int*>(ed + n_sel * kTcBlock);
     const int lane = threadIdx.x & 31;
     const long long qi = (long long)blockIdx.x * kTcSelWarps + (threadIdx.x >> 5);
     if (qi >= nq) return;
-    for (int d = lane; d < dp; d += 32) sq[d] = q[(size_t)qi * dp + d];
+    float qn2 = 0.f;                                        /* |q - c|^2 */
+    for (int d = lane; d < dp; d += 32) {
+        const float v = q[(size_t)qi * dp + d];
+        sq[d] = v;
+        if (flag) { const float c = v - ctr[d]; qn2 = fmaf(c, c, qn2); }
+    }
     for (int c = lane; c < n_cand; c += 32) {
         const int blk = cand_i[(size_t)qi * n_cand + c];
         sd[c] = blk >= 0 ? cand_d[(size_t)qi * n_cand + c] : INFINITY;
         si[c] = blk >= 0 ? blk : INT_MAX;
     }
+    for (int c = lane; c < n_sel * kTcBlock; c += 32) { ed[c] = INFINITY; ei[c] = INT_MAX; }
     __syncwarp();
-    for (int r = 0; r < n_sel; ++r) {
+    /* extraction in ascending (key, id) order: rounds 0 .. n_sel - 1 are re-ranked, the certificate also wants the
+     * kc-th smallest key (K*) and the first key that is NOT re-ranked */
+    float key_kstar = INFINITY, key_next = INFINITY;
+    const int rounds = flag ? (n_sel + 1 > kc ? n_sel + 1 : kc) : n_sel;
+    for (int r = 0; r < rounds; ++r) {
         float bd = INFINITY;
         int bi = INT_MAX, bc = -1;
         for (int c = lane; c < n_cand; c += 32) {
@@ -673,25 +717,30 @@ knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ c
             const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
             if (oc >= 0 && (bc < 0 || od < bd || (od == bd && oi < bi))) { bd = od; bi = oi; bc = oc; }
         }
-        float d = INFINITY;
-        int idx = INT_MAX;
-        if (bc >= 0) {
+        if (bc < 0) break;                                  /* no candidate left (warp-uniform) */
+        if (r == kc - 1) key_kstar = bd;
+        if (r == n_sel) key_next = bd;
+        if (r < n_sel) {
+            float d = INFINITY;
+            int idx = INT_MAX;
             const long long row = (long long)bi * kTcBlock + lane;
             if (row < t_local) {
                 d = exact_l2(sq, db + (size_t)row * dp, dp);
                 idx = (int)row;
             }
+            ed[r * kTcBlock + lane] = d;
+            ei[r * kTcBlock + lane] = idx;
         }
-        ed[r * kTcBlock + lane] = d;
-        ei[r * kTcBlock + lane] = idx;
         __syncwarp();
-        if (lane == 0 && bc >= 0) si[bc] = INT_MAX;
+        if (lane == 0) si[bc] = INT_MAX;
         __syncwarp();
+        if (r >= n_sel && r >= kc - 1) break;
     }
+    float d_kth = INFINITY;
+    bool have_k = true;
     for (int r = 0; r < k; ++r) {
         float bd = INFINITY;
         int bi = INT_MAX, bc = -1;
-#pragma unroll
         for (int c = lane; c < n_sel * kTcBlock; c += 32) {
             const float d = ed[c];
             const int i = ei[c];
@@ -704,6 +753,7 @@ knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ c
             const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
             if (oc >= 0 && (bc < 0 || od < bd || (od == bd && oi < bi))) { bd = od; bi = oi; bc = oc; }
         }
+        if (bc >= 0) d_kth = bd; else have_k = false;
         if (lane == 0) {
             out_idx[(size_t)qi * k + r] = bc >= 0 ? (int)(bi + row_offset) : -1;
             out_dist[(size_t)qi * k + r] = bc >= 0 ? bd : INFINITY;
@@ -711,20 +761,38 @@ knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ c
         }
         __syncwarp();
     }
+    if (flag) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) qn2 += __shfl_xor_sync(0xffffffffu, qn2, off);
+        /* B: lower bound of the scan keys of everything that was not re-ranked (see the comment above) */
+        const float b_key = n_sel >= kc ? key_kstar : key_next;
+        bool proven = true;
+        if (b_key < INFINITY) {
+            const float qn = sqrtf(qn2), tmax = sqrtf(max_norm2);
+            const float eps = 7.62939453125e-6f * qn * tmax + 1.9073486328125e-6f * (max_norm2 + qn2);    /* 2^-17, 2^-19 */
+            const float lb = qn2 + b_key * key_scale[qi] - eps;          /* d^2 of any template that was not re-ranked */
+            const float dk2 = d_kth * d_kth;
+            proven = have_k && dk2 * 1.000002f < lb;
+        }
+        if (!proven && lane == 0) {
+            const int slot = atomicAdd(flag, 1);
+            flag[4 + slot] = (int)qi;
+        }
+    }
 }
 
 /* Hamming twin of knn_tc_select_kernel: exact XOR + POPC distance over the 32 codes of each of the best blocks.  With
  * integer keys the block order (key, id) is exact, and a block holding one of the k nearest (ties -> lower row) is
- * preceded by at most k - 1 others, so the first 8 blocks contain the answer for k <= 5. */
+ * preceded by at most k - 1 others, so the first n_sel >= k blocks contain the answer (no certificate needed). */
 __global__ void __launch_bounds__(32)
 knn_tc_select_hamming_kernel(const float* __restrict__ cand_d, const int* __restrict__ cand_i, int n_cand,
                              const uint32_t* __restrict__ q, const uint32_t* __restrict__ codes, int words, long long t_local,
-                             long long row_offset, int k, int* __restrict__ out_idx, int* __restrict__ out_dist) {
+                             long long row_offset, int k, int n_sel, int* __restrict__ out_idx, int* __restrict__ out_dist) {
     extern __shared__ __align__(16) float sel_smem[];
     float* sd = sel_smem;                                   /* [n_cand] keys */
     int* si = reinterpret_cast<int*>(sd + n_cand);          /* [n_cand] block ids */
-    int* ed = si + n_cand;                                  /* [kTcSelBlocks * 32] exact distances */
-    int* ei = ed + kTcSelBlocks * kTcBlock;
+    int* ed = si + n_cand;                                  /* [n_sel * 32] exact distances */
+    int* ei = ed + n_sel * kTcBlock;
     const int lane = threadIdx.x;
     const long long qi = blockIdx.x;
     uint32_t qc[8];
@@ -735,7 +803,7 @@ knn_tc_select_hamming_kernel(const float* __restrict__ cand_d, const int* __rest
         si[c] = blk >= 0 ? blk : INT_MAX;
     }
     __syncwarp();
-    for (int r = 0; r < kTcSelBlocks; ++r) {
+    for (int r = 0; r < n_sel; ++r) {
         float bd = INFINITY;
         int bi = INT_MAX, bc = -1;
         for (int c = lane; c < n_cand; c += 32) {
@@ -767,8 +835,7 @@ knn_tc_select_hamming_kernel(const float* __restrict__ cand_d, const int* __rest
     }
     for (int r = 0; r < k; ++r) {
         int bd = INT_MAX, bi = INT_MAX, bc = -1;
-#pragma unroll
-        for (int c = lane; c < kTcSelBlocks * kTcBlock; c += 32) {
+        for (int c = lane; c < n_sel * kTcBlock; c += 32) {
             const int d = ed[c], i = ei[c];
             if (i != INT_MAX && (bc < 0 || d < bd || (d == bd && i < bi))) { bd = d; bi = i; bc = c; }
         }
@@ -790,7 +857,7 @@ knn_tc_select_hamming_kernel(const float* __restrict__ cand_d, const int* __rest
 
 }  // namespace
 
-/* packs the (already padded, normed) fp32 DB of `db` into tensor tiles; called once per DB */
+/* packs the (already padded, centred-stats-known) fp32 DB of `db` into tensor tiles; called once per DB */
 int knn_tc_prepare(pe_db* db) {
     db->tc_ready = false;
     if (db->t_local <= 0) return PE_OK;
@@ -809,41 +876,19 @@ int knn_tc_prepare(pe_db* db) {
         db->tc_ready = true;
         return PE_OK;
     }
-    if ((db->dim_pad != 16 && db->dim_pad != 4)) return PE_OK;
-    PE_CUDA(cudaSetDevice(db->device));
     const int ld = db->dim_pad;
-    void* d_tmp = nullptr;
-    PE_CUDA(cudaMalloc(&d_tmp, 16 * sizeof(double) + 2 * sizeof(unsigned)));
-    double* d_sum = reinterpret_cast<double*>(d_tmp);
-    unsigned* d_max = reinterpret_cast<unsigned*>(d_sum + 16);
-    PE_CUDA(cudaMemsetAsync(d_tmp, 0, 16 * sizeof(double) + 2 * sizeof(unsigned), db->stream));
-    tc_mean_kernel<<<296, 256, 0, db->stream>>>(db->d_desc, ld, db->t_local, d_sum);
-    PE_LAUNCHED();
-    double h_sum[16];
-    PE_CUDA(cudaMemcpyAsync(h_sum, d_sum, sizeof(h_sum), cudaMemcpyDeviceToHost, db->stream));
-    PE_CUDA(cudaStreamSynchronize(db->stream));
-    TcCenter ctr;
-    for (int d = 0; d < 16; ++d) {
-        const double m = h_sum[d] / (double)db->t_local;
-        ctr.c[d] = std::isfinite(m) ? (float)m : 0.f;
-        db->tc_center[d] = ctr.c[d];
-    }
-    tc_stats_kernel<<<296, 256, 0, db->stream>>>(db->d_desc, ld, db->t_local, ctr, d_max);
-    PE_LAUNCHED();
-    unsigned h[2];
-    PE_CUDA(cudaMemcpyAsync(h, d_max, sizeof(h), cudaMemcpyDeviceToHost, db->stream));
-    PE_CUDA(cudaStreamSynchronize(db->stream));
-    cudaFree(d_tmp);
-    float mt, mn;
-    memcpy(&mt, &h[0], 4);
-    memcpy(&mn, &h[1], 4);
+    if (ld != 4 && ld != 16 && ld != 64 && ld != 128) return PE_OK;
+    if (!db->d_center) return PE_OK;                        /* knn_center_stats did not run */
+    PE_CUDA(cudaSetDevice(db->device));
+    const float mt = db->max_abs_c, mn = db->max_norm2_c;
     /* s_t: max |s_t (t-c)| in [2^10, 2^11);  s_n: max s_n |t-c|^2 in [2^14, 2^15) */
     db->tc_log2_st = mt > 0.f ? 10 - ilogbf(mt) : 0;
     db->tc_log2_sn = mn > 0.f ? 14 - ilogbf(mn) : 0;
+    const int nch = ld > 16 ? ld / 16 : 1;
     const long long tiles = (db->t_local + kTcRows - 1) / kTcRows;
-    PE_CUDA(cudaMalloc(&db->d_tc, (size_t)tiles * kTcTileBytes));
+    PE_CUDA(cudaMalloc(&db->d_tc, (size_t)tiles * ((size_t)nch * kTcChunkBytes + 2048)));
     tc_pack_db_kernel<<<(unsigned)((tiles * kTcRows + 255) / 256), 256, 0, db->stream>>>(
-        db->d_desc, ld, db->t_local, ctr, ldexpf(1.f, db->tc_log2_st), ldexpf(1.f, db->tc_log2_sn),
+        db->d_desc, ld, nch, db->t_local, db->d_center, ldexpf(1.f, db->tc_log2_st), ldexpf(1.f, db->tc_log2_sn),
         reinterpret_cast<uint4*>(db->d_tc));
     PE_LAUNCHED();
     /* pinned, device-visible flag: the kernels write it only when a pipeline barrier times out */
@@ -854,8 +899,12 @@ int knn_tc_prepare(pe_db* db) {
     return PE_OK;
 }
 
-bool knn_tc_usable(const pe_db* db, int k) { return db->tc_ready && k + 2 <= 7; }
-
+/* the tensor scan serves every (dim, k <= 16) whose shared-memory plan leaves at least two ring stages */
+bool knn_tc_usable(const pe_db* db, int k) {
+    if (!db->tc_ready || k < 1 || k > 16) return false;
+    TcPlan p;
+    return tc_make_plan(db->hamming, db->dim_pad, tc_kc_for(k), &p);
+}
 
 /* plans the chunking; returns the number of candidate lists per query (two per chunk: even and odd tiles) and kc */
 void knn_tc_plan(const pe_db* db, int64_t nq, int k, int* n_lists, int* kc, int* tiles_per_chunk) {
@@ -876,14 +925,16 @@ void knn_tc_plan(const pe_db* db, int64_t nq, int k, int* n_lists, int* kc, int*
     const long long tpc = (tiles + c - 1) / c;
     *tiles_per_chunk = (int)tpc;
     *n_lists = 2 * (int)((tiles + tpc - 1) / tpc);
-    *kc = k <= 1 ? 3 : 7;
+    *kc = tc_kc_for(k);
 }
 
 int knn_tc_scan(pe_db* db, const void* d_q, int64_t nq, int k, int n_lists, int kc, int tiles_per_chunk,
                 float* cand_d, int* cand_i) {
     PE_CHECK(db->tau.reserve((size_t)nq * sizeof(int)));
+    PE_CHECK(db->key_scale.reserve((size_t)nq * sizeof(float)));
     PE_CUDA(cudaMemsetAsync(db->tau.p, 0x7f, (size_t)nq * sizeof(int), db->stream));
     TcArgs a;
+    PE_REQUIRE(tc_make_plan(db->hamming, db->dim_pad, kc, &a.plan), "tensor scan: no shared-memory plan for dim %d, k + 2 = %d", db->dim_pad, kc);
     a.q = db->hamming ? nullptr : static_cast<const float*>(d_q);
     a.qcodes = db->hamming ? static_cast<const uint32_t*>(d_q) : nullptr;
     a.nq = (int)nq;
@@ -900,7 +951,8 @@ int knn_tc_scan(pe_db* db, const void* d_q, int64_t nq, int k, int n_lists, int 
     a.log2_st = db->tc_log2_st;
     a.log2_sn = db->tc_log2_sn;
     a.tau = db->tau.as<int>();
-    for (int d = 0; d < 16; ++d) a.ctr.c[d] = db->tc_center[d];
+    a.ctr = db->d_center;
+    a.key_scale = db->key_scale.as<float>();
     a.cand_d = cand_d;
     a.cand_i = cand_i;
     a.err = db->d_tc_err;
@@ -914,16 +966,21 @@ int knn_tc_scan(pe_db* db, const void* d_q, int64_t nq, int k, int n_lists, int 
     }
     const int items = a.n_chunks * a.n_qpairs;
     const int grid = items < db->num_sms ? items : db->num_sms;
-#define TC_LAUNCH(KCV, DBGV, MODEV) do { \
-        PE_CUDA(cudaFuncSetAttribute(knn_tc_scan_kernel<KCV, DBGV, MODEV>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcLayout<MODEV>::total)); \
-        knn_tc_scan_kernel<KCV, DBGV, MODEV><<<grid, kTcThreads, TcLayout<MODEV>::total, db->stream>>>(a); } while (0)
+    const int smem_bytes = a.plan.total;
+    const bool fast = a.plan.nch == 1 && a.plan.stages == kTcMaxStages;
+#define TC_LAUNCH2(KCV, DBGV, MODEV, FASTV) do { \
+        PE_CUDA(cudaFuncSetAttribute(knn_tc_scan_kernel<KCV, DBGV, MODEV, FASTV>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemMax)); \
+        knn_tc_scan_kernel<KCV, DBGV, MODEV, FASTV><<<grid, kTcThreads, smem_bytes, db->stream>>>(a); } while (0)
+#define TC_LAUNCH(KCV, DBGV, MODEV) do { if (fast) TC_LAUNCH2(KCV, DBGV, MODEV, true); else TC_LAUNCH2(KCV, DBGV, MODEV, false); } while (0)
     if (db->hamming) {
-        if (kc == 3) TC_LAUNCH(3, false, 1); else TC_LAUNCH(7, false, 1);
+        if (kc == 3) TC_LAUNCH(3, false, 1); else if (kc == 7) TC_LAUNCH(7, false, 1); else TC_LAUNCH(18, false, 1);
     } else if (kc == 3) { if (dbg_on) TC_LAUNCH(3, true, 0); else TC_LAUNCH(3, false, 0); }
-    else { if (dbg_on) TC_LAUNCH(7, true, 0); else TC_LAUNCH(7, false, 0); }
+    else if (kc == 7) { if (dbg_on) TC_LAUNCH(7, true, 0); else TC_LAUNCH(7, false, 0); }
+    else TC_LAUNCH(18, false, 0);
+#undef TC_LAUNCH2
 #undef TC_LAUNCH
     PE_LAUNCHED();
-    if (dbg_on && !db->hamming) {
+    if (dbg_on && !db->hamming && a.dbg) {
         unsigned long long h[16];
         PE_CUDA(cudaMemcpyAsync(h, d_dbg, sizeof(h), cudaMemcpyDeviceToHost, db->stream));
         PE_CUDA(cudaStreamSynchronize(db->stream));
@@ -936,18 +993,20 @@ int knn_tc_scan(pe_db* db, const void* d_q, int64_t nq, int k, int n_lists, int 
     return PE_OK;
 }
 
-/* exact re-ranking of the candidate blocks the scan produced: the local top-k of this shard */
+/* exact re-ranking of the candidate blocks the scan produced: the local top-k of this shard.  d_flag (may be null):
+ * [0] counter + [4..] ids of the queries whose result the certificate could not prove */
 int knn_tc_select(pe_db* db, const float* cand_d, const int* cand_i, int n_lists, int kc, const float* d_q,
-                  int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist) {
+                  int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist, int* d_flag) {
     const int n_cand = n_lists * kc;
-    const size_t smem = (size_t)kTcSelWarps * (db->dim_pad + 2 * n_cand + 2 * kTcSelBlocks * kTcBlock) * 4;
+    /* blocks re-ranked exactly: a block holding one of the k nearest is preceded only by blocks whose key lies within the
+     * split's ~2^-22 of it, so k + 3 keeps the margin the k + 2 list entries have (8 for k = 5, 4 for k = 1, 19 for k = 16) */
+    const int n_sel = k + 3 < kTcMaxSel ? k + 3 : kTcMaxSel;
+    const size_t smem = (size_t)kTcSelWarps * (db->dim_pad + 2 * n_cand + 2 * n_sel * kTcBlock) * 4;
     PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
     PE_CUDA(cudaFuncSetAttribute(knn_tc_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    /* blocks re-ranked exactly: a block holding one of the k nearest is preceded only by blocks whose key lies within the
-     * split's ~2^-22 of it, so k + 3 keeps the margin the k + 2 list entries have (8 for k = 5, 4 for k = 1) */
-    const int n_sel = k + 3 < kTcSelBlocks ? k + 3 : kTcSelBlocks;
     knn_tc_select_kernel<<<(unsigned)((nq + kTcSelWarps - 1) / kTcSelWarps), 32 * kTcSelWarps, smem, db->stream>>>(
-        cand_d, cand_i, n_cand, d_q, db->d_desc, db->dim_pad, db->t_local, db->row_offset, k, n_sel, (long long)nq, d_out_idx, d_out_dist);
+        cand_d, cand_i, n_cand, kc, d_q, db->d_desc, db->dim_pad, db->t_local, db->row_offset, k, n_sel, (long long)nq,
+        db->key_scale.as<float>(), db->d_center, db->max_norm2_c, d_flag, d_out_idx, d_out_dist);
     PE_LAUNCHED();
     return PE_OK;
 }
@@ -955,11 +1014,12 @@ int knn_tc_select(pe_db* db, const float* cand_d, const int* cand_i, int n_lists
 int knn_tc_select_hamming(pe_db* db, const float* cand_d, const int* cand_i, int n_lists, int kc, const uint32_t* d_q,
                           int64_t nq, int k, int32_t* d_out_idx, int32_t* d_out_dist) {
     const int n_cand = n_lists * kc;
-    const size_t smem = (size_t)(2 * n_cand + 2 * kTcSelBlocks * kTcBlock) * 4;
+    const int n_sel = k > 8 ? k : 8;
+    const size_t smem = (size_t)(2 * n_cand + 2 * n_sel * kTcBlock) * 4;
     PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
     PE_CUDA(cudaFuncSetAttribute(knn_tc_select_hamming_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     knn_tc_select_hamming_kernel<<<(unsigned)nq, 32, smem, db->stream>>>(cand_d, cand_i, n_cand, d_q, db->d_codes, db->words,
-                                                                        db->t_local, db->row_offset, k, d_out_idx, d_out_dist);
+                                                                        db->t_local, db->row_offset, k, n_sel, d_out_idx, d_out_dist);
     PE_LAUNCHED();
     return PE_OK;
 }

@@ -314,6 +314,7 @@ def gpu_arm(args, rank, world, local_rank, dist):
     launches = capi.launch_count() - launches0
     clocks = sampler.stop()
     last = (args.steps - 1) & 1
+    knn_flagged = db.knn_flagged()      # queries of the last timed step the matcher's certificate sent to the exact re-scan
     # ---- parity of the timed region's own output (untimed): the first 256 patches of the last timed batch against the
     #      oracle chain, both descriptor norms + 1-NN agreement; at N > 1 also sharded == unsharded
     n_par = 256
@@ -483,6 +484,9 @@ def gpu_arm(args, rank, world, local_rank, dist):
         "paths": {"forward": "tcgen05 fp16 x3" if fwd_tensor else "simt", "knn": "tcgen05" if capi.get_option("knn_tensor") else "simt",
                   "streams": "forward on the net's stream, exchange + scan + merge on the DB's stream (pe_match_patches_dev)",
                   "exchange": ("one peer-memory kernel over NVLink (CUDA IPC windows)" if comm.p2p_active() else "NCCL all-gather") if world > 1 else None},
+        "knn_certificate": {"queries_per_step": nq_all, "flagged_last_timed_step": int(knn_flagged),
+                            "note": "L2 matcher proves per query that no unexamined template beats the reported neighbour; "
+                                    "unproven queries are re-scanned with the direct fp32 (q-t)^2 expression inside the step"},
         "ms_per_step_serialised": ms_serial / args.steps,
         "kernels_ms_per_step": {"conv1_pool_act": conv1_ms, "conv2_pool_act": net_ms[1] / max(1, net_calls),
                                 "fc_act": net_ms[2] / max(1, net_calls), "knn_l2_scan": scan_ms,

@@ -201,6 +201,11 @@ PE_API int pe_knn(pe_db* db, const float* queries, int64_t nq, int k, int32_t* o
                   float* out_dist);
 PE_API int pe_knn_dev(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* d_out_idx,
                       float* d_out_dist);
+/* exactness certificate of the L2 matcher (pe_set_option("knn_certify"), default on): number of queries of the LAST
+ * L2 kNN call on this DB whose neighbours the ranking pass could not prove and that were therefore re-scanned with the
+ * direct fp32 (q-t)^2 expression (synchronises the DB's stream).  New: OpenCV's BFMatcher computes that expression for
+ * every pair (reference src/networkevaluator.cpp:197); here it is the proof obligation of the tensor / SIMT scans. */
+PE_API int pe_db_knn_flagged(pe_db* db, int64_t* n);
 /* Hamming variant; distances are bit counts. */
 PE_API int pe_knn_hamming(pe_db* db, const uint32_t* qcodes, int64_t nq, int k, int32_t* out_idx,
                           int32_t* out_dist);

@@ -241,7 +241,11 @@ def test_knn_l2_matches_cv2_golden(gpu, synth, golden, dim, knn_path):
 
 @pytest.mark.parametrize("dim,nq,nt,k", [(16, 1500, 19500, 1), (16, 700, 5000, 5), (16, 64, 333, 3), (3, 2000, 19500, 1),
                                          (3, 300, 1000, 5), (64, 300, 3000, 3), (128, 200, 2500, 5), (16, 130, 70000, 16),
-                                         (16, 1, 1000, 1), (7, 50, 400, 2)])
+                                         (16, 1, 1000, 1), (7, 50, 400, 2),
+                                         # the descriptors the reference L2-matches beyond 16-d (manifold_wang: 64, float
+                                         # bin_ip2: 128) and k > 5: tensor scan with D / 16 K chunks, 18-entry lists
+                                         (64, 700, 40000, 1), (128, 600, 30000, 3), (64, 300, 9000, 16), (128, 257, 5000, 16),
+                                         (128, 300, 70001, 1), (40, 100, 3000, 6), (100, 120, 2000, 9)])
 def test_knn_l2_matches_oracle(gpu, po, synth, dim, nq, nt, k, knn_path):
     _, t, _, _ = mg.eval_problem(synth.BASE_SEED + dim + k, 10, (nt + 9) // 10, 3, dim)
     t = t[:nt]
@@ -251,6 +255,10 @@ def test_knn_l2_matches_oracle(gpu, po, synth, dim, nq, nt, k, knn_path):
     q[0] = t[3]
     db = gpu.TemplateDB(desc=t)
     idx, dist = db.knn(q, k)
+    # the exact re-scan must stay the exception on well-spread data: a scan that nominates wrong blocks would hide
+    # behind it otherwise
+    flagged = db.knn_flagged()
+    assert flagged <= 2 + nq // 20, f"{flagged} of {nq} queries needed the exact re-scan"
     oi, od, gap = po.knn_l2(q, t, k, want_gap=True)
     frac = check_knn(idx, dist, oi, od, gap)
     assert frac < 0.01
@@ -289,6 +297,42 @@ def test_knn_l2_clustered_descriptors(gpu, po, knn_path):
     assert check_knn(idx, dist, oi, od, gap) < 0.05
 
 
+@pytest.mark.parametrize("n_clusters,k", [(15, 1), (15, 5), (300, 1), (300, 5)])
+def test_knn_l2_many_tight_clusters(gpu, po, n_clusters, k, knn_path):
+    """several tight object clusters far apart (radius ~1e-2 at distance ~5 from the DB mean): the ranking
+    value |t'|^2 - 2 q'.t' of both scans is then no more accurate than the neighbour distances themselves, centring on
+    the global mean does not help, and candidates can be lost silently.  The certificate must notice (queries flagged)
+    and the exact re-scan must return the oracle's neighbours - not merely near-ties of them."""
+    rng = np.random.default_rng(100 + n_clusters)
+    per = 40000 // n_clusters
+    centres = rng.standard_normal((n_clusters, 16))
+    centres *= 5.0 / np.linalg.norm(centres, axis=1, keepdims=True)
+    t = (centres[:, None, :] + 0.01 * rng.standard_normal((n_clusters, per, 16))).reshape(-1, 16).astype(np.float32)
+    pick = rng.integers(0, len(t), 400)
+    q = (t[pick] + 0.003 * rng.standard_normal((400, 16))).astype(np.float32)
+    db = gpu.TemplateDB(desc=t)
+    idx, dist = db.knn(q, k)
+    flagged = db.knn_flagged()
+    oi, od, gap = po.knn_l2(q, t, k, want_gap=True)
+    assert check_knn(idx, dist, oi, od, gap, tol=1e-6) < 0.02      # only genuine fp32 ties may differ
+    if n_clusters == 15 and knn_path:      # tensor scan (22-bit products), 2,666 templates per cluster: neighbours closer than the ranking error -> must be noticed
+        assert flagged > 0    # (300 clusters of 133 leave gaps the bound can prove, nothing needs the re-scan)
+    # the same data without the certificate is allowed to be wrong - but a well-spread DB must not be flagged much
+    t2 = rng.standard_normal((40000, 16)).astype(np.float32)
+    q2 = (t2[pick] + 0.1 * rng.standard_normal((400, 16))).astype(np.float32)
+    db2 = gpu.TemplateDB(desc=t2)
+    i2, d2 = db2.knn(q2, k)
+    assert db2.knn_flagged() <= 8
+    o2, od2, g2 = po.knn_l2(q2, t2, k, want_gap=True)
+    assert check_knn(i2, d2, o2, od2, g2) < 0.01
+    gpu.set_option("knn_certify", 0)
+    try:
+        i3, d3 = db2.knn(q2, k)
+        assert db2.knn_flagged() == 0 and np.array_equal(i3, i2) and np.array_equal(d3, d2)
+    finally:
+        gpu.set_option("knn_certify", 1)
+
+
 def test_knn_hamming_matches_oracle_and_golden(gpu, po, synth, golden, knn_path):
     codes_t = (synth.uniform01(synth.BASE_SEED, 50, 512 * 4) * 2 ** 24).astype(np.uint32).reshape(512, 4)
     codes_t = codes_t * np.uint32(257) ^ (codes_t >> np.uint32(3))
@@ -299,7 +343,7 @@ def test_knn_hamming_matches_oracle_and_golden(gpu, po, synth, golden, knn_path)
     assert np.array_equal(idx, oi) and np.array_equal(dist, od)
     rng = np.random.default_rng(2)
     for words, nq, nt, k in ((4, 1100, 30000, 5), (1, 300, 5000, 3), (2, 64, 999, 1), (8, 100, 3000, 4), (4, 5, 3, 4), (4, 700, 40001, 2),
-                             (1, 513, 70000, 5)):
+                             (1, 513, 70000, 5), (4, 300, 20000, 16), (2, 200, 9000, 9)):
         t = rng.integers(0, 2 ** 32, (nt, words), dtype=np.uint64).astype(np.uint32)
         if words == 1:
             t &= np.uint32(0xFFFF)        # 16-bit codes: many equal distances, ties -> lower index
