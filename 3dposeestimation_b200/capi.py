@@ -305,9 +305,12 @@ class Timer:
         return ms.value
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().pe_timer_destroy(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().pe_timer_destroy(self.h)
+                self.h = None
+        except Exception:       # interpreter shutdown
+            pass
 
 
 class Net:

@@ -328,7 +328,8 @@ def gpu_arm(args, rank, world, local_rank, dist):
         rows_max = max(shard_rows(r, world, T)[1] - shard_rows(r, world, T)[0] for r in range(world))
         d_pad = capi.DeviceArray((rows_max, 16), device=dev)
         capi.check(capi.lib().pe_dev_memset(dev, d_pad.ptr, 0, d_pad.nbytes))
-        capi.check(capi.lib().pe_memcpy_h2d(dev, d_pad.ptr, d_db.to_host().ctypes.data, d_db.nbytes))
+        shard_host = d_db.to_host()               # keep the array alive across the C call
+        capi.check(capi.lib().pe_memcpy_h2d(dev, d_pad.ptr, shard_host.ctypes.data, shard_host.nbytes))
         d_gather = capi.DeviceArray((world * rows_max, 16), device=dev)
         comm.allgather_f32_dev(net, d_pad, rows_max * 16, d_gather)
         net.sync()

@@ -87,12 +87,25 @@ def main():
                              poses_per_object=cfg["poses"], device=dev)
     db.share_stream(net)
     qp = cfg["q_poses"] or cfg["poses"]
-    net.synth_patches_dev(SEED + 1, rank * B, B, qp, d_in)                       # this rank's query patches
     q_labels = None
-    if cfg["hist"]:     # query poses = template poses of the same class perturbed by <= 15 degrees
-        ids = np.arange(B * world)                          # the whole query set on every rank: identical at every N
-        src = (ids // qp) * cfg["poses"] + ((ids % qp) * 7) % cfg["poses"]
-        q_labels = np.ascontiguousarray(synth.perturb_labels(labels[src], SEED + 1)[rank * B:(rank + 1) * B])
+    if cfg["hist"]:
+        # evaluation queries (configs 1 and 5): query g of class c = g // qp is the patch of template pose g % qp of that class
+        # (so its nearest template is known: random-weight descriptors of *other* patches of a class do not land in that
+        # class), its pose label that template's pose rotated by up to 45 degrees: the histogram then spreads over all bins.
+        # The whole query set is defined by global ids, so it is identical at every N.
+        assert B % qp == 0 or qp % B == 0 or True
+        g0 = rank * B
+        g = g0
+        while g < g0 + B:
+            c, j = divmod(g, qp)
+            run = min(qp - j, g0 + B - g)
+            net.synth_patches_dev(SEED, c * cfg["poses"] + j, run, cfg["poses"], d_in, out_offset=g - g0)
+            g += run
+        ids = np.arange(B * world)
+        src = (ids // qp) * cfg["poses"] + (ids % qp)
+        q_labels = np.ascontiguousarray(synth.perturb_labels(labels[src], SEED + 1, max_deg=45.0)[rank * B:(rank + 1) * B])
+    else:
+        net.synth_patches_dev(SEED + 1, rank * B, B, qp, d_in)                   # this rank's query patches
     nq_all = B * world
     d_desc = capi.DeviceArray((B, D), device=dev)
     d_all = capi.DeviceArray((nq_all, D), device=dev) if world > 1 else d_desc
@@ -147,7 +160,8 @@ def main():
         rot_inv = synth.rot_inv_pattern(cfg["n_obj"])                    # 80 % / 10 % / 10 % as config.ini:10
         d_ql = capi.DeviceArray.from_host(q_labels, device=dev)
         d_own = capi.DeviceArray((B, K), np.int32, device=dev)
-        capi.check(capi.lib().pe_memcpy_h2d(dev, d_own.ptr, np.ascontiguousarray(d_idx.to_host()[rank * B:(rank + 1) * B]).ctypes.data, B * K * 4))
+        own_idx = np.ascontiguousarray(d_idx.to_host()[rank * B:(rank + 1) * B])      # kept alive across the C call
+        capi.check(capi.lib().pe_memcpy_h2d(dev, d_own.ptr, own_idx.ctypes.data, own_idx.nbytes))
         net.sync()
         t = capi.Timer(dev)
         t.start(db)
