@@ -141,6 +141,14 @@ SIGNATURES = {
     "pe_miner_flags": (C.c_int, [vp, C.c_int, vp]),
     "pe_sphere_views": (C.c_int, [C.c_int, vp, vp, C.c_int, vp, C.c_int64, C.POINTER(C.c_int64)]),
     "pe_render_views": (C.c_int, [C.c_int, vp, vp, C.c_int, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, vp]),
+    "pe_render_views_tex": (C.c_int, [C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float,
+                                      C.c_float, vp, vp]),
+    "pe_render_views_tex_dev": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int,
+                                          C.c_float, C.c_float, vp, vp]),
+    "pe_mesh_load_ply": (C.c_int, [C.c_char_p, C.POINTER(vp)]),
+    "pe_mesh_info": (C.c_int, [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), fp]),
+    "pe_mesh_data": (C.c_int, [vp, vp, vp, vp, vp]),
+    "pe_mesh_destroy": (None, [vp]),
     "pe_render_views_dev": (C.c_int, [vp, C.c_int, vp, vp, C.c_int, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
                                       vp, vp]),
 }
@@ -754,6 +762,36 @@ def render_views(vertices, colors, faces, cam4, poses, rows=480, cols=640, z_nea
     check(lib().pe_render_views(device, _ptr(v), _ptr(c), v.shape[0], _ptr(f), f.shape[0], _ptr(k), _ptr(p), n, rows, cols, z_near, z_far,
                                 _ptr(col), _ptr(dep)))
     return col, dep
+
+
+def render_views_tex(vertices, colors, uv, faces, tex, cam4, poses, rows=480, cols=640, z_near=0.001, z_far=4.0, device=0):
+    """textured mesh: uv [nv, 2], tex [th, tw, 3] BGR u8 (pe_render_views_tex)"""
+    v, c, t, f = _f32(vertices), _f32(colors), _f32(uv), _i32(faces)
+    w = np.ascontiguousarray(tex, np.uint8)
+    k, p = _f32(cam4), _f32(poses).reshape(-1, 12)
+    n = p.shape[0]
+    col = np.empty((n, rows, cols, 3), np.uint8)
+    dep = np.empty((n, rows, cols), np.float32)
+    check(lib().pe_render_views_tex(device, _ptr(v), _ptr(c), _ptr(t), v.shape[0], _ptr(f), f.shape[0], _ptr(w), w.shape[0], w.shape[1],
+                                    _ptr(k), _ptr(p), n, rows, cols, z_near, z_far, _ptr(col), _ptr(dep)))
+    return col, dep
+
+
+def load_ply(path):
+    """Model::loadModel: dict(vertices [nv, 3], colors [nv, 3] in [0, 1], uv [nv, 2] or None, faces [nf, 3], centroid [3])"""
+    h = vp()
+    check(lib().pe_mesh_load_ply(str(path).encode(), C.byref(h)))
+    try:
+        nv, nf, hc, hu = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        cen = np.zeros(3, np.float32)
+        check(lib().pe_mesh_info(h, C.byref(nv), C.byref(nf), C.byref(hc), C.byref(hu), cen.ctypes.data_as(fp)))
+        v, c = np.empty((nv.value, 3), np.float32), np.empty((nv.value, 3), np.float32)
+        uv = np.empty((nv.value, 2), np.float32) if hu.value else None
+        f = np.empty((nf.value, 3), np.int32)
+        check(lib().pe_mesh_data(h, _ptr(v), _ptr(c), _ptr(uv) if uv is not None else None, _ptr(f)))
+        return dict(vertices=v, colors=c, uv=uv, faces=f, centroid=cen, has_colors=bool(hc.value))
+    finally:
+        lib().pe_mesh_destroy(h)
 
 
 def render_views_dev(net, d_vertices, d_colors, n_vertices, d_faces, n_faces, cam4, d_poses, n_views, rows, cols, d_color, d_depth,

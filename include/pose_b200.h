@@ -277,12 +277,37 @@ PE_API int pe_sphere_views(int sphere_depth, const float* scale3, const float* r
  * [n_vertices][3] RGB in [0,1], faces [n_faces][3], cam4 = {fx, fy, ox, oy}, z_near / z_far (0.001 / 4.0 in the
  * reference) -> out_color [n_views][rows][cols][3] u8 BGR (black background), out_depth [n_views][rows][cols] f32
  * metres (0 = background): the frame layout pe_sample_patches reads.  OpenGL itself is unavailable on this box. */
+/* (a triangle that crosses the near plane is clipped at Zc = z_near, not dropped) */
 PE_API int pe_render_views(int device, const float* vertices, const float* colors, int n_vertices, const int32_t* faces,
                            int n_faces, const float* cam4, const float* poses, int n_views, int rows, int cols,
                            float z_near, float z_far, uint8_t* out_color, float* out_depth);
 PE_API int pe_render_views_dev(pe_net* net, int device, const float* d_vertices, const float* d_colors, int n_vertices,
                                const int32_t* d_faces, int n_faces, const float* cam4, const float* d_poses, int n_views,
                                int rows, int cols, float z_near, float z_far, uint8_t* d_out_color, float* d_out_depth);
+
+/* The same for a TEXTURED mesh (BigBIRD models; reference src/model.cpp:330-350, src/painter.cpp:140-160): uv [n_vertices][2]
+ * per-vertex texture coordinates, tex [tex_rows][tex_cols][3] u8 BGR in the row order glTexImage2D receives it (t = 0 at
+ * row 0; the reference flips, shrinks by 6 and brightens the PNG on the host before the upload - that preparation stays
+ * with the caller).  Fixed-function semantics: fragment = vertex colour x texel (GL_MODULATE), GL_REPEAT, GL_LINEAR on
+ * level 0.  uv and tex are both null for an untextured mesh (= pe_render_views).  Triangles that cross the near plane are
+ * clipped at Zc = z_near, as GL clips them. */
+PE_API int pe_render_views_tex(int device, const float* vertices, const float* colors, const float* uv, int n_vertices,
+                               const int32_t* faces, int n_faces, const uint8_t* tex, int tex_rows, int tex_cols, const float* cam4,
+                               const float* poses, int n_views, int rows, int cols, float z_near, float z_far, uint8_t* out_color,
+                               float* out_depth);
+PE_API int pe_render_views_tex_dev(pe_net* net, int device, const float* d_vertices, const float* d_colors, const float* d_uv,
+                                   int n_vertices, const int32_t* d_faces, int n_faces, const uint8_t* d_tex, int tex_rows,
+                                   int tex_cols, const float* cam4, const float* d_poses, int n_views, int rows, int cols,
+                                   float z_near, float z_far, uint8_t* d_out_color, float* d_out_depth);
+/* Model::loadModel (reference src/model.cpp:296-352, there through cv::viz::Mesh::load) as a minimal PLY reader on the
+ * host: ascii / binary_little_endian, triangles only (the reference asserts that, :318), per-vertex colours (uchar / 255;
+ * 127 grey when absent, :325) and texture coordinates (u v | s t | texture_u texture_v).  pe_mesh_data copies into
+ * caller arrays sized by pe_mesh_info (uv only when has_uv; any pointer may be null). */
+typedef struct pe_mesh pe_mesh;
+PE_API int pe_mesh_load_ply(const char* path, pe_mesh** out);
+PE_API int pe_mesh_info(const pe_mesh* mesh, int* n_vertices, int* n_faces, int* has_colors, int* has_uv, float* centroid3);
+PE_API int pe_mesh_data(const pe_mesh* mesh, float* vertices, float* colors, float* uv, int32_t* faces);
+PE_API void pe_mesh_destroy(pe_mesh* mesh);
 
 /* ------------------------------------------------ on-disk sample sets --- */
 /* hdf5Handler::write / read (reference src/hdf5handler.cpp:11-132) without HDF5: one flat little-endian file holding

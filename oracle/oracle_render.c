@@ -17,8 +17,9 @@
  * is affine in 1/Zc, which convertZBufferToDepth maps back to Zc.  Rasterisation as GPUs do it: vertices snapped to 1/256
  * pixel, exact integer edge functions at pixel centres, top-left style tie rule (each shared edge belongs to exactly one
  * triangle), screen-space barycentrics, 1/Z interpolated linearly (= GL's window depth), colour perspective-correct,
- * round-to-nearest to 8 bits.  Not restated: the 24-bit quantisation of GL's depth buffer (<= 0.06 mm at 1 m with
- * near 0.001 / far 4.0), near-plane clipping (a triangle with a vertex at Zc <= near is dropped), textures.
+ * round-to-nearest to 8 bits; triangles that cross the near plane are clipped; textured meshes (BigBIRD) modulate the
+ * vertex colour with a bilinear GL_REPEAT texture fetch.  Not restated: the 24-bit quantisation of GL's depth buffer
+ * (<= 0.06 mm at 1 m with near 0.001 / far 4.0) and the fixed-point weights of a hardware texture unit.
  */
 #include <math.h>
 #include <stdint.h>
@@ -120,76 +121,155 @@ static int owns_edge(int64_t ax, int64_t ay, int64_t bx, int64_t by) {
 }
 
 /* vertices [nv][3], colors [nv][3] RGB in [0,1], faces [nf][3]; cam = {fx, fy, ox, oy}; rt = row-major 3x4;
- * out_color [rows][cols][3] BGR u8, out_depth [rows][cols] f32 metres (0 = background) */
-void orc_render(const float* vertices, const float* colors, int nv, const int32_t* faces, int nf, const float* cam,
-                const float* rt, int rows, int cols, float z_near, float z_far, uint8_t* out_color, float* out_depth) {
-    float* sx = (float*)malloc(sizeof(float) * (size_t)nv * 3);
-    int32_t* fx_ = (int32_t*)malloc(sizeof(int32_t) * (size_t)nv * 2);
+ * out_color [rows][cols][3] BGR u8, out_depth [rows][cols] f32 metres (0 = background).
+ * uv [nv][2] + tex [tex_rows][tex_cols][3] BGR u8 (both or neither): GL_TEXTURE_2D with the fixed-function default
+ * GL_MODULATE (fragment = vertex colour x texel), GL_REPEAT wrap, GL_LINEAR filtering of level 0, the image rows in
+ * the order glTexImage2D receives them (t = 0 at row 0), as Model::loadModel / bindVBOs set it up
+ * (src/model.cpp:330-350, src/painter.cpp:140-160).
+ * Near-plane clipping (GL clips every primitive against the frustum; the reference's near is 0.001, src/painter.cpp:9):
+ * a triangle with vertices on both sides of Zc = z_near is cut by Sutherland-Hodgman in camera space, every cut point
+ * computed from the inside vertex towards the outside one (so both triangles at a shared edge get the same point),
+ * attributes interpolated with the same parameter; a quad is split as a fan from its first vertex.  The side and far
+ * planes need no geometry: coverage is clamped to the frame and z < z_far is tested per fragment. */
+typedef struct { int32_t x, y; float z; int i0, i1; float t; } cvert;
+
+static void project_snap(const float* cam, float xc, float yc, float zc, int32_t* px, int32_t* py) {
+    const float u = (cam[0] * xc + cam[2] * zc) / zc, v = (cam[1] * yc + cam[3] * zc) / zc;
+    /* snap to 1/256 pixel; clamp far-off vertices so that the integer edge functions cannot overflow */
+    float us = u * 256.f, vs = v * 256.f;
+    const float lim = 1048576.f * 256.f;
+    if (us > lim) us = lim;
+    if (us < -lim) us = -lim;
+    if (vs > lim) vs = lim;
+    if (vs < -lim) vs = -lim;
+    *px = (int32_t)floorf(us + 0.5f);
+    *py = (int32_t)floorf(vs + 0.5f);
+}
+
+static float attr_at(const float* a, int stride, int ch, const cvert* v) {
+    const float a0 = a[stride * v->i0 + ch];
+    if (v->i0 == v->i1) return a0;
+    return a0 + v->t * (a[stride * v->i1 + ch] - a0);
+}
+
+/* GL_LINEAR, GL_REPEAT: texel centres at (i + 0.5) / size */
+static float tex_bilinear(const uint8_t* tex, int th, int tw, float s, float t, int ch_rgb) {
+    const float fu = s * (float)tw - 0.5f, fv = t * (float)th - 0.5f;
+    const float x0f = floorf(fu), y0f = floorf(fv);
+    const float ax = fu - x0f, ay = fv - y0f;
+    int x0 = (int)fmodf(x0f, (float)tw), y0 = (int)fmodf(y0f, (float)th);
+    if (x0 < 0) x0 += tw;
+    if (y0 < 0) y0 += th;
+    const int x1 = x0 + 1 == tw ? 0 : x0 + 1, y1 = y0 + 1 == th ? 0 : y0 + 1;
+    const int c = 2 - ch_rgb;                                     /* the image is BGR */
+    const float t00 = tex[((size_t)y0 * tw + x0) * 3 + c], t10 = tex[((size_t)y0 * tw + x1) * 3 + c];
+    const float t01 = tex[((size_t)y1 * tw + x0) * 3 + c], t11 = tex[((size_t)y1 * tw + x1) * 3 + c];
+    const float top = t00 + ax * (t10 - t00), bot = t01 + ax * (t11 - t01);
+    return (top + ay * (bot - top)) / 255.f;
+}
+
+void orc_render_tex(const float* vertices, const float* colors, const float* uv, int nv, const int32_t* faces, int nf,
+                    const uint8_t* tex, int tex_rows, int tex_cols, const float* cam, const float* rt, int rows, int cols,
+                    float z_near, float z_far, uint8_t* out_color, float* out_depth) {
+    float* cc = (float*)malloc(sizeof(float) * (size_t)(nv > 0 ? nv : 1) * 3);       /* camera-space points */
+    int32_t* fx_ = (int32_t*)malloc(sizeof(int32_t) * (size_t)(nv > 0 ? nv : 1) * 2);
+    const int textured = uv && tex && tex_rows > 0 && tex_cols > 0;
     for (int i = 0; i < nv; ++i) {
         const float x = vertices[3 * i], y = vertices[3 * i + 1], z = vertices[3 * i + 2];
         const float xc = rt[0] * x + rt[1] * y + rt[2] * z + rt[3];
         const float yc = rt[4] * x + rt[5] * y + rt[6] * z + rt[7];
         const float zc = rt[8] * x + rt[9] * y + rt[10] * z + rt[11];
-        sx[3 * i + 2] = zc;
-        if (zc > z_near) {
-            const float u = (cam[0] * xc + cam[2] * zc) / zc, v = (cam[1] * yc + cam[3] * zc) / zc;
-            sx[3 * i] = u; sx[3 * i + 1] = v;
-            /* snap to 1/256 pixel; clamp far-off vertices so that the integer edge functions cannot overflow */
-            float us = u * 256.f, vs = v * 256.f;
-            const float lim = 1048576.f * 256.f;
-            if (us > lim) us = lim; if (us < -lim) us = -lim;
-            if (vs > lim) vs = lim; if (vs < -lim) vs = -lim;
-            fx_[2 * i] = (int32_t)floorf(us + 0.5f);
-            fx_[2 * i + 1] = (int32_t)floorf(vs + 0.5f);
-        }
+        cc[3 * i] = xc; cc[3 * i + 1] = yc; cc[3 * i + 2] = zc;
+        fx_[2 * i] = fx_[2 * i + 1] = 0;
+        if (zc > z_near) project_snap(cam, xc, yc, zc, &fx_[2 * i], &fx_[2 * i + 1]);
     }
     memset(out_color, 0, (size_t)rows * cols * 3);
     for (size_t i = 0; i < (size_t)rows * cols; ++i) out_depth[i] = INFINITY;
     for (int f = 0; f < nf; ++f) {
-        int ia = faces[3 * f], ib = faces[3 * f + 1], ic = faces[3 * f + 2];
-        if (ia < 0 || ib < 0 || ic < 0 || ia >= nv || ib >= nv || ic >= nv) continue;
-        if (!(sx[3 * ia + 2] > z_near) || !(sx[3 * ib + 2] > z_near) || !(sx[3 * ic + 2] > z_near)) continue;
-        int64_t ax = fx_[2 * ia], ay = fx_[2 * ia + 1], bx = fx_[2 * ib], by = fx_[2 * ib + 1], cx = fx_[2 * ic], cy = fx_[2 * ic + 1];
-        int64_t area = edge(ax, ay, bx, by, cx, cy);
-        if (area == 0) continue;
-        if (area < 0) {      /* no culling (src/model.cpp:29-54): flip to positive orientation */
-            int t = ib; ib = ic; ic = t;
-            int64_t tx = bx, ty = by; bx = cx; by = cy; cx = tx; cy = ty;
-            area = -area;
-        }
-        int64_t minx = ax < bx ? ax : bx, maxx = ax > bx ? ax : bx, miny = ay < by ? ay : by, maxy = ay > by ? ay : by;
-        if (cx < minx) minx = cx; if (cx > maxx) maxx = cx; if (cy < miny) miny = cy; if (cy > maxy) maxy = cy;
-        /* pixel px has its centre at 256 px + 128 */
-        int x0 = (int)((minx - 128 + 255) >> 8), x1 = (int)((maxx - 128) >> 8), y0 = (int)((miny - 128 + 255) >> 8), y1 = (int)((maxy - 128) >> 8);
-        if (x0 < 0) x0 = 0; if (y0 < 0) y0 = 0; if (x1 > cols - 1) x1 = cols - 1; if (y1 > rows - 1) y1 = rows - 1;
-        const int oa = owns_edge(bx, by, cx, cy), ob = owns_edge(cx, cy, ax, ay), oc = owns_edge(ax, ay, bx, by);
-        const float iza = 1.f / sx[3 * ia + 2], izb = 1.f / sx[3 * ib + 2], izc = 1.f / sx[3 * ic + 2];
-        const float farea = (float)area;
-        for (int py = y0; py <= y1; ++py)
-            for (int px = x0; px <= x1; ++px) {
-                const int64_t qx = 256 * (int64_t)px + 128, qy = 256 * (int64_t)py + 128;
-                const int64_t wa = edge(bx, by, cx, cy, qx, qy), wb = edge(cx, cy, ax, ay, qx, qy), wc = edge(ax, ay, bx, by, qx, qy);
-                if (wa < 0 || wb < 0 || wc < 0) continue;
-                if ((wa == 0 && !oa) || (wb == 0 && !ob) || (wc == 0 && !oc)) continue;
-                const float ba = (float)wa / farea, bb = (float)wb / farea, bc = (float)wc / farea;
-                const float iz = ba * iza + bb * izb + bc * izc;
-                const float z = 1.f / iz;
-                if (!(z > z_near) || !(z < z_far)) continue;
-                float* dp = out_depth + (size_t)py * cols + px;
-                if (!(z < *dp)) continue;          /* GL_LESS: the first drawn fragment keeps an equal depth */
-                *dp = z;
-                uint8_t* cp = out_color + ((size_t)py * cols + px) * 3;
-                for (int ch = 0; ch < 3; ++ch) {
-                    const float c = (ba * (colors[3 * ia + ch] * iza) + bb * (colors[3 * ib + ch] * izb) + bc * (colors[3 * ic + ch] * izc)) / iz;
-                    float q = c * 255.f + 0.5f;
-                    if (q < 0.f) q = 0.f;
-                    if (q > 255.f) q = 255.f;
-                    cp[2 - ch] = (uint8_t)q;        /* BGR read-back */
-                }
+        const int idx[3] = {faces[3 * f], faces[3 * f + 1], faces[3 * f + 2]};
+        if (idx[0] < 0 || idx[1] < 0 || idx[2] < 0 || idx[0] >= nv || idx[1] >= nv || idx[2] >= nv) continue;
+        /* ---- clip against Zc = z_near (a vertex exactly on the plane counts as outside) */
+        cvert poly[4];
+        int np_ = 0;
+        const int in[3] = {cc[3 * idx[0] + 2] > z_near, cc[3 * idx[1] + 2] > z_near, cc[3 * idx[2] + 2] > z_near};
+        if (!in[0] && !in[1] && !in[2]) continue;
+        for (int e = 0; e < 3; ++e) {
+            const int p = e, q = (e + 1) % 3;
+            if (in[p]) {
+                cvert v = {fx_[2 * idx[p]], fx_[2 * idx[p] + 1], cc[3 * idx[p] + 2], idx[p], idx[p], 0.f};
+                poly[np_++] = v;
             }
+            if (in[p] != in[q]) {
+                const int a = in[p] ? idx[p] : idx[q], b = in[p] ? idx[q] : idx[p];      /* a inside, b outside */
+                const float t = (cc[3 * a + 2] - z_near) / (cc[3 * a + 2] - cc[3 * b + 2]);
+                const float xc = cc[3 * a] + t * (cc[3 * b] - cc[3 * a]), yc = cc[3 * a + 1] + t * (cc[3 * b + 1] - cc[3 * a + 1]);
+                cvert v = {0, 0, z_near, a, b, t};
+                project_snap(cam, xc, yc, z_near, &v.x, &v.y);
+                poly[np_++] = v;
+            }
+        }
+        for (int sub = 0; sub + 2 < np_; ++sub) {
+            cvert va = poly[0], vb = poly[sub + 1], vc = poly[sub + 2];
+            int64_t ax = va.x, ay = va.y, bx = vb.x, by = vb.y, cx = vc.x, cy = vc.y;
+            int64_t area = edge(ax, ay, bx, by, cx, cy);
+            if (area == 0) continue;
+            if (area < 0) {      /* no culling (src/model.cpp:29-54): flip to positive orientation */
+                cvert tv = vb; vb = vc; vc = tv;
+                int64_t tx = bx, ty = by; bx = cx; by = cy; cx = tx; cy = ty;
+                area = -area;
+            }
+            int64_t minx = ax < bx ? ax : bx, maxx = ax > bx ? ax : bx, miny = ay < by ? ay : by, maxy = ay > by ? ay : by;
+            if (cx < minx) minx = cx;
+            if (cx > maxx) maxx = cx;
+            if (cy < miny) miny = cy;
+            if (cy > maxy) maxy = cy;
+            /* pixel px has its centre at 256 px + 128 */
+            int x0 = (int)((minx - 128 + 255) >> 8), x1 = (int)((maxx - 128) >> 8), y0 = (int)((miny - 128 + 255) >> 8), y1 = (int)((maxy - 128) >> 8);
+            if (x0 < 0) x0 = 0;
+            if (y0 < 0) y0 = 0;
+            if (x1 > cols - 1) x1 = cols - 1;
+            if (y1 > rows - 1) y1 = rows - 1;
+            const int oa = owns_edge(bx, by, cx, cy), ob = owns_edge(cx, cy, ax, ay), oc = owns_edge(ax, ay, bx, by);
+            const float iza = 1.f / va.z, izb = 1.f / vb.z, izc = 1.f / vc.z;
+            const float farea = (float)area;
+            for (int py = y0; py <= y1; ++py)
+                for (int px = x0; px <= x1; ++px) {
+                    const int64_t qx = 256 * (int64_t)px + 128, qy = 256 * (int64_t)py + 128;
+                    const int64_t wa = edge(bx, by, cx, cy, qx, qy), wb = edge(cx, cy, ax, ay, qx, qy), wc = edge(ax, ay, bx, by, qx, qy);
+                    if (wa < 0 || wb < 0 || wc < 0) continue;
+                    if ((wa == 0 && !oa) || (wb == 0 && !ob) || (wc == 0 && !oc)) continue;
+                    const float ba = (float)wa / farea, bb = (float)wb / farea, bc = (float)wc / farea;
+                    const float iz = ba * iza + bb * izb + bc * izc;
+                    const float z = 1.f / iz;
+                    if (!(z > z_near) || !(z < z_far)) continue;
+                    float* dp = out_depth + (size_t)py * cols + px;
+                    if (!(z < *dp)) continue;          /* GL_LESS: the first drawn fragment keeps an equal depth */
+                    *dp = z;
+                    uint8_t* cp = out_color + ((size_t)py * cols + px) * 3;
+                    float s = 0.f, t = 0.f;
+                    if (textured) {
+                        s = (ba * (attr_at(uv, 2, 0, &va) * iza) + bb * (attr_at(uv, 2, 0, &vb) * izb) + bc * (attr_at(uv, 2, 0, &vc) * izc)) / iz;
+                        t = (ba * (attr_at(uv, 2, 1, &va) * iza) + bb * (attr_at(uv, 2, 1, &vb) * izb) + bc * (attr_at(uv, 2, 1, &vc) * izc)) / iz;
+                    }
+                    for (int ch = 0; ch < 3; ++ch) {
+                        float c = (ba * (attr_at(colors, 3, ch, &va) * iza) + bb * (attr_at(colors, 3, ch, &vb) * izb) +
+                                   bc * (attr_at(colors, 3, ch, &vc) * izc)) / iz;
+                        if (textured) c = c * tex_bilinear(tex, tex_rows, tex_cols, s, t, ch);      /* GL_MODULATE */
+                        float q = c * 255.f + 0.5f;
+                        if (q < 0.f) q = 0.f;
+                        if (q > 255.f) q = 255.f;
+                        cp[2 - ch] = (uint8_t)q;        /* BGR read-back */
+                    }
+                }
+        }
     }
     for (size_t i = 0; i < (size_t)rows * cols; ++i)
         if (out_depth[i] == INFINITY) out_depth[i] = 0.f;
-    free(sx);
+    free(cc);
     free(fx_);
+}
+
+void orc_render(const float* vertices, const float* colors, int nv, const int32_t* faces, int nf, const float* cam,
+                const float* rt, int rows, int cols, float z_near, float z_far, uint8_t* out_color, float* out_depth) {
+    orc_render_tex(vertices, colors, 0, nv, faces, nf, 0, 0, 0, cam, rt, rows, cols, z_near, z_far, out_color, out_depth);
 }

@@ -89,6 +89,9 @@ def lib():
         L.orc_view_pose.restype = None
         L.orc_view_pose.argtypes = [fp, C.c_float, C.c_float, fp]
         L.orc_render.restype = None
+        L.orc_render_tex.argtypes = [fp, fp, fp, C.c_int, ip, C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_int, fp, fp, C.c_int, C.c_int,
+                                     C.c_float, C.c_float, C.POINTER(C.c_uint8), fp]
+        L.orc_render_tex.restype = None
         L.orc_render.argtypes = [fp, fp, C.c_int, ip, C.c_int, fp, fp, C.c_int, C.c_int, C.c_float, C.c_float, C.POINTER(C.c_uint8), fp]
         i64p = C.POINTER(C.c_int64)
         L.orc_max_sim_tmpl.restype = None
@@ -462,14 +465,21 @@ def sphere_views(depth, scale, rotation, skip_lower_hemi=True):
     return np.stack(poses) if poses else np.zeros((0, 3, 4), np.float32)
 
 
-def render(vertices, colors, faces, cam, rt, rows=480, cols=640, z_near=0.001, z_far=4.0):
-    """Painter::paint with RealWorldCamera + Model -> (BGR u8 [rows, cols, 3], depth f32 [rows, cols], 0 = background)"""
+def render(vertices, colors, faces, cam, rt, rows=480, cols=640, z_near=0.001, z_far=4.0, uv=None, tex=None):
+    """Painter::paint with RealWorldCamera + Model -> (BGR u8 [rows, cols, 3], depth f32 [rows, cols], 0 = background);
+    uv [nv, 2] + tex [th, tw, 3] BGR u8: textured mesh (GL_MODULATE, GL_REPEAT, GL_LINEAR)"""
     v, c, f = _f32(vertices), _f32(colors), _i32(faces)
     k, p = _f32(cam), _f32(rt)
     col = np.empty((rows, cols, 3), np.uint8)
     dep = np.empty((rows, cols), np.float32)
-    lib().orc_render(_p(v, C.c_float), _p(c, C.c_float), v.shape[0], _p(f, C.c_int32), f.shape[0], _p(k, C.c_float), _p(p, C.c_float),
-                     rows, cols, z_near, z_far, _p(col, C.c_uint8), _p(dep, C.c_float))
+    if uv is not None and tex is not None:
+        t, w = _f32(uv), np.ascontiguousarray(tex, np.uint8)
+        lib().orc_render_tex(_p(v, C.c_float), _p(c, C.c_float), _p(t, C.c_float), v.shape[0], _p(f, C.c_int32), f.shape[0],
+                             _p(w, C.c_uint8), w.shape[0], w.shape[1], _p(k, C.c_float), _p(p, C.c_float),
+                             rows, cols, z_near, z_far, _p(col, C.c_uint8), _p(dep, C.c_float))
+    else:
+        lib().orc_render(_p(v, C.c_float), _p(c, C.c_float), v.shape[0], _p(f, C.c_int32), f.shape[0], _p(k, C.c_float), _p(p, C.c_float),
+                         rows, cols, z_near, z_far, _p(col, C.c_uint8), _p(dep, C.c_float))
     return col, dep
 
 

@@ -60,3 +60,23 @@ def cube(half=0.05):
     f = np.array([[0, 1, 3], [0, 3, 2], [4, 6, 7], [4, 7, 5], [0, 4, 5], [0, 5, 1], [2, 3, 7], [2, 7, 6], [0, 2, 6], [0, 6, 4], [1, 5, 7], [1, 7, 3]], np.int32)
     c = (v / (2 * half) + 0.5).astype(np.float32)            # colour = position in the unit cube
     return v, c, f
+
+
+def ground_plane():
+    """a ground plane through the camera's near plane (camera at the origin, identity pose): Y = 0.1, X in [-2, 2],
+    Z from -1 (behind the camera) to 3; vertex colour (Z + 1) / 4 in all channels; two triangles sharing the diagonal"""
+    v = np.array([[-2, 0.1, -1], [2, 0.1, -1], [2, 0.1, 3], [-2, 0.1, 3]], np.float32)
+    c = np.repeat(((v[:, 2:3] + 1) / 4), 3, axis=1).astype(np.float32)
+    f = np.array([[0, 1, 2], [0, 2, 3]], np.int32)
+    return v, c, f
+
+
+def textured_quad(seed=5, th=37, tw=53):
+    """fronto-parallel quad at Z = 1 covering the frame, uv running past [0, 1] (GL_REPEAT), random BGR texture"""
+    rng = np.random.default_rng(seed)
+    v = np.array([[-0.7, -0.5, 1], [0.7, -0.5, 1], [0.7, 0.5, 1], [-0.7, 0.5, 1]], np.float32)
+    uv = np.array([[-0.3, -0.2], [1.6, -0.2], [1.6, 1.4], [-0.3, 1.4]], np.float32)
+    c = np.array([[1, 1, 1], [1, 0.5, 1], [0.25, 1, 1], [1, 1, 0.5]], np.float32)
+    f = np.array([[0, 1, 2], [0, 2, 3]], np.int32)
+    tex = rng.integers(0, 256, (th, tw, 3)).astype(np.uint8)
+    return v, c, uv, f, tex

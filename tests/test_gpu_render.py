@@ -76,3 +76,53 @@ def test_views_to_descriptors_on_device(gpu, po, synth):
     # distinct views give distinct descriptors
     dd = d_desc.to_host()
     assert len(np.unique(np.round(dd, 4), axis=0)) == n
+
+
+def test_near_plane_clipping_bit_exact_vs_oracle(gpu, po):
+    """triangles through the near plane are clipped, not dropped: the analytic ground-plane scene of
+    tests/test_render_oracle.py and a mesh the camera sits inside, CUDA == oracle bit for bit"""
+    v, c, f = scenes.ground_plane()
+    rt = np.zeros((1, 3, 4), np.float32)
+    rt[0, :, :3] = np.eye(3)
+    gc, gd = gpu.render_views(v, c, f, CAM, rt, z_near=0.3, z_far=4.0)
+    oc, od = po.render(v, c, f, CAM, rt[0], z_near=0.3, z_far=4.0)
+    assert np.array_equal(gd[0], od) and np.array_equal(gc[0], oc) and (od > 0).sum() > 100000
+    # camera inside a bumpy sphere: most triangles straddle or lie behind the near plane somewhere
+    sv, sf = scenes.icosphere(3, 0.5)
+    sc = (sv + 0.5).astype(np.float32)
+    poses = po.sphere_views(0, (0.05, 0.2, 0.45), (0, 90, 90))[::5]
+    g2c, g2d = gpu.render_views(sv, sc, sf, CAM, poses, z_near=0.2, z_far=4.0)
+    for i, p in enumerate(poses):
+        oc, od = po.render(sv, sc, sf, CAM, p, z_near=0.2, z_far=4.0)
+        assert np.array_equal(g2d[i], od) and np.array_equal(g2c[i], oc), i
+    assert (g2d > 0).mean() > 0.5
+
+
+def test_textured_mesh_bit_exact_vs_oracle(gpu, po, tmp_path):
+    """per-vertex uv + BGR texture, GL_MODULATE / GL_REPEAT / GL_LINEAR (reference src/model.cpp:330-350,
+    src/painter.cpp:140-160): the analytic quad and a textured blob loaded through the PLY reader"""
+    v, c, uv, f, tex = scenes.textured_quad()
+    rt = np.zeros((1, 3, 4), np.float32)
+    rt[0, :, :3] = np.eye(3)
+    gc, gd = gpu.render_views_tex(v, c, uv, f, tex, CAM, rt)
+    oc, od = po.render(v, c, f, CAM, rt[0], uv=uv, tex=tex)
+    assert np.array_equal(gd[0], od) and np.array_equal(gc[0], oc)
+    from tests.test_formats_cpu import _write_ply
+    rng = np.random.default_rng(9)
+    bv, bf = scenes.icosphere(3, 0.09)
+    buv = (np.stack([np.arctan2(bv[:, 1], bv[:, 0]) / np.pi, bv[:, 2] / 0.09], 1) * 1.5).astype(np.float32)
+    _write_ply(tmp_path / "blob.ply", bv, bf, rng.integers(60, 256, (len(bv), 3)), buv, binary=True)
+    m = gpu.load_ply(tmp_path / "blob.ply")
+    big = rng.integers(0, 256, (64, 96, 3)).astype(np.uint8)
+    poses = po.sphere_views(1, (0.4, 0.3, 0.7), (-30, 60, 30))[::11]
+    gc, gd = gpu.render_views_tex(m["vertices"], m["colors"], m["uv"], m["faces"], big, CAM, poses)
+    for i, p in enumerate(poses):
+        oc, od = po.render(m["vertices"], m["colors"], m["faces"], CAM, p, uv=m["uv"], tex=big)
+        assert np.array_equal(gd[i], od) and np.array_equal(gc[i], oc), i
+    plain = gpu.render_views(m["vertices"], m["colors"], m["faces"], CAM, poses[:1])[0]
+    assert not np.array_equal(plain[0], gc[0])
+    with pytest.raises(gpu.PoseError):      # uv without a texture
+        gpu.lib().pe_render_views_tex  # symbol exists
+        gpu.check(gpu.lib().pe_render_views_tex(0, m["vertices"].ctypes.data, m["colors"].ctypes.data, m["uv"].ctypes.data, len(m["vertices"]),
+                                                m["faces"].ctypes.data, len(m["faces"]), None, 0, 0, CAM.ctypes.data, poses.ctypes.data, 1, 480, 640,
+                                                0.001, 4.0, plain.ctypes.data, gd.ctypes.data))

@@ -105,3 +105,74 @@ def test_sphere_depth_matches_ray_casting(po):
     assert np.abs(dep[core] - z[core]).max() < 4e-4      # facet sag of a level-4 icosphere of radius 0.1 (~0.2 mm)
     assert np.all(dep[~hit & (disc < -0.02 * disc.max())] == 0)
     assert np.all(col[core] == 128)                     # 0.5 * 255 + 0.5 -> 128
+
+
+def test_near_plane_clipping_of_a_ground_plane(po):
+    """triangles with vertices behind the camera are clipped at Zc = near, not dropped (GL clips every primitive;
+    reference near plane src/painter.cpp:9): depth and perspective-correct colour of the visible part are the analytic
+    plane's, rows whose plane depth is below near stay empty, the shared (clipped) diagonal leaves no crack"""
+    v, c, f = scenes.ground_plane()
+    near, far = 0.3, 4.0
+    col, dep = po.render(v, c, f, CAM, eye_pose(0.0), z_near=near, z_far=far)
+    fy, oy = float(CAM[1]), float(CAM[3])
+    py = np.arange(480) + 0.5
+    with np.errstate(divide="ignore"):
+        z_row = np.where(py > oy, 0.1 * fy / (py - oy), np.inf)          # plane depth along image row py
+    visible = (z_row > near * 1.001) & (z_row < 3.0 * 0.999)
+    hidden = (z_row < near * 0.999) | (z_row > 3.0 * 1.001)
+    assert visible.sum() > 150 and (hidden & (py > oy)).sum() > 40
+    assert np.all(dep[hidden] == 0)
+    band = dep[visible]
+    assert np.all(band > 0), "a crack along the clipped diagonal or a dropped triangle"
+    np.testing.assert_allclose(band, np.repeat(z_row[visible][:, None], 640, 1), rtol=2e-4)
+    want_c = np.round(255 * (z_row[visible] + 1) / 4)
+    assert np.abs(col[visible][:, :, 0].astype(np.float64) - want_c[:, None]).max() <= 1.0
+    # a triangle entirely in front of the near plane is untouched by the clipper
+    v2 = v.copy(); v2[:, 2] = np.array([0.5, 0.5, 3, 3], np.float32)
+    a = po.render(v2, c, f, CAM, eye_pose(0.0), z_near=near, z_far=far)
+    b = po.render(v2, c, f, CAM, eye_pose(0.0), z_near=0.001, z_far=far)
+    assert np.array_equal(a[1], b[1]) and np.array_equal(a[0], b[0])
+    # entirely behind: nothing
+    v3 = v.copy(); v3[:, 2] = -np.abs(v3[:, 2]) - 0.1
+    assert not po.render(v3, c, f, CAM, eye_pose(0.0), z_near=near, z_far=far)[1].any()
+
+
+def test_textured_quad_matches_bilinear_repeat_sampling(po):
+    """GL_TEXTURE_2D as Model::loadModel / bindVBOs configure it (src/model.cpp:330-350, src/painter.cpp:140-160):
+    GL_MODULATE with the vertex colour, GL_REPEAT, GL_LINEAR on level 0"""
+    v, c, uv, f, tex = scenes.textured_quad()
+    col, dep = po.render(v, c, f, CAM, eye_pose(0.0), uv=uv, tex=tex)
+    fx, fy, ox, oy = [float(x) for x in CAM]
+    yy, xx = np.mgrid[0:480, 0:640].astype(np.float64)
+    X, Y = (xx + 0.5 - ox) / fx, (yy + 0.5 - oy) / fy               # Z = 1
+    inside = (np.abs(X) < 0.69) & (np.abs(Y) < 0.49)
+    assert np.abs(dep[inside] - 1.0).max() < 1e-6
+    # the quad's attributes are affine in (X, Y) on the plane Z = 1 (both triangles agree: bilinear with no xy term)
+    s = -0.3 + (X + 0.7) / 1.4 * 1.9
+    t = -0.2 + (Y + 0.5) / 1.0 * 1.6
+    th, tw = tex.shape[:2]
+    fu, fv = s * tw - 0.5, t * th - 0.5
+    x0, y0 = np.floor(fu), np.floor(fv)
+    ax, ay = fu - x0, fv - y0
+    x0i, y0i = x0.astype(int) % tw, y0.astype(int) % th
+    x1i, y1i = (x0i + 1) % tw, (y0i + 1) % th
+    texf = tex.astype(np.float64)
+    samp = ((1 - ax) * (1 - ay))[..., None] * texf[y0i, x0i] + (ax * (1 - ay))[..., None] * texf[y0i, x1i] + \
+           ((1 - ax) * ay)[..., None] * texf[y1i, x0i] + (ax * ay)[..., None] * texf[y1i, x1i]      # BGR
+    # vertex colours: corners (1,1,1) (1,.5,1) (.25,1,1) (1,1,.5) - each triangle interpolates its own three corners
+    def tri_colour(i0, i1, i2):
+        a = np.stack([v[[i0, i1, i2], 0], v[[i0, i1, i2], 1], np.ones(3)], 1).astype(np.float64)
+        w = np.linalg.solve(a.T, np.stack([X.ravel(), Y.ravel(), np.ones(X.size)]))
+        return (w.T @ c[[i0, i1, i2]].astype(np.float64)).reshape(480, 640, 3), w.T.reshape(480, 640, 3)
+    c1, w1 = tri_colour(0, 1, 2)
+    c2, w2 = tri_colour(0, 2, 3)
+    in1 = inside & (w1.min(-1) > 0.02)
+    in2 = inside & (w2.min(-1) > 0.02)
+    assert in1.sum() > 50000 and in2.sum() > 50000
+    for m, cc in ((in1, c1), (in2, c2)):
+        want_rgb = cc[m] * samp[m][:, ::-1] / 255.0
+        got_rgb = col[m][:, ::-1].astype(np.float64) / 255.0
+        assert np.abs(got_rgb - want_rgb).max() < 1.5 / 255
+    # without texture coordinates the same mesh renders its vertex colours only
+    plain = po.render(v, c, f, CAM, eye_pose(0.0))[0]
+    assert np.abs(plain[in1][:, ::-1].astype(np.float64) / 255 - c1[in1]).max() < 1.5 / 255
