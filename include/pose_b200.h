@@ -375,7 +375,7 @@ PE_API void pe_comm_destroy(pe_comm* comm);
 PE_API int pe_comm_info(const pe_comm* comm, int* rank, int* world);
 /* *active = 1 when every rank mapped every peer's window (CUDA IPC over NVLink) AND pe_set_option("p2p", 1) selected the
  * peer-memory all-gather (one kernel: push to every peer's window, publish the epoch, wait, copy out) instead of the
- * NCCL call.  Default 0: measured on B200 (tools/p2p_check.py, 262 KB per rank) the kernel takes 15 us at 2 GPUs and
+ * NCCL call.  Default 0: measured on B200 (tests/multigpu_check.py, 262 KB per rank) the kernel takes 15 us at 2 GPUs and
  * 21 us at 8 against 12 and 23 us for ncclAllGather - a tie, so NCCL stays the default.  PE_NO_P2P=1 skips the window
  * set-up.  A peer-window all-gather that timed out waiting for a rank makes the sharded entry point that issued it (or the
  * pe_db_sync that completes it) return PE_ERR_NCCL; so does this call. */

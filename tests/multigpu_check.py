@@ -12,7 +12,7 @@ of the NCCL path"):
 
 Prints one JSON line on rank 0 (kept under profiles/ by tools/gpu_scale.sh) and exits non-zero on a mismatch.
 
-   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/p2p_check.py"""
+   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tests/multigpu_check.py"""
 import importlib, json, os, sys
 import numpy as np
 import torch.distributed as dist

@@ -545,7 +545,7 @@ def test_match_patches_dev_pipeline(gpu, po, synth, knn_path):
 
 def test_sharded_entry_points_degenerate_without_a_communicator(gpu, po, synth):
     """pe_histogram_sharded_dev / pe_confusion_sharded_dev / pe_knn_hamming_sharded_dev with comm == null are the
-    single-rank calls (the multi-rank side: tools/p2p_check.py under torchrun, tests/test_sharding_gloo.py on CPU)"""
+    single-rank calls (the multi-rank side: tests/multigpu_check.py under torchrun, tests/test_sharding_gloo.py on CPU)"""
     n_obj, nr_t, nr_q, k = 6, 40, 15, 3
     q, t, ql, tl = mg.eval_problem(synth.BASE_SEED, n_obj, nr_t, nr_q, 16)
     rot_inv = np.array([0, 0, 1, 0, 2, 0], np.int32)

@@ -110,11 +110,13 @@ def main(argv):
     for name, blobs in layers:
         print(f"{name}: " + ", ".join(f"{tuple(s) if s else (a.size,)}" for a, s in blobs))
     if "--prototxt" in argv:
+        import importlib
         import os
         sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-        from oracle import pyoracle as po        # the prototxt reader only
-        net = po.parse_prototxt(open(argv[argv.index("--prototxt") + 1]).read())
-        want = [int(np.prod(s)) for s in net.blob_shapes]
+        # the library's own prototxt reader through the C ABI (pe_net_create_from_prototxt + pe_net_blob_info; no GPU needed)
+        capi = importlib.import_module("3dposeestimation_b200.capi")
+        net = capi.Net(path=argv[argv.index("--prototxt") + 1])
+        want = [cnt for _, cnt in net.blob_info()]
         got = [a.size for a in arrays]
         if want != got:
             print(f"blob sizes {got} do not match the prototxt's {want}")

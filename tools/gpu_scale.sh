@@ -1,11 +1,11 @@
 #!/bin/bash
-# Runs on an N-GPU box: multi-GPU parity (tools/p2p_check.py), bench.py at N ranks (both arms), BASELINE configs 3, 4, 5, 6
+# Runs on an N-GPU box: multi-GPU parity (tests/multigpu_check.py), bench.py at N ranks (both arms), BASELINE configs 3, 4, 5, 6
 # sharded over N ranks.  Raw JSON lines land in gpurun_out/ (copied to profiles/ for the record).  usage: gpu_scale.sh N [quick]
 cd "$(dirname "$0")/.."
 N=$1; QUICK=${2:-}; O=gpurun_out; mkdir -p $O
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 nvidia-smi topo -m > $O/topo_n$N.txt 2>&1
-timeout 600 $TR --master-port 29511 tools/p2p_check.py > $O/p2p_n$N.log 2> $O/p2p_n$N.err; echo "p2p_check rc=$?"; tail -n 1 $O/p2p_n$N.log
+timeout 600 $TR --master-port 29511 tests/multigpu_check.py > $O/p2p_n$N.log 2> $O/p2p_n$N.err; echo "p2p_check rc=$?"; tail -n 1 $O/p2p_n$N.log
 timeout 600 $TR --master-port 29521 bench.py --gpus $N --steps 10 --warmup 3 > $O/bench_n$N.log 2> $O/bench_n$N.err; echo "bench rc=$?"
 for c in 3 4 5 6; do
   timeout 600 $TR --master-port 2953$c tools/run_configs.py --config $c > $O/cfg${c}_n$N.log 2> $O/cfg${c}_n$N.err; echo "config $c rc=$?"

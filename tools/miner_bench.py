@@ -2,13 +2,12 @@
 """Throughput of the triplet miner at LineMOD scale: 15 objects x 1,241 templates x 1,200 training
 samples of 64x64x7 (both pools resident in HBM, filled by the device generator): computeMaxSimTmpl, computeKNN
 (forward of both pools + 3-NN + table) and buildBatch (selection + Caffe-layout gather [+ colour fill]) for the
-reference's batch of 300 and for a 30,000-sample batch; the CPU oracle's buildBatch timed beside it."""
+reference's batch of 300 and for a 30,000-sample batch."""
 import importlib, json, os, sys, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 capi = importlib.import_module("3dposeestimation_b200.capi")
 from tests import miner_cases as mc
-from oracle import pyoracle as po
 
 N_OBJ, N_T, N_Q, CH = 15, int(os.environ.get("TEMPLATES", 1241)), int(os.environ.get("TRAINING", 1200)), 7
 tl, ql = mc.make_labels(1, N_OBJ, N_T), mc.make_labels(2, N_OBJ, N_Q)
@@ -51,16 +50,6 @@ for batch in (300, 30000):
     out[f"batch_{batch}"] = {"ms_build_batch": ms0, "samples_per_s": batch / ms0 * 1e3, "algorithmic_GBps": 2 * batch * img / ms0 / 1e6,
                              "ms_with_colour_fill": ms1}
     d_b.free()
-# CPU oracle: selection + gather for one reference batch (pools of 4 objects' worth are enough for the gather timing)
-tp = mc.make_pool(3, N_OBJ * 64, CH); qp = mc.make_pool(4, N_OBJ * 64, CH)
-tl_s, ql_s = mc.make_labels(1, N_OBJ, 64), mc.make_labels(2, N_OBJ, 64)
-ms_s = po.max_sim_tmpl(tl_s, ql_s, N_OBJ, True)
-t0 = time.perf_counter()
-for it in range(3):
-    idx, _ = po.triplet_indices(tl_s, ms_s, None, None, rot_inv, None, N_OBJ, 64, 300, 5, it, 11)
-    po.gather_batch(tp, qp, None, idx, it * 60, 11)
-out["cpu_oracle_ms_per_batch_300_1_thread"] = (time.perf_counter() - t0) * 1e3 / 3
-t0 = time.perf_counter(); po.max_sim_tmpl(tl, ql, N_OBJ, True); out["cpu_oracle_ms_max_sim_1_thread"] = (time.perf_counter() - t0) * 1e3
 t = capi.Timer(0); m2 = capi.Miner(None, tl, None, ql, N_OBJ, rot_inv, inplane=True, channels=CH); m2.share_stream(net)
 net.sync(); t.start(net); m2.max_sim(); t.stop(net); out["ms_max_sim_kernel"] = t.elapsed_ms()
 print(json.dumps(out))

@@ -1,12 +1,11 @@
 #!/usr/bin/env python
 """Throughput of the patch extraction on device-resident 640x480 frames: one 64x64x7 patch per frame
-(the reference's use), normals on the fly vs. full-frame depth2normals first; the CPU oracle timed beside it."""
+(the reference's use), normals on the fly vs. full-frame depth2normals first."""
 import importlib, json, os, sys, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 capi = importlib.import_module("3dposeestimation_b200.capi")
 from tests import scenes
-from oracle import pyoracle as po
 
 F = int(os.environ.get("FRAMES", 1024))
 base = [scenes.make_frame(s) for s in range(8)]
@@ -32,13 +31,10 @@ full = lambda: (capi.check(capi.lib().pe_depth2normals_dev(net.h, 0, d_dep.ptr, 
                 capi.sample_patches_dev(net, d_col, d_dep, d_nor, F, 480, 640, None, d_ctr, d_z, F, cam["fx"], cam["fy"], 0.2, d_p))
 chain = lambda: (fly(), net.compute_descriptors_dev(d_p, F, d_desc))
 ms_fly, ms_full, ms_chain = timed(fly), timed(full), timed(chain)
-ok, (x, y, w, h) = po.patch_rect(480, 640, int(ctr[0, 0]), int(ctr[0, 1]), float(z[0]), cam["fx"], cam["fy"])
+# the cut rectangle of samplePatchWithScale (reference src/datasetmanager.cpp:303-309): 0.2 m scaled by f / z
+w, h = int(cam["fx"] * 0.2 / float(z[0])), int(cam["fy"] * 0.2 / float(z[0]))
 bytes_patch = 64 * 64 * 7 * 4 + (w + 8) * (h + 8) * 7          # output + the cut (colour 3 B, depth 4 B) with the stencil halo
-t0 = time.perf_counter(); n_cpu = 4
-for i in range(n_cpu):
-    nor = po.depth2normals(depth[i], cam["fx"], cam["fy"]); po.sample_patch(color[i], depth[i], nor, ctr[i, 0], ctr[i, 1], float(z[i]), cam["fx"], cam["fy"])
-cpu_ms = (time.perf_counter() - t0) * 1e3 / n_cpu
 print(json.dumps({"frames": F, "cut": [w, h], "ms_sample_normals_on_the_fly": ms_fly, "patches_per_s": F / ms_fly * 1e3,
                   "algorithmic_GBps": F * bytes_patch / ms_fly / 1e6, "ms_depth2normals_full_plus_sample": ms_full,
                   "full_frame_normals_GBps": F * 480 * 640 * 16 / (ms_full - ms_fly + 1e-9) / 1e6,
-                  "ms_frames_to_descriptors": ms_chain, "cpu_oracle_ms_per_frame_1_thread": cpu_ms}))
+                  "ms_frames_to_descriptors": ms_chain}))

@@ -1,13 +1,12 @@
 #!/usr/bin/env python
 """Throughput of the template pass on the device (SURVEY 8f rank 1 + 2 + the forward): the view sphere of one object
 (depth 2, 7 in-plane rotations, 3 distances = 1869 views) rendered at 640x480 from a 20,480-triangle mesh, one patch per
-view, one descriptor per patch.  The CPU oracle renderer is timed beside it on a few views."""
+view, one descriptor per patch.  (CPU timings of the oracle renderer: tests/ only - the oracle is test infrastructure.)"""
 import importlib, json, os, sys, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 capi = importlib.import_module("3dposeestimation_b200.capi")
 from tests import scenes
-from oracle import pyoracle as po
 
 CAM = np.array([572.4114, 573.57043, 325.2611, 242.04899], np.float32)
 LEVEL = int(os.environ.get("LEVEL", 5)); B = int(os.environ.get("BATCH", 128))
@@ -41,9 +40,5 @@ def timed(fn, reps=3):
     t.stop(net); return t.elapsed_ms() / reps
 
 ms_r, ms_all = timed(lambda: run(True)), timed(lambda: run(False))
-t0 = time.perf_counter(); k = 3
-for i in range(k): po.render(v, c, f, CAM, poses[i * 200])
-cpu_ms = (time.perf_counter() - t0) * 1e3 / k
 print(json.dumps({"views": n, "triangles": int(len(f)), "vertices": int(len(v)), "batch": B, "ms_render_all_views": ms_r, "views_per_s_render": n / ms_r * 1e3,
-                  "Mtri_per_s": n * len(f) / ms_r / 1e3, "ms_render_patch_descriptor": ms_all, "templates_per_s": n / ms_all * 1e3,
-                  "cpu_oracle_ms_per_view_1_thread": cpu_ms}))
+                  "Mtri_per_s": n * len(f) / ms_r / 1e3, "ms_render_patch_descriptor": ms_all, "templates_per_s": n / ms_all * 1e3}))
