@@ -97,6 +97,7 @@ SIGNATURES = {
     "pe_knn_hamming_dev": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp, vp]),
     "pe_histogram": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, C.c_int, vp, C.c_int, vp]),
     "pe_histogram_dev": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, C.c_int, vp, C.c_int, vp]),
+    "pe_histogram_dev_noalloc": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, C.c_int, vp, C.c_int, vp]),
     "pe_confusion": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp]),
     "pe_knn_bootstrap": (C.c_int, [vp, vp, C.c_int64, C.c_int, vp, vp]),
     "pe_knn_accuracy": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, fp, fp]),
@@ -595,6 +596,13 @@ class TemplateDB:
         rot, bn = _i32(rot_inv), _f32(bins)
         out = np.empty(bn.size + 2, np.float32)
         check(lib().pe_histogram_dev(self.h, d_idx.ptr, d_qlabels.ptr, nq, k, _ptr(rot), rot.size, _ptr(bn), bn.size, _ptr(out)))
+        return out
+
+    def histogram_dev_noalloc(self, d_idx, d_qlabels, nq, k, rot_inv, bins):
+        """pe_histogram_dev_noalloc: the same reduction on a fixed file-scope device scratch (no cudaMalloc); nq <= 65,536"""
+        rot, bn = _i32(rot_inv), _f32(bins)
+        out = np.empty(bn.size + 2, np.float32)
+        check(lib().pe_histogram_dev_noalloc(self.h, d_idx.ptr, d_qlabels.ptr, nq, k, _ptr(rot), rot.size, _ptr(bn), bn.size, _ptr(out)))
         return out
 
     def confusion(self, knn_idx, q_labels, class_to_local, n_local, nr_test_poses):

@@ -17,6 +17,7 @@
 #include <cfloat>
 #include <cmath>
 
+#include <mutex>
 #include <vector>
 
 #include "common.h"
@@ -377,3 +378,99 @@ int pose_accuracy_dev(pe_db* db, const int* d_max_sim0, const int* d_boot, int64
 }
 
 }  // namespace pe
+
+/* ------------------------------------------------------------------------------------------------
+ * pe_histogram_dev_noalloc - the histogram reduction for callers that may not allocate (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same kernels and arithmetic as pe_histogram_dev; the only difference is where the scratch lives:
+ * a file-scope device array of fixed size instead of the DB's growable buffer.
+ *
+ * Every GPU that loads the library holds these kNaScratchBytes (260.2 KiB) until the process exits.  In HOST code the
+ * array's name is only a stand-in for the symbol, never a device address: its address is resolved once per device with
+ * cudaGetSymbolAddress (that device current) and that pointer is what the kernels get.
+ * All calls on a device share the array and it keeps the last call's contents: the counters that must start at zero are
+ * cleared on the stream at the start of every call, the rest is overwritten before it is read.  Calls that overlap on the
+ * GPU (two DBs / two streams of one device) race on it: serialise them.
+ * ------------------------------------------------------------------------------------------------ */
+namespace pe {
+namespace {
+
+constexpr int kNaMaxQueries = 65536;    /* per call */
+constexpr int kNaMaxClasses = 1024;     /* rot_inv entries */
+/* [counts: 16 x u64][sum: f64][median: f32 + pad][rot_inv: kNaMaxClasses x i32][bins: 16 x f32][err: kNaMaxQueries x f32] */
+constexpr size_t kNaOffSum = kMaxBins * 8, kNaOffMed = kNaOffSum + 8, kNaOffRot = kNaOffMed + 8;
+constexpr size_t kNaOffBins = kNaOffRot + (size_t)kNaMaxClasses * 4, kNaOffErr = kNaOffBins + kMaxBins * 4;
+constexpr size_t kNaScratchBytes = kNaOffErr + (size_t)kNaMaxQueries * 4;      /* 266,448 B */
+
+static __device__ __align__(256) unsigned char g_hist_noalloc_scratch[kNaScratchBytes];
+
+constexpr int kNaMaxDevices = 64;
+std::mutex g_na_mutex;
+unsigned char* g_na_ptr[kNaMaxDevices] = {};
+
+/* device address of the array on `device` (which must be current); resolved on the first call per device */
+int noalloc_scratch(int device, unsigned char** out) {
+    PE_REQUIRE(device >= 0 && device < kNaMaxDevices, "device %d outside 0..%d", device, kNaMaxDevices - 1);
+    std::lock_guard<std::mutex> lock(g_na_mutex);
+    if (!g_na_ptr[device]) {
+        void* p = nullptr;
+        PE_CUDA(cudaGetSymbolAddress(&p, g_hist_noalloc_scratch));
+        PE_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address for the scratch array");
+        g_na_ptr[device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_na_ptr[device];
+    return PE_OK;
+}
+
+}  // namespace
+}  // namespace pe
+
+extern "C" int pe_histogram_dev_noalloc(pe_db* db, const int32_t* d_knn_idx, const float* d_q_labels, int64_t nq, int k,
+                                        const int* rot_inv, int n_rot, const float* bins, int n_bins, float* out) {
+    using namespace pe;
+    PE_REQUIRE(db && bins && out && (rot_inv || n_rot == 0), "null pointer");
+    PE_REQUIRE(nq >= 0 && (nq == 0 || (d_knn_idx && d_q_labels)), "null pointer");
+    PE_REQUIRE(nq <= kNaMaxQueries, "pe_histogram_dev_noalloc: %lld queries exceed the fixed scratch (at most %d per call; "
+               "use pe_histogram_dev, which allocates)", (long long)nq, kNaMaxQueries);
+    PE_REQUIRE(n_rot >= 0 && n_rot <= kNaMaxClasses, "pe_histogram_dev_noalloc: %d rotInv classes exceed the fixed scratch (at most %d; "
+               "use pe_histogram_dev, which allocates)", n_rot, kNaMaxClasses);
+    PE_REQUIRE(db->d_labels != nullptr, "DB was created without labels");
+    PE_REQUIRE(n_bins >= 2 && n_bins <= kMaxBins, "n_bins=%d outside 2..%d", n_bins, kMaxBins);
+    PE_REQUIRE(k >= 1 && k <= 32, "k=%d outside 1..32", k);
+    PE_REQUIRE(db->poses_per_object > 0, "poses_per_object not set");
+    PE_CUDA(cudaSetDevice(db->device));
+    unsigned char* base = nullptr;
+    PE_CHECK(noalloc_scratch(db->device, &base));
+    unsigned long long* d_counts = reinterpret_cast<unsigned long long*>(base);
+    double* d_sum = reinterpret_cast<double*>(base + kNaOffSum);
+    float* d_med = reinterpret_cast<float*>(base + kNaOffMed);
+    int* d_rot = reinterpret_cast<int*>(base + kNaOffRot);
+    float* d_bins = reinterpret_cast<float*>(base + kNaOffBins);
+    float* d_err = reinterpret_cast<float*>(base + kNaOffErr);
+    /* the array keeps the previous call's contents: counts, sum and median start at zero, the tables are rewritten,
+     * err[0, nq) is written by pose_err_kernel before median_select_kernel reads exactly that range */
+    PE_CUDA(cudaMemsetAsync(base, 0, kNaOffRot, db->stream));
+    if (n_rot > 0) PE_CUDA(cudaMemcpyAsync(d_rot, rot_inv, (size_t)n_rot * 4, cudaMemcpyHostToDevice, db->stream));
+    PE_CUDA(cudaMemcpyAsync(d_bins, bins, (size_t)n_bins * 4, cudaMemcpyHostToDevice, db->stream));
+    if (nq > 0) {
+        pose_err_kernel<<<(unsigned)((nq + kPoseWarps - 1) / kPoseWarps), kPoseWarps * 32, 0, db->stream>>>(
+            d_knn_idx, nq, k, d_q_labels, db->d_labels, db->t_total, db->poses_per_object, d_rot, n_rot, d_bins, n_bins,
+            d_err, d_counts, d_sum);
+        PE_LAUNCHED();
+    }
+    median_select_kernel<<<1, 1024, 0, db->stream>>>(d_err, nq, d_med);
+    PE_LAUNCHED();
+    unsigned long long h_counts[kMaxBins];
+    double h_sum = 0.0;
+    float h_med = 0.f;
+    PE_CUDA(cudaMemcpyAsync(h_counts, d_counts, sizeof(h_counts), cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaMemcpyAsync(&h_sum, d_sum, 8, cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaMemcpyAsync(&h_med, d_med, 4, cudaMemcpyDeviceToHost, db->stream));
+    PE_CUDA(cudaStreamSynchronize(db->stream));
+    /* normalisation of src/networkevaluator.cpp:342-346, as pose_hist_finish */
+    const float total = (float)h_counts[0] + (float)h_counts[n_bins - 1];
+    for (int b = 0; b < n_bins; ++b) out[b] = (float)h_counts[b] / total;
+    out[n_bins] = (float)(h_sum / (double)nq);
+    out[n_bins + 1] = h_med;
+    return PE_OK;
+}

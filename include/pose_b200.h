@@ -223,6 +223,21 @@ PE_API int pe_histogram(pe_db* db, const int32_t* knn_idx, const float* q_labels
 PE_API int pe_histogram_dev(pe_db* db, const int32_t* d_knn_idx, const float* d_q_labels, int64_t nq,
                             int k, const int* rot_inv, int n_rot, const float* bins, int n_bins,
                             float* out);
+/* pe_histogram_dev without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same arguments, kernels and results as pe_histogram_dev; the scratch (bin counts, error sum, median slot, rotInv
+ * table, bin edges, per-query errors) lives in a fixed file-scope device array of 266,448 bytes (260.2 KiB) that every
+ * GPU which loads the library holds until the process exits, so the sizes are capped:
+ *     nq <= 65,536 queries per call and n_rot <= 1,024 classes - larger values return PE_ERR_INVALID (use
+ *     pe_histogram_dev, which allocates).
+ * The call makes no cudaMalloc / cudaFree / allocating library call; the first call on a device resolves the array's
+ * device address (cudaGetSymbolAddress), so make one call outside a capture first.  All calls on a device share the
+ * array, which keeps the previous call's contents (what must start at zero is cleared on the DB's stream at the start of
+ * each call): calls that overlap on the GPU - two DBs or two streams of one device - race on it and must be serialised
+ * by the caller.  Synchronises the DB's stream before it returns, like pe_histogram_dev. */
+PE_API int pe_histogram_dev_noalloc(pe_db* db, const int32_t* d_knn_idx, const float* d_q_labels, int64_t nq,
+                                    int k, const int* rot_inv, int n_rot, const float* bins, int n_bins,
+                                    float* out);
 /* body of computeConfusionMatrix after knnMatch (src/networkevaluator.cpp:199-245).
  * class_to_local[c] = local_index[models[c]] (:215-216); out: n_local x n_local,
  * row-normalised by nr_test_poses. */
