@@ -39,7 +39,9 @@ def short(name):
 def launches(tag, steps, warmup, per_step):
     path = os.path.join(ROOT, "gpurun_out", f"launches_{tag}.csv")
     rows = []
-    with open(path) as f:
+    import gzip
+    opener = (lambda: gzip.open(path + ".gz", "rt")) if os.path.exists(path + ".gz") else (lambda: open(path))
+    with opener() as f:
         lines = [l for l in f if l.startswith('"')]
     for r in csv.DictReader(io.StringIO("".join(lines))):
         if r["Metric Name"] == "gpu__time_duration.sum":
@@ -49,7 +51,7 @@ def launches(tag, steps, warmup, per_step):
     # conv1 launch with a grid smaller than a full batch (1024-patch H2D stages) -- or fall back to the tail.
     names = [r[1] for r in rows]
     first_scan = next(i for i, n in enumerate(names) if "scan" in n)
-    start = first_scan - (per_step - 2) + warmup * per_step          # first launch of timed step 0
+    start = first_scan - 4 + warmup * per_step          # first launch of timed step 0 (conv1, conv2, fc, fc precede the scan)
     timed = rows[start:start + steps * per_step]
     agg = OrderedDict()
     for _, n, us, g, b in timed:
@@ -70,7 +72,7 @@ def launches(tag, steps, warmup, per_step):
         a = allagg.setdefault(n, [0, 0.0])
         a[0] += 1
         a[1] += us
-    out += ["", "Whole process (set-up of the 1,000,200-row DB, warm-up, timed steps, host-API e2e steps):", "",
+    out += ["", "Whole process (set-up of the 1,000,200-row DB, warm-up, timed steps, e4m3 / serialised / sustained replays, host-API e2e steps):", "",
             "| kernel | launches | total us |", "|---|---|---|"]
     for n, (c, us) in allagg.items():
         out.append(f"| `{n}` | {c} | {us:.1f} |")
@@ -123,7 +125,8 @@ def main():
     ap.add_argument("tag")
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--launches-per-step", type=int, default=6)
+    # round 2: conv1, conv2, fc x2, scan, select, exact re-scan of unproven queries (knn_exact_fallback: exits at once when none)
+    ap.add_argument("--launches-per-step", type=int, default=7)
     a = ap.parse_args()
     per = launches(a.tag, a.steps, a.warmup, a.launches_per_step)
     tr = full(a.tag)
