@@ -4,7 +4,7 @@
  * Replaces Caffe's InnerProduct + ReLU/ELU/PReLU inside `CNN.Forward()` (reference src/networkevaluator.cpp:45;
  * network/manifold_rgbdnor_16.prototxt:75-108, manifold_rgbdnor_16_bin.prototxt:113-154):
  *     Y[m][o] = act(bias[o] + sum_k X[m][k] W[o][k])
- * M = patches of the chunk (128 per CTA), N = outputs (128 per CTA), K = fan-in in blocks of 64.
+ * M = patches of the chunk (64 per CTA, issued as M = 128 MMAs), N = outputs (128 per CTA), K = fan-in in blocks of 64.
  * Both operands K-major, no swizzle (umma.cuh): a K block is 8 chunks of [128 rows][8 halves].  Weights are
  * packed once on the host (fp16 hi / lo, power-of-two scale) and arrive by one 32 KB cp.async.bulk per K block;
  * activations are fp32 in HBM and are converted (scale 2^4, hi / lo) by the four loader warps, which also drain
@@ -31,6 +31,7 @@ constexpr int kFcOffBar = kFcStages * kFcStageBytes;
 constexpr int kFcSmem = kFcOffBar + 256;
 constexpr int kFcThreads = 320;                    /* warp 0 weight copies, warp 1 MMA, warps 2-9 loaders + epilogue */
 constexpr int kLog2SxFc = 4;                       /* activation scale 2^4: |x| < 4094 */
+constexpr int kFcRows = 64;                        /* batch rows per CTA (the MMA is M = 128, see the kernel) */
 
 __device__ __forceinline__ float fc_act(float v, int act, float slope) {
     const float pos = fmaxf(v, 0.f), neg = fminf(v, 0.f);
@@ -66,7 +67,12 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
     uint64_t* acc_full = bars + 3 * kFcStages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int m0 = blockIdx.x * 128, n0 = blockIdx.y * 128;
+    /* a CTA owns kFcRows = 64 rows of the batch but issues M = 128 MMAs: a row of D depends on the same row of A only, so
+     * accumulator lanes 64..127 hold whatever the never-written upper half of the A tile produces and are never read.
+     * 64-row tiles put (M / 64) x (N / 128) = 128 CTAs on the 148 SMs for the 4096-patch batch (128-row tiles: 64) and
+     * halve what a loader thread converts per K block - the kernel is bound by that load -> convert -> store chain,
+     * not by the tensor pipe (12 MMAs of 64 cycles per K block). */
+    const int m0 = blockIdx.x * kFcRows, n0 = blockIdx.y * 128;
     int n_mma = a.N - n0;
     n_mma = n_mma >= 128 ? 128 : ((n_mma + 15) & ~15);
     if (tid == 0) {
@@ -121,31 +127,31 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
         if (ok && elect_one()) mma_commit(acc_full);
         __syncwarp();
     } else {
-        /* ---- loaders: two threads per row m0 + r (k halves of 32), one K block at a time.  The loads of block kb + 1 are
+        /* ---- loaders: four threads per row m0 + r (k quarters of 16), one K block at a time.  The loads of block kb + 1 are
          * in flight while block kb is converted (two register buffers): a row is 4.7 KB away from the next one, so every
-         * load is its own pair of cache lines and its latency would otherwise be paid 19 times in a row ---- */
-        const int r = (warp & 3) * 32 + lane;     /* = the TMEM lane this thread may read in the epilogue */
-        const int half = (warp - 2) >> 2;
+         * load is its own cache line and its latency would otherwise be paid 19 times in a row ---- */
+        const int lt = tid - 64;                  /* 0..255 */
+        const int r = lt & 63, kq = lt >> 6;
         const int m = m0 + r;
         const bool row_ok = m < a.M;
         const float sx = static_cast<float>(1 << kLog2SxFc);
-        const float* xrow = a.x + (size_t)(row_ok ? m : 0) * a.ldx + 32 * half;
+        const float* xrow = a.x + (size_t)(row_ok ? m : 0) * a.ldx + 16 * kq;
         float vmax = 0.f;
         bool ok = true;
-        auto load = [&](float4 (&v)[8], int kb) {
+        auto load = [&](float4 (&v)[4], int kb) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int k = kb * kFcKB + 32 * half + 4 * i;
+            for (int i = 0; i < 4; ++i) {
+                const int k = kb * kFcKB + 16 * kq + 4 * i;
                 v[i] = (row_ok && k < a.K) ? *reinterpret_cast<const float4*>(xrow + kb * kFcKB + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
         };
-        auto convert = [&](const float4 (&v)[8], int kb) {
+        auto convert = [&](const float4 (&v)[4], int kb) {
             const int s = kb % kFcStages;
             if (!mbar_wait(&empty[s], ((kb / kFcStages) & 1) ^ 1)) { atomicExch(a.err, 14); ok = false; return; }
-            uint4* dst_hi = reinterpret_cast<uint4*>(smem + s * kFcStageBytes) + (4 * half) * 128 + r;
+            uint4* dst_hi = reinterpret_cast<uint4*>(smem + s * kFcStageBytes) + (2 * kq) * 128 + r;
             uint4* dst_lo = dst_hi + kFcTerm / 16;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < 2; ++c) {
                 const float e[8] = {v[2 * c].x, v[2 * c].y, v[2 * c].z, v[2 * c].w, v[2 * c + 1].x, v[2 * c + 1].y, v[2 * c + 1].z, v[2 * c + 1].w};
                 uint32_t hi[4], lo[4];
 #pragma unroll
@@ -163,7 +169,7 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
             fence_async_smem();
             mbar_arrive(&full_a[s]);
         };
-        float4 va[8], vb[8];
+        float4 va[4], vb[4];
         load(va, 0);
 #pragma unroll 1
         for (int kb = 0; kb < a.k_blocks && ok; kb += 2) {
@@ -175,30 +181,36 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
             }
         }
         if (!(vmax <= 4000.f)) atomicExch(a.err, 101);
-        /* ---- epilogue: accumulator row r -> bias, activation, store ---- */
-        if (ok && mbar_wait(acc_full, 0)) {
-            fence_after_sync();
-            const uint32_t tbase = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
-            float* yrow = a.y + (size_t)(row_ok ? m : 0) * a.ldy + n0;
-            const int groups = n_mma / 16, g_split = (groups + 1) / 2;
-            for (int c0 = (half ? g_split : 0) * 16; c0 < (half ? groups : g_split) * 16; c0 += 16) {
-                uint32_t w[16], wx[16];
-                tmem_ld16(tbase + c0, w);
-                tmem_ld16(tbase + 128 + c0, wx);
-                tmem_ld_wait();
+        /* ---- epilogue: accumulator row er -> bias, activation, store.  Rows 0..63 live in TMEM lanes 0..63, which only
+         * warps with warp % 4 in {0, 1} may read: warps 4, 5 take the first half of the columns, warps 8, 9 the second ---- */
+        if ((warp & 3) < 2) {
+            const int er = (warp & 3) * 32 + lane, half = (warp - 2) >> 2;
+            const int em = m0 + er;
+            const bool erow_ok = em < a.M;
+            if (ok && mbar_wait(acc_full, 0)) {
+                fence_after_sync();
+                const uint32_t tbase = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+                float* yrow = a.y + (size_t)(erow_ok ? em : 0) * a.ldy + n0;
+                const int groups = n_mma / 16, g_split = (groups + 1) / 2;
+                for (int c0 = (half ? g_split : 0) * 16; c0 < (half ? groups : g_split) * 16; c0 += 16) {
+                    uint32_t w[16], wx[16];
+                    tmem_ld16(tbase + c0, w);
+                    tmem_ld16(tbase + 128 + c0, wx);
+                    tmem_ld_wait();
 #pragma unroll
-                for (int j = 0; j < 16; ++j) w[j] = __float_as_uint(__uint_as_float(w[j]) + __uint_as_float(wx[j]));
-                if (row_ok) {
+                    for (int j = 0; j < 16; ++j) w[j] = __float_as_uint(__uint_as_float(w[j]) + __uint_as_float(wx[j]));
+                    if (erow_ok) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const int o = n0 + c0 + j;
-                        if (o < a.N) yrow[c0 + j] = fc_act(fmaf(__uint_as_float(w[j]), a.inv_scale, a.bias[o]), a.act, a.slope ? a.slope[o] : 0.f);
-                        else if (o < a.n_store) yrow[c0 + j] = 0.f;
+                        for (int j = 0; j < 16; ++j) {
+                            const int o = n0 + c0 + j;
+                            if (o < a.N) yrow[c0 + j] = fc_act(fmaf(__uint_as_float(w[j]), a.inv_scale, a.bias[o]), a.act, a.slope ? a.slope[o] : 0.f);
+                            else if (o < a.n_store) yrow[c0 + j] = 0.f;
+                        }
                     }
                 }
+            } else if (ok) {
+                atomicExch(a.err, 15);
             }
-        } else if (ok) {
-            atomicExch(a.err, 15);
         }
     }
     fence_before_sync();
@@ -261,7 +273,7 @@ int fc_tc_launch(pe_net* net, const FcPlan& fc, const float* x, int ldx, float* 
         PE_CUDA(cudaFuncSetAttribute(fc_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFcSmem));
         attr_done[net->device & 15] = true;
     }
-    dim3 grid((unsigned)((m + 127) / 128), (unsigned)((fc.out + 127) / 128));
+    dim3 grid((unsigned)((m + kFcRows - 1) / kFcRows), (unsigned)((fc.out + 127) / 128));
     fc_tc_kernel<<<grid, kFcThreads, kFcSmem, net->stream>>>(a);
     PE_LAUNCHED();
     return PE_OK;

@@ -8,8 +8,13 @@
  *       263-267 and src/networksolver.cpp:466-472: dist = sqrt(sum_d (q_d - t_d)^2) in fp32,
  *       k smallest ascending; equal distances keep the lower train index (batchDistance
  *       scans templates in order and only replaces on strictly smaller).
- *   Eigen 3.x Quaternionf::angularDistance   - src/networkevaluator.cpp:297,331:
- *       2*acos(min(1,|a.b|))  (3.2 omits the clamp and returns NaN past 1; we clamp).
+ *   Eigen Quaternionf::angularDistance       - src/networkevaluator.cpp:297,331.  ASSUMED VERSION: Eigen 3.2.x (what
+ *       `libeigen3-dev` installs on the Ubuntu 14.04 / 16.04 + CUDA 7.5 / 8.0 systems of README.md:10-14), whose
+ *       Quaternion.h computes  d = |a.b|; if (d >= 1) return 0; return 2*acos(d)  =  2*acos(min(1,|a.b|)).
+ *       Eigen 3.3+ instead returns 2*atan2(|(a * conj(b)).vec()|, |(a * conj(b)).w()|): the same angle, better conditioned
+ *       near 0 degrees.  That form is restated too (orc_angular_distance_atan2, selected with orc_set_angular_form(1));
+ *       tests/test_oracle_golden.py bounds the disagreement of the two (<= 0.07 deg near 0, <= 1e-3 deg beyond 5 deg,
+ *       a handful of bin / exact-match flips per 3,000 queries).  The CUDA path implements the 3.2 form.
  *       std::acos(float) is restated as the correctly rounded value (float)acos((double)x):
  *       any libm acosf is within 1 ulp of it, and it is reproducible bit for bit on the GPU,
  *       so the strict `<` of the exact-match scan (:331) agrees between oracle and CUDA.
@@ -166,7 +171,22 @@ void orc_merge_topk_i32(const int32_t* idx, const int32_t* dist, int n_shards, i
 /* ------------------------------------------------------------------ Eigen --- */
 static inline float acos_cr(float x) { return (float)acos((double)x); }
 
+static int g_angular_form = 0;      /* 0: Eigen 3.2 (acos of the dot product), 1: Eigen 3.3+ (atan2 of q * conj(k)) */
+void orc_set_angular_form(int form) { g_angular_form = form ? 1 : 0; }
+
+/* Eigen 3.3+ Quaternion.h angularDistance: d = a * conj(b); 2 * atan2(d.vec().norm(), abs(d.w())), all in float */
+float orc_angular_distance_atan2(const float* a, const float* b) {
+    /* coefficients are (x, y, z, w); conj(b) = (-bx, -by, -bz, bw); quaternion product a * conj(b) */
+    const float ax = a[0], ay = a[1], az = a[2], aw = a[3], bx = -b[0], by = -b[1], bz = -b[2], bw = b[3];
+    const float w = aw * bw - ax * bx - ay * by - az * bz;
+    const float x = aw * bx + ax * bw + ay * bz - az * by;
+    const float y = aw * by + ay * bw + az * bx - ax * bz;
+    const float z = aw * bz + az * bw + ax * by - ay * bx;
+    return 2.0f * atan2f(sqrtf(x * x + y * y + z * z), fabsf(w));
+}
+
 float orc_angular_distance(const float* a, const float* b) {
+    if (g_angular_form) return orc_angular_distance_atan2(a, b);
     float d = a[0] * b[0];
     d = d + a[1] * b[1];
     d = d + a[2] * b[2];

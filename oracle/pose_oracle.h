@@ -75,7 +75,9 @@ void orc_merge_topk_i32(const int32_t* idx, const int32_t* dist, int n_shards, i
                         int32_t* out_idx, int32_t* out_dist);
 
 /* Eigen restatements */
-float orc_angular_distance(const float* qa_xyzw, const float* qb_xyzw); /* radians */
+float orc_angular_distance(const float* qa_xyzw, const float* qb_xyzw); /* radians; Eigen 3.2 form unless switched */
+float orc_angular_distance_atan2(const float* qa_xyzw, const float* qb_xyzw); /* Eigen 3.3+ form */
+void orc_set_angular_form(int form);    /* 0 (default): Eigen 3.2 acos form, 1: Eigen 3.3+ atan2 form (process-wide; tests only) */
 float orc_rot22(const float* q_xyzw);                                   /* toRotationMatrix()(2,2) */
 
 /* networkEvaluator::computeHistogram body, src/networkevaluator.cpp:269-355 */

@@ -66,6 +66,10 @@ def lib():
         L.orc_merge_topk_i32.restype = None
         L.orc_merge_topk_i32.argtypes = [ip, ip, C.c_int, C.c_int64, C.c_int, ip, ip]
         L.orc_angular_distance.restype = C.c_float
+        L.orc_angular_distance_atan2.argtypes = [fp, fp]
+        L.orc_angular_distance_atan2.restype = C.c_float
+        L.orc_set_angular_form.argtypes = [C.c_int]
+        L.orc_set_angular_form.restype = None
         L.orc_angular_distance.argtypes = [fp, fp]
         L.orc_rot22.restype = C.c_float
         L.orc_rot22.argtypes = [fp]
@@ -359,6 +363,17 @@ def merge_topk(idx, dist):
 def angular_distance(qa, qb):
     qa, qb = _f32(qa), _f32(qb)
     return float(lib().orc_angular_distance(_p(qa, C.c_float), _p(qb, C.c_float)))
+
+
+def angular_distance_atan2(qa, qb):
+    """Eigen 3.3+ form of angularDistance (radians)"""
+    a, b = _f32(qa), _f32(qb)
+    return float(lib().orc_angular_distance_atan2(_p(a, C.c_float), _p(b, C.c_float)))
+
+
+def set_angular_form(form: int):
+    """0: Eigen 3.2 acos form (default, what the CUDA path implements), 1: Eigen 3.3+ atan2 form"""
+    lib().orc_set_angular_form(int(form))
 
 
 def rot22(q):

@@ -220,3 +220,47 @@ def test_parity_metrics():
     same, unexplained = parity.knn_agreement(np.array([[1], [2], [3]]), np.array([[1], [5], [6]]), np.array([[1.0], [1.0], [1.0]]),
                                              np.array([0.5, 1e-6, 0.5]))
     assert abs(same - 1 / 3) < 1e-12 and abs(unexplained - 1 / 3) < 1e-12
+
+
+def test_eigen_32_and_33_angular_distance_forms_agree(po, synth):
+    """the oracle (and the CUDA path) restate Eigen 3.2's angularDistance, 2 acos(min(1, |a.b|)); Eigen 3.3+
+    computes 2 atan2(|vec(a conj b)|, |w|).  Same angle; this bounds what the choice can change: <= 0.07 degrees near 0
+    (where the acos form is ill-conditioned), <= 1e-3 degrees beyond 5 degrees, and only a handful of histogram-bin /
+    exact-match decisions per 3,000 queries."""
+    rng = np.random.default_rng(12)
+    q = synth.random_quaternions(3, 7, 4000)
+    worst_small, worst_large = 0.0, 0.0
+    for i in range(0, 4000, 2):
+        for scale in (1.0, 0.02, 0.0005):        # arbitrary pairs, a few degrees apart, almost identical
+            b = q[i] + scale * (q[i + 1] - q[i])
+            b = (b / np.linalg.norm(b)).astype(np.float32)
+            a32, a33 = np.degrees(po.angular_distance(q[i], b)), np.degrees(po.angular_distance_atan2(q[i], b))
+            # reference angle in double, insensitive to the float quaternions' norm error: atan2(|a x b part|, |a.b|)
+            a64, b64 = q[i].astype(np.float64), b.astype(np.float64)
+            d = abs(float(np.dot(a64, b64)))
+            ref = np.degrees(2 * np.arctan2(np.sqrt(max(0.0, float(a64 @ a64) * float(b64 @ b64) - d * d)), d))
+            assert abs(a33 - ref) < 2e-3
+            if ref > 5:
+                worst_large = max(worst_large, abs(a32 - a33))
+            else:
+                worst_small = max(worst_small, abs(a32 - a33))
+    assert worst_large < 1e-3 and worst_small < 0.07
+    # what the choice changes in computeHistogram on a 3,000-query problem
+    n_obj, nr_t, nr_q, k = 20, 700, 150, 5
+    tl = synth.make_labels(77, n_obj, nr_t)
+    src = (np.arange(nr_q) * 13) % nr_t
+    ql = synth.perturb_labels(tl.reshape(n_obj, nr_t, 8)[:, src].reshape(-1, 8), 78, max_deg=25.0)
+    nq = n_obj * nr_q
+    own = (np.repeat(np.arange(n_obj), nr_q) * nr_t)[:, None] + rng.integers(0, nr_t, (nq, k))
+    idx = own.astype(np.int32)
+    idx[::5, 0] = (np.repeat(np.arange(n_obj), nr_q) * nr_t + np.tile(src, n_obj))[::5]       # many near-0-degree matches
+    rot = np.zeros(n_obj, np.int32)
+    bins = np.array([-1, 0, 10, 20, 40, 180], np.float32)
+    h32 = po.histogram(idx, ql, tl, nr_t, rot, bins)
+    try:
+        po.set_angular_form(1)
+        h33 = po.histogram(idx, ql, tl, nr_t, rot, bins)
+    finally:
+        po.set_angular_form(0)
+    assert np.abs(h32[:6] - h33[:6]).max() * nq <= 6        # at most a few queries change bin / exact-match status
+    assert abs(h32[6] - h33[6]) < 2e-3 and abs(h32[7] - h33[7]) < 0.07
