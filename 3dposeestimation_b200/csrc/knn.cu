@@ -419,10 +419,11 @@ __global__ void center_stats_kernel(const float* __restrict__ desc, int dp, long
 /* --------------------------------------------- exact re-scan of unproven queries ---- */
 /* The matcher's last resort and its ground truth: for every flagged query the reference's own expression
  * sqrt(sum (q-t)^2) over ALL rows of the shard (no ranking shortcut), k smallest by (distance, row).
- * grid (slots, chunks): CTA (x, y) serves flagged queries x, x + gridDim.x, ... on row chunk y; each thread keeps a sorted
- * top-k of its rows (row order ascending: a strict '<' keeps the lower row among equals), the CTA merges them in shared
- * memory, writes its chunk's k best, and the last chunk to arrive (counter per query) merges the chunks and writes the result. */
-constexpr int kFbThreads = 256, kFbChunks = 16, kFbMaxK = 16;
+ * grid (slots, chunks): CTA (x, y) serves flagged queries x, x + gridDim.x, ... on row chunk y (up to 64 chunks, so that a
+ * single flagged query - the common case - is spread over 64 SMs: ~10 us against 1 M rows).  A thread keeps a sorted
+ * top-KT of its rows in registers (rows ascend per thread: a strict '<' keeps the lower row among equals), the CTA merges
+ * them in shared memory and writes its chunk's k best; the last chunk to arrive (counter per query) merges the chunks. */
+constexpr int kFbThreads = 256, kFbMaxChunks = 64, kFbMaxK = 16;
 
 __device__ void fb_block_topk(float* s_d, int* s_i, int n, int k, float* out_d, int* out_i) {
     /* warp 0: k rounds of (distance, row) argmin over n shared-memory entries */
@@ -452,59 +453,81 @@ __device__ void fb_block_topk(float* s_d, int* s_i, int n, int k, float* out_d, 
     }
 }
 
+template <int KT>
 __global__ void __launch_bounds__(kFbThreads)
 knn_exact_fallback_kernel(const int* __restrict__ flag, const float* __restrict__ q, int dp, const float* __restrict__ db,
-                          long long t_local, long long row_offset, int k, float* __restrict__ part_d, int* __restrict__ part_i,
-                          unsigned* __restrict__ done, int* __restrict__ out_idx, float* __restrict__ out_dist) {
+                          long long t_local, long long row_offset, int k, int n_chunks, float* __restrict__ part_d,
+                          int* __restrict__ part_i, unsigned* __restrict__ done, int* __restrict__ out_idx,
+                          float* __restrict__ out_dist) {
     extern __shared__ __align__(16) float fb_smem[];
     float* sq = fb_smem;                                        /* [dp] */
-    float* s_d = fb_smem + dp;                                  /* [kFbThreads * k] */
-    int* s_i = reinterpret_cast<int*>(s_d + kFbThreads * k);
+    float* s_d = fb_smem + dp;                                  /* [max(kFbThreads * KT, n_chunks * k)] */
+    int* s_i = reinterpret_cast<int*>(s_d + (kFbThreads * KT > kFbMaxChunks * kFbMaxK ? kFbThreads * KT : kFbMaxChunks * kFbMaxK));
     __shared__ float r_d[kFbMaxK];
     __shared__ int r_i[kFbMaxK];
     __shared__ bool s_last;
     const int count = flag[0];
+    if (count == 0) return;
     const int chunk = blockIdx.y;
-    const long long rows_per = (t_local + kFbChunks - 1) / kFbChunks;
+    const long long rows_per = (t_local + n_chunks - 1) / n_chunks;
     const long long r0 = chunk * rows_per, r1 = (r0 + rows_per < t_local) ? r0 + rows_per : t_local;
     for (int f = blockIdx.x; f < count; f += gridDim.x) {
         const int qi = flag[4 + f];
         __syncthreads();
         for (int d = threadIdx.x; d < dp; d += kFbThreads) sq[d] = q[(size_t)qi * dp + d];
         __syncthreads();
-        float bd[kFbMaxK];
-        int bi[kFbMaxK];
+        float bd[KT];
+        int bi[KT];
 #pragma unroll
-        for (int p = 0; p < kFbMaxK; ++p) { bd[p] = INFINITY; bi[p] = INT_MAX; }
-        for (long long r = r0 + threadIdx.x; r < r1; r += kFbThreads) {
-            const float d = exact_l2(sq, db + (size_t)r * dp, dp);
-            if (d < bd[k - 1]) {
-                int p = k - 1;
-                while (p > 0 && d < bd[p - 1]) { bd[p] = bd[p - 1]; bi[p] = bi[p - 1]; --p; }
-                bd[p] = d;
-                bi[p] = (int)r;
+        for (int p = 0; p < KT; ++p) { bd[p] = INFINITY; bi[p] = INT_MAX; }
+        /* four rows in flight per thread: the loop is bound by the latency of the row reads */
+        for (long long r = r0 + threadIdx.x; r < r1; r += 4 * kFbThreads) {
+            float dj[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const long long rr = r + (long long)j * kFbThreads;
+                dj[j] = rr < r1 ? exact_l2(sq, db + (size_t)rr * dp, dp) : INFINITY;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float d = dj[j];
+                if (d < bd[KT - 1]) {       /* into the last slot, then bubble towards the front (all indices compile-time) */
+                    bd[KT - 1] = d;
+                    bi[KT - 1] = (int)(r + (long long)j * kFbThreads);
+#pragma unroll
+                    for (int p = KT - 1; p > 0; --p) {
+                        const bool sw = bd[p] < bd[p - 1];
+                        const float td = bd[p - 1];
+                        const int ti = bi[p - 1];
+                        bd[p - 1] = sw ? bd[p] : td;
+                        bi[p - 1] = sw ? bi[p] : ti;
+                        bd[p] = sw ? td : bd[p];
+                        bi[p] = sw ? ti : bi[p];
+                    }
+                }
             }
         }
-        for (int p = 0; p < k; ++p) { s_d[threadIdx.x * k + p] = bd[p]; s_i[threadIdx.x * k + p] = bi[p]; }
+#pragma unroll
+        for (int p = 0; p < KT; ++p) { s_d[threadIdx.x * KT + p] = bd[p]; s_i[threadIdx.x * KT + p] = bi[p]; }
         __syncthreads();
-        fb_block_topk(s_d, s_i, kFbThreads * k, k, r_d, r_i);
+        fb_block_topk(s_d, s_i, kFbThreads * KT, k, r_d, r_i);
         __syncthreads();
         if (threadIdx.x < k) {
-            part_d[((size_t)f * kFbChunks + chunk) * k + threadIdx.x] = r_d[threadIdx.x];
-            part_i[((size_t)f * kFbChunks + chunk) * k + threadIdx.x] = r_i[threadIdx.x];
+            part_d[((size_t)f * n_chunks + chunk) * k + threadIdx.x] = r_d[threadIdx.x];
+            part_i[((size_t)f * n_chunks + chunk) * k + threadIdx.x] = r_i[threadIdx.x];
         }
         __threadfence();
         __syncthreads();
-        if (threadIdx.x == 0) s_last = atomicAdd(done + f, 1u) == kFbChunks - 1;
+        if (threadIdx.x == 0) s_last = atomicAdd(done + f, 1u) == (unsigned)n_chunks - 1;
         __syncthreads();
         if (s_last) {
             __threadfence();
-            for (int c = threadIdx.x; c < kFbChunks * k; c += kFbThreads) {
-                s_d[c] = __ldcg(part_d + (size_t)f * kFbChunks * k + c);
-                s_i[c] = __ldcg(part_i + (size_t)f * kFbChunks * k + c);
+            for (int c = threadIdx.x; c < n_chunks * k; c += kFbThreads) {
+                s_d[c] = __ldcg(part_d + (size_t)f * n_chunks * k + c);
+                s_i[c] = __ldcg(part_i + (size_t)f * n_chunks * k + c);
             }
             __syncthreads();
-            fb_block_topk(s_d, s_i, kFbChunks * k, k, r_d, r_i);
+            fb_block_topk(s_d, s_i, n_chunks * k, k, r_d, r_i);
             __syncthreads();
             if (threadIdx.x < k) {
                 const bool ok = r_i[threadIdx.x] != INT_MAX;
@@ -653,21 +676,29 @@ int knn_l2_local(pe_db* db, const float* d_queries, int64_t nq, int k, int32_t* 
     return PE_OK;
 }
 
-/* re-scan of the queries listed in d_flag with the direct expression; a no-op (one early-exit launch) when none is */
+/* re-scan of the queries listed in d_flag with the direct expression; one early-exit launch when none is listed */
 int knn_exact_fallback(pe_db* db, const int* d_flag, const float* d_q, int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist) {
-    const int slots = (int)(nq < 4 * (int64_t)db->num_sms / kFbChunks + 1 ? nq : 4 * (int64_t)db->num_sms / kFbChunks + 1);
-    const size_t part = (size_t)nq * kFbChunks * k;
+    /* row chunks per query: as many as a 64 MB partial-result buffer allows, 4..64 (a power of two) */
+    int n_chunks = kFbMaxChunks;
+    while (n_chunks > 4 && (size_t)nq * n_chunks * k * 8 > ((size_t)64 << 20)) n_chunks >>= 1;
+    int slots = (4 * db->num_sms + n_chunks - 1) / n_chunks;
+    if ((int64_t)slots > nq) slots = (int)nq;
+    if (slots < 1) slots = 1;
+    const size_t part = (size_t)nq * n_chunks * k;
     PE_CHECK(db->fb_d.reserve(part * sizeof(float)));
     PE_CHECK(db->fb_i.reserve(part * sizeof(int)));
     if (db->fb_done.cap < (size_t)nq * sizeof(unsigned)) PE_CHECK(db->fb_done.reserve((size_t)nq * sizeof(unsigned), true));
-    const size_t smem = (size_t)(db->dim_pad + 2 * kFbThreads * k) * 4;
-    PE_CUDA(cudaFuncSetAttribute(knn_exact_fallback_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid((unsigned)(slots > 0 ? slots : 1), kFbChunks);
-    knn_exact_fallback_kernel<<<grid, kFbThreads, smem, db->stream>>>(d_flag, d_q, db->dim_pad, db->d_desc, db->t_local, db->row_offset, k,
-                                                                      db->fb_d.as<float>(), db->fb_i.as<int>(), db->fb_done.as<unsigned>(),
-                                                                      d_out_idx, d_out_dist);
+    const int kt = k <= 1 ? 1 : (k <= 4 ? 4 : (k <= 8 ? 8 : 16));
+    const size_t lists = (size_t)(kFbThreads * kt > kFbMaxChunks * kFbMaxK ? kFbThreads * kt : kFbMaxChunks * kFbMaxK);
+    const size_t smem = (size_t)(db->dim_pad + 2 * lists) * 4;
+    dim3 grid((unsigned)slots, (unsigned)n_chunks);
+#define FB_LAUNCH(KT) do { \
+        PE_CUDA(cudaFuncSetAttribute(knn_exact_fallback_kernel<KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        knn_exact_fallback_kernel<KT><<<grid, kFbThreads, smem, db->stream>>>(d_flag, d_q, db->dim_pad, db->d_desc, db->t_local, db->row_offset, k, \
+            n_chunks, db->fb_d.as<float>(), db->fb_i.as<int>(), db->fb_done.as<unsigned>(), d_out_idx, d_out_dist); } while (0)
+    if (kt == 1) FB_LAUNCH(1); else if (kt == 4) FB_LAUNCH(4); else if (kt == 8) FB_LAUNCH(8); else FB_LAUNCH(16);
+#undef FB_LAUNCH
     PE_LAUNCHED();
-    /* statistics: flagged queries accumulate in flag[1..2] on the device (read by pe_db_knn_stats) */
     return PE_OK;
 }
 

@@ -8,16 +8,23 @@ namespace pe {
  * separately, fixed combine tree, then sqrt. */
 __device__ __forceinline__ float exact_l2(const float* __restrict__ a, const float* __restrict__ b, int dp) {
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int i = 0; i < dp; i += 4) {
+    /* dims i .. i + 3 go to acc[i % 8 ..]: two float4 per iteration keep every accumulator index static (registers);
+     * the order of operations per accumulator is that of the oracle's loop */
+    auto step = [&](int i, int l) {
         const float4 x = *reinterpret_cast<const float4*>(a + i);
         const float4 y = __ldg(reinterpret_cast<const float4*>(b + i));
-        const int l = i & 7;
         const float d0 = __fsub_rn(x.x, y.x), d1 = __fsub_rn(x.y, y.y), d2 = __fsub_rn(x.z, y.z), d3 = __fsub_rn(x.w, y.w);
         acc[l + 0] = __fadd_rn(acc[l + 0], __fmul_rn(d0, d0));
         acc[l + 1] = __fadd_rn(acc[l + 1], __fmul_rn(d1, d1));
         acc[l + 2] = __fadd_rn(acc[l + 2], __fmul_rn(d2, d2));
         acc[l + 3] = __fadd_rn(acc[l + 3], __fmul_rn(d3, d3));
+    };
+    int i = 0;
+    for (; i + 8 <= dp; i += 8) {
+        step(i, 0);
+        step(i + 4, 4);
     }
+    if (i < dp) step(i, 0);          /* dp = 4 (mod 8): the last four dims have i % 8 == 0 */
     const float s = __fadd_rn(__fadd_rn(__fadd_rn(acc[0], acc[4]), __fadd_rn(acc[2], acc[6])),
                               __fadd_rn(__fadd_rn(acc[1], acc[5]), __fadd_rn(acc[3], acc[7])));
     return __fsqrt_rn(s);

@@ -671,7 +671,7 @@ __global__ void __launch_bounds__(32 * kTcSelWarps)
 knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ cand_i, int n_cand, int kc,
                      const float* __restrict__ q, const float* __restrict__ db, int dp, long long t_local,
                      long long row_offset, int k, int n_sel, long long nq, const float* __restrict__ key_scale,
-                     const float* __restrict__ ctr, float max_norm2, int* __restrict__ flag,
+                     const float* __restrict__ ctr, float max_norm2, float eps_rel, int* __restrict__ flag,
                      int* __restrict__ out_idx, float* __restrict__ out_dist) {
     extern __shared__ __align__(16) float sel_smem_all[];
     /* one warp per query, kTcSelWarps independent queries per CTA (32-thread CTAs cap an SM at 32 resident warps, and
@@ -769,7 +769,7 @@ knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ c
         bool proven = true;
         if (b_key < INFINITY) {
             const float qn = sqrtf(qn2), tmax = sqrtf(max_norm2);
-            const float eps = 7.62939453125e-6f * qn * tmax + 1.9073486328125e-6f * (max_norm2 + qn2);    /* 2^-17, 2^-19 */
+            const float eps = eps_rel * qn * tmax + 1.9073486328125e-6f * (max_norm2 + qn2);    /* eps_rel (2^-17), 2^-19 */
             const float lb = qn2 + b_key * key_scale[qi] - eps;          /* d^2 of any template that was not re-ranked */
             const float dk2 = d_kth * d_kth;
             proven = have_k && dk2 * 1.000002f < lb;
@@ -1004,9 +1004,11 @@ int knn_tc_select(pe_db* db, const float* cand_d, const int* cand_i, int n_lists
     const size_t smem = (size_t)kTcSelWarps * (db->dim_pad + 2 * n_cand + 2 * n_sel * kTcBlock) * 4;
     PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
     PE_CUDA(cudaFuncSetAttribute(knn_tc_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    /* relative error bound of a scan key in units of |q'| T (see the kernel); PE_KNN_EPS_LOG2 overrides it for experiments */
+    static const float eps_rel = std::ldexp(1.f, getenv("PE_KNN_EPS_LOG2") ? atoi(getenv("PE_KNN_EPS_LOG2")) : -17);
     knn_tc_select_kernel<<<(unsigned)((nq + kTcSelWarps - 1) / kTcSelWarps), 32 * kTcSelWarps, smem, db->stream>>>(
         cand_d, cand_i, n_cand, kc, d_q, db->d_desc, db->dim_pad, db->t_local, db->row_offset, k, n_sel, (long long)nq,
-        db->key_scale.as<float>(), db->d_center, db->max_norm2_c, d_flag, d_out_idx, d_out_dist);
+        db->key_scale.as<float>(), db->d_center, db->max_norm2_c, eps_rel, d_flag, d_out_idx, d_out_dist);
     PE_LAUNCHED();
     return PE_OK;
 }

@@ -151,6 +151,7 @@ def main():
            "matcher": "hamming" if cfg["hamming"] else "l2", "descriptors_per_s": B * world / (ms_f * 1e-3),
            "knn_queries_per_s": nq_all / (ms_m * 1e-3), "patches_per_s_forward_plus_knn": B * world / (ms_both * 1e-3),
            "ms_forward": ms_f, "ms_knn": ms_m, "ms_step": ms_both,
+           "knn_flagged": None if cfg["hamming"] else int(db.knn_flagged()),     # queries of the last call sent to the exact re-scan
            "paths": {"forward": "tcgen05" if capi.get_option("forward_tensor") else "simt",
                      "knn": ("tcgen05 +-1 e4m3" if capi.get_option("knn_tensor") and D <= 128 and K <= 5 else "simt xor+popc") if cfg["hamming"]
                      else ("tcgen05" if capi.get_option("knn_tensor") and D <= 128 and K <= 16 else "simt")}}
