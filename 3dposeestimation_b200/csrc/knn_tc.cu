@@ -999,8 +999,12 @@ int knn_tc_select(pe_db* db, const float* cand_d, const int* cand_i, int n_lists
                   int64_t nq, int k, int32_t* d_out_idx, float* d_out_dist, int* d_flag) {
     const int n_cand = n_lists * kc;
     /* blocks re-ranked exactly: a block holding one of the k nearest is preceded only by blocks whose key lies within the
-     * split's ~2^-22 of it, so k + 3 keeps the margin the k + 2 list entries have (8 for k = 5, 4 for k = 1, 19 for k = 16) */
-    const int n_sel = k + 3 < kTcMaxSel ? k + 3 : kTcMaxSel;
+     * split's ~2^-22 of it, so a small margin beyond k suffices - and since round 2 the certificate proves every result, so
+     * the margin only trades select time against the flag rate, never correctness.  tools/knn_nsel_experiment.py (32,768
+     * queries vs a 125 k-row shard, the 8-GPU shape): k + 3 blocks 0.092 ms, k + 2 0.075, k + 1 0.062, all with 0 queries
+     * flagged; k + 0 flags 13 (k = 1) / 113 (k = 5).  k + 2 keeps one block of slack over what the data needed. */
+    static const int extra = getenv("PE_KNN_NSEL_EXTRA") ? atoi(getenv("PE_KNN_NSEL_EXTRA")) : 2;     /* experiment knob */
+    const int n_sel = k + extra < kTcMaxSel ? (k + extra < 1 ? 1 : k + extra) : kTcMaxSel;
     const size_t smem = (size_t)kTcSelWarps * (db->dim_pad + 2 * n_cand + 2 * n_sel * kTcBlock) * 4;
     PE_REQUIRE(smem <= 200 * 1024, "candidate set too large for the select kernel");
     PE_CUDA(cudaFuncSetAttribute(knn_tc_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
