@@ -398,6 +398,14 @@ def gpu_arm(args, rank, world, local_rank, dist):
     ms_serial, _ = timed_steps(args.steps)
     net_ms, net_calls = net.profile_read()
     db_ms, db_calls = db.profile_read()
+    # the same serialised replay for the opt-in e4m3 conv1 (3 steps): its launch time, for a like-for-like roofline line
+    capi.set_option("forward_fp8", 2)
+    step_device(0); barrier()
+    net.profile_read(); db.profile_read()
+    timed_steps(3)
+    net8_ms, net8_calls = net.profile_read()
+    db.profile_read()
+    capi.set_option("forward_fp8", 0)
     net.profile(False); db.profile(False)
     # ---- timed region 1d: sustained, >= 2 s of back-to-back steps (power / clock steady state)
     n_sus = int(max(args.steps, min(4000, np.ceil(2000.0 / max(1e-3, ms_total / args.steps)))))
@@ -481,7 +489,11 @@ def gpu_arm(args, rank, world, local_rank, dist):
                      "executed_frac": executed_tf / peaks[peak_key] if executed_tf else None,
                      "fp32_fma_frac": None if fwd_tensor else achieved_tf / 74.4,
                      "achieved_hbm_gbs": BATCH * (7 * 64 * 64 * 4 + (81920 if fwd_tensor else 16 * 30 * 32 * 4)) / (conv1_ms * 1e-3) / 1e9 if conv1_ms > 0 else 0.0,
-                     "hbm_peak_gbs": peaks["hbm_gbs"]},
+                     "hbm_peak_gbs": peaks["hbm_gbs"],
+                     "e4m3_optin": {"kernel": "conv1_tc_kernel<7, fp16 + e4m3 cross terms> (pe_set_option forward_fp8; round 1's default, 1-3e-5 descriptor error)",
+                                    "launch_ms": net8_ms[0] / max(1, net8_calls),
+                                    "achieved": conv1_flops / (net8_ms[0] / max(1, net8_calls) * 1e-3) / 1e12 if net8_ms[0] > 0 else None,
+                                    "frac": conv1_flops / (net8_ms[0] / max(1, net8_calls) * 1e-3) / 1e12 / peaks[peak_key] if net8_ms[0] > 0 else None}},
         "paths": {"forward": "tcgen05 fp16 x3" if fwd_tensor else "simt", "knn": "tcgen05" if capi.get_option("knn_tensor") else "simt",
                   "streams": "forward on the net's stream, exchange + scan + merge on the DB's stream (pe_match_patches_dev)",
                   "exchange": ("one peer-memory kernel over NVLink (CUDA IPC windows)" if comm.p2p_active() else "NCCL all-gather") if world > 1 else None},
