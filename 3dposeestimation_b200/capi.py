@@ -146,6 +146,11 @@ SIGNATURES = {
                                       C.c_float, vp, vp]),
     "pe_render_views_tex_dev": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int,
                                           C.c_float, C.c_float, vp, vp]),
+    "pe_template_samples": (C.c_int, [C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, vp, vp, C.c_int64, C.c_int, vp, C.c_int, C.c_int,
+                                      C.c_float, C.c_float, C.c_float, vp, vp, vp]),
+    "pe_template_samples_dev": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, vp, vp, C.c_int64, C.c_int, vp, C.c_int,
+                                          C.c_int, C.c_float, C.c_float, C.c_float, vp, vp, vp]),
+    "pe_pose_labels": (C.c_int, [vp, C.c_int64, C.c_int, vp]),
     "pe_mesh_load_ply": (C.c_int, [C.c_char_p, C.POINTER(vp)]),
     "pe_mesh_info": (C.c_int, [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), fp]),
     "pe_mesh_data": (C.c_int, [vp, vp, vp, vp, vp]),
@@ -783,6 +788,31 @@ def render_views_tex(vertices, colors, uv, faces, tex, cam4, poses, rows=480, co
     check(lib().pe_render_views_tex(device, _ptr(v), _ptr(c), _ptr(t), v.shape[0], _ptr(f), f.shape[0], _ptr(w), w.shape[0], w.shape[1],
                                     _ptr(k), _ptr(p), n, rows, cols, z_near, z_far, _ptr(col), _ptr(dep)))
     return col, dep
+
+
+def pose_labels(poses, index):
+    p = _f32(poses).reshape(-1, 12)
+    out = np.empty((p.shape[0], 8), np.float32)
+    check(lib().pe_pose_labels(_ptr(p), p.shape[0], int(index), _ptr(out)))
+    return out
+
+
+def template_samples(vertices, colors, faces, cam4, poses, index, uv=None, tex=None, z_override=None, rows=480, cols=640, z_near=0.001,
+                     z_far=4.0, m=0.2, device=0):
+    """datasetManager::createSynthSamples*: (patches [n, 64, 64, 7], labels [n, 8], status [n]) of n poses of one mesh"""
+    v, c, f = _f32(vertices), _f32(colors), _i32(faces)
+    k, p = _f32(cam4), _f32(poses).reshape(-1, 12)
+    t = _f32(uv) if uv is not None else None
+    w = np.ascontiguousarray(tex, np.uint8) if tex is not None else None
+    z = _f32(z_override) if z_override is not None else None
+    n = p.shape[0]
+    patches = np.empty((n, 64, 64, 7), np.float32)
+    labels = np.empty((n, 8), np.float32)
+    status = np.empty(n, np.int32)
+    check(lib().pe_template_samples(device, _ptr(v), _ptr(c), _ptr(t), v.shape[0], _ptr(f), f.shape[0], _ptr(w), w.shape[0] if w is not None else 0,
+                                    w.shape[1] if w is not None else 0, _ptr(k), _ptr(p), n, int(index), _ptr(z), rows, cols, z_near, z_far, m,
+                                    _ptr(patches), _ptr(labels), _ptr(status)))
+    return patches, labels, status
 
 
 def load_ply(path):

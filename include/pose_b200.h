@@ -324,6 +324,29 @@ PE_API int pe_mesh_info(const pe_mesh* mesh, int* n_vertices, int* n_faces, int*
 PE_API int pe_mesh_data(const pe_mesh* mesh, float* vertices, float* colors, float* uv, int32_t* faces);
 PE_API void pe_mesh_destroy(pe_mesh* mesh);
 
+/* The producer of a template set: datasetManager::createSynthSamplesWadim / createSynthSamplesPaul (reference
+ * src/datasetmanager.cpp:440-496, 498-535) for n_views poses (row-major 3x4 [R|t], e.g. from pe_sphere_views, or camPos x
+ * trans as the Paul variant builds them) of one mesh: every view is rendered, its patch is cut at the principal point
+ * (cam4[2], cam4[3] truncated to int, as the reference passes them) with z = the pose's z translation (z_override[n_views]
+ * replaces it when not null: the Paul variant's trans(2) after its BigBIRD pose adaptation) and metric size m (0.2), and
+ * labelled {index, Quaternionf(pose.linear()).coeffs() = x y z w, pose.inverse().translation()} (:484-491, :523-530).
+ * out_patches [n_views][64][64][7] (the layout pe_compute_descriptors reads), out_labels [n_views][8] (may be null),
+ * status [n_views] as pe_sample_patches (may be null).  uv / tex as pe_render_views_tex (both null: untextured).
+ * The _dev variant takes the mesh and writes the patches on the device (poses and labels stay host arrays: 20 floats per
+ * view) on the net's stream, so mesh -> patches -> descriptors needs no host round trip; frames never leave the GPU. */
+PE_API int pe_template_samples(int device, const float* vertices, const float* colors, const float* uv, int n_vertices,
+                               const int32_t* faces, int n_faces, const uint8_t* tex, int tex_rows, int tex_cols,
+                               const float* cam4, const float* poses, int64_t n_views, int index, const float* z_override,
+                               int rows, int cols, float z_near, float z_far, float m, float* out_patches,
+                               float* out_labels, int32_t* status);
+PE_API int pe_template_samples_dev(pe_net* net, int device, const float* d_vertices, const float* d_colors, const float* d_uv,
+                                   int n_vertices, const int32_t* d_faces, int n_faces, const uint8_t* d_tex, int tex_rows,
+                                   int tex_cols, const float* cam4, const float* poses_host, int64_t n_views, int index,
+                                   const float* z_override, int rows, int cols, float z_near, float z_far, float m,
+                                   float* d_out_patches, float* out_labels_host, int32_t* d_status);
+/* the labels alone (host arithmetic): poses [n][12] -> labels [n][8] */
+PE_API int pe_pose_labels(const float* poses, int64_t n, int index, float* out_labels);
+
 /* ------------------------------------------------ on-disk sample sets --- */
 /* hdf5Handler::write / read (reference src/hdf5handler.cpp:11-132) without HDF5: one flat little-endian file holding
  * the same two arrays as the reference's datasets - "data" [n][C][H][W] f32 and "label" [n][label_dim] f32 - behind a

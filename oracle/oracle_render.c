@@ -273,3 +273,38 @@ void orc_render(const float* vertices, const float* colors, int nv, const int32_
                 const float* rt, int rows, int cols, float z_near, float z_far, uint8_t* out_color, float* out_depth) {
     orc_render_tex(vertices, colors, 0, nv, faces, nf, 0, 0, 0, cam, rt, rows, cols, z_near, z_far, out_color, out_depth);
 }
+
+/* ------------------------------------------------------------------ template labels ---- */
+/* The 8-float label datasetManager::createSynthSamplesPaul / createSynthSamplesWadim attach to a rendered view
+ * (src/datasetmanager.cpp:484-491, 523-530):  {index, Quaternionf(pose.linear()).coeffs() = (x, y, z, w),
+ * pose.inverse().translation()}.  Eigen (3.2 and 3.3 alike) builds a quaternion from a rotation matrix with Shoemake's
+ * branch on the trace (Quaternion.h quaternionbase_assign_impl<Other,3,3>); Isometry3f::inverse() is
+ * [R^T | -(R^T t)].  rt = row-major 3x4 [R|t]. */
+void orc_pose_label(const float* rt, int index, float* out8) {
+    const float m[3][3] = {{rt[0], rt[1], rt[2]}, {rt[4], rt[5], rt[6]}, {rt[8], rt[9], rt[10]}};
+    float q[4];   /* x y z w */
+    float t = m[0][0] + m[1][1] + m[2][2];
+    if (t > 0.f) {
+        t = sqrtf(t + 1.0f);
+        q[3] = 0.5f * t;
+        t = 0.5f / t;
+        q[0] = (m[2][1] - m[1][2]) * t;
+        q[1] = (m[0][2] - m[2][0]) * t;
+        q[2] = (m[1][0] - m[0][1]) * t;
+    } else {
+        int i = 0;
+        if (m[1][1] > m[0][0]) i = 1;
+        if (m[2][2] > m[i][i]) i = 2;
+        const int j = (i + 1) % 3, k = (j + 1) % 3;
+        t = sqrtf(m[i][i] - m[j][j] - m[k][k] + 1.0f);
+        q[i] = 0.5f * t;
+        t = 0.5f / t;
+        q[3] = (m[k][j] - m[j][k]) * t;
+        q[j] = (m[j][i] + m[i][j]) * t;
+        q[k] = (m[k][i] + m[i][k]) * t;
+    }
+    out8[0] = (float)index;
+    for (int c = 0; c < 4; ++c) out8[1 + c] = q[c];
+    for (int r = 0; r < 3; ++r)      /* -(R^T t): row r of R^T is column r of R */
+        out8[5 + r] = -(m[0][r] * rt[3] + m[1][r] * rt[7] + m[2][r] * rt[11]);
+}

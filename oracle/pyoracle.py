@@ -93,6 +93,8 @@ def lib():
         L.orc_view_pose.restype = None
         L.orc_view_pose.argtypes = [fp, C.c_float, C.c_float, fp]
         L.orc_render.restype = None
+        L.orc_pose_label.argtypes = [fp, C.c_int, fp]
+        L.orc_pose_label.restype = None
         L.orc_render_tex.argtypes = [fp, fp, fp, C.c_int, ip, C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_int, fp, fp, C.c_int, C.c_int,
                                      C.c_float, C.c_float, C.POINTER(C.c_uint8), fp]
         L.orc_render_tex.restype = None
@@ -496,6 +498,14 @@ def render(vertices, colors, faces, cam, rt, rows=480, cols=640, z_near=0.001, z
         lib().orc_render(_p(v, C.c_float), _p(c, C.c_float), v.shape[0], _p(f, C.c_int32), f.shape[0], _p(k, C.c_float), _p(p, C.c_float),
                          rows, cols, z_near, z_far, _p(col, C.c_uint8), _p(dep, C.c_float))
     return col, dep
+
+
+def pose_label(rt, index):
+    """label of a rendered template view: {index, Quaternionf(R).coeffs() xyzw, pose.inverse().translation()}"""
+    p = _f32(rt).reshape(12)
+    out = np.empty(8, np.float32)
+    lib().orc_pose_label(_p(p, C.c_float), int(index), _p(out, C.c_float))
+    return out
 
 
 # ----------------------------------------------------------------------- triplet miner ---

@@ -185,3 +185,18 @@ def test_ply_reader_round_trip(capi, tmp_path):
     (tmp_path / "cut.ply").write_bytes(data[:len(data) // 2])
     with pytest.raises(capi.PoseError):
         capi.load_ply(tmp_path / "cut.ply")
+
+
+def test_pose_labels_equal_oracle(capi, po):
+    """pe_pose_labels (host arithmetic of the template producer) == the oracle's restatement of the reference's label
+    (src/datasetmanager.cpp:484-491, 523-530), bit for bit, on view-sphere poses and random rotations (all four branches)"""
+    from scipy.spatial.transform import Rotation
+    views = capi.sphere_views(2, (0.4, 0.35, 1.1), (-45, 15, 45), False)
+    extra = np.zeros((300, 3, 4), np.float32)
+    extra[:, :, :3] = Rotation.random(300, random_state=8).as_matrix().astype(np.float32)
+    extra[:, :, 3] = np.random.default_rng(2).standard_normal((300, 3)).astype(np.float32)
+    poses = np.concatenate([views, extra])
+    got = capi.pose_labels(poses, 11)
+    want = np.stack([po.pose_label(p, 11) for p in poses])
+    assert np.array_equal(got, want)
+    assert capi.pose_labels(poses[:0], 0).shape == (0, 8)

@@ -126,3 +126,46 @@ def test_textured_mesh_bit_exact_vs_oracle(gpu, po, tmp_path):
         gpu.check(gpu.lib().pe_render_views_tex(0, m["vertices"].ctypes.data, m["colors"].ctypes.data, m["uv"].ctypes.data, len(m["vertices"]),
                                                 m["faces"].ctypes.data, len(m["faces"]), None, 0, 0, CAM.ctypes.data, poses.ctypes.data, 1, 480, 640,
                                                 0.001, 4.0, plain.ctypes.data, gd.ctypes.data))
+
+
+def test_template_samples_equal_the_oracle_chain(gpu, po, synth):
+    """pe_template_samples = datasetManager::createSynthSamplesWadim (src/datasetmanager.cpp:498-535): view -> render ->
+    normals -> patch at the principal point with z = pose t_z -> label; bit-exact against the oracle's stages chained by
+    hand, for an untextured and a textured mesh, and the device variant feeds the forward without a host round trip"""
+    rng = np.random.default_rng(6)
+    v, f = scenes.icosphere(3, 0.08)
+    v = (v * (1 + 0.12 * np.sin(6 * v[:, 1:2]))).astype(np.float32)
+    c = (v / 0.2 + 0.5).clip(0, 1).astype(np.float32)
+    uv = (np.stack([np.arctan2(v[:, 1], v[:, 0]) / np.pi, v[:, 2] / 0.08], 1)).astype(np.float32)
+    tex = rng.integers(0, 256, (48, 64, 3)).astype(np.uint8)
+    poses = gpu.sphere_views(1, (0.4, 0.35, 1.1), (-45, 45, 45))[::7]       # the reference's scales (0.4, 1.1, 1.0) -> one distance
+    n = len(poses)
+    cx, cy = int(CAM[2]), int(CAM[3])
+    for kw in ({}, {"uv": uv, "tex": tex}):
+        patches, labels, status = gpu.template_samples(v, c, f, CAM, poses, 3, **kw)
+        assert patches.shape == (n, 64, 64, 7) and not status.any()
+        for i, rt in enumerate(poses):
+            col, dep = po.render(v, c, f, CAM, rt, **kw)
+            nor = po.depth2normals(dep, float(CAM[0]), float(CAM[1]))
+            want = po.sample_patch(col, dep, nor, cx, cy, float(rt[2, 3]), float(CAM[0]), float(CAM[1]))
+            assert np.array_equal(patches[i], want), i
+            assert np.array_equal(labels[i], po.pose_label(rt, 3))
+        assert np.all(labels[:, 0] == 3) and np.abs(np.linalg.norm(labels[:, 1:5], axis=1) - 1).max() < 1e-6
+    # z override (the Paul variant passes trans(2)): a nearer z cuts a larger rectangle -> another patch
+    p2, _, _ = gpu.template_samples(v, c, f, CAM, poses[:2], 3, z_override=np.array([0.35, 0.35], np.float32))
+    assert not np.array_equal(p2, patches[:2])
+    # device variant on the net's stream: mesh -> patches -> descriptors
+    net = gpu.Net(named="manifold_rgbdnor_16")
+    net.fill(4, 1)
+    d_v, d_c, d_f = gpu.DeviceArray.from_host(v), gpu.DeviceArray.from_host(c), gpu.DeviceArray.from_host(f)
+    d_p = gpu.DeviceArray((n, 64, 64, 7))
+    d_desc = gpu.DeviceArray((n, 16))
+    lab = np.empty((n, 8), np.float32)
+    pp = np.ascontiguousarray(poses.reshape(-1, 12), np.float32)
+    gpu.check(gpu.lib().pe_template_samples_dev(net.h, 0, d_v.ptr, d_c.ptr, None, len(v), d_f.ptr, len(f), None, 0, 0, CAM.ctypes.data, pp.ctypes.data, n, 3,
+                                                None, 480, 640, 0.001, 4.0, 0.2, d_p.ptr, lab.ctypes.data, None))
+    net.compute_descriptors_dev(d_p, n, d_desc)
+    net.sync()
+    plain, plain_lab, _ = gpu.template_samples(v, c, f, CAM, poses, 3)
+    assert np.array_equal(d_p.to_host(), plain) and np.array_equal(lab, plain_lab)
+    assert np.array_equal(d_desc.to_host(), net.compute_descriptors(plain))

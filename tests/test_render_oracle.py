@@ -176,3 +176,29 @@ def test_textured_quad_matches_bilinear_repeat_sampling(po):
     # without texture coordinates the same mesh renders its vertex colours only
     plain = po.render(v, c, f, CAM, eye_pose(0.0))[0]
     assert np.abs(plain[in1][:, ::-1].astype(np.float64) / 255 - c1[in1]).max() < 1.5 / 255
+
+
+def test_pose_label_matches_scipy_and_the_rotation(po):
+    """the label of a template view (src/datasetmanager.cpp:484-491, 523-530): Eigen's Quaternionf(R) (Shoemake's branches)
+    reproduces R, agrees with scipy's conversion up to sign, and the translation part is that of the inverse pose"""
+    from scipy.spatial.transform import Rotation
+    views = po.sphere_views(2, (0.4, 0.35, 1.1), (-45, 15, 45), skip_lower_hemi=False)
+    rng = np.random.default_rng(4)
+    extra = np.zeros((200, 3, 4), np.float32)
+    extra[:, :, :3] = Rotation.random(200, random_state=5).as_matrix().astype(np.float32)       # all four branches
+    extra[:, :, 3] = rng.standard_normal((200, 3)).astype(np.float32)
+    branches = set()
+    for rt in list(views[::9]) + list(extra):
+        lab = po.pose_label(rt, 7)
+        r = rt[:, :3].astype(np.float64)
+        q = lab[1:5].astype(np.float64)
+        assert lab[0] == 7 and abs(np.linalg.norm(q) - 1) < 2e-6
+        assert np.abs(Rotation.from_quat(q).as_matrix() - r).max() < 3e-6
+        ref = Rotation.from_matrix(r).as_quat()
+        assert min(np.abs(q - ref).max(), np.abs(q + ref).max()) < 3e-6
+        np.testing.assert_allclose(lab[5:], -(r.T @ rt[:, 3].astype(np.float64)), atol=3e-6)
+        tr = np.trace(r)
+        branches.add(3 if tr > 0 else int(np.argmax(np.diag(r))))
+        if tr > 0:
+            assert q[3] > 0                       # Eigen's trace branch gives w > 0
+    assert branches == {0, 1, 2, 3}
