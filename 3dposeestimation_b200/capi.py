@@ -151,6 +151,7 @@ SIGNATURES = {
     "pe_template_samples_dev": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, vp, vp, C.c_int64, C.c_int, vp, C.c_int,
                                           C.c_int, C.c_float, C.c_float, C.c_float, vp, vp, vp]),
     "pe_pose_labels": (C.c_int, [vp, C.c_int64, C.c_int, vp]),
+    "pe_scene_samples": (C.c_int, [C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp, vp, vp]),
     "pe_mesh_load_ply": (C.c_int, [C.c_char_p, C.POINTER(vp)]),
     "pe_mesh_info": (C.c_int, [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), fp]),
     "pe_mesh_data": (C.c_int, [vp, vp, vp, vp, vp]),
@@ -812,6 +813,20 @@ def template_samples(vertices, colors, faces, cam4, poses, index, uv=None, tex=N
     check(lib().pe_template_samples(device, _ptr(v), _ptr(c), _ptr(t), v.shape[0], _ptr(f), f.shape[0], _ptr(w), w.shape[0] if w is not None else 0,
                                     w.shape[1] if w is not None else 0, _ptr(k), _ptr(p), n, int(index), _ptr(z), rows, cols, z_near, z_far, m,
                                     _ptr(patches), _ptr(labels), _ptr(status)))
+    return patches, labels, status
+
+
+def scene_samples(color, depth, cam4, poses, index, centroid=None, z_from_depth=False, m=0.2, device=0):
+    """datasetManager::extractRealSamplesPaul / Wadim: frames + ground-truth poses -> (patches, labels, status)"""
+    col, dep = np.ascontiguousarray(color, np.uint8), _f32(depth)
+    k, p = _f32(cam4), _f32(poses).reshape(-1, 12)
+    c = _f32(centroid) if centroid is not None else None
+    n, rows, cols = dep.shape
+    patches = np.empty((n, 64, 64, 7), np.float32)
+    labels = np.empty((n, 8), np.float32)
+    status = np.empty(n, np.int32)
+    check(lib().pe_scene_samples(device, _ptr(col), _ptr(dep), n, rows, cols, _ptr(k), _ptr(p), _ptr(c), int(z_from_depth), int(index), m,
+                                 _ptr(patches), _ptr(labels), _ptr(status)))
     return patches, labels, status
 
 

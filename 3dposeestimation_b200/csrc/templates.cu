@@ -53,6 +53,30 @@ void pose_label(const float* rt, int index, float* out8) {
     }
 }
 
+/* extractRealSamplesPaul / Wadim (reference src/datasetmanager.cpp:348-411): projected centroid truncated to int and the
+ * centroid's depth; same statements as oracle/oracle_render.c orc_project_centroid (products and sums rounded separately) */
+float project_centroid(const float* cam, const float* rt, const float* centroid3, int32_t* out_xy) {
+    volatile float c[3];
+    if (centroid3) {
+        for (int r = 0; r < 3; ++r) {
+            volatile float a = rt[4 * r] * centroid3[0], b = rt[4 * r + 1] * centroid3[1], d = rt[4 * r + 2] * centroid3[2];
+            volatile float s = a + b;
+            s = s + d;
+            c[r] = s + rt[4 * r + 3];
+        }
+    } else {
+        c[0] = rt[3]; c[1] = rt[7]; c[2] = rt[11];
+    }
+    volatile float x0 = cam[0] * c[0], x1 = 0.f * c[1], x2 = cam[2] * c[2];
+    volatile float y0 = 0.f * c[0], y1 = cam[1] * c[1], y2 = cam[3] * c[2];
+    volatile float z0 = 0.f * c[0], z1 = 0.f * c[1], z2 = 1.f * c[2];
+    volatile float px = x0 + x1, py = y0 + y1, pz = z0 + z1;
+    px = px + x2; py = py + y2; pz = pz + z2;
+    out_xy[0] = (int32_t)(px / pz);
+    out_xy[1] = (int32_t)(py / pz);
+    return c[2];
+}
+
 }  // namespace
 }  // namespace pe
 
@@ -64,6 +88,28 @@ int pe_pose_labels(const float* poses, int64_t n, int index, float* out_labels) 
     PE_REQUIRE(n >= 0 && (n == 0 || (poses && out_labels)), "null pointer");
     for (int64_t i = 0; i < n; ++i) pose_label(poses + i * 12, index, out_labels + i * 8);
     return PE_OK;
+}
+
+int pe_scene_samples(int device, const uint8_t* color, const float* depth, int n_frames, int rows, int cols, const float* cam4,
+                     const float* poses, const float* centroid3, int z_from_depth, int index, float m, float* out_patches,
+                     float* out_labels, int32_t* status) {
+    PE_REQUIRE(n_frames >= 0 && rows > 0 && cols > 0 && cam4, "bad arguments");
+    if (n_frames == 0) return PE_OK;
+    PE_REQUIRE(color && depth && poses && out_patches, "null pointer");
+    std::vector<int32_t> ctr((size_t)n_frames * 2);
+    std::vector<float> z((size_t)n_frames);
+    for (int i = 0; i < n_frames; ++i) {
+        z[i] = project_centroid(cam4, poses + (size_t)i * 12, centroid3, &ctr[2 * i]);
+        if (z_from_depth) {      /* the Wadim variant: the surface point under the projected centroid (:388-389, asserted > 0 there) */
+            const int x = ctr[2 * i], y = ctr[2 * i + 1];
+            PE_REQUIRE(x >= 0 && y >= 0 && x < cols && y < rows, "frame %d: projected centroid (%d, %d) outside the frame", i, x, y);
+            z[i] = depth[((size_t)i * rows + y) * cols + x];
+            PE_REQUIRE(z[i] > 0.f, "frame %d: no depth under the projected centroid (the reference asserts z > 0)", i);
+        }
+    }
+    if (out_labels) PE_CHECK(pe_pose_labels(poses, n_frames, index, out_labels));
+    return pe_sample_patches(device, color, depth, nullptr, n_frames, rows, cols, nullptr, ctr.data(), z.data(), n_frames, cam4[0], cam4[1], m,
+                             out_patches, status);
 }
 
 int pe_template_samples_dev(pe_net* net, int device, const float* d_vertices, const float* d_colors, const float* d_uv, int n_vertices,

@@ -344,6 +344,15 @@ PE_API int pe_template_samples_dev(pe_net* net, int device, const float* d_verti
                                    int tex_cols, const float* cam4, const float* poses_host, int64_t n_views, int index,
                                    const float* z_override, int rows, int cols, float z_near, float z_far, float m,
                                    float* d_out_patches, float* out_labels_host, int32_t* d_status);
+/* The producer of a test / training set from real frames: datasetManager::extractRealSamplesPaul / extractRealSamplesWadim
+ * (reference src/datasetmanager.cpp:348-411): frame i (colour u8 BGR, metric depth) with ground-truth pose poses[i]
+ * ([R|t]) -> the patch around the projected centroid (cam * centroid / z truncated to int; centroid = the pose's
+ * translation, or pose * centroid3 when centroid3 is not null: the BigBIRD branch) at depth z = centroid z (Paul) or, with
+ * z_from_depth != 0, the depth under that pixel (Wadim; PE_ERR_INVALID where the reference asserts), normals computed on
+ * the fly, and the same label as pe_template_samples. */
+PE_API int pe_scene_samples(int device, const uint8_t* color, const float* depth, int n_frames, int rows, int cols,
+                            const float* cam4, const float* poses, const float* centroid3, int z_from_depth, int index,
+                            float m, float* out_patches, float* out_labels, int32_t* status);
 /* the labels alone (host arithmetic): poses [n][12] -> labels [n][8] */
 PE_API int pe_pose_labels(const float* poses, int64_t n, int index, float* out_labels);
 

@@ -308,3 +308,24 @@ void orc_pose_label(const float* rt, int index, float* out8) {
     for (int r = 0; r < 3; ++r)      /* -(R^T t): row r of R^T is column r of R */
         out8[5 + r] = -(m[0][r] * rt[3] + m[1][r] * rt[7] + m[2][r] * rt[11]);
 }
+
+/* datasetManager::extractRealSamplesPaul / extractRealSamplesWadim (src/datasetmanager.cpp:348-411): where the patch of
+ * a real frame is cut.  centroid = pose translation (LineMOD, Washington, and the Wadim variant) or pose * model
+ * centroid (BigBIRD: centroid3 != NULL); projCentroid = cam * centroid (Eigen's 3x3 product with the zeros of the
+ * intrinsic matrix included), divided by its z; the float coordinates are passed to int parameters (truncation).
+ * Returns z = centroid(2) (the Paul variant; the Wadim variant reads the depth frame at the pixel instead). */
+float orc_project_centroid(const float* cam /* fx fy ox oy */, const float* rt, const float* centroid3, int32_t* out_xy) {
+    float c[3];
+    if (centroid3) {
+        for (int r = 0; r < 3; ++r)
+            c[r] = (rt[4 * r] * centroid3[0] + rt[4 * r + 1] * centroid3[1] + rt[4 * r + 2] * centroid3[2]) + rt[4 * r + 3];
+    } else {
+        c[0] = rt[3]; c[1] = rt[7]; c[2] = rt[11];
+    }
+    const float px = (cam[0] * c[0] + 0.f * c[1]) + cam[2] * c[2];
+    const float py = (0.f * c[0] + cam[1] * c[1]) + cam[3] * c[2];
+    const float pz = (0.f * c[0] + 0.f * c[1]) + 1.f * c[2];
+    out_xy[0] = (int32_t)(px / pz);
+    out_xy[1] = (int32_t)(py / pz);
+    return c[2];
+}

@@ -110,6 +110,8 @@ int orc_init_sphere(int depth, float* out_xyz, int cap);
 void orc_view_pose(const float* vertex, float scale, float angle_deg, float* out_rt /* row-major 3x4 */);
 /* label of a rendered template view (src/datasetmanager.cpp:484-491, 523-530): {index, quaternion xyzw of R, -(R^T t)} */
 void orc_pose_label(const float* rt /* row-major 3x4 */, int index, float* out8);
+/* patch centre of a real frame (src/datasetmanager.cpp:348-411): projected centroid truncated to int; returns centroid z */
+float orc_project_centroid(const float* cam, const float* rt, const float* centroid3 /* or NULL */, int32_t* out_xy);
 void orc_render_tex(const float* vertices, const float* colors, const float* uv /* [nv][2] or NULL */, int nv, const int32_t* faces, int nf,
                     const uint8_t* tex /* [tex_rows][tex_cols][3] BGR or NULL */, int tex_rows, int tex_cols, const float* cam, const float* rt,
                     int rows, int cols, float z_near, float z_far, uint8_t* out_color, float* out_depth);

@@ -93,6 +93,8 @@ def lib():
         L.orc_view_pose.restype = None
         L.orc_view_pose.argtypes = [fp, C.c_float, C.c_float, fp]
         L.orc_render.restype = None
+        L.orc_project_centroid.argtypes = [fp, fp, fp, ip]
+        L.orc_project_centroid.restype = C.c_float
         L.orc_pose_label.argtypes = [fp, C.c_int, fp]
         L.orc_pose_label.restype = None
         L.orc_render_tex.argtypes = [fp, fp, fp, C.c_int, ip, C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_int, fp, fp, C.c_int, C.c_int,
@@ -498,6 +500,15 @@ def render(vertices, colors, faces, cam, rt, rows=480, cols=640, z_near=0.001, z
         lib().orc_render(_p(v, C.c_float), _p(c, C.c_float), v.shape[0], _p(f, C.c_int32), f.shape[0], _p(k, C.c_float), _p(p, C.c_float),
                          rows, cols, z_near, z_far, _p(col, C.c_uint8), _p(dep, C.c_float))
     return col, dep
+
+
+def project_centroid(cam, rt, centroid=None):
+    """(center_x, center_y, z) of extractRealSamplesPaul: cam * centroid / z truncated to int, z = centroid z"""
+    k, p = _f32(cam), _f32(rt).reshape(12)
+    c = _f32(centroid) if centroid is not None else None
+    xy = np.empty(2, np.int32)
+    z = lib().orc_project_centroid(_p(k, C.c_float), _p(p, C.c_float), _p(c, C.c_float) if c is not None else None, _p(xy, C.c_int32))
+    return int(xy[0]), int(xy[1]), float(z)
 
 
 def pose_label(rt, index):

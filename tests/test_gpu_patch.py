@@ -75,3 +75,43 @@ def test_frames_to_descriptors_on_device(gpu, po, synth):
     want = po.OracleNet(ref, blobs).forward(patches)
     scale = np.abs(want).max(axis=-1, keepdims=True)
     assert float((np.abs(d_desc.to_host() - want) / scale).max()) < 1e-4
+
+
+def test_scene_samples_equal_the_oracle_chain(gpu, po):
+    """pe_scene_samples = datasetManager::extractRealSamplesPaul / Wadim (src/datasetmanager.cpp:348-411): projected
+    centroid (truncated to int) -> normals -> patch -> label, against the oracle's stages chained by hand"""
+    from scipy.spatial.transform import Rotation
+    cam = np.array([scenes.CAM["fx"], scenes.CAM["fy"], scenes.CAM["ox"], scenes.CAM["oy"]], np.float32)
+    frames = [scenes.make_frame(40 + i) for i in range(4)]
+    color = np.stack([f[0] for f in frames])
+    depth = np.stack([f[1] for f in frames])
+    poses = np.zeros((4, 3, 4), np.float32)
+    poses[:, :, :3] = Rotation.random(4, random_state=3).as_matrix().astype(np.float32)
+    for i, (_, dep, (cx, cy)) in enumerate(frames):       # ground-truth translation = the sphere's surface point back-projected
+        z = float(dep[cy, cx])
+        poses[i, :, 3] = [(cx + 0.3 - cam[2]) * z / cam[0], (cy + 0.6 - cam[3]) * z / cam[1], z]
+    centroid = np.array([0.01, -0.02, 0.015], np.float32)
+    for kw, ora in (({}, dict(centroid=None, from_depth=False)), ({"z_from_depth": True}, dict(centroid=None, from_depth=True)),
+                    ({"centroid": centroid}, dict(centroid=centroid, from_depth=False))):
+        patches, labels, status = gpu.scene_samples(color, depth, cam, poses, 5, **kw)
+        assert not status.any()
+        for i in range(4):
+            x, y, z = po.project_centroid(cam, poses[i], ora["centroid"])
+            if ora["from_depth"]:
+                z = float(depth[i, y, x])
+            nor = po.depth2normals(depth[i], float(cam[0]), float(cam[1]))
+            want = po.sample_patch(color[i], depth[i], nor, x, y, z, float(cam[0]), float(cam[1]))
+            assert np.array_equal(patches[i], want), (kw, i)
+            assert np.array_equal(labels[i], po.pose_label(poses[i], 5))
+    # the projected centroid of frame 0 is where the scene put it (truncation, not rounding)
+    x, y, _ = po.project_centroid(cam, poses[0])
+    assert (x, y) == (frames[0][2][0], frames[0][2][1])
+    # the Wadim variant refuses a centroid over missing depth / outside the frame (the reference asserts)
+    bad = poses.copy()
+    bad[0, :, 3] = [(80 - cam[2]) * 1.0 / cam[0], (70 - cam[3]) * 1.0 / cam[1], 1.0]      # inside the sensor-hole rectangle of make_frame
+    with pytest.raises(gpu.PoseError) as e:
+        gpu.scene_samples(color, depth, cam, bad, 5, z_from_depth=True)
+    assert e.value.code == gpu.PE_ERR_INVALID and "depth" in str(e.value)
+    bad[0, :, 3] = [5.0, 0.0, 1.0]
+    with pytest.raises(gpu.PoseError):
+        gpu.scene_samples(color, depth, cam, bad, 5, z_from_depth=True)
