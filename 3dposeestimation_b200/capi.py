@@ -184,6 +184,11 @@ HOST_SIGNATURES = {
     "pe_host_save_logs": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_char_p, C.c_int, C.c_float]),
     "pe_host_build_batch": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, vp, C.c_int, vp, vp, C.c_int, C.c_int,
                                       C.c_uint64, C.c_int, vp, vp, vp, vp]),
+    "pe_host_create_synth_samples": (C.c_int, [C.c_char_p, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_char_p, vp, C.c_int,
+                                               C.c_int, vp, vp, C.c_int64, C.POINTER(C.c_int64)]),
+    "pe_host_extract_real_samples": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, C.c_char_p, C.c_char_p, vp, vp,
+                                               C.c_int64, C.POINTER(C.c_int64)]),
+    "pe_host_create_views": (C.c_int, [C.c_char_p, vp, C.c_int, vp, vp, C.c_int, vp, vp, vp, C.c_int64, C.POINTER(C.c_int64)]),
 }
 
 

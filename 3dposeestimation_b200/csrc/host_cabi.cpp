@@ -186,3 +186,96 @@ HOST_API int pe_host_build_batch(const float* t_patches, const float* t_labels, 
         }
     });
 }
+
+/* ---- sample producers through the mirror (include/datasetmanager_b200.hpp) ---- */
+#include "../../include/datasetmanager_b200.hpp"
+
+namespace {
+sz::Matrix3f make_cam(const float* cam9) {
+    sz::Matrix3f cam;
+    std::copy(cam9, cam9 + 9, cam.v.begin());
+    return cam;
+}
+/* out_patches / out_labels may be null to query the count; cap = samples the arrays hold */
+void copy_samples(const std::vector<sz::Sample>& s, float* out_patches, float* out_labels, int64_t cap, int64_t* n) {
+    *n = (int64_t)s.size();
+    if (!out_patches && !out_labels) return;
+    if (cap < *n) throw std::runtime_error("output arrays hold " + std::to_string(cap) + " samples, " + std::to_string(*n) + " produced");
+    const size_t img = (size_t)64 * 64 * 7;
+    for (size_t i = 0; i < s.size(); ++i) {
+        if (out_patches) std::memcpy(out_patches + i * img, s[i].data.buf.data(), img * sizeof(float));
+        if (out_labels) std::memcpy(out_labels + i * 8, s[i].label.buf.data(), 8 * sizeof(float));
+    }
+}
+}  // namespace
+
+/* Model::loadModel + datasetManager::createSynthSamplesWadim (paul == 0) or createSynthSamplesPaul (paul != 0, reads
+ * dataset_path + "paul/camPositionsElAz.txt"); tex (may be null) [tex_rows][tex_cols][3] for a textured model */
+HOST_API int pe_host_create_synth_samples(const char* ply_path, const float* cam9, int index, int subdiv, int inplane, int paul,
+                                          const char* dataset_path, const char* dataset_name, const uint8_t* tex, int tex_rows,
+                                          int tex_cols, float* out_patches, float* out_labels, int64_t cap, int64_t* n) {
+    return guarded([&] {
+        sz::Model model;
+        if (!model.loadModel(ply_path)) throw std::runtime_error(std::string("pose_b200: ") + pe_last_error());
+        if (tex) model.setTexture(tex, tex_rows, tex_cols);
+        sz::Matrix3f cam = make_cam(cam9);
+        sz::datasetManager db;
+        db.inplane = inplane != 0;
+        if (dataset_path) db.dataset_path = dataset_path;
+        if (dataset_name) db.dataset_name = dataset_name;
+        copy_samples(paul ? db.createSynthSamplesPaul(model, cam, index) : db.createSynthSamplesWadim(model, cam, index, subdiv),
+                     out_patches, out_labels, cap, n);
+    });
+}
+
+/* datasetManager::extractRealSamplesPaul (wadim == 0; ply_path gives Model::centroid for dataset_name "BigBIRD") or
+ * extractRealSamplesWadim (wadim != 0) over n_frames frames with one ground-truth pose each */
+HOST_API int pe_host_extract_real_samples(const uint8_t* color, const float* depth, int n_frames, int rows, int cols,
+                                          const float* poses, const float* cam9, int index, int wadim, const char* ply_path,
+                                          const char* dataset_name, float* out_patches, float* out_labels, int64_t cap, int64_t* n) {
+    return guarded([&] {
+        const size_t px = (size_t)rows * cols;
+        std::vector<sz::Frame> frames(n_frames);
+        for (int i = 0; i < n_frames; ++i) {
+            sz::Frame& f = frames[i];
+            f.nr = i; f.rows = rows; f.cols = cols;
+            f.color.assign(color + i * px * 3, color + (i + 1) * px * 3);
+            f.depth.assign(depth + i * px, depth + (i + 1) * px);
+            sz::Isometry3f pose;
+            std::copy(poses + (size_t)i * 12, poses + (size_t)i * 12 + 12, pose.m.begin());
+            f.gt.push_back({"object", pose});
+        }
+        sz::Model model;
+        if (ply_path && !model.loadModel(ply_path)) throw std::runtime_error(std::string("pose_b200: ") + pe_last_error());
+        sz::Matrix3f cam = make_cam(cam9);
+        sz::datasetManager db;
+        if (dataset_name) db.dataset_name = dataset_name;
+        copy_samples(wadim ? db.extractRealSamplesWadim(frames, cam, index) : db.extractRealSamplesPaul(frames, cam, index, model),
+                     out_patches, out_labels, cap, n);
+    });
+}
+
+/* SphereRenderer::createViews (clip = false) keeping the frames: out_color [n][480][640][3], out_depth [n][480][640],
+ * out_poses [n][12]; all three null to query the count */
+HOST_API int pe_host_create_views(const char* ply_path, const float* cam9, int sphere_dep, const float* scale3, const float* rot3,
+                                  int skip_lower_hemi, uint8_t* out_color, float* out_depth, float* out_poses, int64_t cap, int64_t* n) {
+    return guarded([&] {
+        const sz::Vector3f sc(scale3[0], scale3[1], scale3[2]), ro(rot3[0], rot3[1], rot3[2]);
+        if (!out_color && !out_depth && !out_poses) {
+            *n = (int64_t)sz::SphereRenderer::createPoses(sphere_dep, sc, ro, skip_lower_hemi != 0).size();
+            return;
+        }
+        sz::Model model;
+        if (!model.loadModel(ply_path)) throw std::runtime_error(std::string("pose_b200: ") + pe_last_error());
+        sz::SphereRenderer sphere(make_cam(cam9));
+        const std::vector<sz::RenderView> views = sphere.createViews(model, sphere_dep, sc, ro, skip_lower_hemi != 0, false);
+        *n = (int64_t)views.size();
+        if (cap < *n) throw std::runtime_error("output arrays hold " + std::to_string(cap) + " views, " + std::to_string(*n) + " produced");
+        const size_t px = (size_t)sz::kFrameRows * sz::kFrameCols;
+        for (size_t i = 0; i < views.size(); ++i) {
+            if (out_color) std::memcpy(out_color + i * px * 3, views[i].col.data(), px * 3);
+            if (out_depth) std::memcpy(out_depth + i * px, views[i].dep.data(), px * sizeof(float));
+            if (out_poses) std::memcpy(out_poses + i * 12, views[i].pose.m.data(), 12 * sizeof(float));
+        }
+    });
+}

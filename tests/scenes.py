@@ -1,6 +1,8 @@
 """Seeded synthetic RGB-D frames for the patch-extraction tests (numpy only; shared by tests/golden/make_golden_patch.py,
 the CPU oracle tests and the GPU parity tests).  A frame is a tilted background plane with a sphere and a box in front
 of it, a rectangle of missing depth (zeros, as a real sensor gives), and smooth random colour."""
+import struct
+
 import numpy as np
 
 CAM = dict(fx=572.4114, fy=573.57043, ox=325.2611, oy=242.04899)     # LineMOD intrinsics (640 x 480)
@@ -80,3 +82,34 @@ def textured_quad(seed=5, th=37, tw=53):
     f = np.array([[0, 1, 2], [0, 2, 3]], np.int32)
     tex = rng.integers(0, 256, (th, tw, 3)).astype(np.uint8)
     return v, c, uv, f, tex
+
+
+def write_ply(path, v, f, colors=None, uv=None, binary=False, uv_names=("u", "v"), index_name="vertex_indices"):
+    hdr = ["ply", "format binary_little_endian 1.0" if binary else "format ascii 1.0", "comment written by the test",
+           f"element vertex {len(v)}", "property float x", "property float y", "property float z"]
+    if colors is not None:
+        hdr += ["property uchar red", "property uchar green", "property uchar blue"]
+    if uv is not None:
+        hdr += [f"property float {uv_names[0]}", f"property float {uv_names[1]}"]
+    hdr += [f"element face {len(f)}", f"property list uchar int {index_name}", "end_header"]
+    with open(path, "wb") as fh:
+        fh.write(("\n".join(hdr) + "\n").encode())
+        for i in range(len(v)):
+            if binary:
+                fh.write(struct.pack("<3f", *v[i]))
+                if colors is not None:
+                    fh.write(struct.pack("<3B", *colors[i]))
+                if uv is not None:
+                    fh.write(struct.pack("<2f", *uv[i]))
+            else:
+                row = [repr(float(x)) for x in v[i]]
+                if colors is not None:
+                    row += [str(int(x)) for x in colors[i]]
+                if uv is not None:
+                    row += [repr(float(x)) for x in uv[i]]
+                fh.write((" ".join(row) + "\n").encode())
+        for t in f:
+            if binary:
+                fh.write(struct.pack("<B3i", 3, *t))
+            else:
+                fh.write(("3 " + " ".join(str(int(x)) for x in t) + "\n").encode())

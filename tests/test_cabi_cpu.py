@@ -1,6 +1,7 @@
 """CPU-side checks of the C-ABI library: it loads, exports every symbol include/pose_b200.h
 declares, and its host logic (prototxt reader, blob bookkeeping, fillers, weight files, label
 generator, error returns) behaves.  No compute entry point is called here."""
+import ctypes as C
 import os
 import re
 
@@ -47,6 +48,29 @@ def test_host_mirror_library_loads_and_exports_its_doors(capi):
         code = H.pe_host_build_batch(vp(z), vp(lab), 2, 1, vp(z), vp(lab), 1, 7, vp(rot), 1, None, None, 10, 0, 1, 0, vp(out), vp(idx),
                                      vp(ms), None)
         assert code != 0 and b"pose_b200" in H.pe_host_last_error()
+
+
+def test_producer_mirror_host_side(capi, tmp_path):
+    """include/datasetmanager_b200.hpp without a GPU: the view count of SphereRenderer::createViews' pose list, Model::loadModel
+    reading a PLY, and - with no device - the producers reporting the library's error instead of producing anything"""
+    from tests import scenes
+    H = capi.host_lib()
+    vp = lambda a: a.ctypes.data_as(capi.vp)
+    cam9 = np.array([572.4, 0, 325.3, 0, 573.6, 242.0, 0, 0, 1], np.float32)
+    sc, ro = np.float32([0.4, 1.1, 1.0]), np.float32([-45, 15, 45])
+    n = C.c_int64()
+    assert H.pe_host_create_views(None, vp(cam9), 1, vp(sc), vp(ro), 1, None, None, None, 0, C.byref(n)) == 0
+    assert n.value == len(capi.sphere_views(1, sc, ro)) and n.value % 7 == 0
+    patches, labels = np.zeros((4, 64, 64, 7), np.float32), np.zeros((4, 8), np.float32)
+    code = H.pe_host_create_synth_samples(b"/nonexistent.ply", vp(cam9), 0, 0, 0, 0, None, None, None, 0, 0, vp(patches), vp(labels), 4,
+                                          C.byref(n))
+    assert code != 0 and b"nonexistent.ply" in H.pe_host_last_error()
+    if capi.device_count() == 0:
+        v, f = scenes.icosphere(1, 0.05)
+        scenes.write_ply(tmp_path / "m.ply", v, f)
+        code = H.pe_host_create_synth_samples(str(tmp_path / "m.ply").encode(), vp(cam9), 0, 0, 0, 0, None, None, None, 0, 0, vp(patches),
+                                              vp(labels), 4, C.byref(n))
+        assert code != 0 and b"pose_b200" in H.pe_host_last_error() and not patches.any()
 
 
 def test_header_cites_reference_interfaces():

@@ -113,38 +113,6 @@ def test_caffemodel_converter(capi, po, synth, tmp_path):
     assert all(np.array_equal(x, np.asarray(b, np.float32).ravel()) for x, b in zip(flat, blobs)) and len(flat) == len(blobs)
 
 
-def _write_ply(path, v, f, colors=None, uv=None, binary=False, uv_names=("u", "v"), index_name="vertex_indices"):
-    import struct
-    hdr = ["ply", "format binary_little_endian 1.0" if binary else "format ascii 1.0", "comment written by the test",
-           f"element vertex {len(v)}", "property float x", "property float y", "property float z"]
-    if colors is not None:
-        hdr += ["property uchar red", "property uchar green", "property uchar blue"]
-    if uv is not None:
-        hdr += [f"property float {uv_names[0]}", f"property float {uv_names[1]}"]
-    hdr += [f"element face {len(f)}", f"property list uchar int {index_name}", "end_header"]
-    with open(path, "wb") as fh:
-        fh.write(("\n".join(hdr) + "\n").encode())
-        for i in range(len(v)):
-            if binary:
-                fh.write(struct.pack("<3f", *v[i]))
-                if colors is not None:
-                    fh.write(struct.pack("<3B", *colors[i]))
-                if uv is not None:
-                    fh.write(struct.pack("<2f", *uv[i]))
-            else:
-                row = [repr(float(x)) for x in v[i]]
-                if colors is not None:
-                    row += [str(int(x)) for x in colors[i]]
-                if uv is not None:
-                    row += [repr(float(x)) for x in uv[i]]
-                fh.write((" ".join(row) + "\n").encode())
-        for t in f:
-            if binary:
-                fh.write(struct.pack("<B3i", 3, *t))
-            else:
-                fh.write(("3 " + " ".join(str(int(x)) for x in t) + "\n").encode())
-
-
 def test_ply_reader_round_trip(capi, tmp_path):
     """pe_mesh_load_ply = what Model::loadModel keeps of cv::viz::Mesh::load (reference src/model.cpp:296-352): points,
     colours / 255 (127 grey when absent), per-vertex texture coordinates, triangle faces, centroid; ascii and binary"""
@@ -155,7 +123,7 @@ def test_ply_reader_round_trip(capi, tmp_path):
     uv = rng.random((len(v), 2)).astype(np.float32)
     for binary in (False, True):
         p = tmp_path / f"m{int(binary)}.ply"
-        _write_ply(p, v, f, col, uv, binary, uv_names=("texture_u", "texture_v") if binary else ("u", "v"),
+        scenes.write_ply(p, v, f, col, uv, binary, uv_names=("texture_u", "texture_v") if binary else ("u", "v"),
                    index_name="vertex_index" if binary else "vertex_indices")
         m = capi.load_ply(p)
         assert np.array_equal(m["vertices"], v) and np.array_equal(m["faces"], f)
@@ -163,7 +131,7 @@ def test_ply_reader_round_trip(capi, tmp_path):
         assert np.array_equal(m["uv"], uv)
         np.testing.assert_allclose(m["centroid"], v.astype(np.float64).mean(0), atol=1e-7)
     p = tmp_path / "plain.ply"
-    _write_ply(p, v, f)
+    scenes.write_ply(p, v, f)
     m = capi.load_ply(p)
     assert m["uv"] is None and not m["has_colors"] and np.all(m["colors"] == np.float32(127 / 255))
     # errors: missing file, not a PLY, a quad face, an index out of range, a truncated body
@@ -178,7 +146,7 @@ def test_ply_reader_round_trip(capi, tmp_path):
     with pytest.raises(capi.PoseError) as e:
         capi.load_ply(tmp_path / "quad.ply")
     assert "triangle" in str(e.value)
-    _write_ply(tmp_path / "oor.ply", v, np.array([[0, 1, len(v)]], np.int32))
+    scenes.write_ply(tmp_path / "oor.ply", v, np.array([[0, 1, len(v)]], np.int32))
     with pytest.raises(capi.PoseError):
         capi.load_ply(tmp_path / "oor.ply")
     data = (tmp_path / "m1.ply").read_bytes()

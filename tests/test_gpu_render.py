@@ -107,11 +107,10 @@ def test_textured_mesh_bit_exact_vs_oracle(gpu, po, tmp_path):
     gc, gd = gpu.render_views_tex(v, c, uv, f, tex, CAM, rt)
     oc, od = po.render(v, c, f, CAM, rt[0], uv=uv, tex=tex)
     assert np.array_equal(gd[0], od) and np.array_equal(gc[0], oc)
-    from tests.test_formats_cpu import _write_ply
     rng = np.random.default_rng(9)
     bv, bf = scenes.icosphere(3, 0.09)
     buv = (np.stack([np.arctan2(bv[:, 1], bv[:, 0]) / np.pi, bv[:, 2] / 0.09], 1) * 1.5).astype(np.float32)
-    _write_ply(tmp_path / "blob.ply", bv, bf, rng.integers(60, 256, (len(bv), 3)), buv, binary=True)
+    scenes.write_ply(tmp_path / "blob.ply", bv, bf, rng.integers(60, 256, (len(bv), 3)), buv, binary=True)
     m = gpu.load_ply(tmp_path / "blob.ply")
     big = rng.integers(0, 256, (64, 96, 3)).astype(np.uint8)
     poses = po.sphere_views(1, (0.4, 0.3, 0.7), (-30, 60, 30))[::11]
