@@ -114,6 +114,78 @@ def run_eval(gpu, po, synth, rng):
         assert db.knn_accuracy(ms, out, nr_q) == po.knn_accuracy(ms, out, nr_q), tag + " accuracy"
 
 
+def _rand_pose(rng, dist):
+    a = rng.standard_normal(4)
+    w, x, y, z = a / np.linalg.norm(a)
+    r = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                  [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                  [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+    t = np.array([rng.normal(0, 0.05), rng.normal(0, 0.05), dist])
+    return np.concatenate([r, t[:, None]], 1).astype(np.float32)
+
+
+def run_render(gpu, po, rng):
+    """triangle soups the fixed scenes do not hold: slivers, zero-area and repeated-vertex faces, huge triangles, faces behind
+    the camera / through the near plane / off screen, odd frame sizes, textured or not - CUDA == oracle bit for bit"""
+    from tests import scenes
+    kind = int(rng.integers(0, 4))
+    if kind == 0:                                   # random soup around the origin
+        nv, nf = int(rng.integers(3, 200)), int(rng.integers(1, 300))
+        v = (rng.standard_normal((nv, 3)) * rng.choice([0.02, 0.1, 0.6])).astype(np.float32)
+        f = rng.integers(0, nv, (nf, 3)).astype(np.int32)            # repeated vertices -> degenerate faces among them
+    elif kind == 1:                                 # slivers and coplanar overlaps (z fights resolved by face id)
+        nv = 60
+        v = np.zeros((nv, 3), np.float32)
+        v[:, 0] = rng.uniform(-0.1, 0.1, nv)
+        v[:, 1] = rng.uniform(-0.1, 0.1, nv) * rng.choice([1.0, 1e-3])
+        f = rng.integers(0, nv, (80, 3)).astype(np.int32)
+    elif kind == 2:                                 # a mesh the camera may sit inside
+        v, f = scenes.icosphere(2, float(rng.choice([0.05, 0.3, 1.0])))
+    else:                                           # a few huge triangles
+        v = (rng.standard_normal((9, 3)) * 3).astype(np.float32)
+        f = np.arange(9, dtype=np.int32).reshape(3, 3)
+    c = rng.random(v.shape).astype(np.float32)
+    rows, cols = [(480, 640), (120, 160), (97, 131), (33, 17)][int(rng.integers(0, 4))]
+    cam = np.array([572.4 * cols / 640, 573.6 * rows / 480, cols * 0.51, rows * 0.49], np.float32)
+    z_near = float(rng.choice([0.001, 0.05, 0.3]))
+    poses = np.stack([_rand_pose(rng, float(rng.choice([-0.5, 0.0, 0.02, 0.2, 0.6, 1.5, 5.0]))) for _ in range(3)])
+    kw = {}
+    if rng.random() < 0.4:
+        kw = dict(uv=(rng.standard_normal((len(v), 2)) * 2).astype(np.float32),
+                  tex=rng.integers(0, 256, (int(rng.integers(1, 40)), int(rng.integers(1, 40)), 3)).astype(np.uint8))
+    tag = f"render kind={kind} {rows}x{cols} near={z_near} tex={bool(kw)} nv={len(v)} nf={len(f)}"
+    if kw:
+        gc, gd = gpu.render_views_tex(v, c, kw["uv"], f, kw["tex"], cam, poses, rows=rows, cols=cols, z_near=z_near, z_far=4.0)
+    else:
+        gc, gd = gpu.render_views(v, c, f, cam, poses, rows=rows, cols=cols, z_near=z_near, z_far=4.0)
+    for i, rt in enumerate(poses):
+        oc, od = po.render(v, c, f, cam, rt, rows=rows, cols=cols, z_near=z_near, z_far=4.0, **kw)
+        assert np.array_equal(gd[i], od), tag + f" view {i}: depth differs at {int((gd[i] != od).sum())} pixels"
+        assert np.array_equal(gc[i], oc), tag + f" view {i}: colour differs at {int((gc[i] != oc).any(-1).sum())} pixels"
+    return float((gd > 0).mean())
+
+
+def run_patch(gpu, po, rng):
+    """samplePatchWithScale + depth2normals at random centres / depths, incl. cuts clamped at the border and impossible ones"""
+    from tests import scenes
+    rows, cols = [(480, 640), (240, 320), (200, 333)][int(rng.integers(0, 3))]
+    col, dep, _ = scenes.make_frame(int(rng.integers(1 << 20)), rows, cols)
+    fx, fy = 572.4 * cols / 640, 573.6 * rows / 480
+    n = 24
+    ctr = np.stack([rng.integers(-20, cols + 20, n), rng.integers(-20, rows + 20, n)], 1).astype(np.int32)
+    z = rng.choice([0.25, 0.4, 0.72, 1.0, 2.5, 0.0, -1.0, np.inf, np.nan], n).astype(np.float32)
+    got, status = gpu.sample_patches(col[None], dep[None], ctr, z, fx, fy, frame_of=np.zeros(n, np.int32))
+    nor = po.depth2normals(dep, fx, fy)
+    for i in range(n):
+        want = po.sample_patch(col, dep, nor, ctr[i, 0], ctr[i, 1], float(z[i]), fx, fy)
+        tag = f"patch {rows}x{cols} centre {ctr[i].tolist()} z {z[i]}"
+        if want is None:
+            assert status[i] == 1 and not got[i].any(), tag + " should be rejected"
+        else:
+            assert status[i] == 0 and np.array_equal(got[i], want), tag + f" differs at {int((got[i] != want).sum())} values"
+    return float((status == 0).mean())
+
+
 def main(argv):
     n_cases = int(argv[1]) if len(argv) > 1 else 120
     seed = int(argv[2]) if len(argv) > 2 else 1
@@ -152,6 +224,16 @@ def main(argv):
         except Exception as e:  # noqa: BLE001
             bad += 1
             print("FAIL", repr(e)[:400], flush=True)
+    for fn in (run_render, run_patch):
+        seen = []
+        for _ in range(n_cases // 4):
+            try:
+                seen.append(fn(gpu, po, rng))
+            except Exception as e:  # noqa: BLE001
+                bad += 1
+                print("FAIL", repr(e)[:400], flush=True)
+        what = "covered pixels" if fn is run_render else "accepted cuts"
+        print(f"{fn.__name__}: {len(seen)} cases ok, {what}: mean {np.mean(seen):.3f}, cases with none {int(np.sum(np.array(seen) == 0))}")
     print(f"fuzz: {bad} failing cases (seed {seed}, {n_cases} knn cases per path)")
     return 1 if bad else 0
 

@@ -31,3 +31,13 @@ def test_forward_batch_sizes_and_eval_tables(gpu, po, synth):
         fuzz_gpu.run_forward(gpu, po, synth, rng, name)
     for _ in range(40):
         fuzz_gpu.run_eval(gpu, po, synth, rng)
+
+
+def test_render_and_patch_random_scenes(gpu, po):
+    """triangle soups (slivers, degenerate and huge faces, faces behind the camera / through the near plane), odd frame sizes,
+    textures; patch cuts at random centres and depths incl. impossible ones: bit-exact against the oracle"""
+    rng = np.random.default_rng(5150)
+    covered = [fuzz_gpu.run_render(gpu, po, rng) for _ in range(24)]
+    assert np.mean(covered) > 0.05                   # the scenes do put triangles on screen
+    accepted = [fuzz_gpu.run_patch(gpu, po, rng) for _ in range(12)]
+    assert 0.2 < np.mean(accepted) < 0.95            # both accepted and rejected cuts occur
