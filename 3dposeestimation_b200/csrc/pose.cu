@@ -6,7 +6,8 @@
  *                      best same-class neighbour by angular error (Eigen angularDistance, or the
  *                      elevation difference |acos(Rq22)-acos(Rk22)| for rotInv classes, :296-301),
  *                      exact-match scan over the matched object's templates (:326-334),
- *                      cumulative bins (:337-338).  One warp per query.
+ *                      cumulative bins (:337-338).  One warp per eight queries, the scan shared by queries
+ *                      that matched the same object.
  *   median_select      the sort + middle element of :349-350 as a 4-pass radix select.
  *   confusion_kernel   computeConfusionMatrix body (:201-239).
  *   bootstrap_kernel   networkSolver::computeKNN body (src/networksolver.cpp:474-504).
@@ -51,8 +52,16 @@ __device__ __forceinline__ float to_degrees(float rad) {
 }
 
 constexpr int kPoseWarps = 4;
+constexpr int kPoseQ = 8;      /* consecutive queries per warp */
 constexpr int kMaxBins = 16;
 
+/* One warp per kPoseQ consecutive queries.  Step 1 (per query): lane nn < k scores neighbour nn, a warp reduction picks the
+ * best same-class one.  Step 2: the exact-match scan over the matched object's templates - the expensive part: 32 bytes
+ * of label per template, 3,334 templates per object in config 5 - runs once per DISTINCT matched object among the warp's
+ * queries: a lane loads a template's quaternion once and scores it against every query of the group (query sets are laid
+ * out [object][pose], so the eight queries normally share one object and the label traffic per query drops eightfold;
+ * queries in any other order still work, a group is then a single query).  max() over |dot| is exact in any order, so the
+ * grouping does not change a bit of the result. */
 __global__ void __launch_bounds__(kPoseWarps * 32)
 pose_err_kernel(const int* __restrict__ knn_idx, long long nq, int k, const float* __restrict__ q_labels,
                 const float* __restrict__ t_labels, long long t_total, int nr_tmpl_poses,
@@ -65,14 +74,23 @@ pose_err_kernel(const int* __restrict__ knn_idx, long long nq, int k, const floa
     if (threadIdx.x < kMaxBins) s_cnt[threadIdx.x] = 0;
     if (lane == 0) s_sum[warp] = 0.0;
     __syncthreads();
-    const long long qi = (long long)blockIdx.x * kPoseWarps + warp;
-    if (qi < nq) {
+    const long long q0 = ((long long)blockIdx.x * kPoseWarps + warp) * kPoseQ;
+    float qv[kPoseQ][4], refv[kPoseQ], bdv[kPoseQ];        /* warp-uniform, indexed by unrolled loops only */
+    long long objv[kPoseQ];
+    unsigned pending = 0;
+    double wsum = 0.0;
+#pragma unroll
+    for (int j = 0; j < kPoseQ; ++j) {
+        const long long qi = q0 + j;
+        objv[j] = -1;
+        refv[j] = bdv[j] = 0.f;
+        qv[j][0] = qv[j][1] = qv[j][2] = qv[j][3] = 0.f;
+        if (qi >= nq) continue;
         const float* ql = q_labels + qi * 8;
         const float qc = ql[0];
-        float qq[4] = {ql[1], ql[2], ql[3], ql[4]};
-        int cls = (int)qc;
+        const float qq[4] = {ql[1], ql[2], ql[3], ql[4]};
+        const int cls = (int)qc;
         const int inv = (cls >= 0 && cls < n_rot) ? rot_inv[cls] : 0;
-        /* lane nn < k scores neighbour nn */
         float d = FLT_MAX;
         int ti = -1;
         if (lane < k) {
@@ -106,26 +124,54 @@ pose_err_kernel(const int* __restrict__ knn_idx, long long nq, int k, const floa
             }
         } else {
             const int best_t = __shfl_sync(0xffffffffu, ti, bn);
-            /* exact match: no template of the matched object is strictly closer */
-            const long long obj0 = (long long)(best_t / nr_tmpl_poses) * nr_tmpl_poses;
-            const float ref = quat_absdot(qq, t_labels + (long long)best_t * 8 + 1);
-            float mx = 0.f;
-            for (int p = lane; p < nr_tmpl_poses; p += 32) {
-                const long long t = obj0 + p;
-                if (t < t_total) mx = fmaxf(mx, quat_absdot(qq, t_labels + t * 8 + 1));
-            }
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-            if (lane == 0) {
-                const bool exact = !(mx > ref && acos_cr(mx) < acos_cr(ref));
-                err_out[qi] = bd;
-                if (exact) atomicAdd(&s_cnt[1], 1u);
-                for (int b = 2; b < n_bins; ++b)
-                    if (bd < bins[b]) atomicAdd(&s_cnt[b], 1u);
-                s_sum[warp] = (double)bd;
-            }
+            objv[j] = (long long)(best_t / nr_tmpl_poses) * nr_tmpl_poses;
+            refv[j] = quat_absdot(qq, t_labels + (long long)best_t * 8 + 1);
+            bdv[j] = bd;
+            qv[j][0] = qq[0]; qv[j][1] = qq[1]; qv[j][2] = qq[2]; qv[j][3] = qq[3];
+            pending |= 1u << j;
         }
     }
+    /* exact match: no template of the matched object is strictly closer */
+#pragma unroll
+    for (int j0 = 0; j0 < kPoseQ; ++j0) {
+        if (!((pending >> j0) & 1u)) continue;
+        const long long obj0 = objv[j0];
+        unsigned grp = 0;
+#pragma unroll
+        for (int j = 0; j < kPoseQ; ++j)
+            if (((pending >> j) & 1u) && objv[j] == obj0) grp |= 1u << j;
+        float mx[kPoseQ];
+#pragma unroll
+        for (int j = 0; j < kPoseQ; ++j) mx[j] = 0.f;
+        for (int p = lane; p < nr_tmpl_poses; p += 32) {
+            const long long t = obj0 + p;
+            if (t >= t_total) break;
+            const float4 a = __ldg(reinterpret_cast<const float4*>(t_labels + t * 8));
+            const float4 b = __ldg(reinterpret_cast<const float4*>(t_labels + t * 8) + 1);
+            const float tq[4] = {a.y, a.z, a.w, b.x};
+#pragma unroll
+            for (int j = 0; j < kPoseQ; ++j)
+                if ((grp >> j) & 1u) mx[j] = fmaxf(mx[j], quat_absdot(qv[j], tq));
+        }
+#pragma unroll
+        for (int j = 0; j < kPoseQ; ++j) {
+            if (!((grp >> j) & 1u)) continue;
+            float m = mx[j];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+            if (lane == 0) {
+                const float ref = refv[j], bd = bdv[j];
+                const bool exact = !(m > ref && acos_cr(m) < acos_cr(ref));
+                err_out[q0 + j] = bd;
+                if (exact) atomicAdd(&s_cnt[1], 1u);
+                for (int b2 = 2; b2 < n_bins; ++b2)
+                    if (bd < bins[b2]) atomicAdd(&s_cnt[b2], 1u);
+                wsum += (double)bd;
+            }
+        }
+        pending &= ~grp;
+    }
+    if (lane == 0) s_sum[warp] = wsum;
     __syncthreads();
     if (threadIdx.x < n_bins && s_cnt[threadIdx.x]) atomicAdd(&counts[threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
     if (threadIdx.x == 0) {
@@ -261,7 +307,7 @@ int pose_hist_local(pe_db* db, const int* d_knn_idx, const float* d_q_labels, in
     double* d_sum = reinterpret_cast<double*>(base + off_sum);
     float* d_err = reinterpret_cast<float*>(base + off_err);
     if (nq > 0) {
-        pose_err_kernel<<<(unsigned)((nq + kPoseWarps - 1) / kPoseWarps), kPoseWarps * 32, 0, db->stream>>>(
+        pose_err_kernel<<<(unsigned)((nq + kPoseWarps * kPoseQ - 1) / (kPoseWarps * kPoseQ)), kPoseWarps * 32, 0, db->stream>>>(
             d_knn_idx, nq, k, d_q_labels, db->d_labels, db->t_total, db->poses_per_object,
             reinterpret_cast<const int*>(base + off_rot), n_rot, reinterpret_cast<const float*>(base + off_bins),
             n_bins, d_err, d_counts, d_sum);
@@ -280,13 +326,16 @@ int pose_hist_finish(pe_db* db, const unsigned long long* d_counts, const double
                      int64_t n_err, int64_t nq_total, int n_bins, float* out_host) {
     median_select_kernel<<<1, 1024, 0, db->stream>>>(d_err, n_err, d_med);
     PE_LAUNCHED();
-    unsigned long long h_counts[kMaxBins];
-    double h_sum = 0.0;
-    float h_med = 0.f;
-    PE_CUDA(cudaMemcpyAsync(h_counts, d_counts, sizeof(h_counts), cudaMemcpyDeviceToHost, db->stream));
-    PE_CUDA(cudaMemcpyAsync(&h_sum, d_sum, 8, cudaMemcpyDeviceToHost, db->stream));
-    PE_CUDA(cudaMemcpyAsync(&h_med, d_med, 4, cudaMemcpyDeviceToHost, db->stream));
+    /* counts, sum and median are neighbours in the scratch (pose_hist_local's layout): one copy back */
+    struct { unsigned long long counts[kMaxBins]; double sum; float med; float pad; } h;
+    static_assert(sizeof(h) == kMaxBins * 8 + 16, "layout of the head of db->scratch");
+    PE_REQUIRE(reinterpret_cast<const char*>(d_sum) == reinterpret_cast<const char*>(d_counts) + kMaxBins * 8 &&
+               reinterpret_cast<const char*>(d_med) == reinterpret_cast<const char*>(d_sum) + 8, "histogram scratch layout");
+    PE_CUDA(cudaMemcpyAsync(&h, d_counts, sizeof(h), cudaMemcpyDeviceToHost, db->stream));
     PE_CUDA(cudaStreamSynchronize(db->stream));
+    const unsigned long long* h_counts = h.counts;
+    const double h_sum = h.sum;
+    const float h_med = h.med;
     /* normalisation of src/networkevaluator.cpp:342-346 */
     const float total = (float)h_counts[0] + (float)h_counts[n_bins - 1];
     for (int b = 0; b < n_bins; ++b) out_host[b] = (float)h_counts[b] / total;
@@ -453,7 +502,7 @@ extern "C" int pe_histogram_dev_noalloc(pe_db* db, const int32_t* d_knn_idx, con
     if (n_rot > 0) PE_CUDA(cudaMemcpyAsync(d_rot, rot_inv, (size_t)n_rot * 4, cudaMemcpyHostToDevice, db->stream));
     PE_CUDA(cudaMemcpyAsync(d_bins, bins, (size_t)n_bins * 4, cudaMemcpyHostToDevice, db->stream));
     if (nq > 0) {
-        pose_err_kernel<<<(unsigned)((nq + kPoseWarps - 1) / kPoseWarps), kPoseWarps * 32, 0, db->stream>>>(
+        pose_err_kernel<<<(unsigned)((nq + kPoseWarps * kPoseQ - 1) / (kPoseWarps * kPoseQ)), kPoseWarps * 32, 0, db->stream>>>(
             d_knn_idx, nq, k, d_q_labels, db->d_labels, db->t_total, db->poses_per_object, d_rot, n_rot, d_bins, n_bins,
             d_err, d_counts, d_sum);
         PE_LAUNCHED();

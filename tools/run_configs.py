@@ -164,11 +164,13 @@ def main():
         own_idx = np.ascontiguousarray(d_idx.to_host()[rank * B:(rank + 1) * B])      # kept alive across the C call
         capi.check(capi.lib().pe_memcpy_h2d(dev, d_own.ptr, own_idx.ctypes.data, own_idx.nbytes))
         net.sync()
+        h = db.histogram_sharded_dev(comm, d_own, d_ql, B, K, rot_inv, BINS)       # first call: sizes the scratch (cudaMalloc)
         t = capi.Timer(dev)
         t.start(db)
-        h = db.histogram_sharded_dev(comm, d_own, d_ql, B, K, rot_inv, BINS)
+        for _ in range(5):
+            h = db.histogram_sharded_dev(comm, d_own, d_ql, B, K, rot_inv, BINS)
         t.stop(db)
-        out["ms_histogram"] = t.elapsed_ms()
+        out["ms_histogram"] = t.elapsed_ms() / 5
         out["histogram"] = [float(x) for x in h]
         out["histogram_queries"] = B * world
         out["rot_inv"] = "0 / 1 / 2 for 80 / 10 / 10 % of the classes (synth.rot_inv_pattern)"
