@@ -367,8 +367,16 @@ static void im2col(const float* in, shape3 s, int k, float* col) {
             }
 }
 
-int orc_forward_im2col(const orc_layer* layers, int n_layers, const float* const* blobs, const int* sel, int n_sel, int h,
-                       int w, const float* patches_hwc, int64_t n, int patch_c, int batch, float* out) {
+/* threads > 1: the samples of a batch are spread over OpenMP threads in every layer (own im2col buffer per thread, the
+ * InnerProduct GEMM split by rows) - what a threaded BLAS under Caffe amounts to; results do not depend on the count */
+int orc_forward_im2col_mt(const orc_layer* layers, int n_layers, const float* const* blobs, const int* sel, int n_sel, int h,
+                          int w, const float* patches_hwc, int64_t n, int patch_c, int batch, float* out, int threads) {
+#ifdef _OPENMP
+    const int nt = threads > 0 ? threads : omp_get_max_threads();
+#else
+    const int nt = 1;
+    (void)threads;
+#endif
     shape3 in = {n_sel, h, w}, fin;
     for (int c = 0; c < n_sel; ++c)
         if (sel[c] < 0 || sel[c] >= patch_c) return -1;
@@ -391,13 +399,14 @@ int orc_forward_im2col(const orc_layer* layers, int n_layers, const float* const
     }
     float* a = (float*)malloc(sizeof(float) * mx * batch);
     float* b = (float*)malloc(sizeof(float) * mx * batch);
-    float* col = (float*)malloc(sizeof(float) * col_n);
+    float* col = (float*)malloc(sizeof(float) * col_n * (size_t)nt);
     if (!a || !b || !col) { free(a); free(b); free(col); return -1; }
     for (int64_t first = 0; first < n; first += batch) {
         const int m = (int)(n - first < batch ? n - first : batch);
         shape3 cur = in;
         size_t cnt = (size_t)cur.c * cur.h * cur.w;
         /* the staging copy of src/networkevaluator.cpp:33-42: HWC -> CHW (+ channel select) for the whole batch */
+#pragma omp parallel for num_threads(nt) schedule(static) if (nt > 1)
         for (int s = 0; s < m; ++s) {
             const float* patch = patches_hwc + (size_t)(first + s) * h * w * patch_c;
             for (int c = 0; c < n_sel; ++c)
@@ -411,10 +420,16 @@ int orc_forward_im2col(const orc_layer* layers, int n_layers, const float* const
             const size_t ncnt = (size_t)nx.c * nx.h * nx.w;
             if (L->kind == ORC_CONV) {
                 const int K = cur.c * L->b * L->b, N = nx.h * nx.w;
+#pragma omp parallel for num_threads(nt) schedule(dynamic, 1) if (nt > 1)
                 for (int s = 0; s < m; ++s) {
-                    im2col(src + (size_t)s * cnt, cur, L->b, col);
+#ifdef _OPENMP
+                    float* mycol = col + col_n * (size_t)omp_get_thread_num();
+#else
+                    float* mycol = col;
+#endif
+                    im2col(src + (size_t)s * cnt, cur, L->b, mycol);
                     float* o = dst + (size_t)s * ncnt;
-                    sgemm_nn(L->a, N, K, blobs[L->blob0], col, o);
+                    sgemm_nn(L->a, N, K, blobs[L->blob0], mycol, o);
                     for (int f = 0; f < L->a; ++f) {
                         const float bf = blobs[L->blob1][f];
                         for (int i = 0; i < N; ++i) o[(size_t)f * N + i] += bf;
@@ -422,12 +437,21 @@ int orc_forward_im2col(const orc_layer* layers, int n_layers, const float* const
                 }
                 float* t = src; src = dst; dst = t;
             } else if (L->kind == ORC_POOL) {
+#pragma omp parallel for num_threads(nt) schedule(static) if (nt > 1)
                 for (int s = 0; s < m; ++s) pool_forward(src + (size_t)s * cnt, cur, L->a, L->b, dst + (size_t)s * ncnt);
                 float* t = src; src = dst; dst = t;
             } else if (L->kind == ORC_ACT) {
+#pragma omp parallel for num_threads(nt) schedule(static) if (nt > 1)
                 for (int s = 0; s < m; ++s) act_forward(src + (size_t)s * cnt, cur, L->a, L->blob0 >= 0 ? blobs[L->blob0] : 0);
             } else if (L->kind == ORC_FC) {
-                sgemm_nt(m, L->a, (int)cnt, src, blobs[L->blob0], dst);
+                {
+                    const int rows_per = (m + nt - 1) / nt;       /* row blocks: a row of the product depends on its own row of A only */
+#pragma omp parallel for num_threads(nt) schedule(static) if (nt > 1)
+                    for (int blk = 0; blk < nt; ++blk) {
+                        const int r0 = blk * rows_per, r1 = r0 + rows_per < m ? r0 + rows_per : m;
+                        if (r0 < r1) sgemm_nt(r1 - r0, L->a, (int)cnt, src + (size_t)r0 * cnt, blobs[L->blob0], dst + (size_t)r0 * L->a);
+                    }
+                }
                 for (int s = 0; s < m; ++s)
                     for (int o = 0; o < L->a; ++o) dst[(size_t)s * L->a + o] += blobs[L->blob1][o];
                 float* t = src; src = dst; dst = t;
@@ -439,4 +463,10 @@ int orc_forward_im2col(const orc_layer* layers, int n_layers, const float* const
     }
     free(a); free(b); free(col);
     return D;
+}
+
+/* one thread: a stock Caffe-CPU build without a threaded BLAS */
+int orc_forward_im2col(const orc_layer* layers, int n_layers, const float* const* blobs, const int* sel, int n_sel, int h,
+                       int w, const float* patches_hwc, int64_t n, int patch_c, int batch, float* out) {
+    return orc_forward_im2col_mt(layers, n_layers, blobs, sel, n_sel, h, w, patches_hwc, n, patch_c, batch, out, 1);
 }

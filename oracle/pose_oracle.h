@@ -47,6 +47,9 @@ int orc_forward(const orc_layer* layers, int n_layers, const float* const* blobs
  * timing baseline of SURVEY 8(d); equal to orc_forward up to the summation order */
 int orc_forward_im2col(const orc_layer* layers, int n_layers, const float* const* blobs, const int* sel, int n_sel, int h,
                        int w, const float* patches_hwc, int64_t n, int patch_c, int batch, float* out);
+/* ... with the samples of a batch spread over `threads` OpenMP threads (0 = all): Caffe-CPU on a threaded BLAS; same result */
+int orc_forward_im2col_mt(const orc_layer* layers, int n_layers, const float* const* blobs, const int* sel, int n_sel, int h,
+                          int w, const float* patches_hwc, int64_t n, int patch_c, int batch, float* out, int threads);
 
 /* also return intermediate activations of ONE patch (debug / layer-wise parity):
  * stage index s = output of layer s; buf must hold max activation size; returns count. */

@@ -51,6 +51,9 @@ def lib():
         L.orc_forward_im2col.argtypes = [C.POINTER(_Layer), C.c_int, C.POINTER(fp), ip, C.c_int, C.c_int, C.c_int,
                                          fp, C.c_int64, C.c_int, C.c_int, fp]
         L.orc_forward_im2col.restype = C.c_int
+        L.orc_forward_im2col_mt.argtypes = [C.POINTER(_Layer), C.c_int, C.POINTER(fp), ip, C.c_int, C.c_int, C.c_int,
+                                            fp, C.c_int64, C.c_int, C.c_int, fp, C.c_int]
+        L.orc_forward_im2col_mt.restype = C.c_int
         L.orc_forward_stage.argtypes = [C.POINTER(_Layer), C.c_int, C.POINTER(fp), ip, C.c_int, C.c_int, C.c_int,
                                         fp, C.c_int, C.c_int, fp, C.c_int]
         L.orc_knn_l2.restype = None
@@ -289,14 +292,16 @@ class OracleNet:
             raise RuntimeError(f"oracle forward failed ({d})")
         return out
 
-    def forward_im2col(self, patches_hwc: np.ndarray, batch: int | None = None) -> np.ndarray:
-        """the same forward the way Caffe-CPU runs it (im2col + SGEMM, `batch` samples per pass, one thread)"""
+    def forward_im2col(self, patches_hwc: np.ndarray, batch: int | None = None, threads: int = 1) -> np.ndarray:
+        """the same forward the way Caffe-CPU runs it (im2col + SGEMM, `batch` samples per pass); threads = 1: a build without
+        a threaded BLAS, threads = 0 / n: the samples of a batch spread over all / n OpenMP threads"""
         x = _f32(patches_hwc)
         n, h, w, c = x.shape
         assert (h, w, c) == (self.net.height, self.net.width, self.net.channels)
         out = np.empty((n, self.net.desc_dim), np.float32)
-        d = lib().orc_forward_im2col(self._layers, len(self.net.layers), self._blob_ptrs, _p(self._sel, C.c_int32),
-                                     len(self.net.sel), h, w, _p(x, C.c_float), n, c, int(batch or self.net.batch), _p(out, C.c_float))
+        d = lib().orc_forward_im2col_mt(self._layers, len(self.net.layers), self._blob_ptrs, _p(self._sel, C.c_int32),
+                                        len(self.net.sel), h, w, _p(x, C.c_float), n, c, int(batch or self.net.batch), _p(out, C.c_float),
+                                        int(threads))
         if d != self.net.desc_dim:
             raise RuntimeError(f"oracle im2col forward failed ({d})")
         return out

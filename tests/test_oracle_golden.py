@@ -206,6 +206,9 @@ def test_im2col_sgemm_form_equals_direct_form(po, synth):
         assert parity.rowscale_err(b, a) < 1e-5
         # two exact fp32 evaluation orders: the element-relative reading of SURVEY 8(c) is met by most, not all, elements
         assert parity.elementrel(b, a)[0] > 0.95
+        # the threaded form (samples of a batch over OpenMP threads: bench.py's all-cores CPU arm) is the same arithmetic
+        assert np.array_equal(net.forward_im2col(x, batch=3, threads=3), b)
+        assert np.array_equal(net.forward_im2col(x, batch=300, threads=0), net.forward_im2col(x, batch=300))
 
 
 def test_parity_metrics():
