@@ -73,6 +73,15 @@ def test_producer_mirror_host_side(capi, tmp_path):
         assert code != 0 and b"pose_b200" in H.pe_host_last_error() and not patches.any()
 
 
+def test_every_entry_point_survives_null_arguments():
+    """SURVEY 8b "Errors": the C ABI returns status codes, never faults - every entry point called with null pointers and
+    zero sizes, in a process of its own (tests/nullfuzz_cabi.py); the GPU suite repeats this with a device present"""
+    import subprocess
+    import sys
+    r = subprocess.run([sys.executable, "-m", "tests.nullfuzz_cabi"], cwd=ROOT, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "all returned" in r.stdout, r.stdout[-600:] + r.stderr[-600:]
+
+
 def test_header_cites_reference_interfaces():
     text = open(os.path.join(ROOT, "include", "pose_b200.h")).read()
     for cite in ("src/networkevaluator.cpp:9-54", "src/networkevaluator.cpp:269-355", "src/networkevaluator.cpp:199-245",

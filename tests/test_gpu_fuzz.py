@@ -41,3 +41,14 @@ def test_render_and_patch_random_scenes(gpu, po):
     assert np.mean(covered) > 0.05                   # the scenes do put triangles on screen
     accepted = [fuzz_gpu.run_patch(gpu, po, rng) for _ in range(12)]
     assert 0.2 < np.mean(accepted) < 0.95            # both accepted and rejected cuts occur
+
+
+def test_every_entry_point_survives_null_arguments_with_a_device(gpu):
+    """tests/nullfuzz_cabi.py on a box with a GPU: with a device present the calls get past the "no CUDA device" answer,
+    so the argument checks themselves are what returns"""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "tests.nullfuzz_cabi"], cwd=root, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "all returned" in r.stdout, r.stdout[-800:] + r.stderr[-800:]
