@@ -193,6 +193,22 @@ static size_t max_activation(const orc_layer* layers, int n_layers, shape3 in, s
     return mx;
 }
 
+/* floats conv_forward's zero-padded input copy needs: the largest c x h x (ROWP + k) over the Convolution layers */
+static size_t pad_floats(const orc_layer* layers, int n_layers, shape3 in) {
+    size_t need = 1;
+    shape3 cur = in;
+    for (int i = 0; i < n_layers; ++i) {
+        shape3 nx;
+        if (layer_out_shape(&layers[i], cur, &nx)) return 0;
+        if (layers[i].kind == ORC_CONV) {
+            const size_t n = (size_t)cur.c * cur.h * (ROWP + layers[i].b);
+            if (n > need) need = n;
+        }
+        cur = nx;
+    }
+    return need;
+}
+
 /* runs one patch; returns final count; if stage >= 0 stops after that layer */
 static int forward_one(const orc_layer* layers, int n_layers, const float* const* blobs,
                        const int* sel, int n_sel, int h, int w, const float* patch, int patch_c,
@@ -236,7 +252,7 @@ int orc_forward(const orc_layer* layers, int n_layers, const float* const* blobs
     const size_t mx = max_activation(layers, n_layers, in, &fin);
     if (!mx) return -1;
     const int D = fin.c * fin.h * fin.w;
-    const size_t pad_n = (size_t)(mx + 1) * 3; /* generous: padded rows are < 3x wider */
+    const size_t pad_n = pad_floats(layers, n_layers, in);
     int err = 0;
 #ifdef _OPENMP
     const int nt = threads > 0 ? threads : omp_get_max_threads();
@@ -271,7 +287,7 @@ int orc_forward_stage(const orc_layer* layers, int n_layers, const float* const*
     if (!mx) return -1;
     float* a = (float*)malloc(sizeof(float) * mx);
     float* b = (float*)malloc(sizeof(float) * mx);
-    float* pad = (float*)malloc(sizeof(float) * (mx + 1) * 3);
+    float* pad = (float*)malloc(sizeof(float) * pad_floats(layers, n_layers, in));
     float* res = 0;
     int cnt = forward_one(layers, n_layers, blobs, sel, n_sel, h, w, patch_hwc, patch_c, a, b, pad,
                           stage, &res);

@@ -211,6 +211,27 @@ def test_im2col_sgemm_form_equals_direct_form(po, synth):
         assert np.array_equal(net.forward_im2col(x, batch=300, threads=0), net.forward_im2col(x, batch=300))
 
 
+def test_pooling_against_caffes_own_known_answers(po):
+    """The arithmetic of this path lives in BVLC Caffe, which is not under /root/reference; its published test suite holds
+    known answers for the Pooling layer (src/caffe/test/test_pooling_layer.cpp: TestForwardSquare - MAX, kernel 2, stride 1 on
+    the 3 x 5 pattern below gives [9 5 5 8] twice; TestSetup - kernel 3, stride 2 on a 6 x 5 blob gives 3 x 2, the ceil-mode
+    shape rule that makes the nets' 57 -> 29 and 25 -> 13).  Restated here and run through the oracle behind an identity
+    1 x 1 convolution (the prototxt reader wants a Convolution first)."""
+    def net_for(n, c, h, w, k, s):
+        txt = (f'name: "pool_kat"\ninput: "data"\ninput_shape {{ dim: {n} dim: {c} dim: {h} dim: {w} }}\n'
+               f'layer {{ name: "id" type: "Convolution" bottom: "data" top: "id" convolution_param {{ num_output: {c} kernel_size: 1 }} }}\n'
+               f'layer {{ name: "pool1" type: "Pooling" bottom: "id" top: "pool1" pooling_param {{ pool: MAX kernel_size: {k} stride: {s} }} }}\n')
+        ref = po.parse_prototxt(txt)
+        return ref, po.OracleNet(ref, [np.eye(c, dtype=np.float32).reshape(c, c, 1, 1), np.zeros(c, np.float32)])
+    ref, net = net_for(2, 2, 3, 5, 2, 1)
+    img = np.array([[1, 2, 5, 2, 3], [9, 4, 1, 4, 8], [1, 2, 5, 2, 3]], np.float32)
+    x = np.stack([img, img], -1)[None].repeat(2, 0)                      # N H W C
+    out = net.forward(x).reshape(2, 2, 2, 4)
+    assert np.array_equal(out, np.broadcast_to(np.array([[9, 5, 5, 8], [9, 5, 5, 8]], np.float32), (2, 2, 2, 4)))
+    ref, _ = net_for(2, 3, 6, 5, 3, 2)
+    assert ref.desc_dim == 3 * 3 * 2                                       # channels x pooled height 3 x pooled width 2
+
+
 def test_parity_metrics():
     import importlib
     parity = importlib.import_module("3dposeestimation_b200.parity")
