@@ -54,3 +54,50 @@ def test_create_use_destroy_returns_device_memory(gpu, synth):
     assert lost < 16 << 20, f"{lost / 2**20:.1f} MB of device memory not returned after 25 create / use / destroy rounds"
     grown = psutil.Process().memory_info().rss - rss0        # pinned staging buffers are host memory of this process
     assert grown < 256 << 20, f"host memory grew by {grown / 2**20:.0f} MB over 25 rounds"
+
+
+def test_distinct_handles_from_distinct_threads(gpu, synth):
+    """SURVEY 8b "Threading": a handle belongs to one thread at a time, distinct handles may run on distinct threads (one
+    stream per handle).  Four threads, each with its own net + DB, run forward -> k-NN -> histogram concurrently (ctypes
+    drops the GIL during the calls); every thread must get exactly what it gets alone."""
+    import threading
+    names = ["manifold_rgbdnor_16", "manifold_rgbd_16", "manifold_rgbdnor_16_bin", "manifold_rgb_16"]
+    n_obj, nr_t = 4, 500
+
+    def work(i, rounds):
+        net = gpu.Net(named=names[i])
+        net.fill(10 + i, 1)
+        x = synth.make_patches(20 + i, 0, 200, 7, 10)
+        tl = synth.make_labels(30 + i, n_obj, nr_t)
+        out = []
+        for r in range(rounds):
+            d = net.compute_descriptors(x[r * 7:r * 7 + 150])
+            t = np.random.default_rng(40 + i).standard_normal((n_obj * nr_t, d.shape[1])).astype(np.float32) * np.abs(d).mean()
+            db = gpu.TemplateDB(desc=t, labels_all=tl, poses_per_object=nr_t)
+            idx, dist = db.knn(d, 3)
+            h = db.histogram(idx, tl[idx[:, 0]].copy(), np.zeros(n_obj, np.int32), BINS)
+            db.close()
+            out.append((d, idx, dist, h))
+        net.close()
+        return out
+
+    alone = [work(i, 4) for i in range(4)]
+    got = [None] * 4
+    errs = []
+
+    def run(i):
+        try:
+            got[i] = work(i, 4)
+        except Exception as e:  # noqa: BLE001
+            errs.append((i, repr(e)))
+
+    threads = [threading.Thread(target=run, args=(i,)) for i in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(300)
+    assert not errs, errs
+    for i in range(4):
+        for a, b in zip(alone[i], got[i]):
+            for u, v in zip(a, b):
+                assert np.array_equal(u, v, equal_nan=True), f"thread {i} got another result than alone"
