@@ -8,14 +8,19 @@
  *   sz::datasetManager::createSynthSamplesWadim / createSynthSamplesPaul     src/datasetmanager.cpp:498-535, 425-496
  *   sz::datasetManager::extractRealSamplesPaul / extractRealSamplesWadim     src/datasetmanager.cpp:348-411
  *   sz::Frame                                  include/datatypes.h:18-23 (colour, depth and gt only)
+ *   sz::hdf5Handler::read / write              include/hdf5handler.h:15-16 (on PESS0001 files, not HDF5)
+ *   sz::datasetManager(config), generateDatasets, getTemplateSet / getTrainingSet / getTestSet
+ *                                              src/datasetmanager.cpp:802-831, 602-676, include/datasetmanager.h:59-61
  * Substitutions: Eigen::Matrix3f -> sz::Matrix3f (row-major 9 floats, cam(r, c)); Eigen::Isometry3f -> sz::Isometry3f
  * (row-major 3x4 [R|t]); cv::Mat frames -> flat arrays in the layout pe_sample_patches reads.  Rendering, normals, patch
  * cut and labels all run inside the C ABI (pe_template_samples / pe_scene_samples): rendered frames never reach the host.
- * The datasetManager mirror holds only what the four producers read (dataset_path, dataset_name, inplane); HDF5 storage,
- * benchmark loaders and the background set are outside this path.
+ * The datasetManager mirror holds what the producers and the evaluator read; the benchmark loaders (image files through
+ * OpenCV), generateAndStoreSamples, the background set and the hard negatives are outside this path.
  */
 #pragma once
 #include <array>
+#include <limits>
+#include <random>
 #include <utility>
 
 #include "networkevaluator_b200.hpp"
@@ -158,12 +163,146 @@ private:
 
 static_assert(sizeof(Isometry3f) == 12 * sizeof(float), "poses are passed to the C ABI as one flat array");
 
-class datasetManager {
+/* hdf5Handler::read / write (include/hdf5handler.h:15-16, src/hdf5handler.cpp:11-132) on the flat PESS0001 files of
+ * pe_samples_read / pe_samples_write: the same two arrays as the reference's HDF5 datasets ("data" [n][C][H][W], "label"
+ * [n][8]); tools/h5_to_pess.py converts a reference .h5 file.  HDF5 itself is not linked. */
+class hdf5Handler {
 public:
-    std::string dataset_path, dataset_name = "LineMOD";
-    bool inplane = false;
+    std::vector<Sample> read(const std::string& filename) const {
+        int64_t n = 0;
+        int c = 0, h = 0, w = 0, ld = 0;
+        pe_check(pe_samples_info(filename.c_str(), &n, &c, &h, &w, &ld));
+        std::vector<Sample> samples((size_t)n);
+        if (n == 0) return samples;
+        const size_t img = (size_t)h * w * c;
+        std::vector<float> data((size_t)n * img), labels((size_t)n * ld);
+        pe_check(pe_samples_read(filename.c_str(), 0, n, data.data(), labels.data()));
+        for (int64_t i = 0; i < n; ++i) {
+            samples[i].data = Mat(h, w, c);
+            std::memcpy(samples[i].data.ptr<float>(0), data.data() + i * img, img * sizeof(float));
+            samples[i].label = Mat(1, ld);
+            std::memcpy(samples[i].label.ptr<float>(0), labels.data() + (size_t)i * ld, ld * sizeof(float));
+        }
+        return samples;
+    }
+    void write(const std::string& filename, std::vector<Sample>& samples) const {
+        if (samples.empty()) throw std::runtime_error("hdf5Handler::write: no samples for " + filename);
+        const Mat& d0 = samples[0].data;
+        const int ld = samples[0].label.cols;
+        const size_t img = (size_t)d0.rows * d0.cols * d0.ch;
+        std::vector<float> data(samples.size() * img), labels(samples.size() * ld);
+        for (size_t i = 0; i < samples.size(); ++i) {
+            const Sample& s = samples[i];
+            if (s.data.rows != d0.rows || s.data.cols != d0.cols || s.data.ch != d0.ch || s.label.cols != ld)
+                throw std::runtime_error("hdf5Handler::write: sample " + std::to_string(i) + " has another shape");
+            std::memcpy(data.data() + i * img, s.data.buf.data(), img * sizeof(float));
+            std::memcpy(labels.data() + i * ld, s.label.buf.data(), ld * sizeof(float));
+        }
+        pe_check(pe_samples_write(filename.c_str(), data.data(), labels.data(), (int64_t)samples.size(), d0.ch, d0.rows, d0.cols, ld));
+    }
+};
+
+class datasetManager : public DatasetView {
+public:
+    std::string dataset_path, hdf5_path, dataset_name = "LineMOD";
+    std::string sample_ext = ".pess";                   /* the reference's ".h5" files, converted by tools/h5_to_pess.py */
+    bool inplane = false, use_real = true;
+    int random_background = 0;
+    std::vector<std::string> models, used_models;
+    std::vector<int> rotInv;
+    std::unordered_map<std::string, int> model_index;
+    uint64_t shuffle_seed = 5489;                       /* the reference shuffles with the C library's rand(): order is not portable */
     int device = 0;
     float patch_metric_size = 0.2f;                     /* samplePatchWithScale's m, src/datasetmanager.cpp:302-306 */
+    hdf5Handler h5;
+
+    datasetManager() = default;
+    /* src/datasetmanager.cpp:802-831: the keys of config.ini this mirror uses (background_path and the simulated-data keys
+     * belong to parts that are not mirrored and are not required) */
+    explicit datasetManager(const std::string& config) {
+        IniFile pt(config);
+        dataset_path = pt.get<std::string>("paths.dataset_path");
+        hdf5_path = pt.get<std::string>("paths.hdf5_path");
+        dataset_name = pt.get<std::string>("input.dataset_name");
+        random_background = pt.get<int>("input.random_background");
+        use_real = pt.get<bool>("input.use_real");
+        inplane = pt.get<bool>("input.inplane");
+        models = to_array<std::string>(pt.get<std::string>("input.models"));
+        used_models = to_array<std::string>(pt.get<std::string>("input.used_models"));
+        rotInv = to_array<int>(pt.get<std::string>("input.rotInv"));
+        if (dataset_name != "LineMOD" && dataset_name != "BigBIRD" && dataset_name != "Washington")
+            throw std::runtime_error("Unknown dataset: " + dataset_name + "!");
+        for (size_t i = 0; i < models.size(); ++i) model_index[models[i]] = (int)i;
+    }
+
+    const SampleSet& getTrainingSet() const override { return training_set; }
+    const SampleSet& getTemplateSet() const override { return template_set; }
+    const SampleSet& getTestSet() const override { return test_set; }
+    const std::vector<std::string>& getModels() const { return used_models; }
+    std::string getDatasetPath() const { return dataset_path; }
+    std::string getHDF5Path() const { return hdf5_path; }
+
+    /* src/datasetmanager.cpp:602-676 without generateAndStoreSamples (the three files per model must exist), the
+     * background set and the hard negatives: per used model read realSamples_ / synthSamples_ / templates_, hang every real
+     * sample on its closest template (angularDistance, first minimum), send the first ceil(n / 2) of each template's
+     * samples to the training set (when use_real) and the rest to the test set, crop every object to the smallest count,
+     * shuffle.  maxSimTmpl is the miner's business (pe_miner_max_sim). */
+    void generateDatasets() {
+        training_set.clear();
+        template_set.clear();
+        test_set.clear();
+        for (const std::string& seq : used_models) {
+            std::vector<Sample> train_real = h5.read(hdf5_path + "realSamples_" + seq + sample_ext);
+            std::vector<Sample> train_synth = h5.read(hdf5_path + "synthSamples_" + seq + sample_ext);
+            template_set.push_back(h5.read(hdf5_path + "templates_" + seq + sample_ext));
+            test_set.push_back(std::vector<Sample>());
+            const size_t nr_template_poses = template_set[0].size(), nr_real_poses = train_real.size();
+            if (template_set.back().size() < nr_template_poses)
+                throw std::runtime_error("templates_" + seq + ": fewer templates than the first model");
+            std::vector<std::vector<int>> maxSimTmpl(nr_template_poses);
+            for (size_t real_sample = 0; real_sample < nr_real_poses; ++real_sample) {
+                float best_dist = std::numeric_limits<float>::max(), q[4];
+                size_t sim_tmpl = 0;
+                train_real[real_sample].getQuat(q);
+                for (size_t tmpl = 0; tmpl < nr_template_poses; ++tmpl) {
+                    float t[4];
+                    template_set.back()[tmpl].getQuat(t);
+                    const float temp_dist = angularDistance(q, t);
+                    if (temp_dist >= best_dist) continue;
+                    best_dist = temp_dist;
+                    sim_tmpl = tmpl;
+                }
+                if (nr_template_poses) maxSimTmpl[sim_tmpl].push_back((int)real_sample);
+            }
+            for (size_t tmpl = 0; tmpl < nr_template_poses; ++tmpl) {
+                const std::vector<int>& of = maxSimTmpl[tmpl];
+                const size_t half = (size_t)std::ceil(of.size() / 2.0);
+                if (use_real)
+                    for (size_t i = 0; i < half; ++i) train_synth.push_back(train_real[of[i]]);
+                for (size_t i = half; i < of.size(); ++i) test_set.back().push_back(train_real[of[i]]);
+            }
+            training_set.push_back(std::move(train_synth));
+        }
+        size_t min_training = std::numeric_limits<size_t>::max(), min_test = min_training;
+        for (size_t object = 0; object < used_models.size(); ++object) {
+            min_training = std::min(min_training, training_set[object].size());
+            min_test = std::min(min_test, test_set[object].size());
+        }
+        std::mt19937_64 rng(shuffle_seed);
+        for (size_t object = 0; object < used_models.size(); ++object) {
+            training_set[object].resize(min_training);
+            test_set[object].resize(min_test);
+            std::shuffle(training_set[object].begin(), training_set[object].end(), rng);
+            std::shuffle(test_set[object].begin(), test_set[object].end(), rng);
+        }
+    }
+
+    /* Eigen 3.2 Quaternionf::angularDistance as DESIGN 2 states it: 2 acos(min(1, |a.b|)) */
+    static float angularDistance(const float a[4], const float b[4]) {
+        float d = std::fabs(a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3]);
+        if (d > 1.f) d = 1.f;
+        return 2.f * std::acos(d);
+    }
 
     /* src/datasetmanager.cpp:498-535 */
     std::vector<Sample> createSynthSamplesWadim(Model& model, Matrix3f& cam, int index, int subdiv) const {
@@ -216,6 +355,7 @@ public:
     }
 
 private:
+    SampleSet template_set, training_set, test_set;
     static void mul3(const float* a, const float* b, float* o) {
         for (int r = 0; r < 3; ++r)
             for (int c = 0; c < 3; ++c) o[3 * r + c] = a[3 * r] * b[c] + a[3 * r + 1] * b[3 + c] + a[3 * r + 2] * b[6 + c];

@@ -82,6 +82,18 @@ def test_every_entry_point_survives_null_arguments():
     assert r.returncode == 0 and "all returned" in r.stdout, r.stdout[-600:] + r.stderr[-600:]
 
 
+def test_example_program_builds_and_reports_errors():
+    """examples/evaluate (the evaluation half of the reference's main.cpp on the mirror headers) is built with the library
+    and answers a missing config / no argument the way main.cpp does, without a GPU"""
+    import subprocess
+    exe = os.path.join(ROOT, "examples", "evaluate")
+    assert os.path.exists(exe)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and "Specify config file as argument" in r.stderr          # main.cpp:16-20
+    r = subprocess.run([exe, "/nonexistent/config.ini"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and "cannot open config" in r.stderr
+
+
 def test_header_cites_reference_interfaces():
     text = open(os.path.join(ROOT, "include", "pose_b200.h")).read()
     for cite in ("src/networkevaluator.cpp:9-54", "src/networkevaluator.cpp:269-355", "src/networkevaluator.cpp:199-245",
