@@ -28,7 +28,8 @@ constexpr int kFcStages = 3;
 constexpr int kFcTerm = 8 * 2048;                  /* one term of one operand block: 8 chunks x 128 rows x 16 B */
 constexpr int kFcStageBytes = 4 * kFcTerm;         /* A hi | A lo | B hi | B lo */
 constexpr int kFcOffBar = kFcStages * kFcStageBytes;
-constexpr int kFcSmem = kFcOffBar + 256;
+constexpr int kFcOffBias = kFcOffBar + 256;           /* bias[128] | slope[128] of this CTA's N tile */
+constexpr int kFcSmem = kFcOffBias + 1024;
 constexpr int kFcThreads = 320;                    /* warp 0 weight copies, warp 1 MMA, warps 2-9 loaders + epilogue */
 constexpr int kLog2SxFc = 4;                       /* activation scale 2^4: |x| < 4094 */
 constexpr int kFcRows = 64;                        /* batch rows per CTA (the MMA is M = 128, see the kernel) */
@@ -75,6 +76,13 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
     const int m0 = blockIdx.x * kFcRows, n0 = blockIdx.y * 128;
     int n_mma = a.N - n0;
     n_mma = n_mma >= 128 ? 128 : ((n_mma + 15) & ~15);
+    float* s_bias = reinterpret_cast<float*>(smem + kFcOffBias);
+    float* s_slope = s_bias + 128;
+    if (tid < 128) {
+        const int o = n0 + tid;
+        s_bias[tid] = o < a.N ? a.bias[o] : 0.f;
+        s_slope[tid] = (a.slope && o < a.N) ? a.slope[o] : 0.f;
+    }
     if (tid == 0) {
         for (int s = 0; s < kFcStages; ++s) { mbar_init(&full_a[s], 256); mbar_init(&full_b[s], 1); mbar_init(&empty[s], 1); }
         mbar_init(acc_full, 1);
@@ -191,20 +199,29 @@ __global__ void __launch_bounds__(kFcThreads, 1) fc_tc_kernel(const FcArgs a) {
                 fence_after_sync();
                 const uint32_t tbase = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
                 float* yrow = a.y + (size_t)(erow_ok ? em : 0) * a.ldy + n0;
+                const bool vec_ok = (a.ldy & 3) == 0 && (reinterpret_cast<uintptr_t>(a.y) & 15) == 0;
                 const int groups = n_mma / 16, g_split = (groups + 1) / 2;
                 for (int c0 = (half ? g_split : 0) * 16; c0 < (half ? groups : g_split) * 16; c0 += 16) {
                     uint32_t w[16], wx[16];
                     tmem_ld16(tbase + c0, w);
                     tmem_ld16(tbase + 128 + c0, wx);
                     tmem_ld_wait();
+                    float r[16];
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) w[j] = __float_as_uint(__uint_as_float(w[j]) + __uint_as_float(wx[j]));
+                    for (int j = 0; j < 16; ++j)
+                        r[j] = fc_act(fmaf(__uint_as_float(w[j]) + __uint_as_float(wx[j]), a.inv_scale, s_bias[c0 + j]), a.act, s_slope[c0 + j]);
                     if (erow_ok) {
+                        if (n0 + c0 + 16 <= a.N && vec_ok) {          /* a whole group in range: four 16-byte stores */
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            const int o = n0 + c0 + j;
-                            if (o < a.N) yrow[c0 + j] = fc_act(fmaf(__uint_as_float(w[j]), a.inv_scale, a.bias[o]), a.act, a.slope ? a.slope[o] : 0.f);
-                            else if (o < a.n_store) yrow[c0 + j] = 0.f;
+                            for (int j = 0; j < 16; j += 4)
+                                *reinterpret_cast<float4*>(yrow + c0 + j) = make_float4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                const int o = n0 + c0 + j;
+                                if (o < a.N) yrow[c0 + j] = r[j];
+                                else if (o < a.n_store) yrow[c0 + j] = 0.f;
+                            }
                         }
                     }
                 }
