@@ -321,12 +321,11 @@ knn_select_kernel(const T* __restrict__ cand_d, const int* __restrict__ cand_i, 
             const int i = si[c];
             if (d < bd || (d == bd && i < bi)) { bd = d; bi = i; bc = c; }
         }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            const T od = __shfl_xor_sync(0xffffffffu, bd, off);
-            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-            const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
-            if (od < bd || (od == bd && oi < bi)) { bd = od; bi = oi; bc = oc; }
+        {
+            const int w = warp_argmin(bd, bi, bi != INT_MAX);   /* an entry with id INT_MAX is an empty slot */
+            bd = __shfl_sync(0xffffffffu, bd, w < 0 ? 0 : w);
+            bi = w < 0 ? INT_MAX : __shfl_sync(0xffffffffu, bi, w);
+            bc = w < 0 ? -1 : __shfl_sync(0xffffffffu, bc, w);
         }
         if (bi == INT_MAX) have_k = false; else d_kth = bd;
         if (lane == 0) {
@@ -437,12 +436,11 @@ __device__ void fb_block_topk(float* s_d, int* s_i, int n, int k, float* out_d, 
             const int i = s_i[c];
             if (i != INT_MAX && (bc < 0 || d < bd || (d == bd && i < bi))) { bd = d; bi = i; bc = c; }
         }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            const float od = __shfl_xor_sync(0xffffffffu, bd, off);
-            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-            const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
-            if (oc >= 0 && (bc < 0 || od < bd || (od == bd && oi < bi))) { bd = od; bi = oi; bc = oc; }
+        {
+            const int w = warp_argmin(bd, bi, bc >= 0);     /* lane holding the smallest (key, id), -1: none */
+            bd = __shfl_sync(0xffffffffu, bd, w < 0 ? 0 : w);
+            bi = __shfl_sync(0xffffffffu, bi, w < 0 ? 0 : w);
+            bc = w < 0 ? -1 : __shfl_sync(0xffffffffu, bc, w);
         }
         if (lane == 0) {
             out_d[r] = bc >= 0 ? bd : INFINITY;

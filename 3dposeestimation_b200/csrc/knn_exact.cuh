@@ -1,5 +1,6 @@
 /* knn_exact.cuh - the matcher's exact fp32 distance, shared by the SIMT and the tensor candidate refinement. */
 #pragma once
+#include <climits>
 
 namespace pe {
 
@@ -28,6 +29,21 @@ __device__ __forceinline__ float exact_l2(const float* __restrict__ a, const flo
     const float s = __fadd_rn(__fadd_rn(__fadd_rn(acc[0], acc[4]), __fadd_rn(acc[2], acc[6])),
                               __fadd_rn(__fadd_rn(acc[1], acc[5]), __fadd_rn(acc[3], acc[7])));
     return __fsqrt_rn(s);
+}
+
+/* Warp-wide arg-min of (key, id) with distinct ids: returns the lane that holds the smallest pair, -1 when no lane has one.
+ * Two redux.sync and a ballot instead of fifteen shuffle steps over three registers.  Float keys compare as floats
+ * (-0 = +0: canonicalised before the order-preserving integer map). */
+__device__ __forceinline__ int warp_argmin(int key, int id, bool has) {
+    const int ko = has ? key : INT_MAX;
+    const int kmin = __reduce_min_sync(0xffffffffu, ko);
+    const int imin = __reduce_min_sync(0xffffffffu, (has && ko == kmin) ? id : INT_MAX);
+    const unsigned win = __ballot_sync(0xffffffffu, has && ko == kmin && id == imin);
+    return win ? __ffs(win) - 1 : -1;
+}
+__device__ __forceinline__ int warp_argmin(float key, int id, bool has) {
+    const int b = __float_as_int(key + 0.0f);
+    return warp_argmin(b ^ ((b >> 31) & 0x7FFFFFFF), id, has);
 }
 
 }  // namespace pe

@@ -701,6 +701,7 @@ knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ c
     /* extraction in ascending (key, id) order: rounds 0 .. n_sel - 1 are re-ranked, the certificate also wants the
      * kc-th smallest key (K*) and the first key that is NOT re-ranked */
     float key_kstar = INFINITY, key_next = INFINITY;
+    int my_blk = 0, n_rerank = 0;                           /* lane r keeps the block of round r (n_sel <= 18) */
     const int rounds = flag ? (n_sel + 1 > kc ? n_sel + 1 : kc) : n_sel;
     for (int r = 0; r < rounds; ++r) {
         float bd = INFINITY;
@@ -710,32 +711,40 @@ knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ c
             const int i = si[c];
             if (i != INT_MAX && (d < bd || (d == bd && i < bi) || bc < 0)) { bd = d; bi = i; bc = c; }
         }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            const float od = __shfl_xor_sync(0xffffffffu, bd, off);
-            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-            const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
-            if (oc >= 0 && (bc < 0 || od < bd || (od == bd && oi < bi))) { bd = od; bi = oi; bc = oc; }
+        {
+            const int w = warp_argmin(bd, bi, bc >= 0);     /* lane holding the smallest (key, id), -1: none */
+            bd = __shfl_sync(0xffffffffu, bd, w < 0 ? 0 : w);
+            bi = __shfl_sync(0xffffffffu, bi, w < 0 ? 0 : w);
+            bc = w < 0 ? -1 : __shfl_sync(0xffffffffu, bc, w);
         }
         if (bc < 0) break;                                  /* no candidate left (warp-uniform) */
         if (r == kc - 1) key_kstar = bd;
         if (r == n_sel) key_next = bd;
         if (r < n_sel) {
-            float d = INFINITY;
-            int idx = INT_MAX;
+            /* the block's 32 rows are re-ranked after the extraction rounds; their lines are requested now, so the
+             * n_sel gathers (random rows of the DB) overlap instead of queueing behind one another */
+            if (lane == r) my_blk = bi;
             const long long row = (long long)bi * kTcBlock + lane;
             if (row < t_local) {
-                d = exact_l2(sq, db + (size_t)row * dp, dp);
-                idx = (int)row;
+                const char* p = reinterpret_cast<const char*>(db + (size_t)row * dp);
+                for (int b = 0; b < dp * 4; b += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + b));
             }
-            ed[r * kTcBlock + lane] = d;
-            ei[r * kTcBlock + lane] = idx;
+            n_rerank = r + 1;
         }
         __syncwarp();
         if (lane == 0) si[bc] = INT_MAX;
         __syncwarp();
         if (r >= n_sel && r >= kc - 1) break;
     }
+    for (int r = 0; r < n_rerank; ++r) {
+        const int blk = __shfl_sync(0xffffffffu, my_blk, r);
+        const long long row = (long long)blk * kTcBlock + lane;
+        if (row < t_local) {
+            ed[r * kTcBlock + lane] = exact_l2(sq, db + (size_t)row * dp, dp);
+            ei[r * kTcBlock + lane] = (int)row;
+        }
+    }
+    __syncwarp();
     float d_kth = INFINITY;
     bool have_k = true;
     for (int r = 0; r < k; ++r) {
@@ -746,12 +755,11 @@ knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ c
             const int i = ei[c];
             if (i != INT_MAX && (bc < 0 || d < bd || (d == bd && i < bi))) { bd = d; bi = i; bc = c; }
         }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            const float od = __shfl_xor_sync(0xffffffffu, bd, off);
-            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-            const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
-            if (oc >= 0 && (bc < 0 || od < bd || (od == bd && oi < bi))) { bd = od; bi = oi; bc = oc; }
+        {
+            const int w = warp_argmin(bd, bi, bc >= 0);     /* lane holding the smallest (key, id), -1: none */
+            bd = __shfl_sync(0xffffffffu, bd, w < 0 ? 0 : w);
+            bi = __shfl_sync(0xffffffffu, bi, w < 0 ? 0 : w);
+            bc = w < 0 ? -1 : __shfl_sync(0xffffffffu, bc, w);
         }
         if (bc >= 0) d_kth = bd; else have_k = false;
         if (lane == 0) {
@@ -811,12 +819,11 @@ knn_tc_select_hamming_kernel(const float* __restrict__ cand_d, const int* __rest
             const int i = si[c];
             if (i != INT_MAX && (bc < 0 || d < bd || (d == bd && i < bi))) { bd = d; bi = i; bc = c; }
         }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            const float od = __shfl_xor_sync(0xffffffffu, bd, off);
-            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-            const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
-            if (oc >= 0 && (bc < 0 || od < bd || (od == bd && oi < bi))) { bd = od; bi = oi; bc = oc; }
+        {
+            const int w = warp_argmin(bd, bi, bc >= 0);     /* lane holding the smallest (key, id), -1: none */
+            bd = __shfl_sync(0xffffffffu, bd, w < 0 ? 0 : w);
+            bi = __shfl_sync(0xffffffffu, bi, w < 0 ? 0 : w);
+            bc = w < 0 ? -1 : __shfl_sync(0xffffffffu, bc, w);
         }
         int d = INT_MAX, idx = INT_MAX;
         if (bc >= 0) {
@@ -839,12 +846,11 @@ knn_tc_select_hamming_kernel(const float* __restrict__ cand_d, const int* __rest
             const int d = ed[c], i = ei[c];
             if (i != INT_MAX && (bc < 0 || d < bd || (d == bd && i < bi))) { bd = d; bi = i; bc = c; }
         }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            const int od = __shfl_xor_sync(0xffffffffu, bd, off);
-            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-            const int oc = __shfl_xor_sync(0xffffffffu, bc, off);
-            if (oc >= 0 && (bc < 0 || od < bd || (od == bd && oi < bi))) { bd = od; bi = oi; bc = oc; }
+        {
+            const int w = warp_argmin(bd, bi, bc >= 0);     /* lane holding the smallest (key, id), -1: none */
+            bd = __shfl_sync(0xffffffffu, bd, w < 0 ? 0 : w);
+            bi = __shfl_sync(0xffffffffu, bi, w < 0 ? 0 : w);
+            bc = w < 0 ? -1 : __shfl_sync(0xffffffffu, bc, w);
         }
         if (lane == 0) {
             out_idx[(size_t)qi * k + r] = bc >= 0 ? (int)(bi + row_offset) : -1;
