@@ -727,7 +727,7 @@ knn_tc_select_kernel(const float* __restrict__ cand_d, const int* __restrict__ c
             const long long row = (long long)bi * kTcBlock + lane;
             if (row < t_local) {
                 const char* p = reinterpret_cast<const char*>(db + (size_t)row * dp);
-                for (int b = 0; b < dp * 4; b += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + b));
+                for (int b = 0; b < dp * 4; b += 128) asm volatile("prefetch.L2 [%0];" ::"l"(p + b));
             }
             n_rerank = r + 1;
         }
